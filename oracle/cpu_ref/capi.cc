@@ -1,0 +1,113 @@
+// capi.cc — flat C entry points over the CPU oracle so tests/bench can drive it with ctypes.
+// TEST INFRASTRUCTURE: never linked into, or called from, the product library.
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "cvprim.h"
+#include "orb_ref.h"
+
+using namespace orbref;
+
+extern "C" {
+
+void* orbref_create(int nf, float sf, int nl, int ini, int mn) { return new OrbExtractorRef(nf, sf, nl, ini, mn); }
+void orbref_destroy(void* h) { delete (OrbExtractorRef*)h; }
+void orbref_set_tie_rule(void* h, int rule) { ((OrbExtractorRef*)h)->pointerTieRule = rule; }
+
+void orbref_tables(void* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2, int* per_level, int* umax) {
+    OrbExtractorRef* e = (OrbExtractorRef*)h;
+    for (int i = 0; i < e->nlevels; ++i) {
+        scale[i] = e->mvScaleFactor[i];
+        inv_scale[i] = e->mvInvScaleFactor[i];
+        sigma2[i] = e->mvLevelSigma2[i];
+        inv_sigma2[i] = e->mvInvLevelSigma2[i];
+        per_level[i] = e->mnFeaturesPerLevel[i];
+    }
+    for (int i = 0; i < 16; ++i) umax[i] = e->umax[i];
+}
+
+// Returns monoIndex (>= 0) or -1 (empty image) or -2 (cap too small); *n_out = keypoint count.
+int orbref_extract(void* h, const uint8_t* img, int w, int hgt, long stride, int lap0, int lap1, KeyPoint* kps,
+                   uint8_t* desc, int cap, int* n_out) {
+    OrbExtractorRef* e = (OrbExtractorRef*)h;
+    std::vector<KeyPoint> k;
+    std::vector<uint8_t> d;
+    int mono = e->extract(img, w, hgt, stride, lap0, lap1, k, d);
+    if (mono < 0) return mono;
+    *n_out = (int)k.size();
+    if ((int)k.size() > cap) return -2;
+    if (!k.empty()) {
+        std::memcpy(kps, k.data(), k.size() * sizeof(KeyPoint));
+        std::memcpy(desc, d.data(), d.size());
+    }
+    return mono;
+}
+
+int orbref_level_size(void* h, int level, int* w, int* hgt) {
+    OrbExtractorRef* e = (OrbExtractorRef*)h;
+    if (level < 0 || level >= e->nlevels) return -1;
+    *w = e->pyramid[level].w;
+    *hgt = e->pyramid[level].h;
+    return 0;
+}
+// dst: dense (h+38) x (w+38) bordered level.
+int orbref_get_level(void* h, int level, uint8_t* dst) {
+    OrbExtractorRef* e = (OrbExtractorRef*)h;
+    if (level < 0 || level >= e->nlevels) return -1;
+    std::memcpy(dst, e->pyramid[level].buf.data(), e->pyramid[level].buf.size());
+    return 0;
+}
+// FAST candidates of a level in reference push order, as (x, y, response) float triples.
+int orbref_get_candidates(void* h, int level, float* xyr, int cap) {
+    OrbExtractorRef* e = (OrbExtractorRef*)h;
+    if (level < 0 || level >= (int)e->candidates.size()) return -1;
+    const auto& c = e->candidates[level];
+    int n = (int)c.size() < cap ? (int)c.size() : cap;
+    for (int i = 0; i < n; ++i) { xyr[3 * i] = c[i].x; xyr[3 * i + 1] = c[i].y; xyr[3 * i + 2] = c[i].response; }
+    return (int)c.size();
+}
+
+// ---- primitives (for the cv2 known-answer tests)
+void orbref_resize(const uint8_t* s, int sw, int sh, long ss, uint8_t* d, int dw, int dh, long ds) {
+    resizeLinearU8(s, sw, sh, ss, d, dw, dh, ds);
+}
+void orbref_border101(uint8_t* buf, int w, int h, int b, long step) { fillBorderReflect101(buf, w, h, b, step); }
+int orbref_fast(const uint8_t* img, int w, int h, long step, int t, int* xys, int cap) {
+    std::vector<FastKp> k;
+    fast9_16(img, w, h, step, t, k);
+    int n = (int)k.size() < cap ? (int)k.size() : cap;
+    for (int i = 0; i < n; ++i) { xys[3 * i] = k[i].x; xys[3 * i + 1] = k[i].y; xys[3 * i + 2] = k[i].score; }
+    return (int)k.size();
+}
+void orbref_blur(const uint8_t* s, int w, int h, long ss, uint8_t* d, long ds) { gaussianBlur7x7(s, w, h, ss, d, ds); }
+float orbref_fast_atan2(float y, float x) { return fastAtan2(y, x); }
+void orbref_knn2(const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx, int32_t* dist) {
+    knn2Hamming(q, nq, t, nt, idx, dist);
+}
+int orbref_hamming(const uint8_t* a, const uint8_t* b) { return hammingDistance256(a, b); }
+
+// ---- timed CPU baseline: extract `nframes` frames (dense w x h each) on `nthreads` host threads,
+// one extractor instance per thread (the reference runs one instance per image thread,
+// Frame.cc:119-122).  Returns total keypoints so the work cannot be optimised away.
+long orbref_extract_many(int nf, float sf, int nl, int ini, int mn, const uint8_t* frames, int nframes, int w, int h,
+                         int lap0, int lap1, int nthreads) {
+    std::vector<long> counts(nthreads, 0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t)
+        th.emplace_back([&, t]() {
+            OrbExtractorRef e(nf, sf, nl, ini, mn);
+            std::vector<KeyPoint> k;
+            std::vector<uint8_t> d;
+            for (int f = t; f < nframes; f += nthreads) {
+                e.extract(frames + (size_t)f * w * h, w, h, w, lap0, lap1, k, d);
+                counts[t] += (long)k.size();
+            }
+        });
+    for (auto& x : th) x.join();
+    long total = 0;
+    for (long c : counts) total += c;
+    return total;
+}
+
+}  // extern "C"
