@@ -1,0 +1,66 @@
+"""In-tree builds: the CUDA product library (nvcc, sm_100a), the synthetic-frame generator (gcc) and,
+for the checker only, the CPU oracle (make -C oracle).  Nothing here needs a GPU."""
+import glob
+import os
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+LIB = os.path.join(CSRC, "liborbfe.so")
+SYNTH = os.path.join(CSRC, "liborbfe_synth.so")
+ORACLE = os.path.join(ROOT, "oracle", "_build", "liborbref.so")
+
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17", "-Xcompiler", "-fPIC",
+              "-shared"]
+
+
+def _newer(target, sources):
+    if not os.path.exists(target):
+        return False
+    t = os.path.getmtime(target)
+    return all(os.path.getmtime(s) <= t for s in sources)
+
+
+def _run(cmd, **kw):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, **kw)
+    if r.returncode != 0:
+        sys.stderr.write(r.stdout)
+        raise RuntimeError("build failed: " + " ".join(cmd))
+    return r.stdout
+
+
+def build_cuda(force=False):
+    srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
+    deps = srcs + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.inc")) + \
+        glob.glob(os.path.join(ROOT, "include", "*.h"))
+    if not force and _newer(LIB, deps):
+        return LIB
+    nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
+    _run([nvcc] + NVCC_FLAGS + ["-o", LIB] + srcs)
+    return LIB
+
+
+def build_synth(force=False):
+    src = os.path.join(CSRC, "synth.c")
+    if not force and _newer(SYNTH, [src]):
+        return SYNTH
+    _run(["gcc", "-O2", "-shared", "-fPIC", "-o", SYNTH, src])
+    return SYNTH
+
+
+def build_oracle(force=False):
+    srcs = glob.glob(os.path.join(ROOT, "oracle", "cpu_ref", "*")) + [os.path.join(CSRC, "orb_pattern.inc")]
+    if not force and _newer(ORACLE, srcs):
+        return ORACLE
+    _run(["make", "-C", os.path.join(ROOT, "oracle")] + (["-B"] if force else []))
+    return ORACLE
+
+
+def build_all(force=False):
+    return build_cuda(force), build_synth(force), build_oracle(force)
+
+
+if __name__ == "__main__":
+    print(build_all(force="--force" in sys.argv))

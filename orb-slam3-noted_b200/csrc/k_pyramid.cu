@@ -1,0 +1,83 @@
+// k_pyramid.cu — image pyramid: ORBextractor::ComputePyramid (ORBextractor.cc:1152-1177).
+//
+// Level 0 is the input with a 19-px reflect-101 border; level l > 0 is the OpenCV 8-bit bilinear
+// resize (11-bit fixed-point taps, see ResizeTap) of level l-1's ROI, again with the border.  A
+// border pixel equals the ROI pixel at the reflected coordinate, so every thread simply evaluates
+// the level function at reflect101(x), reflect101(y): one kernel writes ROI and border together
+// and the level never has to be re-read to make its border.
+//
+// Layout: each level lives in a bordered buffer whose ROI column 0 sits at byte ORBFE_XO (32) of a
+// 128-byte-multiple pitch, so ROI words are 4-byte aligned for the uchar4 stores below.  One thread
+// produces one 32-bit word (4 pixels) of a bordered row; blockIdx.y = row, blockIdx.z = frame.
+#include "orbfe_internal.h"
+
+__device__ __forceinline__ int reflect101(int i, int n) {
+    // valid for -n < i < 2n-1, which the 19-px border guarantees for every level with n >= 20
+    i = i < 0 ? -i : i;
+    return i >= n ? 2 * n - 2 - i : i;
+}
+
+__global__ void __launch_bounds__(128) k_pyr_level0(const uint8_t* __restrict__ in, long long stride,
+                                                    long long frameStride, uint8_t* __restrict__ out, LevelGeom g) {
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int row = blockIdx.y;
+    if (word * 4 >= g.pitch) return;
+    const int y = reflect101(row - ORBFE_EDGE, g.h);
+    const uint8_t* src = in + (long long)blockIdx.z * frameStride + (long long)y * stride;
+    const int x0 = word * 4 - ORBFE_XO;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = x0 + k;
+        if (x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE) v |= (uint32_t)__ldg(src + reflect101(x, g.w)) << (8 * k);
+    }
+    uint8_t* dst = out + g.base + (long long)blockIdx.z * g.plane + (long long)row * g.pitch;
+    reinterpret_cast<uint32_t*>(dst)[word] = v;
+}
+
+// gs = source level geometry, gd = destination level geometry.
+__global__ void __launch_bounds__(128) k_pyr_resize(uint8_t* __restrict__ pyr, LevelGeom gs, LevelGeom gd,
+                                                    const ResizeTap* __restrict__ taps) {
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int row = blockIdx.y;
+    if (word * 4 >= gd.pitch) return;
+    const int y = reflect101(row - ORBFE_EDGE, gd.h);
+    const ResizeTap ty = taps[gd.tabY + y];
+    const uint8_t* sbase = pyr + gs.base + (long long)blockIdx.z * gs.plane + (long long)ORBFE_EDGE * gs.pitch + ORBFE_XO;
+    const uint8_t* S0 = sbase + (long long)ty.s0 * gs.pitch;
+    const uint8_t* S1 = sbase + (long long)ty.s1 * gs.pitch;
+    const int x0 = word * 4 - ORBFE_XO;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = x0 + k;
+        if (x >= -ORBFE_EDGE && x < gd.w + ORBFE_EDGE) {
+            const ResizeTap tx = taps[gd.tabX + reflect101(x, gd.w)];
+            const int r0 = (int)S0[tx.s0] * tx.a0 + (int)S0[tx.s1] * tx.a1;
+            const int r1 = (int)S1[tx.s0] * tx.a0 + (int)S1[tx.s1] * tx.a1;
+            const int o = ((((int)ty.a0 * (r0 >> 4)) >> 16) + (((int)ty.a1 * (r1 >> 4)) >> 16) + 2) >> 2;
+            v |= (uint32_t)(o & 0xFF) << (8 * k);
+        }
+    }
+    uint8_t* dst = pyr + gd.base + (long long)blockIdx.z * gd.plane + (long long)row * gd.pitch;
+    reinterpret_cast<uint32_t*>(dst)[word] = v;
+}
+
+cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int batch, int width, int height,
+                                 long long stride, long long frameStride) {
+    (void)width; (void)height;
+    const int nl = h->p.nlevels;
+    {
+        const LevelGeom& g = h->geom[0];
+        dim3 grid((g.pitch / 4 + 127) / 128, g.rows, batch);
+        k_pyr_level0<<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g);
+        h->launches++;
+    }
+    for (int l = 1; l < nl; ++l) {
+        const LevelGeom& gd = h->geom[l];
+        dim3 grid((gd.pitch / 4 + 127) / 128, gd.rows, batch);
+        k_pyr_resize<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps);
+        h->launches++;
+    }
+    return cudaGetLastError();
+}

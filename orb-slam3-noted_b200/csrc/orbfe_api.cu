@@ -1,0 +1,456 @@
+// orbfe_api.cu — the C ABI (include/orbfe.h): handle life cycle, per-shape geometry, the extract
+// entry points and the result / pyramid taps.  Host side of the hot path; all pixel work is in the
+// k_*.cu kernels.  There is no CPU fallback: without a CUDA device every call returns an error.
+#include <math.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <mutex>
+#include <vector>
+
+#include "orbfe_internal.h"
+
+static thread_local char g_cudaErr[256] = "";
+
+static int cuda_fail(cudaError_t e, const char* what) {
+    snprintf(g_cudaErr, sizeof(g_cudaErr), "%s: %s", what, cudaGetErrorString(e));
+    return ORBFE_ERR_CUDA;
+}
+#define CK(call)                                             \
+    do {                                                     \
+        cudaError_t e_ = (call);                             \
+        if (e_ != cudaSuccess) return cuda_fail(e_, #call);  \
+    } while (0)
+
+static inline int cvRoundF(float v) { return (int)lrintf(v); }   // half-to-even
+
+// ---- reference tables, ORBextractor.cc:413-444 ----------------------------------------------------
+static void build_tables(orbfe_handle* h) {
+    const int nl = h->p.nlevels;
+    const double sf = (double)h->p.scale_factor;   // the member is a double assigned from a float
+    h->scale[0] = 1.0f;
+    h->sigma2[0] = 1.0f;
+    for (int i = 1; i < nl; i++) {
+        h->scale[i] = (float)(h->scale[i - 1] * sf);
+        h->sigma2[i] = h->scale[i] * h->scale[i];
+    }
+    for (int i = 0; i < nl; i++) {
+        h->invScale[i] = 1.0f / h->scale[i];
+        h->invSigma2[i] = 1.0f / h->sigma2[i];
+    }
+    const float factor = (float)(1.0f / sf);
+    float nDesired = h->p.nfeatures * (1 - factor) / (1 - (float)pow((double)factor, (double)nl));
+    int sum = 0;
+    for (int l = 0; l < nl - 1; l++) {
+        h->featPerLevel[l] = cvRoundF(nDesired);
+        sum += h->featPerLevel[l];
+        nDesired *= factor;
+    }
+    h->featPerLevel[nl - 1] = std::max(h->p.nfeatures - sum, 0);
+}
+
+// OpenCV resize(INTER_LINEAR) taps for one axis (src n -> dst m).  clampFrac: the x axis zeroes the
+// fraction at the clamped ends, the y axis only clamps the row index.
+static void build_taps(int n, int m, bool clampFrac, ResizeTap* out) {
+    const double scale = 1. / ((double)m / n);
+    for (int d = 0; d < m; ++d) {
+        float f = (float)((d + 0.5) * scale - 0.5);
+        int s = (int)floorf(f);
+        f -= s;
+        if (clampFrac) {
+            if (s < 0) { f = 0; s = 0; }
+            if (s >= n - 1) { f = 0; s = n - 1; }
+        }
+        ResizeTap t;
+        t.s0 = (short)std::min(std::max(s, 0), n - 1);
+        t.s1 = (short)std::min(std::max(s + 1, 0), n - 1);
+        t.a0 = (short)cvRoundF((1.f - f) * 2048.f);
+        t.a1 = (short)cvRoundF(f * 2048.f);
+        out[d] = t;
+    }
+}
+
+struct ShapePlan {
+    LevelGeom geom[ORBFE_MAX_LEVELS];
+    std::vector<CellDesc> cells;
+    std::vector<ResizeTap> taps;
+    size_t pyrBytesPerFrame = 0;
+    long long candPerFrame = 0;
+    int kpPerFrame = 0;
+    int maxCellBytes = 0;
+    int status = ORBFE_OK;
+};
+
+// Geometry for one image shape: level sizes (ORBextractor.cc:1156-1157), FAST grid (:771-805),
+// quadtree roots (:541-543), arena offsets.  Pure host arithmetic.
+static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
+    const int nl = h->p.nlevels;
+    long long pyrOff = 0, candOff = 0;
+    int kpOff = 0, tapOff = 0;
+    for (int l = 0; l < nl; ++l) {
+        LevelGeom& g = sp.geom[l];
+        memset(&g, 0, sizeof(g));
+        g.w = cvRoundF((float)W * h->invScale[l]);
+        g.h = cvRoundF((float)H * h->invScale[l]);
+        g.maxBX = g.w - ORBFE_EDGE + 3;
+        g.maxBY = g.h - ORBFE_EDGE + 3;
+        const float width = (float)(g.maxBX - ORBFE_MIN_BORDER), height = (float)(g.maxBY - ORBFE_MIN_BORDER);
+        g.nCols = (int)(width / 35.f);
+        g.nRows = (int)(height / 35.f);
+        if (g.w < 64 || g.h < 64 || g.nCols < 1 || g.nRows < 1 || g.w > 2047 + ORBFE_MIN_BORDER || g.h > 2047 + ORBFE_MIN_BORDER) {
+            sp.status = ORBFE_ERR_TOO_LARGE;   // level too small for a FAST cell / too large for the packed coordinates
+            return;
+        }
+        g.wCell = (int)ceilf(width / g.nCols);
+        g.hCell = (int)ceilf(height / g.nRows);
+        if (g.wCell + 3 > 127 || g.hCell + 3 > 127) { sp.status = ORBFE_ERR_TOO_LARGE; return; }
+        g.pitch = (ORBFE_XO + g.w + ORBFE_EDGE + 127) & ~127;
+        g.rows = g.h + 2 * ORBFE_EDGE;
+        g.plane = (long long)g.pitch * g.rows;
+        g.base = pyrOff;   // frame stride applied later (needs batch): base = pyrOff * maxBatch
+        pyrOff += g.plane;
+        g.nfeat = h->featPerLevel[l];
+        g.nIni = (int)roundf((float)(g.maxBX - ORBFE_MIN_BORDER) / (g.maxBY - ORBFE_MIN_BORDER));
+        if (g.nIni < 1) { sp.status = ORBFE_ERR_TOO_LARGE; return; }
+        g.hX = (float)(g.maxBX - ORBFE_MIN_BORDER) / g.nIni;
+        g.scale = h->scale[l];
+        g.size = (float)(int)(31 * h->scale[l]);
+        g.kpCap = std::max(g.nfeat, 4 * g.nIni) + 3;
+        if (g.kpCap > ORBFE_MAX_NODES) { sp.status = ORBFE_ERR_TOO_LARGE; return; }
+        g.kpCap = (g.kpCap + 3) & ~3;
+        g.kpBase = kpOff;
+        kpOff += g.kpCap;
+        // cells, in the reference's loop order
+        g.cellBase = (int)sp.cells.size();
+        int cap = 0;
+        for (int i = 0; i < g.nRows; i++) {
+            const int iniY = ORBFE_MIN_BORDER + i * g.hCell;
+            int maxY = iniY + g.hCell + 6;
+            if (iniY >= g.maxBY - 3) continue;
+            if (maxY > g.maxBY) maxY = g.maxBY;
+            for (int j = 0; j < g.nCols; j++) {
+                const int iniX = ORBFE_MIN_BORDER + j * g.wCell;
+                int maxX = iniX + g.wCell + 6;
+                if (iniX >= g.maxBX - 6) continue;
+                if (maxX > g.maxBX) maxX = g.maxBX;
+                CellDesc c;
+                c.level = (short)l; c.x0 = (short)iniX; c.y0 = (short)iniY;
+                c.cw = (short)(maxX - iniX); c.ch = (short)(maxY - iniY);
+                c.ox = (short)(j * g.wCell); c.oy = (short)(i * g.hCell); c.pad = 0;
+                const int tw = c.cw - 6, th = c.ch - 6;
+                if (tw <= 0 || th <= 0) continue;   // FAST on a < 7 px ROI finds nothing
+                sp.cells.push_back(c);
+                const int keptCap = ((tw + 1) / 2) * ((th + 1) / 2);
+                cap += keptCap;
+                const int tp = (c.cw + 3) & ~3;
+                const int bytes = 2 * tp * c.ch + 2 * ((tw * th + 1) & ~1) + 4 * keptCap + 16;
+                sp.maxCellBytes = std::max(sp.maxCellBytes, bytes);
+            }
+        }
+        g.nCells = (int)sp.cells.size() - g.cellBase;
+        g.candCap = (cap + 3) & ~3;
+        g.candBase = candOff;
+        candOff += g.candCap;
+        // resize taps (level l from level l-1)
+        g.tabX = tapOff;
+        g.tabY = tapOff + g.w;
+        tapOff += g.w + g.h;
+        sp.taps.resize(tapOff);
+        if (l > 0) {
+            build_taps(sp.geom[l - 1].w, g.w, true, &sp.taps[g.tabX]);
+            build_taps(sp.geom[l - 1].h, g.h, false, &sp.taps[g.tabY]);
+        }
+    }
+    sp.pyrBytesPerFrame = (size_t)pyrOff;
+    sp.candPerFrame = candOff;
+    sp.kpPerFrame = kpOff;
+}
+
+// ---- handle life cycle ---------------------------------------------------------------------------
+static void free_handle(orbfe_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->device);
+    cudaFree(h->dIn); cudaFree(h->dPyr); cudaFree(h->dCand); cudaFree(h->dNodeOf); cudaFree(h->dCandCount);
+    cudaFree(h->dLvlKp); cudaFree(h->dLvlCount); cudaFree(h->dGeom); cudaFree(h->dCells); cudaFree(h->dTaps);
+    cudaFree(h->dKps); cudaFree(h->dDesc); cudaFree(h->dSlot); cudaFree(h->dN); cudaFree(h->dMono);
+    if (h->hN) cudaFreeHost(h->hN);
+    if (h->hMono) cudaFreeHost(h->hMono);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+}
+
+// Upload the geometry of a new image shape (no-op when the shape is unchanged).
+static int configure_shape(orbfe_handle* h, int W, int H) {
+    if (W == h->curW && H == h->curH) return ORBFE_OK;
+    if (W > h->p.max_width || H > h->p.max_height) return ORBFE_ERR_TOO_LARGE;
+    ShapePlan sp;
+    plan_shape(h, W, H, sp);
+    if (sp.status != ORBFE_OK) return sp.status;
+    const size_t B = (size_t)h->p.max_batch;
+    if (sp.pyrBytesPerFrame * B > h->pyrBytes || (size_t)sp.candPerFrame * B > h->candEntries ||
+        (int)sp.cells.size() > h->cellCap || (int)sp.taps.size() > h->tabCap || sp.kpPerFrame > h->kpCapPerFrame)
+        return ORBFE_ERR_TOO_LARGE;
+    for (int l = 0; l < h->p.nlevels; ++l) {
+        h->geom[l] = sp.geom[l];
+        h->geom[l].base = sp.geom[l].base * (long long)B;
+    }
+    h->nCellsTotal = (int)sp.cells.size();
+    h->maxCellBytes = sp.maxCellBytes;
+    h->candPerFrame = sp.candPerFrame;
+    h->kpPerFrame = sp.kpPerFrame;
+    CK(cudaStreamSynchronize(h->stream));   // previous work may still read the old tables
+    CK(cudaMemcpyAsync(h->dGeom, h->geom, sizeof(LevelGeom) * h->p.nlevels, cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->dCells, sp.cells.data(), sizeof(CellDesc) * sp.cells.size(), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->dTaps, sp.taps.data(), sizeof(ResizeTap) * sp.taps.size(), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaStreamSynchronize(h->stream));   // sp's vectors die at return
+    h->curW = W;
+    h->curH = H;
+    h->lastBatch = 0;
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
+    if (!params || !out) return ORBFE_ERR_BAD_ARGUMENT;
+    *out = nullptr;
+    const orbfe_params& p = *params;
+    if (p.nfeatures < 1 || p.nlevels < 1 || p.nlevels > ORBFE_MAX_LEVELS || !(p.scale_factor > 1.0f) || p.ini_th_fast < 1 ||
+        p.min_th_fast < 1 || p.ini_th_fast > 254 || p.min_th_fast > 254 || p.max_width < 1 || p.max_height < 1 || p.max_batch < 1)
+        return ORBFE_ERR_BAD_ARGUMENT;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { cudaGetLastError(); return ORBFE_ERR_NO_DEVICE; }
+    if (p.device < 0 || p.device >= ndev) return ORBFE_ERR_BAD_ARGUMENT;
+    orbfe_handle* h = new orbfe_handle();
+    memset(h, 0, sizeof(*h));
+    h->p = p;
+    h->device = p.device;
+    build_tables(h);
+    ShapePlan sp;
+    plan_shape(h, p.max_width, p.max_height, sp);
+    if (sp.status != ORBFE_OK) { delete h; return sp.status; }
+    const size_t B = (size_t)p.max_batch;
+    // a little slack so that smaller shapes whose rounding goes the other way still fit
+    h->pyrBytes = sp.pyrBytesPerFrame * B + 4096;
+    h->candEntries = ((size_t)sp.candPerFrame + 256) * B;
+    h->cellCap = (int)sp.cells.size() + 64;
+    h->tabCap = (int)sp.taps.size() + 64;
+    h->kpCapPerFrame = sp.kpPerFrame + 16 * p.nlevels;
+    h->inBytes = (size_t)p.max_width * p.max_height * B;
+#define CKC(call)                                                              \
+    do {                                                                       \
+        cudaError_t e_ = (call);                                               \
+        if (e_ != cudaSuccess) { cuda_fail(e_, #call); free_handle(h); return ORBFE_ERR_CUDA; } \
+    } while (0)
+    CKC(cudaSetDevice(h->device));
+    CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CKC(cudaMalloc(&h->dIn, h->inBytes));
+    CKC(cudaMalloc(&h->dPyr, h->pyrBytes));
+    CKC(cudaMalloc(&h->dCand, h->candEntries * 4));
+    CKC(cudaMalloc(&h->dNodeOf, h->candEntries * 4));
+    CKC(cudaMalloc(&h->dCandCount, sizeof(int) * B * ORBFE_MAX_LEVELS));
+    CKC(cudaMalloc(&h->dLvlKp, sizeof(uint32_t) * B * h->kpCapPerFrame));
+    CKC(cudaMalloc(&h->dLvlCount, sizeof(int) * B * ORBFE_MAX_LEVELS));
+    CKC(cudaMalloc(&h->dGeom, sizeof(LevelGeom) * ORBFE_MAX_LEVELS));
+    CKC(cudaMalloc(&h->dCells, sizeof(CellDesc) * h->cellCap));
+    CKC(cudaMalloc(&h->dTaps, sizeof(ResizeTap) * h->tabCap));
+    CKC(cudaMalloc(&h->dKps, sizeof(orbfe_keypoint) * B * h->kpCapPerFrame));
+    CKC(cudaMalloc(&h->dDesc, (size_t)32 * B * h->kpCapPerFrame));
+    CKC(cudaMalloc(&h->dSlot, sizeof(uint32_t) * B * h->kpCapPerFrame));
+    CKC(cudaMalloc(&h->dN, sizeof(int) * B));
+    CKC(cudaMalloc(&h->dMono, sizeof(int) * B));
+    CKC(cudaMallocHost(&h->hN, sizeof(int) * B));
+    CKC(cudaMallocHost(&h->hMono, sizeof(int) * B));
+    CKC(cudaMemset(h->dPyr, 0, h->pyrBytes));
+#undef CKC
+    *out = h;
+    return ORBFE_OK;
+}
+
+extern "C" void orbfe_destroy(orbfe_handle* h) { free_handle(h); }
+
+extern "C" int orbfe_get_tables(const orbfe_handle* h, float* scale, float* inv_scale, float* sigma2, float* inv_sigma2,
+                                int* features_per_level) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int l = 0; l < h->p.nlevels; ++l) {
+        if (scale) scale[l] = h->scale[l];
+        if (inv_scale) inv_scale[l] = h->invScale[l];
+        if (sigma2) sigma2[l] = h->sigma2[l];
+        if (inv_sigma2) inv_sigma2[l] = h->invSigma2[l];
+        if (features_per_level) features_per_level[l] = h->featPerLevel[l];
+    }
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_max_keypoints(const orbfe_handle* h) { return h ? h->kpCapPerFrame : ORBFE_ERR_BAD_ARGUMENT; }
+
+// ---- extraction -------------------------------------------------------------------------------------
+static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int batch, int W, int H, long long stride,
+                           long long frameStride, int lap0, int lap1) {
+    cudaError_t e;
+    if ((e = orbfe_launch_pyramid(h, dImages, batch, W, H, stride, frameStride)) != cudaSuccess) return cuda_fail(e, "pyramid");
+    if ((e = orbfe_launch_fast(h, batch)) != cudaSuccess) return cuda_fail(e, "fast");
+    if ((e = orbfe_launch_octree(h, batch)) != cudaSuccess) return cuda_fail(e, "octree");
+    if ((e = orbfe_launch_describe(h, batch, lap0, lap1)) != cudaSuccess) return cuda_fail(e, "describe");
+    h->lastBatch = batch;
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_extract_batch_device(orbfe_handle* h, const uint8_t* d_images, int batch, int width, int height,
+                                          ptrdiff_t stride, ptrdiff_t frame_stride, int lap0, int lap1) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    if (!d_images || width <= 0 || height <= 0 || batch <= 0) return ORBFE_ERR_EMPTY_IMAGE;
+    if (stride < width || batch > h->p.max_batch) return batch > h->p.max_batch ? ORBFE_ERR_TOO_LARGE : ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    int st = configure_shape(h, width, height);
+    if (st != ORBFE_OK) return st;
+    return enqueue_extract(h, d_images, batch, width, height, stride, frame_stride, lap0, lap1);
+}
+
+extern "C" int orbfe_fetch_results(orbfe_handle* h, int batch, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n_out,
+                                   int* mono_out) {
+    if (!h || !kps || !desc || !n_out || batch <= 0) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->lastBatch < batch) return ORBFE_ERR_NOT_READY;
+    CK(cudaSetDevice(h->device));
+    CK(cudaMemcpyAsync(h->hN, h->dN, sizeof(int) * batch, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaMemcpyAsync(h->hMono, h->dMono, sizeof(int) * batch, cudaMemcpyDeviceToHost, h->stream));
+    const int kpf = h->kpPerFrame;
+    if (cap >= kpf) {
+        // common case: one strided copy per array, rows of kpf entries into rows of cap entries
+        CK(cudaMemcpy2DAsync(kps, sizeof(orbfe_keypoint) * (size_t)cap, h->dKps, sizeof(orbfe_keypoint) * (size_t)kpf,
+                             sizeof(orbfe_keypoint) * (size_t)kpf, batch, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpy2DAsync(desc, 32 * (size_t)cap, h->dDesc, 32 * (size_t)kpf, 32 * (size_t)kpf, batch, cudaMemcpyDeviceToHost,
+                             h->stream));
+        CK(cudaStreamSynchronize(h->stream));
+        for (int b = 0; b < batch; ++b) { n_out[b] = h->hN[b]; if (mono_out) mono_out[b] = h->hMono[b]; }
+        return ORBFE_OK;
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    for (int b = 0; b < batch; ++b) {
+        n_out[b] = h->hN[b];
+        if (mono_out) mono_out[b] = h->hMono[b];
+        if (h->hN[b] > cap) return ORBFE_ERR_CAPACITY;
+    }
+    for (int b = 0; b < batch; ++b) {
+        const int n = h->hN[b];
+        if (n == 0) continue;
+        CK(cudaMemcpyAsync(kps + (size_t)b * cap, h->dKps + (size_t)b * kpf, sizeof(orbfe_keypoint) * n, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(desc + (size_t)b * cap * 32, h->dDesc + (size_t)b * kpf * 32, 32 * (size_t)n, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int batch, int width, int height, ptrdiff_t stride,
+                                   ptrdiff_t frame_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
+                                   int* n_out, int* mono_out) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    if (!images || width <= 0 || height <= 0 || batch <= 0) return ORBFE_ERR_EMPTY_IMAGE;
+    if (stride < width) return ORBFE_ERR_BAD_ARGUMENT;
+    if (batch > h->p.max_batch || width > h->p.max_width || height > h->p.max_height) return ORBFE_ERR_TOO_LARGE;
+    CK(cudaSetDevice(h->device));
+    int st = configure_shape(h, width, height);
+    if (st != ORBFE_OK) return st;
+    // stage the frames densely (row stride = width) in the input arena
+    if (stride == width && frame_stride == (ptrdiff_t)width * height) {
+        CK(cudaMemcpyAsync(h->dIn, images, (size_t)width * height * batch, cudaMemcpyHostToDevice, h->stream));
+    } else {
+        for (int b = 0; b < batch; ++b)
+            CK(cudaMemcpy2DAsync(h->dIn + (size_t)b * width * height, width, images + (size_t)b * frame_stride, stride, width, height,
+                                 cudaMemcpyHostToDevice, h->stream));
+    }
+    st = enqueue_extract(h, h->dIn, batch, width, height, width, (long long)width * height, lap0, lap1);
+    if (st != ORBFE_OK) return st;
+    return orbfe_fetch_results(h, batch, kps, desc, cap, n_out, mono_out);
+}
+
+extern "C" int orbfe_extract(orbfe_handle* h, const uint8_t* image, int width, int height, ptrdiff_t stride, int lap0, int lap1,
+                             orbfe_keypoint* kps, uint8_t* desc, int cap, int* n_out) {
+    int n = 0, mono = 0;
+    int st = orbfe_extract_batch(h, image, 1, width, height, stride, (ptrdiff_t)stride * height, lap0, lap1, kps, desc, cap, &n, &mono);
+    if (n_out) *n_out = n;
+    return st < 0 ? st : mono;
+}
+
+extern "C" int orbfe_device_results(orbfe_handle* h, const orbfe_keypoint** d_kps, const uint8_t** d_desc, const int** d_n,
+                                    const int** d_mono, int* cap) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->lastBatch <= 0) return ORBFE_ERR_NOT_READY;
+    if (d_kps) *d_kps = h->dKps;
+    if (d_desc) *d_desc = h->dDesc;
+    if (d_n) *d_n = h->dN;
+    if (d_mono) *d_mono = h->dMono;
+    if (cap) *cap = h->kpPerFrame;
+    return ORBFE_OK;
+}
+
+// ---- taps ---------------------------------------------------------------------------------------------
+extern "C" int orbfe_get_pyramid_level(orbfe_handle* h, int frame, int level, uint8_t* dst, ptrdiff_t dst_stride, int* w, int* hgt) {
+    if (!h || level < 0 || level >= h->p.nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->lastBatch <= 0) return ORBFE_ERR_NOT_READY;
+    if (frame < 0 || frame >= h->lastBatch) return ORBFE_ERR_BAD_ARGUMENT;
+    const LevelGeom& g = h->geom[level];
+    if (w) *w = g.w;
+    if (hgt) *hgt = g.h;
+    if (!dst) return ORBFE_OK;
+    const int bw = g.w + 2 * ORBFE_EDGE;
+    if (dst_stride < bw) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    const uint8_t* src = h->dPyr + g.base + (long long)frame * g.plane + (ORBFE_XO - ORBFE_EDGE);
+    CK(cudaMemcpy2DAsync(dst, dst_stride, src, g.pitch, bw, g.rows, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_get_candidates(orbfe_handle* h, int frame, int level, int32_t* xyr, int cap) {
+    if (!h || level < 0 || level >= h->p.nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->lastBatch <= 0) return ORBFE_ERR_NOT_READY;
+    if (frame < 0 || frame >= h->lastBatch) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    const LevelGeom& g = h->geom[level];
+    int n = 0;
+    CK(cudaMemcpyAsync(&n, h->dCandCount + frame * h->p.nlevels + level, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    if (n <= 0 || !xyr) return n;
+    std::vector<uint32_t> c((size_t)n);
+    CK(cudaMemcpyAsync(c.data(), h->dCand + (long long)frame * h->candPerFrame + g.candBase, sizeof(uint32_t) * n,
+                       cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    // restore the reference's push order: cell-row-major, then row-major inside the cell
+    auto key = [&](uint32_t v) {
+        const int x = ORBFE_CAND_X(v), y = ORBFE_CAND_Y(v);
+        const long long cj = (x - 3) / g.wCell, ci = (y - 3) / g.hCell;
+        return ((ci * g.nCols + cj) << 22) | ((long long)y << 11) | x;
+    };
+    std::sort(c.begin(), c.end(), [&](uint32_t a, uint32_t b) { return key(a) < key(b); });
+    for (int i = 0; i < n && i < cap; ++i) {
+        xyr[3 * i] = ORBFE_CAND_X(c[i]);
+        xyr[3 * i + 1] = ORBFE_CAND_Y(c[i]);
+        xyr[3 * i + 2] = ORBFE_CAND_R(c[i]);
+    }
+    return n;
+}
+
+extern "C" void* orbfe_stream(orbfe_handle* h) { return h ? (void*)h->stream : nullptr; }
+extern "C" int orbfe_synchronize(orbfe_handle* h) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    return ORBFE_OK;
+}
+extern "C" long long orbfe_launch_count(const orbfe_handle* h) { return h ? h->launches : 0; }
+
+extern "C" const char* orbfe_strerror(int status) {
+    switch (status) {
+        case ORBFE_OK: return "ok";
+        case ORBFE_ERR_EMPTY_IMAGE: return "empty image";
+        case ORBFE_ERR_BAD_ARGUMENT: return "bad argument";
+        case ORBFE_ERR_TOO_LARGE: return "image, batch or feature count outside what the handle supports";
+        case ORBFE_ERR_CAPACITY: return "output buffer too small";
+        case ORBFE_ERR_CUDA: return "CUDA error";
+        case ORBFE_ERR_NO_DEVICE: return "no CUDA device";
+        case ORBFE_ERR_NOT_READY: return "no extraction result available";
+        default: return status > 0 ? "ok" : "unknown error";
+    }
+}
+extern "C" const char* orbfe_last_cuda_error(void) { return g_cudaErr; }
+extern "C" const char* orbfe_version(void) { return "orbfe 0.1 sm_100a"; }

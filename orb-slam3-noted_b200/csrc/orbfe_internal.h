@@ -1,0 +1,99 @@
+// orbfe_internal.h — handle layout, level geometry and kernel launchers shared by the .cu files.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <vector>
+
+#include "../../include/orbfe.h"
+
+#define ORBFE_MAX_LEVELS 16
+#define ORBFE_EDGE 19          // EDGE_THRESHOLD, ORBextractor.cc:71
+#define ORBFE_XO 32            // byte offset of ROI column 0 inside a bordered row (keeps ROI 32B-aligned)
+#define ORBFE_MIN_BORDER 16    // EDGE_THRESHOLD - 3, ORBextractor.cc:771
+#define ORBFE_MAX_NODES 2048   // per-level quota ceiling of the on-chip quadtree
+
+// Packed FAST candidate: x | y << 11 | response << 22, (x, y) relative to (minBorderX, minBorderY).
+#define ORBFE_CAND_X(c) ((int)((c) & 0x7FFu))
+#define ORBFE_CAND_Y(c) ((int)(((c) >> 11) & 0x7FFu))
+#define ORBFE_CAND_R(c) ((int)((c) >> 22))
+
+// Geometry of one pyramid level (host-computed once per image shape, read by every kernel).
+struct LevelGeom {
+    int w, h;              // ROI size, ORBextractor.cc:1156-1157
+    int pitch;             // bytes per row of the bordered device buffer
+    int rows;              // h + 38
+    long long base;        // byte offset of frame 0 of this level inside the pyramid arena
+    long long plane;       // bytes per frame of this level (pitch * rows)
+    // FAST grid, ORBextractor.cc:771-785
+    int maxBX, maxBY, nCols, nRows, wCell, hCell;
+    int cellBase, nCells;  // slice of the flattened cell table
+    // quadtree, ORBextractor.cc:541-543 and :433-444
+    int nfeat, nIni;
+    float hX;
+    int candCap;           // worst-case candidates of this level
+    long long candBase;    // offset (entries) of frame 0 / this level in the candidate arena
+    int kpCap, kpBase;     // slots for selected keypoints of this level (per frame)
+    float scale;           // mvScaleFactor[level]
+    float size;            // (float)(int)(31 * scale)
+    int tabX, tabY;        // offsets into the resize tables (entries)
+};
+
+// One FAST cell = one CTA of k_fast (ORBextractor.cc:787-853).
+struct CellDesc {
+    short level, x0, y0, cw, ch;   // ROI-relative origin (iniX, iniY) and size (maxX-iniX, maxY-iniY)
+    short ox, oy;                  // j*wCell, i*hCell
+    short pad;
+};
+
+// Bilinear resize coefficients of one destination column/row (OpenCV 11-bit fixed point).
+struct ResizeTap {
+    short s0, s1, a0, a1;
+};
+
+struct orbfe_handle {
+    orbfe_params p;
+    int device;
+    cudaStream_t stream;
+    long long launches;
+    // reference tables (ORBextractor.cc:413-444)
+    float scale[ORBFE_MAX_LEVELS], invScale[ORBFE_MAX_LEVELS], sigma2[ORBFE_MAX_LEVELS], invSigma2[ORBFE_MAX_LEVELS];
+    int featPerLevel[ORBFE_MAX_LEVELS];
+    // current shape
+    int curW, curH;
+    int lastBatch;
+    LevelGeom geom[ORBFE_MAX_LEVELS];
+    int nCellsTotal;
+    int maxCellBytes;       // smem tile bytes of the largest cell
+    long long candPerFrame; // candidate entries per frame (all levels)
+    int kpPerFrame;         // output slots per frame (= cap of device results)
+    // capacities fixed at create
+    size_t pyrBytes, candEntries, inBytes;
+    int cellCap, tabCap, kpCapPerFrame;
+    // device arenas
+    uint8_t* dIn;           // staged input frames (host path)
+    uint8_t* dPyr;          // pyramid arena [level][frame][rows][pitch]
+    uint32_t* dCand;        // packed candidates [frame][level slice]
+    uint32_t* dNodeOf;      // quadtree scratch, same indexing as dCand
+    int* dCandCount;        // [frame][level]
+    uint32_t* dLvlKp;       // selected keypoints per (frame, level slice): packed like candidates
+    int* dLvlCount;         // [frame][level]
+    LevelGeom* dGeom;
+    CellDesc* dCells;
+    ResizeTap* dTaps;
+    orbfe_keypoint* dKps;   // [frame][kpPerFrame]
+    uint8_t* dDesc;         // [frame][kpPerFrame][32]
+    uint32_t* dSlot;        // [frame][kpPerFrame] : level << 28 | y << 14 | x (level coords) of the keypoint at dst slot
+    int* dN;                // [frame]
+    int* dMono;             // [frame]
+    // pinned host staging for the small results
+    int* hN;
+    int* hMono;
+};
+
+// ---- launchers (each returns cudaGetLastError()) -------------------------------------------------
+cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int batch, int width, int height,
+                                 long long stride, long long frameStride);
+cudaError_t orbfe_launch_fast(orbfe_handle* h, int batch);
+cudaError_t orbfe_launch_octree(orbfe_handle* h, int batch);
+cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch, int lap0, int lap1);
