@@ -1,0 +1,106 @@
+"""GPU parity: the CUDA extractor (through the C ABI) against the CPU oracle, stage by stage.
+
+Bars (BASELINE.json north_star / SURVEY.md Appendix B): pyramid bytes, FAST candidates, selected
+keypoint set + order + response/octave/size/pt: bit-exact; angles within 1e-4 rad; >= 99.99 % of
+descriptors bit-identical.
+"""
+import numpy as np
+import pytest
+
+import orbfe
+from oracle_binding import OrbRef
+
+pytestmark = pytest.mark.gpu
+
+ANGLE_TOL_DEG = 1e-4 * 180.0 / np.pi   # 1e-4 rad
+
+# (name, w, h, nfeatures, lapping) — the five BASELINE.json shapes
+SHAPES = [
+    ("euroc_mono", 752, 480, 1000, (0, 1000)),
+    ("euroc_stereo", 752, 480, 1200, (0, 0)),
+    ("tumvi_fisheye", 512, 512, 1500, (128, 511)),
+    ("kitti", 1241, 376, 2000, (0, 0)),
+    ("hd", 1920, 1080, 4000, (0, 1000)),
+]
+
+
+def check_frame(ex, ref, img, lap, frame=0, got=None, stages=True):
+    rmono, rkps, rdesc = ref(img, lap)
+    if got is None:
+        got = ex(img, None, lap)
+    mono, kps, desc = got
+    if stages:
+        for l in range(ex.nlevels):
+            buf, _ = ex.image_pyramid(l, frame)
+            assert np.array_equal(buf, ref.level(l)), f"pyramid level {l}"
+        for l in range(ex.nlevels):
+            assert np.array_equal(ex.candidates(l, frame), ref.candidates(l)), f"FAST candidates level {l}"
+    assert len(kps) == len(rkps)
+    assert mono == rmono
+    for f in ("octave", "x", "y", "response", "size", "class_id"):
+        assert np.array_equal(kps[f], rkps[f]), f
+    assert np.max(np.abs(kps["angle"] - rkps["angle"]), initial=0) <= ANGLE_TOL_DEG
+    same = np.all(desc == rdesc, axis=1)
+    return int(same.sum()), len(same)
+
+
+@pytest.mark.parametrize("name,w,h,nf,lap", SHAPES, ids=[s[0] for s in SHAPES])
+def test_extract_parity(name, w, h, nf, lap):
+    ex = orbfe.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    ref = OrbRef(nf, 1.2, 8, 20, 7)
+    ok = tot = 0
+    for seed in range(3):
+        img = orbfe.synth.frame(1000 + 100 * SHAPES.index((name, w, h, nf, lap)) + seed, w, h)
+        a, b = check_frame(ex, ref, img, lap)
+        ok += a
+        tot += b
+    assert tot > 0.9 * 3 * nf
+    assert ok >= 0.9999 * tot, (ok, tot)
+
+
+def test_batch_equals_single():
+    w, h, nf = 752, 480, 1000
+    imgs = orbfe.synth.frames(2000, 6, w, h)
+    ex = orbfe.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=6)
+    ref = OrbRef(nf, 1.2, 8, 20, 7)
+    res = ex.extract_batch(imgs, (0, 1000))
+    ok = tot = 0
+    for b in range(6):
+        a, t = check_frame(ex, ref, imgs[b], (0, 1000), frame=b, got=res[b])
+        ok += a
+        tot += t
+    assert ok >= 0.9999 * tot
+
+
+def test_low_texture_retry_and_strided_input():
+    """Flat regions force the minThFAST retry (ORBextractor.cc:825-828); input with a row stride > width."""
+    w, h = 752, 480
+    img = orbfe.synth.frame(77, w, h).copy()
+    img[:, : w // 2] = (img[:, : w // 2].astype(np.int32) // 8 + 112).astype(np.uint8)   # contrast / 8
+    img[: h // 3, : w // 4] = 90                                                        # fully flat block
+    big = np.zeros((h, w + 40), np.uint8)
+    big[:, :w] = img
+    view = big[:, :w]
+    ex = orbfe.ORBextractor(1000, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    ref = OrbRef(1000, 1.2, 8, 20, 7)
+    ok, tot = check_frame(ex, ref, img, (0, 0), got=ex(view, None, (0, 0)))
+    assert tot > 300 and ok >= 0.9999 * tot
+
+
+def test_shape_change_and_errors():
+    ex = orbfe.ORBextractor(500, 1.2, 8, 20, 7, max_width=800, max_height=600)
+    ref = OrbRef(500, 1.2, 8, 20, 7)
+    for (w, h) in [(640, 480), (800, 600), (376, 240)]:
+        img = orbfe.synth.frame(5, w, h)
+        ok, tot = check_frame(ex, ref, img, (0, 0))
+        assert ok >= 0.9999 * tot
+    mono, kps, desc = ex(np.zeros((0, 0), np.uint8))
+    assert mono == -1 and len(kps) == 0
+    with pytest.raises(orbfe.OrbfeError):
+        ex(np.zeros((700, 900), np.uint8))
+
+
+def test_blank_image_gives_no_keypoints():
+    ex = orbfe.ORBextractor(1000, 1.2, 8, 20, 7, max_width=752, max_height=480)
+    mono, kps, desc = ex(np.full((480, 752), 128, np.uint8), None, (0, 0))
+    assert mono == 0 and len(kps) == 0 and desc.shape == (0, 32)
