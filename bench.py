@@ -1,0 +1,320 @@
+#!/usr/bin/env python
+"""bench.py — ORB extract+describe frames/s (752x480, 1000 keypoints) on N B200s, one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--batch B] [--impl orbfe|reference]
+
+A step is one pass of the hot path (pyramid -> grid FAST -> quadtree -> orientation -> blur +
+rBRIEF) over one batch of B synthetic 752x480 frames, nFeatures=1000 (BASELINE.json's metric
+shape, EuRoC mono settings).  `value` is device-resident throughput (frames already in HBM),
+`e2e` is the same workload through the host-buffer C-ABI call (H2D of the frames and D2H of the
+keypoints + descriptors inside the timed region).  Under torchrun each rank drives its own GPU on
+its own frames (no data-path collective: frames are independent); the timed region
+is bracketed by barrier + synchronize and the max over ranks is reported.
+
+`--impl reference` times the CPU restatement of the reference path (oracle/, the reference's own
+C++ cannot be compiled here: it needs OpenCV C++ headers) on all host cores, rank 0 only.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "orb-slam3-noted_b200")
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+W, H, NFEAT = 752, 480, 1000
+ORB_PARAMS = (NFEAT, 1.2, 8, 20, 7)
+LAPPING = (0, 1000)           # what the mono Frame ctor passes (Frame.cc:306)
+METRIC = "ORB extract+describe frames/s (752x480, 1000 kp)"
+UNIT = "frames/s"
+WORKLOAD = "ORBextractor 752x480 nFeatures=1000 nLevels=8 scale=1.2 iniThFAST=20 minThFAST=7, synthetic textured frames"
+
+
+def algorithmic_bytes_per_frame(w, h, n_kp, level_sizes):
+    """read the input once + write the API-visible bordered pyramid once + outputs."""
+    return w * h + sum((lw + 38) * (lh + 38) for lw, lh in level_sizes) + n_kp * (28 + 32)
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        try:
+            return float(json.load(open(p))["hbm_gbs"]), "measured"
+        except Exception:
+            pass
+    return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0]))
+                mx.append(float(f[1]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---- CPU arm: the oracle (a port of the reference's CPU path), the only place bench.py runs oracle/ ----
+def _oracle():
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import oracle_binding
+    return oracle_binding
+
+
+def cpu_frames_per_s(frames, nthreads, budget_s):
+    """Times orbref_extract_many (one extractor instance per thread, frame-parallel) for about budget_s."""
+    ob = _oracle()
+    n = len(frames)
+    t0 = time.perf_counter()
+    ob.extract_many(ORB_PARAMS, frames, LAPPING, nthreads)          # warm-up + rate estimate
+    rate = n / (time.perf_counter() - t0)
+    reps = max(1, int(budget_s * rate / n))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        ob.extract_many(ORB_PARAMS, frames, LAPPING, nthreads)
+    dt = time.perf_counter() - t0
+    return reps * n / dt, reps * n
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import __graft_entry__ as g
+    import orbfe
+    g._load_build_module().build_synth()
+    g._load_build_module().build_oracle()
+    cores = os.cpu_count() or 1
+    per_step = 16 * cores
+    frames = orbfe.synth.frames(1000, per_step, W, H)
+    ob = _oracle()
+    for _ in range(args.warmup):
+        ob.extract_many(ORB_PARAMS, frames, LAPPING, cores)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        ob.extract_many(ORB_PARAMS, frames, LAPPING, cores)
+    dt = time.perf_counter() - t0
+    v = args.steps * per_step / dt
+    sample = f"{per_step} frames per step x {args.steps} steps, frame-parallel over {cores} host threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u8", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_step": per_step,
+                   "note": "CPU restatement (oracle/cpu_ref, -O3 -march=native) of ORBextractor.cc with OpenCV 4.x "
+                           "arithmetic; the reference's own sources need OpenCV C++ headers, absent here"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+# ---- GPU arm ---------------------------------------------------------------------------------------
+def run_orbfe(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import __graft_entry__ as g
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; orbfe has no CPU path (use --impl reference for the CPU arm)")
+    if rank == 0:
+        g.build()
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        dist.barrier()
+    import orbfe
+
+    B, K, Wm = args.batch, args.steps, args.warmup
+    ex = orbfe.ORBextractor(*ORB_PARAMS, device=local, max_width=W, max_height=H, max_batch=B)
+    # each rank gets its own frames (frame-sharded, weak scaling); NDISTINCT distinct frames tiled to B
+    nd = min(B, args.distinct)
+    base = orbfe.synth.frames(1000 + 7919 * rank, nd, W, H)
+    host = torch.empty((B, H, W), dtype=torch.uint8).pin_memory()
+    hnp = host.numpy()
+    for b in range(B):
+        hnp[b] = base[b % nd]
+    dev = host.cuda(non_blocking=False)
+    stream = torch.cuda.ExternalStream(ex.stream(), device=local)
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing
+    for _ in range(Wm):
+        ex.extract_batch_device(dev.data_ptr(), B, W, H)
+    ex.synchronize()
+    res = ex.fetch_results(B)
+    n_kp = float(np.mean([len(r[1]) for r in res]))
+    ex.set_profiling(True)
+    ex.stage_times()
+    clocks = ClockSampler(local)
+    barrier()
+    clocks.start()
+    l0 = ex.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(K):
+        ex.extract_batch_device(dev.data_ptr(), B, W, H)
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = ex.launch_count() - l0
+    stage_ms, calls = ex.stage_times()
+    ex.set_profiling(False)
+
+    # ---- end to end through the host-buffer C-ABI call (pinned host in, pinned host out)
+    kps = torch.empty((B, ex.cap, 28), dtype=torch.uint8).pin_memory().numpy().view(orbfe.KEYPOINT_DTYPE).reshape(B, ex.cap)
+    desc = torch.empty((B, ex.cap, 32), dtype=torch.uint8).pin_memory().numpy()
+    n_out = np.zeros(B, np.int32)
+    mono = np.zeros(B, np.int32)
+    L = orbfe.lib()
+
+    def e2e_step():
+        st = L.orbfe_extract_batch(ex.handle, hnp.ctypes.data, B, W, H, W, W * H, LAPPING[0], LAPPING[1], kps.ctypes.data,
+                                   desc.ctypes.data, ex.cap, n_out.ctypes.data, mono.ctypes.data)
+        if st < 0:
+            raise orbfe.OrbfeError(st, "orbfe_extract_batch")
+
+    for _ in range(Wm):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        e2e_step()
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    clk = clocks.stop()
+
+    if world > 1:
+        t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1]) / 1e3
+        tl = torch.tensor([launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(tl)
+        launches = int(tl[0])
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    value = world * K * B / (ms / 1e3)
+    e2e_v = world * K * B / e2e_s
+    # roofline of the dominant stage (per launch of that stage = one batch of B frames)
+    level_sizes = []
+    for l in range(ex.nlevels):
+        _, roi = ex.image_pyramid(l, 0)
+        level_sizes.append((roi.shape[1], roi.shape[0]))
+    b_alg = algorithmic_bytes_per_frame(W, H, n_kp, level_sizes)
+    top = max(stage_ms, key=stage_ms.get)
+    top_ms = stage_ms[top] / max(calls, 1)
+    peak, how = measured_peaks()
+    achieved = b_alg * B / (top_ms / 1e3) / 1e9
+    whole = b_alg * B * K / (ms / 1e3) / 1e9
+    out = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
+        "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
+        "data": "synthetic",
+        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "distinct_frames": nd, "lapping": list(LAPPING),
+                   "mean_keypoints_per_frame": n_kp, "parallelism": f"frame-sharded x{world}, no collective",
+                   "l2": f"inputs larger than L2: {B * W * H / 1e6:.0f} MB of frames and a "
+                         f"{B * sum((a + 38) * (b + 38) for a, b in level_sizes) / 1e6:.0f} MB pyramid per step vs 126 MB L2"},
+        "e2e": {"value": e2e_v, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),
+                "d2h_bytes_per_step": int(B * ex.cap * 60 + 8 * B), "ms_per_step": 1e3 * e2e_s / K,
+                "api": "orbfe_extract_batch (host buffers, pinned)"},
+        "gpu_launches": int(launches),
+        "clocks": clk,
+        "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": None, "peak_source": how,
+                     "algorithmic_bytes_per_frame": b_alg, "frames_per_launch": B, "kernel_ms_per_launch": top_ms,
+                     "whole_path_achieved": whole, "whole_path_frac": whole / peak,
+                     "stage_ms_per_step": {k: v / max(calls, 1) for k, v in stage_ms.items()}},
+    }
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        frames = orbfe.synth.frames(1000, 8 * cores, W, H)
+        v, nfr = cpu_frames_per_s(frames, cores, args.cpu_seconds)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
+                               "sample": f"{nfr} frames of the same workload, frame-parallel over {cores} host threads "
+                                         "(oracle/cpu_ref, one extractor per thread)"}
+    print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--batch", type=int, default=512, help="frames per step per GPU")
+    ap.add_argument("--distinct", type=int, default=64, help="distinct synthetic frames tiled into the batch")
+    ap.add_argument("--impl", default="orbfe", choices=["orbfe", "reference"])
+    ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--no-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3:
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_orbfe(args)
+
+
+if __name__ == "__main__":
+    main()

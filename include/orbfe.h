@@ -118,6 +118,17 @@ int orbfe_synchronize(orbfe_handle* h);
 /* Number of kernels this handle has launched since creation. */
 long long orbfe_launch_count(const orbfe_handle* h);
 
+/* Per-stage device timing (the REGISTER_TIMES switch of include/Config.h:4 / Frame.cc:116-127, done
+ * with CUDA events on the handle's stream).  While enabled every extract call brackets its stages
+ * with events; orbfe_get_stage_times synchronises, adds up the elapsed milliseconds per stage since
+ * the last read into ms[ORBFE_NUM_STAGES], stores the number of extract calls covered in *calls and
+ * resets the accumulators.  Stages: 0 pyramid, 1 grid FAST, 2 quadtree, 3 assemble, 4 orientation +
+ * blur + descriptors. */
+#define ORBFE_NUM_STAGES 5
+int orbfe_set_profiling(orbfe_handle* h, int enabled);
+int orbfe_get_stage_times(orbfe_handle* h, double* ms, long long* calls);
+const char* orbfe_stage_name(int stage);
+
 const char* orbfe_strerror(int status);
 const char* orbfe_last_cuda_error(void);
 /* "orbfe <version> sm_100a" */

@@ -204,10 +204,14 @@ __global__ void __launch_bounds__(DESC_THREADS) k_describe(const uint8_t* __rest
     }
 }
 
-cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch, int lap0, int lap1) {
+cudaError_t orbfe_launch_assemble(orbfe_handle* h, int batch, int lap0, int lap1) {
     k_assemble<<<batch, ASM_THREADS, 0, h->stream>>>(h->dGeom, h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, lap0, lap1,
                                                      h->dKps, h->dSlot, h->dN, h->dMono);
     h->launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch) {
     dim3 grid(h->kpPerFrame, batch);
     k_describe<<<grid, DESC_THREADS, 0, h->stream>>>(h->dPyr, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps, h->dDesc);
     h->launches++;

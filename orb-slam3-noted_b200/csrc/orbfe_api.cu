@@ -176,6 +176,11 @@ static void free_handle(orbfe_handle* h) {
     cudaFree(h->dKps); cudaFree(h->dDesc); cudaFree(h->dSlot); cudaFree(h->dN); cudaFree(h->dMono);
     if (h->hN) cudaFreeHost(h->hN);
     if (h->hMono) cudaFreeHost(h->hMono);
+    if (h->profEv) {
+        for (int i = 0; i < ORBFE_PROF_RING; ++i)
+            for (int s = 0; s <= ORBFE_NUM_STAGES; ++s) cudaEventDestroy(h->profEv[i][s]);
+        delete[] h->profEv;
+    }
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -284,15 +289,69 @@ extern "C" int orbfe_get_tables(const orbfe_handle* h, float* scale, float* inv_
 extern "C" int orbfe_max_keypoints(const orbfe_handle* h) { return h ? h->kpCapPerFrame : ORBFE_ERR_BAD_ARGUMENT; }
 
 // ---- extraction -------------------------------------------------------------------------------------
+// ---- stage profiling ----------------------------------------------------------------------------------
+static int prof_fold_oldest(orbfe_handle* h) {
+    cudaEvent_t* ev = h->profEv[h->profHead];
+    CK(cudaEventSynchronize(ev[ORBFE_NUM_STAGES]));
+    for (int s = 0; s < ORBFE_NUM_STAGES; ++s) {
+        float ms = 0.f;
+        CK(cudaEventElapsedTime(&ms, ev[s], ev[s + 1]));
+        h->profMs[s] += ms;
+    }
+    h->profCalls++;
+    h->profHead = (h->profHead + 1) % ORBFE_PROF_RING;
+    h->profCount--;
+    return ORBFE_OK;
+}
+
 static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int batch, int W, int H, long long stride,
                            long long frameStride, int lap0, int lap1) {
     cudaError_t e;
+    cudaEvent_t* ev = nullptr;
+    if (h->profiling) {
+        if (h->profCount == ORBFE_PROF_RING) { int st = prof_fold_oldest(h); if (st != ORBFE_OK) return st; }
+        ev = h->profEv[(h->profHead + h->profCount) % ORBFE_PROF_RING];
+        CK(cudaEventRecord(ev[0], h->stream));
+    }
     if ((e = orbfe_launch_pyramid(h, dImages, batch, W, H, stride, frameStride)) != cudaSuccess) return cuda_fail(e, "pyramid");
+    if (ev) CK(cudaEventRecord(ev[1], h->stream));
     if ((e = orbfe_launch_fast(h, batch)) != cudaSuccess) return cuda_fail(e, "fast");
+    if (ev) CK(cudaEventRecord(ev[2], h->stream));
     if ((e = orbfe_launch_octree(h, batch)) != cudaSuccess) return cuda_fail(e, "octree");
-    if ((e = orbfe_launch_describe(h, batch, lap0, lap1)) != cudaSuccess) return cuda_fail(e, "describe");
+    if (ev) CK(cudaEventRecord(ev[3], h->stream));
+    if ((e = orbfe_launch_assemble(h, batch, lap0, lap1)) != cudaSuccess) return cuda_fail(e, "assemble");
+    if (ev) CK(cudaEventRecord(ev[4], h->stream));
+    if ((e = orbfe_launch_describe(h, batch)) != cudaSuccess) return cuda_fail(e, "describe");
+    if (ev) { CK(cudaEventRecord(ev[5], h->stream)); h->profCount++; }
     h->lastBatch = batch;
     return ORBFE_OK;
+}
+
+extern "C" int orbfe_set_profiling(orbfe_handle* h, int enabled) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    if (enabled && !h->profEv) {
+        h->profEv = new cudaEvent_t[ORBFE_PROF_RING][ORBFE_NUM_STAGES + 1];
+        for (int i = 0; i < ORBFE_PROF_RING; ++i)
+            for (int s = 0; s <= ORBFE_NUM_STAGES; ++s) CK(cudaEventCreate(&h->profEv[i][s]));
+    }
+    h->profiling = enabled ? 1 : 0;
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_get_stage_times(orbfe_handle* h, double* ms, long long* calls) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    while (h->profCount > 0) { int st = prof_fold_oldest(h); if (st != ORBFE_OK) return st; }
+    for (int s = 0; s < ORBFE_NUM_STAGES; ++s) { if (ms) ms[s] = h->profMs[s]; h->profMs[s] = 0; }
+    if (calls) *calls = h->profCalls;
+    h->profCalls = 0;
+    return ORBFE_OK;
+}
+
+extern "C" const char* orbfe_stage_name(int stage) {
+    static const char* names[ORBFE_NUM_STAGES] = {"pyramid", "fast", "octree", "assemble", "describe"};
+    return stage >= 0 && stage < ORBFE_NUM_STAGES ? names[stage] : "?";
 }
 
 extern "C" int orbfe_extract_batch_device(orbfe_handle* h, const uint8_t* d_images, int batch, int width, int height,

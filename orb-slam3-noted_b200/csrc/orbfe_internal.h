@@ -89,11 +89,19 @@ struct orbfe_handle {
     // pinned host staging for the small results
     int* hN;
     int* hMono;
+    // stage profiling: a ring of event sets, one per extract call in flight
+    int profiling;
+    int profHead, profCount;                  // ring state
+    cudaEvent_t (*profEv)[ORBFE_NUM_STAGES + 1];
+    double profMs[ORBFE_NUM_STAGES];
+    long long profCalls;
 };
+#define ORBFE_PROF_RING 64
 
 // ---- launchers (each returns cudaGetLastError()) -------------------------------------------------
 cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int batch, int width, int height,
                                  long long stride, long long frameStride);
 cudaError_t orbfe_launch_fast(orbfe_handle* h, int batch);
 cudaError_t orbfe_launch_octree(orbfe_handle* h, int batch);
-cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch, int lap0, int lap1);
+cudaError_t orbfe_launch_assemble(orbfe_handle* h, int batch, int lap0, int lap1);
+cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch);

@@ -168,3 +168,19 @@ class ORBextractor:
 
     def launch_count(self):
         return int(self._lib.orbfe_launch_count(self._h))
+
+    STAGES = ("pyramid", "fast", "octree", "assemble", "describe")
+
+    def set_profiling(self, enabled=True):
+        st = self._lib.orbfe_set_profiling(self._h, int(bool(enabled)))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_set_profiling")
+
+    def stage_times(self):
+        """({stage: total ms since the last read}, extract calls covered); synchronises the stream."""
+        ms = np.zeros(len(self.STAGES), np.float64)
+        calls = C.c_longlong(0)
+        st = self._lib.orbfe_get_stage_times(self._h, ptr(ms), C.byref(calls))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_get_stage_times")
+        return dict(zip(self.STAGES, ms.tolist())), int(calls.value)
