@@ -8,6 +8,7 @@ import numpy as np
 import pytest
 
 import orbfe
+from common import check_against_golden, golden_cases, golden_input
 from oracle_binding import OrbRef
 
 pytestmark = pytest.mark.gpu
@@ -104,3 +105,20 @@ def test_blank_image_gives_no_keypoints():
     ex = orbfe.ORBextractor(1000, 1.2, 8, 20, 7, max_width=752, max_height=480)
     mono, kps, desc = ex(np.full((480, 752), 128, np.uint8), None, (0, 0))
     assert mono == 0 and len(kps) == 0 and desc.shape == (0, 32)
+
+
+GOLD = golden_cases("extract_")
+
+
+@pytest.mark.parametrize("path", GOLD, ids=[p.split("extract_")[1][:-4] for p in GOLD])
+def test_extract_matches_golden(path):
+    """The CUDA path against the committed cv2-generated fixtures (no oracle in the loop)."""
+    g = np.load(path)
+    img = golden_input(g)
+    sf, nl, ini, mn = g["orb"]
+    ex = orbfe.ORBextractor(int(g["nfeatures"]), float(sf), int(nl), int(ini), int(mn), max_width=int(g["w"]),
+                            max_height=int(g["h"]))
+    mono, kps, desc = ex(img, None, tuple(int(v) for v in g["lapping"]))
+    ok, tot = check_against_golden(g, mono, kps, desc, pyramid_level=lambda l: ex.image_pyramid(l)[0],
+                                   candidates=ex.candidates)
+    assert ok >= 0.9999 * tot, (ok, tot)

@@ -1,0 +1,110 @@
+"""CPU: known-answer tests of the oracle's OpenCV-free primitives (oracle/cpu_ref/cvprim.cc) against
+the real OpenCV (cv2 4.13.0, the pinned version), and of the whole C++
+extractor against the cv2-backed restatement (oracle/py/orb_cv2.py).  Skipped where cv2 is absent;
+the golden-vector test covers that case."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+cv2 = pytest.importorskip("cv2")
+
+import orbfe  # noqa: E402
+import oracle_binding as ob  # noqa: E402
+from oracle_binding import OrbRef, _p  # noqa: E402
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "py"))
+from orb_cv2 import ORBextractorCv2  # noqa: E402
+
+
+def rnd_img(seed, w, h):
+    return np.random.default_rng(seed).integers(0, 256, (h, w), dtype=np.uint8)
+
+
+@pytest.mark.parametrize("sw,sh,dw,dh", [(752, 480, 627, 400), (627, 400, 522, 333), (252, 161, 210, 134),
+                                         (1920, 1080, 1600, 900), (512, 512, 427, 427), (97, 61, 80, 51)])
+def test_resize_linear(sw, sh, dw, dh):
+    src = rnd_img(sw * 7 + dh, sw, sh)
+    want = cv2.resize(src, (dw, dh), interpolation=cv2.INTER_LINEAR)
+    got = np.zeros((dh, dw), np.uint8)
+    ob.lib().orbref_resize(_p(src), sw, sh, sw, _p(got), dw, dh, dw)
+    assert np.array_equal(got, want)
+
+
+def test_border_reflect101():
+    src = rnd_img(3, 70, 50)
+    want = cv2.copyMakeBorder(src, 19, 19, 19, 19, cv2.BORDER_REFLECT_101)
+    buf = np.zeros_like(want)
+    buf[19:-19, 19:-19] = src
+    ob.lib().orbref_border101(_p(buf), 70, 50, 19, buf.strides[0])
+    assert np.array_equal(buf, want)
+
+
+@pytest.mark.parametrize("t", [7, 20])
+def test_fast_9_16_nms(t):
+    img = orbfe.synth.frame(5, 160, 120)
+    want = cv2.FastFeatureDetector_create(t, True).detect(img)
+    out = np.zeros((20000, 3), np.int32)
+    n = ob.lib().orbref_fast(_p(img), 160, 120, 160, t, _p(out), len(out))
+    assert n == len(want) and n > 50
+    w = np.array([[k.pt[0], k.pt[1], k.response] for k in want]).astype(np.int32)
+    assert np.array_equal(out[:n], w)
+    # a 42x44 cell-sized ROI behaves the same (ORBextractor.cc:808 passes views of this size)
+    cell = np.ascontiguousarray(img[30:74, 50:92])
+    want = cv2.FastFeatureDetector_create(t, True).detect(cell)
+    n = ob.lib().orbref_fast(_p(cell), 42, 44, 42, t, _p(out), len(out))
+    assert n == len(want)
+    if n:
+        assert np.array_equal(out[:n], np.array([[k.pt[0], k.pt[1], k.response] for k in want]).astype(np.int32))
+
+
+def test_gaussian_blur_7x7_fixed_point():
+    for (w, h, seed) in [(160, 120, 1), (37, 41, 2), (752, 480, 3)]:
+        src = rnd_img(seed, w, h)
+        want = cv2.GaussianBlur(src, (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+        got = np.zeros_like(src)
+        ob.lib().orbref_blur(_p(src), w, h, w, _p(got), w)
+        assert np.array_equal(got, want)
+
+
+def test_fast_atan2():
+    rng = np.random.default_rng(11)
+    ys = rng.integers(-200000, 200000, 20000).astype(np.float32)
+    xs = rng.integers(-200000, 200000, 20000).astype(np.float32)
+    ys[:4], xs[:4] = [0, 0, 5, -5], [0, 7, 0, 0]
+    for y, x in zip(ys, xs):
+        assert ob.lib().orbref_fast_atan2(float(y), float(x)) == np.float32(cv2.fastAtan2(float(y), float(x)))
+
+
+def test_knn2_matches_bfmatcher_tie_rule():
+    q = orbfe.synth.descriptors(1, 300)
+    t = orbfe.synth.descriptors(2, 5000)
+    t[100] = t[7]           # crafted ties: the lower train index must win (Appendix A.7)
+    t[4000] = t[7]
+    q[0] = t[7]
+    idx, dist = ob.knn2(q, t)
+    m = cv2.BFMatcher(cv2.NORM_HAMMING).knnMatch(q, t, k=2)
+    want_i = np.array([[a.trainIdx, b.trainIdx] for a, b in m])
+    want_d = np.array([[a.distance, b.distance] for a, b in m]).astype(np.int32)
+    assert np.array_equal(idx, want_i) and np.array_equal(dist, want_d)
+    assert idx[0].tolist() == [7, 100] and dist[0].tolist() == [0, 0]
+
+
+@pytest.mark.parametrize("w,h,nf,lap,seed", [(752, 480, 1000, (0, 1000), 1003), (752, 480, 1200, (0, 0), 1104),
+                                             (512, 512, 1500, (128, 511), 1205), (1241, 376, 2000, (0, 0), 1306),
+                                             (640, 480, 500, (100, 300), 9)])
+def test_cpp_oracle_equals_cv2_restatement(w, h, nf, lap, seed):
+    img = orbfe.synth.frame(seed, w, h)
+    py = ORBextractorCv2(nf, 1.2, 8, 20, 7)
+    kp, desc, mono = py(img, lap)
+    ref = OrbRef(nf, 1.2, 8, 20, 7)
+    rmono, rk, rd = ref(img, lap)
+    assert rmono == mono and len(rk) == len(kp)
+    for l in range(8):
+        assert np.array_equal(ref.level(l), py.pyramid[l])
+        assert np.array_equal(ref.candidates(l), np.array(py.candidates[l], np.float64).reshape(-1, 3).astype(np.int32))
+    for i, f in enumerate(("x", "y", "size", "angle", "response")):
+        assert np.array_equal(rk[f], kp[:, i].astype(np.float32)), f
+    assert np.array_equal(rk["octave"], kp[:, 5].astype(np.int32))
+    assert np.array_equal(rd, desc)
