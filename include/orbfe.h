@@ -129,6 +129,123 @@ int orbfe_set_profiling(orbfe_handle* h, int enabled);
 int orbfe_get_stage_times(orbfe_handle* h, double* ms, long long* calls);
 const char* orbfe_stage_name(int stage);
 
+/* ---- matchers: replace ORB_SLAM3::ORBmatcher (include/ORBmatcher.h:35-111) and the two stereo ---
+ * ---- matchers of Frame (Frame.cc:794-964, 1116-1156) -------------------------------------------- */
+
+/* ORBmatcher::TH_LOW / TH_HIGH / HISTO_LENGTH (ORBmatcher.cc:36-38). */
+#define ORBFE_TH_LOW 50
+#define ORBFE_TH_HIGH 100
+#define ORBFE_HISTO_LENGTH 30
+
+/* ORBmatcher::DescriptorDistance (ORBmatcher.cc:2561-2577): Hamming distance of two 32-byte
+ * descriptors.  A static host function in the reference (one pair, host cv::Mat rows), so it stays
+ * a host function here; every bulk distance computation goes through the device entry points. */
+static inline int orbfe_descriptor_distance(const uint8_t* a, const uint8_t* b) {
+    int d = 0, i;
+    for (i = 0; i < 32; i += 4) {
+        uint32_t x = ((uint32_t)(a[i] ^ b[i])) | ((uint32_t)(a[i + 1] ^ b[i + 1]) << 8) |
+                     ((uint32_t)(a[i + 2] ^ b[i + 2]) << 16) | ((uint32_t)(a[i + 3] ^ b[i + 3]) << 24);
+        d += __builtin_popcount(x);
+    }
+    return d;
+}
+
+/* An ORBmatcher(nnratio, checkOri) object (ORBmatcher.h:39): owns one CUDA stream, pinned staging
+ * and growable device scratch.  Single-threaded per handle; handles are independent. */
+typedef struct orbfe_matcher orbfe_matcher;
+int orbfe_matcher_create(float nnratio, int check_orientation, int device, orbfe_matcher** out);
+void orbfe_matcher_destroy(orbfe_matcher* m);
+void* orbfe_matcher_stream(orbfe_matcher* m);
+int orbfe_matcher_synchronize(orbfe_matcher* m);
+long long orbfe_matcher_launch_count(const orbfe_matcher* m);
+
+/* DBoW2::FeatureVector (Thirdparty/DBoW2/DBoW2/FeatureVector.h:24-25: std::map<NodeId,
+ * std::vector<unsigned>>) flattened to CSR: node_ids ascending, the features of node k are
+ * indices[offsets[k] .. offsets[k+1]), ascending as DBoW2 appends them. */
+typedef struct orbfe_feature_vector {
+    int nnodes;
+    const uint32_t* node_ids; /* [nnodes] */
+    const int32_t* offsets;   /* [nnodes + 1] */
+    const int32_t* indices;   /* [offsets[nnodes]] */
+} orbfe_feature_vector;
+
+/* cv::BFMatcher(NORM_HAMMING).knnMatch(q, t, k=2) (Frame.cc:43,1134): the two nearest train rows
+ * of every query row, ties to the lowest train index.  idx2 / dist2: nq x 2 int32, -1 where the
+ * train set has fewer than two rows.  Host buffers. */
+int orbfe_hamming_knn2(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx2,
+                       int32_t* dist2);
+/* Batched device-resident form: problem b matches the d_nq[b] rows at d_q + b*q_stride against the
+ * d_nt[b] rows at d_t + b*t_stride (d_nq / d_nt: device int arrays, or NULL for nq_max / nt_max
+ * everywhere).  Results into device arrays d_idx2 / d_dist2 of [batch][nq_max][2].  Asynchronous on
+ * the matcher's stream.  Used for sequence matching frame t <-> t+1 straight from an extractor's
+ * device results. */
+int orbfe_hamming_knn2_batch_device(orbfe_matcher* m, const uint8_t* d_q, ptrdiff_t q_stride, const int* d_nq, int nq_max,
+                                    const uint8_t* d_t, ptrdiff_t t_stride, const int* d_nt, int nt_max, int batch,
+                                    int32_t* d_idx2, int32_t* d_dist2);
+/* Frame::ComputeStereoFishEyeMatches up to the descriptor test (Frame.cc:1134-1141): 2-NN + Lowe
+ * ratio (d0 < d1 * ratio in double precision, ratio = the double literal 0.7 there).  match[nq] = train index or -1.  Returns the number
+ * of matches. */
+int orbfe_match_lapping(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio,
+                        int32_t* match);
+
+/* Frame::ComputeStereoMatches (Frame.cc:794-964), "SearchStereo": rectified-stereo row-band search
+ * (Hamming < 75 among right keypoints whose row band covers the left keypoint, octave within +-1,
+ * disparity in [0, bf/b]), 11x11 SAD refinement over +-5 px on the pyramid level of the left
+ * keypoint, parabola sub-pixel fit, 2.1 x median SAD outlier cut.  Works on the DEVICE-resident
+ * results and pyramids of the last extract of `left` (frame index frame_l) and `right` (frame
+ * index frame_r); the two handles may be the same object (batch extract of the pair) and must live
+ * on one device.  u_right / depth: host arrays of n_left floats (mvuRight / mvDepth, -1 = none).
+ * Returns the number of left keypoints with a depth. */
+int orbfe_stereo_match(orbfe_matcher* m, orbfe_handle* left, int frame_l, orbfe_handle* right, int frame_r, float bf,
+                       float b, float* u_right, float* depth, int cap);
+/* Batched device-resident form for stereo sequences: pair p = frames (2p, 2p+1) of one batch
+ * extract on `h`.  Results stay on the device: d_u_right / d_depth are [npairs][cap] floats
+ * (cap = orbfe_max_keypoints(h)).  Asynchronous on the matcher's stream (ordered after the
+ * extractor's stream). */
+int orbfe_stereo_match_batch_device(orbfe_matcher* m, orbfe_handle* h, int npairs, float bf, float b, float* d_u_right,
+                                    float* d_depth);
+
+/* One side of a BoW-guided search. */
+typedef struct orbfe_bow_side {
+    const uint8_t* desc;          /* n x 32 */
+    int n;
+    orbfe_feature_vector fv;
+    const uint8_t* mask;          /* n bytes; meaning depends on the call, may be NULL where stated */
+    const orbfe_keypoint* kps;    /* n keypoints (angle, pt, octave are read); may be NULL if unused */
+} orbfe_bow_side;
+
+/* ORBmatcher::SearchByBoW, both overloads, `nprob` independent problems in one call (Tracking::
+ * Relocalization and LoopClosing call it once per candidate keyframe).
+ *   form 0  SearchByBoW(KeyFrame*, Frame&, vpMapPointMatches)   ORBmatcher.cc:269-471
+ *           A = keyframe (mask = has a good MapPoint), B = frame (mask NULL); accept bestDist1 <= TH_LOW;
+ *           nleft_b = F.Nleft (-1 without a second camera) selects the left/right split of :330-368.
+ *           Output b2a[p][B.n]: keyframe feature matched to each frame feature, -1 none.
+ *   form 1  SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12)      ORBmatcher.cc:823-963
+ *           A = pKF1, B = pKF2, both masks = has a good MapPoint; accept bestDist1 < TH_LOW.
+ *           Output a2b[p][A.n]: pKF2 feature matched to each pKF1 feature, -1 none.
+ * Both outputs are always written (either may be NULL).  If b_shared != 0 every problem uses B[0].
+ * nmatches[p] = the function's return value.  Returns 0 or a negative status. */
+int orbfe_search_bow(orbfe_matcher* m, int form, const orbfe_bow_side* A, const orbfe_bow_side* B, int nprob, int b_shared,
+                     int nleft_b, int32_t* const* a2b, int32_t* const* b2a, int* nmatches);
+
+/* Two-view geometry of SearchForTriangulation for pinhole cameras. */
+typedef struct orbfe_epipolar {
+    float F12[9];      /* row-major K1^-T [t12]x R12 K2^-1, as Pinhole::epipolarConstrain_ forms it (Pinhole.cpp:161-164) */
+    float ex, ey;      /* projection of camera 1's centre into image 2 (ORBmatcher.cc:1213-1218) */
+    const float* sigma2_b;  /* pKF2->mvLevelSigma2 [nlevels] */
+    const float* scale_b;   /* pKF2->mvScaleFactors [nlevels] */
+    int nlevels;
+} orbfe_epipolar;
+
+/* ORBmatcher::SearchForTriangulation / SearchForTriangulation_ (ORBmatcher.cc:965-1432), pinhole
+ * cameras without a second camera.  A = pKF1, B = pKF2; mask = feature already HAS a MapPoint
+ * (skipped); u_right_* = mvuRight (>= 0: stereo observation; NULL = all mono).  kps = mvKeysUn.
+ * matches12[A.n] = pKF2 index or -1; the reference's vMatchedPairs is the ascending list of
+ * (i, matches12[i]).  Returns the match count or a negative status. */
+int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_bow_side* A, const float* u_right_a, const orbfe_bow_side* B,
+                               const float* u_right_b, const orbfe_epipolar* geo, int only_stereo, int coarse,
+                               int32_t* matches12);
+
 const char* orbfe_strerror(int status);
 const char* orbfe_last_cuda_error(void);
 /* "orbfe <version> sm_100a" */

@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "cvprim.h"
+#include "match_ref.h"
 #include "orb_ref.h"
 
 using namespace orbref;
@@ -108,6 +109,60 @@ long orbref_extract_many(int nf, float sf, int nl, int ini, int mn, const uint8_
     long total = 0;
     for (long c : counts) total += c;
     return total;
+}
+
+// ---- matchers (match_ref.cc)
+int orbref_descriptor_distance(const uint8_t* a, const uint8_t* b) { return descriptorDistanceSwar(a, b); }
+void orbref_three_maxima(const int* counts, int L, int* ind) {
+    int a = -1, b = -1, c = -1;
+    computeThreeMaxima(counts, L, a, b, c);
+    ind[0] = a; ind[1] = b; ind[2] = c;
+}
+// Runs both extractors' pyramids must be current (call orbref_extract on each first).
+void orbref_stereo_match(void* hl, void* hr, const KeyPoint* kpL, const uint8_t* descL, int nL, const KeyPoint* kpR,
+                         const uint8_t* descR, int nR, float bf, float b, float* uRight, float* depth, int32_t* bestDist) {
+    computeStereoMatches(*(OrbExtractorRef*)hl, *(OrbExtractorRef*)hr, kpL, descL, nL, kpR, descR, nR, bf, b, uRight, depth,
+                         bestDist);
+}
+int orbref_search_bow(const uint8_t* descA, int nA, int nnA, const uint32_t* nodeA, const int32_t* offA, const int32_t* idxA,
+                      const uint8_t* maskA, const float* angA, const uint8_t* descB, int nB, int nnB, const uint32_t* nodeB,
+                      const int32_t* offB, const int32_t* idxB, const uint8_t* maskB, const float* angB, float ratio,
+                      int checkOri, int th, int strictTh, int nleftB, int32_t* a2b, int32_t* b2a) {
+    FeatureVectorCsr fa{nnA, nodeA, offA, idxA}, fb{nnB, nodeB, offB, idxB};
+    BowParams p{ratio, checkOri, th, strictTh, nleftB};
+    return searchByBoW(descA, nA, fa, maskA, angA, descB, nB, fb, maskB, angB, p, a2b, b2a);
+}
+int orbref_search_triangulation(const KeyPoint* kpA, const uint8_t* descA, int nA, int nnA, const uint32_t* nodeA,
+                                const int32_t* offA, const int32_t* idxA, const uint8_t* mpA, const float* urA,
+                                const KeyPoint* kpB, const uint8_t* descB, int nB, int nnB, const uint32_t* nodeB,
+                                const int32_t* offB, const int32_t* idxB, const uint8_t* mpB, const float* urB,
+                                const float* sigma2B, const float* scaleB, const float* F12, float ex, float ey,
+                                int checkOri, int onlyStereo, int coarse, int32_t* m12) {
+    FeatureVectorCsr fa{nnA, nodeA, offA, idxA}, fb{nnB, nodeB, offB, idxB};
+    TriParams p;
+    p.checkOri = checkOri; p.onlyStereo = onlyStereo; p.coarse = coarse; p.ex = ex; p.ey = ey;
+    std::memcpy(p.F12, F12, sizeof(p.F12));
+    return searchForTriangulation(kpA, descA, nA, fa, mpA, urA, kpB, descB, nB, fb, mpB, urB, sigma2B, scaleB, p, m12);
+}
+void orbref_knn2_ratio(const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match) {
+    knn2RatioMatch(q, nq, t, nt, ratio, match);
+}
+// Timed CPU baseline for matching: `npairs` independent knn2 problems on `nthreads` host threads.
+long orbref_knn2_many(const uint8_t* q, int nq, const uint8_t* t, int nt, int npairs, long qstride, long tstride, int nthreads) {
+    std::vector<long> acc(nthreads, 0);
+    std::vector<std::thread> th;
+    for (int w = 0; w < nthreads; ++w)
+        th.emplace_back([&, w]() {
+            std::vector<int32_t> idx(2 * (size_t)nq), dist(2 * (size_t)nq);
+            for (int p = w; p < npairs; p += nthreads) {
+                knn2Hamming(q + p * qstride, nq, t + p * tstride, nt, idx.data(), dist.data());
+                acc[w] += dist[0];
+            }
+        });
+    for (auto& x : th) x.join();
+    long s = 0;
+    for (long a : acc) s += a;
+    return s;
 }
 
 }  // extern "C"

@@ -1,0 +1,81 @@
+// match_ref.h — CPU restatement of the reference's Hamming matchers (TEST INFRASTRUCTURE).
+//
+// Follows /root/reference/src/ORBmatcher.cc (DescriptorDistance :2561-2577, ComputeThreeMaxima
+// :2515-2556, SearchByBoW(KF,Frame) :269-471, SearchByBoW(KF,KF) :823-963, SearchForTriangulation_
+// :1208-1432) and /root/reference/src/Frame.cc (ComputeStereoMatches :794-964,
+// ComputeStereoFishEyeMatches :1116-1141 up to the Lowe-ratio test), with Pinhole::epipolarConstrain_
+// (src/CameraModels/Pinhole.cpp:159-181).  Objects the reference reaches through KeyFrame / Frame /
+// MapPoint pointers are flattened to arrays here exactly as at the C ABI (include/orbfe.h): a
+// DBoW2::FeatureVector is a CSR (node ids ascending, feature indices per node), "has a good
+// MapPoint" is a byte mask.  Only tests/, __graft_entry__.smoke() and bench.py's CPU legs use it.
+// Parity pin: tests/golden/match_*.npz, produced by oracle/py/match_py.py (a line-by-line Python
+// restatement that calls cv2.BFMatcher / cv2.norm for the OpenCV parts).
+#pragma once
+#include <cstdint>
+#include <utility>
+#include <vector>
+
+#include "orb_ref.h"
+
+namespace orbref {
+
+static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;   // ORBmatcher.cc:36-38
+
+// The SWAR popcount of ORBmatcher.cc:2561-2577, verbatim arithmetic.
+int descriptorDistanceSwar(const uint8_t* a, const uint8_t* b);
+
+// ORBmatcher.cc:2515-2556.  counts[L] = histo[i].size().
+void computeThreeMaxima(const int* counts, int L, int& ind1, int& ind2, int& ind3);
+
+// DBoW2::FeatureVector flattened: nodeIds ascending, features of node k = indices[offsets[k] .. offsets[k+1]).
+struct FeatureVectorCsr {
+    int nnodes;
+    const uint32_t* nodeIds;
+    const int32_t* offsets;
+    const int32_t* indices;
+};
+
+// Frame::ComputeStereoMatches (Frame.cc:794-964).  uRight / depth: nL floats, -1 where unmatched.
+// bestDistOut (nullable): the SAD of accepted matches, -1 elsewhere (debug tap).
+void computeStereoMatches(const OrbExtractorRef& left, const OrbExtractorRef& right, const KeyPoint* kpL,
+                          const uint8_t* descL, int nL, const KeyPoint* kpR, const uint8_t* descR, int nR, float mbf,
+                          float mb, float* uRight, float* depth, int32_t* bestDistOut);
+
+struct BowParams {
+    float nnRatio;      // mfNNratio
+    int checkOri;       // mbCheckOrientation
+    int th;             // TH_LOW
+    int strictTh;       // 0: bestDist1 <= th (KF,Frame :373); 1: bestDist1 < th (KF,KF :904)
+    int nleftB;         // F.Nleft (-1: no second camera); >= 0 selects the left/right split of :330-368
+};
+// SearchByBoW, both overloads.  Side A iterates in the outer loop (the KeyFrame / pKF1), side B is
+// searched and claimed (the Frame / pKF2).  maskA[i] != 0: feature i of A has a good MapPoint
+// (required); maskB may be null (KF,Frame form: every Frame feature is eligible) or gives pKF2's
+// MapPoint validity.  matchBtoA[nB]: index in A claimed for each B feature (-1 none) — this is
+// vpMapPointMatches of :269; matchAtoB[nA]: vpMatches12 of :823 (left-camera match when nleftB >= 0).
+int searchByBoW(const uint8_t* descA, int nA, const FeatureVectorCsr& fvA, const uint8_t* maskA, const float* angleA,
+                const uint8_t* descB, int nB, const FeatureVectorCsr& fvB, const uint8_t* maskB, const float* angleB,
+                const BowParams& p, int32_t* matchAtoB, int32_t* matchBtoA);
+
+struct TriParams {
+    int checkOri;        // mbCheckOrientation
+    int onlyStereo;      // bOnlyStereo
+    int coarse;          // bCoarse: accept without the epipolar test (:1361)
+    float F12[9];        // row-major fundamental matrix K1^-T [t12]x R12 K2^-1, as epipolarConstrain_ builds it
+    float ex, ey;        // epipole of camera 1 in image 2 (:1218)
+};
+// SearchForTriangulation_ (pinhole cameras, no second camera).  hasMp*: feature already has a
+// MapPoint (skipped); uRight*: mvuRight (>= 0 means stereo observation); kp*: undistorted keypoints;
+// sigma2B / scaleB: pKF2->mvLevelSigma2 / mvScaleFactors.  Writes matches12[nA] (-1 none); the
+// reference's vMatchedPairs is the ascending list of (i, matches12[i]) with matches12[i] >= 0.
+int searchForTriangulation(const KeyPoint* kpA, const uint8_t* descA, int nA, const FeatureVectorCsr& fvA,
+                           const uint8_t* hasMpA, const float* uRightA, const KeyPoint* kpB, const uint8_t* descB, int nB,
+                           const FeatureVectorCsr& fvB, const uint8_t* hasMpB, const float* uRightB, const float* sigma2B,
+                           const float* scaleB, const TriParams& p, int32_t* matches12);
+
+// Frame::ComputeStereoFishEyeMatches up to the descriptor test (Frame.cc:1134-1141): 2-NN brute force
+// (BFMatcher NORM_HAMMING, ties to the lowest train index) + Lowe ratio d0 < 0.7 * d1.
+// match[nq] = train index or -1.
+void knn2RatioMatch(const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match);
+
+}  // namespace orbref

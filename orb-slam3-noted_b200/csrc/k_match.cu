@@ -1,0 +1,145 @@
+// k_match.cu — brute-force Hamming 2-NN: cv::BFMatcher(NORM_HAMMING).knnMatch(k=2) as used by
+// Frame::ComputeStereoFishEyeMatches (Frame.cc:43,1134), with ORBmatcher::DescriptorDistance
+// (ORBmatcher.cc:2561-2577) as the metric.
+//
+// One thread owns one query descriptor (8 x u32 in registers) and scans a slice of the train set,
+// which the CTA streams through shared memory in 128-row tiles (4 KB, uint4 loads; every thread
+// reads the same train row at the same time, so the shared reads are broadcasts).  The distance
+// is 8 x (xor, popc); best and second best are kept as packed keys  dist << 20 | trainIndex , so
+// "two smallest keys" is exactly "two smallest distances, ties to the lowest train index"
+// (OpenCV's order) and the update is three min/max ops without a branch.  The train set is split
+// over blockIdx.y to fill the GPU when there are few queries; partial results are merged by a
+// second tiny kernel.  Integer-pipe (popc) bound by construction: HBM traffic is nq*32 + nt*32
+// bytes per tile pass, re-used 128 times from registers / shared memory.
+#include "orbfe_internal.h"
+
+#define KNN_THREADS 128
+#define KNN_TILE 128
+#define KNN_IDX_BITS 20
+#define KNN_IDX_MASK ((1u << KNN_IDX_BITS) - 1u)
+#define KNN_NONE 0xFFFFFFFFu
+
+__device__ __forceinline__ void knn_update(uint32_t& k0, uint32_t& k1, uint32_t k) {
+    const uint32_t hi = max(k0, k);
+    k0 = min(k0, k);
+    k1 = min(k1, hi);
+}
+
+__device__ __forceinline__ void knn_store(uint32_t k0, uint32_t k1, int32_t* idx, int32_t* dist) {
+    idx[0] = k0 == KNN_NONE ? -1 : (int)(k0 & KNN_IDX_MASK);
+    dist[0] = k0 == KNN_NONE ? -1 : (int)(k0 >> KNN_IDX_BITS);
+    idx[1] = k1 == KNN_NONE ? -1 : (int)(k1 & KNN_IDX_MASK);
+    dist[1] = k1 == KNN_NONE ? -1 : (int)(k1 >> KNN_IDX_BITS);
+}
+
+// grid = (query tiles, train splits, batch)
+__global__ void __launch_bounds__(KNN_THREADS) k_knn2(const uint8_t* __restrict__ q, long long qStride, const int* __restrict__ nqArr,
+                                                      int nqMax, const uint8_t* __restrict__ t, long long tStride,
+                                                      const int* __restrict__ ntArr, int ntMax, int splitLen,
+                                                      uint2* __restrict__ partial, int32_t* __restrict__ idx2,
+                                                      int32_t* __restrict__ dist2) {
+    __shared__ uint4 tile[KNN_TILE * 2];
+    const int b = blockIdx.z, split = blockIdx.y, nsplit = gridDim.y;
+    const int nq = nqArr ? min(nqArr[b], nqMax) : nqMax;
+    const int nt = ntArr ? min(ntArr[b], ntMax) : ntMax;
+    const int qi = blockIdx.x * KNN_THREADS + threadIdx.x;
+    if (blockIdx.x * KNN_THREADS >= nq) return;
+    const bool live = qi < nq;
+    uint32_t qa[8];
+    {
+        const uint4* qp = reinterpret_cast<const uint4*>(q + (long long)b * qStride) + 2 * (long long)(live ? qi : 0);
+        const uint4 a = __ldg(qp), c = __ldg(qp + 1);
+        qa[0] = a.x; qa[1] = a.y; qa[2] = a.z; qa[3] = a.w; qa[4] = c.x; qa[5] = c.y; qa[6] = c.z; qa[7] = c.w;
+    }
+    const uint4* tp = reinterpret_cast<const uint4*>(t + (long long)b * tStride);
+    const int t0 = split * splitLen, t1 = min(t0 + splitLen, nt);
+    uint32_t k0 = KNN_NONE, k1 = KNN_NONE;
+    for (int base = t0; base < t1; base += KNN_TILE) {
+        const int n = min(KNN_TILE, t1 - base);
+        __syncthreads();
+        for (int i = threadIdx.x; i < 2 * n; i += KNN_THREADS) tile[i] = __ldg(tp + 2 * (long long)base + i);
+        __syncthreads();
+#pragma unroll 4
+        for (int j = 0; j < n; ++j) {
+            const uint4 a = tile[2 * j], c = tile[2 * j + 1];
+            const int d = __popc(qa[0] ^ a.x) + __popc(qa[1] ^ a.y) + __popc(qa[2] ^ a.z) + __popc(qa[3] ^ a.w) +
+                          __popc(qa[4] ^ c.x) + __popc(qa[5] ^ c.y) + __popc(qa[6] ^ c.z) + __popc(qa[7] ^ c.w);
+            knn_update(k0, k1, ((uint32_t)d << KNN_IDX_BITS) | (uint32_t)(base + j));
+        }
+    }
+    if (!live) return;
+    if (nsplit == 1) {
+        const long long o = ((long long)b * nqMax + qi) * 2;
+        knn_store(k0, k1, idx2 + o, dist2 + o);
+    } else {
+        partial[((long long)b * nsplit + split) * nqMax + qi] = make_uint2(k0, k1);
+    }
+}
+
+__global__ void __launch_bounds__(KNN_THREADS) k_knn2_merge(const uint2* __restrict__ partial, const int* __restrict__ nqArr,
+                                                            int nqMax, int nsplit, int32_t* __restrict__ idx2,
+                                                            int32_t* __restrict__ dist2) {
+    const int b = blockIdx.y, qi = blockIdx.x * KNN_THREADS + threadIdx.x;
+    const int nq = nqArr ? min(nqArr[b], nqMax) : nqMax;
+    if (qi >= nq) return;
+    uint32_t k0 = KNN_NONE, k1 = KNN_NONE;
+    for (int s = 0; s < nsplit; ++s) {
+        const uint2 p = partial[((long long)b * nsplit + s) * nqMax + qi];
+        knn_update(k0, k1, p.x);
+        knn_update(k0, k1, p.y);   // KNN_NONE entries never displace a real key
+    }
+    const long long o = ((long long)b * nqMax + qi) * 2;
+    knn_store(k0, k1, idx2 + o, dist2 + o);
+}
+
+// Lowe-ratio filter of Frame.cc:1141 on 2-NN results: match = idx0 if both exist and d0 < d1 * ratio.
+// DMatch::distance is float and the literal 0.7 is double in the reference, hence the double compare.
+__global__ void k_ratio_filter(const int32_t* __restrict__ idx2, const int32_t* __restrict__ dist2, int nq, double ratio,
+                               int32_t* __restrict__ match, int* __restrict__ count) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nq) return;
+    const bool ok = idx2[2 * i + 1] >= 0 && (double)(float)dist2[2 * i] < (double)(float)dist2[2 * i + 1] * ratio;
+    match[i] = ok ? idx2[2 * i] : -1;
+    if (ok) atomicAdd(count, 1);
+}
+
+// Number of train splits / rows per split for a problem set (host).
+void orbfe_knn2_plan(int nqMax, int ntMax, int batch, int smCount, int* nsplit, int* splitLen) {
+    const int qTiles = (nqMax + KNN_THREADS - 1) / KNN_THREADS;
+    const long long ctas = (long long)qTiles * batch;
+    const long long want = 4LL * smCount;                       // ~4 resident CTAs' worth of queries per SM
+    int s = (int)((want + ctas - 1) / (ctas > 0 ? ctas : 1));
+    const int maxSplit = (ntMax + KNN_TILE - 1) / KNN_TILE;
+    s = s < 1 ? 1 : s > maxSplit ? maxSplit : s;
+    if (s > 64) s = 64;
+    int len = (ntMax + s - 1) / (s > 0 ? s : 1);
+    len = (len + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+    if (len < KNN_TILE) len = KNN_TILE;
+    s = (ntMax + len - 1) / len;
+    *nsplit = s < 1 ? 1 : s;
+    *splitLen = len;
+}
+
+cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStride, const int* dNq, int nqMax, const uint8_t* dt,
+                              long long tStride, const int* dNt, int ntMax, int batch, int nsplit, int splitLen, uint2* dPartial,
+                              int32_t* dIdx2, int32_t* dDist2, long long* launches) {
+    if (nqMax <= 0 || batch <= 0) return cudaSuccess;
+    if (ntMax > (int)KNN_IDX_MASK) return cudaErrorInvalidValue;
+    dim3 grid((nqMax + KNN_THREADS - 1) / KNN_THREADS, nsplit, batch);
+    k_knn2<<<grid, KNN_THREADS, 0, st>>>(dq, qStride, dNq, nqMax, dt, tStride, dNt, ntMax, splitLen, dPartial, dIdx2, dDist2);
+    ++*launches;
+    if (nsplit > 1) {
+        dim3 g2((nqMax + KNN_THREADS - 1) / KNN_THREADS, batch);
+        k_knn2_merge<<<g2, KNN_THREADS, 0, st>>>(dPartial, dNq, nqMax, nsplit, dIdx2, dDist2);
+        ++*launches;
+    }
+    return cudaGetLastError();
+}
+
+cudaError_t orbfe_launch_ratio_filter(cudaStream_t st, const int32_t* dIdx2, const int32_t* dDist2, int nq, double ratio,
+                                      int32_t* dMatch, int* dCount, long long* launches) {
+    if (nq <= 0) return cudaSuccess;
+    k_ratio_filter<<<(nq + 127) / 128, 128, 0, st>>>(dIdx2, dDist2, nq, ratio, dMatch, dCount);
+    ++*launches;
+    return cudaGetLastError();
+}

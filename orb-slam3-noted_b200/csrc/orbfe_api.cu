@@ -17,6 +17,7 @@ static int cuda_fail(cudaError_t e, const char* what) {
     snprintf(g_cudaErr, sizeof(g_cudaErr), "%s: %s", what, cudaGetErrorString(e));
     return ORBFE_ERR_CUDA;
 }
+int orbfe_set_cuda_error(cudaError_t e, const char* what) { return cuda_fail(e, what); }   // for the other .cu files
 #define CK(call)                                             \
     do {                                                     \
         cudaError_t e_ = (call);                             \

@@ -1,0 +1,51 @@
+// orbfe_match.h — device-side problem descriptors and launchers of the matcher kernels
+// (k_match.cu, k_stereo.cu, k_bow.cu), shared with the matcher C ABI (orbfe_match_api.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "orbfe_internal.h"
+
+// One BoW / triangulation problem: all pointers are device pointers into the matcher's staging arena.
+struct MatchProblem {
+    const uint8_t* descA;     // nA x 32
+    const uint8_t* descB;     // nB x 32
+    const int32_t* idxA;      // CSR indices of A (all nodes, concatenated)
+    const int32_t* idxB;
+    const uint8_t* maskA;     // SearchByBoW: has a good MapPoint; SearchForTriangulation: already has a MapPoint
+    const uint8_t* maskB;     // may be null in SearchByBoW form 0
+    const float4* kpA;        // (x, y, angle, octave as int bits)
+    const float4* kpB;
+    const float* uRightA;     // triangulation only; may be null (all mono)
+    const float* uRightB;
+    int32_t* a2b;             // nA
+    int32_t* b2a;             // nB
+    int nA, nB;
+};
+
+// One vocabulary node present in both FeatureVectors of problem `prob`.
+struct MatchItem {
+    int prob;
+    int a0, a1;               // range in idxA
+    int b0, b1;               // range in idxB
+};
+
+struct TriGeo {
+    float F[9];
+    float ex, ey;
+    float sigma2B[ORBFE_MAX_LEVELS], scaleB[ORBFE_MAX_LEVELS];
+};
+
+void orbfe_knn2_plan(int nqMax, int ntMax, int batch, int smCount, int* nsplit, int* splitLen);
+cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStride, const int* dNq, int nqMax, const uint8_t* dt,
+                              long long tStride, const int* dNt, int ntMax, int batch, int nsplit, int splitLen, uint2* dPartial,
+                              int32_t* dIdx2, int32_t* dDist2, long long* launches);
+cudaError_t orbfe_launch_ratio_filter(cudaStream_t st, const int32_t* dIdx2, const int32_t* dDist2, int nq, double ratio,
+                                      int32_t* dMatch, int* dCount, long long* launches);
+cudaError_t orbfe_launch_stereo(cudaStream_t st, const orbfe_handle* hl, int frameL0, int frameLStep, const orbfe_handle* hr,
+                                int frameR0, int frameRStep, int npairs, float bf, float b, float* dURight, float* dDepth,
+                                int* dSad, int* dCount, long long* launches);
+cudaError_t orbfe_launch_bow(cudaStream_t st, const MatchProblem* dProbs, int nprob, const MatchItem* dItems, int nitems,
+                             float nnRatio, int th, int strictTh, int nleftB, int checkOri, int* dCounts, long long* launches);
+cudaError_t orbfe_launch_tri(cudaStream_t st, const MatchProblem* dProbs, const MatchItem* dItems, int nitems, const TriGeo& geo,
+                             int onlyStereo, int coarse, int checkOri, int* dCounts, long long* launches);

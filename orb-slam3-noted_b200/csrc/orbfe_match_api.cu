@@ -1,0 +1,427 @@
+// orbfe_match_api.cu — C ABI of the matchers (include/orbfe.h, "matchers" section): the
+// orbfe_matcher object (one stream, a pinned host / device staging arena pair and device scratch,
+// all grown on demand), host-side flattening of the reference's inputs and the launches.
+// No CPU fallback: every entry point needs the CUDA device the matcher was created on.
+#include <stdio.h>
+#include <string.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "orbfe_internal.h"
+#include "orbfe_match.h"
+
+int orbfe_set_cuda_error(cudaError_t e, const char* what);   // orbfe_api.cu
+
+#define CK(call)                                                         \
+    do {                                                                 \
+        cudaError_t e_ = (call);                                         \
+        if (e_ != cudaSuccess) return orbfe_set_cuda_error(e_, #call);   \
+    } while (0)
+
+struct orbfe_matcher {
+    float nnRatio;
+    int checkOri;
+    int device;
+    int smCount;
+    cudaStream_t stream;
+    cudaEvent_t ev;
+    long long launches;
+    // staging arena: host (pinned) and device mirrors with identical offsets
+    uint8_t* hStage;
+    uint8_t* dStage;
+    size_t stageCap, stageUsed;
+    // device-only scratch (knn2 partials, stereo SAD, counters)
+    uint8_t* dScratch;
+    size_t scratchCap;
+};
+
+static int ensure_stage(orbfe_matcher* m, size_t bytes) {
+    if (bytes <= m->stageCap) return ORBFE_OK;
+    CK(cudaStreamSynchronize(m->stream));
+    size_t cap = std::max(bytes + bytes / 4, (size_t)1 << 20);
+    if (m->hStage) cudaFreeHost(m->hStage);
+    if (m->dStage) cudaFree(m->dStage);
+    m->hStage = nullptr; m->dStage = nullptr; m->stageCap = 0;
+    CK(cudaMallocHost(&m->hStage, cap));
+    CK(cudaMalloc(&m->dStage, cap));
+    m->stageCap = cap;
+    return ORBFE_OK;
+}
+
+static int ensure_scratch(orbfe_matcher* m, size_t bytes) {
+    if (bytes <= m->scratchCap) return ORBFE_OK;
+    CK(cudaStreamSynchronize(m->stream));
+    size_t cap = std::max(bytes + bytes / 4, (size_t)1 << 20);
+    if (m->dScratch) cudaFree(m->dScratch);
+    m->dScratch = nullptr; m->scratchCap = 0;
+    CK(cudaMalloc(&m->dScratch, cap));
+    m->scratchCap = cap;
+    return ORBFE_OK;
+}
+
+// Bump allocation inside the staging arena (256-byte aligned so uint4 / float4 loads are legal).
+static inline size_t stage_take(size_t& used, size_t bytes) {
+    const size_t off = (used + 255) & ~(size_t)255;
+    used = off + bytes;
+    return off;
+}
+
+extern "C" int orbfe_matcher_create(float nnratio, int check_orientation, int device, orbfe_matcher** out) {
+    if (!out) return ORBFE_ERR_BAD_ARGUMENT;
+    *out = nullptr;
+    if (!(nnratio > 0.f)) return ORBFE_ERR_BAD_ARGUMENT;
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev < 1) { cudaGetLastError(); return ORBFE_ERR_NO_DEVICE; }
+    if (device < 0 || device >= ndev) return ORBFE_ERR_BAD_ARGUMENT;
+    orbfe_matcher* m = new orbfe_matcher();
+    memset(m, 0, sizeof(*m));
+    m->nnRatio = nnratio;
+    m->checkOri = check_orientation ? 1 : 0;
+    m->device = device;
+    cudaError_t e = cudaSetDevice(device);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev, cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaDeviceGetAttribute(&m->smCount, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess) { orbfe_set_cuda_error(e, "orbfe_matcher_create"); orbfe_matcher_destroy(m); return ORBFE_ERR_CUDA; }
+    *out = m;
+    return ORBFE_OK;
+}
+
+extern "C" void orbfe_matcher_destroy(orbfe_matcher* m) {
+    if (!m) return;
+    cudaSetDevice(m->device);
+    if (m->stream) cudaStreamSynchronize(m->stream);
+    if (m->hStage) cudaFreeHost(m->hStage);
+    if (m->dStage) cudaFree(m->dStage);
+    if (m->dScratch) cudaFree(m->dScratch);
+    if (m->ev) cudaEventDestroy(m->ev);
+    if (m->stream) cudaStreamDestroy(m->stream);
+    delete m;
+}
+
+extern "C" void* orbfe_matcher_stream(orbfe_matcher* m) { return m ? (void*)m->stream : nullptr; }
+extern "C" int orbfe_matcher_synchronize(orbfe_matcher* m) {
+    if (!m) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(m->device));
+    CK(cudaStreamSynchronize(m->stream));
+    return ORBFE_OK;
+}
+extern "C" long long orbfe_matcher_launch_count(const orbfe_matcher* m) { return m ? m->launches : 0; }
+
+// ---- brute-force 2-NN ----------------------------------------------------------------------------------
+extern "C" int orbfe_hamming_knn2_batch_device(orbfe_matcher* m, const uint8_t* d_q, ptrdiff_t q_stride, const int* d_nq,
+                                               int nq_max, const uint8_t* d_t, ptrdiff_t t_stride, const int* d_nt, int nt_max,
+                                               int batch, int32_t* d_idx2, int32_t* d_dist2) {
+    if (!m || !d_q || !d_t || !d_idx2 || !d_dist2 || nq_max < 0 || nt_max < 0 || batch < 0) return ORBFE_ERR_BAD_ARGUMENT;
+    if (nt_max >= (1 << 20)) return ORBFE_ERR_TOO_LARGE;
+    if (nq_max == 0 || batch == 0) return ORBFE_OK;
+    CK(cudaSetDevice(m->device));
+    int nsplit = 1, splitLen = nt_max;
+    orbfe_knn2_plan(nq_max, nt_max, batch, m->smCount, &nsplit, &splitLen);
+    uint2* partial = nullptr;
+    if (nsplit > 1) {
+        int st = ensure_scratch(m, sizeof(uint2) * (size_t)batch * nsplit * nq_max);
+        if (st != ORBFE_OK) return st;
+        partial = reinterpret_cast<uint2*>(m->dScratch);
+    }
+    CK(orbfe_launch_knn2(m->stream, d_q, q_stride, d_nq, nq_max, d_t, t_stride, d_nt, nt_max, batch, nsplit, splitLen, partial,
+                         d_idx2, d_dist2, &m->launches));
+    return ORBFE_OK;
+}
+
+// Stages q and t, runs the 2-NN; leaves idx2 / dist2 (nq x 2 each) in the device staging arena at the returned offsets.
+static int knn2_staged(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, size_t* offIdx, size_t* offDist,
+                       size_t* used) {
+    size_t u = 0;
+    const size_t oq = stage_take(u, (size_t)nq * 32), ot = stage_take(u, (size_t)std::max(nt, 1) * 32);
+    const size_t inBytes = u;
+    const size_t oi = stage_take(u, sizeof(int32_t) * 2 * nq), od = stage_take(u, sizeof(int32_t) * 2 * nq);
+    const size_t extra = stage_take(u, 256 + sizeof(int32_t) * (size_t)nq);   // room for the lapping filter's outputs
+    (void)extra;
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    memcpy(m->hStage + oq, q, (size_t)nq * 32);
+    if (nt > 0) memcpy(m->hStage + ot, t, (size_t)nt * 32);
+    CK(cudaMemcpyAsync(m->dStage, m->hStage, inBytes, cudaMemcpyHostToDevice, m->stream));
+    st = orbfe_hamming_knn2_batch_device(m, m->dStage + oq, 0, nullptr, nq, m->dStage + ot, 0, nullptr, nt, 1,
+                                         reinterpret_cast<int32_t*>(m->dStage + oi), reinterpret_cast<int32_t*>(m->dStage + od));
+    if (st != ORBFE_OK) return st;
+    *offIdx = oi; *offDist = od; *used = u;
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_hamming_knn2(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, int32_t* idx2,
+                                  int32_t* dist2) {
+    if (!m || nq < 0 || nt < 0 || (nq > 0 && (!q || !idx2 || !dist2)) || (nt > 0 && !t)) return ORBFE_ERR_BAD_ARGUMENT;
+    if (nq == 0) return ORBFE_OK;
+    CK(cudaSetDevice(m->device));
+    size_t oi, od, used;
+    int st = knn2_staged(m, q, nq, t, nt, &oi, &od, &used);
+    if (st != ORBFE_OK) return st;
+    // idx and dist are adjacent allocations: one copy back covers both
+    CK(cudaMemcpyAsync(m->hStage + oi, m->dStage + oi, od + sizeof(int32_t) * 2 * nq - oi, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(idx2, m->hStage + oi, sizeof(int32_t) * 2 * nq);
+    memcpy(dist2, m->hStage + od, sizeof(int32_t) * 2 * nq);
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_match_lapping(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio,
+                                   int32_t* match) {
+    if (!m || nq < 0 || nt < 0 || (nq > 0 && (!q || !match)) || (nt > 0 && !t)) return ORBFE_ERR_BAD_ARGUMENT;
+    if (nq == 0) return 0;
+    CK(cudaSetDevice(m->device));
+    size_t oi, od, used;
+    int st = knn2_staged(m, q, nq, t, nt, &oi, &od, &used);
+    if (st != ORBFE_OK) return st;
+    const size_t oc = (od + sizeof(int32_t) * 2 * nq + 255) & ~(size_t)255, om = oc + 256;
+    CK(cudaMemsetAsync(m->dStage + oc, 0, sizeof(int), m->stream));
+    const double r = ratio;   // the reference multiplies DMatch::distance (float) by the double literal 0.7 (Frame.cc:1141)
+    CK(orbfe_launch_ratio_filter(m->stream, reinterpret_cast<int32_t*>(m->dStage + oi), reinterpret_cast<int32_t*>(m->dStage + od), nq,
+                                 r, reinterpret_cast<int32_t*>(m->dStage + om), reinterpret_cast<int*>(m->dStage + oc),
+                                 &m->launches));
+    CK(cudaMemcpyAsync(m->hStage + oc, m->dStage + oc, 256 + sizeof(int32_t) * (size_t)nq, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(match, m->hStage + om, sizeof(int32_t) * (size_t)nq);
+    return *reinterpret_cast<int*>(m->hStage + oc);
+}
+
+// ---- rectified stereo ----------------------------------------------------------------------------------
+// Orders the matcher's stream after everything already enqueued on an extractor's stream.
+static int wait_for(orbfe_matcher* m, orbfe_handle* h) {
+    CK(cudaEventRecord(m->ev, h->stream));
+    CK(cudaStreamWaitEvent(m->stream, m->ev, 0));
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_stereo_match_batch_device(orbfe_matcher* m, orbfe_handle* h, int npairs, float bf, float b, float* d_u_right,
+                                               float* d_depth) {
+    if (!m || !h || !d_u_right || !d_depth || npairs <= 0 || !(b > 0.f)) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->device != m->device) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->lastBatch < 2 * npairs) return ORBFE_ERR_NOT_READY;
+    CK(cudaSetDevice(m->device));
+    int st = ensure_scratch(m, sizeof(int) * ((size_t)npairs * h->kpPerFrame + npairs));
+    if (st != ORBFE_OK) return st;
+    if ((st = wait_for(m, h)) != ORBFE_OK) return st;
+    int* dSad = reinterpret_cast<int*>(m->dScratch);
+    int* dCount = dSad + (size_t)npairs * h->kpPerFrame;
+    CK(orbfe_launch_stereo(m->stream, h, 0, 2, h, 1, 2, npairs, bf, b, d_u_right, d_depth, dSad, dCount, &m->launches));
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_stereo_match(orbfe_matcher* m, orbfe_handle* left, int frame_l, orbfe_handle* right, int frame_r, float bf,
+                                  float b, float* u_right, float* depth, int cap) {
+    if (!m || !left || !right || !u_right || !depth || !(b > 0.f)) return ORBFE_ERR_BAD_ARGUMENT;
+    if (left->device != m->device || right->device != m->device) return ORBFE_ERR_BAD_ARGUMENT;
+    if (frame_l < 0 || frame_l >= left->lastBatch || frame_r < 0 || frame_r >= right->lastBatch) return ORBFE_ERR_NOT_READY;
+    if (left->curW != right->curW || left->curH != right->curH || left->p.nlevels != right->p.nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(m->device));
+    const int kpf = left->kpPerFrame;
+    size_t u = 0;
+    const size_t oU = stage_take(u, sizeof(float) * kpf), oD = stage_take(u, sizeof(float) * kpf), oN = stage_take(u, 256);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    if ((st = ensure_scratch(m, sizeof(int) * ((size_t)kpf + 64))) != ORBFE_OK) return st;
+    if ((st = wait_for(m, left)) != ORBFE_OK) return st;
+    if (right != left && (st = wait_for(m, right)) != ORBFE_OK) return st;
+    int* dSad = reinterpret_cast<int*>(m->dScratch);
+    int* dCount = dSad + kpf;
+    float* dU = reinterpret_cast<float*>(m->dStage + oU);
+    float* dD = reinterpret_cast<float*>(m->dStage + oD);
+    CK(orbfe_launch_stereo(m->stream, left, frame_l, 0, right, frame_r, 0, 1, bf, b, dU, dD, dSad, dCount, &m->launches));
+    CK(cudaMemcpyAsync(m->dStage + oN, left->dN + frame_l, sizeof(int), cudaMemcpyDeviceToDevice, m->stream));
+    CK(cudaMemcpyAsync(m->dStage + oN + 4, dCount, sizeof(int), cudaMemcpyDeviceToDevice, m->stream));
+    CK(cudaMemcpyAsync(m->hStage, m->dStage, u, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    const int nL = reinterpret_cast<int*>(m->hStage + oN)[0], cnt = reinterpret_cast<int*>(m->hStage + oN)[1];
+    if (nL > cap) return ORBFE_ERR_CAPACITY;
+    memcpy(u_right, m->hStage + oU, sizeof(float) * nL);
+    memcpy(depth, m->hStage + oD, sizeof(float) * nL);
+    return cnt;
+}
+
+// ---- BoW-guided searches --------------------------------------------------------------------------------
+struct SideLayout {
+    size_t desc, idx, mask, kp, ur, out;   // offsets in the staging arena
+};
+
+static bool valid_side(const orbfe_bow_side& s) {
+    if (s.n < 0 || (s.n > 0 && !s.desc)) return false;
+    if (s.fv.nnodes < 0 || (s.fv.nnodes > 0 && (!s.fv.node_ids || !s.fv.offsets || !s.fv.indices))) return false;
+    for (int k = 0; k < s.fv.nnodes; ++k) {
+        if (s.fv.offsets[k] > s.fv.offsets[k + 1] || s.fv.offsets[k] < 0) return false;
+        if (k > 0 && s.fv.node_ids[k] <= s.fv.node_ids[k - 1]) return false;
+    }
+    const int tot = s.fv.nnodes ? s.fv.offsets[s.fv.nnodes] : 0;
+    for (int i = 0; i < tot; ++i)
+        if (s.fv.indices[i] < 0 || s.fv.indices[i] >= s.n) return false;
+    return true;
+}
+
+static void reserve_side(const orbfe_bow_side& s, bool needUr, size_t& u, SideLayout& L) {
+    const int tot = s.fv.nnodes ? s.fv.offsets[s.fv.nnodes] : 0;
+    L.desc = stage_take(u, (size_t)std::max(s.n, 1) * 32);
+    L.idx = stage_take(u, sizeof(int32_t) * std::max(tot, 1));
+    L.mask = stage_take(u, (size_t)std::max(s.n, 1));
+    L.kp = stage_take(u, sizeof(float4) * std::max(s.n, 1));
+    L.ur = needUr ? stage_take(u, sizeof(float) * std::max(s.n, 1)) : 0;
+}
+
+// maskDefault: value used when the caller passes no mask.
+static void fill_side(uint8_t* base, const orbfe_bow_side& s, const SideLayout& L, uint8_t maskDefault, const float* uRight) {
+    const int tot = s.fv.nnodes ? s.fv.offsets[s.fv.nnodes] : 0;
+    if (s.n > 0) memcpy(base + L.desc, s.desc, (size_t)s.n * 32);
+    if (tot > 0) memcpy(base + L.idx, s.fv.indices, sizeof(int32_t) * tot);
+    if (s.mask) memcpy(base + L.mask, s.mask, s.n);
+    else memset(base + L.mask, maskDefault, std::max(s.n, 1));
+    float4* kp = reinterpret_cast<float4*>(base + L.kp);
+    for (int i = 0; i < s.n; ++i) {
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (s.kps) {
+            v.x = s.kps[i].x; v.y = s.kps[i].y; v.z = s.kps[i].angle;
+            memcpy(&v.w, &s.kps[i].octave, 4);
+        }
+        kp[i] = v;
+    }
+    if (L.ur) {
+        float* ur = reinterpret_cast<float*>(base + L.ur);
+        for (int i = 0; i < s.n; ++i) ur[i] = uRight ? uRight[i] : -1.f;
+    }
+}
+
+// The merge-join of ORBmatcher.cc:289-429 over two CSR FeatureVectors.
+static void join_nodes(int prob, const orbfe_feature_vector& a, const orbfe_feature_vector& b, std::vector<MatchItem>& items) {
+    int i = 0, j = 0;
+    while (i < a.nnodes && j < b.nnodes) {
+        if (a.node_ids[i] == b.node_ids[j]) {
+            MatchItem it{prob, a.offsets[i], a.offsets[i + 1], b.offsets[j], b.offsets[j + 1]};
+            if (it.a1 > it.a0 && it.b1 > it.b0) items.push_back(it);
+            ++i; ++j;
+        } else if (a.node_ids[i] < b.node_ids[j]) ++i;
+        else ++j;
+    }
+}
+
+extern "C" int orbfe_search_bow(orbfe_matcher* m, int form, const orbfe_bow_side* A, const orbfe_bow_side* B, int nprob,
+                                int b_shared, int nleft_b, int32_t* const* a2b, int32_t* const* b2a, int* nmatches) {
+    if (!m || !A || !B || nprob <= 0 || (form != 0 && form != 1)) return ORBFE_ERR_BAD_ARGUMENT;
+    const int nB = b_shared ? 1 : nprob;
+    for (int p = 0; p < nprob; ++p)
+        if (!valid_side(A[p]) || !A[p].mask || (m->checkOri && !A[p].kps)) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int p = 0; p < nB; ++p)
+        if (!valid_side(B[p]) || (form == 1 && !B[p].mask) || (m->checkOri && !B[p].kps) || B[p].n >= 65536)
+            return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(m->device));
+    // ---- layout: inputs first (one H2D), then outputs (one D2H)
+    size_t u = 0;
+    std::vector<SideLayout> LA(nprob), LB(nB);
+    for (int p = 0; p < nprob; ++p) reserve_side(A[p], false, u, LA[p]);
+    for (int p = 0; p < nB; ++p) reserve_side(B[p], false, u, LB[p]);
+    std::vector<MatchItem> items;
+    for (int p = 0; p < nprob; ++p) join_nodes(p, A[p].fv, B[b_shared ? 0 : p].fv, items);
+    const size_t oProb = stage_take(u, sizeof(MatchProblem) * nprob);
+    const size_t oItems = stage_take(u, sizeof(MatchItem) * std::max<size_t>(items.size(), 1));
+    const size_t inBytes = u;
+    const size_t oOut = stage_take(u, 0);
+    std::vector<size_t> oA2B(nprob), oB2A(nprob);
+    for (int p = 0; p < nprob; ++p) {
+        oA2B[p] = stage_take(u, sizeof(int32_t) * std::max(A[p].n, 1));
+        oB2A[p] = stage_take(u, sizeof(int32_t) * std::max(B[b_shared ? 0 : p].n, 1));
+    }
+    const size_t oCnt = stage_take(u, sizeof(int) * nprob);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));   // the host arena may still be the source / target of an earlier copy
+    for (int p = 0; p < nprob; ++p) fill_side(m->hStage, A[p], LA[p], 1, nullptr);
+    for (int p = 0; p < nB; ++p) fill_side(m->hStage, B[p], LB[p], 1, nullptr);
+    MatchProblem* probs = reinterpret_cast<MatchProblem*>(m->hStage + oProb);
+    for (int p = 0; p < nprob; ++p) {
+        const int q = b_shared ? 0 : p;
+        MatchProblem P;
+        memset(&P, 0, sizeof(P));
+        P.descA = m->dStage + LA[p].desc; P.descB = m->dStage + LB[q].desc;
+        P.idxA = reinterpret_cast<const int32_t*>(m->dStage + LA[p].idx);
+        P.idxB = reinterpret_cast<const int32_t*>(m->dStage + LB[q].idx);
+        P.maskA = m->dStage + LA[p].mask;
+        P.maskB = (form == 1) ? m->dStage + LB[q].mask : nullptr;
+        P.kpA = reinterpret_cast<const float4*>(m->dStage + LA[p].kp);
+        P.kpB = reinterpret_cast<const float4*>(m->dStage + LB[q].kp);
+        P.a2b = reinterpret_cast<int32_t*>(m->dStage + oA2B[p]);
+        P.b2a = reinterpret_cast<int32_t*>(m->dStage + oB2A[p]);
+        P.nA = A[p].n; P.nB = B[q].n;
+        probs[p] = P;
+    }
+    if (!items.empty()) memcpy(m->hStage + oItems, items.data(), sizeof(MatchItem) * items.size());
+    CK(cudaMemcpyAsync(m->dStage, m->hStage, inBytes, cudaMemcpyHostToDevice, m->stream));
+    CK(cudaMemsetAsync(m->dStage + oOut, 0xFF, u - oOut, m->stream));   // every match slot = -1
+    CK(orbfe_launch_bow(m->stream, reinterpret_cast<const MatchProblem*>(m->dStage + oProb), nprob,
+                        reinterpret_cast<const MatchItem*>(m->dStage + oItems), (int)items.size(), m->nnRatio, ORBFE_TH_LOW,
+                        form == 1, form == 0 ? nleft_b : -1, m->checkOri, reinterpret_cast<int*>(m->dStage + oCnt), &m->launches));
+    CK(cudaMemcpyAsync(m->hStage + oOut, m->dStage + oOut, u - oOut, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    for (int p = 0; p < nprob; ++p) {
+        const int q = b_shared ? 0 : p;
+        if (a2b && a2b[p] && A[p].n > 0) memcpy(a2b[p], m->hStage + oA2B[p], sizeof(int32_t) * A[p].n);
+        if (b2a && b2a[p] && B[q].n > 0) memcpy(b2a[p], m->hStage + oB2A[p], sizeof(int32_t) * B[q].n);
+        if (nmatches) nmatches[p] = reinterpret_cast<int*>(m->hStage + oCnt)[p];
+    }
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_bow_side* A, const float* u_right_a,
+                                          const orbfe_bow_side* B, const float* u_right_b, const orbfe_epipolar* geo,
+                                          int only_stereo, int coarse, int32_t* matches12) {
+    if (!m || !A || !B || !geo || !matches12 || !valid_side(*A) || !valid_side(*B) || !A->kps || !B->kps) return ORBFE_ERR_BAD_ARGUMENT;
+    if (!geo->sigma2_b || !geo->scale_b || geo->nlevels < 1 || geo->nlevels > ORBFE_MAX_LEVELS || B->n >= 65536)
+        return ORBFE_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < B->n; ++i)
+        if (B->kps[i].octave < 0 || B->kps[i].octave >= geo->nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(m->device));
+    size_t u = 0;
+    SideLayout LA, LB;
+    reserve_side(*A, true, u, LA);
+    reserve_side(*B, true, u, LB);
+    std::vector<MatchItem> items;
+    join_nodes(0, A->fv, B->fv, items);
+    const size_t oProb = stage_take(u, sizeof(MatchProblem));
+    const size_t oItems = stage_take(u, sizeof(MatchItem) * std::max<size_t>(items.size(), 1));
+    const size_t inBytes = u;
+    const size_t oOut = stage_take(u, 0);
+    const size_t oM = stage_take(u, sizeof(int32_t) * std::max(A->n, 1));
+    const size_t oCnt = stage_take(u, sizeof(int));
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));
+    fill_side(m->hStage, *A, LA, 0, u_right_a);   // no mask = no feature has a MapPoint yet
+    fill_side(m->hStage, *B, LB, 0, u_right_b);
+    MatchProblem P;
+    memset(&P, 0, sizeof(P));
+    P.descA = m->dStage + LA.desc; P.descB = m->dStage + LB.desc;
+    P.idxA = reinterpret_cast<const int32_t*>(m->dStage + LA.idx);
+    P.idxB = reinterpret_cast<const int32_t*>(m->dStage + LB.idx);
+    P.maskA = m->dStage + LA.mask; P.maskB = m->dStage + LB.mask;
+    P.kpA = reinterpret_cast<const float4*>(m->dStage + LA.kp);
+    P.kpB = reinterpret_cast<const float4*>(m->dStage + LB.kp);
+    P.uRightA = reinterpret_cast<const float*>(m->dStage + LA.ur);
+    P.uRightB = reinterpret_cast<const float*>(m->dStage + LB.ur);
+    P.a2b = reinterpret_cast<int32_t*>(m->dStage + oM);
+    P.b2a = nullptr;
+    P.nA = A->n; P.nB = B->n;
+    memcpy(m->hStage + oProb, &P, sizeof(P));
+    if (!items.empty()) memcpy(m->hStage + oItems, items.data(), sizeof(MatchItem) * items.size());
+    TriGeo g;
+    memset(&g, 0, sizeof(g));
+    memcpy(g.F, geo->F12, sizeof(g.F));
+    g.ex = geo->ex; g.ey = geo->ey;
+    for (int l = 0; l < geo->nlevels; ++l) { g.sigma2B[l] = geo->sigma2_b[l]; g.scaleB[l] = geo->scale_b[l]; }
+    CK(cudaMemcpyAsync(m->dStage, m->hStage, inBytes, cudaMemcpyHostToDevice, m->stream));
+    CK(cudaMemsetAsync(m->dStage + oOut, 0xFF, u - oOut, m->stream));
+    CK(orbfe_launch_tri(m->stream, reinterpret_cast<const MatchProblem*>(m->dStage + oProb),
+                        reinterpret_cast<const MatchItem*>(m->dStage + oItems), (int)items.size(), g, only_stereo, coarse,
+                        m->checkOri, reinterpret_cast<int*>(m->dStage + oCnt), &m->launches));
+    CK(cudaMemcpyAsync(m->hStage + oOut, m->dStage + oOut, u - oOut, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    if (A->n > 0) memcpy(matches12, m->hStage + oM, sizeof(int32_t) * A->n);
+    return *reinterpret_cast<int*>(m->hStage + oCnt);
+}

@@ -1,2 +1,35 @@
-"""Prototypes of the matcher entry points of include/orbfe.h (filled as the kernels land)."""
-PROTO = {}
+"""ctypes structures and prototypes of the matcher entry points of include/orbfe.h."""
+import ctypes as C
+
+_P, _I, _F, _PD = C.c_void_p, C.c_int, C.c_float, C.c_ssize_t
+
+
+class FeatureVector(C.Structure):
+    """orbfe_feature_vector"""
+    _fields_ = [("nnodes", _I), ("node_ids", _P), ("offsets", _P), ("indices", _P)]
+
+
+class BowSide(C.Structure):
+    """orbfe_bow_side"""
+    _fields_ = [("desc", _P), ("n", _I), ("fv", FeatureVector), ("mask", _P), ("kps", _P)]
+
+
+class Epipolar(C.Structure):
+    """orbfe_epipolar"""
+    _fields_ = [("F12", _F * 9), ("ex", _F), ("ey", _F), ("sigma2_b", _P), ("scale_b", _P), ("nlevels", _I)]
+
+
+PROTO = {
+    "orbfe_matcher_create": (_I, [_F, _I, _I, C.POINTER(_P)]),
+    "orbfe_matcher_destroy": (None, [_P]),
+    "orbfe_matcher_stream": (_P, [_P]),
+    "orbfe_matcher_synchronize": (_I, [_P]),
+    "orbfe_matcher_launch_count": (C.c_longlong, [_P]),
+    "orbfe_hamming_knn2": (_I, [_P, _P, _I, _P, _I, _P, _P]),
+    "orbfe_hamming_knn2_batch_device": (_I, [_P, _P, _PD, _P, _I, _P, _PD, _P, _I, _I, _P, _P]),
+    "orbfe_match_lapping": (_I, [_P, _P, _I, _P, _I, C.c_double, _P]),
+    "orbfe_stereo_match": (_I, [_P, _P, _I, _P, _I, _F, _F, _P, _P, _I]),
+    "orbfe_stereo_match_batch_device": (_I, [_P, _P, _I, _F, _F, _P, _P]),
+    "orbfe_search_bow": (_I, [_P, _I, C.POINTER(BowSide), C.POINTER(BowSide), _I, _I, _I, C.POINTER(_P), C.POINTER(_P), _P]),
+    "orbfe_search_triangulation": (_I, [_P, C.POINTER(BowSide), _P, C.POINTER(BowSide), _P, C.POINTER(Epipolar), _I, _I, _P]),
+}

@@ -48,3 +48,32 @@ def descriptors(seed, n):
     out = np.empty((n, 32), np.uint8)
     _l().orbfe_synth_descriptors(int(seed), n, out.ctypes.data)
     return out
+
+
+# ---- synthetic matcher inputs: the vocabulary file is not available, so the node of a
+# feature is a deterministic function of its descriptor; MapPoint masks and two-view geometry are seeded.
+def node_of_feature(desc):
+    """<= 100 level-2-like node ids; descriptors that agree in their first two bytes mod 10 share a node."""
+    desc = np.asarray(desc, np.uint8).reshape(-1, 32)
+    return (1 + 10 * (desc[:, 0].astype(np.int64) % 10) + (desc[:, 1].astype(np.int64) % 10)).astype(np.uint32)
+
+
+def _splitmix(seed, n):
+    with np.errstate(over="ignore"):
+        x = np.arange(1, n + 1, dtype=np.uint64) * np.uint64(0x9E3779B97F4A7C15) + np.uint64(seed)
+        x = (x ^ (x >> np.uint64(30))) * np.uint64(0xBF58476D1CE4E5B9)
+        x = (x ^ (x >> np.uint64(27))) * np.uint64(0x94D049BB133111EB)
+        return x ^ (x >> np.uint64(31))
+
+
+def mask(seed, n, percent):
+    """n bytes, 1 with probability percent/100 (integer hash, machine independent)."""
+    return (_splitmix(seed, n) % np.uint64(100) < np.uint64(percent)).astype(np.uint8)
+
+
+def fundamental_x_shift(fx, fy, cx, cy, tx):
+    """F12 = K^-T [t]x R K^-1 (Pinhole.cpp:161-164) for R = I, t12 = (tx, 0, 0), in float32 like cv::Matx33f."""
+    f = np.float32
+    Kinv = np.array([[f(1) / f(fx), 0, -f(cx) / f(fx)], [0, f(1) / f(fy), -f(cy) / f(fy)], [0, 0, 1]], np.float32)
+    tx_ = np.array([[0, 0, 0], [0, 0, -tx], [0, tx, 0]], np.float32)
+    return (Kinv.T @ tx_ @ Kinv).astype(np.float32)

@@ -34,6 +34,15 @@ def lib():
             "orbref_knn2": (None, [_P, _I, _P, _I, _P, _P]),
             "orbref_hamming": (_I, [_P, _P]),
             "orbref_extract_many": (_L, [_I, _F, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I]),
+            "orbref_descriptor_distance": (_I, [_P, _P]),
+            "orbref_three_maxima": (None, [_P, _I, _P]),
+            "orbref_stereo_match": (None, [_P, _P, _P, _P, _I, _P, _P, _I, _F, _F, _P, _P, _P]),
+            "orbref_search_bow": (_I, [_P, _I, _I, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _F, _I, _I, _I, _I,
+                                       _P, _P]),
+            "orbref_search_triangulation": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _P,
+                                                 _P, _P, _F, _F, _I, _I, _I, _P]),
+            "orbref_knn2_ratio": (None, [_P, _I, _P, _I, C.c_double, _P]),
+            "orbref_knn2_many": (_L, [_P, _I, _P, _I, _I, _L, _L, _I]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
@@ -109,3 +118,75 @@ def extract_many(params, frames, lap, nthreads):
     n, h, w = frames.shape
     nf, sf, nl, ini, mn = params
     return lib().orbref_extract_many(nf, sf, nl, ini, mn, _p(frames), n, w, h, int(lap[0]), int(lap[1]), nthreads)
+
+
+# ---- matchers (oracle/cpu_ref/match_ref.cc) ----------------------------------------------------------
+def _pn(a):
+    return None if a is None else a.ctypes.data_as(_P)
+
+
+def descriptor_distance(a, b):
+    a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
+    return lib().orbref_descriptor_distance(_p(a), _p(b))
+
+
+def three_maxima(counts):
+    c = np.ascontiguousarray(counts, np.int32)
+    out = np.zeros(3, np.int32)
+    lib().orbref_three_maxima(_p(c), len(c), _p(out))
+    return tuple(int(v) for v in out)
+
+
+def stereo_match(ref_left, ref_right, kpL, descL, kpR, descR, bf, b):
+    """ref_left / ref_right: OrbRef objects that have just extracted the two views (their pyramids are read)."""
+    kpL, kpR = np.ascontiguousarray(kpL), np.ascontiguousarray(kpR)
+    descL, descR = np.ascontiguousarray(descL), np.ascontiguousarray(descR)
+    u = np.zeros(len(kpL), np.float32)
+    d = np.zeros(len(kpL), np.float32)
+    sad = np.zeros(len(kpL), np.int32)
+    lib().orbref_stereo_match(ref_left.h, ref_right.h, _p(kpL), _p(descL), len(kpL), _p(kpR), _p(descR), len(kpR), bf, b, _p(u),
+                              _p(d), _p(sad))
+    return u, d, sad
+
+
+def _fv(fv):
+    return len(fv.node_ids), _p(fv.node_ids), _p(fv.offsets), _p(fv.indices)
+
+
+def search_bow(descA, fvA, maskA, angA, descB, fvB, maskB, angB, ratio, check_ori, strict, nleft=-1, th=50):
+    descA, descB = np.ascontiguousarray(descA, np.uint8), np.ascontiguousarray(descB, np.uint8)
+    maskA = np.ascontiguousarray(maskA).astype(np.uint8)
+    maskB = None if maskB is None else np.ascontiguousarray(maskB).astype(np.uint8)
+    angA, angB = np.ascontiguousarray(angA, np.float32), np.ascontiguousarray(angB, np.float32)
+    a2b = np.zeros(max(len(descA), 1), np.int32)
+    b2a = np.zeros(max(len(descB), 1), np.int32)
+    n = lib().orbref_search_bow(_p(descA), len(descA), *_fv(fvA), _p(maskA), _p(angA), _p(descB), len(descB), *_fv(fvB),
+                                _pn(maskB), _p(angB), ratio, int(check_ori), th, int(strict), nleft, _p(a2b), _p(b2a))
+    return a2b[:len(descA)], b2a[:len(descB)], n
+
+
+def search_triangulation(kpA, descA, fvA, mpA, urA, kpB, descB, fvB, mpB, urB, sigma2, scale, F12, ep, check_ori, only_stereo,
+                         coarse):
+    kpA, kpB = np.ascontiguousarray(kpA), np.ascontiguousarray(kpB)
+    descA, descB = np.ascontiguousarray(descA, np.uint8), np.ascontiguousarray(descB, np.uint8)
+    mpA, mpB = np.ascontiguousarray(mpA).astype(np.uint8), np.ascontiguousarray(mpB).astype(np.uint8)
+    urA, urB = np.ascontiguousarray(urA, np.float32), np.ascontiguousarray(urB, np.float32)
+    sigma2, scale = np.ascontiguousarray(sigma2, np.float32), np.ascontiguousarray(scale, np.float32)
+    F12 = np.ascontiguousarray(F12, np.float32).reshape(9)
+    m12 = np.zeros(max(len(descA), 1), np.int32)
+    n = lib().orbref_search_triangulation(_p(kpA), _p(descA), len(descA), *_fv(fvA), _p(mpA), _p(urA), _p(kpB), _p(descB),
+                                          len(descB), *_fv(fvB), _p(mpB), _p(urB), _p(sigma2), _p(scale), _p(F12), float(ep[0]),
+                                          float(ep[1]), int(check_ori), int(only_stereo), int(coarse), _p(m12))
+    return m12[:len(descA)], n
+
+
+def knn2_ratio(q, t, ratio=0.7):
+    q, t = np.ascontiguousarray(q, np.uint8), np.ascontiguousarray(t, np.uint8)
+    m = np.zeros(max(len(q), 1), np.int32)
+    lib().orbref_knn2_ratio(_p(q), len(q), _p(t), len(t), ratio, _p(m))
+    return m[:len(q)]
+
+
+def knn2_many(q, t, npairs, qstride, tstride, nthreads):
+    """q, t: arrays holding `npairs` problems (nq x 32, nt x 32 each) at the given byte strides."""
+    return lib().orbref_knn2_many(_p(q), q.shape[-2], _p(t), t.shape[-2], npairs, qstride, tstride, nthreads)

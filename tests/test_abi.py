@@ -19,6 +19,7 @@ def declared_functions():
     txt = open(HEADER).read()
     txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
     txt = re.sub(r"//[^\n]*", "", txt)
+    txt = re.sub(r"static inline[^{;]*\{.*?\n\}", "", txt, flags=re.S)   # host-side inline helpers are not exports
     return sorted(set(re.findall(r"\b(orbfe_[a-z0-9_]+)\s*\(", txt)))
 
 
@@ -73,3 +74,6 @@ def test_fails_loudly_without_gpu():
     with pytest.raises(orbfe.OrbfeError) as e:
         orbfe.ORBextractor(1000, 1.2, 8, 20, 7)
     assert e.value.status == -6   # ORBFE_ERR_NO_DEVICE
+    with pytest.raises(orbfe.OrbfeError) as e:
+        orbfe.ORBmatcher()
+    assert e.value.status == -6

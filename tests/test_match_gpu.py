@@ -1,0 +1,228 @@
+"""GPU parity of the matchers (through the C ABI) against the CPU oracle on identical inputs and
+against the committed golden vectors.  Bar (north_star): match indices / distances bit-exact given
+identical descriptors; mvuRight / mvDepth float32-exact."""
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+import match_cases as mc
+import oracle_binding as ob
+import orbfe
+from common import GOLDEN
+from oracle_binding import OrbRef
+
+pytestmark = pytest.mark.gpu
+
+
+def crc(*arrays):
+    c = 0
+    for a in arrays:
+        c = zlib.crc32(np.ascontiguousarray(a).tobytes(), c)
+    return c & 0xFFFFFFFF
+
+
+def gold(name):
+    return np.load(os.path.join(GOLDEN, f"match_{name}.npz"))
+
+
+def extract_ref(img, nf, lap):
+    ref = OrbRef(nf, *mc.ORB)
+    mono, k, d = ref(img, lap)
+    return mono, k, d, ref
+
+
+@pytest.fixture(scope="module")
+def matcher():
+    return {r: orbfe.ORBmatcher(r, True) for r in (0.7, 0.8)}
+
+
+def test_knn2_ties_and_golden():
+    m = orbfe.ORBmatcher()
+    q, t = mc.knn_inputs()
+    g = gold("knn_ties")
+    idx, dist = m.knn2(q, t)
+    assert np.array_equal(idx, g["idx"]) and np.array_equal(dist, g["dist"])
+    match, n = m.match_lapping(q, t, 0.7)
+    assert np.array_equal(match, g["match"]) and n == (g["match"] >= 0).sum()
+
+
+@pytest.mark.parametrize("nq,nt", [(1, 1), (3, 1), (5, 2), (127, 129), (128, 128), (1000, 4000), (4000, 4000), (300, 70000),
+                                   (0, 10), (10, 0)])
+def test_knn2_sizes(nq, nt):
+    """Ragged / empty / split-train shapes against the oracle (ties resolved to the lowest train index)."""
+    m = orbfe.ORBmatcher()
+    q = orbfe.synth.descriptors(nq * 31 + nt, max(nq, 1))[:nq]
+    t = orbfe.synth.descriptors(nq + nt * 17, max(nt, 1))[:nt]
+    if nt > 100 and nq > 2:
+        t[nt // 2] = t[3]        # ties across tiles / splits
+        q[2] = t[3]
+    idx, dist = m.knn2(q, t)
+    ridx, rdist = ob.knn2(q, t) if nq else (idx, dist)
+    assert np.array_equal(idx, ridx) and np.array_equal(dist, rdist)
+
+
+def test_knn2_batch_device_from_extractor_results():
+    """Sequence matching frame t <-> t+1 straight from the extractor's device results."""
+    import torch
+    w, h, nf, B = 752, 480, 1000, 4
+    imgs = orbfe.synth.frames(3000, B, w, h)
+    ex = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h, max_batch=B)
+    res = ex.extract_batch(imgs, (0, 0))
+    d_kps, d_desc, d_n, d_mono, cap = ex.device_results()
+    m = orbfe.ORBmatcher()
+    idx = torch.full((B - 1, cap, 2), -7, dtype=torch.int32, device="cuda")
+    dist = torch.full((B - 1, cap, 2), -7, dtype=torch.int32, device="cuda")
+    m.knn2_batch_device(d_desc, cap * 32, d_n, cap, d_desc + cap * 32, cap * 32, d_n + 4, cap, B - 1, idx.data_ptr(),
+                        dist.data_ptr())
+    m.synchronize()
+    idx, dist = idx.cpu().numpy(), dist.cpu().numpy()
+    for b in range(B - 1):
+        q, t = res[b][2], res[b + 1][2]
+        ridx, rdist = ob.knn2(q, t)
+        assert np.array_equal(idx[b, :len(q)], ridx) and np.array_equal(dist[b, :len(q)], rdist)
+
+
+@pytest.mark.parametrize("name", list(mc.LAP_CASES))
+def test_lapping_match(name):
+    c = mc.lap_inputs(name, extract_ref)
+    g = gold(name)
+    m = orbfe.ORBmatcher()
+    match, n = m.match_lapping(c["q"], c["t"], 0.7)
+    assert np.array_equal(match, ob.knn2_ratio(c["q"], c["t"], 0.7))
+    if crc(c["q"], c["t"]) == int(g["in_crc"]):
+        assert np.array_equal(match, g["match"])
+    assert n == (match >= 0).sum() > 100
+
+
+@pytest.mark.parametrize("name", list(mc.STEREO_CASES))
+@pytest.mark.parametrize("mode", ["two_handles", "batch_pair"])
+def test_stereo_match(name, mode):
+    cam, nf, seed = mc.STEREO_CASES[name]
+    w, h = cam["w"], cam["h"]
+    imL, imR = orbfe.synth.stereo_pair(seed, w, h)
+    bf = float(np.float32(cam["bf"]))
+    b = float(np.float32(np.float32(cam["bf"]) / np.float32(cam["fx"])))
+    m = orbfe.ORBmatcher()
+    if mode == "two_handles":      # Frame.cc:119-122: one extractor per eye
+        exL = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h)
+        exR = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h)
+        _, kL, dL = exL(imL, None, (0, 0))
+        _, kR, dR = exR(imR, None, (0, 0))
+        u, d, n = m.stereo_match(exL, exR, bf, b)
+    else:                          # the pair as one batch of two on one handle
+        ex = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h, max_batch=2)
+        (_, kL, dL), (_, kR, dR) = ex.extract_batch(np.stack([imL, imR]), (0, 0))
+        u, d, n = m.stereo_match(ex, ex, bf, b, 0, 1)
+    u, d = u[:len(kL)], d[:len(kL)]
+    # oracle on the very same keypoints / descriptors (its pyramids are bit-identical to the device's)
+    rL, rR = OrbRef(nf, *mc.ORB), OrbRef(nf, *mc.ORB)
+    rL(imL, (0, 0))
+    rR(imR, (0, 0))
+    ru, rd, rsad = ob.stereo_match(rL, rR, kL, dL, kR, dR, bf, b)
+    assert np.array_equal(d > 0, rd > 0)
+    assert np.array_equal(u, ru) and np.array_equal(d, rd)
+    assert n == (rd > 0).sum() > 0.4 * len(kL)
+    g = gold(name)
+    if crc(kL, dL, kR, dR) == int(g["in_crc"]):
+        assert np.array_equal(u, g["u_right"]) and np.array_equal(d, g["depth"])
+
+
+def test_stereo_batch_device():
+    import torch
+    cam, nf, seed = mc.STEREO_CASES["stereo_euroc"]
+    w, h, P = cam["w"], cam["h"], 3
+    ims = []
+    for p in range(P):
+        ims += list(orbfe.synth.stereo_pair(seed + p, w, h))
+    ex = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h, max_batch=2 * P)
+    res = ex.extract_batch(np.stack(ims), (0, 0))
+    bf = float(np.float32(cam["bf"]))
+    b = float(np.float32(np.float32(cam["bf"]) / np.float32(cam["fx"])))
+    m = orbfe.ORBmatcher()
+    du = torch.zeros((P, ex.cap), dtype=torch.float32, device="cuda")
+    dd = torch.zeros((P, ex.cap), dtype=torch.float32, device="cuda")
+    m.stereo_match_batch_device(ex, P, bf, b, du.data_ptr(), dd.data_ptr())
+    m.synchronize()
+    du, dd = du.cpu().numpy(), dd.cpu().numpy()
+    for p in range(P):
+        (_, kL, dL), (_, kR, dR) = res[2 * p], res[2 * p + 1]
+        rL, rR = OrbRef(nf, *mc.ORB), OrbRef(nf, *mc.ORB)
+        rL(ims[2 * p], (0, 0))
+        rR(ims[2 * p + 1], (0, 0))
+        ru, rd, _ = ob.stereo_match(rL, rR, kL, dL, kR, dR, bf, b)
+        assert np.array_equal(du[p, :len(kL)], ru) and np.array_equal(dd[p, :len(kL)], rd)
+
+
+@pytest.mark.parametrize("name", list(mc.BOW_CASES))
+def test_search_by_bow(name, matcher):
+    c = mc.bow_inputs(name, extract_ref)
+    g = gold(name)
+    same_inputs = crc(c["d1"], c["d2"], c["mp1"], c["mp2"]) == int(g["in_crc"])
+    m7 = orbfe.ORBmatcher(0.7, c["check_ori"])
+    m8 = orbfe.ORBmatcher(0.8, c["check_ori"])
+    b2a, n = m7.SearchByBoW_KF_F(c["d1"], c["fv1"], c["mp1"], c["k1"], c["d2"], c["fv2"], c["k2"], c["nleft"])
+    _, rb2a, rn = ob.search_bow(c["d1"], c["fv1"], c["mp1"], c["k1"]["angle"], c["d2"], c["fv2"], None, c["k2"]["angle"], 0.7,
+                                c["check_ori"], strict=False, nleft=c["nleft"])
+    assert n == rn and np.array_equal(b2a, rb2a)
+    if same_inputs:
+        assert n == int(g["n_kf_f"]) and np.array_equal(b2a, g["kf_f"])
+    a2b, n = m8.SearchByBoW_KF_KF(c["d1"], c["fv1"], c["mp1"], c["k1"], c["d2"], c["fv2"], c["mp2"], c["k2"])
+    ra2b, _, rn = ob.search_bow(c["d1"], c["fv1"], c["mp1"], c["k1"]["angle"], c["d2"], c["fv2"], c["mp2"], c["k2"]["angle"], 0.8,
+                                c["check_ori"], strict=True)
+    assert n == rn and np.array_equal(a2b, ra2b)
+    if same_inputs:
+        assert n == int(g["n_kf_kf"]) and np.array_equal(a2b, g["kf_kf"])
+
+
+def test_search_by_bow_many_keyframes_one_frame():
+    """Relocalisation shape: several keyframes against one frame in one call; each equals the single call."""
+    cam, nf = mc.EUROC, 1000
+    w, h = cam["w"], cam["h"]
+
+    def ext(seed, shift):
+        return extract_ref(orbfe.synth.frame(seed, w, h, 0, shift), nf, (0, 0))
+
+    _, kF, dF, _ = ext(4000, 4)
+    kfs = []
+    for i, shift in enumerate((0, 2, 7, 11)):
+        _, k, d, _ = ext(4000, shift)
+        kfs.append((d, mc.fv_of(d), orbfe.synth.mask(100 + i, len(d), 70), k))
+    _, k, d, _ = ext(4001, 0)                       # an unrelated keyframe: few or no matches
+    kfs.append((d, mc.fv_of(d), orbfe.synth.mask(200, len(d), 70), k))
+    m = orbfe.ORBmatcher(0.75, True)
+    many, counts = m.SearchByBoW_KFs_F(kfs, dF, mc.fv_of(dF), kF)
+    for (d, fv, mp, k), got, cnt in zip(kfs, many, counts):
+        _, rb2a, rn = ob.search_bow(d, fv, mp, k["angle"], dF, mc.fv_of(dF), None, kF["angle"], 0.75, True, strict=False)
+        assert cnt == rn and np.array_equal(got, rb2a)
+    assert counts[0] > 100 and counts[-1] < counts[0] // 4
+
+
+@pytest.mark.parametrize("name", list(mc.TRI_CASES))
+def test_search_for_triangulation(name):
+    sc, isc, s2, is2, per, umax = OrbRef(1000, *mc.ORB).tables()
+    c = mc.tri_inputs(name, extract_ref, sc, s2)
+    g = gold(name)
+    m = orbfe.ORBmatcher(0.6, c["check_ori"])
+    pairs, n, m12 = m.SearchForTriangulation(c["d1"], c["fv1"], c["mp1"], c["k1"], c["ur1"], c["d2"], c["fv2"], c["mp2"], c["k2"],
+                                             c["ur2"], c["F12"], c["ep"], s2, sc, c["only_stereo"], c["coarse"])
+    rm12, rn = ob.search_triangulation(c["k1"], c["d1"], c["fv1"], c["mp1"], c["ur1"], c["k2"], c["d2"], c["fv2"], c["mp2"],
+                                       c["ur2"], s2, sc, c["F12"], c["ep"], c["check_ori"], c["only_stereo"], c["coarse"])
+    assert n == rn and np.array_equal(m12, rm12)
+    assert len(pairs) == n and np.all(np.diff(pairs[:, 0]) > 0)
+    if crc(c["d1"], c["d2"], c["mp1"], c["mp2"], c["F12"]) == int(g["in_crc"]):
+        assert n == int(g["n"]) and np.array_equal(m12, g["m12"])
+
+
+def test_empty_and_disjoint_feature_vectors():
+    m = orbfe.ORBmatcher(0.7, True)
+    d1, d2 = orbfe.synth.descriptors(1, 50), orbfe.synth.descriptors(2, 60)
+    k1, k2 = np.zeros(50, orbfe.KEYPOINT_DTYPE), np.zeros(60, orbfe.KEYPOINT_DTYPE)
+    fv1 = orbfe.FeatureVectorCSR.from_node_of_feature(np.full(50, 3))
+    fv2 = orbfe.FeatureVectorCSR.from_node_of_feature(np.full(60, 4))      # no shared node
+    b2a, n = m.SearchByBoW_KF_F(d1, fv1, np.ones(50, np.uint8), k1, d2, fv2, k2)
+    assert n == 0 and (b2a == -1).all() and len(b2a) == 60
+    a2b, n = m.SearchByBoW_KF_KF(d1, fv1, np.zeros(50, np.uint8), k1, d2, fv1.__class__.from_node_of_feature(np.full(60, 3)),
+                                 np.ones(60, np.uint8), k2)             # shared node, but no MapPoints in KF1
+    assert n == 0 and (a2b == -1).all()

@@ -1,0 +1,124 @@
+"""CPU: the C++ matcher oracle (oracle/cpu_ref/match_ref.cc) against the committed golden vectors
+produced by the independent Python restatement (oracle/py/match_py.py + cv2), on inputs rebuilt with
+the C++ extractor oracle.  Plus small known-answer tests of the primitives."""
+import os
+import zlib
+
+import numpy as np
+import pytest
+
+import match_cases as mc
+import oracle_binding as ob
+import orbfe
+from common import GOLDEN
+from oracle_binding import OrbRef
+
+
+def crc(*arrays):
+    c = 0
+    for a in arrays:
+        c = zlib.crc32(np.ascontiguousarray(a).tobytes(), c)
+    return c & 0xFFFFFFFF
+
+
+def extract(img, nf, lap):
+    ref = OrbRef(nf, *mc.ORB)
+    mono, k, d = ref(img, lap)
+    return mono, k, d, ref
+
+
+def gold(name):
+    return np.load(os.path.join(GOLDEN, f"match_{name}.npz"))
+
+
+def tables():
+    return OrbRef(1000, *mc.ORB).tables()
+
+
+def test_descriptor_distance_swar_equals_popcount():
+    d = orbfe.synth.descriptors(3, 64)
+    for i in range(0, 64, 2):
+        want = int(np.unpackbits(d[i] ^ d[i + 1]).sum())
+        assert ob.descriptor_distance(d[i], d[i + 1]) == want
+        assert orbfe.ORBmatcher.DescriptorDistance(d[i], d[i + 1]) == want
+    assert ob.descriptor_distance(d[0], d[0]) == 0
+    assert ob.descriptor_distance(np.zeros(32, np.uint8), np.full(32, 255, np.uint8)) == 256
+
+
+def test_three_maxima_rules():
+    """ORBmatcher.cc:2515-2556: strict '>' keeps the first of equal bins, the 0.1*max1 cut drops weak bins."""
+    h = [0] * 30
+    h[3], h[7], h[9] = 50, 50, 4
+    assert ob.three_maxima(h) == (3, 7, -1)          # 4 < 0.1 * 50
+    h[9] = 5
+    assert ob.three_maxima(h) == (3, 7, 9)
+    assert ob.three_maxima([0] * 30) == (-1, -1, -1)
+    h = [0] * 30
+    h[12] = 9
+    assert ob.three_maxima(h) == (12, -1, -1)
+
+
+@pytest.mark.parametrize("name", list(mc.STEREO_CASES))
+def test_stereo_matches_golden(name):
+    c = mc.stereo_inputs(name, extract)
+    (_, kL, dL, rL), (_, kR, dR, rR) = c["L"], c["R"]
+    g = gold(name)
+    assert crc(kL, dL, kR, dR) == int(g["in_crc"])
+    u, d, sad = ob.stereo_match(rL, rR, kL, dL, kR, dR, c["bf"], c["b"])
+    assert np.array_equal(sad, g["sad"])
+    assert np.array_equal(u, g["u_right"]) and np.array_equal(d, g["depth"])   # float32-exact
+    assert (d > 0).sum() > 0.4 * len(kL)
+    # ground truth of the synthetic pair: disparity is one of three integer planes
+    ok = d > 0
+    disp = kL["x"][ok] - u[ok]
+    true = np.array([orbfe.synth.disparity(int(y), c["cam"]["h"]) for y in kL["y"][ok]])
+    assert np.mean(np.abs(disp - true) < 1.5) > 0.95
+
+
+@pytest.mark.parametrize("name", list(mc.BOW_CASES))
+def test_bow_matches_golden(name):
+    c = mc.bow_inputs(name, extract)
+    g = gold(name)
+    assert crc(c["d1"], c["d2"], c["mp1"], c["mp2"]) == int(g["in_crc"])
+    a2b, b2a, n = ob.search_bow(c["d1"], c["fv1"], c["mp1"], c["k1"]["angle"], c["d2"], c["fv2"], None, c["k2"]["angle"], 0.7,
+                                c["check_ori"], strict=False, nleft=c["nleft"])
+    assert n == int(g["n_kf_f"]) and np.array_equal(b2a, g["kf_f"])
+    assert n > 100
+    a2b, b2a, n = ob.search_bow(c["d1"], c["fv1"], c["mp1"], c["k1"]["angle"], c["d2"], c["fv2"], c["mp2"], c["k2"]["angle"],
+                                0.8, c["check_ori"], strict=True)
+    assert n == int(g["n_kf_kf"]) and np.array_equal(a2b, g["kf_kf"])
+    assert n == (a2b >= 0).sum() == (b2a >= 0).sum()
+
+
+@pytest.mark.parametrize("name", list(mc.TRI_CASES))
+def test_triangulation_matches_golden(name):
+    sc, isc, s2, is2, per, umax = tables()
+    c = mc.tri_inputs(name, extract, sc, s2)
+    g = gold(name)
+    assert crc(c["d1"], c["d2"], c["mp1"], c["mp2"], c["F12"]) == int(g["in_crc"])
+    m12, n = ob.search_triangulation(c["k1"], c["d1"], c["fv1"], c["mp1"], c["ur1"], c["k2"], c["d2"], c["fv2"], c["mp2"],
+                                     c["ur2"], s2, sc, c["F12"], c["ep"], c["check_ori"], c["only_stereo"], c["coarse"])
+    assert n == int(g["n"]) and np.array_equal(m12, g["m12"])
+    assert n > 30
+
+
+@pytest.mark.parametrize("name", list(mc.LAP_CASES))
+def test_lapping_matches_golden(name):
+    c = mc.lap_inputs(name, extract)
+    g = gold(name)
+    assert crc(c["q"], c["t"]) == int(g["in_crc"])
+    idx, dist = ob.knn2(c["q"], c["t"])
+    assert np.array_equal(idx, g["idx"]) and np.array_equal(dist, g["dist"])
+    assert np.array_equal(ob.knn2_ratio(c["q"], c["t"], 0.7), g["match"])
+
+
+def test_knn2_tie_rule_golden():
+    q, t = mc.knn_inputs()
+    g = gold("knn_ties")
+    idx, dist = ob.knn2(q, t)
+    assert np.array_equal(idx, g["idx"]) and np.array_equal(dist, g["dist"])
+    assert idx[0].tolist() == [7, 100] and idx[5].tolist() == [1500, 1501]
+    # fewer than two train rows: missing neighbours are -1 (Frame.cc:1141 checks size() >= 2)
+    idx, dist = ob.knn2(q[:3], t[:1])
+    assert idx[:, 1].tolist() == [-1, -1, -1] and (idx[:, 0] == 0).all()
+    assert (ob.knn2_ratio(q[:3], t[:1]) == -1).all()
