@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(256) k_stereo_filter(StereoSide L, float* __re
 
 cudaError_t orbfe_launch_stereo(cudaStream_t st, const orbfe_handle* hl, int frameL0, int frameLStep, const orbfe_handle* hr,
                                 int frameR0, int frameRStep, int npairs, float bf, float b, float* dURight, float* dDepth,
-                                int* dSad, int* dCount, long long* launches) {
+                                int* dSad, int* dCount, int outStride, long long* launches) {
     StereoSide L{hl->dKps, hl->dDesc, hl->dN, hl->dPyr, hl->dGeom, hl->kpPerFrame, frameL0, frameLStep};
     StereoSide R{hr->dKps, hr->dDesc, hr->dN, hr->dPyr, hr->dGeom, hr->kpPerFrame, frameR0, frameRStep};
     StereoTables tb;
@@ -236,9 +236,9 @@ cudaError_t orbfe_launch_stereo(cudaStream_t st, const orbfe_handle* hl, int fra
         configured = smem;
     }
     dim3 grid((hl->kpPerFrame + ST_THREADS - 1) / ST_THREADS, npairs);
-    k_stereo_search<<<grid, ST_THREADS, smem, st>>>(L, R, tb, bf, b, dURight, dDepth, dSad, hl->kpPerFrame);
+    k_stereo_search<<<grid, ST_THREADS, smem, st>>>(L, R, tb, bf, b, dURight, dDepth, dSad, outStride);
     ++*launches;
-    k_stereo_filter<<<npairs, 256, 0, st>>>(L, dURight, dDepth, dSad, hl->kpPerFrame, dCount);
+    k_stereo_filter<<<npairs, 256, 0, st>>>(L, dURight, dDepth, dSad, outStride, dCount);
     ++*launches;
     return cudaGetLastError();
 }

@@ -44,7 +44,7 @@ cudaError_t orbfe_launch_ratio_filter(cudaStream_t st, const int32_t* dIdx2, con
                                       int32_t* dMatch, int* dCount, long long* launches);
 cudaError_t orbfe_launch_stereo(cudaStream_t st, const orbfe_handle* hl, int frameL0, int frameLStep, const orbfe_handle* hr,
                                 int frameR0, int frameRStep, int npairs, float bf, float b, float* dURight, float* dDepth,
-                                int* dSad, int* dCount, long long* launches);
+                                int* dSad, int* dCount, int outStride, long long* launches);
 cudaError_t orbfe_launch_bow(cudaStream_t st, const MatchProblem* dProbs, int nprob, const MatchItem* dItems, int nitems,
                              float nnRatio, int th, int strictTh, int nleftB, int checkOri, int* dCounts, long long* launches);
 cudaError_t orbfe_launch_tri(cudaStream_t st, const MatchProblem* dProbs, const MatchItem* dItems, int nitems, const TriGeo& geo,

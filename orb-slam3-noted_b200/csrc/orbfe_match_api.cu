@@ -201,12 +201,12 @@ extern "C" int orbfe_stereo_match_batch_device(orbfe_matcher* m, orbfe_handle* h
     if (h->device != m->device) return ORBFE_ERR_BAD_ARGUMENT;
     if (h->lastBatch < 2 * npairs) return ORBFE_ERR_NOT_READY;
     CK(cudaSetDevice(m->device));
-    int st = ensure_scratch(m, sizeof(int) * ((size_t)npairs * h->kpPerFrame + npairs));
+    int st = ensure_scratch(m, sizeof(int) * ((size_t)npairs * h->kpCapPerFrame + npairs));
     if (st != ORBFE_OK) return st;
     if ((st = wait_for(m, h)) != ORBFE_OK) return st;
     int* dSad = reinterpret_cast<int*>(m->dScratch);
-    int* dCount = dSad + (size_t)npairs * h->kpPerFrame;
-    CK(orbfe_launch_stereo(m->stream, h, 0, 2, h, 1, 2, npairs, bf, b, d_u_right, d_depth, dSad, dCount, &m->launches));
+    int* dCount = dSad + (size_t)npairs * h->kpCapPerFrame;
+    CK(orbfe_launch_stereo(m->stream, h, 0, 2, h, 1, 2, npairs, bf, b, d_u_right, d_depth, dSad, dCount, h->kpCapPerFrame, &m->launches));
     return ORBFE_OK;
 }
 
@@ -229,7 +229,7 @@ extern "C" int orbfe_stereo_match(orbfe_matcher* m, orbfe_handle* left, int fram
     int* dCount = dSad + kpf;
     float* dU = reinterpret_cast<float*>(m->dStage + oU);
     float* dD = reinterpret_cast<float*>(m->dStage + oD);
-    CK(orbfe_launch_stereo(m->stream, left, frame_l, 0, right, frame_r, 0, 1, bf, b, dU, dD, dSad, dCount, &m->launches));
+    CK(orbfe_launch_stereo(m->stream, left, frame_l, 0, right, frame_r, 0, 1, bf, b, dU, dD, dSad, dCount, kpf, &m->launches));
     CK(cudaMemcpyAsync(m->dStage + oN, left->dN + frame_l, sizeof(int), cudaMemcpyDeviceToDevice, m->stream));
     CK(cudaMemcpyAsync(m->dStage + oN + 4, dCount, sizeof(int), cudaMemcpyDeviceToDevice, m->stream));
     CK(cudaMemcpyAsync(m->hStage, m->dStage, u, cudaMemcpyDeviceToHost, m->stream));
