@@ -157,6 +157,100 @@ def run_reference(args):
     }))
 
 
+# ---- matching leg: brute-force Hamming 2-NN between consecutive 1920x1080 frames (BASELINE config 5) ----
+MW, MH, MNF = 1920, 1080, 4000
+MATCH_WORKLOAD = "brute-force Hamming 2-NN (BFMatcher knnMatch k=2), consecutive 1920x1080 frames, 4000 features/frame"
+
+
+def cpu_pairs_per_s(descs, nthreads, budget_s):
+    """oracle knn2 (one problem per thread) on consecutive frames of `descs` [(n, 32) arrays]; returns pairs/s."""
+    import numpy as np
+    ob = _oracle()
+    n = min(len(d) for d in descs)
+    arr = np.ascontiguousarray(np.stack([d[:n] for d in descs]))
+    npairs = len(descs) - 1
+    t0 = time.perf_counter()
+    ob.knn2_many(arr, arr[1:], min(npairs, nthreads), n * 32, n * 32, nthreads)
+    rate = min(npairs, nthreads) * n * n / (time.perf_counter() - t0)
+    reps = max(1, int(budget_s * rate / (npairs * n * n)))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        ob.knn2_many(arr, arr[1:], npairs, n * 32, n * 32, nthreads)
+    dt = time.perf_counter() - t0
+    return reps * npairs * n * n / dt, reps * npairs, n
+
+
+def run_matching(args, torch, orbfe, rank, local, world, barrier, dist):
+    """Returns the `matching` object of the JSON line (rank 0) or None."""
+    import numpy as np
+    B, K, Wm = args.match_frames, args.steps, args.warmup
+    ex = orbfe.ORBextractor(MNF, 1.2, 8, 20, 7, device=local, max_width=MW, max_height=MH, max_batch=B)
+    frames = orbfe.synth.frames(1400 + 7919 * rank, B, MW, MH)
+    res = ex.extract_batch(frames, (0, 0))
+    d_kps, d_desc, d_n, d_mono, cap = ex.device_results()
+    n = np.array([len(r[1]) for r in res], np.int64)
+    pairs_per_step = int((n[:-1] * n[1:]).sum())
+    m = orbfe.ORBmatcher(0.7, True, device=local)
+    idx = torch.empty((B - 1, cap, 2), dtype=torch.int32, device="cuda")
+    dst = torch.empty((B - 1, cap, 2), dtype=torch.int32, device="cuda")
+    stream = torch.cuda.ExternalStream(m.stream(), device=local)
+
+    def step():
+        m.knn2_batch_device(d_desc, cap * 32, d_n, cap, d_desc + cap * 32, cap * 32, d_n + 4, cap, B - 1, idx.data_ptr(),
+                            dst.data_ptr())
+
+    for _ in range(Wm):
+        step()
+    m.synchronize()
+    barrier()
+    l0 = m.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(K):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = m.launch_count() - l0
+    # end to end: the host-buffer call, one frame pair per call
+    descs = [r[2] for r in res]
+    for _ in range(Wm):
+        m.knn2(descs[0], descs[1])
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(K):
+        for b in range(B - 1):
+            m.knn2(descs[b], descs[b + 1])
+    barrier()
+    e2e_s = time.perf_counter() - t0
+    if world > 1:
+        t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1]) / 1e3
+    if rank != 0:
+        return None
+    value = world * K * pairs_per_step / (ms / 1e3)
+    popc = orbfe.measure_popc_peak(local)
+    out = {
+        "metric": "Hamming matches/s (descriptor pairs evaluated per second)", "value": value, "unit": "pairs/s",
+        "ms_per_step": ms / K, "gpu_launches": int(launches),
+        "config": {"workload": MATCH_WORKLOAD, "frames_per_step_per_gpu": B, "pairs_of_frames_per_step": B - 1,
+                   "descriptor_pairs_per_step_per_gpu": pairs_per_step, "mean_features": float(n.mean())},
+        "e2e": {"value": world * K * pairs_per_step / e2e_s, "unit": "pairs/s",
+                "h2d_bytes_per_step": int(32 * (n[:-1] + n[1:]).sum()), "d2h_bytes_per_step": int(16 * n[:-1].sum()),
+                "api": "orbfe_hamming_knn2 (host buffers), one call per frame pair"},
+        "roofline": {"bound": "int-popc", "kernel": "k_knn2", "achieved": value / world * 8 / 1e12, "peak": popc / 1e12,
+                     "unit": "Tpopc/s", "frac": value / world * 8 / popc, "peak_source": "measured (orbfe_measure_popc_peak)",
+                     "popc_per_pair": 8},
+    }
+    if world == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        v, nprob, nn = cpu_pairs_per_s(descs[:min(B, cores + 1)], cores, args.cpu_seconds / 2)
+        out["cpu_baseline"] = {"value": v, "unit": "pairs/s", "cores": cores, "kind": "port",
+                               "sample": f"{nprob} knn2 problems of {nn}x{nn} descriptors over {cores} host threads (oracle/cpu_ref)"}
+    return out
+
+
 # ---- GPU arm ---------------------------------------------------------------------------------------
 def run_orbfe(args):
     import numpy as np
@@ -248,6 +342,7 @@ def run_orbfe(args):
         tl = torch.tensor([launches], dtype=torch.int64, device="cuda")
         dist.all_reduce(tl)
         launches = int(tl[0])
+    matching = None if args.no_match else run_matching(args, torch, orbfe, rank, local, world, barrier, dist)
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -292,6 +387,8 @@ def run_orbfe(args):
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"{nfr} frames of the same workload, frame-parallel over {cores} host threads "
                                          "(oracle/cpu_ref, one extractor per thread)"}
+    if matching is not None:
+        out["matching"] = matching
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -307,6 +404,8 @@ def main():
     ap.add_argument("--impl", default="orbfe", choices=["orbfe", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-match", action="store_true", help="skip the matching leg")
+    ap.add_argument("--match-frames", type=int, default=24, help="1920x1080 frames per matching step per GPU")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

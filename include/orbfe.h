@@ -246,6 +246,11 @@ int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_bow_side* A, const 
                                const float* u_right_b, const orbfe_epipolar* geo, int only_stereo, int coarse,
                                int32_t* matches12);
 
+/* Measured integer-pipe ceiling of the Hamming matchers: sustained 32-bit POPC instructions per
+ * second of device `device` (register-only micro-benchmark, ~10 ms).  One 256-bit descriptor pair
+ * costs 8 POPC, so popc_per_s / 8 is the roofline of the matching kernels in pairs/s. */
+int orbfe_measure_popc_peak(int device, double* popc_per_s);
+
 const char* orbfe_strerror(int status);
 const char* orbfe_last_cuda_error(void);
 /* "orbfe <version> sm_100a" */

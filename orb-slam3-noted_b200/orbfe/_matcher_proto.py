@@ -31,5 +31,6 @@ PROTO = {
     "orbfe_stereo_match": (_I, [_P, _P, _I, _P, _I, _F, _F, _P, _P, _I]),
     "orbfe_stereo_match_batch_device": (_I, [_P, _P, _I, _F, _F, _P, _P]),
     "orbfe_search_bow": (_I, [_P, _I, C.POINTER(BowSide), C.POINTER(BowSide), _I, _I, _I, C.POINTER(_P), C.POINTER(_P), _P]),
+    "orbfe_measure_popc_peak": (_I, [_I, C.POINTER(C.c_double)]),
     "orbfe_search_triangulation": (_I, [_P, C.POINTER(BowSide), _P, C.POINTER(BowSide), _P, C.POINTER(Epipolar), _I, _I, _P]),
 }

@@ -50,6 +50,15 @@ class FeatureVectorCSR:
         return FeatureVector(len(self.node_ids), _p(self.node_ids), _p(self.offsets), _p(self.indices))
 
 
+def measure_popc_peak(device=0):
+    """Sustained POPC instructions/s of the device (the matching roofline's denominator is this / 8)."""
+    v = C.c_double(0)
+    st = lib().orbfe_measure_popc_peak(int(device), C.byref(v))
+    if st < 0:
+        raise OrbfeError(st, "orbfe_measure_popc_peak")
+    return v.value
+
+
 class _Side:
     """Keeps the arrays behind an orbfe_bow_side alive."""
 
