@@ -1,0 +1,203 @@
+// ORBmatcher.h — ORB_SLAM3::ORBmatcher over the orbfe C ABI (include/orbfe.h).
+//
+// Keeps the reference's class name, constructor, static DescriptorDistance and TH_LOW / TH_HIGH /
+// HISTO_LENGTH (include/ORBmatcher.h:35-111).  The searches come in two layers:
+//   * array layer (always available): the reference's inputs already flattened — descriptors,
+//     keypoints, a FeatureVector as CSR, MapPoint-validity masks.  This is what the tests drive.
+//   * object layer (#ifdef ORBFE_WITH_ORBSLAM3, needs the reference's Frame.h / KeyFrame.h /
+//     MapPoint.h): SearchByBoW(KeyFrame*, Frame&, ...), SearchByBoW(KeyFrame*, KeyFrame*, ...),
+//     SearchForTriangulation_(...) with the reference's signatures; they flatten the objects and
+//     call the array layer.  Not compiled in this repository (ORB-SLAM3's headers need OpenCV/Eigen).
+#ifndef ORBMATCHER_H
+#define ORBMATCHER_H
+
+#include <cstdint>
+#include <map>
+#include <utility>
+#include <vector>
+
+#ifdef ORBFE_NO_OPENCV
+#include "cv_standin.h"
+#else
+#include <opencv2/core/core.hpp>
+#endif
+
+#include "../orbfe.h"
+
+#ifdef ORBFE_WITH_ORBSLAM3
+#include "Frame.h"
+#include "KeyFrame.h"
+#include "MapPoint.h"
+#endif
+
+namespace ORB_SLAM3 {
+
+namespace orbfe_shim {
+
+// A DBoW2::FeatureVector (std::map<unsigned, std::vector<unsigned>>) flattened to the ABI's CSR.
+struct FeatureVectorCsr {
+    std::vector<uint32_t> nodeIds;
+    std::vector<int32_t> offsets, indices;
+
+    template <class Map>   // any std::map<NodeId, std::vector<unsigned>>-like container
+    explicit FeatureVectorCsr(const Map& fv) {
+        offsets.push_back(0);
+        for (const auto& kv : fv) {
+            nodeIds.push_back((uint32_t)kv.first);
+            for (unsigned i : kv.second) indices.push_back((int32_t)i);
+            offsets.push_back((int32_t)indices.size());
+        }
+    }
+    orbfe_feature_vector view() const {
+        orbfe_feature_vector v;
+        v.nnodes = (int)nodeIds.size();
+        v.node_ids = nodeIds.data();
+        v.offsets = offsets.data();
+        v.indices = indices.data();
+        return v;
+    }
+};
+
+// One side of a BoW-guided search, as arrays.
+struct Side {
+    const uint8_t* desc = nullptr;            // n x 32, continuous (cv::Mat::data of mDescriptors)
+    int n = 0;
+    const FeatureVectorCsr* fv = nullptr;
+    const uint8_t* mask = nullptr;
+    const cv::KeyPoint* kps = nullptr;        // mvKeysUn
+    orbfe_bow_side view() const {
+        orbfe_bow_side s;
+        s.desc = desc; s.n = n; s.fv = fv->view(); s.mask = mask;
+        s.kps = reinterpret_cast<const orbfe_keypoint*>(kps);
+        return s;
+    }
+};
+
+}  // namespace orbfe_shim
+
+class ORBmatcher {
+public:
+    ORBmatcher(float nnratio = 0.6, bool checkOri = true, int device = 0) : mfNNratio(nnratio), mbCheckOrientation(checkOri) {
+        status_ = orbfe_matcher_create(nnratio, checkOri ? 1 : 0, device, &m_);
+        if (status_ != ORBFE_OK) m_ = nullptr;
+    }
+    ~ORBmatcher() { orbfe_matcher_destroy(m_); }
+    ORBmatcher(const ORBmatcher&) = delete;
+    ORBmatcher& operator=(const ORBmatcher&) = delete;
+
+    // ORBmatcher.cc:2561-2577
+    static int DescriptorDistance(const cv::Mat& a, const cv::Mat& b) { return orbfe_descriptor_distance(a.ptr(), b.ptr()); }
+
+    // ---- array layer ---------------------------------------------------------------------------------
+    // SearchByBoW(KeyFrame*, Frame&, ...) (ORBmatcher.cc:269-471): kfOfFrameFeature[j] = keyframe feature
+    // matched to frame feature j or -1.  Returns nmatches (0 on error, see lastStatus()).
+    int SearchByBoWArrays(const orbfe_shim::Side& kf, const orbfe_shim::Side& frame, int frameNleft,
+                          std::vector<int32_t>& kfOfFrameFeature) {
+        kfOfFrameFeature.assign(frame.n, -1);
+        if (!m_) return 0;
+        orbfe_bow_side A = kf.view(), B = frame.view();
+        B.mask = nullptr;
+        int32_t* out = kfOfFrameFeature.data();
+        int n = 0;
+        status_ = orbfe_search_bow(m_, 0, &A, &B, 1, 0, frameNleft, nullptr, &out, &n);
+        return status_ < 0 ? 0 : n;
+    }
+    // SearchByBoW(KeyFrame*, KeyFrame*, ...) (ORBmatcher.cc:823-963): kf2OfKf1Feature[i] = pKF2 feature or -1.
+    int SearchByBoWArrays(const orbfe_shim::Side& kf1, const orbfe_shim::Side& kf2, std::vector<int32_t>& kf2OfKf1Feature) {
+        kf2OfKf1Feature.assign(kf1.n, -1);
+        if (!m_) return 0;
+        orbfe_bow_side A = kf1.view(), B = kf2.view();
+        int32_t* out = kf2OfKf1Feature.data();
+        int n = 0;
+        status_ = orbfe_search_bow(m_, 1, &A, &B, 1, 0, -1, &out, nullptr, &n);
+        return status_ < 0 ? 0 : n;
+    }
+    // SearchForTriangulation_ (ORBmatcher.cc:1208-1432), pinhole: masks = "already has a MapPoint".
+    int SearchForTriangulationArrays(const orbfe_shim::Side& kf1, const float* uRight1, const orbfe_shim::Side& kf2,
+                                     const float* uRight2, const orbfe_epipolar& geo, bool bOnlyStereo, bool bCoarse,
+                                     std::vector<std::pair<size_t, size_t>>& vMatchedPairs) {
+        vMatchedPairs.clear();
+        if (!m_) return 0;
+        std::vector<int32_t> m12(kf1.n > 0 ? kf1.n : 1, -1);
+        orbfe_bow_side A = kf1.view(), B = kf2.view();
+        const int n = orbfe_search_triangulation(m_, &A, uRight1, &B, uRight2, &geo, bOnlyStereo, bCoarse, m12.data());
+        status_ = n < 0 ? n : ORBFE_OK;
+        if (n < 0) return 0;
+        vMatchedPairs.reserve(n);
+        for (int i = 0; i < kf1.n; ++i)
+            if (m12[i] >= 0) vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[i]));
+        return n;
+    }
+    // Frame::ComputeStereoMatches (Frame.cc:794-964) on the device-resident results of two extractor handles.
+    int ComputeStereoMatches(orbfe_handle* left, orbfe_handle* right, float mbf, float mb, std::vector<float>& mvuRight,
+                             std::vector<float>& mvDepth, int N) {
+        mvuRight.assign(N, -1.0f);
+        mvDepth.assign(N, -1.0f);
+        if (!m_ || N == 0) return 0;
+        const int n = orbfe_stereo_match(m_, left, 0, right, 0, mbf, mb, mvuRight.data(), mvDepth.data(), N);
+        status_ = n < 0 ? n : ORBFE_OK;
+        return n < 0 ? 0 : n;
+    }
+    // Frame::ComputeStereoFishEyeMatches up to the ratio test (Frame.cc:1134-1141).
+    int MatchLapping(const cv::Mat& descLeft, const cv::Mat& descRight, std::vector<int32_t>& match) {
+        match.assign(descLeft.rows, -1);
+        if (!m_ || descLeft.rows == 0) return 0;
+        const int n = orbfe_match_lapping(m_, descLeft.ptr(), descLeft.rows, descRight.ptr(), descRight.rows, 0.7, match.data());
+        status_ = n < 0 ? n : ORBFE_OK;
+        return n < 0 ? 0 : n;
+    }
+
+#ifdef ORBFE_WITH_ORBSLAM3
+    // ---- object layer: the reference's signatures ------------------------------------------------------
+    int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches) {
+        const std::vector<MapPoint*> vpMapPointsKF = pKF->GetMapPointMatches();
+        std::vector<uint8_t> mask(vpMapPointsKF.size());
+        for (size_t i = 0; i < mask.size(); ++i) mask[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();
+        orbfe_shim::FeatureVectorCsr fvKF(pKF->mFeatVec), fvF(F.mFeatVec);
+        orbfe_shim::Side a, b;
+        a.desc = pKF->mDescriptors.data; a.n = pKF->mDescriptors.rows; a.fv = &fvKF; a.mask = mask.data(); a.kps = pKF->mvKeysUn.data();
+        b.desc = F.mDescriptors.data; b.n = F.mDescriptors.rows; b.fv = &fvF; b.kps = F.mvKeys.data();
+        std::vector<int32_t> m;
+        const int n = SearchByBoWArrays(a, b, F.Nleft, m);
+        vpMapPointMatches.assign(F.N, static_cast<MapPoint*>(NULL));
+        for (int j = 0; j < (int)m.size(); ++j)
+            if (m[j] >= 0) vpMapPointMatches[j] = vpMapPointsKF[m[j]];
+        return n;
+    }
+    int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12) {
+        const std::vector<MapPoint*> mp1 = pKF1->GetMapPointMatches(), mp2 = pKF2->GetMapPointMatches();
+        std::vector<uint8_t> k1(mp1.size()), k2(mp2.size());
+        for (size_t i = 0; i < k1.size(); ++i) k1[i] = mp1[i] && !mp1[i]->isBad();
+        for (size_t i = 0; i < k2.size(); ++i) k2[i] = mp2[i] && !mp2[i]->isBad();
+        orbfe_shim::FeatureVectorCsr fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
+        orbfe_shim::Side a, b;
+        a.desc = pKF1->mDescriptors.data; a.n = pKF1->mDescriptors.rows; a.fv = &fv1; a.mask = k1.data(); a.kps = pKF1->mvKeysUn.data();
+        b.desc = pKF2->mDescriptors.data; b.n = pKF2->mDescriptors.rows; b.fv = &fv2; b.mask = k2.data(); b.kps = pKF2->mvKeysUn.data();
+        std::vector<int32_t> m;
+        const int n = SearchByBoWArrays(a, b, m);
+        vpMatches12.assign(mp1.size(), static_cast<MapPoint*>(NULL));
+        for (size_t i = 0; i < m.size(); ++i)
+            if (m[i] >= 0) vpMatches12[i] = mp2[m[i]];
+        return n;
+    }
+#endif
+
+    static const int TH_LOW = ORBFE_TH_LOW;
+    static const int TH_HIGH = ORBFE_TH_HIGH;
+    static const int HISTO_LENGTH = ORBFE_HISTO_LENGTH;
+
+    orbfe_matcher* handle() { return m_; }
+    int lastStatus() const { return status_; }
+
+protected:
+    float mfNNratio;
+    bool mbCheckOrientation;
+
+private:
+    orbfe_matcher* m_ = nullptr;
+    int status_ = ORBFE_OK;
+};
+
+}  // namespace ORB_SLAM3
+
+#endif  // ORBMATCHER_H

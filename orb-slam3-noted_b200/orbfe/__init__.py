@@ -10,3 +10,4 @@ from ._lib import (KEYPOINT_DTYPE, OrbfeError, lib, lib_path, strerror, version)
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import ORBmatcher, FeatureVectorCSR, measure_popc_peak  # noqa: F401
 from . import synth  # noqa: F401
+from . import shard  # noqa: F401

@@ -1,0 +1,94 @@
+// shim_test.cc — drives the C++ shim classes (include/orbfe_shim/) the way Frame.cc drives the
+// reference's ORBextractor / ORBmatcher, with the OpenCV stand-in types (TEST INFRASTRUCTURE).
+//
+//   shim_test <left.raw> <right.raw> <w> <h> <nfeatures> <bf> <b> <out.bin>
+//
+// Writes: int32 nL, monoL, nR | nL keypoints (28 B) | nL x 32 descriptors | nL floats mvuRight | nL floats
+// mvDepth | int32 nmatchesBoW | nR int32 (SearchByBoW KF=left, Frame=right with the node function of
+// orbfe/synth.py and every left feature holding a MapPoint) | 8 floats scale factors | pyramid level 1 ROI bytes.
+// Exit code 3 = no CUDA device (the CPU-side test expects exactly that), 0 = ok.
+#define ORBFE_NO_OPENCV 1
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <vector>
+
+#include "ORBextractor.h"
+#include "ORBmatcher.h"
+
+using namespace ORB_SLAM3;
+
+static std::vector<unsigned char> read_file(const char* p, size_t n) {
+    std::vector<unsigned char> v(n);
+    FILE* f = fopen(p, "rb");
+    if (!f || fread(v.data(), 1, n, f) != n) { fprintf(stderr, "cannot read %s\n", p); exit(2); }
+    fclose(f);
+    return v;
+}
+
+static std::map<unsigned, std::vector<unsigned>> feature_vector(const cv::Mat& d) {
+    std::map<unsigned, std::vector<unsigned>> fv;
+    for (int i = 0; i < d.rows; ++i) fv[1 + 10 * (d.ptr(i)[0] % 10) + (d.ptr(i)[1] % 10)].push_back(i);
+    return fv;
+}
+
+int main(int argc, char** argv) {
+    if (argc != 9) return 2;
+    const int w = atoi(argv[3]), h = atoi(argv[4]), nf = atoi(argv[5]);
+    const float bf = (float)atof(argv[6]), b = (float)atof(argv[7]);
+    std::vector<unsigned char> bl = read_file(argv[1], (size_t)w * h), br = read_file(argv[2], (size_t)w * h);
+    cv::Mat imL(h, w, CV_8U, bl.data(), w), imR(h, w, CV_8U, br.data(), w);
+
+    ORBextractor exL(nf, 1.2f, 8, 20, 7), exR(nf, 1.2f, 8, 20, 7);
+    std::vector<cv::KeyPoint> kL, kR;
+    cv::Mat dL, dR, none;
+    std::vector<int> lap = {0, 0};
+    const int monoL = exL(imL, none, kL, dL, lap);
+    if (monoL < 0 && exL.lastStatus() == ORBFE_ERR_NO_DEVICE) { printf("no CUDA device\n"); return 3; }
+    if (monoL < 0) { fprintf(stderr, "extract: %s\n", orbfe_strerror(exL.lastStatus())); return 1; }
+    if (exR(imR, none, kR, dR, lap) < 0) return 1;
+    cv::Mat empty;
+    std::vector<cv::KeyPoint> kE;
+    cv::Mat dE;
+    if (exL.lastStatus() != ORBFE_OK || ORBextractor(nf, 1.2f, 8, 20, 7)(empty, none, kE, dE, lap) != -1) return 1;
+
+    ORBmatcher matcher(0.7f, true);
+    std::vector<float> uRight, depth;
+    matcher.ComputeStereoMatches(exL.handle(), exR.handle(), bf, b, uRight, depth, (int)kL.size());
+    if (matcher.lastStatus() != ORBFE_OK) { fprintf(stderr, "stereo: %s\n", orbfe_strerror(matcher.lastStatus())); return 1; }
+
+    orbfe_shim::FeatureVectorCsr fvL(feature_vector(dL)), fvR(feature_vector(dR));
+    std::vector<uint8_t> all(kL.size(), 1);
+    orbfe_shim::Side a, f;
+    a.desc = dL.data; a.n = dL.rows; a.fv = &fvL; a.mask = all.data(); a.kps = kL.data();
+    f.desc = dR.data; f.n = dR.rows; f.fv = &fvR; f.kps = kR.data();
+    std::vector<int32_t> bow;
+    const int nb = matcher.SearchByBoWArrays(a, f, -1, bow);
+    if (matcher.lastStatus() != ORBFE_OK) return 1;
+    if (ORBmatcher::DescriptorDistance(dL.row(0), dL.row(0)) != 0) return 1;
+
+    std::vector<float> sf = exL.GetScaleFactors();
+    if (!exL.FetchImagePyramid()) return 1;
+    const cv::Mat& p1 = exL.mvImagePyramid[1];
+
+    FILE* o = fopen(argv[8], "wb");
+    if (!o) return 2;
+    int32_t hdr[3] = {(int32_t)kL.size(), monoL, (int32_t)kR.size()};
+    fwrite(hdr, 4, 3, o);
+    fwrite(kL.data(), sizeof(cv::KeyPoint), kL.size(), o);
+    for (int i = 0; i < dL.rows; ++i) fwrite(dL.ptr(i), 1, 32, o);
+    fwrite(uRight.data(), 4, uRight.size(), o);
+    fwrite(depth.data(), 4, depth.size(), o);
+    int32_t nb32 = nb;
+    fwrite(&nb32, 4, 1, o);
+    fwrite(bow.data(), 4, bow.size(), o);
+    fwrite(sf.data(), 4, 8, o);
+    int32_t ps[2] = {p1.cols, p1.rows};
+    fwrite(ps, 4, 2, o);
+    for (int r = 0; r < p1.rows; ++r) fwrite(p1.ptr(r), 1, p1.cols, o);
+    fclose(o);
+    printf("shim ok: %zu left keypoints, %d stereo depths, %d BoW matches\n", kL.size(),
+           (int)std::count_if(depth.begin(), depth.end(), [](float d) { return d > 0; }), nb);
+    return 0;
+}
