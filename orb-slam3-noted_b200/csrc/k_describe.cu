@@ -3,20 +3,25 @@
 //   k_assemble  ORBextractor.cc:862-872 (add border, octave, size) and :1100-1149 (scale to level-0
 //               units, lapping-area two-ended placement, monoIndex).  One CTA per frame; the
 //               sequential monoIndex++/stereoIndex-- walk is a prefix sum over "in lapping area" flags.
-//   k_describe  IC_Angle (:75-102) + GaussianBlur 7x7 sigma 2 (:1114-1115) + computeOrbDescriptor
-//               (:106-145), fused per keypoint: one CTA stages the 43x43 unblurred patch around the
-//               keypoint in shared memory, takes the intensity-centroid moments from it, runs the
-//               separable 8.8 fixed-point Gaussian on the 37x37 window the rotated pattern can reach
-//               (|coord| <= 18), and evaluates the 256 tests; __ballot_sync packs 32 tests per word.
-//               Blurring only what the descriptors read replaces two full passes over every level.
-//               All taps fall inside the stored 19-px reflect-101 border (keypoints are >= 19 px from
-//               the ROI edge, taps reach 21 px), which equals what GaussianBlur synthesises.
+//   k_blur      GaussianBlur 7x7 sigma 2, BORDER_REFLECT_101 (:1114-1115) of every level, OpenCV's 8.8
+//               fixed point {18,34,48,56,48,34,18}.  One warp owns a 128 x 32 tile, one thread a 4-pixel-wide
+//               column strip: per row it forms the 4 horizontal sums with 6 PRMT + 8 DP4A from three aligned
+//               words and keeps the last 7 rows in registers for the vertical pass, so there is no shared
+//               memory, no barrier, and every level is read once (L1 absorbs the 3x word overlap) and the
+//               blurred copy written once.  The stored 19-px reflect-101 border IS the border GaussianBlur
+//               synthesises, so edges need no special case.  Only ROI pixels are written: rotated pattern
+//               samples stay >= 1 px inside the ROI (keypoints sit >= 19 px from its edge, reach <= 18 px).
+//   k_describe  IC_Angle (:75-102) + computeOrbDescriptor (:106-145), one WARP per keypoint, no barriers:
+//               the 31 disc rows are read straight from the (L1/L2-resident) level, lanes = columns,
+//               butterfly reduction of m10/m01; then lane i evaluates tests 8i..8i+7 on the blurred level
+//               and owns byte i of the descriptor, exactly the reference's inner loop.
 #include "orbfe_internal.h"
 
 #define ASM_THREADS 256
-#define DESC_THREADS 128
 
-__constant__ int8_t c_pattern[1024] = {
+// bit_pattern_31_ (ORBextractor.cc:147-406) as 256 tests x (x0, y0, x1, y1) int8; staged per CTA into
+// shared memory in [test & 7][test >> 3] order so that lane i's k-th test is a conflict-free word read.
+__device__ const int8_t d_pattern[1024] = {
 #include "orb_pattern.inc"
 };
 // umax of ORBextractor.cc:452-467 (radius-15 disc)
@@ -111,46 +116,91 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
     return a;
 }
 
-#define PR 21                 // patch radius: 18 (pattern reach) + 3 (blur taps)
-#define PW 43                 // patch width
-#define PP 48                 // patch pitch in shared memory (12 words)
-#define BW 37                 // blurred window width
-#define HP 38                 // pitch of the horizontal-pass buffer (uint16)
-#define BP 40                 // pitch of the blurred window
+#define BLUR_TW 128            // tile width  (one warp, 4 px per lane)
+#define BLUR_TH 32             // tile height (rows walked by a thread)
 
-__global__ void __launch_bounds__(DESC_THREADS) k_describe(const uint8_t* __restrict__ pyr, const LevelGeom* __restrict__ geom,
-                                                           const uint32_t* __restrict__ slot, const int* __restrict__ nOut,
-                                                           int kpPerFrame, orbfe_keypoint* __restrict__ kps,
-                                                           uint8_t* __restrict__ desc) {
-    __shared__ __align__(16) uint8_t P[PW * PP + 16];
-    __shared__ uint16_t H[PW * HP];
-    __shared__ uint8_t B[BW * BP];
-    __shared__ int red[2 * (DESC_THREADS / 32)];
-    __shared__ float rot[2];
-    const int frame = blockIdx.y, i = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+// grid.x = ceil(total tiles / 4) (4 warps per CTA, each decodes its own tile), grid.y = frame
+__global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
+                                              const LevelGeom* __restrict__ geom, int nlevels, int totalTiles) {
+    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = blockIdx.y;
+    if (tile >= totalTiles) return;
+    int level = 0;
+    while (level + 1 < nlevels && tile >= geom[level + 1].blurTileBase) ++level;
+    const LevelGeom& g = geom[level];
+    const int t = tile - g.blurTileBase;
+    const int ty = t / g.blurTilesX, tx = t - ty * g.blurTilesX;
+    const int x0 = tx * BLUR_TW + lane * 4, y0 = ty * BLUR_TH;
+    if (x0 >= g.w) return;
+    const int rows = min(BLUR_TH, g.h - y0);
+    const long long lvl = g.base + (long long)frame * g.plane;
+    const int pw = g.pitch >> 2;
+    // word pointer to (x0, y0 - 3) of the bordered level
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(pyr + lvl + (long long)(y0 - 3 + ORBFE_EDGE) * g.pitch + ORBFE_XO + x0);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(blur + lvl + (long long)(y0 + ORBFE_EDGE) * g.pitch + ORBFE_XO + x0);
+    const uint32_t qa = 18u | 34u << 8 | 48u << 16 | 56u << 24, qb = 48u | 34u << 8 | 18u << 16;
+    uint32_t h[7][4];
+#pragma unroll
+    for (int r = 0; r < BLUR_TH + 6; ++r) {
+        if (r < rows + 6) {
+            const uint32_t* p = src + (long long)r * pw;
+            const uint32_t wm = __ldg(p - 1), w0 = __ldg(p), wp = __ldg(p + 1);
+            uint32_t hn[4];
+            hn[0] = __dp4a(__byte_perm(wm, w0, 0x4321), qa, __dp4a(__byte_perm(w0, wp, 0x4321), qb, 0u));
+            hn[1] = __dp4a(__byte_perm(wm, w0, 0x5432), qa, __dp4a(__byte_perm(w0, wp, 0x5432), qb, 0u));
+            hn[2] = __dp4a(__byte_perm(wm, w0, 0x6543), qa, __dp4a(__byte_perm(w0, wp, 0x6543), qb, 0u));
+            hn[3] = __dp4a(w0, qa, __dp4a(wp, qb, 0u));
+#pragma unroll
+            for (int j = 0; j < 6; ++j)
+#pragma unroll
+                for (int k = 0; k < 4; ++k) h[j][k] = h[j + 1][k];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) h[6][k] = hn[k];
+            if (r >= 6) {
+                uint32_t o = 0;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const uint32_t v = 18u * (h[0][k] + h[6][k]) + 34u * (h[1][k] + h[5][k]) + 48u * (h[2][k] + h[4][k]) + 56u * h[3][k];
+                    o |= ((v + 32768u) >> 16) << (8 * k);
+                }
+                dst[(long long)(r - 6) * pw] = o;
+            }
+        }
+    }
+}
+
+#define DESC_WARPS 8
+
+__global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
+                                                              const LevelGeom* __restrict__ geom,
+                                                              const uint32_t* __restrict__ slot, const int* __restrict__ nOut,
+                                                              int kpPerFrame, orbfe_keypoint* __restrict__ kps,
+                                                              uint8_t* __restrict__ desc) {
+    __shared__ uint32_t sPat[256];
+    {
+        const int T = threadIdx.x;   // DESC_WARPS * 32 == 256 tests
+        sPat[(T & 7) * 32 + (T >> 3)] = __ldg(reinterpret_cast<const uint32_t*>(d_pattern) + T);
+    }
+    __syncthreads();
+    const int frame = blockIdx.y, i = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (i >= nOut[frame]) return;
     const uint32_t s = slot[(long long)frame * kpPerFrame + i];
     const int level = s >> 28, cy = (s >> 14) & 0x3FFF, cx = s & 0x3FFF;
     const LevelGeom& g = geom[level];
-    // ---- stage the 43x43 patch with aligned 32-bit loads
-    const long long col0 = ORBFE_XO + cx - PR;               // byte column of patch column 0 in the bordered row
-    const int sh = (int)(col0 & 3);
-    const uint8_t* base = pyr + g.base + (long long)frame * g.plane + (long long)(cy + ORBFE_EDGE - PR) * g.pitch + (col0 - sh);
-    for (int w = tid; w < PW * (PP / 4); w += DESC_THREADS) {
-        const int r = w / (PP / 4), c = w - r * (PP / 4);
-        reinterpret_cast<uint32_t*>(P)[r * (PP / 4) + c] = __ldg(reinterpret_cast<const uint32_t*>(base + (long long)r * g.pitch) + c);
-    }
-    __syncthreads();
-    const uint8_t* Pc = P + sh;   // Pc[r * PP + c] = pixel (cx - 21 + c, cy - 21 + r)
-    // ---- intensity centroid (IC_Angle): 31 rows x 4 segments
+    const long long centre = g.base + (long long)frame * g.plane + (long long)(cy + ORBFE_EDGE) * g.pitch + ORBFE_XO + cx;
+    // ---- intensity centroid (IC_Angle): lane = column u = lane - 15, rows v = -15..15 clipped to the disc
     int m10 = 0, m01 = 0;
-    if (tid < 124) {
-        const int v = (tid >> 2) - 15, d = c_umax[v < 0 ? -v : v];
-        const uint8_t* row = Pc + (v + PR) * PP + PR;
-        for (int u = -d + (tid & 3); u <= d; u += 4) {
-            const int I = row[u];
-            m10 += u * I;
-            m01 += v * I;
+    {
+        const uint8_t* c = pyr + centre;
+        const int u = lane - 15;
+        const int au = u < 0 ? -u : u;
+#pragma unroll
+        for (int v = -15; v <= 15; ++v) {
+            const int d = c_umax[v < 0 ? -v : v];
+            if (au <= d && lane < 31) {
+                const int I = __ldg(c + (long long)v * g.pitch + u);
+                m10 += u * I;
+                m01 += v * I;
+            }
         }
     }
 #pragma unroll
@@ -158,50 +208,31 @@ __global__ void __launch_bounds__(DESC_THREADS) k_describe(const uint8_t* __rest
         m10 += __shfl_xor_sync(0xffffffffu, m10, o);
         m01 += __shfl_xor_sync(0xffffffffu, m01, o);
     }
-    if (lane == 0) { red[wid] = m10; red[DESC_THREADS / 32 + wid] = m01; }
-    // ---- horizontal pass of the 7x7 Gaussian, 8.8 fixed point {18,34,48,56,48,34,18}
-    for (int o = tid; o < PW * BW; o += DESC_THREADS) {
-        const int r = o / BW, c = o - r * BW;
-        const uint8_t* p = Pc + r * PP + c;
-        H[r * HP + c] = (uint16_t)(18 * (p[0] + p[6]) + 34 * (p[1] + p[5]) + 48 * (p[2] + p[4]) + 56 * p[3]);
-    }
-    __syncthreads();
-    if (tid == 0) {
-        int a10 = 0, a01 = 0;
+    const float angle = fast_atan2_deg((float)m01, (float)m10);
+    if (lane == 0) kps[(long long)frame * kpPerFrame + i].angle = angle;
+    // a = cosf(angle * factorPI), b = sinf(...): float argument, result rounded from double precision
+    const float rad = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.f));
+    const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+    // ---- lane computes descriptor byte `lane`: tests 8*lane .. 8*lane+7
+    const uint8_t* Bc = blur + centre;
+    const int pitch = g.pitch;
+    uint32_t byte = 0;
 #pragma unroll
-        for (int w = 0; w < DESC_THREADS / 32; ++w) { a10 += red[w]; a01 += red[DESC_THREADS / 32 + w]; }
-        const float angle = fast_atan2_deg((float)a01, (float)a10);
-        kps[(long long)frame * kpPerFrame + i].angle = angle;
-        // a = cosf(angle * factorPI), b = sinf(...): float argument, result rounded from double precision
-        const float rad = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.f));
-        rot[0] = (float)cos((double)rad);
-        rot[1] = (float)sin((double)rad);
+    for (int k = 0; k < 8; ++k) {
+        const uint32_t pw = sPat[k * 32 + lane];   // test 8*lane + k
+        const float x0 = (float)(int8_t)(pw & 0xFF), y0 = (float)(int8_t)(pw >> 8 & 0xFF);
+        const float x1 = (float)(int8_t)(pw >> 16 & 0xFF), y1 = (float)(int8_t)(pw >> 24);
+        const int t0 = __ldg(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * pitch +
+                             __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b))));
+        const int t1 = __ldg(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a))) * pitch +
+                             __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b))));
+        byte |= (uint32_t)(t0 < t1) << k;
     }
-    // ---- vertical pass
-    for (int o = tid; o < BW * BW; o += DESC_THREADS) {
-        const int r = o / BW, c = o - r * BW;
-        const uint16_t* hcol = H + r * HP + c;
-        const uint32_t v = 18u * (hcol[0] + hcol[6 * HP]) + 34u * (hcol[HP] + hcol[5 * HP]) + 48u * (hcol[2 * HP] + hcol[4 * HP]) +
-                           56u * hcol[3 * HP];
-        B[r * BP + c] = (uint8_t)((v + 32768u) >> 16);
-    }
-    __syncthreads();
-    // ---- 256 rotated-pattern tests
-    const float a = rot[0], b = rot[1];
-    const uint8_t* Bc = B + 18 * BP + 18;
-    uint32_t* dout = reinterpret_cast<uint32_t*>(desc + ((long long)frame * kpPerFrame + i) * 32);
-#pragma unroll
-    for (int half = 0; half < 2; ++half) {
-        const int T = half * DESC_THREADS + tid;
-        const float x0 = (float)c_pattern[4 * T], y0 = (float)c_pattern[4 * T + 1];
-        const float x1 = (float)c_pattern[4 * T + 2], y1 = (float)c_pattern[4 * T + 3];
-        const int t0 = Bc[__float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * BP +
-                          __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b)))];
-        const int t1 = Bc[__float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a))) * BP +
-                          __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b)))];
-        const uint32_t bits = __ballot_sync(0xffffffffu, t0 < t1);
-        if (lane == 0) dout[half * (DESC_THREADS / 32) + wid] = bits;
-    }
+    // gather 4 bytes per word: lanes 4j..4j+3 -> word j, written by lane 4j
+    uint32_t w = byte << (8 * (lane & 3));
+    w |= __shfl_xor_sync(0xffffffffu, w, 1);
+    w |= __shfl_xor_sync(0xffffffffu, w, 2);
+    if ((lane & 3) == 0) reinterpret_cast<uint32_t*>(desc + ((long long)frame * kpPerFrame + i) * 32)[lane >> 2] = w;
 }
 
 cudaError_t orbfe_launch_assemble(orbfe_handle* h, int batch, int lap0, int lap1) {
@@ -212,8 +243,14 @@ cudaError_t orbfe_launch_assemble(orbfe_handle* h, int batch, int lap0, int lap1
 }
 
 cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch) {
-    dim3 grid(h->kpPerFrame, batch);
-    k_describe<<<grid, DESC_THREADS, 0, h->stream>>>(h->dPyr, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps, h->dDesc);
+    {
+        dim3 grid((h->blurTiles + 3) / 4, batch);
+        k_blur<<<grid, 128, 0, h->stream>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles);
+        h->launches++;
+    }
+    dim3 grid((h->kpPerFrame + DESC_WARPS - 1) / DESC_WARPS, batch);
+    k_describe<<<grid, DESC_WARPS * 32, 0, h->stream>>>(h->dPyr, h->dBlur, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps,
+                                                       h->dDesc);
     h->launches++;
     return cudaGetLastError();
 }

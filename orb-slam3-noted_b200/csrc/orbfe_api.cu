@@ -80,6 +80,7 @@ struct ShapePlan {
     long long candPerFrame = 0;
     int kpPerFrame = 0;
     int maxCellBytes = 0;
+    int blurTiles = 0;
     int status = ORBFE_OK;
 };
 
@@ -88,7 +89,7 @@ struct ShapePlan {
 static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
     const int nl = h->p.nlevels;
     long long pyrOff = 0, candOff = 0;
-    int kpOff = 0, tapOff = 0;
+    int kpOff = 0, tapOff = 0, blurTiles = 0;
     for (int l = 0; l < nl; ++l) {
         LevelGeom& g = sp.geom[l];
         memset(&g, 0, sizeof(g));
@@ -144,8 +145,8 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
                 sp.cells.push_back(c);
                 const int keptCap = ((tw + 1) / 2) * ((th + 1) / 2);
                 cap += keptCap;
-                const int tp = (c.cw + 3) & ~3;
-                const int bytes = 2 * tp * c.ch + 2 * ((tw * th + 1) & ~1) + 4 * keptCap + 16;
+                const int tp = (c.cw + 6) & ~3;   // worst-case tile pitch (k_fast.cu: alignment shift + width, whole words)
+                const int bytes = 2 * tp * c.ch + 2 * 2 * ((tw * th + 1) & ~1) + 4 * keptCap + 16;
                 sp.maxCellBytes = std::max(sp.maxCellBytes, bytes);
             }
         }
@@ -154,6 +155,9 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
         g.candBase = candOff;
         candOff += g.candCap;
         // resize taps (level l from level l-1)
+        g.blurTileBase = blurTiles;
+        g.blurTilesX = (g.w + 127) / 128;
+        blurTiles += g.blurTilesX * ((g.h + 31) / 32);
         g.tabX = tapOff;
         g.tabY = tapOff + g.w;
         tapOff += g.w + g.h;
@@ -166,13 +170,14 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
     sp.pyrBytesPerFrame = (size_t)pyrOff;
     sp.candPerFrame = candOff;
     sp.kpPerFrame = kpOff;
+    sp.blurTiles = blurTiles;
 }
 
 // ---- handle life cycle ---------------------------------------------------------------------------
 static void free_handle(orbfe_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
-    cudaFree(h->dIn); cudaFree(h->dPyr); cudaFree(h->dCand); cudaFree(h->dNodeOf); cudaFree(h->dCandCount);
+    cudaFree(h->dIn); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dCand); cudaFree(h->dNodeOf); cudaFree(h->dCandCount);
     cudaFree(h->dLvlKp); cudaFree(h->dLvlCount); cudaFree(h->dGeom); cudaFree(h->dCells); cudaFree(h->dTaps);
     cudaFree(h->dKps); cudaFree(h->dDesc); cudaFree(h->dSlot); cudaFree(h->dN); cudaFree(h->dMono);
     if (h->hN) cudaFreeHost(h->hN);
@@ -205,6 +210,7 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     h->maxCellBytes = sp.maxCellBytes;
     h->candPerFrame = sp.candPerFrame;
     h->kpPerFrame = sp.kpPerFrame;
+    h->blurTiles = sp.blurTiles;
     CK(cudaStreamSynchronize(h->stream));   // previous work may still read the old tables
     CK(cudaMemcpyAsync(h->dGeom, h->geom, sizeof(LevelGeom) * h->p.nlevels, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->dCells, sp.cells.data(), sizeof(CellDesc) * sp.cells.size(), cudaMemcpyHostToDevice, h->stream));
@@ -251,6 +257,7 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKC(cudaMalloc(&h->dIn, h->inBytes));
     CKC(cudaMalloc(&h->dPyr, h->pyrBytes));
+    CKC(cudaMalloc(&h->dBlur, h->pyrBytes));
     CKC(cudaMalloc(&h->dCand, h->candEntries * 4));
     CKC(cudaMalloc(&h->dNodeOf, h->candEntries * 4));
     CKC(cudaMalloc(&h->dCandCount, sizeof(int) * B * ORBFE_MAX_LEVELS));
@@ -267,6 +274,7 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaMallocHost(&h->hN, sizeof(int) * B));
     CKC(cudaMallocHost(&h->hMono, sizeof(int) * B));
     CKC(cudaMemset(h->dPyr, 0, h->pyrBytes));
+    CKC(cudaMemset(h->dBlur, 0, h->pyrBytes));
 #undef CKC
     *out = h;
     return ORBFE_OK;

@@ -37,6 +37,7 @@ struct LevelGeom {
     float scale;           // mvScaleFactor[level]
     float size;            // (float)(int)(31 * scale)
     int tabX, tabY;        // offsets into the resize tables (entries)
+    int blurTileBase, blurTilesX;   // 128 x 32 tiles of k_blur: first tile id of this level, tiles per tile row
 };
 
 // One FAST cell = one CTA of k_fast (ORBextractor.cc:787-853).
@@ -73,6 +74,8 @@ struct orbfe_handle {
     // device arenas
     uint8_t* dIn;           // staged input frames (host path)
     uint8_t* dPyr;          // pyramid arena [level][frame][rows][pitch]
+    uint8_t* dBlur;         // Gaussian-blurred levels, same layout (ROI pixels only are defined)
+    int blurTiles;          // k_blur tiles per frame (all levels)
     uint32_t* dCand;        // packed candidates [frame][level slice]
     uint32_t* dNodeOf;      // quadtree scratch, same indexing as dCand
     int* dCandCount;        // [frame][level]
