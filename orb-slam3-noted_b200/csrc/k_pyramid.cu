@@ -63,6 +63,54 @@ __global__ void __launch_bounds__(128) k_pyr_resize(uint8_t* __restrict__ pyr, L
     reinterpret_cast<uint32_t*>(dst)[word] = v;
 }
 
+// ---- fast path: column plans ---------------------------------------------------------------------------
+// The x side of the resize does not depend on the row, so the host precomputes, per 32-bit word of a
+// bordered destination row, a ColPlan: where the (at most 8-byte) source windows of its column pairs
+// start, the PRMT selectors that gather (S[s0], S[s1]) of two columns into one word, the packed int16
+// weights (a0 | a1 << 16) of the four columns and a byte mask for columns outside the 19-px border.
+// A thread owns one destination word and walks PYR_TH rows with the plan in registers: per row
+// 8 word loads (L1-resident), 4 PRMT, 8 DP2A (the 11-bit horizontal blend), the vertical blend, 1 store.
+// One warp = a 128-byte x PYR_TH-row tile, 4 tiles per CTA.
+#define PYR_TH 16
+
+__global__ void __launch_bounds__(128) k_pyr_resize_plan(uint8_t* __restrict__ pyr, LevelGeom gs, LevelGeom gd,
+                                                         const ResizeTap* __restrict__ taps, const ColPlan* __restrict__ plans,
+                                                         int tilesX, int totalTiles) {
+    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = blockIdx.y;
+    if (tile >= totalTiles) return;
+    const int ty = tile / tilesX, tx = tile - ty * tilesX;
+    const int word = tx * 32 + lane;
+    const ColPlan cp = plans[gd.planBase + word];
+    const int row0 = ty * PYR_TH, row1 = min(row0 + PYR_TH, gd.rows);
+    const uint32_t* sbase = reinterpret_cast<const uint32_t*>(pyr + gs.base + (long long)frame * gs.plane +
+                                                              (long long)ORBFE_EDGE * gs.pitch + ORBFE_XO);
+    const int spw = gs.pitch >> 2;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(pyr + gd.base + (long long)frame * gd.plane) + word;
+    const int dpw = gd.pitch >> 2;
+    for (int row = row0; row < row1; ++row) {
+        const int y = reflect101(row - ORBFE_EDGE, gd.h);
+        const ResizeTap tyv = taps[gd.tabY + y];
+        const uint32_t* S0 = sbase + (long long)tyv.s0 * spw;
+        const uint32_t* S1 = sbase + (long long)tyv.s1 * spw;
+        const uint32_t p0a = __byte_perm(S0[cp.base01], S0[cp.base01 + 1], cp.sel & 0xFFFF);
+        const uint32_t p0b = __byte_perm(S0[cp.base23], S0[cp.base23 + 1], cp.sel >> 16);
+        const uint32_t p1a = __byte_perm(S1[cp.base01], S1[cp.base01 + 1], cp.sel & 0xFFFF);
+        const uint32_t p1b = __byte_perm(S1[cp.base23], S1[cp.base23 + 1], cp.sel >> 16);
+        int r0[4], r1[4];
+        r0[0] = __dp2a_lo(cp.a[0], p0a, 0u); r0[1] = __dp2a_hi(cp.a[1], p0a, 0u);
+        r0[2] = __dp2a_lo(cp.a[2], p0b, 0u); r0[3] = __dp2a_hi(cp.a[3], p0b, 0u);
+        r1[0] = __dp2a_lo(cp.a[0], p1a, 0u); r1[1] = __dp2a_hi(cp.a[1], p1a, 0u);
+        r1[2] = __dp2a_lo(cp.a[2], p1b, 0u); r1[3] = __dp2a_hi(cp.a[3], p1b, 0u);
+        uint32_t v = 0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int o = ((((int)tyv.a0 * (r0[k] >> 4)) >> 16) + (((int)tyv.a1 * (r1[k] >> 4)) >> 16) + 2) >> 2;
+            v |= (uint32_t)(o & 0xFF) << (8 * k);
+        }
+        dst[(long long)row * dpw] = v & cp.keep;
+    }
+}
+
 cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int batch, int width, int height,
                                  long long stride, long long frameStride) {
     (void)width; (void)height;
@@ -75,8 +123,14 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int ba
     }
     for (int l = 1; l < nl; ++l) {
         const LevelGeom& gd = h->geom[l];
-        dim3 grid((gd.pitch / 4 + 127) / 128, gd.rows, batch);
-        k_pyr_resize<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps);
+        if (gd.planBase >= 0) {
+            const int tilesX = gd.pitch / 128, total = tilesX * ((gd.rows + PYR_TH - 1) / PYR_TH);
+            dim3 grid((total + 3) / 4, batch);
+            k_pyr_resize_plan<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total);
+        } else {   // scale factors whose 2-column source window exceeds 8 bytes: generic kernel
+            dim3 grid((gd.pitch / 4 + 127) / 128, gd.rows, batch);
+            k_pyr_resize<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps);
+        }
         h->launches++;
     }
     return cudaGetLastError();

@@ -72,8 +72,50 @@ static void build_taps(int n, int m, bool clampFrac, ResizeTap* out) {
     }
 }
 
+// Column plans of one level (see ColPlan / k_pyr_resize_plan).  Leaves g.planBase = -1 if some column
+// pair's source bytes do not fit an 8-byte window (scale factors above ~2).
+static void build_col_plans(LevelGeom& g, const ResizeTap* tx, std::vector<ColPlan>& plans) {
+    const int nwords = g.pitch / 4;
+    const size_t first = plans.size();
+    plans.resize(first + nwords);
+    for (int word = 0; word < nwords; ++word) {
+        ColPlan cp;
+        memset(&cp, 0, sizeof(cp));
+        int s0[4], s1[4];
+        for (int k = 0; k < 4; ++k) {
+            const int x = word * 4 - ORBFE_XO + k;
+            const bool in = x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE;
+            int xr = x < 0 ? -x : x;
+            if (xr >= g.w) xr = 2 * g.w - 2 - xr;
+            // columns outside the border are masked off by `keep`; give them the tap of the nearest stored column
+            // so that they do not widen the source window
+            const int xc = in ? xr : (x < 0 ? ORBFE_EDGE : g.w - 2 - (ORBFE_EDGE - 1));
+            const ResizeTap t = tx[std::min(std::max(xc, 0), g.w - 1)];
+            s0[k] = t.s0; s1[k] = t.s1;
+            cp.a[k] = (uint32_t)(uint16_t)t.a0 | (uint32_t)(uint16_t)t.a1 << 16;
+            if (in) cp.keep |= 0xFFu << (8 * k);
+        }
+        uint32_t sel = 0;
+        for (int pair = 0; pair < 2; ++pair) {
+            const int b[4] = {s0[2 * pair], s1[2 * pair], s0[2 * pair + 1], s1[2 * pair + 1]};
+            const int lo = std::min(std::min(b[0], b[1]), std::min(b[2], b[3]));
+            const int hi = std::max(std::max(b[0], b[1]), std::max(b[2], b[3]));
+            const int base = lo >> 2;
+            if (hi - base * 4 > 7) { plans.resize(first); g.planBase = -1; return; }
+            (pair ? cp.base23 : cp.base01) = base;
+            uint32_t sl = 0;
+            for (int j = 0; j < 4; ++j) sl |= (uint32_t)(b[j] - base * 4) << (4 * j);
+            sel |= sl << (16 * pair);
+        }
+        cp.sel = sel;
+        plans[first + word] = cp;
+    }
+    g.planBase = (int)first;
+}
+
 struct ShapePlan {
     LevelGeom geom[ORBFE_MAX_LEVELS];
+    std::vector<ColPlan> plans;
     std::vector<CellDesc> cells;
     std::vector<ResizeTap> taps;
     size_t pyrBytesPerFrame = 0;
@@ -162,9 +204,11 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
         g.tabY = tapOff + g.w;
         tapOff += g.w + g.h;
         sp.taps.resize(tapOff);
+        g.planBase = -1;
         if (l > 0) {
             build_taps(sp.geom[l - 1].w, g.w, true, &sp.taps[g.tabX]);
             build_taps(sp.geom[l - 1].h, g.h, false, &sp.taps[g.tabY]);
+            build_col_plans(g, &sp.taps[g.tabX], sp.plans);
         }
     }
     sp.pyrBytesPerFrame = (size_t)pyrOff;
@@ -178,7 +222,7 @@ static void free_handle(orbfe_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaFree(h->dIn); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dCand); cudaFree(h->dNodeOf); cudaFree(h->dCandCount);
-    cudaFree(h->dLvlKp); cudaFree(h->dLvlCount); cudaFree(h->dGeom); cudaFree(h->dCells); cudaFree(h->dTaps);
+    cudaFree(h->dLvlKp); cudaFree(h->dLvlCount); cudaFree(h->dGeom); cudaFree(h->dCells); cudaFree(h->dTaps); cudaFree(h->dPlans);
     cudaFree(h->dKps); cudaFree(h->dDesc); cudaFree(h->dSlot); cudaFree(h->dN); cudaFree(h->dMono);
     if (h->hN) cudaFreeHost(h->hN);
     if (h->hMono) cudaFreeHost(h->hMono);
@@ -200,7 +244,8 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     if (sp.status != ORBFE_OK) return sp.status;
     const size_t B = (size_t)h->p.max_batch;
     if (sp.pyrBytesPerFrame * B > h->pyrBytes || (size_t)sp.candPerFrame * B > h->candEntries ||
-        (int)sp.cells.size() > h->cellCap || (int)sp.taps.size() > h->tabCap || sp.kpPerFrame > h->kpCapPerFrame)
+        (int)sp.cells.size() > h->cellCap || (int)sp.taps.size() > h->tabCap || sp.kpPerFrame > h->kpCapPerFrame ||
+        (int)sp.plans.size() > h->planCap)
         return ORBFE_ERR_TOO_LARGE;
     for (int l = 0; l < h->p.nlevels; ++l) {
         h->geom[l] = sp.geom[l];
@@ -215,6 +260,8 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     CK(cudaMemcpyAsync(h->dGeom, h->geom, sizeof(LevelGeom) * h->p.nlevels, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->dCells, sp.cells.data(), sizeof(CellDesc) * sp.cells.size(), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->dTaps, sp.taps.data(), sizeof(ResizeTap) * sp.taps.size(), cudaMemcpyHostToDevice, h->stream));
+    if (!sp.plans.empty())
+        CK(cudaMemcpyAsync(h->dPlans, sp.plans.data(), sizeof(ColPlan) * sp.plans.size(), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));   // sp's vectors die at return
     h->curW = W;
     h->curH = H;
@@ -246,6 +293,7 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     h->candEntries = ((size_t)sp.candPerFrame + 256) * B;
     h->cellCap = (int)sp.cells.size() + 64;
     h->tabCap = (int)sp.taps.size() + 64;
+    h->planCap = (int)sp.plans.size() + 32 * p.nlevels + 64;
     h->kpCapPerFrame = sp.kpPerFrame + 16 * p.nlevels;
     h->inBytes = (size_t)p.max_width * p.max_height * B;
 #define CKC(call)                                                              \
@@ -266,6 +314,7 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaMalloc(&h->dGeom, sizeof(LevelGeom) * ORBFE_MAX_LEVELS));
     CKC(cudaMalloc(&h->dCells, sizeof(CellDesc) * h->cellCap));
     CKC(cudaMalloc(&h->dTaps, sizeof(ResizeTap) * h->tabCap));
+    CKC(cudaMalloc(&h->dPlans, sizeof(ColPlan) * h->planCap));
     CKC(cudaMalloc(&h->dKps, sizeof(orbfe_keypoint) * B * h->kpCapPerFrame));
     CKC(cudaMalloc(&h->dDesc, (size_t)32 * B * h->kpCapPerFrame));
     CKC(cudaMalloc(&h->dSlot, sizeof(uint32_t) * B * h->kpCapPerFrame));

@@ -38,6 +38,7 @@ struct LevelGeom {
     float size;            // (float)(int)(31 * scale)
     int tabX, tabY;        // offsets into the resize tables (entries)
     int blurTileBase, blurTilesX;   // 128 x 32 tiles of k_blur: first tile id of this level, tiles per tile row
+    int planBase;          // first ColPlan of this level (pitch/4 entries), -1: no plan (generic resize kernel)
 };
 
 // One FAST cell = one CTA of k_fast (ORBextractor.cc:787-853).
@@ -50,6 +51,14 @@ struct CellDesc {
 // Bilinear resize coefficients of one destination column/row (OpenCV 11-bit fixed point).
 struct ResizeTap {
     short s0, s1, a0, a1;
+};
+
+// x side of the bilinear resize for one 32-bit word (4 columns) of a bordered destination row.
+struct ColPlan {
+    int base01, base23;    // source word offsets (from ROI column 0) of the 8-byte windows of columns 0-1 / 2-3
+    uint32_t sel;          // PRMT selectors: low half gathers (S[s0_0], S[s1_0], S[s0_1], S[s1_1]), high half columns 2-3
+    uint32_t a[4];         // a0 | a1 << 16 per column (11-bit fixed point, a0 + a1 = 2048)
+    uint32_t keep;         // 0xFF per byte inside [-19, w + 19)
 };
 
 struct orbfe_handle {
@@ -84,6 +93,8 @@ struct orbfe_handle {
     LevelGeom* dGeom;
     CellDesc* dCells;
     ResizeTap* dTaps;
+    ColPlan* dPlans;
+    int planCap;
     orbfe_keypoint* dKps;   // [frame][kpPerFrame]
     uint8_t* dDesc;         // [frame][kpPerFrame][32]
     uint32_t* dSlot;        // [frame][kpPerFrame] : level << 28 | y << 14 | x (level coords) of the keypoint at dst slot
