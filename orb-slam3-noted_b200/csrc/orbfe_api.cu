@@ -121,7 +121,7 @@ struct ShapePlan {
     size_t pyrBytesPerFrame = 0;
     long long candPerFrame = 0;
     int kpPerFrame = 0;
-    int maxCellBytes = 0;
+    int maxCellBytes = 0, maxCw = 0, maxCh = 0, maxKept = 0, boxW = 0, boxH = 0;
     int blurTiles = 0;
     int status = ORBFE_OK;
 };
@@ -187,9 +187,9 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
                 sp.cells.push_back(c);
                 const int keptCap = ((tw + 1) / 2) * ((th + 1) / 2);
                 cap += keptCap;
-                const int tp = (c.cw + 6) & ~3;   // worst-case tile pitch (k_fast.cu: alignment shift + width, whole words)
-                const int bytes = 2 * tp * c.ch + 2 * 2 * ((tw * th + 1) & ~1) + 4 * keptCap + 16;
-                sp.maxCellBytes = std::max(sp.maxCellBytes, bytes);
+                sp.maxCw = std::max(sp.maxCw, (int)c.cw);
+                sp.maxCh = std::max(sp.maxCh, (int)c.ch);
+                sp.maxKept = std::max(sp.maxKept, keptCap);
             }
         }
         g.nCells = (int)sp.cells.size() - g.cellBase;
@@ -215,6 +215,12 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
     sp.candPerFrame = candOff;
     sp.kpPerFrame = kpOff;
     sp.blurTiles = blurTiles;
+    // FAST tile = TMA box: inner extent a multiple of 16 bytes; layout of k_fast_cells' dynamic smem
+    sp.boxW = (sp.maxCw + 15 + 15) & ~15;   // + up to 15 bytes of alignment shift (TMA start column is 16-byte aligned)
+    sp.boxH = sp.maxCh;
+    const int listCap = ((sp.boxW - 6) * (sp.boxH - 6) + 1) & ~1;
+    sp.maxCellBytes = 2 * sp.boxW * sp.boxH + 2 * 2 * listCap + 4 * sp.maxKept + 16;
+    if (sp.boxW > 256 || sp.boxH > 256) sp.status = ORBFE_ERR_TOO_LARGE;
 }
 
 // ---- handle life cycle ---------------------------------------------------------------------------
@@ -235,6 +241,38 @@ static void free_handle(orbfe_handle* h) {
     delete h;
 }
 
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time dependency on libcuda).
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int encode_fast_maps(orbfe_handle* h) {
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return cuda_fail(e != cudaSuccess ? e : cudaErrorUnknown, "cuTensorMapEncodeTiled entry point");
+        encode = (EncodeTiledFn)fn;
+    }
+    const size_t B = (size_t)h->p.max_batch;
+    for (int l = 0; l < h->p.nlevels; ++l) {
+        const LevelGeom& g = h->geom[l];
+        const cuuint64_t dims[3] = {(cuuint64_t)g.pitch, (cuuint64_t)g.rows, (cuuint64_t)B};
+        const cuuint64_t strides[2] = {(cuuint64_t)g.pitch, (cuuint64_t)g.plane};   // bytes, dims 1 and 2
+        const cuuint32_t box[3] = {(cuuint32_t)h->fastBoxW, (cuuint32_t)h->fastBoxH, 1};
+        const cuuint32_t estr[3] = {1, 1, 1};
+        CUresult r = encode(&h->fastMaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->dPyr + g.base, dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            snprintf(g_cudaErr, sizeof(g_cudaErr), "cuTensorMapEncodeTiled(level %d) failed: CUresult %d", l, (int)r);
+            return ORBFE_ERR_CUDA;
+        }
+    }
+    return ORBFE_OK;
+}
+
 // Upload the geometry of a new image shape (no-op when the shape is unchanged).
 static int configure_shape(orbfe_handle* h, int W, int H) {
     if (W == h->curW && H == h->curH) return ORBFE_OK;
@@ -253,6 +291,12 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     }
     h->nCellsTotal = (int)sp.cells.size();
     h->maxCellBytes = sp.maxCellBytes;
+    h->fastBoxW = sp.boxW;
+    h->fastBoxH = sp.boxH;
+    {
+        int st = encode_fast_maps(h);
+        if (st != ORBFE_OK) return st;
+    }
     h->candPerFrame = sp.candPerFrame;
     h->kpPerFrame = sp.kpPerFrame;
     h->blurTiles = sp.blurTiles;

@@ -1,5 +1,6 @@
 // orbfe_internal.h — handle layout, level geometry and kernel launchers shared by the .cu files.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -61,6 +62,11 @@ struct ColPlan {
     uint32_t keep;         // 0xFF per byte inside [-19, w + 19)
 };
 
+// One tiled tensor map per pyramid level: dims (pitch, rows, frames) of the bordered level, box = FAST tile.
+struct FastMaps {
+    CUtensorMap m[ORBFE_MAX_LEVELS];
+};
+
 struct orbfe_handle {
     orbfe_params p;
     int device;
@@ -74,7 +80,9 @@ struct orbfe_handle {
     int lastBatch;
     LevelGeom geom[ORBFE_MAX_LEVELS];
     int nCellsTotal;
-    int maxCellBytes;       // smem tile bytes of the largest cell
+    int maxCellBytes;       // dynamic smem of k_fast_cells
+    int fastBoxW, fastBoxH; // TMA box of the FAST tile (>= the largest cell, width a multiple of 16)
+    FastMaps fastMaps;
     long long candPerFrame; // candidate entries per frame (all levels)
     int kpPerFrame;         // output slots per frame (= cap of device results)
     // capacities fixed at create
