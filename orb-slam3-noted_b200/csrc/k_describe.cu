@@ -31,10 +31,10 @@ __global__ void __launch_bounds__(ASM_THREADS) k_assemble(const LevelGeom* __res
                                                           const int* __restrict__ lvlCount, int kpPerFrame, int nlevels,
                                                           int lap0, int lap1, orbfe_keypoint* __restrict__ kps,
                                                           uint32_t* __restrict__ slot, int* __restrict__ nOut,
-                                                          int* __restrict__ monoOut) {
+                                                          int* __restrict__ monoOut, int frame0) {
     __shared__ int lvlStart[ORBFE_MAX_LEVELS + 1];
     __shared__ int warpSums[ASM_THREADS / 32 + 1];
-    const int frame = blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+    const int frame = frame0 + blockIdx.x, tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     if (tid == 0) {
         int s = 0;
         for (int l = 0; l < nlevels; ++l) { lvlStart[l] = s; s += lvlCount[frame * nlevels + l]; }
@@ -121,8 +121,8 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 
 // grid.x = ceil(total tiles / 4) (4 warps per CTA, each decodes its own tile), grid.y = frame
 __global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
-                                              const LevelGeom* __restrict__ geom, int nlevels, int totalTiles) {
-    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = blockIdx.y;
+                                              const LevelGeom* __restrict__ geom, int nlevels, int totalTiles, int frame0) {
+    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = frame0 + blockIdx.y;
     if (tile >= totalTiles) return;
     int level = 0;
     while (level + 1 < nlevels && tile >= geom[level + 1].blurTileBase) ++level;
@@ -174,14 +174,14 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const uint8_t* __r
                                                               const LevelGeom* __restrict__ geom,
                                                               const uint32_t* __restrict__ slot, const int* __restrict__ nOut,
                                                               int kpPerFrame, orbfe_keypoint* __restrict__ kps,
-                                                              uint8_t* __restrict__ desc) {
+                                                              uint8_t* __restrict__ desc, int frame0) {
     __shared__ uint32_t sPat[256];
     {
         const int T = threadIdx.x;   // DESC_WARPS * 32 == 256 tests
         sPat[(T & 7) * 32 + (T >> 3)] = __ldg(reinterpret_cast<const uint32_t*>(d_pattern) + T);
     }
     __syncthreads();
-    const int frame = blockIdx.y, i = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const int frame = frame0 + blockIdx.y, i = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (i >= nOut[frame]) return;
     const uint32_t s = slot[(long long)frame * kpPerFrame + i];
     const int level = s >> 28, cy = (s >> 14) & 0x3FFF, cx = s & 0x3FFF;
@@ -235,22 +235,22 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const uint8_t* __r
     if ((lane & 3) == 0) reinterpret_cast<uint32_t*>(desc + ((long long)frame * kpPerFrame + i) * 32)[lane >> 2] = w;
 }
 
-cudaError_t orbfe_launch_assemble(orbfe_handle* h, int batch, int lap0, int lap1) {
+cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int lap0, int lap1) {
     k_assemble<<<batch, ASM_THREADS, 0, h->stream>>>(h->dGeom, h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, lap0, lap1,
-                                                     h->dKps, h->dSlot, h->dN, h->dMono);
+                                                     h->dKps, h->dSlot, h->dN, h->dMono, frame0);
     h->launches++;
     return cudaGetLastError();
 }
 
-cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch) {
+cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch) {
     {
         dim3 grid((h->blurTiles + 3) / 4, batch);
-        k_blur<<<grid, 128, 0, h->stream>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles);
+        k_blur<<<grid, 128, 0, h->stream>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles, frame0);
         h->launches++;
     }
     dim3 grid((h->kpPerFrame + DESC_WARPS - 1) / DESC_WARPS, batch);
     k_describe<<<grid, DESC_WARPS * 32, 0, h->stream>>>(h->dPyr, h->dBlur, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps,
-                                                       h->dDesc);
+                                                       h->dDesc, frame0);
     h->launches++;
     return cudaGetLastError();
 }

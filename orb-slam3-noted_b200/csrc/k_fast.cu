@@ -104,12 +104,12 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
                                                              const LevelGeom* __restrict__ geom,
                                                              const CellDesc* __restrict__ cells, uint32_t* __restrict__ cand,
                                                              int* __restrict__ candCount, long long candPerFrame,
-                                                             int nlevels, int iniTh, int minTh, int boxW, int boxH) {
+                                                             int nlevels, int iniTh, int minTh, int boxW, int boxH, int frame0) {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t sBar;
     __shared__ int sCand, sCorners, sKept, sBase;
     const CellDesc cd = cells[blockIdx.x];
-    const int frame = blockIdx.y;
+    const int frame = frame0 + blockIdx.y;
     const LevelGeom& g = geom[cd.level];
     const int cw = cd.cw, ch = cd.ch;
     const int tp = boxW;                     // dense tile as delivered by TMA
@@ -258,8 +258,8 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
     for (int i = tid; i < nk; i += FAST_THREADS) out[i] = kept[i];
 }
 
-cudaError_t orbfe_launch_fast(orbfe_handle* h, int batch) {
-    cudaError_t e = cudaMemsetAsync(h->dCandCount, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->stream);
+cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
+    cudaError_t e = cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->stream);
     if (e != cudaSuccess) return e;
     static size_t configured = 0;
     if ((size_t)h->maxCellBytes > 48 * 1024 && (size_t)h->maxCellBytes > configured) {
@@ -270,7 +270,7 @@ cudaError_t orbfe_launch_fast(orbfe_handle* h, int batch) {
     dim3 grid(h->nCellsTotal, batch);
     k_fast_cells<<<grid, FAST_THREADS, h->maxCellBytes, h->stream>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,
                                                                      h->candPerFrame, h->p.nlevels, h->p.ini_th_fast,
-                                                                     h->p.min_th_fast, h->fastBoxW, h->fastBoxH);
+                                                                     h->p.min_th_fast, h->fastBoxW, h->fastBoxH, frame0);
     h->launches++;
     return cudaGetLastError();
 }

@@ -99,10 +99,10 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(const LevelGeom* __restr
                                                         uint32_t* __restrict__ nodeOfAll, const int* __restrict__ candCount,
                                                         long long candPerFrame, uint32_t* __restrict__ lvlKp,
                                                         int* __restrict__ lvlCount, int kpPerFrame, int nlevels, int Lcap,
-                                                        int sortCap) {
+                                                        int sortCap, int frame0) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ int warpSums[OCT_THREADS / 32 + 1];
-    const int level = blockIdx.x, frame = blockIdx.y, tid = threadIdx.x;
+    const int level = blockIdx.x, frame = frame0 + blockIdx.y, tid = threadIdx.x;
     const LevelGeom& g = geom[level];
     const int K = candCount[frame * nlevels + level];
     const uint32_t* keys = cand + (long long)frame * candPerFrame + g.candBase;
@@ -324,7 +324,7 @@ static size_t octree_smem_bytes(int Lcap, int sortCap) {
     return (size_t)sortCap * 8 + (size_t)Lcap * (2 * sizeof(NodeS) + 4 * 4 + 4 + 4 + 4 * 2 + 2) + 64;
 }
 
-cudaError_t orbfe_launch_octree(orbfe_handle* h, int batch) {
+cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch) {
     int Lcap = 0;
     for (int l = 0; l < h->p.nlevels; ++l) Lcap = h->geom[l].kpCap > Lcap ? h->geom[l].kpCap : Lcap;
     Lcap = (Lcap + 7) & ~7;
@@ -339,7 +339,7 @@ cudaError_t orbfe_launch_octree(orbfe_handle* h, int batch) {
     }
     dim3 grid(h->p.nlevels, batch);
     k_octree<<<grid, OCT_THREADS, smem, h->stream>>>(h->dGeom, h->dCand, h->dNodeOf, h->dCandCount, h->candPerFrame,
-                                                     h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, Lcap, sortCap);
+                                                     h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, Lcap, sortCap, frame0);
     h->launches++;
     return cudaGetLastError();
 }

@@ -18,7 +18,7 @@ __device__ __forceinline__ int reflect101(int i, int n) {
 }
 
 __global__ void __launch_bounds__(128) k_pyr_level0(const uint8_t* __restrict__ in, long long stride,
-                                                    long long frameStride, uint8_t* __restrict__ out, LevelGeom g) {
+                                                    long long frameStride, uint8_t* __restrict__ out, LevelGeom g, int frame0) {
     const int word = blockIdx.x * blockDim.x + threadIdx.x;
     const int row = blockIdx.y;
     if (word * 4 >= g.pitch) return;
@@ -31,19 +31,19 @@ __global__ void __launch_bounds__(128) k_pyr_level0(const uint8_t* __restrict__ 
         const int x = x0 + k;
         if (x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE) v |= (uint32_t)__ldg(src + reflect101(x, g.w)) << (8 * k);
     }
-    uint8_t* dst = out + g.base + (long long)blockIdx.z * g.plane + (long long)row * g.pitch;
+    uint8_t* dst = out + g.base + (long long)(frame0 + blockIdx.z) * g.plane + (long long)row * g.pitch;
     reinterpret_cast<uint32_t*>(dst)[word] = v;
 }
 
 // gs = source level geometry, gd = destination level geometry.
 __global__ void __launch_bounds__(128) k_pyr_resize(uint8_t* __restrict__ pyr, LevelGeom gs, LevelGeom gd,
-                                                    const ResizeTap* __restrict__ taps) {
+                                                    const ResizeTap* __restrict__ taps, int frame0) {
     const int word = blockIdx.x * blockDim.x + threadIdx.x;
     const int row = blockIdx.y;
     if (word * 4 >= gd.pitch) return;
     const int y = reflect101(row - ORBFE_EDGE, gd.h);
     const ResizeTap ty = taps[gd.tabY + y];
-    const uint8_t* sbase = pyr + gs.base + (long long)blockIdx.z * gs.plane + (long long)ORBFE_EDGE * gs.pitch + ORBFE_XO;
+    const uint8_t* sbase = pyr + gs.base + (long long)(frame0 + blockIdx.z) * gs.plane + (long long)ORBFE_EDGE * gs.pitch + ORBFE_XO;
     const uint8_t* S0 = sbase + (long long)ty.s0 * gs.pitch;
     const uint8_t* S1 = sbase + (long long)ty.s1 * gs.pitch;
     const int x0 = word * 4 - ORBFE_XO;
@@ -59,7 +59,7 @@ __global__ void __launch_bounds__(128) k_pyr_resize(uint8_t* __restrict__ pyr, L
             v |= (uint32_t)(o & 0xFF) << (8 * k);
         }
     }
-    uint8_t* dst = pyr + gd.base + (long long)blockIdx.z * gd.plane + (long long)row * gd.pitch;
+    uint8_t* dst = pyr + gd.base + (long long)(frame0 + blockIdx.z) * gd.plane + (long long)row * gd.pitch;
     reinterpret_cast<uint32_t*>(dst)[word] = v;
 }
 
@@ -75,8 +75,8 @@ __global__ void __launch_bounds__(128) k_pyr_resize(uint8_t* __restrict__ pyr, L
 
 __global__ void __launch_bounds__(128) k_pyr_resize_plan(uint8_t* __restrict__ pyr, LevelGeom gs, LevelGeom gd,
                                                          const ResizeTap* __restrict__ taps, const ColPlan* __restrict__ plans,
-                                                         int tilesX, int totalTiles) {
-    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = blockIdx.y;
+                                                         int tilesX, int totalTiles, int frame0) {
+    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = frame0 + blockIdx.y;
     if (tile >= totalTiles) return;
     const int ty = tile / tilesX, tx = tile - ty * tilesX;
     const int word = tx * 32 + lane;
@@ -111,14 +111,14 @@ __global__ void __launch_bounds__(128) k_pyr_resize_plan(uint8_t* __restrict__ p
     }
 }
 
-cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int batch, int width, int height,
+cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int width, int height,
                                  long long stride, long long frameStride) {
     (void)width; (void)height;
     const int nl = h->p.nlevels;
     {
         const LevelGeom& g = h->geom[0];
         dim3 grid((g.pitch / 4 + 127) / 128, g.rows, batch);
-        k_pyr_level0<<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g);
+        k_pyr_level0<<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
         h->launches++;
     }
     for (int l = 1; l < nl; ++l) {
@@ -126,10 +126,10 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int ba
         if (gd.planBase >= 0) {
             const int tilesX = gd.pitch / 128, total = tilesX * ((gd.rows + PYR_TH - 1) / PYR_TH);
             dim3 grid((total + 3) / 4, batch);
-            k_pyr_resize_plan<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total);
+            k_pyr_resize_plan<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total, frame0);
         } else {   // scale factors whose 2-column source window exceeds 8 bytes: generic kernel
             dim3 grid((gd.pitch / 4 + 127) / 128, gd.rows, batch);
-            k_pyr_resize<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps);
+            k_pyr_resize<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, frame0);
         }
         h->launches++;
     }

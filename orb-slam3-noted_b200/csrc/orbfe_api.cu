@@ -237,6 +237,11 @@ static void free_handle(orbfe_handle* h) {
             for (int s = 0; s <= ORBFE_NUM_STAGES; ++s) cudaEventDestroy(h->profEv[i][s]);
         delete[] h->profEv;
     }
+    for (int c = 0; c < ORBFE_PIPE_MAX_CHUNKS; ++c)
+        for (int k = 0; k < 3; ++k)
+            if (h->evPipe[c][k]) cudaEventDestroy(h->evPipe[c][k]);
+    if (h->sIn) cudaStreamDestroy(h->sIn);
+    if (h->sOut) cudaStreamDestroy(h->sOut);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -347,6 +352,10 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     } while (0)
     CKC(cudaSetDevice(h->device));
     CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    CKC(cudaStreamCreateWithFlags(&h->sIn, cudaStreamNonBlocking));
+    CKC(cudaStreamCreateWithFlags(&h->sOut, cudaStreamNonBlocking));
+    for (int c = 0; c < ORBFE_PIPE_MAX_CHUNKS; ++c)
+        for (int k = 0; k < 3; ++k) CKC(cudaEventCreateWithFlags(&h->evPipe[c][k], cudaEventDisableTiming));
     CKC(cudaMalloc(&h->dIn, h->inBytes));
     CKC(cudaMalloc(&h->dPyr, h->pyrBytes));
     CKC(cudaMalloc(&h->dBlur, h->pyrBytes));
@@ -406,7 +415,8 @@ static int prof_fold_oldest(orbfe_handle* h) {
     return ORBFE_OK;
 }
 
-static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int batch, int W, int H, long long stride,
+// Enqueues the five stages for frames [frame0, frame0 + batch) of the arenas; dImages = first of those frames.
+static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int W, int H, long long stride,
                            long long frameStride, int lap0, int lap1) {
     cudaError_t e;
     cudaEvent_t* ev = nullptr;
@@ -415,17 +425,17 @@ static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int batch, i
         ev = h->profEv[(h->profHead + h->profCount) % ORBFE_PROF_RING];
         CK(cudaEventRecord(ev[0], h->stream));
     }
-    if ((e = orbfe_launch_pyramid(h, dImages, batch, W, H, stride, frameStride)) != cudaSuccess) return cuda_fail(e, "pyramid");
+    if ((e = orbfe_launch_pyramid(h, dImages, frame0, batch, W, H, stride, frameStride)) != cudaSuccess) return cuda_fail(e, "pyramid");
     if (ev) CK(cudaEventRecord(ev[1], h->stream));
-    if ((e = orbfe_launch_fast(h, batch)) != cudaSuccess) return cuda_fail(e, "fast");
+    if ((e = orbfe_launch_fast(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "fast");
     if (ev) CK(cudaEventRecord(ev[2], h->stream));
-    if ((e = orbfe_launch_octree(h, batch)) != cudaSuccess) return cuda_fail(e, "octree");
+    if ((e = orbfe_launch_octree(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "octree");
     if (ev) CK(cudaEventRecord(ev[3], h->stream));
-    if ((e = orbfe_launch_assemble(h, batch, lap0, lap1)) != cudaSuccess) return cuda_fail(e, "assemble");
+    if ((e = orbfe_launch_assemble(h, frame0, batch, lap0, lap1)) != cudaSuccess) return cuda_fail(e, "assemble");
     if (ev) CK(cudaEventRecord(ev[4], h->stream));
-    if ((e = orbfe_launch_describe(h, batch)) != cudaSuccess) return cuda_fail(e, "describe");
+    if ((e = orbfe_launch_describe(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "describe");
     if (ev) { CK(cudaEventRecord(ev[5], h->stream)); h->profCount++; }
-    h->lastBatch = batch;
+    h->lastBatch = std::max(h->lastBatch, frame0 + batch);
     return ORBFE_OK;
 }
 
@@ -464,7 +474,8 @@ extern "C" int orbfe_extract_batch_device(orbfe_handle* h, const uint8_t* d_imag
     CK(cudaSetDevice(h->device));
     int st = configure_shape(h, width, height);
     if (st != ORBFE_OK) return st;
-    return enqueue_extract(h, d_images, batch, width, height, stride, frame_stride, lap0, lap1);
+    h->lastBatch = 0;
+    return enqueue_extract(h, d_images, 0, batch, width, height, stride, frame_stride, lap0, lap1);
 }
 
 extern "C" int orbfe_fetch_results(orbfe_handle* h, int batch, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n_out,
@@ -511,17 +522,50 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
     CK(cudaSetDevice(h->device));
     int st = configure_shape(h, width, height);
     if (st != ORBFE_OK) return st;
-    // stage the frames densely (row stride = width) in the input arena
-    if (stride == width && frame_stride == (ptrdiff_t)width * height) {
-        CK(cudaMemcpyAsync(h->dIn, images, (size_t)width * height * batch, cudaMemcpyHostToDevice, h->stream));
-    } else {
-        for (int b = 0; b < batch; ++b)
-            CK(cudaMemcpy2DAsync(h->dIn + (size_t)b * width * height, width, images + (size_t)b * frame_stride, stride, width, height,
-                                 cudaMemcpyHostToDevice, h->stream));
+    if (!kps || !desc || !n_out) return ORBFE_ERR_BAD_ARGUMENT;
+    // Chunked pipeline: the H2D copy of chunk k+1 (copy-in stream) overlaps the kernels of chunk k (main
+    // stream) and the D2H copy of chunk k-1's results (copy-out stream).  Frames are staged densely
+    // (row stride = width) in the input arena.
+    const int chunk = batch <= ORBFE_PIPE_CHUNK + ORBFE_PIPE_CHUNK / 2 ? batch : ORBFE_PIPE_CHUNK;
+    const int nchunks = (batch + chunk - 1) / chunk;
+    if (nchunks > ORBFE_PIPE_MAX_CHUNKS) return ORBFE_ERR_TOO_LARGE;
+    const int kpf = h->kpPerFrame;
+    const size_t fbytes = (size_t)width * height;
+    h->lastBatch = 0;
+    CK(cudaEventRecord(h->evPipe[0][0], h->stream));          // copy-in must not overtake earlier work on the arenas
+    CK(cudaStreamWaitEvent(h->sIn, h->evPipe[0][0], 0));
+    for (int c = 0; c < nchunks; ++c) {
+        const int f0 = c * chunk, nb = std::min(chunk, batch - f0);
+        if (stride == width && frame_stride == (ptrdiff_t)fbytes) {
+            CK(cudaMemcpyAsync(h->dIn + f0 * fbytes, images + f0 * fbytes, fbytes * nb, cudaMemcpyHostToDevice, h->sIn));
+        } else {
+            for (int b = f0; b < f0 + nb; ++b)
+                CK(cudaMemcpy2DAsync(h->dIn + b * fbytes, width, images + (size_t)b * frame_stride, stride, width, height,
+                                     cudaMemcpyHostToDevice, h->sIn));
+        }
+        CK(cudaEventRecord(h->evPipe[c][1], h->sIn));
+        CK(cudaStreamWaitEvent(h->stream, h->evPipe[c][1], 0));
+        st = enqueue_extract(h, h->dIn + f0 * fbytes, f0, nb, width, height, width, (long long)fbytes, lap0, lap1);
+        if (st != ORBFE_OK) return st;
+        CK(cudaEventRecord(h->evPipe[c][2], h->stream));
+        CK(cudaStreamWaitEvent(h->sOut, h->evPipe[c][2], 0));
+        CK(cudaMemcpyAsync(h->hN + f0, h->dN + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
+        CK(cudaMemcpyAsync(h->hMono + f0, h->dMono + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
+        if (cap >= kpf) {
+            CK(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, sizeof(orbfe_keypoint) * (size_t)cap, h->dKps + (size_t)f0 * kpf,
+                                 sizeof(orbfe_keypoint) * (size_t)kpf, sizeof(orbfe_keypoint) * (size_t)kpf, nb,
+                                 cudaMemcpyDeviceToHost, h->sOut));
+            CK(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, 32 * (size_t)cap, h->dDesc + (size_t)f0 * kpf * 32, 32 * (size_t)kpf,
+                                 32 * (size_t)kpf, nb, cudaMemcpyDeviceToHost, h->sOut));
+        }
     }
-    st = enqueue_extract(h, h->dIn, batch, width, height, width, (long long)width * height, lap0, lap1);
-    if (st != ORBFE_OK) return st;
-    return orbfe_fetch_results(h, batch, kps, desc, cap, n_out, mono_out);
+    CK(cudaStreamSynchronize(h->sOut));
+    CK(cudaStreamSynchronize(h->stream));
+    if (cap >= kpf) {
+        for (int b = 0; b < batch; ++b) { n_out[b] = h->hN[b]; if (mono_out) mono_out[b] = h->hMono[b]; }
+        return ORBFE_OK;
+    }
+    return orbfe_fetch_results(h, batch, kps, desc, cap, n_out, mono_out);   // tight caller buffers: per-frame copies
 }
 
 extern "C" int orbfe_extract(orbfe_handle* h, const uint8_t* image, int width, int height, ptrdiff_t stride, int lap0, int lap1,

@@ -12,7 +12,9 @@
 #define ORBFE_EDGE 19          // EDGE_THRESHOLD, ORBextractor.cc:71
 #define ORBFE_XO 32            // byte offset of ROI column 0 inside a bordered row (keeps ROI 32B-aligned)
 #define ORBFE_MIN_BORDER 16    // EDGE_THRESHOLD - 3, ORBextractor.cc:771
-#define ORBFE_MAX_NODES 2048   // per-level quota ceiling of the on-chip quadtree
+#define ORBFE_MAX_NODES 2048
+#define ORBFE_PIPE_CHUNK 128       // frames per chunk of the pipelined host path (orbfe_extract_batch)
+#define ORBFE_PIPE_MAX_CHUNKS 64   // per-level quota ceiling of the on-chip quadtree
 
 // Packed FAST candidate: x | y << 11 | response << 22, (x, y) relative to (minBorderX, minBorderY).
 #define ORBFE_CAND_X(c) ((int)((c) & 0x7FFu))
@@ -71,6 +73,8 @@ struct orbfe_handle {
     orbfe_params p;
     int device;
     cudaStream_t stream;
+    cudaStream_t sIn, sOut;                          // copy-in / copy-out streams of the pipelined host path
+    cudaEvent_t evPipe[ORBFE_PIPE_MAX_CHUNKS][3];    // per chunk: [0][0] fence, [c][1] frames landed, [c][2] results ready
     long long launches;
     // reference tables (ORBextractor.cc:413-444)
     float scale[ORBFE_MAX_LEVELS], invScale[ORBFE_MAX_LEVELS], sigma2[ORBFE_MAX_LEVELS], invSigma2[ORBFE_MAX_LEVELS];
@@ -121,9 +125,11 @@ struct orbfe_handle {
 #define ORBFE_PROF_RING 64
 
 // ---- launchers (each returns cudaGetLastError()) -------------------------------------------------
-cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int batch, int width, int height,
+// Every launcher processes frames [frame0, frame0 + batch) of the handle's arenas (chunked pipelining of
+// the host path); dImages points at the first of those frames.
+cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int width, int height,
                                  long long stride, long long frameStride);
-cudaError_t orbfe_launch_fast(orbfe_handle* h, int batch);
-cudaError_t orbfe_launch_octree(orbfe_handle* h, int batch);
-cudaError_t orbfe_launch_assemble(orbfe_handle* h, int batch, int lap0, int lap1);
-cudaError_t orbfe_launch_describe(orbfe_handle* h, int batch);
+cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch);
+cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch);
+cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int lap0, int lap1);
+cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch);
