@@ -3,6 +3,7 @@
 // k_*.cu kernels.  There is no CPU fallback: without a CUDA device every call returns an error.
 #include <math.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -242,6 +243,7 @@ static void free_handle(orbfe_handle* h) {
             if (h->evPipe[c][k]) cudaEventDestroy(h->evPipe[c][k]);
     if (h->sIn) cudaStreamDestroy(h->sIn);
     if (h->sOut) cudaStreamDestroy(h->sOut);
+    if (h->sAlt) cudaStreamDestroy(h->sAlt);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -354,6 +356,7 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&h->sIn, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&h->sOut, cudaStreamNonBlocking));
+    CKC(cudaStreamCreateWithFlags(&h->sAlt, cudaStreamNonBlocking));
     for (int c = 0; c < ORBFE_PIPE_MAX_CHUNKS; ++c)
         for (int k = 0; k < 3; ++k) CKC(cudaEventCreateWithFlags(&h->evPipe[c][k], cudaEventDisableTiming));
     CKC(cudaMalloc(&h->dIn, h->inBytes));
@@ -526,16 +529,31 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
     // Chunked pipeline: the H2D copy of chunk k+1 (copy-in stream) overlaps the kernels of chunk k (main
     // stream) and the D2H copy of chunk k-1's results (copy-out stream).  Frames are staged densely
     // (row stride = width) in the input arena.
-    const int chunk = batch <= ORBFE_PIPE_CHUNK + ORBFE_PIPE_CHUNK / 2 ? batch : ORBFE_PIPE_CHUNK;
-    const int nchunks = (batch + chunk - 1) / chunk;
-    if (nchunks > ORBFE_PIPE_MAX_CHUNKS) return ORBFE_ERR_TOO_LARGE;
+    static const int pipeChunk = [] { const char* e = getenv("ORBFE_PIPE_CHUNK"); int v = e ? atoi(e) : 0; return v > 0 ? v : ORBFE_PIPE_CHUNK; }();
+    // chunk boundaries: a short first chunk (its copy-in is the only one nothing overlaps), then full chunks
+    int bounds[ORBFE_PIPE_MAX_CHUNKS + 1];
+    int nchunks = 0;
+    bounds[0] = 0;
+    if (batch <= pipeChunk + pipeChunk / 2) {
+        bounds[++nchunks] = batch;
+    } else {
+        int f = std::min(pipeChunk / 4 > 0 ? pipeChunk / 4 : 1, batch);
+        bounds[++nchunks] = f;
+        while (f < batch) {
+            if (nchunks >= ORBFE_PIPE_MAX_CHUNKS) return ORBFE_ERR_TOO_LARGE;
+            f = batch - f <= pipeChunk + pipeChunk / 2 ? batch : f + pipeChunk;
+            bounds[++nchunks] = f;
+        }
+    }
     const int kpf = h->kpPerFrame;
     const size_t fbytes = (size_t)width * height;
     h->lastBatch = 0;
-    CK(cudaEventRecord(h->evPipe[0][0], h->stream));          // copy-in must not overtake earlier work on the arenas
+    cudaStream_t mainStream = h->stream;
+    CK(cudaEventRecord(h->evPipe[0][0], h->stream));          // copy-in / the second compute stream must not overtake earlier work
     CK(cudaStreamWaitEvent(h->sIn, h->evPipe[0][0], 0));
+    CK(cudaStreamWaitEvent(h->sAlt, h->evPipe[0][0], 0));
     for (int c = 0; c < nchunks; ++c) {
-        const int f0 = c * chunk, nb = std::min(chunk, batch - f0);
+        const int f0 = bounds[c], nb = bounds[c + 1] - f0;
         if (stride == width && frame_stride == (ptrdiff_t)fbytes) {
             CK(cudaMemcpyAsync(h->dIn + f0 * fbytes, images + f0 * fbytes, fbytes * nb, cudaMemcpyHostToDevice, h->sIn));
         } else {
@@ -544,10 +562,15 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
                                      cudaMemcpyHostToDevice, h->sIn));
         }
         CK(cudaEventRecord(h->evPipe[c][1], h->sIn));
-        CK(cudaStreamWaitEvent(h->stream, h->evPipe[c][1], 0));
+        // chunks alternate between two compute streams, so the latency-bound stages of one chunk (small
+        // pyramid levels, quadtree) run under the wide stages of its neighbour
+        cudaStream_t compute = (c & 1) ? h->sAlt : mainStream;
+        CK(cudaStreamWaitEvent(compute, h->evPipe[c][1], 0));
+        h->stream = compute;
         st = enqueue_extract(h, h->dIn + f0 * fbytes, f0, nb, width, height, width, (long long)fbytes, lap0, lap1);
+        h->stream = mainStream;
         if (st != ORBFE_OK) return st;
-        CK(cudaEventRecord(h->evPipe[c][2], h->stream));
+        CK(cudaEventRecord(h->evPipe[c][2], compute));
         CK(cudaStreamWaitEvent(h->sOut, h->evPipe[c][2], 0));
         CK(cudaMemcpyAsync(h->hN + f0, h->dN + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
         CK(cudaMemcpyAsync(h->hMono + f0, h->dMono + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
@@ -560,6 +583,7 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
         }
     }
     CK(cudaStreamSynchronize(h->sOut));
+    CK(cudaStreamSynchronize(h->sAlt));
     CK(cudaStreamSynchronize(h->stream));
     if (cap >= kpf) {
         for (int b = 0; b < batch; ++b) { n_out[b] = h->hN[b]; if (mono_out) mono_out[b] = h->hMono[b]; }

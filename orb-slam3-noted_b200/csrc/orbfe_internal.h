@@ -13,7 +13,7 @@
 #define ORBFE_XO 32            // byte offset of ROI column 0 inside a bordered row (keeps ROI 32B-aligned)
 #define ORBFE_MIN_BORDER 16    // EDGE_THRESHOLD - 3, ORBextractor.cc:771
 #define ORBFE_MAX_NODES 2048
-#define ORBFE_PIPE_CHUNK 128       // frames per chunk of the pipelined host path (orbfe_extract_batch)
+#define ORBFE_PIPE_CHUNK 64        // frames per chunk of the pipelined host path (orbfe_extract_batch)
 #define ORBFE_PIPE_MAX_CHUNKS 64   // per-level quota ceiling of the on-chip quadtree
 
 // Packed FAST candidate: x | y << 11 | response << 22, (x, y) relative to (minBorderX, minBorderY).
@@ -74,6 +74,7 @@ struct orbfe_handle {
     int device;
     cudaStream_t stream;
     cudaStream_t sIn, sOut;                          // copy-in / copy-out streams of the pipelined host path
+    cudaStream_t sAlt;                               // second compute stream: odd chunks of the pipelined host path
     cudaEvent_t evPipe[ORBFE_PIPE_MAX_CHUNKS][3];    // per chunk: [0][0] fence, [c][1] frames landed, [c][2] results ready
     long long launches;
     // reference tables (ORBextractor.cc:413-444)
