@@ -53,7 +53,7 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled every 200 ms during the timed region."""
+    """nvidia-smi clocks / throttle reasons sampled every 50 ms during the timed regions."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -65,7 +65,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "200"], stdout=subprocess.PIPE,
+                                          "--format=csv,noheader,nounits", "-lms", "50"], stdout=subprocess.PIPE,
                                          stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -333,7 +333,6 @@ def run_orbfe(args):
         e2e_step()
     barrier()
     e2e_s = time.perf_counter() - t0
-    clk = clocks.stop()
 
     if world > 1:
         t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
@@ -343,6 +342,7 @@ def run_orbfe(args):
         dist.all_reduce(tl)
         launches = int(tl[0])
     matching = None if args.no_match else run_matching(args, torch, orbfe, rank, local, world, barrier, dist)
+    clk = clocks.stop()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -359,6 +359,13 @@ def run_orbfe(args):
     top = max(stage_ms, key=stage_ms.get)
     top_ms = stage_ms[top] / max(calls, 1)
     peak, how = measured_peaks()
+    traffic = None
+    try:   # DRAM bytes per launch of the dominant stage from the committed ncu --set full capture
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        if top in tj["dram_bytes_per_frame"]:
+            traffic = tj["dram_bytes_per_frame"][top] * B
+    except Exception:
+        pass
     achieved = b_alg * B / (top_ms / 1e3) / 1e9
     whole = b_alg * B * K / (ms / 1e3) / 1e9
     out = {
@@ -371,11 +378,12 @@ def run_orbfe(args):
                          f"{B * sum((a + 38) * (b + 38) for a, b in level_sizes) / 1e6:.0f} MB pyramid per step vs 126 MB L2"},
         "e2e": {"value": e2e_v, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),
                 "d2h_bytes_per_step": int(B * ex.cap * 60 + 8 * B), "ms_per_step": 1e3 * e2e_s / K,
-                "api": "orbfe_extract_batch (host buffers, pinned)"},
+                "api": "orbfe_extract_batch (pinned host buffers; 64-frame chunks pipelined over copy-in / 2 compute / copy-out streams)"},
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None, "peak_source": how,
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": "profiles/traffic.json (ncu dram__bytes_read+write, scaled per frame)",
+                     "peak_source": how,
                      "algorithmic_bytes_per_frame": b_alg, "frames_per_launch": B, "kernel_ms_per_launch": top_ms,
                      "whole_path_achieved": whole, "whole_path_frac": whole / peak,
                      "stage_ms_per_step": {k: v / max(calls, 1) for k, v in stage_ms.items()}},
@@ -397,7 +405,7 @@ def run_orbfe(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--batch", type=int, default=512, help="frames per step per GPU")
     ap.add_argument("--distinct", type=int, default=64, help="distinct synthetic frames tiled into the batch")
