@@ -188,6 +188,21 @@ int orbfe_hamming_knn2_batch_device(orbfe_matcher* m, const uint8_t* d_q, ptrdif
 int orbfe_match_lapping(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio,
                         int32_t* match);
 
+/* Frame::ComputeStereoFishEyeMatches (Frame.cc:1116-1156), whole function: 2-NN + Lowe ratio 0.7 between
+ * the lapping-area features (rows mono_left.. of the left list, mono_right.. of the right list), then
+ * KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:338-407: parallax cos < 0.9998, both depths
+ * positive, reprojection error^2 <= 5.991 sigma^2 in both views) and depth > 1e-4.
+ * cam1 / cam2: fx, fy, cx, cy, k1..k4 of the two Kannala-Brandt cameras; R12 (row-major 3x3), t12:
+ * mRlr / mtlr; sigma2: mvLevelSigma2[nlevels].  Outputs (host): left_to_right[n_left],
+ * right_to_left[n_right] (-1 none), depth[n_left] (-1 none), p3d[n_left * 3] (mvStereo3Dpoints).
+ * The triangulation ends in a 4x4 SVD (cv::SVD in the reference): results agree to float tolerance.
+ * Returns nMatches or a negative status. */
+int orbfe_fisheye_stereo_match(orbfe_matcher* m, const orbfe_keypoint* kps_left, const uint8_t* desc_left, int n_left,
+                               int mono_left, const orbfe_keypoint* kps_right, const uint8_t* desc_right, int n_right,
+                               int mono_right, const float* cam1, const float* cam2, const float* R12, const float* t12,
+                               const float* sigma2, int nlevels, int32_t* left_to_right, int32_t* right_to_left, float* depth,
+                               float* p3d);
+
 /* Frame::ComputeStereoMatches (Frame.cc:794-964), "SearchStereo": rectified-stereo row-band search
  * (Hamming < 75 among right keypoints whose row band covers the left keypoint, octave within +-1,
  * disparity in [0, bf/b]), 11x11 SAD refinement over +-5 px on the pyramid level of the left

@@ -166,3 +166,15 @@ long orbref_knn2_many(const uint8_t* q, int nq, const uint8_t* t, int nt, int np
 }
 
 }  // extern "C"
+
+extern "C" {
+// ---- KB8 fisheye (kb8_ref.cc)
+void orbref_kb8_project(const float* cam, const float* p, float* uv) { kb8Project(*(const Kb8*)cam, p, uv); }
+void orbref_kb8_unproject(const float* cam, float u, float v, float* ray) { kb8Unproject(*(const Kb8*)cam, u, v, ray); }
+int orbref_fisheye_stereo(const float* cam1, const float* cam2, const KeyPoint* kpL, const uint8_t* descL, int nL, int monoLeft,
+                          const KeyPoint* kpR, const uint8_t* descR, int nR, int monoRight, const float* R12, const float* t12,
+                          const float* sigma2, int32_t* l2r, int32_t* r2l, float* depth, float* p3d, float* margins) {
+    return computeStereoFishEyeMatches(*(const Kb8*)cam1, *(const Kb8*)cam2, kpL, descL, nL, monoLeft, kpR, descR, nR, monoRight, R12,
+                                       t12, sigma2, l2r, r2l, depth, p3d, margins);
+}
+}

@@ -79,3 +79,26 @@ int searchForTriangulation(const KeyPoint* kpA, const uint8_t* descA, int nA, co
 void knn2RatioMatch(const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match);
 
 }  // namespace orbref
+
+// ---- Kannala-Brandt fisheye stereo (Frame::ComputeStereoFishEyeMatches, Frame.cc:1116-1156) ------------
+namespace orbref {
+
+struct Kb8 { float fx, fy, cx, cy, k0, k1, k2, k3; };   // mvParameters[0..7]
+
+// KannalaBrandt8::project / unproject (KannalaBrandt8.cpp:24-40, 96-123), float32 like the reference.
+void kb8Project(const Kb8& c, const float p[3], float uv[2]);
+void kb8Unproject(const Kb8& c, float u, float v, float ray[3]);
+// KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:338-407): returns z1 (depth in camera 1) or -1.
+// The 4x4 cv::SVD of Triangulate (:514-526) is replaced by a double-precision Jacobi eigen-solve of A^T A:
+// float-tolerance parity only.  margin (nullable) receives the smallest relative distance
+// of any of the five accept tests to its threshold, so tests can skip knife-edge cases.
+float kb8TriangulateMatches(const Kb8& c1, const Kb8& c2, const KeyPoint& kp1, const KeyPoint& kp2, const float R12[9],
+                            const float t12[3], float sigmaLevel, float unc, float p3D[3], float* margin);
+// The whole function: lapping-area 2-NN + Lowe ratio 0.7 + triangulation; accept depth > 0.0001.
+// leftToRight[nL], rightToLeft[nR] (-1 none), depth[nL] (-1 none), p3d[nL*3].
+int computeStereoFishEyeMatches(const Kb8& c1, const Kb8& c2, const KeyPoint* kpL, const uint8_t* descL, int nL, int monoLeft,
+                                const KeyPoint* kpR, const uint8_t* descR, int nR, int monoRight, const float R12[9],
+                                const float t12[3], const float* sigma2, int32_t* leftToRight, int32_t* rightToLeft,
+                                float* depth, float* p3d, float* margins);
+
+}  // namespace orbref

@@ -83,6 +83,16 @@ def main():
         np.savez_compressed(os.path.join(out, f"match_{name}.npz"), in_crc=crc(c["q"], c["t"]), match=match, idx=idx, dist=dist)
         print(name, len(c["q"]), "x", len(c["t"]), "->", int((match >= 0).sum()), "matches")
 
+    for name in mc.FISHEYE_CASES:
+        c = mc.fisheye_inputs(name)
+        l2r, r2l, depth, p3d, margins, n = mp.compute_stereo_fisheye_matches(c["cam1"], c["cam2"], c["kL"], c["dL"], c["mono_l"],
+                                                                            c["kR"], c["dR"], c["mono_r"], c["R12"], c["t12"],
+                                                                            sigma2)
+        np.savez_compressed(os.path.join(out, f"match_{name}.npz"), in_crc=crc(c["kL"], c["dL"], c["kR"], c["dR"]), l2r=l2r,
+                            r2l=r2l, depth=depth, p3d=p3d, margins=margins, n=n)
+        tried = int((margins < 1e29).sum())
+        print(name, tried, "descriptor matches ->", n, "triangulated; knife-edge (margin < 1e-3):", int((margins < 1e-3).sum()))
+
     q, t = mc.knn_inputs()
     match, idx, dist = mp.fisheye_lapping_match(q, t)
     np.savez_compressed(os.path.join(out, "match_knn_ties.npz"), in_crc=crc(q, t), match=match, idx=idx, dist=dist)

@@ -344,3 +344,105 @@ def fisheye_lapping_match(descL, descR):
         if len(it) >= 2 and it[0].distance < it[1].distance * 0.7:
             out[i] = it[0].trainIdx
     return out, idx, dist
+
+
+# ---- Kannala-Brandt fisheye stereo (Frame.cc:1116-1156, KannalaBrandt8.cpp) ------------------------------
+def kb8_project(cam, p):
+    """KannalaBrandt8.cpp:24-40.  cam = (fx, fy, cx, cy, k0..k3) float32."""
+    x, y, z = (F32(v) for v in p)
+    x2y2 = F32(F32(x * x) + F32(y * y))
+    theta = F32(math.atan2(float(F32(np.sqrt(x2y2))), float(z)))          # atan2f
+    psi = F32(math.atan2(float(y), float(x)))
+    t2 = F32(theta * theta); t3 = F32(theta * t2); t5 = F32(t3 * t2); t7 = F32(t5 * t2); t9 = F32(t7 * t2)
+    r = F32(F32(F32(F32(theta + F32(cam[4] * t3)) + F32(cam[5] * t5)) + F32(cam[6] * t7)) + F32(cam[7] * t9))
+    u = F32(float(F32(cam[0] * r)) * math.cos(float(psi)) + float(cam[2]))     # cos(float) -> double arithmetic
+    v = F32(float(F32(cam[1] * r)) * math.sin(float(psi)) + float(cam[3]))
+    return u, v
+
+
+def kb8_unproject(cam, u, v):
+    """KannalaBrandt8.cpp:96-123, precision 1e-6."""
+    pwx = F32(F32(F32(u) - cam[2]) / cam[0]); pwy = F32(F32(F32(v) - cam[3]) / cam[1])
+    scale = F32(1)
+    theta_d = F32(np.sqrt(F32(F32(pwx * pwx) + F32(pwy * pwy))))
+    theta_d = min(max(F32(-math.pi / 2), theta_d), F32(math.pi / 2))
+    if theta_d > 1e-8:
+        theta = theta_d
+        for _ in range(10):
+            t2 = F32(theta * theta); t4 = F32(t2 * t2); t6 = F32(t4 * t2); t8 = F32(t4 * t4)
+            a, b, c, d = F32(cam[4] * t2), F32(cam[5] * t4), F32(cam[6] * t6), F32(cam[7] * t8)
+            num = F32(F32(theta * F32(F32(F32(F32(F32(1) + a) + b) + c) + d)) - theta_d)
+            den = F32(F32(F32(F32(F32(1) + F32(F32(3) * a)) + F32(F32(5) * b)) + F32(F32(7) * c)) + F32(F32(9) * d))
+            fix = F32(num / den)
+            theta = F32(theta - fix)
+            if abs(fix) < F32(1e-6):
+                break
+        scale = F32(F32(math.tan(float(theta))) / theta_d)
+    return np.array([F32(pwx * scale), F32(pwy * scale), F32(1)], F32)
+
+
+def kb8_triangulate_matches(cam1, cam2, pt1, pt2, R12, t12, sigma_level, unc):
+    """KannalaBrandt8::TriangulateMatches (KannalaBrandt8.cpp:338-407) with the real cv2.SVDecomp on the float32
+    4x4 system (Triangulate, :514-526).  Returns (z1 or -1, p3D, margin)."""
+    R12 = np.asarray(R12, F32).reshape(3, 3)
+    t12 = np.asarray(t12, F32).reshape(3, 1)
+    r1 = kb8_unproject(cam1, pt1[0], pt1[1]).reshape(3, 1)
+    r2 = kb8_unproject(cam2, pt2[0], pt2[1]).reshape(3, 1)
+    r21 = (R12 @ r2).astype(F32)
+    cosp = F32(float(r1.astype(np.float64).T @ r21.astype(np.float64)) / (cv2.norm(r1) * cv2.norm(r21)))
+    margin = abs(float(cosp) - 0.9998) / 2e-4      # relative to 1 - threshold: cosines cluster next to 1
+    if cosp > 0.9998:
+        return -1.0, None, margin
+    R21 = R12.T.copy()
+    t21 = (-(R21 @ t12)).astype(F32)
+    Tcw1 = np.hstack([np.eye(3, dtype=F32), np.zeros((3, 1), F32)])
+    Tcw2 = np.hstack([R21, t21]).astype(F32)
+    A = np.zeros((4, 4), F32)
+    A[0] = r1[0, 0] * Tcw1[2] - Tcw1[0]
+    A[1] = r1[1, 0] * Tcw1[2] - Tcw1[1]
+    A[2] = r2[0, 0] * Tcw2[2] - Tcw2[0]
+    A[3] = r2[1, 0] * Tcw2[2] - Tcw2[1]
+    w, u, vt = cv2.SVDecomp(A, flags=cv2.SVD_MODIFY_A | cv2.SVD_FULL_UV)
+    xh = vt[3].astype(F32)
+    x3D = (xh[:3] / xh[3]).astype(F32)
+    z1 = x3D[2]
+    if z1 <= 0:
+        return -1.0, None, margin
+    z2 = F32(float(R21[2].astype(np.float64) @ x3D.astype(np.float64)) + float(t21[2, 0]))
+    if z2 <= 0:
+        return -1.0, None, margin
+    u1, v1 = kb8_project(cam1, x3D)
+    e1 = F32(F32(F32(u1 - F32(pt1[0])) ** 2) + F32(F32(v1 - F32(pt1[1])) ** 2))
+    margin = min(margin, abs(float(e1) - 5.991 * float(sigma_level)) / (5.991 * float(sigma_level)))
+    if float(e1) > 5.991 * float(F32(sigma_level)):
+        return -1.0, None, margin
+    x3D2 = ((R21 @ x3D.reshape(3, 1)) + t21).astype(F32).reshape(3)
+    u2, v2 = kb8_project(cam2, x3D2)
+    e2 = F32(F32(F32(u2 - F32(pt2[0])) ** 2) + F32(F32(v2 - F32(pt2[1])) ** 2))
+    margin = min(margin, abs(float(e2) - 5.991 * float(unc)) / (5.991 * float(unc)))
+    if float(e2) > 5.991 * float(F32(unc)):
+        return -1.0, None, margin
+    return float(z1), x3D, margin
+
+
+def compute_stereo_fisheye_matches(cam1, cam2, kpL, descL, mono_left, kpR, descR, mono_right, R12, t12, sigma2):
+    """Frame.cc:1116-1156.  Returns (mvLeftToRightMatch, mvRightToLeftMatch, mvDepth, p3D (n, 3), margins, nMatches)."""
+    nL, nR = len(kpL), len(kpR)
+    l2r = np.full(nL, -1, np.int32)
+    r2l = np.full(nR, -1, np.int32)
+    depth = np.full(nL, -1.0, F32)
+    p3d = np.zeros((nL, 3), F32)
+    margins = np.full(nL, 1e30, F32)
+    match, _, _ = fisheye_lapping_match(descL[mono_left:], descR[mono_right:])
+    n = 0
+    for q, tr in enumerate(match):
+        if tr < 0:
+            continue
+        iL, iR = q + mono_left, int(tr) + mono_right
+        d, p, mg = kb8_triangulate_matches(cam1, cam2, (kpL["x"][iL], kpL["y"][iL]), (kpR["x"][iR], kpR["y"][iR]), R12, t12,
+                                           sigma2[kpL["octave"][iL]], sigma2[kpR["octave"][iR]])
+        margins[iL] = min(mg, abs(d - 1e-4) / 1e-4)
+        if d > 0.0001:
+            l2r[iL], r2l[iR], depth[iL], p3d[iL] = iR, iL, d, p
+            n += 1
+    return l2r, r2l, depth, p3d, margins, n

@@ -36,6 +36,16 @@ struct TriGeo {
     float sigma2B[ORBFE_MAX_LEVELS], scaleB[ORBFE_MAX_LEVELS];
 };
 
+// Kannala-Brandt stereo geometry (cameras 1 = left, 2 = right; x1 = R12 x2 + t12).
+struct Kb8Geo {
+    float cam1[8], cam2[8];     // fx, fy, cx, cy, k0..k3 (KannalaBrandt8::mvParameters)
+    float R12[9], t12[3];
+    float sigma2[ORBFE_MAX_LEVELS];
+};
+
+cudaError_t orbfe_launch_fisheye_triangulate(cudaStream_t st, const Kb8Geo& G, const orbfe_keypoint* kpL, const orbfe_keypoint* kpR,
+                                             int monoLeft, int monoRight, int nq, const int32_t* dMatch, int32_t* l2r, int32_t* r2l,
+                                             float* depth, float* p3d, int* count, long long* launches);
 void orbfe_knn2_plan(int nqMax, int ntMax, int batch, int smCount, int* nsplit, int* splitLen);
 cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStride, const int* dNq, int nqMax, const uint8_t* dt,
                               long long tStride, const int* dNt, int ntMax, int batch, int nsplit, int splitLen, uint2* dPartial,

@@ -425,3 +425,81 @@ extern "C" int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_bow_side
     if (A->n > 0) memcpy(matches12, m->hStage + oM, sizeof(int32_t) * A->n);
     return *reinterpret_cast<int*>(m->hStage + oCnt);
 }
+
+// ---- Kannala-Brandt fisheye stereo ----------------------------------------------------------------------
+extern "C" int orbfe_fisheye_stereo_match(orbfe_matcher* m, const orbfe_keypoint* kps_left, const uint8_t* desc_left, int n_left,
+                                          int mono_left, const orbfe_keypoint* kps_right, const uint8_t* desc_right, int n_right,
+                                          int mono_right, const float* cam1, const float* cam2, const float* R12, const float* t12,
+                                          const float* sigma2, int nlevels, int32_t* left_to_right, int32_t* right_to_left,
+                                          float* depth, float* p3d) {
+    if (!m || n_left < 0 || n_right < 0 || mono_left < 0 || mono_right < 0 || mono_left > n_left || mono_right > n_right)
+        return ORBFE_ERR_BAD_ARGUMENT;
+    if (!cam1 || !cam2 || !R12 || !t12 || !sigma2 || nlevels < 1 || nlevels > ORBFE_MAX_LEVELS) return ORBFE_ERR_BAD_ARGUMENT;
+    if ((n_left > 0 && (!kps_left || !desc_left || !left_to_right || !depth || !p3d)) || (n_right > 0 && (!kps_right || !desc_right || !right_to_left)))
+        return ORBFE_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < n_left; ++i)
+        if (kps_left[i].octave < 0 || kps_left[i].octave >= nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < n_right; ++i)
+        if (kps_right[i].octave < 0 || kps_right[i].octave >= nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    const int nq = n_left - mono_left, nt = n_right - mono_right;
+    for (int i = 0; i < n_left; ++i) { left_to_right[i] = -1; depth[i] = -1.f; p3d[3 * i] = p3d[3 * i + 1] = p3d[3 * i + 2] = 0.f; }
+    for (int i = 0; i < n_right; ++i) right_to_left[i] = -1;
+    if (nq <= 0) return 0;
+    CK(cudaSetDevice(m->device));
+    // inputs
+    size_t u = 0;
+    const size_t oKL = stage_take(u, sizeof(orbfe_keypoint) * n_left), oKR = stage_take(u, sizeof(orbfe_keypoint) * std::max(n_right, 1));
+    const size_t oQ = stage_take(u, (size_t)nq * 32), oT = stage_take(u, (size_t)std::max(nt, 1) * 32);
+    const size_t inBytes = u;
+    // device-only intermediates
+    const size_t oIdx = stage_take(u, sizeof(int32_t) * 2 * nq), oDist = stage_take(u, sizeof(int32_t) * 2 * nq);
+    const size_t oMatch = stage_take(u, sizeof(int32_t) * nq), oTmp = stage_take(u, 256);
+    // outputs (one D2H)
+    const size_t oOut = stage_take(u, 0);
+    const size_t oL2R = stage_take(u, sizeof(int32_t) * n_left), oR2L = stage_take(u, sizeof(int32_t) * std::max(n_right, 1));
+    const size_t oCnt = stage_take(u, 256);
+    const size_t oNeg = u;                                   // everything from oOut to here is initialised to -1 / 0xFF
+    const size_t oDepth = stage_take(u, sizeof(float) * n_left), oP3d = stage_take(u, sizeof(float) * 3 * n_left);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(m->hStage + oKL, kps_left, sizeof(orbfe_keypoint) * n_left);
+    if (n_right > 0) memcpy(m->hStage + oKR, kps_right, sizeof(orbfe_keypoint) * n_right);
+    memcpy(m->hStage + oQ, desc_left + (size_t)mono_left * 32, (size_t)nq * 32);
+    if (nt > 0) memcpy(m->hStage + oT, desc_right + (size_t)mono_right * 32, (size_t)nt * 32);
+    CK(cudaMemcpyAsync(m->dStage, m->hStage, inBytes, cudaMemcpyHostToDevice, m->stream));
+    int32_t* dIdx = reinterpret_cast<int32_t*>(m->dStage + oIdx);
+    int32_t* dDist = reinterpret_cast<int32_t*>(m->dStage + oDist);
+    st = orbfe_hamming_knn2_batch_device(m, m->dStage + oQ, 0, nullptr, nq, m->dStage + oT, 0, nullptr, nt, 1, dIdx, dDist);
+    if (st != ORBFE_OK) return st;
+    CK(cudaMemsetAsync(m->dStage + oTmp, 0, sizeof(int), m->stream));
+    CK(orbfe_launch_ratio_filter(m->stream, dIdx, dDist, nq, 0.7, reinterpret_cast<int32_t*>(m->dStage + oMatch),
+                                 reinterpret_cast<int*>(m->dStage + oTmp), &m->launches));
+    CK(cudaMemsetAsync(m->dStage + oOut, 0xFF, oNeg - oOut, m->stream));
+    CK(cudaMemsetAsync(m->dStage + oCnt, 0, sizeof(int), m->stream));
+    CK(cudaMemsetAsync(m->dStage + oDepth, 0, u - oDepth, m->stream));
+    Kb8Geo G;
+    memset(&G, 0, sizeof(G));
+    memcpy(G.cam1, cam1, sizeof(G.cam1));
+    memcpy(G.cam2, cam2, sizeof(G.cam2));
+    memcpy(G.R12, R12, sizeof(G.R12));
+    memcpy(G.t12, t12, sizeof(G.t12));
+    for (int l = 0; l < nlevels; ++l) G.sigma2[l] = sigma2[l];
+    CK(orbfe_launch_fisheye_triangulate(m->stream, G, reinterpret_cast<const orbfe_keypoint*>(m->dStage + oKL),
+                                        reinterpret_cast<const orbfe_keypoint*>(m->dStage + oKR), mono_left, mono_right, nq,
+                                        reinterpret_cast<const int32_t*>(m->dStage + oMatch), reinterpret_cast<int32_t*>(m->dStage + oL2R),
+                                        reinterpret_cast<int32_t*>(m->dStage + oR2L), reinterpret_cast<float*>(m->dStage + oDepth),
+                                        reinterpret_cast<float*>(m->dStage + oP3d), reinterpret_cast<int*>(m->dStage + oCnt),
+                                        &m->launches));
+    CK(cudaMemcpyAsync(m->hStage + oOut, m->dStage + oOut, u - oOut, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    const int32_t* hl = reinterpret_cast<const int32_t*>(m->hStage + oL2R);
+    const float* hd = reinterpret_cast<const float*>(m->hStage + oDepth);
+    const float* hp = reinterpret_cast<const float*>(m->hStage + oP3d);
+    for (int i = 0; i < n_left; ++i) {
+        left_to_right[i] = hl[i];
+        if (hl[i] >= 0) { depth[i] = hd[i]; p3d[3 * i] = hp[3 * i]; p3d[3 * i + 1] = hp[3 * i + 1]; p3d[3 * i + 2] = hp[3 * i + 2]; }
+    }
+    if (n_right > 0) memcpy(right_to_left, m->hStage + oR2L, sizeof(int32_t) * n_right);
+    return *reinterpret_cast<int*>(m->hStage + oCnt);
+}

@@ -28,6 +28,7 @@ PROTO = {
     "orbfe_hamming_knn2": (_I, [_P, _P, _I, _P, _I, _P, _P]),
     "orbfe_hamming_knn2_batch_device": (_I, [_P, _P, _PD, _P, _I, _P, _PD, _P, _I, _I, _P, _P]),
     "orbfe_match_lapping": (_I, [_P, _P, _I, _P, _I, C.c_double, _P]),
+    "orbfe_fisheye_stereo_match": (_I, [_P, _P, _P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _P, _P, _I, _P, _P, _P, _P]),
     "orbfe_stereo_match": (_I, [_P, _P, _I, _P, _I, _F, _F, _P, _P, _I]),
     "orbfe_stereo_match_batch_device": (_I, [_P, _P, _I, _F, _F, _P, _P]),
     "orbfe_search_bow": (_I, [_P, _I, C.POINTER(BowSide), C.POINTER(BowSide), _I, _I, _I, C.POINTER(_P), C.POINTER(_P), _P]),

@@ -149,6 +149,25 @@ class ORBmatcher:
             raise OrbfeError(n, "orbfe_match_lapping")
         return match, n
 
+    def ComputeStereoFishEyeMatches(self, kps_left, desc_left, mono_left, kps_right, desc_right, mono_right, cam1, cam2, R12,
+                                    t12, sigma2):
+        """Frame::ComputeStereoFishEyeMatches (Frame.cc:1116-1156).  Returns (mvLeftToRightMatch,
+        mvRightToLeftMatch, mvDepth, mvStereo3Dpoints (n, 3), nMatches)."""
+        kL, kR = np.ascontiguousarray(kps_left, KEYPOINT_DTYPE), np.ascontiguousarray(kps_right, KEYPOINT_DTYPE)
+        dL = np.ascontiguousarray(desc_left, np.uint8).reshape(-1, 32)
+        dR = np.ascontiguousarray(desc_right, np.uint8).reshape(-1, 32)
+        f = lambda a, n: np.ascontiguousarray(a, np.float32).reshape(n)
+        cam1, cam2, R12, t12 = f(cam1, 8), f(cam2, 8), f(R12, 9), f(t12, 3)
+        sigma2 = np.ascontiguousarray(sigma2, np.float32)
+        l2r, r2l = np.full(max(len(kL), 1), -1, np.int32), np.full(max(len(kR), 1), -1, np.int32)
+        depth, p3d = np.full(max(len(kL), 1), -1, np.float32), np.zeros((max(len(kL), 1), 3), np.float32)
+        n = self._lib.orbfe_fisheye_stereo_match(self._m, _p(kL), _p(dL), len(kL), int(mono_left), _p(kR), _p(dR), len(kR),
+                                                 int(mono_right), _p(cam1), _p(cam2), _p(R12), _p(t12), _p(sigma2), len(sigma2),
+                                                 _p(l2r), _p(r2l), _p(depth), _p(p3d))
+        if n < 0:
+            raise OrbfeError(n, "orbfe_fisheye_stereo_match")
+        return l2r[:len(kL)], r2l[:len(kR)], depth[:len(kL)], p3d[:len(kL)], n
+
     # ---- Frame::ComputeStereoMatches (Frame.cc:794-964)
     def stereo_match(self, left, right, bf, b, frame_l=0, frame_r=0):
         """left / right: ORBextractor objects whose last extraction holds the two views (the same object

@@ -103,3 +103,62 @@ def knn_inputs(seed=5, nq=700, nt=3000):
     q[1] = t[2999]
     t[1500:1510] = q[5]          # ten-way tie at distance 0
     return q, t
+
+
+# TUM-VI 512 calibration (Examples/Stereo/TUM_512.yaml:9-46): KB8 intrinsics of both cameras and Tlr
+KB8_LEFT = np.array([190.97847715128717, 190.9733070521226, 254.93170605935475, 256.8974428996504, 0.0034823894022493434,
+                     0.0007150348452162257, -0.0020532361418706202, 0.00020293673591811182], np.float32)
+KB8_RIGHT = np.array([190.44236969414825, 190.4344384721956, 252.59949716835982, 254.91723064636983, 0.0034003170790442797,
+                      0.001766278153469831, -0.00266312569781606, 0.0003299517423931039], np.float32)
+TLR = np.array([[0.999999445773493, 0.000791687752817, 0.000694034010224, 0.101063427414194],
+                [-0.000823363992158, 0.998899461915674, 0.046895490788700, 0.001946204678584],
+                [-0.000656143613644, -0.046896036240590, 0.998899560146304, 0.001015350132563]], np.float32)
+
+FISHEYE_CASES = {"fisheye_tumvi": (2100, 900), "fisheye_tumvi_b": (2101, 1500)}   # name: (seed, stereo points)
+
+
+def _kb8_project64(cam, P):
+    cam = cam.astype(np.float64)
+    th = np.arctan2(np.hypot(P[:, 0], P[:, 1]), P[:, 2])
+    psi = np.arctan2(P[:, 1], P[:, 0])
+    r = th + cam[4] * th ** 3 + cam[5] * th ** 5 + cam[6] * th ** 7 + cam[7] * th ** 9
+    return np.stack([cam[0] * r * np.cos(psi) + cam[2], cam[1] * r * np.sin(psi) + cam[3]], axis=1)
+
+
+def fisheye_inputs(name):
+    """Synthetic fisheye stereo frame: 3-D points seen by both KB8 cameras (pixel noise, a few gross outliers,
+    depths from 0.4 m to 12 m so that the parallax test fires), descriptors of the right view = left +
+    bit flips, plus unmatched mono features in front of both lists.  Coordinates are snapped to 1/16 px
+    so the float32 inputs are identical on every machine."""
+    seed, n = FISHEYE_CASES[name]
+    rng = np.random.default_rng(seed)
+    nlev = 8
+    P1 = np.stack([rng.uniform(-2.5, 2.5, n), rng.uniform(-1.8, 1.8, n), rng.uniform(0.4, 12.0, n)], axis=1)
+    R12, t12 = TLR[:, :3].astype(np.float64), TLR[:, 3].astype(np.float64)
+    P2 = (P1 - t12) @ R12            # R12^T (P1 - t12)
+    uvL = _kb8_project64(KB8_LEFT, P1) + rng.normal(0, 0.4, (n, 2))
+    uvR = _kb8_project64(KB8_RIGHT, P2) + rng.normal(0, 0.4, (n, 2))
+    bad = rng.random(n) < 0.08
+    uvR[bad] += rng.uniform(-12, 12, (int(bad.sum()), 2))
+    mono_l, mono_r = 150, 210
+    nL, nR = n + mono_l, n + mono_r
+    kL, kR = np.zeros(nL, orbfe.KEYPOINT_DTYPE), np.zeros(nR, orbfe.KEYPOINT_DTYPE)
+    perm = rng.permutation(n)        # right list order differs from the left one
+    snap = lambda a: (np.round(a * 16) / 16).astype(np.float32)
+    kL["x"][mono_l:], kL["y"][mono_l:] = snap(uvL[:, 0]), snap(uvL[:, 1])
+    kR["x"][mono_r:][perm], kR["y"][mono_r:][perm] = snap(uvR[:, 0]), snap(uvR[:, 1])
+    kL["x"][:mono_l], kL["y"][:mono_l] = snap(rng.uniform(20, 120, mono_l)), snap(rng.uniform(20, 490, mono_l))
+    kR["x"][:mono_r], kR["y"][:mono_r] = snap(rng.uniform(390, 490, mono_r)), snap(rng.uniform(20, 490, mono_r))
+    kL["octave"], kR["octave"] = rng.integers(0, nlev, nL), rng.integers(0, nlev, nR)
+    kL["class_id"] = kR["class_id"] = -1
+    dL = rng.integers(0, 256, (nL, 32), dtype=np.uint8)
+    dR = rng.integers(0, 256, (nR, 32), dtype=np.uint8)
+    flips = rng.integers(0, 60, n)
+    src = dL[mono_l:].copy()
+    for i in range(n):
+        bits = rng.choice(256, int(flips[i]), replace=False)
+        for b in bits:
+            src[i, b >> 3] ^= 1 << (b & 7)
+    dR[mono_r:][perm] = src
+    return dict(cam1=KB8_LEFT, cam2=KB8_RIGHT, R12=TLR[:, :3].copy(), t12=TLR[:, 3].copy(), kL=kL, dL=dL, kR=kR, dR=dR,
+                mono_l=mono_l, mono_r=mono_r, nlevels=nlev)

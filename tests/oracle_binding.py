@@ -43,6 +43,9 @@ def lib():
                                                  _P, _P, _F, _F, _I, _I, _I, _P]),
             "orbref_knn2_ratio": (None, [_P, _I, _P, _I, C.c_double, _P]),
             "orbref_knn2_many": (_L, [_P, _I, _P, _I, _I, _L, _L, _I]),
+            "orbref_kb8_project": (None, [_P, _P, _P]),
+            "orbref_kb8_unproject": (None, [_P, _F, _F, _P]),
+            "orbref_fisheye_stereo": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)
@@ -190,3 +193,18 @@ def knn2_ratio(q, t, ratio=0.7):
 def knn2_many(q, t, npairs, qstride, tstride, nthreads):
     """q, t: arrays holding `npairs` problems (nq x 32, nt x 32 each) at the given byte strides."""
     return lib().orbref_knn2_many(_p(q), q.shape[-2], _p(t), t.shape[-2], npairs, qstride, tstride, nthreads)
+
+
+def fisheye_stereo(cam1, cam2, kpL, descL, mono_left, kpR, descR, mono_right, R12, t12, sigma2):
+    """Frame::ComputeStereoFishEyeMatches (oracle/cpu_ref/kb8_ref.cc).  Returns (l2r, r2l, depth, p3d, margins, n)."""
+    cam1, cam2 = np.ascontiguousarray(cam1, np.float32), np.ascontiguousarray(cam2, np.float32)
+    kpL, kpR = np.ascontiguousarray(kpL), np.ascontiguousarray(kpR)
+    descL, descR = np.ascontiguousarray(descL, np.uint8), np.ascontiguousarray(descR, np.uint8)
+    R12, t12 = np.ascontiguousarray(R12, np.float32).reshape(9), np.ascontiguousarray(t12, np.float32).reshape(3)
+    sigma2 = np.ascontiguousarray(sigma2, np.float32)
+    nL, nR = len(kpL), len(kpR)
+    l2r, r2l = np.zeros(max(nL, 1), np.int32), np.zeros(max(nR, 1), np.int32)
+    depth, p3d, mg = np.zeros(max(nL, 1), np.float32), np.zeros((max(nL, 1), 3), np.float32), np.zeros(max(nL, 1), np.float32)
+    n = lib().orbref_fisheye_stereo(_p(cam1), _p(cam2), _p(kpL), _p(descL), nL, mono_left, _p(kpR), _p(descR), nR, mono_right,
+                                    _p(R12), _p(t12), _p(sigma2), _p(l2r), _p(r2l), _p(depth), _p(p3d), _p(mg))
+    return l2r[:nL], r2l[:nR], depth[:nL], p3d[:nL], mg[:nL], n

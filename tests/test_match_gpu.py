@@ -226,3 +226,54 @@ def test_empty_and_disjoint_feature_vectors():
     a2b, n = m.SearchByBoW_KF_KF(d1, fv1, np.zeros(50, np.uint8), k1, d2, fv1.__class__.from_node_of_feature(np.full(60, 3)),
                                  np.ones(60, np.uint8), k2)             # shared node, but no MapPoints in KF1
     assert n == 0 and (a2b == -1).all()
+
+
+@pytest.mark.parametrize("name", list(mc.FISHEYE_CASES))
+def test_fisheye_stereo(name):
+    """Frame::ComputeStereoFishEyeMatches on the GPU vs the oracle and the golden: the 2-NN / ratio stage is
+    bit-exact (same candidate set: margins < 1e29 at the same rows); the KB8 triangulation ends in a 4x4 SVD,
+    so accept/reject is compared where neither side is within 1e-3 (relative) of a threshold and depths /
+    points to rtol 2e-3."""
+    c = mc.fisheye_inputs(name)
+    g = gold(name)
+    s2 = OrbRef(1000, *mc.ORB).tables()[2]
+    m = orbfe.ORBmatcher(0.7, True)
+    l2r, r2l, depth, p3d, n = m.ComputeStereoFishEyeMatches(c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], c["mono_r"], c["cam1"],
+                                                            c["cam2"], c["R12"], c["t12"], s2)
+    rl2r, rr2l, rdepth, rp3d, mg, rn = ob.fisheye_stereo(c["cam1"], c["cam2"], c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"],
+                                                         c["mono_r"], c["R12"], c["t12"], s2)
+    tried = mg < 1e29
+    assert (l2r[~tried] == -1).all() and (l2r[:c["mono_l"]] == -1).all()
+    for ref_l2r, ref_depth, ref_p3d, margins in ((rl2r, rdepth, rp3d, mg), (g["l2r"], g["depth"], g["p3d"], np.minimum(mg, g["margins"]))):
+        safe = margins > 1e-3
+        assert np.array_equal(l2r[safe], ref_l2r[safe])
+        ok = safe & (ref_l2r >= 0)
+        assert ok.sum() > 200
+        assert np.allclose(depth[ok], ref_depth[ok], rtol=2e-3, atol=1e-5)
+        assert np.allclose(p3d[ok], ref_p3d[ok], rtol=2e-3, atol=2e-4)
+    assert abs(n - rn) <= (tried & (mg <= 1e-3)).sum()
+    assert n == (l2r >= 0).sum()
+    assert (depth[l2r < 0] == -1).all()
+    # r2l: a right feature claimed by several left ones keeps one of them (the reference keeps the last in
+    # query order: Frame.cc:1148 overwrites), and it points back
+    want = np.full(len(c["kR"]), -1, np.int32)
+    for i in np.nonzero(l2r >= 0)[0]:
+        want[l2r[i]] = i
+    assert np.array_equal(r2l, want)
+
+
+def test_fisheye_stereo_empty_sides():
+    c = mc.fisheye_inputs("fisheye_tumvi")
+    s2 = OrbRef(1000, *mc.ORB).tables()[2]
+    m = orbfe.ORBmatcher(0.7, True)
+    nL = len(c["kL"])
+    # no lapping features on the left / on the right
+    out = m.ComputeStereoFishEyeMatches(c["kL"], c["dL"], nL, c["kR"], c["dR"], c["mono_r"], c["cam1"], c["cam2"], c["R12"], c["t12"], s2)
+    assert out[4] == 0 and (out[0] == -1).all() and (out[2] == -1).all()
+    out = m.ComputeStereoFishEyeMatches(c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], len(c["kR"]), c["cam1"], c["cam2"], c["R12"],
+                                        c["t12"], s2)
+    assert out[4] == 0 and (out[0] == -1).all() and (out[1] == -1).all()
+    # a single right lapping feature: knn has < 2 neighbours, nothing passes (Frame.cc:1141)
+    out = m.ComputeStereoFishEyeMatches(c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], len(c["kR"]) - 1, c["cam1"], c["cam2"],
+                                        c["R12"], c["t12"], s2)
+    assert out[4] == 0

@@ -122,3 +122,39 @@ def test_knn2_tie_rule_golden():
     idx, dist = ob.knn2(q[:3], t[:1])
     assert idx[:, 1].tolist() == [-1, -1, -1] and (idx[:, 0] == 0).all()
     assert (ob.knn2_ratio(q[:3], t[:1]) == -1).all()
+
+
+@pytest.mark.parametrize("name", list(mc.FISHEYE_CASES))
+def test_fisheye_stereo_matches_golden(name):
+    """KB8 triangulation ends in a 4x4 SVD (cv::SVD in the reference, cv2.SVDecomp in the golden generator, a
+    double-precision Jacobi solve here): float tolerance, decisions compared away from the thresholds."""
+    c = mc.fisheye_inputs(name)
+    g = gold(name)
+    assert crc(c["kL"], c["dL"], c["kR"], c["dR"]) == int(g["in_crc"])
+    s2 = tables()[2]
+    l2r, r2l, depth, p3d, mg, n = ob.fisheye_stereo(c["cam1"], c["cam2"], c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"],
+                                                    c["mono_r"], c["R12"], c["t12"], s2)
+    safe = np.minimum(mg, g["margins"]) > 1e-3          # both sides agree the decision is not knife-edge
+    assert safe.sum() > 0.95 * (g["margins"] < 1e29).sum()
+    assert np.array_equal(l2r[safe], g["l2r"][safe])
+    ok = safe & (g["l2r"] >= 0)
+    assert ok.sum() > 200
+    assert np.allclose(depth[ok], g["depth"][ok], rtol=2e-3, atol=1e-5)
+    assert np.allclose(p3d[ok], g["p3d"][ok], rtol=2e-3, atol=2e-4)
+    assert abs(n - int(g["n"])) <= (~safe & (g["margins"] < 1e29)).sum()
+    # every right index claimed at most once per surviving left match
+    m = l2r[l2r >= 0]
+    assert np.array_equal(r2l[m] >= 0, np.ones(len(m), bool))
+
+
+def test_kb8_project_unproject_roundtrip():
+    cam = mc.KB8_LEFT
+    L = ob.lib()
+    rng = np.random.default_rng(1)
+    for _ in range(200):
+        u, v = rng.uniform(80, 430, 2)      # inside the 90-degree cone (unproject clamps theta_d at pi/2)
+        ray = np.zeros(3, np.float32)
+        L.orbref_kb8_unproject(ob._p(cam), float(u), float(v), ob._p(ray))
+        uv = np.zeros(2, np.float32)
+        L.orbref_kb8_project(ob._p(cam), ob._p(ray), ob._p(uv))
+        assert abs(uv[0] - u) < 2e-3 and abs(uv[1] - v) < 2e-3
