@@ -261,6 +261,34 @@ int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_bow_side* A, const 
                                const float* u_right_b, const orbfe_epipolar* geo, int only_stereo, int coarse,
                                int32_t* matches12);
 
+/* Two-view geometry of SearchForTriangulation for Kannala-Brandt (fisheye) keyframes. */
+typedef struct orbfe_kb8_epipolar {
+    float cam_a[2][8];  /* pKF1: [0] = mpCamera, [1] = mpCamera2 (ignored when nleft_a < 0); fx, fy, cx, cy, k1..k4 */
+    float cam_b[2][8];  /* pKF2 likewise */
+    int nleft_a;        /* pKF1->NLeft: features [0, nleft) belong to mpCamera, the rest to mpCamera2; -1 = one camera */
+    int nleft_b;
+    float R12[4][9];    /* x1 = R12 x2 + t12 for the pairings ll, lr, rl, rr (ORBmatcher.cc:1248-1262), row-major; */
+    float t12[4][3];    /* entry 0 alone is used unless both keyframes have two cameras (:1332) */
+    float ex, ey;       /* epipole in image 2; tested (:1321-1327) only when pKF1 has one camera */
+    const float* sigma2_a;  /* pKF1->mvLevelSigma2 [nlevels] */
+    const float* sigma2_b;  /* pKF2->mvLevelSigma2 [nlevels] */
+    const float* scale_b;   /* pKF2->mvScaleFactors [nlevels] */
+    int nlevels;
+} orbfe_kb8_epipolar;
+
+/* ORBmatcher::SearchForTriangulation / SearchForTriangulation_ (ORBmatcher.cc:965-1432) for keyframes with
+ * KannalaBrandt8 cameras: the geometric test is KannalaBrandt8::epipolarConstrain_ (KannalaBrandt8.cpp:239-242,
+ * i.e. TriangulateMatches_ (:409-480) returns a depth > 1e-4) with the cameras and relative pose of the
+ * pairing (left/right camera of each keyframe) the two features belong to.  A.kps / B.kps: mvKeys followed
+ * by mvKeysRight.  Fisheye keyframes carry no mvuRight, hence only_stereo != 0 matches nothing (:1280-1283).
+ * matches12[A.n] as orbfe_search_triangulation.  points12 (nullable, A.n x 3 floats): the triangulated point
+ * in camera-1 coordinates of every row with matches12 >= 0 (what the matchAndtriangulate overload,
+ * :1435-1624, hands back, there in world coordinates); zero with coarse != 0.  The triangulation ends in a
+ * 4x4 SVD: decisions agree with the reference except within float rounding of a threshold. */
+int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_side* A, const orbfe_bow_side* B,
+                                   const orbfe_kb8_epipolar* geo, int only_stereo, int coarse, int32_t* matches12,
+                                   float* points12);
+
 /* Measured integer-pipe ceiling of the Hamming matchers: sustained 32-bit POPC instructions per
  * second of device `device` (register-only micro-benchmark, ~10 ms).  One 256-bit descriptor pair
  * costs 8 POPC, so popc_per_s / 8 is the roofline of the matching kernels in pairs/s. */

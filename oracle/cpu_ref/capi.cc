@@ -177,4 +177,23 @@ int orbref_fisheye_stereo(const float* cam1, const float* cam2, const KeyPoint* 
     return computeStereoFishEyeMatches(*(const Kb8*)cam1, *(const Kb8*)cam2, kpL, descL, nL, monoLeft, kpR, descR, nR, monoRight, R12,
                                        t12, sigma2, l2r, r2l, depth, p3d, margins);
 }
+// camA / camB: 2 x 8 floats (mpCamera, mpCamera2); R12: 4 x 9, t12: 4 x 3 in the order ll, lr, rl, rr.
+int orbref_search_triangulation_kb8(const KeyPoint* kpA, const uint8_t* descA, int nA, int nnA, const uint32_t* nodeA,
+                                    const int32_t* offA, const int32_t* idxA, const uint8_t* mpA, const float* sigma2A,
+                                    const KeyPoint* kpB, const uint8_t* descB, int nB, int nnB, const uint32_t* nodeB,
+                                    const int32_t* offB, const int32_t* idxB, const uint8_t* mpB, const float* sigma2B,
+                                    const float* scaleB, const float* camA, const float* camB, int nleftA, int nleftB,
+                                    const float* R12, const float* t12, float ex, float ey, int checkOri, int onlyStereo,
+                                    int coarse, int32_t* m12, float* points12, float* margins) {
+    FeatureVectorCsr fa{nnA, nodeA, offA, idxA}, fb{nnB, nodeB, offB, idxB};
+    TriKb8Params p;
+    p.checkOri = checkOri; p.onlyStereo = onlyStereo; p.coarse = coarse; p.ex = ex; p.ey = ey;
+    p.nleftA = nleftA; p.nleftB = nleftB;
+    std::memcpy(p.camA, camA, sizeof(p.camA));
+    std::memcpy(p.camB, camB, sizeof(p.camB));
+    std::memcpy(p.R12, R12, sizeof(p.R12));
+    std::memcpy(p.t12, t12, sizeof(p.t12));
+    return searchForTriangulationKb8(kpA, descA, nA, fa, mpA, sigma2A, kpB, descB, nB, fb, mpB, sigma2B, scaleB, p, m12, points12,
+                                     margins);
+}
 }

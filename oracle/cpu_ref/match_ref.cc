@@ -283,6 +283,73 @@ int searchForTriangulation(const KeyPoint* kpA, const uint8_t* descA, int nA, co
     return nmatches;
 }
 
+// ORBmatcher.cc:1208-1432 with KannalaBrandt8::epipolarConstrain_ as the geometric test.
+int searchForTriangulationKb8(const KeyPoint* kpA, const uint8_t* descA, int nA, const FeatureVectorCsr& fvA,
+                              const uint8_t* hasMpA, const float* sigma2A, const KeyPoint* kpB, const uint8_t* descB, int nB,
+                              const FeatureVectorCsr& fvB, const uint8_t* hasMpB, const float* sigma2B, const float* scaleB,
+                              const TriKb8Params& p, int32_t* vMatches12, float* points12, float* margins) {
+    (void)nB;
+    for (int i = 0; i < nA; ++i) {
+        vMatches12[i] = -1;
+        if (margins) margins[i] = 1e30f;
+        if (points12) points12[3 * i] = points12[3 * i + 1] = points12[3 * i + 2] = 0.f;
+    }
+    int nmatches = 0;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    const bool dual = p.nleftA >= 0 && p.nleftB >= 0;          // pKF1->mpCamera2 && pKF2->mpCamera2 (:1332)
+    forSharedNodes(fvA, fvB, [&](int kA, int kB) {
+        for (int ia = fvA.offsets[kA]; ia < fvA.offsets[kA + 1]; ++ia) {
+            const int idx1 = fvA.indices[ia];
+            if (hasMpA[idx1]) continue;
+            if (p.onlyStereo) continue;                            // bStereo1 is false for every fisheye feature
+            const KeyPoint& kp1 = kpA[idx1];
+            const bool bRight1 = !(p.nleftA == -1 || idx1 < p.nleftA);
+            const uint8_t* d1 = descA + 32 * (size_t)idx1;
+            int bestDist = TH_LOW, bestIdx2 = -1;
+            float bestP[3] = {0, 0, 0};
+            for (int ib = fvB.offsets[kB]; ib < fvB.offsets[kB + 1]; ++ib) {
+                const int idx2 = fvB.indices[ib];
+                if (hasMpB[idx2]) continue;
+                const int dist = descriptorDistanceSwar(d1, descB + 32 * (size_t)idx2);
+                if (dist > TH_LOW) continue;
+                const KeyPoint& kp2 = kpB[idx2];
+                const bool bRight2 = !(p.nleftB == -1 || idx2 < p.nleftB);
+                if (p.nleftA < 0) {                                // !pKF1->mpCamera2
+                    const float distex = p.ex - kp2.x, distey = p.ey - kp2.y;
+                    if (distex * distex + distey * distey < 100 * scaleB[kp2.octave]) continue;
+                }
+                const int c = dual ? 2 * (int)bRight1 + (int)bRight2 : 0;
+                const Kb8& cam1 = dual && bRight1 ? p.camA[1] : p.camA[0];
+                const Kb8& cam2 = dual && bRight2 ? p.camB[1] : p.camB[0];
+                float P[3] = {0, 0, 0}, mg = 1e30f;
+                // evaluated for every candidate (the reference skips it when dist > bestDist; the test is pure,
+                // so the outcome is the same) to report the margin of everything a parallel search evaluates
+                const bool ok = kb8TriangulateMatches(cam1, cam2, kp1, kp2, p.R12[c], p.t12[c], sigma2A[kp1.octave],
+                                                      sigma2B[kp2.octave], P, &mg) > 0.0001f;
+                if (margins && !p.coarse && mg < margins[idx1]) margins[idx1] = mg;
+                if (dist > bestDist) continue;
+                if (ok || p.coarse) { bestIdx2 = idx2; bestDist = dist; bestP[0] = P[0]; bestP[1] = P[1]; bestP[2] = P[2]; }
+            }
+            if (bestIdx2 >= 0) {
+                vMatches12[idx1] = bestIdx2;
+                if (points12) { points12[3 * idx1] = bestP[0]; points12[3 * idx1 + 1] = bestP[1]; points12[3 * idx1 + 2] = bestP[2]; }
+                nmatches++;
+                if (p.checkOri) rotHist[rotBin(kp1.angle, kpB[bestIdx2].angle)].push_back(idx1);
+            }
+        }
+    });
+    if (p.checkOri) {
+        int counts[HISTO_LENGTH], ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; ++i) counts[i] = (int)rotHist[i].size();
+        computeThreeMaxima(counts, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx : rotHist[i]) { vMatches12[idx] = -1; nmatches--; }
+        }
+    }
+    return nmatches;
+}
+
 // Frame.cc:1134-1141
 void knn2RatioMatch(const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match) {
     std::vector<int32_t> idx(2 * (size_t)nq), dist(2 * (size_t)nq);

@@ -101,4 +101,25 @@ int computeStereoFishEyeMatches(const Kb8& c1, const Kb8& c2, const KeyPoint* kp
                                 const float t12[3], const float* sigma2, int32_t* leftToRight, int32_t* rightToLeft,
                                 float* depth, float* p3d, float* margins);
 
+// SearchForTriangulation / SearchForTriangulation_ with Kannala-Brandt cameras (ORBmatcher.cc:965-1432 with
+// KannalaBrandt8::epipolarConstrain_, KannalaBrandt8.cpp:239-242: a pair passes iff TriangulateMatches_ > 1e-4).
+// nleft* = KeyFrame::NLeft (-1: single camera; else features [0,nleft) come from mpCamera, the rest from
+// mpCamera2).  cam*[0] = mpCamera, cam*[1] = mpCamera2.  R12 / t12 [4] = {ll, lr, rl, rr} (:1248-1262),
+// indexed 2*bRight1 + bRight2; entry 0 alone is used unless both keyframes have a second camera (:1332).
+// mvuRight is never set with a fisheye camera, so bStereo1/2 are false: onlyStereo yields no matches, the
+// epipole test (:1321-1327) applies iff pKF1 has no second camera.  points12 (nullable, nA*3): the
+// triangulated point (camera-1 frame) of each accepted match; margins (nullable, nA): smallest threshold
+// margin over every candidate pair of feature i that reached the geometric test.
+struct TriKb8Params {
+    int checkOri, onlyStereo, coarse;
+    Kb8 camA[2], camB[2];
+    int nleftA, nleftB;
+    float R12[4][9], t12[4][3];
+    float ex, ey;
+};
+int searchForTriangulationKb8(const KeyPoint* kpA, const uint8_t* descA, int nA, const FeatureVectorCsr& fvA,
+                              const uint8_t* hasMpA, const float* sigma2A, const KeyPoint* kpB, const uint8_t* descB, int nB,
+                              const FeatureVectorCsr& fvB, const uint8_t* hasMpB, const float* sigma2B, const float* scaleB,
+                              const TriKb8Params& p, int32_t* matches12, float* points12, float* margins);
+
 }  // namespace orbref

@@ -93,6 +93,16 @@ def main():
         tried = int((margins < 1e29).sum())
         print(name, tried, "descriptor matches ->", n, "triangulated; knife-edge (margin < 1e-3):", int((margins < 1e-3).sum()))
 
+    for name in mc.TRI_KB8_CASES:
+        c = mc.tri_kb8_inputs(name)
+        m12, n, pts, margins = mp.search_for_triangulation_kb8(c["k1"], c["d1"], c["fv1"].to_dict(), c["mp1"], sigma2, c["k2"],
+                                                               c["d2"], c["fv2"].to_dict(), c["mp2"], sigma2, scale, c["cam_a"],
+                                                               c["cam_b"], c["nleft_a"], c["nleft_b"], c["R12"], c["t12"], c["ep"],
+                                                               c["check_ori"], c["only_stereo"], c["coarse"])
+        np.savez_compressed(os.path.join(out, f"match_{name}.npz"), in_crc=crc(c["k1"], c["d1"], c["k2"], c["d2"], c["R12"]),
+                            m12=m12, n=n, points=pts, margins=margins)
+        print(name, n, "pairs; knife-edge rows:", int((margins < 1e-3).sum()))
+
     q, t = mc.knn_inputs()
     match, idx, dist = mp.fisheye_lapping_match(q, t)
     np.savez_compressed(os.path.join(out, "match_knn_ties.npz"), in_crc=crc(q, t), match=match, idx=idx, dist=dist)

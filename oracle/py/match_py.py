@@ -331,6 +331,65 @@ def search_for_triangulation(kp1, desc1, fv1, mp1, ur1, kp2, desc2, fv2, mp2, ur
     return np.array(m12, np.int32), nmatches
 
 
+def search_for_triangulation_kb8(kp1, desc1, fv1, mp1, sigma2_1, kp2, desc2, fv2, mp2, sigma2_2, scale2, cam_a, cam_b, nleft_a,
+                                 nleft_b, R12, t12, ep, check_ori, only_stereo, coarse):
+    """ORBmatcher.cc:1208-1432 with Kannala-Brandt cameras: the geometric test is
+    KannalaBrandt8::epipolarConstrain_ (KannalaBrandt8.cpp:239-242) = TriangulateMatches_ > 1e-4, the
+    (R12, t12, cameras) are picked per pair from {ll, lr, rl, rr} when both keyframes have two cameras
+    (:1332-1366).  mvuRight stays -1 with fisheye cameras, so bStereo1 = bStereo2 = false.
+    Returns (vMatches12, n, point per match (n1, 3), margin per kp1)."""
+    n1 = len(desc1)
+    m12 = [-1] * n1
+    pts = np.zeros((n1, 3), F32)
+    margins = np.full(n1, 1e30, F32)
+    nmatches = 0
+    rotHist = [[] for _ in range(HISTO_LENGTH)]
+    dual = nleft_a >= 0 and nleft_b >= 0
+    for ids1, ids2 in shared_nodes(fv1, fv2):
+        for idx1 in ids1:
+            if mp1[idx1] or only_stereo:
+                continue
+            right1 = not (nleft_a == -1 or idx1 < nleft_a)
+            bestDist, bestIdx2, bestP = TH_LOW, -1, None
+            for idx2 in ids2:
+                if mp2[idx2]:
+                    continue
+                dist = descriptor_distance(desc1[idx1], desc2[idx2])
+                if dist > TH_LOW or dist > bestDist:
+                    continue
+                right2 = not (nleft_b == -1 or idx2 < nleft_b)
+                if nleft_a < 0:
+                    dx = F32(F32(ep[0]) - F32(kp2["x"][idx2]))
+                    dy = F32(F32(ep[1]) - F32(kp2["y"][idx2]))
+                    if F32(F32(dx * dx) + F32(dy * dy)) < F32(F32(100) * scale2[kp2["octave"][idx2]]):
+                        continue
+                c = 2 * int(right1) + int(right2) if dual else 0
+                c1 = cam_a[1] if dual and right1 else cam_a[0]
+                c2 = cam_b[1] if dual and right2 else cam_b[0]
+                d, p, mg = kb8_triangulate_matches(c1, c2, (kp1["x"][idx1], kp1["y"][idx1]), (kp2["x"][idx2], kp2["y"][idx2]),
+                                                   R12[c], t12[c], sigma2_1[kp1["octave"][idx1]], sigma2_2[kp2["octave"][idx2]])
+                if not coarse:
+                    margins[idx1] = min(margins[idx1], mg)
+                if coarse or d > 0.0001:
+                    bestIdx2, bestDist, bestP = idx2, dist, p
+            if bestIdx2 >= 0:
+                m12[idx1] = bestIdx2
+                if bestP is not None:
+                    pts[idx1] = np.asarray(bestP, F32).reshape(3)
+                nmatches += 1
+                if check_ori:
+                    rotHist[rot_bin(kp1["angle"][idx1], kp2["angle"][bestIdx2])].append(idx1)
+    if check_ori:
+        keep = compute_three_maxima([len(h) for h in rotHist])
+        for i in range(HISTO_LENGTH):
+            if i in keep:
+                continue
+            for j in rotHist[i]:
+                m12[j] = -1
+                nmatches -= 1
+    return np.array(m12, np.int32), nmatches, pts, margins
+
+
 def fisheye_lapping_match(descL, descR):
     """Frame.cc:1134-1141: BFMatcher(NORM_HAMMING).knnMatch(k=2) + Lowe ratio 0.7.  Returns
     (match index per query or -1, knn idx (n,2), knn dist (n,2))."""

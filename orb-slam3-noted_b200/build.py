@@ -33,7 +33,7 @@ def _run(cmd, **kw):
 
 def build_cuda(force=False):
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
-    deps = srcs + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.inc")) + \
+    deps = srcs + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.inc")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
         glob.glob(os.path.join(ROOT, "include", "*.h"))
     if not force and _newer(LIB, deps):
         return LIB

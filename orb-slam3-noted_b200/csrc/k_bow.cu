@@ -19,6 +19,7 @@
 //   picks the three maxima like the reference and clears everything else.
 #include "orbfe_internal.h"
 #include "orbfe_match.h"
+#include "kb8_device.cuh"
 
 #define BOW_WARPS 4
 
@@ -142,6 +143,61 @@ __global__ void __launch_bounds__(BOW_WARPS * 32) k_tri_nodes(const MatchProblem
     }
 }
 
+// The same search with Kannala-Brandt cameras (ORBmatcher.cc:1208-1432 + KannalaBrandt8::epipolarConstrain_,
+// KannalaBrandt8.cpp:239-242): a candidate passes iff TriangulateMatches_ returns a depth > 1e-4 for the
+// camera pairing (left/right of each keyframe) the two features belong to.  Fisheye keyframes carry no
+// mvuRight, so bStereo1/2 are false; the epipole test applies iff keyframe 1 has a single camera.
+__global__ void __launch_bounds__(BOW_WARPS * 32) k_tri_nodes_kb8(const MatchProblem* __restrict__ probs,
+                                                                  const MatchItem* __restrict__ items, int nitems,
+                                                                  const __grid_constant__ TriKb8Geo geo, int coarse,
+                                                                  float* __restrict__ points) {
+    const int item = blockIdx.x * BOW_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (item >= nitems) return;
+    const MatchItem it = items[item];
+    const MatchProblem P = probs[it.prob];
+    const bool dual = geo.nleftA >= 0 && geo.nleftB >= 0;
+    for (int ia = it.a0; ia < it.a1; ++ia) {
+        const int idx1 = P.idxA[ia];
+        if (P.maskA[idx1]) continue;
+        const float4 k1p = P.kpA[idx1];
+        const int oct1 = __float_as_int(k1p.w);
+        const int right1 = !(geo.nleftA == -1 || idx1 < geo.nleftA);
+        const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(P.descA + 32ll * idx1));
+        const uint4 a1 = __ldg(reinterpret_cast<const uint4*>(P.descA + 32ll * idx1) + 1);
+        uint32_t best = 0xFFFFFFFFu, mine = 0xFFFFFFFFu;
+        float bp[3] = {0.f, 0.f, 0.f};
+        for (int jb = it.b0 + lane; jb < it.b1; jb += 32) {
+            const int idx2 = P.idxB[jb];
+            if (P.maskB[idx2]) continue;
+            const int dist = ham(a0, a1, P.descB + 32ll * idx2);
+            if (dist > ORBFE_TH_LOW) continue;
+            const uint32_t key = (uint32_t)dist << 16 | (uint32_t)(0xFFFF - (jb - it.b0));
+            if (key > mine) continue;                           // cannot beat this lane's best: skip the geometry
+            const float4 k2p = P.kpB[idx2];
+            const int oct2 = __float_as_int(k2p.w);
+            const int right2 = !(geo.nleftB == -1 || idx2 < geo.nleftB);
+            if (geo.nleftA < 0) {
+                const float dx = __fsub_rn(geo.ex, k2p.x), dy = __fsub_rn(geo.ey, k2p.y);
+                if (__fadd_rn(__fmul_rn(dx, dx), __fmul_rn(dy, dy)) < __fmul_rn(100.f, geo.scaleB[oct2])) continue;
+            }
+            const int c = dual ? 2 * right1 + right2 : 0;
+            float p[3] = {0.f, 0.f, 0.f};
+            bool ok = coarse != 0;
+            if (!ok)
+                ok = kb8_triangulate_matches(geo.camA[dual ? right1 : 0], geo.camB[dual ? right2 : 0], geo.R12[c], geo.t12[c], k1p.x,
+                                             k1p.y, k2p.x, k2p.y, geo.sigma2A[oct1], geo.sigma2B[oct2], p) > 0.0001f;
+            if (ok) { mine = key; bp[0] = p[0]; bp[1] = p[1]; bp[2] = p[2]; }
+        }
+        best = mine;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+        if (best != 0xFFFFFFFFu && mine == best) {              // keys are unique (they carry the position)
+            P.a2b[idx1] = P.idxB[it.b0 + (0xFFFF - (int)(best & 0xFFFF))];
+            if (points) { points[3 * idx1] = bp[0]; points[3 * idx1 + 1] = bp[1]; points[3 * idx1 + 2] = bp[2]; }
+        }
+    }
+}
+
 // One CTA per problem.  overB != 0: matches are the entries of b2a (SearchByBoW); else of a2b
 // (SearchForTriangulation's vMatches12).  rot = angle(A) - angle(B) in both cases.
 __global__ void __launch_bounds__(256) k_match_finish(const MatchProblem* __restrict__ probs, int overB, int checkOri,
@@ -207,6 +263,17 @@ cudaError_t orbfe_launch_bow(cudaStream_t st, const MatchProblem* dProbs, int np
         ++*launches;
     }
     k_match_finish<<<nprob, 256, 0, st>>>(dProbs, 1, checkOri, dCounts);
+    ++*launches;
+    return cudaGetLastError();
+}
+
+cudaError_t orbfe_launch_tri_kb8(cudaStream_t st, const MatchProblem* dProbs, const MatchItem* dItems, int nitems,
+                                 const TriKb8Geo& geo, int coarse, int checkOri, float* dPoints, int* dCounts, long long* launches) {
+    if (nitems > 0) {
+        k_tri_nodes_kb8<<<(nitems + BOW_WARPS - 1) / BOW_WARPS, BOW_WARPS * 32, 0, st>>>(dProbs, dItems, nitems, geo, coarse, dPoints);
+        ++*launches;
+    }
+    k_match_finish<<<1, 256, 0, st>>>(dProbs, 0, checkOri, dCounts);
     ++*launches;
     return cudaGetLastError();
 }

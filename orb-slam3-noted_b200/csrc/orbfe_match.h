@@ -36,6 +36,16 @@ struct TriGeo {
     float sigma2B[ORBFE_MAX_LEVELS], scaleB[ORBFE_MAX_LEVELS];
 };
 
+// SearchForTriangulation with Kannala-Brandt cameras: cameras [0] = mpCamera, [1] = mpCamera2 of each
+// keyframe, relative poses {ll, lr, rl, rr} (x1 = R12 x2 + t12), NLeft of both keyframes (-1: one camera).
+struct TriKb8Geo {
+    float camA[2][8], camB[2][8];
+    float R12[4][9], t12[4][3];
+    float sigma2A[ORBFE_MAX_LEVELS], sigma2B[ORBFE_MAX_LEVELS], scaleB[ORBFE_MAX_LEVELS];
+    float ex, ey;
+    int nleftA, nleftB;
+};
+
 // Kannala-Brandt stereo geometry (cameras 1 = left, 2 = right; x1 = R12 x2 + t12).
 struct Kb8Geo {
     float cam1[8], cam2[8];     // fx, fy, cx, cy, k0..k3 (KannalaBrandt8::mvParameters)
@@ -46,6 +56,8 @@ struct Kb8Geo {
 cudaError_t orbfe_launch_fisheye_triangulate(cudaStream_t st, const Kb8Geo& G, const orbfe_keypoint* kpL, const orbfe_keypoint* kpR,
                                              int monoLeft, int monoRight, int nq, const int32_t* dMatch, int32_t* l2r, int32_t* r2l,
                                              float* depth, float* p3d, int* count, long long* launches);
+cudaError_t orbfe_launch_tri_kb8(cudaStream_t st, const MatchProblem* dProbs, const MatchItem* dItems, int nitems,
+                                 const TriKb8Geo& geo, int coarse, int checkOri, float* dPoints, int* dCounts, long long* launches);
 void orbfe_knn2_plan(int nqMax, int ntMax, int batch, int smCount, int* nsplit, int* splitLen);
 cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStride, const int* dNq, int nqMax, const uint8_t* dt,
                               long long tStride, const int* dNt, int ntMax, int batch, int nsplit, int splitLen, uint2* dPartial,

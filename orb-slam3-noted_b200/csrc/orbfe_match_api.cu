@@ -426,6 +426,73 @@ extern "C" int orbfe_search_triangulation(orbfe_matcher* m, const orbfe_bow_side
     return *reinterpret_cast<int*>(m->hStage + oCnt);
 }
 
+extern "C" int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_side* A, const orbfe_bow_side* B,
+                                              const orbfe_kb8_epipolar* geo, int only_stereo, int coarse, int32_t* matches12,
+                                              float* points12) {
+    if (!m || !A || !B || !geo || !matches12 || !valid_side(*A) || !valid_side(*B) || !A->kps || !B->kps) return ORBFE_ERR_BAD_ARGUMENT;
+    if (!geo->sigma2_a || !geo->sigma2_b || !geo->scale_b || geo->nlevels < 1 || geo->nlevels > ORBFE_MAX_LEVELS || B->n >= 65536)
+        return ORBFE_ERR_BAD_ARGUMENT;
+    if (geo->nleft_a < -1 || geo->nleft_a > A->n || geo->nleft_b < -1 || geo->nleft_b > B->n) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < A->n; ++i)
+        if (A->kps[i].octave < 0 || A->kps[i].octave >= geo->nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < B->n; ++i)
+        if (B->kps[i].octave < 0 || B->kps[i].octave >= geo->nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int i = 0; i < A->n; ++i) matches12[i] = -1;
+    if (points12) memset(points12, 0, sizeof(float) * 3 * (size_t)A->n);
+    if (only_stereo || A->n == 0) return 0;                       // bStereo1 is false for every fisheye feature
+    CK(cudaSetDevice(m->device));
+    size_t u = 0;
+    SideLayout LA, LB;
+    reserve_side(*A, false, u, LA);
+    reserve_side(*B, false, u, LB);
+    std::vector<MatchItem> items;
+    join_nodes(0, A->fv, B->fv, items);
+    const size_t oProb = stage_take(u, sizeof(MatchProblem));
+    const size_t oItems = stage_take(u, sizeof(MatchItem) * std::max<size_t>(items.size(), 1));
+    const size_t inBytes = u;
+    const size_t oOut = stage_take(u, 0);
+    const size_t oM = stage_take(u, sizeof(int32_t) * A->n);
+    const size_t oCnt = stage_take(u, sizeof(int));
+    const size_t oNeg = u;
+    const size_t oPts = stage_take(u, sizeof(float) * 3 * A->n);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));
+    fill_side(m->hStage, *A, LA, 0, nullptr);
+    fill_side(m->hStage, *B, LB, 0, nullptr);
+    MatchProblem P;
+    memset(&P, 0, sizeof(P));
+    P.descA = m->dStage + LA.desc; P.descB = m->dStage + LB.desc;
+    P.idxA = reinterpret_cast<const int32_t*>(m->dStage + LA.idx);
+    P.idxB = reinterpret_cast<const int32_t*>(m->dStage + LB.idx);
+    P.maskA = m->dStage + LA.mask; P.maskB = m->dStage + LB.mask;
+    P.kpA = reinterpret_cast<const float4*>(m->dStage + LA.kp);
+    P.kpB = reinterpret_cast<const float4*>(m->dStage + LB.kp);
+    P.a2b = reinterpret_cast<int32_t*>(m->dStage + oM);
+    P.nA = A->n; P.nB = B->n;
+    memcpy(m->hStage + oProb, &P, sizeof(P));
+    if (!items.empty()) memcpy(m->hStage + oItems, items.data(), sizeof(MatchItem) * items.size());
+    TriKb8Geo g;
+    memset(&g, 0, sizeof(g));
+    memcpy(g.camA, geo->cam_a, sizeof(g.camA));
+    memcpy(g.camB, geo->cam_b, sizeof(g.camB));
+    memcpy(g.R12, geo->R12, sizeof(g.R12));
+    memcpy(g.t12, geo->t12, sizeof(g.t12));
+    g.ex = geo->ex; g.ey = geo->ey; g.nleftA = geo->nleft_a; g.nleftB = geo->nleft_b;
+    for (int l = 0; l < geo->nlevels; ++l) { g.sigma2A[l] = geo->sigma2_a[l]; g.sigma2B[l] = geo->sigma2_b[l]; g.scaleB[l] = geo->scale_b[l]; }
+    CK(cudaMemcpyAsync(m->dStage, m->hStage, inBytes, cudaMemcpyHostToDevice, m->stream));
+    CK(cudaMemsetAsync(m->dStage + oOut, 0xFF, oNeg - oOut, m->stream));
+    CK(cudaMemsetAsync(m->dStage + oPts, 0, u - oPts, m->stream));
+    CK(orbfe_launch_tri_kb8(m->stream, reinterpret_cast<const MatchProblem*>(m->dStage + oProb),
+                            reinterpret_cast<const MatchItem*>(m->dStage + oItems), (int)items.size(), g, coarse, m->checkOri,
+                            reinterpret_cast<float*>(m->dStage + oPts), reinterpret_cast<int*>(m->dStage + oCnt), &m->launches));
+    CK(cudaMemcpyAsync(m->hStage + oOut, m->dStage + oOut, u - oOut, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(matches12, m->hStage + oM, sizeof(int32_t) * A->n);
+    if (points12) memcpy(points12, m->hStage + oPts, sizeof(float) * 3 * (size_t)A->n);
+    return *reinterpret_cast<int*>(m->hStage + oCnt);
+}
+
 // ---- Kannala-Brandt fisheye stereo ----------------------------------------------------------------------
 extern "C" int orbfe_fisheye_stereo_match(orbfe_matcher* m, const orbfe_keypoint* kps_left, const uint8_t* desc_left, int n_left,
                                           int mono_left, const orbfe_keypoint* kps_right, const uint8_t* desc_right, int n_right,

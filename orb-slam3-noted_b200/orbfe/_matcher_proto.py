@@ -19,7 +19,14 @@ class Epipolar(C.Structure):
     _fields_ = [("F12", _F * 9), ("ex", _F), ("ey", _F), ("sigma2_b", _P), ("scale_b", _P), ("nlevels", _I)]
 
 
+class Kb8Epipolar(C.Structure):
+    """orbfe_kb8_epipolar"""
+    _fields_ = [("cam_a", _F * 16), ("cam_b", _F * 16), ("nleft_a", _I), ("nleft_b", _I), ("R12", _F * 36), ("t12", _F * 12),
+                ("ex", _F), ("ey", _F), ("sigma2_a", _P), ("sigma2_b", _P), ("scale_b", _P), ("nlevels", _I)]
+
+
 PROTO = {
+    "orbfe_search_triangulation_kb8": (_I, [_P, _P, _P, _P, _I, _I, _P, _P]),
     "orbfe_matcher_create": (_I, [_F, _I, _I, C.POINTER(_P)]),
     "orbfe_matcher_destroy": (None, [_P]),
     "orbfe_matcher_stream": (_P, [_P]),

@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from ._lib import KEYPOINT_DTYPE, OrbfeError, lib
-from ._matcher_proto import BowSide, Epipolar, FeatureVector
+from ._matcher_proto import BowSide, Epipolar, Kb8Epipolar, FeatureVector
 
 
 def _p(a):
@@ -245,3 +245,32 @@ class ORBmatcher:
             raise OrbfeError(n, "orbfe_search_triangulation")
         i1 = np.nonzero(m12 >= 0)[0]
         return np.stack([i1, m12[i1]], axis=1).astype(np.int64), n, m12
+
+    def SearchForTriangulationKB8(self, desc1, fv1, has_mp1, kps1, desc2, fv2, has_mp2, kps2, cam_a, cam_b, nleft_a, nleft_b, R12,
+                                  t12, epipole, sigma2_a, sigma2_b, scale_b, bOnlyStereo=False, bCoarse=False):
+        """ORBmatcher::SearchForTriangulation_ (ORBmatcher.cc:1208-1432) for Kannala-Brandt keyframes
+        (KannalaBrandt8::epipolarConstrain_).  cam_*: (2, 8) = mpCamera, mpCamera2; R12 (4, 9) / t12 (4, 3) for the
+        pairings ll, lr, rl, rr.  Returns (vMatchedPairs (n, 2), nmatches, vMatches12, points (n1, 3))."""
+        A, B = _Side(desc1, fv1, has_mp1, kps1), _Side(desc2, fv2, has_mp2, kps2)
+        sa, sb = A.c_struct(), B.c_struct()
+        f = lambda a: np.ascontiguousarray(a, np.float32)
+        sigma2_a, sigma2_b, scale_b = f(sigma2_a), f(sigma2_b), f(scale_b)
+        geo = Kb8Epipolar()
+        for dst, src, n in ((geo.cam_a, cam_a, 16), (geo.cam_b, cam_b, 16), (geo.R12, R12, 36), (geo.t12, t12, 12)):
+            src = f(src).reshape(-1)
+            if src.size != n:
+                raise ValueError("cam_* must hold 2 x 8, R12 4 x 9 and t12 4 x 3 floats")
+            for i in range(n):
+                dst[i] = float(src[i])
+        geo.nleft_a, geo.nleft_b = int(nleft_a), int(nleft_b)
+        geo.ex, geo.ey = float(epipole[0]), float(epipole[1])
+        geo.sigma2_a, geo.sigma2_b, geo.scale_b, geo.nlevels = _p(sigma2_a), _p(sigma2_b), _p(scale_b), len(sigma2_b)
+        m12 = np.full(max(len(A.desc), 1), -1, np.int32)
+        pts = np.zeros((max(len(A.desc), 1), 3), np.float32)
+        n = self._lib.orbfe_search_triangulation_kb8(self._m, C.byref(sa), C.byref(sb), C.byref(geo), int(bool(bOnlyStereo)),
+                                                     int(bool(bCoarse)), _p(m12), _p(pts))
+        if n < 0:
+            raise OrbfeError(n, "orbfe_search_triangulation_kb8")
+        m12, pts = m12[:len(A.desc)], pts[:len(A.desc)]
+        i1 = np.nonzero(m12 >= 0)[0]
+        return np.stack([i1, m12[i1]], axis=1).astype(np.int64), n, m12, pts

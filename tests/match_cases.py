@@ -162,3 +162,91 @@ def fisheye_inputs(name):
     dR[mono_r:][perm] = src
     return dict(cam1=KB8_LEFT, cam2=KB8_RIGHT, R12=TLR[:, :3].copy(), t12=TLR[:, 3].copy(), kL=kL, dL=dL, kR=kR, dR=dR,
                 mono_l=mono_l, mono_r=mono_r, nlevels=nlev)
+
+
+# ---- SearchForTriangulation with Kannala-Brandt cameras --------------------------------------------------
+TRI_KB8_CASES = {
+    # name: (seed, points, dual rig, check_ori, coarse, translation of keyframe 2 in keyframe 1's left camera)
+    "tri_kb8_dual": (2200, 900, True, True, False, (0.22, 0.03, 0.05)),
+    "tri_kb8_mono": (2201, 1400, False, False, False, (0.06, 0.03, -0.30)),     # epipole inside the image
+    "tri_kb8_coarse": (2202, 700, True, True, True, (0.18, -0.02, 0.02)),
+}
+
+
+def _rot(rx, ry, rz):
+    cx, sx, cy, sy, cz, sz = np.cos(rx), np.sin(rx), np.cos(ry), np.sin(ry), np.cos(rz), np.sin(rz)
+    Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
+    Ry = np.array([[cy, 0, sy], [0, 1, 0], [-sy, 0, cy]])
+    Rz = np.array([[cz, -sz, 0], [sz, cz, 0], [0, 0, 1]])
+    return Rz @ Ry @ Rx
+
+
+def tri_kb8_inputs(name):
+    """Two keyframes of a (stereo-)fisheye rig looking at the same 3-D points.  Feature lists are
+    [left-camera features..., right-camera features...] (KeyFrame::NLeft splits them); every observation of
+    a point carries the point's descriptor with a few bits flipped outside bytes 0-1 (which define the
+    stand-in vocabulary node), pixel noise, and 6 % gross outliers so the geometric test rejects some."""
+    seed, n, dual, ori, coarse, trans = TRI_KB8_CASES[name]
+    rng = np.random.default_rng(seed)
+    nlev = 8
+    snap = lambda a: (np.round(a * 16) / 16).astype(np.float32)
+    Pw = np.stack([rng.uniform(-2.5, 2.5, n), rng.uniform(-1.8, 1.8, n), rng.uniform(0.6, 9.0, n)], axis=1)
+    base = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    ang = rng.uniform(0, 360, n)
+    Tlr = np.eye(4)
+    Tlr[:3] = TLR.astype(np.float64)
+    T_w_l1 = np.eye(4)
+    T_w_l2 = np.eye(4)
+    T_w_l2[:3, :3] = _rot(0.02, -0.03, 0.015)
+    T_w_l2[:3, 3] = trans
+    cams = [KB8_LEFT, KB8_RIGHT]
+
+    def keyframe(T_w_l, salt):
+        r = np.random.default_rng(seed * 10 + salt)
+        ks, ds = [], []
+        nleft = -1
+        for ci in range(2 if dual else 1):
+            T_w_c = T_w_l @ Tlr if ci else T_w_l
+            T_c_w = np.linalg.inv(T_w_c)
+            see = np.nonzero(r.random(n) < 0.7)[0]
+            Pc = Pw[see] @ T_c_w[:3, :3].T + T_c_w[:3, 3]
+            uv = _kb8_project64(cams[ci], Pc) + r.normal(0, 0.35, (len(see), 2))
+            bad = r.random(len(see)) < 0.06
+            uv[bad] += r.uniform(-10, 10, (int(bad.sum()), 2))
+            inside = (uv[:, 0] > 20) & (uv[:, 0] < 492) & (uv[:, 1] > 20) & (uv[:, 1] < 492) & (Pc[:, 2] > 0.1)
+            see, uv = see[inside], uv[inside]
+            nz = 80                                     # features of no common point
+            k = np.zeros(len(see) + nz, orbfe.KEYPOINT_DTYPE)
+            k["x"][:len(see)], k["y"][:len(see)] = snap(uv[:, 0]), snap(uv[:, 1])
+            k["x"][len(see):], k["y"][len(see):] = snap(r.uniform(20, 490, nz)), snap(r.uniform(20, 490, nz))
+            k["angle"][:len(see)] = ((ang[see] + r.normal(0, 4, len(see))) % 360).astype(np.float32)
+            k["angle"][len(see):] = r.uniform(0, 360, nz).astype(np.float32)
+            k["octave"] = r.integers(0, nlev, len(k))
+            k["class_id"] = -1
+            d = np.empty((len(k), 32), np.uint8)
+            d[:len(see)] = base[see]
+            d[len(see):] = r.integers(0, 256, (nz, 32), dtype=np.uint8)
+            for i in range(len(see)):
+                for b in r.choice(np.arange(16, 256), int(r.integers(0, 40)), replace=False):
+                    d[i, b >> 3] ^= 1 << (b & 7)
+            perm = r.permutation(len(k))
+            ks.append(k[perm]); ds.append(d[perm])
+            if ci == 0 and dual:
+                nleft = len(k)
+        return np.concatenate(ks), np.concatenate(ds), nleft
+
+    k1, d1, nleft1 = keyframe(T_w_l1, 1)
+    k2, d2, nleft2 = keyframe(T_w_l2, 2)
+    R12, t12 = np.zeros((4, 9), np.float32), np.zeros((4, 3), np.float32)
+    for c in range(4):                                   # ll, lr, rl, rr (ORBmatcher.cc:1248-1262)
+        T1 = T_w_l1 @ Tlr if c >> 1 else T_w_l1
+        T2 = T_w_l2 @ Tlr if c & 1 else T_w_l2
+        T12 = np.linalg.inv(T1) @ T2                     # x1 = R12 x2 + t12
+        R12[c], t12[c] = T12[:3, :3].reshape(9), T12[:3, 3]
+    T21 = np.linalg.inv(np.linalg.inv(T_w_l1) @ T_w_l2)
+    ep = _kb8_project64(KB8_LEFT, T21[:3, 3][None, :])[0]          # camera-1 centre seen by camera 2 (:1213-1218)
+    cam = np.stack([KB8_LEFT, KB8_RIGHT]).astype(np.float32)
+    return dict(k1=k1, d1=d1, fv1=fv_of(d1), mp1=orbfe.synth.mask(seed * 7 + 1, len(d1), 40), k2=k2, d2=d2, fv2=fv_of(d2),
+                mp2=orbfe.synth.mask(seed * 7 + 2, len(d2), 40), cam_a=cam, cam_b=cam, nleft_a=nleft1, nleft_b=nleft2, R12=R12,
+                t12=t12, ep=(float(np.float32(ep[0])), float(np.float32(ep[1]))), check_ori=ori, only_stereo=False,
+                coarse=coarse, nlevels=nlev)

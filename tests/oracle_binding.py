@@ -45,6 +45,8 @@ def lib():
             "orbref_knn2_many": (_L, [_P, _I, _P, _I, _I, _L, _L, _I]),
             "orbref_kb8_project": (None, [_P, _P, _P]),
             "orbref_kb8_unproject": (None, [_P, _F, _F, _P]),
+            "orbref_search_triangulation_kb8": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _P, _P, _P, _P,
+                                                     _P, _P, _I, _I, _P, _P, _F, _F, _I, _I, _I, _P, _P, _P]),
             "orbref_fisheye_stereo": (_I, [_P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P, _P]),
         }
         for name, (res, args) in sig.items():
@@ -208,3 +210,21 @@ def fisheye_stereo(cam1, cam2, kpL, descL, mono_left, kpR, descR, mono_right, R1
     n = lib().orbref_fisheye_stereo(_p(cam1), _p(cam2), _p(kpL), _p(descL), nL, mono_left, _p(kpR), _p(descR), nR, mono_right,
                                     _p(R12), _p(t12), _p(sigma2), _p(l2r), _p(r2l), _p(depth), _p(p3d), _p(mg))
     return l2r[:nL], r2l[:nR], depth[:nL], p3d[:nL], mg[:nL], n
+
+
+def search_triangulation_kb8(kpA, descA, fvA, mpA, sigma2A, kpB, descB, fvB, mpB, sigma2B, scaleB, camA, camB, nleftA, nleftB,
+                             R12, t12, ep, check_ori, only_stereo, coarse):
+    """SearchForTriangulation_ with Kannala-Brandt cameras.  Returns (m12, n, points (nA, 3), margins (nA))."""
+    kpA, kpB = np.ascontiguousarray(kpA), np.ascontiguousarray(kpB)
+    descA, descB = np.ascontiguousarray(descA, np.uint8), np.ascontiguousarray(descB, np.uint8)
+    mpA, mpB = np.ascontiguousarray(mpA).astype(np.uint8), np.ascontiguousarray(mpB).astype(np.uint8)
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    sigma2A, sigma2B, scaleB, camA, camB, R12, t12 = map(f, (sigma2A, sigma2B, scaleB, camA, camB, R12, t12))
+    assert camA.size == 16 and camB.size == 16 and R12.size == 36 and t12.size == 12
+    nA = len(descA)
+    m12, pts, mg = np.zeros(max(nA, 1), np.int32), np.zeros((max(nA, 1), 3), np.float32), np.zeros(max(nA, 1), np.float32)
+    n = lib().orbref_search_triangulation_kb8(_p(kpA), _p(descA), nA, *_fv(fvA), _p(mpA), _p(sigma2A), _p(kpB), _p(descB),
+                                              len(descB), *_fv(fvB), _p(mpB), _p(sigma2B), _p(scaleB), _p(camA), _p(camB),
+                                              int(nleftA), int(nleftB), _p(R12), _p(t12), float(ep[0]), float(ep[1]),
+                                              int(check_ori), int(only_stereo), int(coarse), _p(m12), _p(pts), _p(mg))
+    return m12[:nA], n, pts[:nA], mg[:nA]

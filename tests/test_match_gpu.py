@@ -277,3 +277,34 @@ def test_fisheye_stereo_empty_sides():
     out = m.ComputeStereoFishEyeMatches(c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], len(c["kR"]) - 1, c["cam1"], c["cam2"],
                                         c["R12"], c["t12"], s2)
     assert out[4] == 0
+
+
+@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES))
+def test_search_for_triangulation_kb8(name):
+    """SearchForTriangulation_ with Kannala-Brandt cameras vs the oracle and the golden: rows whose candidate
+    pairs all sit > 1e-3 (relative) away from a threshold of the triangulation test must agree exactly."""
+    sc, isc, s2 = OrbRef(1000, *mc.ORB).tables()[:3]
+    c = mc.tri_kb8_inputs(name)
+    g = gold(name)
+    m = orbfe.ORBmatcher(0.6, c["check_ori"])
+    pairs, n, m12, pts = m.SearchForTriangulationKB8(c["d1"], c["fv1"], c["mp1"], c["k1"], c["d2"], c["fv2"], c["mp2"], c["k2"],
+                                                     c["cam_a"], c["cam_b"], c["nleft_a"], c["nleft_b"], c["R12"], c["t12"], c["ep"],
+                                                     s2, s2, sc, False, c["coarse"])
+    rm12, rn, rpts, mg = ob.search_triangulation_kb8(c["k1"], c["d1"], c["fv1"], c["mp1"], s2, c["k2"], c["d2"], c["fv2"], c["mp2"],
+                                                     s2, sc, c["cam_a"], c["cam_b"], c["nleft_a"], c["nleft_b"], c["R12"], c["t12"],
+                                                     c["ep"], c["check_ori"], False, c["coarse"])
+    assert n == (m12 >= 0).sum() == len(pairs) and n > 60
+    for ref, refn, refp, margins in ((rm12, rn, rpts, mg), (g["m12"], int(g["n"]), g["points"], np.minimum(mg, g["margins"]))):
+        safe = margins > 1e-3
+        if safe.all():
+            assert np.array_equal(m12, ref) and n == refn
+        elif not c["check_ori"]:
+            assert np.array_equal(m12[safe], ref[safe])
+        else:
+            assert np.mean(m12 == ref) > 0.99
+        ok = (m12 >= 0) & (m12 == ref)
+        if not c["coarse"]:
+            assert np.allclose(pts[ok], refp[ok], rtol=2e-3, atol=2e-4)
+    assert m.SearchForTriangulationKB8(c["d1"], c["fv1"], c["mp1"], c["k1"], c["d2"], c["fv2"], c["mp2"], c["k2"], c["cam_a"],
+                                       c["cam_b"], c["nleft_a"], c["nleft_b"], c["R12"], c["t12"], c["ep"], s2, s2, sc, True,
+                                       c["coarse"])[1] == 0

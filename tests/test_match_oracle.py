@@ -147,6 +147,40 @@ def test_fisheye_stereo_matches_golden(name):
     assert np.array_equal(r2l[m] >= 0, np.ones(len(m), bool))
 
 
+def tri_kb8_call(fn, c, s2, sc, **kw):
+    a = dict(check_ori=c["check_ori"], only_stereo=c["only_stereo"], coarse=c["coarse"])
+    a.update(kw)
+    return fn(c["k1"], c["d1"], c["fv1"], c["mp1"], s2, c["k2"], c["d2"], c["fv2"], c["mp2"], s2, sc, c["cam_a"], c["cam_b"],
+              c["nleft_a"], c["nleft_b"], c["R12"], c["t12"], c["ep"], a["check_ori"], a["only_stereo"], a["coarse"])
+
+
+@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES))
+def test_triangulation_kb8_matches_golden(name):
+    """SearchForTriangulation_ with KB8 cameras: the accept test is a triangulation (4x4 SVD), so rows whose
+    candidates all sit away from the thresholds must agree exactly, points to float tolerance."""
+    sc, isc, s2 = tables()[:3]
+    c = mc.tri_kb8_inputs(name)
+    g = gold(name)
+    assert crc(c["k1"], c["d1"], c["k2"], c["d2"], c["R12"]) == int(g["in_crc"])
+    m12, n, pts, mg = tri_kb8_call(ob.search_triangulation_kb8, c, s2, sc)
+    if not c["check_ori"]:
+        safe = np.minimum(mg, g["margins"]) > 1e-3
+        assert np.array_equal(m12[safe], g["m12"][safe])
+        assert abs(n - int(g["n"])) <= (~safe).sum()
+    elif (np.minimum(mg, g["margins"]) > 1e-3).all():
+        assert np.array_equal(m12, g["m12"]) and n == int(g["n"])     # the rotation histogram couples all rows
+    else:
+        assert np.mean(m12 == g["m12"]) > 0.99
+    assert n > 60
+    ok = (m12 >= 0) & (m12 == g["m12"]) & (not c["coarse"])
+    assert np.allclose(pts[ok], g["points"][ok], rtol=2e-3, atol=2e-4)
+    if c["nleft_a"] >= 0:                                             # all four camera pairings occur
+        r1, r2 = np.nonzero(m12 >= 0)[0] >= c["nleft_a"], m12[m12 >= 0] >= c["nleft_b"]
+        assert len(set(zip(r1.tolist(), r2.tolist()))) == 4
+    # bOnlyStereo: a fisheye keyframe has no mvuRight >= 0 (ORBmatcher.cc:1280-1283), nothing matches
+    assert tri_kb8_call(ob.search_triangulation_kb8, c, s2, sc, only_stereo=True)[1] == 0
+
+
 def test_kb8_project_unproject_roundtrip():
     cam = mc.KB8_LEFT
     L = ob.lib()
