@@ -138,32 +138,29 @@ __global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ pyr, u
     const uint32_t* src = reinterpret_cast<const uint32_t*>(pyr + lvl + (long long)(y0 - 3 + ORBFE_EDGE) * g.pitch + ORBFE_XO + x0);
     uint32_t* dst = reinterpret_cast<uint32_t*>(blur + lvl + (long long)(y0 + ORBFE_EDGE) * g.pitch + ORBFE_XO + x0);
     const uint32_t qa = 18u | 34u << 8 | 48u << 16 | 56u << 24, qb = 48u | 34u << 8 | 18u << 16;
+    // The row loop is fully unrolled and its body unconditional (rows past a short last tile re-read the
+    // tile's last row, only the store is predicated), so the 7-row window rotates by register renaming.
     uint32_t h[7][4];
+    const int lastRow = rows + 5;
 #pragma unroll
     for (int r = 0; r < BLUR_TH + 6; ++r) {
-        if (r < rows + 6) {
-            const uint32_t* p = src + (long long)r * pw;
-            const uint32_t wm = __ldg(p - 1), w0 = __ldg(p), wp = __ldg(p + 1);
-            uint32_t hn[4];
-            hn[0] = __dp4a(__byte_perm(wm, w0, 0x4321), qa, __dp4a(__byte_perm(w0, wp, 0x4321), qb, 0u));
-            hn[1] = __dp4a(__byte_perm(wm, w0, 0x5432), qa, __dp4a(__byte_perm(w0, wp, 0x5432), qb, 0u));
-            hn[2] = __dp4a(__byte_perm(wm, w0, 0x6543), qa, __dp4a(__byte_perm(w0, wp, 0x6543), qb, 0u));
-            hn[3] = __dp4a(w0, qa, __dp4a(wp, qb, 0u));
+        const uint32_t* p = src + (long long)min(r, lastRow) * pw;
+        const uint32_t wm = __ldg(p - 1), w0 = __ldg(p), wp = __ldg(p + 1);
 #pragma unroll
-            for (int j = 0; j < 6; ++j)
+        for (int j = 0; j < 6; ++j)
 #pragma unroll
-                for (int k = 0; k < 4; ++k) h[j][k] = h[j + 1][k];
+            for (int k = 0; k < 4; ++k) h[j][k] = h[j + 1][k];
+        h[6][0] = __dp4a(__byte_perm(wm, w0, 0x4321), qa, __dp4a(__byte_perm(w0, wp, 0x4321), qb, 0u));
+        h[6][1] = __dp4a(__byte_perm(wm, w0, 0x5432), qa, __dp4a(__byte_perm(w0, wp, 0x5432), qb, 0u));
+        h[6][2] = __dp4a(__byte_perm(wm, w0, 0x6543), qa, __dp4a(__byte_perm(w0, wp, 0x6543), qb, 0u));
+        h[6][3] = __dp4a(w0, qa, __dp4a(wp, qb, 0u));
+        if (r >= 6) {
+            uint32_t v[4];
 #pragma unroll
-            for (int k = 0; k < 4; ++k) h[6][k] = hn[k];
-            if (r >= 6) {
-                uint32_t o = 0;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const uint32_t v = 18u * (h[0][k] + h[6][k]) + 34u * (h[1][k] + h[5][k]) + 48u * (h[2][k] + h[4][k]) + 56u * h[3][k];
-                    o |= ((v + 32768u) >> 16) << (8 * k);
-                }
-                dst[(long long)(r - 6) * pw] = o;
-            }
+            for (int k = 0; k < 4; ++k)     // < 2^24: the rounded result is byte 2
+                v[k] = 18u * (h[0][k] + h[6][k]) + 34u * (h[1][k] + h[5][k]) + 48u * (h[2][k] + h[4][k]) + 56u * h[3][k] + 32768u;
+            const uint32_t o = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+            if (r - 6 < rows) dst[(long long)(r - 6) * pw] = o;
         }
     }
 }
@@ -175,10 +172,12 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const uint8_t* __r
                                                               const uint32_t* __restrict__ slot, const int* __restrict__ nOut,
                                                               int kpPerFrame, orbfe_keypoint* __restrict__ kps,
                                                               uint8_t* __restrict__ desc, int frame0) {
-    __shared__ uint32_t sPat[256];
+    __shared__ float4 sPat[256];     // (x0, y0, x1, y1) of test T at [(T & 7) * 32 + (T >> 3)]
     {
         const int T = threadIdx.x;   // DESC_WARPS * 32 == 256 tests
-        sPat[(T & 7) * 32 + (T >> 3)] = __ldg(reinterpret_cast<const uint32_t*>(d_pattern) + T);
+        const uint32_t pw = __ldg(reinterpret_cast<const uint32_t*>(d_pattern) + T);
+        sPat[(T & 7) * 32 + (T >> 3)] = make_float4((float)(int8_t)(pw & 0xFF), (float)(int8_t)(pw >> 8 & 0xFF),
+                                                    (float)(int8_t)(pw >> 16 & 0xFF), (float)(int8_t)(pw >> 24));
     }
     __syncthreads();
     const int frame = frame0 + blockIdx.y, i = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
@@ -190,18 +189,21 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const uint8_t* __r
     // ---- intensity centroid (IC_Angle): lane = column u = lane - 15, rows v = -15..15 clipped to the disc
     int m10 = 0, m01 = 0;
     {
-        const uint8_t* c = pyr + centre;
+        // the disc is symmetric: |u| <= umax[|v|]  <=>  |v| <= umax[|u|], one limit per lane
         const int u = lane - 15;
-        const int au = u < 0 ? -u : u;
+        const int lim = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;
+        const uint8_t* c = pyr + centre + u;
+        const int pitch = g.pitch;
+        int sum = 0;
 #pragma unroll
         for (int v = -15; v <= 15; ++v) {
-            const int d = c_umax[v < 0 ? -v : v];
-            if (au <= d && lane < 31) {
-                const int I = __ldg(c + (long long)v * g.pitch + u);
-                m10 += u * I;
+            if ((v < 0 ? -v : v) <= lim) {
+                const int I = __ldg(c + v * pitch);
+                sum += I;
                 m01 += v * I;
             }
         }
+        m10 = u * sum;
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
@@ -219,9 +221,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const uint8_t* __r
     uint32_t byte = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
-        const uint32_t pw = sPat[k * 32 + lane];   // test 8*lane + k
-        const float x0 = (float)(int8_t)(pw & 0xFF), y0 = (float)(int8_t)(pw >> 8 & 0xFF);
-        const float x1 = (float)(int8_t)(pw >> 16 & 0xFF), y1 = (float)(int8_t)(pw >> 24);
+        const float4 pt = sPat[k * 32 + lane];   // test 8*lane + k
+        const float x0 = pt.x, y0 = pt.y, x1 = pt.z, y1 = pt.w;
         const int t0 = __ldg(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * pitch +
                              __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b))));
         const int t1 = __ldg(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a))) * pitch +

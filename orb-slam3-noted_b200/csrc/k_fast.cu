@@ -6,11 +6,11 @@
 // pyramid arena, completion on an mbarrier) issued by thread 0 while the other threads clear the score
 // map; the reference never lets FAST read outside the cell ROI, and neither do we (the TMA box may be
 // larger than the cell, the extra bytes are never tested or used as ring pixels):
-//   A. A1: a packed 4-pixels-per-thread necessary test on two opposite ring pairs (VABSDIFF4 + a
-//      carry-trick byte compare) compacts the tested area (3-px margin) to a survivor list; A2: the
-//      survivors get the 16-bit brighter/darker ring masks, pixels with a 9-contiguous arc go on the
-//      corner list.  Each stage works on a dense list, so the expensive code never runs on mostly-idle warps;
-//   B. list entries get the exact OpenCV score  max(max_k min(d_k..d_k+8), max_k min(-d_k..-d_k+8)) - 1;
+//   A. a packed 4-pixels-per-thread necessary test on two opposite ring pairs (VABSDIFF4 + a
+//      carry-trick byte compare) compacts the tested area (3-px margin) to a survivor list, so the
+//      expensive code never runs on mostly-idle warps;
+//   B. survivors get the exact OpenCV score  max(max_k min(d_k..d_k+8), max_k min(-d_k..-d_k+8)) - 1
+//      (packed 16-bit halves, VIMNMX3.U16x2); score >= t <=> a 9-arc exists, those are the corners;
 //   C. 3x3 strict-greater non-max suppression against the cell's own score map (zero outside the
 //      tested area, exactly like OpenCV's per-call row buffers);
 //   D. if nothing survives at iniThFAST the same CTA redoes A-C at minThFAST (ORBextractor.cc:825-828).
@@ -21,32 +21,29 @@
 
 #define FAST_THREADS 128
 
-__device__ __forceinline__ bool has9(uint32_t m) {
-    m |= m << 16;
-    uint32_t r = m & (m >> 1);
-    r &= r >> 2;
-    r &= r >> 4;
-    r &= m >> 8;
-    return (r & 0xFFFFu) != 0;
-}
-
-// Exact FAST score from the 16 centre-minus-ring differences.
-__device__ __forceinline__ int fast_score(const int (&d)[16]) {
-    int mn[16], mx[16];
+// Exact FAST score of OpenCV, max(max_k min(d_k..d_k+8), max_k min(-d_k..-d_k+8)) - 1 with d_k = centre -
+// ring pixel k, computed on packed halves (DPX VIMNMX3.U16x2): ring pixel k becomes P_k = (256 + c - v_k) |
+// (256 - c + v_k) << 16 (one IMAD: v_k * 0xFFFF + C0, both halves stay in 1..511), the minimum over every
+// 9-arc is two levels of min3, the maximum over the 16 arcs a max3 tree; low half = 256 + max_k min9(d),
+// high half = 256 + max_k min9(-d), so score = max(low, high) - 257.  A pixel is a corner at threshold t
+// iff score >= t (score + 1 is the largest threshold margin some 9-arc clears), which is how the kernel
+// decides corner-ness: no separate ring-mask pass.
+__device__ __forceinline__ int fast_score_packed(const uint8_t* __restrict__ tile, int idx, const int (&off)[16]) {
+    const uint32_t c = tile[idx];
+    const uint32_t c0 = (256u + c) | (256u - c) << 16;
+    uint32_t P[16], m3[16];
 #pragma unroll
-    for (int k = 0; k < 16; ++k) { mn[k] = min(d[k], d[(k + 1) & 15]); mx[k] = max(d[k], d[(k + 1) & 15]); }
-    int mn4[16], mx4[16];
+    for (int k = 0; k < 16; ++k) P[k] = (uint32_t)tile[idx + off[k]] * 0xFFFFu + c0;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) { mn4[k] = min(mn[k], mn[(k + 2) & 15]); mx4[k] = max(mx[k], mx[(k + 2) & 15]); }
-    int a = -256, b = 256;
+    for (int k = 0; k < 16; ++k) m3[k] = __vimin3_u16x2(P[k], P[(k + 1) & 15], P[(k + 2) & 15]);
+    uint32_t best = 0;
 #pragma unroll
-    for (int k = 0; k < 16; ++k) {
-        const int m8 = min(mn4[k], mn4[(k + 4) & 15]);
-        const int x8 = max(mx4[k], mx4[(k + 4) & 15]);
-        a = max(a, min(m8, d[(k + 8) & 15]));
-        b = min(b, max(x8, d[(k + 8) & 15]));
+    for (int k = 0; k < 16; k += 2) {
+        const uint32_t a = __vimin3_u16x2(m3[k], m3[(k + 3) & 15], m3[(k + 6) & 15]);
+        const uint32_t b = __vimin3_u16x2(m3[k + 1], m3[(k + 4) & 15], m3[(k + 7) & 15]);
+        best = __vimax3_u16x2(best, a, b);
     }
-    return max(a, -b) - 1;
+    return (int)max(best & 0xFFFFu, best >> 16) - 257;
 }
 
 // Per-byte unsigned "a > b" of two packed u8x4 words; the answer is bit 7 of each byte (other bits are
@@ -149,7 +146,7 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
     int t = iniTh;
     for (int pass = 0; pass < 2; ++pass) {
         if (tid == 0) { sCand = 0; sCorners = 0; sKept = 0; }
-        for (int i = tid; i < tileBytes / 4; i += FAST_THREADS) reinterpret_cast<uint32_t*>(score)[i] = 0;
+        for (int i = tid; i < tileBytes / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
         __syncthreads();                       // also orders the mbarrier init before everyone's wait
         if (pass == 0) mbar_wait(&sBar, 0);
         // A1: necessary condition on two opposite ring pairs, 4 pixels per step.  A 9-arc covers at least
@@ -180,10 +177,10 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
                     }
                 }
                 // warp-aggregated append of up to 4 survivors per lane
+                if (__ballot_sync(0xffffffffu, vb != 0u) == 0u) continue;
                 const uint32_t b0 = __ballot_sync(0xffffffffu, vb & 1u), b1 = __ballot_sync(0xffffffffu, vb & 2u);
                 const uint32_t b2 = __ballot_sync(0xffffffffu, vb & 4u), b3 = __ballot_sync(0xffffffffu, vb & 8u);
                 const int total = __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
-                if (total == 0) continue;
                 const uint32_t lt = (1u << (tid & 31)) - 1u;
                 int base = 0;
                 if ((tid & 31) == 0) base = atomicAdd(&sCand, total);
@@ -194,40 +191,22 @@ __global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_consta
             }
         }
         __syncthreads();
-        // A2: full ring masks for the survivors
+        // B: exact score of every survivor; the corners (score >= t) go on list2 and into the score map
         const int n1 = sCand;
         for (int i0 = 0; i0 < n1; i0 += FAST_THREADS) {
             const int i = i0 + tid;
             bool corner = false;
-            int idx = 0;
+            int idx = 0, s = 0;
             if (i < n1) {
                 idx = list1[i];
-                const int c = tile[idx];
-                const int lo = c - t, hi = c + t;
-                uint32_t md = 0, mb = 0;
-#pragma unroll
-                for (int k = 0; k < 16; ++k) {
-                    const int v = tile[idx + off[k]];
-                    md |= (uint32_t)(v < lo) << k;
-                    mb |= (uint32_t)(v > hi) << k;
-                }
-                corner = has9(md) || has9(mb);
+                s = fast_score_packed(tile, idx, off);
+                corner = s >= t;
             }
             const int slot = warp_push(corner, &sCorners);
-            if (slot >= 0) list2[slot] = (uint16_t)idx;
+            if (slot >= 0) { list2[slot] = (uint16_t)idx; score[idx] = (uint8_t)s; }
         }
         __syncthreads();
-        // B: exact scores
         const int nc = sCorners;
-        for (int i = tid; i < nc; i += FAST_THREADS) {
-            const int idx = list2[i];
-            const int c = tile[idx];
-            int d[16];
-#pragma unroll
-            for (int k = 0; k < 16; ++k) d[k] = c - (int)tile[idx + off[k]];
-            score[idx] = (uint8_t)fast_score(d);
-        }
-        __syncthreads();
         // C: non-max suppression
         for (int i0 = 0; i0 < nc; i0 += FAST_THREADS) {
             const int i = i0 + tid;

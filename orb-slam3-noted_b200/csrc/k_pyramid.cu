@@ -87,11 +87,21 @@ __global__ void __launch_bounds__(128) k_pyr_resize_plan(uint8_t* __restrict__ p
     const int spw = gs.pitch >> 2;
     uint32_t* dst = reinterpret_cast<uint32_t*>(pyr + gd.base + (long long)frame * gd.plane) + word;
     const int dpw = gd.pitch >> 2;
+    // lane j prepares the vertical tap of row0 + j once (reflection, table read, word offsets of the two
+    // source rows, weights pre-shifted so that (a * x) >> 16 is one IMAD.HI); the row loop broadcasts it
+    int myOff0 = 0, myOff1 = 0;
+    uint32_t myA0 = 0, myA1 = 0;
+    if (lane < PYR_TH && row0 + lane < row1) {
+        const ResizeTap t = taps[gd.tabY + reflect101(row0 + lane - ORBFE_EDGE, gd.h)];
+        myOff0 = (int)t.s0 * spw; myOff1 = (int)t.s1 * spw;
+        myA0 = (uint32_t)t.a0 << 16; myA1 = (uint32_t)t.a1 << 16;
+    }
+#pragma unroll 4
     for (int row = row0; row < row1; ++row) {
-        const int y = reflect101(row - ORBFE_EDGE, gd.h);
-        const ResizeTap tyv = taps[gd.tabY + y];
-        const uint32_t* S0 = sbase + (long long)tyv.s0 * spw;
-        const uint32_t* S1 = sbase + (long long)tyv.s1 * spw;
+        const int j = row - row0;
+        const uint32_t* S0 = sbase + __shfl_sync(0xffffffffu, myOff0, j);
+        const uint32_t* S1 = sbase + __shfl_sync(0xffffffffu, myOff1, j);
+        const uint32_t a0s = __shfl_sync(0xffffffffu, myA0, j), a1s = __shfl_sync(0xffffffffu, myA1, j);
         const uint32_t p0a = __byte_perm(S0[cp.base01], S0[cp.base01 + 1], cp.sel & 0xFFFF);
         const uint32_t p0b = __byte_perm(S0[cp.base23], S0[cp.base23 + 1], cp.sel >> 16);
         const uint32_t p1a = __byte_perm(S1[cp.base01], S1[cp.base01 + 1], cp.sel & 0xFFFF);
@@ -101,12 +111,10 @@ __global__ void __launch_bounds__(128) k_pyr_resize_plan(uint8_t* __restrict__ p
         r0[2] = __dp2a_lo(cp.a[2], p0b, 0u); r0[3] = __dp2a_hi(cp.a[3], p0b, 0u);
         r1[0] = __dp2a_lo(cp.a[0], p1a, 0u); r1[1] = __dp2a_hi(cp.a[1], p1a, 0u);
         r1[2] = __dp2a_lo(cp.a[2], p1b, 0u); r1[3] = __dp2a_hi(cp.a[3], p1b, 0u);
-        uint32_t v = 0;
+        uint32_t o[4];     // ((a0 * (r0 >> 4)) >> 16) + ((a1 * (r1 >> 4)) >> 16) + 2) >> 2, always <= 255
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const int o = ((((int)tyv.a0 * (r0[k] >> 4)) >> 16) + (((int)tyv.a1 * (r1[k] >> 4)) >> 16) + 2) >> 2;
-            v |= (uint32_t)(o & 0xFF) << (8 * k);
-        }
+        for (int k = 0; k < 4; ++k) o[k] = (__umulhi(a0s, (uint32_t)r0[k] >> 4) + __umulhi(a1s, (uint32_t)r1[k] >> 4) + 2u) >> 2;
+        const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
         dst[(long long)row * dpw] = v & cp.keep;
     }
 }
