@@ -17,22 +17,34 @@ __device__ __forceinline__ int reflect101(int i, int n) {
     return i >= n ? 2 * n - 2 - i : i;
 }
 
-__global__ void __launch_bounds__(128) k_pyr_level0(const uint8_t* __restrict__ in, long long stride,
+// One thread = one 16-byte chunk of a bordered row; a warp = 8 chunks (128 bytes) x 4 rows, so only the
+// warps over the left / right border columns diverge into the per-byte reflected path.  Chunks inside the
+// ROI (ROI column 0 sits on a 32-byte boundary, so they start at a multiple of 16 source bytes) are one
+// 128-bit load + store when the source row is 16-byte aligned, four 32-bit loads when 4-byte aligned.
+__global__ void __launch_bounds__(256) k_pyr_level0(const uint8_t* __restrict__ in, long long stride,
                                                     long long frameStride, uint8_t* __restrict__ out, LevelGeom g, int frame0) {
-    const int word = blockIdx.x * blockDim.x + threadIdx.x;
-    const int row = blockIdx.y;
-    if (word * 4 >= g.pitch) return;
+    const int chunk = blockIdx.x * 8 + (threadIdx.x & 7), row = blockIdx.z * 32 + (threadIdx.x >> 3);
+    if (chunk >= (g.pitch >> 4) || row >= g.rows) return;
     const int y = reflect101(row - ORBFE_EDGE, g.h);
-    const uint8_t* src = in + (long long)blockIdx.z * frameStride + (long long)y * stride;
-    const int x0 = word * 4 - ORBFE_XO;
-    uint32_t v = 0;
+    const uint8_t* src = in + (long long)blockIdx.y * frameStride + (long long)y * stride;
+    const int x0 = chunk * 16 - ORBFE_XO;
+    uint4 v;
+    if (x0 >= 0 && x0 + 16 <= g.w && ((reinterpret_cast<uintptr_t>(src + x0) & 15) == 0)) {
+        v = __ldg(reinterpret_cast<const uint4*>(src + x0));
+    } else if (x0 >= 0 && x0 + 16 <= g.w && ((reinterpret_cast<uintptr_t>(src + x0) & 3) == 0)) {
+        const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src + x0);
+        v = make_uint4(__ldg(s4), __ldg(s4 + 1), __ldg(s4 + 2), __ldg(s4 + 3));
+    } else {
+        uint32_t w[4] = {0u, 0u, 0u, 0u};
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int x = x0 + k;
-        if (x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE) v |= (uint32_t)__ldg(src + reflect101(x, g.w)) << (8 * k);
+        for (int k = 0; k < 16; ++k) {
+            const int x = x0 + k;
+            if (x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE) w[k >> 2] |= (uint32_t)__ldg(src + reflect101(x, g.w)) << (8 * (k & 3));
+        }
+        v = make_uint4(w[0], w[1], w[2], w[3]);
     }
-    uint8_t* dst = out + g.base + (long long)(frame0 + blockIdx.z) * g.plane + (long long)row * g.pitch;
-    reinterpret_cast<uint32_t*>(dst)[word] = v;
+    uint8_t* dst = out + g.base + (long long)(frame0 + blockIdx.y) * g.plane + (long long)row * g.pitch;
+    reinterpret_cast<uint4*>(dst)[chunk] = v;
 }
 
 // gs = source level geometry, gd = destination level geometry.
@@ -125,8 +137,8 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int fr
     const int nl = h->p.nlevels;
     {
         const LevelGeom& g = h->geom[0];
-        dim3 grid((g.pitch / 4 + 127) / 128, g.rows, batch);
-        k_pyr_level0<<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
+        dim3 grid(((g.pitch >> 4) + 7) / 8, batch, (g.rows + 31) / 32);
+        k_pyr_level0<<<grid, 256, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
         h->launches++;
     }
     for (int l = 1; l < nl; ++l) {
