@@ -19,7 +19,9 @@
 // pure function of (x, y) and is re-derived where it matters (quadtree tie-break, debug tap).
 #include "orbfe_internal.h"
 
+#ifndef FAST_THREADS
 #define FAST_THREADS 128
+#endif
 
 // Exact FAST score of OpenCV, max(max_k min(d_k..d_k+8), max_k min(-d_k..-d_k+8)) - 1 with d_k = centre -
 // ring pixel k, computed on packed halves (DPX VIMNMX3.U16x2): ring pixel k becomes P_k = (256 + c - v_k) |
