@@ -146,6 +146,50 @@ public:
         status_ = n < 0 ? n : ORBFE_OK;
         return n < 0 ? 0 : n;
     }
+    // Frame::ComputeStereoFishEyeMatches, whole body (Frame.cc:1116-1156).  cam1 / cam2: mvParameters of the two
+    // KannalaBrandt8 cameras (8 floats), Rlr (row-major 3x3) / tlr: Frame::mRlr, mtlr.  Returns nMatches.
+    int ComputeStereoFishEyeMatches(const std::vector<cv::KeyPoint>& mvKeys, const cv::Mat& mDescriptors, int monoLeft,
+                                    const std::vector<cv::KeyPoint>& mvKeysRight, const cv::Mat& mDescriptorsRight, int monoRight,
+                                    const float* cam1, const float* cam2, const float* Rlr, const float* tlr,
+                                    const std::vector<float>& mvLevelSigma2, std::vector<int>& mvLeftToRightMatch,
+                                    std::vector<int>& mvRightToLeftMatch, std::vector<float>& mvDepth, std::vector<float>& p3d) {
+        const int nL = (int)mvKeys.size(), nR = (int)mvKeysRight.size();
+        mvLeftToRightMatch.assign(nL, -1);
+        mvRightToLeftMatch.assign(nR, -1);
+        mvDepth.assign(nL, -1.0f);
+        p3d.assign(3 * (size_t)nL, 0.0f);
+        if (!m_ || nL == 0) return 0;
+        static_assert(sizeof(int) == sizeof(int32_t), "int32 match vectors");
+        const int n = orbfe_fisheye_stereo_match(m_, reinterpret_cast<const orbfe_keypoint*>(mvKeys.data()), mDescriptors.ptr(), nL,
+                                                 monoLeft, reinterpret_cast<const orbfe_keypoint*>(mvKeysRight.data()),
+                                                 nR ? mDescriptorsRight.ptr() : nullptr, nR, monoRight, cam1, cam2, Rlr, tlr,
+                                                 mvLevelSigma2.data(), (int)mvLevelSigma2.size(), mvLeftToRightMatch.data(),
+                                                 mvRightToLeftMatch.data(), mvDepth.data(), p3d.data());
+        status_ = n < 0 ? n : ORBFE_OK;
+        return n < 0 ? 0 : n;
+    }
+    // SearchForTriangulation_ with KannalaBrandt8 cameras (ORBmatcher.cc:1208-1432 + KannalaBrandt8.cpp:239-242).
+    // points (optional): triangulated point of each pair, camera-1 frame (the matchAndtriangulate overload).
+    int SearchForTriangulationKB8Arrays(const orbfe_shim::Side& kf1, const orbfe_shim::Side& kf2, const orbfe_kb8_epipolar& geo,
+                                        bool bOnlyStereo, bool bCoarse, std::vector<std::pair<size_t, size_t>>& vMatchedPairs,
+                                        std::vector<float>* points = nullptr) {
+        vMatchedPairs.clear();
+        if (points) points->clear();
+        if (!m_) return 0;
+        std::vector<int32_t> m12(kf1.n > 0 ? kf1.n : 1, -1);
+        std::vector<float> p(points ? 3 * (size_t)(kf1.n > 0 ? kf1.n : 1) : 0);
+        orbfe_bow_side A = kf1.view(), B = kf2.view();
+        const int n = orbfe_search_triangulation_kb8(m_, &A, &B, &geo, bOnlyStereo, bCoarse, m12.data(), points ? p.data() : nullptr);
+        status_ = n < 0 ? n : ORBFE_OK;
+        if (n < 0) return 0;
+        vMatchedPairs.reserve(n);
+        for (int i = 0; i < kf1.n; ++i)
+            if (m12[i] >= 0) {
+                vMatchedPairs.push_back(std::make_pair((size_t)i, (size_t)m12[i]));
+                if (points) points->insert(points->end(), p.begin() + 3 * (size_t)i, p.begin() + 3 * (size_t)i + 3);
+            }
+        return n;
+    }
 
 #ifdef ORBFE_WITH_ORBSLAM3
     // ---- object layer: the reference's signatures ------------------------------------------------------
