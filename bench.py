@@ -395,6 +395,11 @@ def run_orbfe(args):
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
                                "sample": f"{nfr} frames of the same workload, frame-parallel over {cores} host threads "
                                          "(oracle/cpu_ref, one extractor per thread)"}
+        # what the reference does per image (one thread), and per stereo pair (two threads, Frame.cc:119-122)
+        v1, _ = cpu_frames_per_s(frames[:8], 1, 1.0)
+        v2, _ = cpu_frames_per_s(frames[:16], 2, 1.0)
+        out["cpu_baseline"]["single_thread_ms_per_frame"] = 1e3 / v1
+        out["cpu_baseline"]["two_thread_stereo_pairs_per_s"] = v2 / 2
     if matching is not None:
         out["matching"] = matching
     print(json.dumps(out))

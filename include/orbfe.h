@@ -289,6 +289,44 @@ int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_side* A, co
                                    const orbfe_kb8_epipolar* geo, int only_stereo, int coarse, int32_t* matches12,
                                    float* points12);
 
+/* ---- BoW transform ------------------------------------------------------------------
+ * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (= ORB_SLAM3::ORBVocabulary) flattened: node 0 is the
+ * root, nodes 1.. in the order of the vocabulary text file (saveToTextFile / loadFromTextFile,
+ * Thirdparty/DBoW2/DBoW2/TemplatedVocabulary.h:1350-1454): parent[i] < i, is_leaf[i], a 32-byte descriptor
+ * and a weight per node.  Word ids are assigned to the leaves in that order (:1413-1420); children keep file
+ * order, which decides distance ties (:1256). */
+typedef struct orbfe_vocabulary orbfe_vocabulary;
+enum { ORBFE_BOW_TF_IDF = 0, ORBFE_BOW_TF = 1, ORBFE_BOW_IDF = 2, ORBFE_BOW_BINARY = 3 };   /* DBoW2::WeightingType */
+enum { ORBFE_BOW_NORM_NONE = 0, ORBFE_BOW_NORM_L1 = 1, ORBFE_BOW_NORM_L2 = 2 };             /* mustNormalize(): L1 for ORBvoc */
+
+int orbfe_vocabulary_create(int k, int L, int weighting, int norm, int nnodes, const int32_t* parent, const uint8_t* is_leaf,
+                            const uint8_t* descriptors, const double* weights, int device, orbfe_vocabulary** out);
+/* The ORBvoc.txt format ("k L scoring weighting" + one "parent isLeaf d0..d31 weight" line per node). */
+int orbfe_vocabulary_load_text(const char* path, int norm, int device, orbfe_vocabulary** out);
+void orbfe_vocabulary_destroy(orbfe_vocabulary* v);
+int orbfe_vocabulary_words(const orbfe_vocabulary* v);
+int orbfe_vocabulary_nodes(const orbfe_vocabulary* v);
+void* orbfe_vocabulary_stream(orbfe_vocabulary* v);          /* cudaStream_t of the vocabulary's launches */
+int orbfe_vocabulary_synchronize(orbfe_vocabulary* v);
+long long orbfe_vocabulary_launch_count(const orbfe_vocabulary* v);
+
+/* TemplatedVocabulary::transform(features, BowVector&, FeatureVector&, levelsup) (:1137-1206), what
+ * Frame::ComputeBoW (Frame.cc:721-728) / KeyFrame::ComputeBoW (KeyFrame.cc:105-114) call with levelsup = 4.
+ * Outputs are the two std::map's in key order: words[*nwords] / values (BowVector, double, bit-identical to
+ * the reference's sequential sums and normalisation) and node_ids[*nnodes] + CSR offsets[*nnodes + 1] +
+ * indices (FeatureVector = orbfe_feature_vector).  Capacities: n (offsets: n + 1).  Features whose word has
+ * weight <= 0 (stop words) appear in neither.  A leaf above level L - levelsup reports its own node id (the
+ * reference leaves nid uninitialised there). */
+int orbfe_bow_transform(orbfe_vocabulary* v, const uint8_t* desc, int n, int levelsup, uint32_t* words, double* values,
+                        int* nwords, uint32_t* node_ids, int32_t* offsets, int32_t* indices, int* nnodes);
+/* Same for `batch` frames whose descriptors are already in device memory (e.g. orbfe_device_results):
+ * frame b has d_n[b] rows at d_desc + b * frame_stride.  Device outputs, per frame at strides n_max
+ * (d_words, d_values, d_node_ids, d_indices), n_max + 1 (d_offsets) and 1 (d_nwords, d_nnodes).
+ * Enqueued on orbfe_vocabulary_stream; the caller orders it after the producer of d_desc. */
+int orbfe_bow_transform_batch_device(orbfe_vocabulary* v, const uint8_t* d_desc, ptrdiff_t frame_stride, const int* d_n, int n_max,
+                                     int batch, int levelsup, uint32_t* d_words, double* d_values, int* d_nwords,
+                                     uint32_t* d_node_ids, int32_t* d_offsets, int32_t* d_indices, int* d_nnodes);
+
 /* Measured integer-pipe ceiling of the Hamming matchers: sustained 32-bit POPC instructions per
  * second of device `device` (register-only micro-benchmark, ~10 ms).  One 256-bit descriptor pair
  * costs 8 POPC, so popc_per_s / 8 is the roofline of the matching kernels in pairs/s. */

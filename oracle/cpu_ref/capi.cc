@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "cvprim.h"
+#include "bow_ref.h"
 #include "match_ref.h"
 #include "orb_ref.h"
 
@@ -195,5 +196,51 @@ int orbref_search_triangulation_kb8(const KeyPoint* kpA, const uint8_t* descA, i
     std::memcpy(p.t12, t12, sizeof(p.t12));
     return searchForTriangulationKb8(kpA, descA, nA, fa, mpA, sigma2A, kpB, descB, nB, fb, mpB, sigma2B, scaleB, p, m12, points12,
                                      margins);
+}
+// ---- DBoW2 transform (bow_ref.cc)
+void* orbref_voc_create(int k, int L, int weighting, int norm, int nnodes, const int32_t* parent, const uint8_t* isLeaf,
+                        const uint8_t* desc, const double* weight) {
+    VocabularyRef* v = new VocabularyRef();
+    if (!v->build(k, L, weighting, norm, nnodes, parent, isLeaf, desc, weight)) { delete v; return nullptr; }
+    return v;
+}
+void orbref_voc_destroy(void* v) { delete (VocabularyRef*)v; }
+int orbref_voc_words(void* v) { return ((VocabularyRef*)v)->nwords; }
+// words / values: capacity n; nodeIds: n; offsets: n + 1; indices: n.  counts[0] = words, counts[1] = nodes.
+void orbref_bow_transform(void* voc, const uint8_t* desc, int n, int levelsup, uint32_t* words, double* values,
+                          uint32_t* nodeIds, int32_t* offsets, int32_t* indices, int32_t* counts) {
+    std::vector<uint32_t> w, nd;
+    std::vector<double> val;
+    std::vector<int32_t> off, idx;
+    bowTransform(*(VocabularyRef*)voc, desc, n, levelsup, w, val, nd, off, idx);
+    std::copy(w.begin(), w.end(), words);
+    std::copy(val.begin(), val.end(), values);
+    std::copy(nd.begin(), nd.end(), nodeIds);
+    std::copy(off.begin(), off.end(), offsets);
+    std::copy(idx.begin(), idx.end(), indices);
+    counts[0] = (int32_t)w.size(); counts[1] = (int32_t)nd.size();
+}
+// per-feature tap: word id, weight, node id of every feature (before the map stage)
+void orbref_bow_descend(void* voc, const uint8_t* desc, int n, int levelsup, uint32_t* word, double* w, uint32_t* node) {
+    for (int i = 0; i < n; ++i) ((VocabularyRef*)voc)->transformOne(desc + 32 * (size_t)i, levelsup, word[i], w[i], node[i]);
+}
+// timed CPU baseline: `nframes` transforms of n features each on `nthreads` threads
+long orbref_bow_transform_many(void* voc, const uint8_t* desc, int n, int nframes, long stride, int levelsup, int nthreads) {
+    std::vector<long> acc(nthreads, 0);
+    std::vector<std::thread> th;
+    for (int t = 0; t < nthreads; ++t)
+        th.emplace_back([&, t]() {
+            std::vector<uint32_t> w, nd;
+            std::vector<double> val;
+            std::vector<int32_t> off, idx;
+            for (int f = t; f < nframes; f += nthreads) {
+                bowTransform(*(VocabularyRef*)voc, desc + f * stride, n, levelsup, w, val, nd, off, idx);
+                acc[t] += (long)w.size();
+            }
+        });
+    for (auto& x : th) x.join();
+    long s = 0;
+    for (long a : acc) s += a;
+    return s;
 }
 }

@@ -9,5 +9,6 @@ device is present, calls raise.
 from ._lib import (KEYPOINT_DTYPE, OrbfeError, lib, lib_path, strerror, version)  # noqa: F401
 from .extractor import ORBextractor  # noqa: F401
 from .matcher import ORBmatcher, FeatureVectorCSR, measure_popc_peak  # noqa: F401
+from .vocabulary import ORBVocabulary  # noqa: F401
 from . import synth  # noqa: F401
 from . import shard  # noqa: F401

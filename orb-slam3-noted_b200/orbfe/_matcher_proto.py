@@ -26,6 +26,16 @@ class Kb8Epipolar(C.Structure):
 
 
 PROTO = {
+    "orbfe_vocabulary_create": (_I, [_I, _I, _I, _I, _I, _P, _P, _P, _P, _I, C.POINTER(_P)]),
+    "orbfe_vocabulary_load_text": (_I, [C.c_char_p, _I, _I, C.POINTER(_P)]),
+    "orbfe_vocabulary_destroy": (None, [_P]),
+    "orbfe_vocabulary_words": (_I, [_P]),
+    "orbfe_vocabulary_nodes": (_I, [_P]),
+    "orbfe_vocabulary_stream": (_P, [_P]),
+    "orbfe_vocabulary_synchronize": (_I, [_P]),
+    "orbfe_vocabulary_launch_count": (C.c_longlong, [_P]),
+    "orbfe_bow_transform": (_I, [_P, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
+    "orbfe_bow_transform_batch_device": (_I, [_P, _P, _PD, _P, _I, _I, _I, _P, _P, _P, _P, _P, _P, _P]),
     "orbfe_search_triangulation_kb8": (_I, [_P, _P, _P, _P, _I, _I, _P, _P]),
     "orbfe_matcher_create": (_I, [_F, _I, _I, C.POINTER(_P)]),
     "orbfe_matcher_destroy": (None, [_P]),

@@ -228,3 +228,50 @@ def search_triangulation_kb8(kpA, descA, fvA, mpA, sigma2A, kpB, descB, fvB, mpB
                                               int(nleftA), int(nleftB), _p(R12), _p(t12), float(ep[0]), float(ep[1]),
                                               int(check_ori), int(only_stereo), int(coarse), _p(m12), _p(pts), _p(mg))
     return m12[:nA], n, pts[:nA], mg[:nA]
+
+
+class VocRef:
+    """oracle/cpu_ref/bow_ref.cc: the DBoW2 vocabulary tree and its transform."""
+
+    def __init__(self, k, L, weighting, norm, parent, leaf, desc, weight):
+        L_ = lib()
+        L_.orbref_voc_create.restype = C.c_void_p
+        L_.orbref_voc_create.argtypes = [_I, _I, _I, _I, _I, _P, _P, _P, _P]
+        L_.orbref_voc_destroy.argtypes = [_P]
+        L_.orbref_voc_words.argtypes = [_P]
+        L_.orbref_bow_transform.argtypes = [_P, _P, _I, _I, _P, _P, _P, _P, _P, _P]
+        L_.orbref_bow_descend.argtypes = [_P, _P, _I, _I, _P, _P, _P]
+        L_.orbref_bow_transform_many.restype = _L
+        L_.orbref_bow_transform_many.argtypes = [_P, _P, _I, _I, _L, _I, _I]
+        parent, leaf = np.ascontiguousarray(parent, np.int32), np.ascontiguousarray(leaf, np.uint8)
+        desc, weight = np.ascontiguousarray(desc, np.uint8), np.ascontiguousarray(weight, np.float64)
+        self._v = L_.orbref_voc_create(k, L, weighting, norm, len(parent), _p(parent), _p(leaf), _p(desc), _p(weight))
+        if not self._v:
+            raise ValueError("inconsistent vocabulary arrays")
+        self.nwords = L_.orbref_voc_words(self._v)
+
+    def __del__(self):
+        if getattr(self, "_v", None):
+            lib().orbref_voc_destroy(self._v)
+            self._v = None
+
+    def transform(self, desc, levelsup):
+        """Returns (words, values, node_ids, offsets, indices)."""
+        desc = np.ascontiguousarray(desc, np.uint8)
+        n = len(desc)
+        words, values = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64)
+        nodes, off, idx = np.zeros(max(n, 1), np.uint32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        cnt = np.zeros(2, np.int32)
+        lib().orbref_bow_transform(self._v, _p(desc), n, levelsup, _p(words), _p(values), _p(nodes), _p(off), _p(idx), _p(cnt))
+        nw, nn = int(cnt[0]), int(cnt[1])
+        return words[:nw], values[:nw], nodes[:nn], off[:nn + 1], idx[:off[nn]]
+
+    def descend(self, desc, levelsup):
+        desc = np.ascontiguousarray(desc, np.uint8)
+        n = len(desc)
+        word, w, node = np.zeros(n, np.uint32), np.zeros(n, np.float64), np.zeros(n, np.uint32)
+        lib().orbref_bow_descend(self._v, _p(desc), n, levelsup, _p(word), _p(w), _p(node))
+        return word, w, node
+
+    def transform_many(self, desc, nframes, stride, levelsup, nthreads):
+        return lib().orbref_bow_transform_many(self._v, _p(desc), desc.shape[-2], nframes, stride, levelsup, nthreads)
