@@ -251,6 +251,81 @@ def run_matching(args, torch, orbfe, rank, local, world, barrier, dist):
     return out
 
 
+# ---- BoW leg: DBoW2 transform of every frame's descriptors (Frame::ComputeBoW), ORBvoc-sized tree ----
+def run_bow(args, torch, orbfe, ex, B, rank, local, world, barrier, dist):
+    """Runs on the extractor's device-resident results of the last batch.  Returns the `bow_transform` object."""
+    import numpy as np
+    K, Wm = args.steps, args.warmup
+    parent, leaf, desc, weight = orbfe.synth.vocabulary(4242, 10, 6)
+    voc = orbfe.ORBVocabulary(10, 6, orbfe.vocabulary.TF_IDF, orbfe.vocabulary.NORM_L1, parent, leaf, desc, weight, device=local)
+    d_kps, d_desc, d_n, d_mono, cap = ex.device_results()
+    dev = lambda shape, dt: torch.empty(shape, dtype=dt, device="cuda")
+    words, values = dev((B, cap), torch.int32), dev((B, cap), torch.float64)
+    nodes, off, idx = dev((B, cap), torch.int32), dev((B, cap + 1), torch.int32), dev((B, cap), torch.int32)
+    nw, nn = dev((B,), torch.int32), dev((B,), torch.int32)
+    stream = torch.cuda.ExternalStream(voc.stream(), device=local)
+
+    def step():
+        voc.transform_batch_device(d_desc, cap * 32, d_n, cap, B, 4, words.data_ptr(), values.data_ptr(), nw.data_ptr(),
+                                   nodes.data_ptr(), off.data_ptr(), idx.data_ptr(), nn.data_ptr())
+    ex.synchronize()
+    for _ in range(Wm):
+        step()
+    voc.synchronize()
+    barrier()
+    l0 = voc.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(K):
+        step()
+    e1.record(stream)
+    barrier()
+    ms = e0.elapsed_time(e1)
+    launches = voc.launch_count() - l0
+    res = ex.fetch_results(B)
+    nfeat = int(sum(len(r[1]) for r in res))
+    # end to end through the host-buffer call, one frame per call (what Frame::ComputeBoW does)
+    nh = min(B, 64)
+    barrier()
+    t0 = time.perf_counter()
+    for b in range(nh):
+        voc.transform(res[b][2], 4)
+    e2e_s = time.perf_counter() - t0
+    nfeat_h = int(sum(len(res[b][1]) for b in range(nh)))
+    if world > 1:
+        t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, e2e_s = float(t[0]), float(t[1]) / 1e3
+    if rank != 0:
+        return None
+    value = world * K * nfeat / (ms / 1e3)
+    out = {
+        "metric": "BoW transform features/s (DBoW2 k=10 L=6 tree, levelsup 4)", "value": value, "unit": "features/s",
+        "ms_per_step": ms / K, "gpu_launches": int(launches),
+        "config": {"workload": "TemplatedVocabulary::transform of every frame of the extraction batch, synthetic 1.1 M-node tree "
+                               "(35 MB, L2-resident)", "frames_per_step_per_gpu": B, "features_per_step_per_gpu": nfeat},
+        "e2e": {"value": world * nfeat_h / e2e_s, "unit": "features/s", "h2d_bytes_per_step": 32 * nfeat_h,
+                "d2h_bytes_per_step": 24 * nfeat_h, "api": f"orbfe_bow_transform (host buffers), one call per frame, {nh} frames"},
+        # a descent reads L x k node descriptors of 32 B: bound by L2 / L1 gather throughput, not HBM
+        "roofline": {"bound": "l2-gather", "distance_evaluations_per_s": value / world * 60, "popc_per_s": value / world * 60 * 8},
+    }
+    if world == 1 and not args.no_cpu:
+        ob = _oracle()
+        cores = os.cpu_count() or 1
+        ref = ob.VocRef(10, 6, 0, 1, parent, leaf, desc, weight)
+        n = min(len(r[1]) for r in res[:cores * 4])
+        arr = np.ascontiguousarray(np.stack([r[2][:n] for r in res[:cores * 4]]))
+        t0 = time.perf_counter()
+        reps = 0
+        while time.perf_counter() - t0 < max(args.cpu_seconds / 4, 1.0):
+            ref.transform_many(arr, len(arr), n * 32, 4, cores)
+            reps += 1
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": reps * len(arr) * n / dt, "unit": "features/s", "cores": cores, "kind": "port",
+                               "sample": f"{reps * len(arr)} frames of {n} features over {cores} host threads (oracle/cpu_ref/bow_ref.cc)"}
+    return out
+
+
 # ---- GPU arm ---------------------------------------------------------------------------------------
 def run_orbfe(args):
     import numpy as np
@@ -341,6 +416,7 @@ def run_orbfe(args):
         tl = torch.tensor([launches], dtype=torch.int64, device="cuda")
         dist.all_reduce(tl)
         launches = int(tl[0])
+    bow = None if args.no_match else run_bow(args, torch, orbfe, ex, B, rank, local, world, barrier, dist)
     matching = None if args.no_match else run_matching(args, torch, orbfe, rank, local, world, barrier, dist)
     clk = clocks.stop()
     if rank != 0:
@@ -402,6 +478,8 @@ def run_orbfe(args):
         out["cpu_baseline"]["two_thread_stereo_pairs_per_s"] = v2 / 2
     if matching is not None:
         out["matching"] = matching
+    if bow is not None:
+        out["bow_transform"] = bow
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -417,7 +495,7 @@ def main():
     ap.add_argument("--impl", default="orbfe", choices=["orbfe", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
-    ap.add_argument("--no-match", action="store_true", help="skip the matching leg")
+    ap.add_argument("--no-match", action="store_true", help="skip the matching and BoW legs")
     ap.add_argument("--match-frames", type=int, default=24, help="1920x1080 frames per matching step per GPU")
     args = ap.parse_args()
     if args.warmup < 3:

@@ -77,3 +77,24 @@ def fundamental_x_shift(fx, fy, cx, cy, tx):
     Kinv = np.array([[f(1) / f(fx), 0, -f(cx) / f(fx)], [0, f(1) / f(fy), -f(cy) / f(fy)], [0, 0, 1]], np.float32)
     tx_ = np.array([[0, 0, 0], [0, 0, -tx], [0, tx, 0]], np.float32)
     return (Kinv.T @ tx_ @ Kinv).astype(np.float32)
+
+
+def vocabulary(seed, k=10, L=6, stop_pct=1):
+    """A complete random k-ary vocabulary tree of depth L in breadth-first node order (ORBvoc.txt is not shipped
+    with the reference; k = 10, L = 6 gives its size: 1.1 M nodes, 10^6 words).  Returns the flattened arrays
+    the ABI takes: (parent, is_leaf, descriptors, weights)."""
+    rng = np.random.default_rng(seed)
+    n = (k ** (L + 1) - 1) // (k - 1)
+    parent = np.zeros(n, np.int32)
+    start = 1
+    prev_start = 0
+    for lev in range(1, L + 1):
+        cnt = k ** lev
+        parent[start:start + cnt] = prev_start + np.arange(cnt) // k
+        prev_start, start = start, start + cnt
+    leaf = np.zeros(n, np.uint8)
+    leaf[prev_start:] = 1
+    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
+    weight = np.where(leaf > 0, rng.uniform(0.5, 9.0, n), 0.0)
+    weight[(rng.random(n) < stop_pct / 100.0) & (leaf > 0)] = 0.0
+    return parent, leaf, desc, weight

@@ -5,6 +5,8 @@ consecutive, created before the recursion descends), idf-like positive weights, 
 and a few early leaves (clusters of one descriptor, HKmeansStep :560-575)."""
 import numpy as np
 
+import orbfe
+
 # name: (seed, k, L, weighting, norm, early-leaf %, stop-word %, features, levelsup)
 BOW_VOC_CASES = {
     "voc_k10_L4": (3100, 10, 4, 0, 1, 3, 2, 1500, 2),          # TF_IDF + L1 (what ORBvoc uses), FeatureVector at level 2
@@ -37,23 +39,7 @@ def make_tree(seed, k, L, early_pct, stop_pct):
 
 
 def make_full_tree(seed, k, L, stop_pct=1):
-    """A complete k-ary tree of depth L in breadth-first node order (vectorised: the ORBvoc-sized k = 10, L = 6
-    tree has 1.1 M nodes)."""
-    rng = np.random.default_rng(seed)
-    n = (k ** (L + 1) - 1) // (k - 1)
-    parent = np.zeros(n, np.int32)
-    start = 1
-    prev_start = 0
-    for lev in range(1, L + 1):
-        cnt = k ** lev
-        parent[start:start + cnt] = prev_start + np.arange(cnt) // k
-        prev_start, start = start, start + cnt
-    leaf = np.zeros(n, np.uint8)
-    leaf[prev_start:] = 1
-    desc = rng.integers(0, 256, (n, 32), dtype=np.uint8)
-    weight = np.where(leaf > 0, rng.uniform(0.5, 9.0, n), 0.0)
-    weight[(rng.random(n) < stop_pct / 100.0) & (leaf > 0)] = 0.0
-    return parent, leaf, desc, weight
+    return orbfe.synth.vocabulary(seed, k, L, stop_pct)
 
 
 def features(seed, tree_desc, n):

@@ -1,13 +1,16 @@
 // shim_test.cc — drives the C++ shim classes (include/orbfe_shim/) the way Frame.cc drives the
 // reference's ORBextractor / ORBmatcher, with the OpenCV stand-in types (TEST INFRASTRUCTURE).
 //
-//   shim_test <left.raw> <right.raw> <w> <h> <nfeatures> <bf> <b> <out.bin>
+//   shim_test <left.raw> <right.raw> <w> <h> <nfeatures> <bf> <b> <out.bin> [<vocabulary.txt>]
 //
 // Writes: int32 nL, monoL, nR | nL keypoints (28 B) | nL x 32 descriptors | nL floats mvuRight | nL floats
 // mvDepth | int32 nmatchesBoW | nR int32 (SearchByBoW KF=left, Frame=right with the node function of
 // orbfe/synth.py and every left feature holding a MapPoint) | 8 floats scale factors | pyramid level 1 ROI bytes.
+// With a vocabulary file: | int32 nwords, nnodes | nwords x (uint32 word, double value) | per node: uint32 id,
+// int32 count, count x uint32 feature (ORBVocabulary::transform of the left descriptors, levelsup 4).
 // Exit code 3 = no CUDA device (the CPU-side test expects exactly that), 0 = ok.
 #define ORBFE_NO_OPENCV 1
+#define ORBFE_NO_DBOW2 1
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
@@ -15,6 +18,7 @@
 #include <vector>
 
 #include "ORBextractor.h"
+#include "ORBVocabulary.h"
 #include "ORBmatcher.h"
 
 using namespace ORB_SLAM3;
@@ -34,7 +38,7 @@ static std::map<unsigned, std::vector<unsigned>> feature_vector(const cv::Mat& d
 }
 
 int main(int argc, char** argv) {
-    if (argc != 9) return 2;
+    if (argc != 9 && argc != 10) return 2;
     const int w = atoi(argv[3]), h = atoi(argv[4]), nf = atoi(argv[5]);
     const float bf = (float)atof(argv[6]), b = (float)atof(argv[7]);
     std::vector<unsigned char> bl = read_file(argv[1], (size_t)w * h), br = read_file(argv[2], (size_t)w * h);
@@ -45,7 +49,12 @@ int main(int argc, char** argv) {
     cv::Mat dL, dR, none;
     std::vector<int> lap = {0, 0};
     const int monoL = exL(imL, none, kL, dL, lap);
-    if (monoL < 0 && exL.lastStatus() == ORBFE_ERR_NO_DEVICE) { printf("no CUDA device\n"); return 3; }
+    if (monoL < 0 && exL.lastStatus() == ORBFE_ERR_NO_DEVICE) {
+        ORBVocabulary voc;           // must refuse as well, not fall back
+        if (argc == 10 && (voc.loadFromTextFile(argv[9]) || voc.lastStatus() != ORBFE_ERR_NO_DEVICE)) return 1;
+        printf("no CUDA device\n");
+        return 3;
+    }
     if (monoL < 0) { fprintf(stderr, "extract: %s\n", orbfe_strerror(exL.lastStatus())); return 1; }
     if (exR(imR, none, kR, dR, lap) < 0) return 1;
     cv::Mat empty;
@@ -87,6 +96,23 @@ int main(int argc, char** argv) {
     int32_t ps[2] = {p1.cols, p1.rows};
     fwrite(ps, 4, 2, o);
     for (int r = 0; r < p1.rows; ++r) fwrite(p1.ptr(r), 1, p1.cols, o);
+    if (argc == 10) {
+        ORBVocabulary voc;
+        if (!voc.loadFromTextFile(argv[9]) || voc.empty()) { fprintf(stderr, "vocabulary: %s\n", orbfe_strerror(voc.lastStatus())); return 1; }
+        std::vector<cv::Mat> rows;
+        for (int i = 0; i < dL.rows; ++i) rows.push_back(dL.row(i));
+        DBoW2::BowVector bv;
+        DBoW2::FeatureVector fvv;
+        voc.transform(rows, bv, fvv, 4);
+        if (voc.lastStatus() != ORBFE_OK) return 1;
+        int32_t cnt[2] = {(int32_t)bv.size(), (int32_t)fvv.size()};
+        fwrite(cnt, 4, 2, o);
+        for (const auto& kv : bv) { uint32_t w = kv.first; double x = kv.second; fwrite(&w, 4, 1, o); fwrite(&x, 8, 1, o); }
+        for (const auto& kv : fvv) {
+            uint32_t id = kv.first; int32_t c = (int32_t)kv.second.size();
+            fwrite(&id, 4, 1, o); fwrite(&c, 4, 1, o); fwrite(kv.second.data(), 4, kv.second.size(), o);
+        }
+    }
     fclose(o);
     printf("shim ok: %zu left keypoints, %d stereo depths, %d BoW matches\n", kL.size(),
            (int)std::count_if(depth.begin(), depth.end(), [](float d) { return d > 0; }), nb);

@@ -31,20 +31,36 @@ def build_shim():
     return EXE
 
 
-def run_shim(tmp_path, seed=1100, w=752, h=480, nf=1200, bf=47.9064, b=0.110078):
+def write_voc(tmp_path, name="voc_k10_L4"):
+    """A synthetic vocabulary in the ORBvoc text format, written by the Python restatement."""
+    import sys
+    sys.path.insert(0, os.path.join(ROOT, "oracle", "py"))
+    import bow_cases as bc
+    import bow_py
+    c = bc.voc_inputs(name)
+    v = bow_py.Vocabulary(c["k"], c["L"], c["weighting"], c["norm"])
+    for i in range(1, len(c["parent"])):
+        v.add_node(int(c["parent"][i]), bool(c["leaf"][i]), c["desc"][i], c["weight"][i])
+    p = tmp_path / "voc.txt"
+    v.save_text(str(p))
+    return p, c
+
+
+def run_shim(tmp_path, seed=1100, w=752, h=480, nf=1200, bf=47.9064, b=0.110078, voc=None):
     exe = build_shim()
     l, r = orbfe.synth.stereo_pair(seed, w, h)
     l.tofile(tmp_path / "l.raw")
     r.tofile(tmp_path / "r.raw")
     out = tmp_path / "o.bin"
-    p = subprocess.run([exe, str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(w), str(h), str(nf), repr(bf), repr(b), str(out)],
+    p = subprocess.run([exe, str(tmp_path / "l.raw"), str(tmp_path / "r.raw"), str(w), str(h), str(nf), repr(bf), repr(b), str(out)] +
+                       ([str(voc)] if voc else []),
                        stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     return p, out, (l, r)
 
 
 def test_shim_compiles_and_refuses_without_gpu(tmp_path):
     import torch
-    p, out, _ = run_shim(tmp_path)
+    p, out, _ = run_shim(tmp_path, voc=write_voc(tmp_path)[0])
     if torch.cuda.is_available():
         assert p.returncode == 0, p.stdout
     else:
@@ -56,7 +72,8 @@ def test_shim_equals_python_abi_path(tmp_path):
     w, h, nf = 752, 480, 1200
     bf = float(np.float32(47.9064))
     b = float(np.float32(np.float32(47.9064) / np.float32(435.2047)))
-    p, out, (l, r) = run_shim(tmp_path, 1100, w, h, nf, bf, b)
+    vocp, vc = write_voc(tmp_path)
+    p, out, (l, r) = run_shim(tmp_path, 1100, w, h, nf, bf, b, voc=vocp)
     assert p.returncode == 0, p.stdout
     buf = open(out, "rb").read()
     nL, monoL, nR = np.frombuffer(buf, np.int32, 3)
@@ -69,7 +86,14 @@ def test_shim_equals_python_abi_path(tmp_path):
     bow = np.frombuffer(buf, np.int32, nR, o); o += 4 * nR
     sf = np.frombuffer(buf, np.float32, 8, o); o += 32
     pw, ph = np.frombuffer(buf, np.int32, 2, o); o += 8
-    lvl1 = np.frombuffer(buf, np.uint8, pw * ph, o).reshape(ph, pw)
+    lvl1 = np.frombuffer(buf, np.uint8, pw * ph, o).reshape(ph, pw); o += pw * ph
+    nw, nn = np.frombuffer(buf, np.int32, 2, o); o += 8
+    bv = np.frombuffer(buf, np.dtype([("w", "<u4"), ("v", "<f8")]), nw, o); o += 12 * nw
+    fv = {}
+    for _ in range(nn):
+        nid, cnt = np.frombuffer(buf, np.int32, 2, o); o += 8
+        fv[int(nid)] = np.frombuffer(buf, np.uint32, cnt, o).tolist(); o += 4 * cnt
+    assert o == len(buf)
 
     exL = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h)
     exR = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h)
@@ -84,3 +108,9 @@ def test_shim_equals_python_abi_path(tmp_path):
     assert n == nb and np.array_equal(bow, b2a)
     assert np.array_equal(sf, exL.GetScaleFactors())
     assert np.array_equal(lvl1, exL.image_pyramid(1)[1])
+    # ORBVocabulary::transform through the shim == the oracle on the same descriptors
+    from oracle_binding import VocRef
+    rw, rv, rn, ro, ri = VocRef(vc["k"], vc["L"], vc["weighting"], vc["norm"], vc["parent"], vc["leaf"], vc["desc"],
+                                vc["weight"]).transform(dd, 4)
+    assert np.array_equal(bv["w"], rw) and np.array_equal(bv["v"], rv)
+    assert sorted(fv) == rn.tolist() and all(fv[int(n)] == ri[ro[i]:ro[i + 1]].tolist() for i, n in enumerate(rn))
