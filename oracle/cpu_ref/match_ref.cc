@@ -42,16 +42,6 @@ void computeThreeMaxima(const int* counts, int L, int& ind1, int& ind2, int& ind
     else if (max3 < 0.1f * (float)max1) { ind3 = -1; }
 }
 
-// Rotation-histogram bin of ORBmatcher.cc:390-396 (factor = 1.0f/HISTO_LENGTH, so bins are 30 deg wide).
-static inline int rotBin(float angle1, float angle2) {
-    const float factor = 1.0f / HISTO_LENGTH;
-    float rot = angle1 - angle2;
-    if (rot < 0.0) rot += 360.0f;
-    int bin = (int)std::round(rot * factor);
-    if (bin == HISTO_LENGTH) bin = 0;
-    return bin;
-}
-
 // Exact L1 distance of two 11x11 uint8 windows (cv::norm(IL, IR, NORM_L1), Frame.cc:908).
 static inline int sad11(const uint8_t* a, ptrdiff_t sa, const uint8_t* b, ptrdiff_t sb) {
     int s = 0;

@@ -11,6 +11,7 @@
 // Parity pin: tests/golden/match_*.npz, produced by oracle/py/match_py.py (a line-by-line Python
 // restatement that calls cv2.BFMatcher / cv2.norm for the OpenCV parts).
 #pragma once
+#include <cmath>
 #include <cstdint>
 #include <utility>
 #include <vector>
@@ -20,6 +21,16 @@
 namespace orbref {
 
 static const int TH_HIGH = 100, TH_LOW = 50, HISTO_LENGTH = 30;   // ORBmatcher.cc:36-38
+
+// Rotation-histogram bin of ORBmatcher.cc:390-396 (factor = 1.0f/HISTO_LENGTH, so bins are 30 deg wide).
+inline int rotBin(float angle1, float angle2) {
+    const float factor = 1.0f / HISTO_LENGTH;
+    float rot = angle1 - angle2;
+    if (rot < 0.0) rot += 360.0f;
+    int bin = (int)std::round(rot * factor);
+    if (bin == HISTO_LENGTH) bin = 0;
+    return bin;
+}
 
 // The SWAR popcount of ORBmatcher.cc:2561-2577, verbatim arithmetic.
 int descriptorDistanceSwar(const uint8_t* a, const uint8_t* b);
