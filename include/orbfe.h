@@ -289,6 +289,53 @@ int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_side* A, co
                                    const orbfe_kb8_epipolar* geo, int only_stereo, int coarse, int32_t* matches12,
                                    float* points12);
 
+/* ---- projection-guided searches -----------------------------------------------------
+ * The Frame being searched: what Frame::GetFeaturesInArea (Frame.cc:640-706) and the SearchByProjection loops
+ * read of it. */
+typedef struct orbfe_grid_frame {
+    const orbfe_keypoint* kps;     /* mvKeysUn (nleft == -1) or mvKeys followed by mvKeysRight */
+    const uint8_t* desc;           /* mDescriptors (n x 32; right-camera rows after the left ones) */
+    int n, nleft;                  /* Frame::N, Frame::Nleft */
+    const uint8_t* blocked;        /* [n] mvpMapPoints[i] && mvpMapPoints[i]->Observations() > 0; NULL = none */
+    const float* u_right;          /* mvuRight [n]; NULL = all -1 */
+    const int32_t* left_to_right;  /* mvLeftToRightMatch [nleft]; NULL = all -1 */
+    const int32_t* right_to_left;  /* mvRightToLeftMatch [n - nleft]; NULL = all -1 */
+    float min_x, min_y;            /* Frame::mnMinX, mnMinY */
+    float grid_w_inv, grid_h_inv;  /* mfGridElementWidthInv, mfGridElementHeightInv (64 x 48 grid, Frame.h:45-46) */
+} orbfe_grid_frame;
+
+/* One search window = one GetFeaturesInArea(u, v, r, min_level, max_level, right) call of the reference plus
+ * what is matched inside it.  Windows are listed in the reference's loop order (a MapPoint seen by both cameras
+ * of a fisheye rig gives two consecutive windows).  64 bytes. */
+typedef struct orbfe_proj_query {
+    float u, v, r;
+    float ur;                      /* predicted right-image x; with check_ur: skip features with mvuRight > 0 and
+                                      |ur - mvuRight| > r (ORBmatcher.cc:96-102, :2252-2258; only when nleft == -1) */
+    float angle;                   /* angle of the source keypoint (rotation histogram) */
+    int16_t min_level, max_level;  /* as passed to GetFeaturesInArea (max_level -1 = open) */
+    uint8_t right;                 /* search the right-camera features */
+    uint8_t obs;                   /* the MapPoint has Observations() > 0: once assigned, later windows skip that feature */
+    uint8_t check_ur;
+    uint8_t valid;                 /* 0 = the reference `continue`s before searching (not in view, bad, behind the camera ...) */
+    uint8_t skip_if_prev_ratio_rejected; /* :135: a failed ratio test also skips the same MapPoint's right-camera search */
+    uint8_t pad[3];
+    uint8_t desc[32];              /* pMP->GetDescriptor() */
+} orbfe_proj_query;
+
+/* The loop shared by SearchByProjection(Frame&, const vector<MapPoint*>&, th, ...) (ORBmatcher.cc:44-236: mode 1,
+ * th = TH_HIGH, link_stereo = 1, rot_hist = 0) and SearchByProjection(Frame& Current, const Frame& Last, th, bMono)
+ * (:2173-2389) / (Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:2391-2510) (mode 0, th = TH_HIGH / ORBdist,
+ * rot_hist = 1 (applied iff the matcher checks orientation)).
+ *   mode 0: keep the nearest descriptor, accept dist <= th.
+ *   mode 1: best and second best; accept dist <= th unless both sit on the same pyramid level and
+ *           best > mfNNratio * second (:133-139).
+ * assign[F->n]: index of the window whose MapPoint ends up in mvpMapPoints[i]; -1 = entry untouched;
+ * -2 = set to NULL by the rotation check.  choice[nq] (nullable): feature chosen by each window or -1.
+ * The windows are processed as if one after another (later windows see earlier assignments).
+ * Returns nmatches as the reference counts it, or a negative status. */
+int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_frame* F, const orbfe_proj_query* queries, int nq, int mode,
+                               int th, int link_stereo, int rot_hist, int32_t* assign, int32_t* choice);
+
 /* ---- BoW transform ------------------------------------------------------------------
  * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (= ORB_SLAM3::ORBVocabulary) flattened: node 0 is the
  * root, nodes 1.. in the order of the vocabulary text file (saveToTextFile / loadFromTextFile,

@@ -36,6 +36,34 @@ struct TriGeo {
     float sigma2B[ORBFE_MAX_LEVELS], scaleB[ORBFE_MAX_LEVELS];
 };
 
+// ---- projection-guided window searches (k_project.cu) ----
+struct ProjQueryDev {          // = orbfe_proj_query (include/orbfe.h), 64 bytes
+    float u, v, r, ur, angle;
+    int16_t minLevel, maxLevel;
+    uint8_t right, obs, checkUr, valid, skipIfPrevRatioRejected, pad[3];
+    uint8_t desc[32];
+};
+static_assert(sizeof(ProjQueryDev) == 64, "orbfe_proj_query layout");
+
+struct ProjProblem {
+    const float4* kp;          // (x, y, angle, octave as int bits) per Frame feature
+    const uint8_t* desc;
+    const uint8_t* blocked;    // nullable
+    const float* uRight;       // nullable
+    const int32_t* l2r;        // nullable
+    const int32_t* r2l;        // nullable
+    int n, nleft;
+    float minX, minY, gridWInv, gridHInv;
+    const ProjQueryDev* q;
+    int nq;
+    int32_t* assign;           // n
+    int32_t* choice;           // nq
+    int* nmatches;
+    int* scratch;              // 4 * 3072 + n + 4 * nq ints
+};
+cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int mode, int th,
+                                              float nnRatio, int linkStereo, int rotHist, long long* launches);
+
 // SearchForTriangulation with Kannala-Brandt cameras: cameras [0] = mpCamera, [1] = mpCamera2 of each
 // keyframe, relative poses {ll, lr, rl, rr} (x1 = R12 x2 + t12), NLeft of both keyframes (-1: one camera).
 struct TriKb8Geo {

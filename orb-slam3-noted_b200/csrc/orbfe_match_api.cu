@@ -493,6 +493,77 @@ extern "C" int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_
     return *reinterpret_cast<int*>(m->hStage + oCnt);
 }
 
+// ---- projection-guided window searches ------------------------------------------------------------------
+extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_frame* F, const orbfe_proj_query* queries, int nq,
+                                          int mode, int th, int link_stereo, int rot_hist, int32_t* assign, int32_t* choice) {
+    static_assert(sizeof(orbfe_proj_query) == sizeof(ProjQueryDev), "orbfe_proj_query layout");
+    if (!m || !F || nq < 0 || (nq > 0 && !queries) || !assign || mode < 0 || mode > 1 || F->n < 0) return ORBFE_ERR_BAD_ARGUMENT;
+    if (F->n > 0 && (!F->kps || !F->desc)) return ORBFE_ERR_BAD_ARGUMENT;
+    if (F->nleft < -1 || F->nleft > F->n) return ORBFE_ERR_BAD_ARGUMENT;
+    if (F->n > 16384 || nq > (1 << 24)) return ORBFE_ERR_TOO_LARGE;      // grid keys: 16-bit index, sort in shared memory
+    const int n = F->n;
+    for (int i = 0; i < n; ++i) assign[i] = -1;
+    if (choice) for (int i = 0; i < nq; ++i) choice[i] = -1;
+    if (n == 0 || nq == 0) return 0;
+    if (link_stereo && F->nleft != -1) {
+        if (F->left_to_right) for (int i = 0; i < F->nleft; ++i) if (F->left_to_right[i] < -1 || F->left_to_right[i] >= n - F->nleft) return ORBFE_ERR_BAD_ARGUMENT;
+        if (F->right_to_left) for (int i = 0; i < n - F->nleft; ++i) if (F->right_to_left[i] < -1 || F->right_to_left[i] >= F->nleft) return ORBFE_ERR_BAD_ARGUMENT;
+    }
+    CK(cudaSetDevice(m->device));
+    const int nr = F->nleft == -1 ? 0 : n - F->nleft, nl = F->nleft == -1 ? 0 : F->nleft;
+    size_t u = 0;
+    const size_t oKp = stage_take(u, sizeof(float4) * n), oDesc = stage_take(u, 32 * (size_t)n), oBlk = stage_take(u, n);
+    const size_t oUr = stage_take(u, sizeof(float) * n), oL2R = stage_take(u, sizeof(int32_t) * std::max(nl, 1));
+    const size_t oR2L = stage_take(u, sizeof(int32_t) * std::max(nr, 1)), oQ = stage_take(u, sizeof(ProjQueryDev) * (size_t)nq);
+    const size_t oProb = stage_take(u, sizeof(ProjProblem));
+    const size_t inBytes = u;
+    const size_t oScr = stage_take(u, sizeof(int) * (4 * 3072 + (size_t)n + 4 * (size_t)nq));
+    const size_t oOut = stage_take(u, 0);
+    const size_t oAsg = stage_take(u, sizeof(int32_t) * n), oCh = stage_take(u, sizeof(int32_t) * (size_t)nq), oCnt = stage_take(u, 4);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));
+    uint8_t* hs = m->hStage;
+    uint8_t* ds = m->dStage;
+    float4* kp = reinterpret_cast<float4*>(hs + oKp);
+    for (int i = 0; i < n; ++i) {
+        float4 v = make_float4(F->kps[i].x, F->kps[i].y, F->kps[i].angle, 0.f);
+        memcpy(&v.w, &F->kps[i].octave, 4);
+        kp[i] = v;
+    }
+    memcpy(hs + oDesc, F->desc, 32 * (size_t)n);
+    if (F->blocked) memcpy(hs + oBlk, F->blocked, n);
+    if (F->u_right) memcpy(hs + oUr, F->u_right, sizeof(float) * n);
+    if (F->left_to_right && nl) memcpy(hs + oL2R, F->left_to_right, sizeof(int32_t) * nl);
+    if (F->right_to_left && nr) memcpy(hs + oR2L, F->right_to_left, sizeof(int32_t) * nr);
+    memcpy(hs + oQ, queries, sizeof(ProjQueryDev) * (size_t)nq);
+    ProjProblem P;
+    memset(&P, 0, sizeof(P));
+    P.kp = reinterpret_cast<const float4*>(ds + oKp);
+    P.desc = ds + oDesc;
+    P.blocked = F->blocked ? ds + oBlk : nullptr;
+    P.uRight = F->u_right ? reinterpret_cast<const float*>(ds + oUr) : nullptr;
+    P.l2r = (F->left_to_right && nl) ? reinterpret_cast<const int32_t*>(ds + oL2R) : nullptr;
+    P.r2l = (F->right_to_left && nr) ? reinterpret_cast<const int32_t*>(ds + oR2L) : nullptr;
+    P.n = n; P.nleft = F->nleft;
+    P.minX = F->min_x; P.minY = F->min_y; P.gridWInv = F->grid_w_inv; P.gridHInv = F->grid_h_inv;
+    P.q = reinterpret_cast<const ProjQueryDev*>(ds + oQ);
+    P.nq = nq;
+    P.assign = reinterpret_cast<int32_t*>(ds + oAsg);
+    P.choice = reinterpret_cast<int32_t*>(ds + oCh);
+    P.nmatches = reinterpret_cast<int*>(ds + oCnt);
+    P.scratch = reinterpret_cast<int*>(ds + oScr);
+    memcpy(hs + oProb, &P, sizeof(P));
+    CK(cudaMemcpyAsync(ds, hs, inBytes, cudaMemcpyHostToDevice, m->stream));
+    CK(orbfe_launch_search_by_projection(m->stream, reinterpret_cast<const ProjProblem*>(ds + oProb), 1, n, mode, th, m->nnRatio,
+                                         link_stereo ? 1 : 0, (rot_hist && m->checkOri) ? 1 : 0, &m->launches));
+    CK(cudaMemcpyAsync(hs + oOut, ds + oOut, u - oOut, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(assign, hs + oAsg, sizeof(int32_t) * n);
+    if (choice) memcpy(choice, hs + oCh, sizeof(int32_t) * (size_t)nq);
+    return *reinterpret_cast<int*>(hs + oCnt);
+}
+
 // ---- Kannala-Brandt fisheye stereo ----------------------------------------------------------------------
 extern "C" int orbfe_fisheye_stereo_match(orbfe_matcher* m, const orbfe_keypoint* kps_left, const uint8_t* desc_left, int n_left,
                                           int mono_left, const orbfe_keypoint* kps_right, const uint8_t* desc_right, int n_right,

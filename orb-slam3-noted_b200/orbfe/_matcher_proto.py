@@ -25,7 +25,14 @@ class Kb8Epipolar(C.Structure):
                 ("ex", _F), ("ey", _F), ("sigma2_a", _P), ("sigma2_b", _P), ("scale_b", _P), ("nlevels", _I)]
 
 
+class GridFrameC(C.Structure):
+    """orbfe_grid_frame"""
+    _fields_ = [("kps", _P), ("desc", _P), ("n", _I), ("nleft", _I), ("blocked", _P), ("u_right", _P), ("left_to_right", _P),
+                ("right_to_left", _P), ("min_x", _F), ("min_y", _F), ("grid_w_inv", _F), ("grid_h_inv", _F)]
+
+
 PROTO = {
+    "orbfe_search_by_projection": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "orbfe_vocabulary_create": (_I, [_I, _I, _I, _I, _I, _P, _P, _P, _P, _I, C.POINTER(_P)]),
     "orbfe_vocabulary_load_text": (_I, [C.c_char_p, _I, _I, C.POINTER(_P)]),
     "orbfe_vocabulary_destroy": (None, [_P]),

@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from ._lib import KEYPOINT_DTYPE, OrbfeError, lib
-from ._matcher_proto import BowSide, Epipolar, Kb8Epipolar, FeatureVector
+from ._matcher_proto import BowSide, Epipolar, GridFrameC, Kb8Epipolar, FeatureVector
 
 
 def _p(a):
@@ -245,6 +245,24 @@ class ORBmatcher:
             raise OrbfeError(n, "orbfe_search_triangulation")
         i1 = np.nonzero(m12 >= 0)[0]
         return np.stack([i1, m12[i1]], axis=1).astype(np.int64), n, m12
+
+    def search_by_projection(self, F, queries, mode, th=TH_HIGH, link_stereo=False, rot_hist=False):
+        """The window-search loop of ORBmatcher::SearchByProjection (ORBmatcher.cc:44-236, :2173-2389, :2391-2510) on a
+        projection.GridFrame and an array of projection.PROJ_QUERY_DTYPE records (see orbfe/projection.py for how
+        each overload becomes windows).  Returns (assign [F.n], choice [len(queries)], nmatches)."""
+        from .projection import PROJ_QUERY_DTYPE
+        q = np.ascontiguousarray(queries, PROJ_QUERY_DTYPE)
+        g = GridFrameC()
+        g.kps, g.desc, g.n, g.nleft = _p(F.kps), _p(F.desc), F.n, F.nleft
+        g.blocked, g.u_right = _p(F.blocked), _p(F.u_right)
+        g.left_to_right, g.right_to_left = _p(F.left_to_right), _p(F.right_to_left)
+        g.min_x, g.min_y, g.grid_w_inv, g.grid_h_inv = float(F.min_x), float(F.min_y), float(F.grid_w_inv), float(F.grid_h_inv)
+        assign, choice = np.full(max(F.n, 1), -1, np.int32), np.full(max(len(q), 1), -1, np.int32)
+        n = self._lib.orbfe_search_by_projection(self._m, C.byref(g), _p(q), len(q), int(mode), int(th), int(bool(link_stereo)),
+                                                 int(bool(rot_hist)), _p(assign), _p(choice))
+        if n < 0:
+            raise OrbfeError(n, "orbfe_search_by_projection")
+        return assign[:F.n], choice[:len(q)], n
 
     def SearchForTriangulationKB8(self, desc1, fv1, has_mp1, kps1, desc2, fv2, has_mp2, kps2, cam_a, cam_b, nleft_a, nleft_b, R12,
                                   t12, epipole, sigma2_a, sigma2_b, scale_b, bOnlyStereo=False, bCoarse=False):

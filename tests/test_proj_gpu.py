@@ -1,0 +1,79 @@
+"""GPU parity of the projection-guided window searches (through the C ABI) against the C++ oracle engine on the same
+flattened windows (assign / choice / count bit-exact) and against the golden results of the object-level Python
+restatement of ORBmatcher::SearchByProjection."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle_binding as ob
+import orbfe
+import proj_cases as pc
+from common import GOLDEN
+from orbfe import projection as pj
+from test_proj_oracle import owners, run_lf, run_mp
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_search(ratio, check_ori=True):
+    m = orbfe.ORBmatcher(ratio, check_ori)
+
+    def f(F, q, mode, th, nnratio, link, rot):
+        assert abs(nnratio - ratio) < 1e-9 or mode == 0
+        return m.search_by_projection(F, q, mode, th, link, rot)
+    return f
+
+
+@pytest.mark.parametrize("name", list(pc.MP_CASES))
+def test_search_local_points(name):
+    c = pc.mp_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    res, n, q, choice = run_mp(c, gpu_search(c["nnratio"]))
+    rres, rn, _, rchoice = run_mp(c, ob.search_by_projection)
+    assert n == rn and np.array_equal(choice, rchoice) and np.array_equal(res, rres)
+    assert n == int(g["n"]) and np.array_equal(res, g["mappoint_of_feature"])
+
+
+@pytest.mark.parametrize("name", list(pc.LF_CASES))
+def test_track_last_frame(name):
+    c = pc.lf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    res, n, q, choice = run_lf(c, gpu_search(0.9, c["ori"]))
+    rres, rn, _, rchoice = run_lf(c, ob.search_by_projection)
+    assert n == rn and np.array_equal(choice, rchoice) and np.array_equal(res, rres)
+    assert n == int(g["n"]) and np.array_equal(res, g["lastframe_feature_of_feature"])
+
+
+def test_long_claim_chain_converges():
+    """300 identical MapPoints over a tight cluster of 40 near-identical features: window i can only settle after
+    windows < i have (each takes the best feature still free), the worst case for the parallel sweeps."""
+    rng = np.random.default_rng(5)
+    n = 40
+    k = np.zeros(n, orbfe.KEYPOINT_DTYPE)
+    k["x"], k["y"] = pc.snap(300 + rng.uniform(-3, 3, n)), pc.snap(200 + rng.uniform(-3, 3, n))
+    base = rng.integers(0, 256, 32, dtype=np.uint8)
+    d = np.stack([pc.noisy_desc(rng, base, 30) for _ in range(n)])
+    F = pj.GridFrame(k, d, (0, 0, pc.W, pc.H), pc.SCALE)
+    q = np.zeros(300, pj.PROJ_QUERY_DTYPE)
+    q["u"], q["v"], q["r"], q["min_level"], q["max_level"] = 300, 200, 8, -1, -1
+    q["obs"], q["valid"], q["desc"] = 1, 1, base
+    m = orbfe.ORBmatcher(0.9, False)
+    for mode in (0, 1):
+        assign, choice, cnt = m.search_by_projection(F, q, mode, 100)
+        rassign, rchoice, rcnt = ob.search_by_projection(F, q, mode, 100, 0.9, False, False)
+        assert cnt == rcnt and np.array_equal(choice, rchoice) and np.array_equal(assign, rassign)
+        if mode == 0:       # every feature is taken exactly once, by the first 40 windows
+            assert cnt == n and sorted(choice[:n].tolist()) == list(range(n)) and (choice[n:] == -1).all()
+
+
+def test_empty_inputs():
+    m = orbfe.ORBmatcher(0.9, True)
+    c = pc.mp_inputs("proj_local_mono")
+    q, _ = pj.queries_from_mappoints(c["F"], c["mp"], 1.0)
+    assign, choice, n = m.search_by_projection(c["F"], q[:0], 1)
+    assert n == 0 and (assign == -1).all() and len(choice) == 0
+    q2 = q.copy()
+    q2["valid"] = 0
+    assign, choice, n = m.search_by_projection(c["F"], q2, 1)
+    assert n == 0 and (choice == -1).all()
