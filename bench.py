@@ -326,6 +326,40 @@ def run_bow(args, torch, orbfe, ex, B, rank, local, world, barrier, dist):
     return out
 
 
+# ---- projection-search leg: SearchByProjection(Frame, local MapPoints) through the host API ----
+def run_projection(args, orbfe, rank, local, world):
+    """One frame's SearchLocalPoints-sized problem (1500 features, 1200 MapPoints), calls/s through
+    orbfe_search_by_projection vs the sequential CPU restatement (the reference runs it on one thread)."""
+    if rank != 0:
+        return None
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import proj_cases as pc
+    from orbfe import projection as pj
+    c = pc.mp_inputs("proj_local_mono")
+    q, _ = pj.queries_from_mappoints(c["F"], c["mp"], c["th"])
+    m = orbfe.ORBmatcher(c["nnratio"], True, device=local)
+    for _ in range(max(args.warmup, 3)):
+        m.search_by_projection(c["F"], q, 1, 100, True, False)
+    reps = 200
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        assign, choice, n = m.search_by_projection(c["F"], q, 1, 100, True, False)
+    dt = time.perf_counter() - t0
+    out = {"metric": "SearchByProjection calls/s (1500 features x 1087 windows, host buffers in and out)", "value": reps / dt,
+           "unit": "calls/s", "ms_per_call": 1e3 * dt / reps, "nmatches": int(n),
+           "note": "latency-bound single problem: one CTA; H2D of the frame + windows and D2H of the assignment inside"}
+    if not args.no_cpu:
+        ob = _oracle()
+        t0 = time.perf_counter()
+        r2 = 0
+        while time.perf_counter() - t0 < 1.0:
+            ob.search_by_projection(c["F"], q, 1, 100, c["nnratio"], True, False)
+            r2 += 1
+        out["cpu_baseline"] = {"value": r2 / (time.perf_counter() - t0), "unit": "calls/s", "cores": 1, "kind": "port",
+                               "sample": f"{r2} calls of oracle/cpu_ref/proj_ref.cc (grid build + sequential search), one thread"}
+    return out
+
+
 # ---- GPU arm ---------------------------------------------------------------------------------------
 def run_orbfe(args):
     import numpy as np
@@ -418,6 +452,7 @@ def run_orbfe(args):
         launches = int(tl[0])
     bow = None if args.no_match else run_bow(args, torch, orbfe, ex, B, rank, local, world, barrier, dist)
     matching = None if args.no_match else run_matching(args, torch, orbfe, rank, local, world, barrier, dist)
+    proj = None if args.no_match else run_projection(args, orbfe, rank, local, world)
     clk = clocks.stop()
     if rank != 0:
         if world > 1:
@@ -480,6 +515,8 @@ def run_orbfe(args):
         out["matching"] = matching
     if bow is not None:
         out["bow_transform"] = bow
+    if proj is not None:
+        out["projection_search"] = proj
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

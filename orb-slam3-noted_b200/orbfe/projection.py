@@ -140,3 +140,40 @@ def queries_from_lastframe(Cur, last, Tcw, th, fwd_bwd, project=None, project_ri
             e["angle"], e["obs"], e["valid"], e["desc"] = last["angle"][i], last["obs"][i] > 0, 1, last["desc"][i]
             q.append(e); owner.append(i)
     return (np.array(q, PROJ_QUERY_DTYPE) if q else np.zeros(0, PROJ_QUERY_DTYPE)), np.array(owner, np.int32)
+
+
+def predict_scale(max_distance, current_dist, log_scale_factor, n_levels):
+    """MapPoint::PredictScale (src/MapPoint.cc:551-566): log() of a float ratio in double, ceil, clamp."""
+    import math
+    ratio = F32(F32(max_distance) / F32(current_dist))
+    n = int(math.ceil(math.log(float(ratio)) / float(F32(log_scale_factor))))
+    return 0 if n < 0 else min(n, n_levels - 1)
+
+
+def queries_from_keyframe(Cur, kf, Tcw, th, project, log_scale_factor):
+    """SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, sAlreadyFound, th, ORBdist) :2391-2510 (relocalisation).
+    `kf`: arrays over pKF->GetMapPointMatches(): has_mp, bad, already_found, world_pos (n, 3), min_dist, max_dist
+    (Get{Min,Max}DistanceInvariance), angle (pKF->mvKeysUn[i].angle), desc.  In this overload ANY MapPoint already in
+    CurrentFrame.mvpMapPoints blocks a feature (:2455), so the frame's `blocked` mask is "entry non-NULL" and every
+    window claims (obs = 1); search with mode 0, th = ORBdist, rot_hist = 1."""
+    th = F32(th)
+    T = np.asarray(Tcw, F32)
+    Ow = -(T[:3, :3].T.astype(np.float64) @ T[:3, 3].astype(np.float64))
+    q, owner = [], []
+    for i in range(len(kf["has_mp"])):
+        if not kf["has_mp"][i] or kf["bad"][i] or kf["already_found"][i]:
+            continue
+        x3Dc = transform_point(T, kf["world_pos"][i])
+        u, v = project(x3Dc)
+        if u < Cur.min_x or u > Cur.max_x or v < Cur.min_y or v > Cur.max_y:
+            continue
+        PO = kf["world_pos"][i].astype(np.float64) - Ow
+        dist3D = F32(np.sqrt((PO * PO).sum()))
+        if dist3D < kf["min_dist"][i] or dist3D > kf["max_dist"][i]:
+            continue
+        lev = predict_scale(kf["max_dist"][i], dist3D, log_scale_factor, len(Cur.scale_factors))
+        e = np.zeros((), PROJ_QUERY_DTYPE)
+        e["u"], e["v"], e["r"], e["min_level"], e["max_level"] = u, v, F32(th * Cur.scale_factors[lev]), lev - 1, lev + 1
+        e["angle"], e["obs"], e["valid"], e["desc"] = kf["angle"][i], 1, 1, kf["desc"][i]
+        q.append(e); owner.append(i)
+    return (np.array(q, PROJ_QUERY_DTYPE) if q else np.zeros(0, PROJ_QUERY_DTYPE)), np.array(owner, np.int32)

@@ -77,3 +77,21 @@ def test_empty_inputs():
     q2["valid"] = 0
     assign, choice, n = m.search_by_projection(c["F"], q2, 1)
     assert n == 0 and (choice == -1).all()
+
+
+def test_relocalisation_overload():
+    """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist): same engine, mode 0 with th = ORBdist,
+    every assignment blocks; GPU == oracle engine on the windows built by projection.queries_from_keyframe."""
+    c = pc.lf_inputs("proj_last_mono")
+    rng = np.random.default_rng(77)
+    last, m = c["last"], len(c["last"]["has_mp"])
+    dist = np.sqrt((last["world_pos"].astype(np.float64) ** 2).sum(1)).astype(np.float32)
+    kf = dict(has_mp=last["has_mp"], bad=rng.random(m) < 0.03, already_found=rng.random(m) < 0.2, world_pos=last["world_pos"],
+              min_dist=(dist * rng.uniform(0.3, 1.05, m)).astype(np.float32), max_dist=(dist * rng.uniform(0.95, 4.0, m)).astype(np.float32),
+              angle=last["angle"], desc=last["desc"])
+    q, owner = pj.queries_from_keyframe(c["Cur"], kf, c["Tcw"], 10.0, c["project"], np.float32(np.log(1.2)))
+    assert len(q) > 400 and len(set(q["min_level"].tolist())) > 3
+    for orbdist in (100, 64):
+        assign, choice, n = orbfe.ORBmatcher(0.9, True).search_by_projection(c["Cur"], q, 0, orbdist, False, True)
+        rassign, rchoice, rn = ob.search_by_projection(c["Cur"], q, 0, orbdist, 0.9, False, True)
+        assert n == rn and np.array_equal(assign, rassign) and np.array_equal(choice, rchoice) and n > 60
