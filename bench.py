@@ -347,7 +347,7 @@ def run_projection(args, orbfe, rank, local, world):
     dt = time.perf_counter() - t0
     out = {"metric": "SearchByProjection calls/s (1500 features x 1087 windows, host buffers in and out)", "value": reps / dt,
            "unit": "calls/s", "ms_per_call": 1e3 * dt / reps, "nmatches": int(n),
-           "note": "latency-bound single problem: one CTA; H2D of the frame + windows and D2H of the assignment inside"}
+           "note": "single problem per call: grid sort (1 CTA) + candidate lists (warp per window) + ordered resolve (1 CTA); H2D of the frame + windows and D2H of the assignment inside the timed call"}
     if not args.no_cpu:
         ob = _oracle()
         t0 = time.perf_counter()

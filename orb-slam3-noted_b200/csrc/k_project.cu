@@ -3,18 +3,22 @@
 // ORBmatcher::SearchByProjection(Frame&, vector<MapPoint*>&, th, ...) (src/ORBmatcher.cc:44-236) and the best-only
 // overloads (Frame&, const Frame& LastFrame, ...) :2173-2389, (Frame&, KeyFrame*, ...) :2391-2510.
 //
-// One CTA per problem (one Frame and its ordered list of windows):
-//   1. grid: every feature's cell by PosInGrid's round() rule; a shared-memory bitonic sort of
-//      (side, cell, index) keys gives each cell's features in ascending index = the reference's push order.
-//   2. search: one warp per window.  Lanes take the window's cells in GetFeaturesInArea's order (x outer, y
-//      inner); a candidate's key is dist << 40 | position of its cell << 16 | index, so the two smallest keys
-//      are exactly the reference's best / second best under its strict '<' updates.
-//   3. order: the reference assigns MapPoints one after another and a feature holding a MapPoint with
-//      observations is skipped by every later window.  That recurrence (window i depends on the choices of
-//      windows < i) is solved by Jacobi sweeps: all windows are re-evaluated in parallel against the claims of
-//      the previous sweep, blockedAt[f] = smallest claiming window index, until nothing changes.  Sweep k makes
-//      windows 0..k-1 final, so the fixed point is the sequential result; conflicts are rare and 2-4 sweeps do.
-//   4. finish: last writer per feature (atomicMax), stereo links, rotation histogram, count.
+// Three kernels per call (any number of problems = Frames with their ordered windows per launch):
+//   k_proj_grid (one CTA per problem): every feature's cell by PosInGrid's round() rule; a shared-memory bitonic
+//      sort of (side, cell, index) keys gives each cell's features in ascending index = the reference's push order.
+//   k_proj_candidates (one warp per window, CTAs over all SMs): lanes take the window's cells in
+//      GetFeaturesInArea's order (x outer, y inner); a candidate's key is dist << 40 | position of its cell << 16 |
+//      index, so ascending keys are exactly the order in which the reference's strict '<' updates prefer
+//      candidates.  The PROJ_K smallest keys of the window are stored together with `limit`, the smallest key
+//      that was dropped anywhere (lane-local third best or list overflow): entries below it are a correct prefix
+//      of the window's full sorted candidate list.
+//   k_proj_resolve (one CTA per problem): the reference assigns MapPoints one after another and a feature
+//      holding a MapPoint with observations is skipped by every later window.  That recurrence (window i depends
+//      on the choices of windows < i) is solved by Jacobi sweeps: every window re-reads its short list against the
+//      claims of the previous sweep (blockedAt[f] = smallest claiming window index) until nothing changes.  Sweep
+//      k makes windows 0..k-1 final, so the fixed point is the sequential result; conflicts are rare and 2-4
+//      sweeps do.  A window that runs past its list's valid prefix redoes the full search (rare).  Then: last
+//      writer per feature (atomicMax), stereo links, rotation histogram, count.
 #include "orbfe_internal.h"
 #include "orbfe_match.h"
 
@@ -42,32 +46,41 @@ __device__ __forceinline__ void top2_insert(unsigned long long& k1, unsigned lon
     else if (k < k2) k2 = k;
 }
 
-// Result of one window against the current claims: chosen feature (or -1) and whether the ratio rule rejected it.
-__device__ int2 search_window(const ProjProblem& P, int i, int lane, const uint32_t* __restrict__ sorted,
-                              const int* __restrict__ cellStart, const int* __restrict__ cellEnd,
-                              const int* __restrict__ blockedAt, int mode, int th, float nnRatio) {
-    const ProjQueryDev& Q = P.q[i];
+struct Window {
+    int minCX, maxCX, minCY, maxCY;   // cell range, empty if minCX > maxCX
+};
+
+__device__ __forceinline__ Window window_cells(const ProjProblem& P, const ProjQueryDev& Q) {
     const float x = Q.u, y = Q.v, r = Q.r;
-    const int nMinCellX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, P.minX), r), P.gridWInv)));
-    const int nMaxCellX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, P.minX), r), P.gridWInv)));
-    const int nMinCellY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, P.minY), r), P.gridHInv)));
-    const int nMaxCellY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, P.minY), r), P.gridHInv)));
-    if (nMinCellX >= GRID_COLS || nMaxCellX < 0 || nMinCellY >= GRID_ROWS || nMaxCellY < 0 || nMinCellX > nMaxCellX ||
-        nMinCellY > nMaxCellY)
-        return make_int2(-1, 0);
+    Window w;
+    w.minCX = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(x, P.minX), r), P.gridWInv)));
+    w.maxCX = min(GRID_COLS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(x, P.minX), r), P.gridWInv)));
+    w.minCY = max(0, (int)floorf(__fmul_rn(__fsub_rn(__fsub_rn(y, P.minY), r), P.gridHInv)));
+    w.maxCY = min(GRID_ROWS - 1, (int)ceilf(__fmul_rn(__fadd_rn(__fsub_rn(y, P.minY), r), P.gridHInv)));
+    if (w.minCX >= GRID_COLS || w.maxCX < 0 || w.minCY >= GRID_ROWS || w.maxCY < 0 || w.minCY > w.maxCY) { w.minCX = 1; w.maxCX = 0; }
+    return w;
+}
+
+// Visits the candidates of window i that lane `lane` of `nlanes` owns, in cell order; f(key, idx).
+// blockedAt == nullptr: only the caller's static mask applies.
+template <class F>
+__device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lane, int nlanes, const int* __restrict__ blockedAt, F f) {
+    const ProjQueryDev& Q = P.q[i];
+    const Window w = window_cells(P, Q);
+    if (w.minCX > w.maxCX) return;
+    const float x = Q.u, y = Q.v, r = Q.r;
     const int minLevel = Q.minLevel, maxLevel = Q.maxLevel;
     const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
     const bool right = Q.right != 0;
     const bool checkUr = !right && Q.checkUr && P.nleft == -1 && P.uRight != nullptr;
     const uint4 a0 = *reinterpret_cast<const uint4*>(Q.desc), a1 = *(reinterpret_cast<const uint4*>(Q.desc) + 1);
-    const int ny = nMaxCellY - nMinCellY + 1, ncell = (nMaxCellX - nMinCellX + 1) * ny;
+    const int ny = w.maxCY - w.minCY + 1, ncell = (w.maxCX - w.minCX + 1) * ny;
     const int side = right ? GRID_CELLS : 0;
-    unsigned long long k1 = ~0ull, k2 = ~0ull;
-    for (int e = lane; e < ncell; e += 32) {
-        const int ix = nMinCellX + e / ny, iy = nMinCellY + e % ny;
+    for (int e = lane; e < ncell; e += nlanes) {
+        const int ix = w.minCX + e / ny, iy = w.minCY + e % ny;
         const int c = side + ix * GRID_ROWS + iy;
-        for (int j = cellStart[c]; j < cellEnd[c]; ++j) {
-            const int idx = (int)(sorted[j] & 0xFFFFu);
+        for (int j = P.cellStart[c]; j < P.cellEnd[c]; ++j) {
+            const int idx = (int)(P.sorted[j] & 0xFFFFu);
             const float4 kp = P.kp[idx];
             const int oct = __float_as_int(kp.w);
             if (bCheckLevels) {
@@ -75,22 +88,19 @@ __device__ int2 search_window(const ProjProblem& P, int i, int lane, const uint3
                 if (maxLevel >= 0 && oct > maxLevel) continue;
             }
             if (!(fabsf(__fsub_rn(kp.x, x)) < r && fabsf(__fsub_rn(kp.y, y)) < r)) continue;
-            if (blockedAt[idx] < i) continue;
+            if (blockedAt ? blockedAt[idx] < i : (P.blocked && P.blocked[idx])) continue;
             if (checkUr) {
                 const float ur = P.uRight[idx];
                 if (ur > 0.f && fabsf(__fsub_rn(Q.ur, ur)) > r) continue;
             }
             const int dist = ham_q(a0, a1, P.desc + 32ll * idx);
-            top2_insert(k1, k2, (unsigned long long)dist << 40 | (unsigned long long)e << 16 | (unsigned)idx);
+            f((unsigned long long)dist << 40 | (unsigned long long)e << 16 | (unsigned)idx);
         }
     }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) {
-        const unsigned long long o1 = __shfl_xor_sync(0xffffffffu, k1, o), o2 = __shfl_xor_sync(0xffffffffu, k2, o);
-        const unsigned long long lo = min(k1, o1), hi = max(k1, o1);
-        k2 = min(hi, min(k2, o2));
-        k1 = lo;
-    }
+}
+
+// Accept rule on the best / second-best keys: chosen feature (or -1) and whether the ratio rule rejected it.
+__device__ __forceinline__ int2 decide(const ProjProblem& P, unsigned long long k1, unsigned long long k2, int mode, int th, float nnRatio) {
     if (k1 == ~0ull) return make_int2(-1, 0);
     const int bestDist = (int)(k1 >> 40), bestIdx = (int)(k1 & 0xFFFFu);
     if (bestDist > th) return make_int2(-1, 0);
@@ -113,26 +123,14 @@ __device__ __forceinline__ int stereo_link(const ProjProblem& P, int idx) {
     return P.r2l[idx - P.nleft];          // -1 or a left index
 }
 
-__global__ void __launch_bounds__(PROJ_T) k_search_by_projection(const ProjProblem* __restrict__ probs, int mode, int th,
-                                                                 float nnRatio, int linkStereo, int rotHist) {
+// ---- 1. grid
+__global__ void __launch_bounds__(PROJ_T) k_proj_grid(const ProjProblem* __restrict__ probs) {
     extern __shared__ __align__(16) uint32_t sKeys[];
-    __shared__ int hist[ORBFE_HISTO_LENGTH];
-    __shared__ int keep[3];
-    __shared__ int sChanged, sCount;
     const ProjProblem P = probs[blockIdx.x];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int n = P.n, nq = P.nq;
+    const int tid = threadIdx.x, n = P.n;
     int np2 = 1;
     while (np2 < n) np2 <<= 1;
-    int* cellStart = P.scratch;                       // 2 * GRID_CELLS
-    int* cellEnd = cellStart + 2 * GRID_CELLS;        // 2 * GRID_CELLS
-    int* blockedAt = cellEnd + 2 * GRID_CELLS;        // n
-    int* chA = blockedAt + n;                         // nq   (choice, previous sweep)
-    int* chB = chA + nq;                              // nq
-    int* rjA = chB + nq;                              // nq   (ratio-rejected flag, previous sweep)
-    int* rjB = rjA + nq;                              // nq
-    // ---- 1. grid
-    for (int t = tid; t < 2 * GRID_CELLS; t += PROJ_T) { cellStart[t] = 0; cellEnd[t] = 0; }
+    for (int t = tid; t < 2 * GRID_CELLS; t += PROJ_T) { P.cellStart[t] = 0; P.cellEnd[t] = 0; }
     for (int t = tid; t < np2; t += PROJ_T) {
         uint32_t key = 0xFFFFFFFFu;
         if (t < n) {
@@ -160,14 +158,66 @@ __global__ void __launch_bounds__(PROJ_T) k_search_by_projection(const ProjProbl
         }
     for (int t = tid; t < n; t += PROJ_T) {
         const uint32_t key = sKeys[t];
+        P.sorted[t] = key;
         if (key == 0xFFFFFFFFu) continue;
         const int c = (int)(key >> 16);
-        if (t == 0 || (int)(sKeys[t - 1] >> 16) != c) cellStart[c] = t;
-        if (t == n - 1 || sKeys[t + 1] == 0xFFFFFFFFu || (int)(sKeys[t + 1] >> 16) != c) cellEnd[c] = t + 1;
+        if (t == 0 || (int)(sKeys[t - 1] >> 16) != c) P.cellStart[c] = t;
+        if (t == n - 1 || sKeys[t + 1] == 0xFFFFFFFFu || (int)(sKeys[t + 1] >> 16) != c) P.cellEnd[c] = t + 1;
     }
+}
+
+// ---- 2. candidate lists: blockIdx.y = problem, one warp per window
+__global__ void __launch_bounds__(256) k_proj_candidates(const ProjProblem* __restrict__ probs) {
+    const ProjProblem P = probs[blockIdx.y];
+    const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (i >= P.nq) return;
+    unsigned long long* list = P.cand + (long long)i * PROJ_K;
+    if (!P.q[i].valid) {
+        if (lane < PROJ_K) list[lane] = ~0ull;
+        if (lane == 0) P.limit[i] = ~0ull;
+        return;
+    }
+    unsigned long long k1 = ~0ull, k2 = ~0ull, dropped = ~0ull;     // lane-local best two + smallest key let go
+    scan_window(P, i, lane, 32, nullptr, [&](unsigned long long k) {
+        if (k < k1) { dropped = min(dropped, k2); k2 = k1; k1 = k; }
+        else if (k < k2) { dropped = min(dropped, k2); k2 = k; }
+        else dropped = min(dropped, k);
+    });
+    // the PROJ_K smallest of the 64 kept keys: repeated warp-min extraction
+    unsigned long long lim = dropped;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) lim = min(lim, __shfl_xor_sync(0xffffffffu, lim, o));
+    for (int s = 0; s <= PROJ_K; ++s) {
+        unsigned long long m = k1;
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) m = min(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (s == PROJ_K) { lim = min(lim, m); break; }          // first key that did not fit
+        if (lane == 0) list[s] = m;
+        if (m == ~0ull) {                                         // exhausted: pad
+            if (lane > s && lane < PROJ_K) list[lane] = ~0ull;
+            break;
+        }
+        if (k1 == m) { k1 = k2; k2 = ~0ull; }                     // keys are unique (they carry the feature index)
+    }
+    if (lane == 0) P.limit[i] = lim;
+}
+
+// ---- 3. ordered assignment
+__global__ void __launch_bounds__(PROJ_T) k_proj_resolve(const ProjProblem* __restrict__ probs, int mode, int th, float nnRatio,
+                                                         int linkStereo, int rotHist) {
+    __shared__ int hist[ORBFE_HISTO_LENGTH];
+    __shared__ int keep[3];
+    __shared__ int sChanged, sCount;
+    const ProjProblem P = probs[blockIdx.x];
+    const int tid = threadIdx.x;
+    const int n = P.n, nq = P.nq;
+    int* blockedAt = P.scratch;                       // n
+    int* chA = blockedAt + n;                         // nq   (choice, previous sweep)
+    int* chB = chA + nq;
+    int* rjA = chB + nq;                              // nq   (ratio-rejected flag, previous sweep)
+    int* rjB = rjA + nq;
     for (int i = tid; i < nq; i += PROJ_T) { chA[i] = -1; rjA[i] = 0; }
     __syncthreads();
-    // ---- 2./3. Jacobi sweeps
     int* chOld = chA; int* chNew = chB; int* rjOld = rjA; int* rjNew = rjB;
     for (int sweep = 0; sweep <= nq; ++sweep) {
         for (int t = tid; t < n; t += PROJ_T) blockedAt[t] = (P.blocked && P.blocked[t]) ? -1 : 0x7fffffff;
@@ -182,15 +232,32 @@ __global__ void __launch_bounds__(PROJ_T) k_search_by_projection(const ProjProbl
         }
         __syncthreads();
         int changed = 0;
-        for (int i = warp; i < nq; i += PROJ_T / 32) {
+        for (int i = tid; i < nq; i += PROJ_T) {
             int2 res = make_int2(-1, 0);
             const ProjQueryDev& Q = P.q[i];
             const bool skip = !Q.valid || (Q.skipIfPrevRatioRejected && i > 0 && rjOld[i - 1]);
-            if (!skip) res = search_window(P, i, lane, sKeys, cellStart, cellEnd, blockedAt, mode, th, nnRatio);
-            if (lane == 0) {
-                if (res.x != chOld[i] || res.y != rjOld[i]) changed = 1;
-                chNew[i] = res.x; rjNew[i] = res.y;
+            if (!skip) {
+                const unsigned long long* list = P.cand + (long long)i * PROJ_K;
+                const unsigned long long lim = P.limit[i];
+                unsigned long long k1 = ~0ull, k2 = ~0ull;
+                bool complete = false;                  // enough unblocked entries seen inside the valid prefix
+                for (int s = 0; s < PROJ_K; ++s) {
+                    const unsigned long long k = list[s];
+                    if (k == ~0ull) { complete = lim == ~0ull; break; }
+                    if (k >= lim) break;
+                    if (blockedAt[(int)(k & 0xFFFFu)] < i) continue;
+                    if (k1 == ~0ull) { k1 = k; if (mode == 0) { complete = true; break; } }
+                    else { k2 = k; complete = true; break; }
+                }
+                if (!complete && lim == ~0ull) complete = true;     // list held every candidate
+                if (!complete) {                                     // past the valid prefix: full scan (rare)
+                    k1 = ~0ull; k2 = ~0ull;
+                    scan_window(P, i, 0, 1, blockedAt, [&](unsigned long long k) { top2_insert(k1, k2, k); });
+                }
+                res = decide(P, k1, k2, mode, th, nnRatio);
             }
+            if (res.x != chOld[i] || res.y != rjOld[i]) changed = 1;
+            chNew[i] = res.x; rjNew[i] = res.y;
         }
         if (changed) sChanged = 1;
         __syncthreads();
@@ -200,7 +267,7 @@ __global__ void __launch_bounds__(PROJ_T) k_search_by_projection(const ProjProbl
         __syncthreads();
         if (!any) break;
     }
-    // ---- 4. finish (chOld holds the fixed point)
+    // finish (chOld holds the fixed point)
     for (int t = tid; t < n; t += PROJ_T) P.assign[t] = -1;
     if (tid < ORBFE_HISTO_LENGTH) hist[tid] = 0;
     if (tid == 0) sCount = 0;
@@ -244,19 +311,25 @@ __global__ void __launch_bounds__(PROJ_T) k_search_by_projection(const ProjProbl
     if (tid == 0) *P.nmatches = sCount;
 }
 
-cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int mode, int th,
-                                              float nnRatio, int linkStereo, int rotHist, long long* launches) {
+cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int mode,
+                                              int th, float nnRatio, int linkStereo, int rotHist, long long* launches) {
     if (nprob <= 0) return cudaSuccess;
     int np2 = 1;
     while (np2 < nMax) np2 <<= 1;
     const size_t smem = (size_t)np2 * 4;
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_search_by_projection, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_proj_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    k_search_by_projection<<<nprob, PROJ_T, smem, st>>>(dProbs, mode, th, nnRatio, linkStereo, rotHist);
-    ++*launches;
+    k_proj_grid<<<nprob, PROJ_T, smem, st>>>(dProbs);
+    if (nqMax > 0) {
+        dim3 grid((nqMax + 7) / 8, nprob);
+        k_proj_candidates<<<grid, 256, 0, st>>>(dProbs);
+        ++*launches;
+    }
+    k_proj_resolve<<<nprob, PROJ_T, 0, st>>>(dProbs, mode, th, nnRatio, linkStereo, rotHist);
+    *launches += 2;
     return cudaGetLastError();
 }

@@ -59,10 +59,17 @@ struct ProjProblem {
     int32_t* assign;           // n
     int32_t* choice;           // nq
     int* nmatches;
-    int* scratch;              // 4 * 3072 + n + 4 * nq ints
+    // device scratch
+    uint32_t* sorted;          // n grid keys (side, cell) << 16 | index, ascending
+    int* cellStart;            // 2 * 3072
+    int* cellEnd;              // 2 * 3072
+    unsigned long long* cand;  // nq * PROJ_K smallest candidate keys per window
+    unsigned long long* limit; // nq: keys below it are a correct prefix of the window's sorted candidates
+    int* scratch;              // n + 4 * nq ints
 };
-cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int mode, int th,
-                                              float nnRatio, int linkStereo, int rotHist, long long* launches);
+#define PROJ_K 8
+cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int mode,
+                                              int th, float nnRatio, int linkStereo, int rotHist, long long* launches);
 
 // SearchForTriangulation with Kannala-Brandt cameras: cameras [0] = mpCamera, [1] = mpCamera2 of each
 // keyframe, relative poses {ll, lr, rl, rr} (x1 = R12 x2 + t12), NLeft of both keyframes (-1: one camera).

@@ -517,7 +517,9 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     const size_t oR2L = stage_take(u, sizeof(int32_t) * std::max(nr, 1)), oQ = stage_take(u, sizeof(ProjQueryDev) * (size_t)nq);
     const size_t oProb = stage_take(u, sizeof(ProjProblem));
     const size_t inBytes = u;
-    const size_t oScr = stage_take(u, sizeof(int) * (4 * 3072 + (size_t)n + 4 * (size_t)nq));
+    const size_t oSorted = stage_take(u, sizeof(uint32_t) * n), oCell = stage_take(u, sizeof(int) * 4 * 3072);
+    const size_t oCand = stage_take(u, sizeof(unsigned long long) * (size_t)nq * PROJ_K), oLim = stage_take(u, sizeof(unsigned long long) * (size_t)nq);
+    const size_t oScr = stage_take(u, sizeof(int) * ((size_t)n + 4 * (size_t)nq));
     const size_t oOut = stage_take(u, 0);
     const size_t oAsg = stage_take(u, sizeof(int32_t) * n), oCh = stage_take(u, sizeof(int32_t) * (size_t)nq), oCnt = stage_take(u, 4);
     int st = ensure_stage(m, u);
@@ -552,10 +554,15 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     P.assign = reinterpret_cast<int32_t*>(ds + oAsg);
     P.choice = reinterpret_cast<int32_t*>(ds + oCh);
     P.nmatches = reinterpret_cast<int*>(ds + oCnt);
+    P.sorted = reinterpret_cast<uint32_t*>(ds + oSorted);
+    P.cellStart = reinterpret_cast<int*>(ds + oCell);
+    P.cellEnd = P.cellStart + 2 * 3072;
+    P.cand = reinterpret_cast<unsigned long long*>(ds + oCand);
+    P.limit = reinterpret_cast<unsigned long long*>(ds + oLim);
     P.scratch = reinterpret_cast<int*>(ds + oScr);
     memcpy(hs + oProb, &P, sizeof(P));
     CK(cudaMemcpyAsync(ds, hs, inBytes, cudaMemcpyHostToDevice, m->stream));
-    CK(orbfe_launch_search_by_projection(m->stream, reinterpret_cast<const ProjProblem*>(ds + oProb), 1, n, mode, th, m->nnRatio,
+    CK(orbfe_launch_search_by_projection(m->stream, reinterpret_cast<const ProjProblem*>(ds + oProb), 1, n, nq, mode, th, m->nnRatio,
                                          link_stereo ? 1 : 0, (rot_hist && m->checkOri) ? 1 : 0, &m->launches));
     CK(cudaMemcpyAsync(hs + oOut, ds + oOut, u - oOut, cudaMemcpyDeviceToHost, m->stream));
     CK(cudaStreamSynchronize(m->stream));
