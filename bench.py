@@ -376,6 +376,7 @@ def run_orbfe(args):
         g.build()
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
         dist.barrier()
     import orbfe
