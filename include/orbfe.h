@@ -289,6 +289,13 @@ int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_side* A, co
                                    const orbfe_kb8_epipolar* geo, int only_stereo, int coarse, int32_t* matches12,
                                    float* points12);
 
+/* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:349-423) for `npoints` map points at
+ * once: point p's observed descriptors are rows offsets[p] .. offsets[p+1] of desc (in the order the reference
+ * collects them, MapPoint.cc:368-383).  best[p] = row (relative to offsets[p]) with the least median Hamming
+ * distance to all of the point's rows (median = sorted[0.5 * (n - 1)], first row wins ties); -1 for a point
+ * without observations.  Returns 0 or a negative status. */
+int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best);
+
 /* ---- projection-guided searches -----------------------------------------------------
  * The Frame being searched: what Frame::GetFeaturesInArea (Frame.cc:640-706) and the SearchByProjection loops
  * read of it. */

@@ -262,4 +262,7 @@ int orbref_features_in_area(const KeyPoint* kps, int n, int nleft, float minX, f
     std::copy(v.begin(), v.end(), out);
     return (int)v.size();
 }
+void orbref_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best) {
+    for (int p = 0; p < npoints; ++p) best[p] = distinctiveDescriptor(desc + 32 * (size_t)offsets[p], offsets[p + 1] - offsets[p]);
+}
 }

@@ -340,6 +340,28 @@ int searchForTriangulationKb8(const KeyPoint* kpA, const uint8_t* descA, int nA,
     return nmatches;
 }
 
+// MapPoint.cc:388-417
+int distinctiveDescriptor(const uint8_t* desc, int n) {
+    if (n <= 0) return -1;
+    std::vector<float> D((size_t)n * n);
+    for (int i = 0; i < n; i++) {
+        D[(size_t)i * n + i] = 0;
+        for (int j = i + 1; j < n; j++) {
+            const int distij = descriptorDistanceSwar(desc + 32 * (size_t)i, desc + 32 * (size_t)j);
+            D[(size_t)i * n + j] = (float)distij;
+            D[(size_t)j * n + i] = (float)distij;
+        }
+    }
+    int BestMedian = 0x7fffffff, BestIdx = 0;
+    for (int i = 0; i < n; i++) {
+        std::vector<int> vDists(D.begin() + (size_t)i * n, D.begin() + (size_t)(i + 1) * n);
+        std::sort(vDists.begin(), vDists.end());
+        const int median = vDists[(size_t)(0.5 * (n - 1))];
+        if (median < BestMedian) { BestMedian = median; BestIdx = i; }
+    }
+    return BestIdx;
+}
+
 // Frame.cc:1134-1141
 void knn2RatioMatch(const uint8_t* q, int nq, const uint8_t* t, int nt, double ratio, int32_t* match) {
     std::vector<int32_t> idx(2 * (size_t)nq), dist(2 * (size_t)nq);

@@ -84,6 +84,11 @@ int searchForTriangulation(const KeyPoint* kpA, const uint8_t* descA, int nA, co
                            const FeatureVectorCsr& fvB, const uint8_t* hasMpB, const float* uRightB, const float* sigma2B,
                            const float* scaleB, const TriParams& p, int32_t* matches12);
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423): among the n observed descriptors of a map
+// point, the one with the least median Hamming distance to all of them (median = sorted row [0.5 * (n - 1)], the
+// row includes the 0 to itself; the first index wins ties).  Returns the index, -1 for n == 0.
+int distinctiveDescriptor(const uint8_t* desc, int n);
+
 // Frame::ComputeStereoFishEyeMatches up to the descriptor test (Frame.cc:1134-1141): 2-NN brute force
 // (BFMatcher NORM_HAMMING, ties to the lowest train index) + Lowe ratio d0 < 0.7 * d1.
 // match[nq] = train index or -1.

@@ -103,6 +103,11 @@ def main():
                             m12=m12, n=n, points=pts, margins=margins)
         print(name, n, "pairs; knife-edge rows:", int((margins < 1e-3).sum()))
 
+    d, off = mc.distinctive_inputs()
+    best = np.array([mp.compute_distinctive_descriptor(d[off[i]:off[i + 1]]) for i in range(len(off) - 1)], np.int32)
+    np.savez_compressed(os.path.join(out, "match_distinctive.npz"), in_crc=crc(d, off), best=best)
+    print("distinctive", len(best), "map points,", len(d), "observations")
+
     q, t = mc.knn_inputs()
     match, idx, dist = mp.fisheye_lapping_match(q, t)
     np.savez_compressed(os.path.join(out, "match_knn_ties.npz"), in_crc=crc(q, t), match=match, idx=idx, dist=dist)

@@ -505,3 +505,22 @@ def compute_stereo_fisheye_matches(cam1, cam2, kpL, descL, mono_left, kpR, descR
             l2r[iL], r2l[iR], depth[iL], p3d[iL] = iR, iL, d, p
             n += 1
     return l2r, r2l, depth, p3d, margins, n
+
+
+def compute_distinctive_descriptor(descs):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:388-417) on the list of observed descriptors.
+    Returns the index of the chosen one (-1 for an empty list)."""
+    N = len(descs)
+    if N == 0:
+        return -1
+    D = np.zeros((N, N), np.float32)
+    for i in range(N):
+        for j in range(i + 1, N):
+            D[i, j] = D[j, i] = cv2.norm(descs[i], descs[j], cv2.NORM_HAMMING)
+    best_median, best_idx = 2 ** 31 - 1, 0
+    for i in range(N):
+        v = sorted(int(x) for x in D[i])
+        median = v[int(0.5 * (N - 1))]
+        if median < best_median:
+            best_median, best_idx = median, i
+    return best_idx

@@ -136,6 +136,64 @@ cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStr
     return cudaGetLastError();
 }
 
+// MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:388-417): one warp per map point.  For every row i the
+// lanes evaluate the Hamming distances to all rows into a 257-bin histogram (distances are 0..256), the median is
+// the bin where the running count passes k = (n - 1) / 2; the row with the smallest median wins, first row on ties.
+#define DIST_WARPS 4
+__global__ void __launch_bounds__(DIST_WARPS * 32) k_distinctive(const uint8_t* __restrict__ desc, const int32_t* __restrict__ offsets,
+                                                                 int npoints, int32_t* __restrict__ best) {
+    __shared__ int hist[DIST_WARPS][288];
+    const int w = threadIdx.x >> 5, lane = threadIdx.x & 31, p = blockIdx.x * DIST_WARPS + w;
+    if (p >= npoints) return;
+    const int o = offsets[p], n = offsets[p + 1] - o;
+    if (n <= 0) { if (lane == 0) best[p] = -1; return; }
+    const uint4* D = reinterpret_cast<const uint4*>(desc + 32ll * o);
+    const int k = (int)(0.5 * (n - 1));
+    int bestMedian = 0x7fffffff, bestIdx = 0;
+    int* h = hist[w];
+    for (int i = 0; i < n; ++i) {
+        for (int b = lane; b < 288; b += 32) h[b] = 0;
+        __syncwarp();
+        const uint4 a0 = __ldg(D + 2 * i), a1 = __ldg(D + 2 * i + 1);
+        for (int j = lane; j < n; j += 32) {
+            const uint4 b0 = __ldg(D + 2 * j), b1 = __ldg(D + 2 * j + 1);
+            const int d = __popc(a0.x ^ b0.x) + __popc(a0.y ^ b0.y) + __popc(a0.z ^ b0.z) + __popc(a0.w ^ b0.w) +
+                          __popc(a1.x ^ b1.x) + __popc(a1.y ^ b1.y) + __popc(a1.z ^ b1.z) + __popc(a1.w ^ b1.w);
+            atomicAdd(&h[d], 1);
+        }
+        __syncwarp();
+        // lane owns bins 9*lane .. 9*lane+8; exclusive prefix of the lane totals, then the bin where count passes k
+        int c[9], tot = 0;
+#pragma unroll
+        for (int b = 0; b < 9; ++b) { c[b] = h[9 * lane + b]; tot += c[b]; }
+        int incl = tot;
+#pragma unroll
+        for (int s = 1; s < 32; s <<= 1) {
+            const int y = __shfl_up_sync(0xffffffffu, incl, s);
+            if (lane >= s) incl += y;
+        }
+        int run = incl - tot, med = 0x7fffffff;
+#pragma unroll
+        for (int b = 0; b < 9; ++b) {
+            if (med == 0x7fffffff && run <= k && k < run + c[b]) med = 9 * lane + b;
+            run += c[b];
+        }
+#pragma unroll
+        for (int s = 16; s > 0; s >>= 1) med = min(med, __shfl_xor_sync(0xffffffffu, med, s));
+        if (med < bestMedian) { bestMedian = med; bestIdx = i; }
+        __syncwarp();
+    }
+    if (lane == 0) best[p] = bestIdx;
+}
+
+cudaError_t orbfe_launch_distinctive(cudaStream_t st, const uint8_t* dDesc, const int32_t* dOffsets, int npoints, int32_t* dBest,
+                                     long long* launches) {
+    if (npoints <= 0) return cudaSuccess;
+    k_distinctive<<<(npoints + DIST_WARPS - 1) / DIST_WARPS, DIST_WARPS * 32, 0, st>>>(dDesc, dOffsets, npoints, dBest);
+    ++*launches;
+    return cudaGetLastError();
+}
+
 cudaError_t orbfe_launch_ratio_filter(cudaStream_t st, const int32_t* dIdx2, const int32_t* dDist2, int nq, double ratio,
                                       int32_t* dMatch, int* dCount, long long* launches) {
     if (nq <= 0) return cudaSuccess;

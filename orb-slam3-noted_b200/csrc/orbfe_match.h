@@ -36,6 +36,9 @@ struct TriGeo {
     float sigma2B[ORBFE_MAX_LEVELS], scaleB[ORBFE_MAX_LEVELS];
 };
 
+cudaError_t orbfe_launch_distinctive(cudaStream_t st, const uint8_t* dDesc, const int32_t* dOffsets, int npoints, int32_t* dBest,
+                                     long long* launches);
+
 // ---- projection-guided window searches (k_project.cu) ----
 struct ProjQueryDev {          // = orbfe_proj_query (include/orbfe.h), 64 bytes
     float u, v, r, ur, angle;

@@ -493,6 +493,35 @@ extern "C" int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_
     return *reinterpret_cast<int*>(m->hStage + oCnt);
 }
 
+// ---- distinctive descriptors ----------------------------------------------------------------------------
+extern "C" int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* offsets, int npoints,
+                                             int32_t* best) {
+    if (!m || npoints < 0 || (npoints > 0 && (!offsets || !best))) return ORBFE_ERR_BAD_ARGUMENT;
+    if (npoints == 0) return ORBFE_OK;
+    if (offsets[0] != 0) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int p = 0; p < npoints; ++p)
+        if (offsets[p + 1] < offsets[p]) return ORBFE_ERR_BAD_ARGUMENT;
+    const int total = offsets[npoints];
+    if (total > 0 && !desc) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(m->device));
+    size_t u = 0;
+    const size_t oD = stage_take(u, 32 * (size_t)std::max(total, 1)), oOff = stage_take(u, sizeof(int32_t) * ((size_t)npoints + 1));
+    const size_t inBytes = u;
+    const size_t oBest = stage_take(u, sizeof(int32_t) * (size_t)npoints);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));
+    if (total > 0) memcpy(m->hStage + oD, desc, 32 * (size_t)total);
+    memcpy(m->hStage + oOff, offsets, sizeof(int32_t) * ((size_t)npoints + 1));
+    CK(cudaMemcpyAsync(m->dStage, m->hStage, inBytes, cudaMemcpyHostToDevice, m->stream));
+    CK(orbfe_launch_distinctive(m->stream, m->dStage + oD, reinterpret_cast<const int32_t*>(m->dStage + oOff), npoints,
+                                reinterpret_cast<int32_t*>(m->dStage + oBest), &m->launches));
+    CK(cudaMemcpyAsync(m->hStage + oBest, m->dStage + oBest, sizeof(int32_t) * (size_t)npoints, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(best, m->hStage + oBest, sizeof(int32_t) * (size_t)npoints);
+    return ORBFE_OK;
+}
+
 // ---- projection-guided window searches ------------------------------------------------------------------
 extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_frame* F, const orbfe_proj_query* queries, int nq,
                                           int mode, int th, int link_stereo, int rot_hist, int32_t* assign, int32_t* choice) {

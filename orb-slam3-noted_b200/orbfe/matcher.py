@@ -246,6 +246,18 @@ class ORBmatcher:
         i1 = np.nonzero(m12 >= 0)[0]
         return np.stack([i1, m12[i1]], axis=1).astype(np.int64), n, m12
 
+    def ComputeDistinctiveDescriptors(self, desc, offsets):
+        """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:349-423) for many map points: rows
+        offsets[p]..offsets[p+1] of desc are point p's observed descriptors.  Returns the chosen row per point
+        (relative to offsets[p]; -1 without observations)."""
+        d = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        off = np.ascontiguousarray(offsets, np.int32)
+        best = np.full(max(len(off) - 1, 1), -1, np.int32)
+        st = self._lib.orbfe_distinctive_descriptors(self._m, _p(d), _p(off), len(off) - 1, _p(best))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_distinctive_descriptors")
+        return best[:len(off) - 1]
+
     def search_by_projection(self, F, queries, mode, th=TH_HIGH, link_stereo=False, rot_hist=False):
         """The window-search loop of ORBmatcher::SearchByProjection (ORBmatcher.cc:44-236, :2173-2389, :2391-2510) on a
         projection.GridFrame and an array of projection.PROJ_QUERY_DTYPE records (see orbfe/projection.py for how

@@ -250,3 +250,25 @@ def tri_kb8_inputs(name):
                 mp2=orbfe.synth.mask(seed * 7 + 2, len(d2), 40), cam_a=cam, cam_b=cam, nleft_a=nleft1, nleft_b=nleft2, R12=R12,
                 t12=t12, ep=(float(np.float32(ep[0])), float(np.float32(ep[1]))), check_ori=ori, only_stereo=False,
                 coarse=coarse, nlevels=nlev)
+
+
+def distinctive_inputs(seed=5200, npoints=400):
+    """Observations of `npoints` map points: 0..70 descriptors each (noisy copies of a base descriptor, a few
+    outliers, exact duplicates so that medians tie).  Returns (desc (total, 32), offsets (npoints + 1))."""
+    rng = np.random.default_rng(seed)
+    counts = rng.integers(0, 12, npoints)
+    counts[rng.random(npoints) < 0.15] = rng.integers(12, 71, int((rng.random(npoints) < 0.15).sum()) or 1)[0]
+    counts[:6] = [0, 1, 2, 3, 64, 33]
+    rows = []
+    for c in counts:
+        base = rng.integers(0, 256, 32, dtype=np.uint8)
+        for k in range(int(c)):
+            d = base.copy()
+            nb = int(rng.integers(0, 40)) if rng.random() < 0.85 else 128
+            for b in rng.choice(256, nb, replace=False):
+                d[b >> 3] ^= 1 << (b & 7)
+            if k and rng.random() < 0.1:
+                d = rows[-1].copy()
+            rows.append(d)
+    desc = np.stack(rows) if rows else np.zeros((0, 32), np.uint8)
+    return desc, np.concatenate([[0], np.cumsum(counts)]).astype(np.int32)

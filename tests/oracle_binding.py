@@ -299,3 +299,12 @@ def features_in_area(F, x, y, r, min_level, max_level, right):
     n = L_.orbref_features_in_area(_p(F.kps), F.n, F.nleft, float(F.min_x), float(F.min_y), float(F.grid_w_inv),
                                    float(F.grid_h_inv), float(x), float(y), float(r), min_level, max_level, int(right), _p(out))
     return out[:n]
+
+
+def distinctive_descriptors(desc, offsets):
+    desc, offsets = np.ascontiguousarray(desc, np.uint8), np.ascontiguousarray(offsets, np.int32)
+    best = np.zeros(max(len(offsets) - 1, 1), np.int32)
+    L_ = lib()
+    L_.orbref_distinctive_descriptors.argtypes = [_P, _P, _I, _P]
+    L_.orbref_distinctive_descriptors(_p(desc), _p(offsets), len(offsets) - 1, _p(best))
+    return best[:len(offsets) - 1]

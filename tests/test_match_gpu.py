@@ -308,3 +308,13 @@ def test_search_for_triangulation_kb8(name):
     assert m.SearchForTriangulationKB8(c["d1"], c["fv1"], c["mp1"], c["k1"], c["d2"], c["fv2"], c["mp2"], c["k2"], c["cam_a"],
                                        c["cam_b"], c["nleft_a"], c["nleft_b"], c["R12"], c["t12"], c["ep"], s2, s2, sc, True,
                                        c["coarse"])[1] == 0
+
+
+def test_distinctive_descriptors():
+    """MapPoint::ComputeDistinctiveDescriptors batched over 400 map points (0..64 observations, tied medians)."""
+    d, off = mc.distinctive_inputs()
+    best = orbfe.ORBmatcher().ComputeDistinctiveDescriptors(d, off)
+    assert np.array_equal(best, gold("distinctive")["best"]) and np.array_equal(best, ob.distinctive_descriptors(d, off))
+    d2, off2 = mc.distinctive_inputs(5201, 3000)
+    assert np.array_equal(orbfe.ORBmatcher().ComputeDistinctiveDescriptors(d2, off2), ob.distinctive_descriptors(d2, off2))
+    assert len(orbfe.ORBmatcher().ComputeDistinctiveDescriptors(d[:0], off[:1])) == 0

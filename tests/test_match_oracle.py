@@ -192,3 +192,12 @@ def test_kb8_project_unproject_roundtrip():
         uv = np.zeros(2, np.float32)
         L.orbref_kb8_project(ob._p(cam), ob._p(ray), ob._p(uv))
         assert abs(uv[0] - u) < 2e-3 and abs(uv[1] - v) < 2e-3
+
+
+def test_distinctive_descriptors_golden():
+    d, off = mc.distinctive_inputs()
+    g = gold("distinctive")
+    assert crc(d, off) == int(g["in_crc"])
+    best = ob.distinctive_descriptors(d, off)
+    assert np.array_equal(best, g["best"])
+    assert best[0] == -1 and best[1] == 0 and (np.diff(off)[best < 0] == 0).all()
