@@ -203,6 +203,14 @@ int orbfe_fisheye_stereo_match(orbfe_matcher* m, const orbfe_keypoint* kps_left,
                                const float* sigma2, int nlevels, int32_t* left_to_right, int32_t* right_to_left, float* depth,
                                float* p3d);
 
+/* Colour input.  Tracking::GrabImageMonocular / Stereo / RGBD convert their input with
+ * cv::cvtColor(RGB2GRAY | BGR2GRAY | RGBA2GRAY | BGRA2GRAY) before extraction (Tracking.cc:1233-1258,
+ * 1325-1338); with a colour format set, orbfe_extract* take the interleaved colour image (stride in bytes) and the
+ * conversion — OpenCV's 8-bit fixed point, (R * 9798 + G * 19235 + B * 3735 + 16384) >> 15 — runs inside the
+ * pyramid's level-0 kernel, so no grey image is ever stored and level 0 of the pyramid equals mImGray. */
+enum { ORBFE_FORMAT_GRAY8 = 0, ORBFE_FORMAT_RGB8 = 1, ORBFE_FORMAT_BGR8 = 2, ORBFE_FORMAT_RGBA8 = 3, ORBFE_FORMAT_BGRA8 = 4 };
+int orbfe_set_input_format(orbfe_handle* h, int format);
+
 /* Frame::ComputeStereoMatches (Frame.cc:794-964), "SearchStereo": rectified-stereo row-band search
  * (Hamming < 75 among right keypoints whose row band covers the left keypoint, octave within +-1,
  * disparity in [0, bf/b]), 11x11 SAD refinement over +-5 px on the pyramid level of the left

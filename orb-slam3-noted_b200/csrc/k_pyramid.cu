@@ -47,6 +47,33 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const uint8_t* __restrict__ 
     reinterpret_cast<uint4*>(dst)[chunk] = v;
 }
 
+// Colour input: cv::cvtColor(..., RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of OpenCV 4.x for 8-bit images,
+// (R * 9798 + G * 19235 + B * 3735 + (1 << 14)) >> 15, fused with the border copy.  One thread = one 32-bit word of
+// a bordered row; BPP = 3 or 4, rFirst = the first channel is red.
+template <int BPP>
+__global__ void __launch_bounds__(128) k_pyr_level0_color(const uint8_t* __restrict__ in, long long stride, long long frameStride,
+                                                          uint8_t* __restrict__ out, LevelGeom g, int frame0, int rFirst) {
+    const int word = blockIdx.x * blockDim.x + threadIdx.x;
+    const int row = blockIdx.y;
+    if (word * 4 >= g.pitch) return;
+    const int y = reflect101(row - ORBFE_EDGE, g.h);
+    const uint8_t* src = in + (long long)blockIdx.z * frameStride + (long long)y * stride;
+    const int x0 = word * 4 - ORBFE_XO;
+    const int cr = rFirst ? 9798 : 3735, cb = rFirst ? 3735 : 9798;
+    uint32_t v = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = x0 + k;
+        if (x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE) {
+            const uint8_t* p = src + (long long)reflect101(x, g.w) * BPP;
+            const int grey = ((int)__ldg(p) * cr + (int)__ldg(p + 1) * 19235 + (int)__ldg(p + 2) * cb + (1 << 14)) >> 15;
+            v |= (uint32_t)grey << (8 * k);
+        }
+    }
+    uint8_t* dst = out + g.base + (long long)(frame0 + blockIdx.z) * g.plane + (long long)row * g.pitch;
+    reinterpret_cast<uint32_t*>(dst)[word] = v;
+}
+
 // gs = source level geometry, gd = destination level geometry.
 __global__ void __launch_bounds__(128) k_pyr_resize(uint8_t* __restrict__ pyr, LevelGeom gs, LevelGeom gd,
                                                     const ResizeTap* __restrict__ taps, int frame0) {
@@ -137,8 +164,17 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int fr
     const int nl = h->p.nlevels;
     {
         const LevelGeom& g = h->geom[0];
-        dim3 grid(((g.pitch >> 4) + 7) / 8, batch, (g.rows + 31) / 32);
-        k_pyr_level0<<<grid, 256, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
+        if (h->inFormat == ORBFE_FORMAT_GRAY8) {
+            dim3 grid(((g.pitch >> 4) + 7) / 8, batch, (g.rows + 31) / 32);
+            k_pyr_level0<<<grid, 256, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
+        } else {
+            dim3 grid((g.pitch / 4 + 127) / 128, g.rows, batch);
+            const int rFirst = h->inFormat == ORBFE_FORMAT_RGB8 || h->inFormat == ORBFE_FORMAT_RGBA8;
+            if (h->inFormat <= ORBFE_FORMAT_BGR8)
+                k_pyr_level0_color<3><<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
+            else
+                k_pyr_level0_color<4><<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
+        }
         h->launches++;
     }
     for (int l = 1; l < nl; ++l) {

@@ -347,6 +347,8 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     h->planCap = (int)sp.plans.size() + 32 * p.nlevels + 64;
     h->kpCapPerFrame = sp.kpPerFrame + 16 * p.nlevels;
     h->inBytes = (size_t)p.max_width * p.max_height * B;
+    h->inFormat = ORBFE_FORMAT_GRAY8;
+    h->inBpp = 1;
 #define CKC(call)                                                              \
     do {                                                                       \
         cudaError_t e_ = (call);                                               \
@@ -469,11 +471,33 @@ extern "C" const char* orbfe_stage_name(int stage) {
     return stage >= 0 && stage < ORBFE_NUM_STAGES ? names[stage] : "?";
 }
 
+// Tracking::GrabImage* (src/Tracking.cc:1233-1258, 1325-1338) converts colour input with cv::cvtColor before the
+// extractor sees it; here the conversion is fused into the level-0 kernel (k_pyramid.cu).  The staging arena of
+// the host-buffer entry points grows to bytes-per-pixel times its grey size.
+extern "C" int orbfe_set_input_format(orbfe_handle* h, int format) {
+    if (!h || format < ORBFE_FORMAT_GRAY8 || format > ORBFE_FORMAT_BGRA8) return ORBFE_ERR_BAD_ARGUMENT;
+    const int bpp = format == ORBFE_FORMAT_GRAY8 ? 1 : (format <= ORBFE_FORMAT_BGR8 ? 3 : 4);
+    CK(cudaSetDevice(h->device));
+    if (bpp > h->inBpp) {
+        CK(cudaDeviceSynchronize());
+        const size_t grey = (size_t)h->p.max_width * h->p.max_height * h->p.max_batch;
+        cudaFree(h->dIn);
+        h->dIn = nullptr;
+        CK(cudaMalloc(&h->dIn, grey * bpp));
+        h->inBytes = grey * bpp;
+        h->inBpp = bpp;
+    }
+    h->inFormat = format;
+    return ORBFE_OK;
+}
+
+static inline int format_bpp(int format) { return format == ORBFE_FORMAT_GRAY8 ? 1 : (format <= ORBFE_FORMAT_BGR8 ? 3 : 4); }
+
 extern "C" int orbfe_extract_batch_device(orbfe_handle* h, const uint8_t* d_images, int batch, int width, int height,
                                           ptrdiff_t stride, ptrdiff_t frame_stride, int lap0, int lap1) {
     if (!h) return ORBFE_ERR_BAD_ARGUMENT;
     if (!d_images || width <= 0 || height <= 0 || batch <= 0) return ORBFE_ERR_EMPTY_IMAGE;
-    if (stride < width || batch > h->p.max_batch) return batch > h->p.max_batch ? ORBFE_ERR_TOO_LARGE : ORBFE_ERR_BAD_ARGUMENT;
+    if (stride < (ptrdiff_t)width * format_bpp(h->inFormat) || batch > h->p.max_batch) return batch > h->p.max_batch ? ORBFE_ERR_TOO_LARGE : ORBFE_ERR_BAD_ARGUMENT;
     CK(cudaSetDevice(h->device));
     int st = configure_shape(h, width, height);
     if (st != ORBFE_OK) return st;
@@ -520,7 +544,9 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
                                    int* n_out, int* mono_out) {
     if (!h) return ORBFE_ERR_BAD_ARGUMENT;
     if (!images || width <= 0 || height <= 0 || batch <= 0) return ORBFE_ERR_EMPTY_IMAGE;
-    if (stride < width) return ORBFE_ERR_BAD_ARGUMENT;
+    const int bpp = format_bpp(h->inFormat);
+    const ptrdiff_t rowBytes = (ptrdiff_t)width * bpp;
+    if (stride < rowBytes) return ORBFE_ERR_BAD_ARGUMENT;
     if (batch > h->p.max_batch || width > h->p.max_width || height > h->p.max_height) return ORBFE_ERR_TOO_LARGE;
     CK(cudaSetDevice(h->device));
     int st = configure_shape(h, width, height);
@@ -546,7 +572,7 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
         }
     }
     const int kpf = h->kpPerFrame;
-    const size_t fbytes = (size_t)width * height;
+    const size_t fbytes = (size_t)rowBytes * height;
     h->lastBatch = 0;
     cudaStream_t mainStream = h->stream;
     CK(cudaEventRecord(h->evPipe[0][0], h->stream));          // copy-in / the second compute stream must not overtake earlier work
@@ -554,11 +580,11 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
     CK(cudaStreamWaitEvent(h->sAlt, h->evPipe[0][0], 0));
     for (int c = 0; c < nchunks; ++c) {
         const int f0 = bounds[c], nb = bounds[c + 1] - f0;
-        if (stride == width && frame_stride == (ptrdiff_t)fbytes) {
+        if (stride == rowBytes && frame_stride == (ptrdiff_t)fbytes) {
             CK(cudaMemcpyAsync(h->dIn + f0 * fbytes, images + f0 * fbytes, fbytes * nb, cudaMemcpyHostToDevice, h->sIn));
         } else {
             for (int b = f0; b < f0 + nb; ++b)
-                CK(cudaMemcpy2DAsync(h->dIn + b * fbytes, width, images + (size_t)b * frame_stride, stride, width, height,
+                CK(cudaMemcpy2DAsync(h->dIn + b * fbytes, rowBytes, images + (size_t)b * frame_stride, stride, rowBytes, height,
                                      cudaMemcpyHostToDevice, h->sIn));
         }
         CK(cudaEventRecord(h->evPipe[c][1], h->sIn));
@@ -567,7 +593,7 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
         cudaStream_t compute = (c & 1) ? h->sAlt : mainStream;
         CK(cudaStreamWaitEvent(compute, h->evPipe[c][1], 0));
         h->stream = compute;
-        st = enqueue_extract(h, h->dIn + f0 * fbytes, f0, nb, width, height, width, (long long)fbytes, lap0, lap1);
+        st = enqueue_extract(h, h->dIn + f0 * fbytes, f0, nb, width, height, rowBytes, (long long)fbytes, lap0, lap1);
         h->stream = mainStream;
         if (st != ORBFE_OK) return st;
         CK(cudaEventRecord(h->evPipe[c][2], compute));

@@ -95,6 +95,7 @@ struct orbfe_handle {
     int cellCap, tabCap, kpCapPerFrame;
     // device arenas
     uint8_t* dIn;           // staged input frames (host path)
+    int inFormat, inBpp;    // ORBFE_FORMAT_* of the input images; bytes per pixel the staging arena is sized for
     uint8_t* dPyr;          // pyramid arena [level][frame][rows][pitch]
     uint8_t* dBlur;         // Gaussian-blurred levels, same layout (ROI pixels only are defined)
     int blurTiles;          // k_blur tiles per frame (all levels)

@@ -65,6 +65,7 @@ def lib():
         "orbfe_synchronize": (_I, [_P]),
         "orbfe_launch_count": (C.c_longlong, [_P]),
         "orbfe_set_profiling": (_I, [_P, _I]),
+        "orbfe_set_input_format": (_I, [_P, _I]),
         "orbfe_get_stage_times": (_I, [_P, _P, C.POINTER(C.c_longlong)]),
         "orbfe_stage_name": (C.c_char_p, [_I]),
         "orbfe_strerror": (C.c_char_p, [_I]),
@@ -87,7 +88,7 @@ def exported_symbols():
     return ["orbfe_create", "orbfe_destroy", "orbfe_get_tables", "orbfe_max_keypoints", "orbfe_extract",
             "orbfe_extract_batch", "orbfe_extract_batch_device", "orbfe_device_results", "orbfe_fetch_results",
             "orbfe_get_pyramid_level", "orbfe_get_candidates", "orbfe_stream", "orbfe_synchronize",
-            "orbfe_launch_count", "orbfe_set_profiling", "orbfe_get_stage_times", "orbfe_stage_name", "orbfe_strerror", "orbfe_last_cuda_error", "orbfe_version"] + list(_matcher_proto.PROTO)
+            "orbfe_launch_count", "orbfe_set_profiling", "orbfe_set_input_format", "orbfe_get_stage_times", "orbfe_stage_name", "orbfe_strerror", "orbfe_last_cuda_error", "orbfe_version"] + list(_matcher_proto.PROTO)
 
 
 def strerror(status):

@@ -75,14 +75,29 @@ class ORBextractor:
         except Exception:
             pass
 
+    FORMATS = {"gray": 0, "rgb": 1, "bgr": 2, "rgba": 3, "bgra": 4}
+
+    def set_input_format(self, fmt):
+        """Colour input: the cv::cvtColor(..2GRAY) of Tracking::GrabImage* (Tracking.cc:1233-1258) runs inside the
+        pyramid's level-0 kernel.  fmt: "gray", "rgb", "bgr", "rgba", "bgra"."""
+        st = self._lib.orbfe_set_input_format(self._h, self.FORMATS[fmt])
+        if st < 0:
+            raise OrbfeError(st, "orbfe_set_input_format")
+        self._bpp = 1 if fmt == "gray" else 3 if fmt in ("rgb", "bgr") else 4
+
     # ---- operator()
     def __call__(self, image, mask=None, vLappingArea=(0, 0)):
         """Returns (monoIndex, keypoints, descriptors); monoIndex == -1 for an empty image, like the reference."""
         if image is None or image.size == 0:
             return -1, np.zeros(0, KEYPOINT_DTYPE), np.zeros((0, 32), np.uint8)
-        assert image.dtype == np.uint8 and image.ndim == 2, "CV_8UC1 image expected (ORBextractor.cc:1076)"
-        assert image.strides[1] == 1
-        h, w = image.shape
+        bpp = getattr(self, "_bpp", 1)
+        if bpp == 1:
+            assert image.dtype == np.uint8 and image.ndim == 2, "CV_8UC1 image expected (ORBextractor.cc:1076)"
+            assert image.strides[1] == 1
+        else:
+            assert image.dtype == np.uint8 and image.ndim == 3 and image.shape[2] == bpp and image.strides[2] == 1 and \
+                image.strides[1] == bpp
+        h, w = image.shape[:2]
         kps = np.zeros(self.cap, KEYPOINT_DTYPE)
         desc = np.zeros((self.cap, 32), np.uint8)
         n = C.c_int(0)

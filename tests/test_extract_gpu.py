@@ -122,3 +122,34 @@ def test_extract_matches_golden(path):
     ok, tot = check_against_golden(g, mono, kps, desc, pyramid_level=lambda l: ex.image_pyramid(l)[0],
                                    candidates=ex.candidates)
     assert ok >= 0.9999 * tot, (ok, tot)
+
+
+@pytest.mark.parametrize("fmt", ["rgb", "bgr", "rgba", "bgra"])
+def test_colour_input_equals_cvtcolor_then_extract(fmt):
+    """Tracking::GrabImageMonocular converts colour frames with cv::cvtColor before extraction (Tracking.cc:1233-1258);
+    with orbfe_set_input_format the conversion is fused into the pyramid.  Level 0 must equal OpenCV's grey image
+    (fixed point (R*9798 + G*19235 + B*3735 + 16384) >> 15, verified against cv2 4.13 in the oracle tests) and the
+    features must equal those of the grey path bit for bit."""
+    w, h, nf = 752, 480, 1000
+    rng = np.random.default_rng(11)
+    grey = orbfe.synth.frame(1000, w, h, 0, 0)
+    nch = 3 if fmt in ("rgb", "bgr") else 4
+    col = np.zeros((h, w, nch), np.uint8)
+    # a colourful image whose luminance keeps the synthetic frame's structure
+    col[..., 0] = np.clip(grey.astype(np.int32) + rng.integers(-30, 31, (h, w)), 0, 255)
+    col[..., 1] = grey
+    col[..., 2] = np.clip(grey.astype(np.int32) + rng.integers(-50, 51, (h, w)), 0, 255)
+    if nch == 4:
+        col[..., 3] = rng.integers(0, 256, (h, w))
+    r_idx, b_idx = (0, 2) if fmt in ("rgb", "rgba") else (2, 0)
+    R, G, B = (col[..., i].astype(np.int64) for i in (r_idx, 1, b_idx))
+    want_grey = ((R * 9798 + G * 19235 + B * 3735 + (1 << 14)) >> 15).astype(np.uint8)
+    ex = orbfe.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    mono0, k0, d0 = ex(want_grey, None, (0, 0))
+    ex.set_input_format(fmt)
+    mono1, k1, d1 = ex(col, None, (0, 0))
+    assert np.array_equal(ex.image_pyramid(0)[1], want_grey)
+    assert mono0 == mono1 and k0.tobytes() == k1.tobytes() and np.array_equal(d0, d1) and len(k0) > 900
+    ex.set_input_format("gray")
+    mono2, k2, d2 = ex(want_grey, None, (0, 0))
+    assert k2.tobytes() == k0.tobytes()

@@ -108,3 +108,15 @@ def test_cpp_oracle_equals_cv2_restatement(w, h, nf, lap, seed):
         assert np.array_equal(rk[f], kp[:, i].astype(np.float32)), f
     assert np.array_equal(rk["octave"], kp[:, 5].astype(np.int32))
     assert np.array_equal(rd, desc)
+
+
+def test_grey_conversion_formula_is_opencvs():
+    """The fixed-point luminance the CUDA level-0 kernel applies to colour input (csrc/k_pyramid.cu) == cv2.cvtColor."""
+    cv2 = pytest.importorskip("cv2")
+    rng = np.random.default_rng(3)
+    im = rng.integers(0, 256, (97, 131, 4), dtype=np.uint8)
+    f = lambda r, g, b: ((r.astype(np.int64) * 9798 + g.astype(np.int64) * 19235 + b.astype(np.int64) * 3735 + (1 << 14)) >> 15).astype(np.uint8)
+    assert np.array_equal(cv2.cvtColor(im[..., :3].copy(), cv2.COLOR_RGB2GRAY), f(im[..., 0], im[..., 1], im[..., 2]))
+    assert np.array_equal(cv2.cvtColor(im[..., :3].copy(), cv2.COLOR_BGR2GRAY), f(im[..., 2], im[..., 1], im[..., 0]))
+    assert np.array_equal(cv2.cvtColor(im, cv2.COLOR_RGBA2GRAY), f(im[..., 0], im[..., 1], im[..., 2]))
+    assert np.array_equal(cv2.cvtColor(im, cv2.COLOR_BGRA2GRAY), f(im[..., 2], im[..., 1], im[..., 0]))
