@@ -297,6 +297,13 @@ int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_side* A, co
                                    const orbfe_kb8_epipolar* geo, int only_stereo, int coarse, int32_t* matches12,
                                    float* points12);
 
+/* Frame::UndistortKeyPoints (Frame.cc:730-763): cv::undistortPoints(pts, mK, mDistCoef, I, mK) on
+ * the keypoint positions — OpenCV's five fixed-point iterations in double precision, radial (k1, k2, k3) and
+ * tangential (p1, p2) terms.  K4 = fx, fy, cx, cy; dist = k1, k2, p1, p2[, k3] (ndist 4 or 5).  dist[0] == 0
+ * copies the keypoints unchanged (:732-736).  kps_un may alias kps.  Returns 0 or a negative status. */
+int orbfe_undistort_keypoints(orbfe_matcher* m, const orbfe_keypoint* kps, int n, const float* K4, const float* dist, int ndist,
+                              orbfe_keypoint* kps_un);
+
 /* MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:349-423) for `npoints` map points at
  * once: point p's observed descriptors are rows offsets[p] .. offsets[p+1] of desc (in the order the reference
  * collects them, MapPoint.cc:368-383).  best[p] = row (relative to offsets[p]) with the least median Hamming

@@ -265,4 +265,7 @@ int orbref_features_in_area(const KeyPoint* kps, int n, int nleft, float minX, f
 void orbref_distinctive_descriptors(const uint8_t* desc, const int32_t* offsets, int npoints, int32_t* best) {
     for (int p = 0; p < npoints; ++p) best[p] = distinctiveDescriptor(desc + 32 * (size_t)offsets[p], offsets[p + 1] - offsets[p]);
 }
+void orbref_undistort_keypoints(const KeyPoint* kps, int n, const float* K4, const float* dist, int ndist, KeyPoint* out) {
+    undistortKeyPoints(kps, n, K4, dist, ndist, out);
+}
 }

@@ -340,6 +340,31 @@ int searchForTriangulationKb8(const KeyPoint* kpA, const uint8_t* descA, int nA,
     return nmatches;
 }
 
+// Frame.cc:730-763 + OpenCV's cvUndistortPointsInternal (imgproc/src/undistort.dispatch.cpp), iters = 5
+void undistortKeyPoints(const KeyPoint* kps, int n, const float K4[4], const float* dist, int ndist, KeyPoint* out) {
+    for (int i = 0; i < n; ++i) out[i] = kps[i];
+    if (ndist < 1 || dist[0] == 0.0f) return;
+    double k[5] = {0, 0, 0, 0, 0};                       // k1 k2 p1 p2 k3
+    for (int j = 0; j < ndist && j < 5; ++j) k[j] = (double)dist[j];
+    const double fx = K4[0], fy = K4[1], cx = K4[2], cy = K4[3], ifx = 1.0 / fx, ify = 1.0 / fy;
+    for (int i = 0; i < n; ++i) {
+        const double u = kps[i].x, v = kps[i].y;
+        double x = (u - cx) * ifx, y = (v - cy) * ify;
+        const double x0 = x, y0 = y;
+        for (int j = 0; j < 5; ++j) {
+            const double r2 = x * x + y * y;
+            const double icdist = (1 + ((0 * r2 + 0) * r2 + 0) * r2) / (1 + ((k[4] * r2 + k[1]) * r2 + k[0]) * r2);
+            if (icdist < 0) { x = (u - cx) * ifx; y = (v - cy) * ify; break; }
+            const double deltaX = 2 * k[2] * x * y + k[3] * (r2 + 2 * x * x) + 0 * r2 + 0 * r2 * r2;
+            const double deltaY = k[2] * (r2 + 2 * y * y) + 2 * k[3] * x * y + 0 * r2 + 0 * r2 * r2;
+            x = (x0 - deltaX) * icdist;
+            y = (y0 - deltaY) * icdist;
+        }
+        out[i].x = (float)(fx * x + cx);
+        out[i].y = (float)(fy * y + cy);
+    }
+}
+
 // MapPoint.cc:388-417
 int distinctiveDescriptor(const uint8_t* desc, int n) {
     if (n <= 0) return -1;

@@ -84,6 +84,11 @@ int searchForTriangulation(const KeyPoint* kpA, const uint8_t* descA, int nA, co
                            const FeatureVectorCsr& fvB, const uint8_t* hasMpB, const float* uRightB, const float* sigma2B,
                            const float* scaleB, const TriParams& p, int32_t* matches12);
 
+// Frame::UndistortKeyPoints (src/Frame.cc:730-763): cv::undistortPoints(mat, mat, mK, mDistCoef, cv::Mat(), mK) on
+// every keypoint position: OpenCV's 5 fixed-point iterations in double (radial k1 k2 k3 + tangential p1 p2), back
+// through K, stored as float.  dist = (k1, k2, p1, p2[, k3]); dist[0] == 0 copies the keypoints (:732-736).
+void undistortKeyPoints(const KeyPoint* kps, int n, const float K4[4], const float* dist, int ndist, KeyPoint* out);
+
 // MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423): among the n observed descriptors of a map
 // point, the one with the least median Hamming distance to all of them (median = sorted row [0.5 * (n - 1)], the
 // row includes the 0 to itself; the first index wins ties).  Returns the index, -1 for n == 0.

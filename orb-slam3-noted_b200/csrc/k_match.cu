@@ -12,6 +12,7 @@
 // second tiny kernel.  Integer-pipe (popc) bound by construction: HBM traffic is nq*32 + nt*32
 // bytes per tile pass, re-used 128 times from registers / shared memory.
 #include "orbfe_internal.h"
+#include "orbfe_match.h"
 
 #define KNN_THREADS 128
 #define KNN_TILE 128
@@ -133,6 +134,39 @@ cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStr
         k_knn2_merge<<<g2, KNN_THREADS, 0, st>>>(dPartial, dNq, nqMax, nsplit, dIdx2, dDist2);
         ++*launches;
     }
+    return cudaGetLastError();
+}
+
+// Frame::UndistortKeyPoints (src/Frame.cc:730-763) = cv::undistortPoints with P = K: thread per keypoint, OpenCV's five
+// fixed-point iterations in double, every product and sum rounded separately (no FMA contraction) so the float
+// result is bit-identical to the library's.
+__global__ void __launch_bounds__(128) k_undistort(orbfe_keypoint* __restrict__ kps, int n, const UndistortGeo g) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double u = (double)kps[i].x, v = (double)kps[i].y;
+    const double ifx = __ddiv_rn(1.0, g.fx), ify = __ddiv_rn(1.0, g.fy);
+    double x = __dmul_rn(__dsub_rn(u, g.cx), ifx), y = __dmul_rn(__dsub_rn(v, g.cy), ify);
+    const double x0 = x, y0 = y;
+    for (int j = 0; j < 5; ++j) {
+        const double xx = __dmul_rn(x, x), yy = __dmul_rn(y, y), r2 = __dadd_rn(xx, yy);
+        // (1 + ((k4*r2 + k5)*r2 + k6)*r2) with k4 = k5 = k6 = 0 is exactly 1
+        const double den = __dadd_rn(1.0, __dmul_rn(__dadd_rn(__dmul_rn(__dadd_rn(__dmul_rn(g.k3, r2), g.k2), r2), g.k1), r2));
+        const double icdist = __ddiv_rn(1.0, den);
+        if (icdist < 0) { x = x0; y = y0; break; }
+        // deltaX = 2*p1*x*y + p2*(r2 + 2*x*x);  deltaY = p1*(r2 + 2*y*y) + 2*p2*x*y   (left-to-right products)
+        const double dX = __dadd_rn(__dmul_rn(__dmul_rn(__dmul_rn(2.0, g.p1), x), y), __dmul_rn(g.p2, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, x), x))));
+        const double dY = __dadd_rn(__dmul_rn(g.p1, __dadd_rn(r2, __dmul_rn(__dmul_rn(2.0, y), y))), __dmul_rn(__dmul_rn(__dmul_rn(2.0, g.p2), x), y));
+        x = __dmul_rn(__dsub_rn(x0, dX), icdist);
+        y = __dmul_rn(__dsub_rn(y0, dY), icdist);
+    }
+    kps[i].x = (float)__dadd_rn(__dmul_rn(g.fx, x), g.cx);
+    kps[i].y = (float)__dadd_rn(__dmul_rn(g.fy, y), g.cy);
+}
+
+cudaError_t orbfe_launch_undistort(cudaStream_t st, orbfe_keypoint* dKps, int n, const UndistortGeo& g, long long* launches) {
+    if (n <= 0) return cudaSuccess;
+    k_undistort<<<(n + 127) / 128, 128, 0, st>>>(dKps, n, g);
+    ++*launches;
     return cudaGetLastError();
 }
 

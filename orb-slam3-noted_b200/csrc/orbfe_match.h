@@ -36,6 +36,8 @@ struct TriGeo {
     float sigma2B[ORBFE_MAX_LEVELS], scaleB[ORBFE_MAX_LEVELS];
 };
 
+struct UndistortGeo { double fx, fy, cx, cy, k1, k2, p1, p2, k3; };
+cudaError_t orbfe_launch_undistort(cudaStream_t st, orbfe_keypoint* dKps, int n, const UndistortGeo& g, long long* launches);
 cudaError_t orbfe_launch_distinctive(cudaStream_t st, const uint8_t* dDesc, const int32_t* dOffsets, int npoints, int32_t* dBest,
                                      long long* launches);
 

@@ -493,6 +493,33 @@ extern "C" int orbfe_search_triangulation_kb8(orbfe_matcher* m, const orbfe_bow_
     return *reinterpret_cast<int*>(m->hStage + oCnt);
 }
 
+// ---- Frame::UndistortKeyPoints ---------------------------------------------------------------------------
+extern "C" int orbfe_undistort_keypoints(orbfe_matcher* m, const orbfe_keypoint* kps, int n, const float* K4, const float* dist,
+                                         int ndist, orbfe_keypoint* kps_un) {
+    if (!m || n < 0 || !K4 || !dist || ndist < 4 || ndist > 5 || (n > 0 && (!kps || !kps_un))) return ORBFE_ERR_BAD_ARGUMENT;
+    if (n == 0) return ORBFE_OK;
+    if (dist[0] == 0.0f) {                                   // Frame.cc:732-736: no distortion, plain copy
+        if (kps_un != kps) memmove(kps_un, kps, sizeof(orbfe_keypoint) * (size_t)n);
+        return ORBFE_OK;
+    }
+    CK(cudaSetDevice(m->device));
+    size_t u = 0;
+    const size_t oK = stage_take(u, sizeof(orbfe_keypoint) * (size_t)n);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(m->hStage + oK, kps, sizeof(orbfe_keypoint) * (size_t)n);
+    CK(cudaMemcpyAsync(m->dStage + oK, m->hStage + oK, sizeof(orbfe_keypoint) * (size_t)n, cudaMemcpyHostToDevice, m->stream));
+    UndistortGeo g;
+    g.fx = K4[0]; g.fy = K4[1]; g.cx = K4[2]; g.cy = K4[3];
+    g.k1 = dist[0]; g.k2 = dist[1]; g.p1 = dist[2]; g.p2 = dist[3]; g.k3 = ndist > 4 ? dist[4] : 0.0;
+    CK(orbfe_launch_undistort(m->stream, reinterpret_cast<orbfe_keypoint*>(m->dStage + oK), n, g, &m->launches));
+    CK(cudaMemcpyAsync(m->hStage + oK, m->dStage + oK, sizeof(orbfe_keypoint) * (size_t)n, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(kps_un, m->hStage + oK, sizeof(orbfe_keypoint) * (size_t)n);
+    return ORBFE_OK;
+}
+
 // ---- distinctive descriptors ----------------------------------------------------------------------------
 extern "C" int orbfe_distinctive_descriptors(orbfe_matcher* m, const uint8_t* desc, const int32_t* offsets, int npoints,
                                              int32_t* best) {

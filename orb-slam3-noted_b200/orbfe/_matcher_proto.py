@@ -32,6 +32,7 @@ class GridFrameC(C.Structure):
 
 
 PROTO = {
+    "orbfe_undistort_keypoints": (_I, [_P, _P, _I, _P, _P, _I, _P]),
     "orbfe_distinctive_descriptors": (_I, [_P, _P, _P, _I, _P]),
     "orbfe_search_by_projection": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P]),
     "orbfe_vocabulary_create": (_I, [_I, _I, _I, _I, _I, _P, _P, _P, _P, _I, C.POINTER(_P)]),

@@ -246,6 +246,16 @@ class ORBmatcher:
         i1 = np.nonzero(m12 >= 0)[0]
         return np.stack([i1, m12[i1]], axis=1).astype(np.int64), n, m12
 
+    def UndistortKeyPoints(self, kps, K4, dist):
+        """Frame::UndistortKeyPoints (Frame.cc:730-763).  K4 = (fx, fy, cx, cy), dist = (k1, k2, p1, p2[, k3])."""
+        k = np.ascontiguousarray(kps, KEYPOINT_DTYPE)
+        K4, dist = np.ascontiguousarray(K4, np.float32), np.ascontiguousarray(dist, np.float32)
+        out = np.zeros_like(k)
+        st = self._lib.orbfe_undistort_keypoints(self._m, _p(k), len(k), _p(K4), _p(dist), len(dist), _p(out))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_undistort_keypoints")
+        return out
+
     def ComputeDistinctiveDescriptors(self, desc, offsets):
         """MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:349-423) for many map points: rows
         offsets[p]..offsets[p+1] of desc are point p's observed descriptors.  Returns the chosen row per point

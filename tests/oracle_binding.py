@@ -308,3 +308,13 @@ def distinctive_descriptors(desc, offsets):
     L_.orbref_distinctive_descriptors.argtypes = [_P, _P, _I, _P]
     L_.orbref_distinctive_descriptors(_p(desc), _p(offsets), len(offsets) - 1, _p(best))
     return best[:len(offsets) - 1]
+
+
+def undistort_keypoints(kps, K4, dist):
+    kps = np.ascontiguousarray(kps)
+    K4, dist = np.ascontiguousarray(K4, np.float32), np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(kps)
+    L_ = lib()
+    L_.orbref_undistort_keypoints.argtypes = [_P, _I, _P, _P, _I, _P]
+    L_.orbref_undistort_keypoints(_p(kps), len(kps), _p(K4), _p(dist), len(dist), _p(out))
+    return out

@@ -318,3 +318,13 @@ def test_distinctive_descriptors():
     d2, off2 = mc.distinctive_inputs(5201, 3000)
     assert np.array_equal(orbfe.ORBmatcher().ComputeDistinctiveDescriptors(d2, off2), ob.distinctive_descriptors(d2, off2))
     assert len(orbfe.ORBmatcher().ComputeDistinctiveDescriptors(d[:0], off[:1])) == 0
+
+
+def test_undistort_keypoints():
+    """Frame::UndistortKeyPoints on the GPU == the oracle (itself bit-identical to cv2.undistortPoints)."""
+    from test_oracle_vs_cv2 import UND_CASES, UND_K, und_points
+    k = und_points()
+    m = orbfe.ORBmatcher()
+    for D in UND_CASES:
+        assert m.UndistortKeyPoints(k, UND_K, D).tobytes() == ob.undistort_keypoints(k, UND_K, D).tobytes()
+    assert len(m.UndistortKeyPoints(k[:0], UND_K, UND_CASES[0])) == 0

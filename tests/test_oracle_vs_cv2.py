@@ -120,3 +120,36 @@ def test_grey_conversion_formula_is_opencvs():
     assert np.array_equal(cv2.cvtColor(im[..., :3].copy(), cv2.COLOR_BGR2GRAY), f(im[..., 2], im[..., 1], im[..., 0]))
     assert np.array_equal(cv2.cvtColor(im, cv2.COLOR_RGBA2GRAY), f(im[..., 0], im[..., 1], im[..., 2]))
     assert np.array_equal(cv2.cvtColor(im, cv2.COLOR_BGRA2GRAY), f(im[..., 2], im[..., 1], im[..., 0]))
+
+
+# EuRoC cam0 (Examples/Monocular/EuRoC.yaml:9-17) and a 5-coefficient set
+UND_K = np.array([458.654, 457.296, 367.215, 248.375], np.float32)
+UND_CASES = [np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], np.float32),
+             np.array([-0.2917, 0.08228, 5.333e-05, -1.578e-04, 0.01], np.float32),
+             np.array([0.0, 0.1, 0.001, 0.001], np.float32)]
+
+
+def und_points(n=3000):
+    rng = np.random.default_rng(9)
+    k = np.zeros(n, orbfe.KEYPOINT_DTYPE)
+    k["x"], k["y"] = rng.uniform(0, 752, n).astype(np.float32), rng.uniform(0, 480, n).astype(np.float32)
+    k["octave"], k["angle"], k["size"] = rng.integers(0, 8, n), rng.uniform(0, 360, n), 31
+    return k
+
+
+@pytest.mark.parametrize("ci", range(len(UND_CASES)))
+def test_undistort_keypoints_equals_cv2(ci):
+    """Frame::UndistortKeyPoints = cv::undistortPoints(pts, K, D, I, K): the oracle's double-precision restatement
+    is bit-identical to the library on the float32 outputs."""
+    D = UND_CASES[ci]
+    k = und_points()
+    out = ob.undistort_keypoints(k, UND_K, D)
+    if D[0] == 0:
+        assert out.tobytes() == k.tobytes()        # Frame.cc:732-736
+        return
+    Kmat = np.array([[UND_K[0], 0, UND_K[2]], [0, UND_K[1], UND_K[3]], [0, 0, 1]], np.float32)
+    pts = np.stack([k["x"], k["y"]], 1).reshape(-1, 1, 2).copy()
+    want = cv2.undistortPoints(pts, Kmat, D, None, Kmat).reshape(-1, 2)
+    assert np.array_equal(out["x"], want[:, 0]) and np.array_equal(out["y"], want[:, 1])
+    assert np.array_equal(out["octave"], k["octave"]) and np.array_equal(out["angle"], k["angle"])
+    assert np.abs(out["x"] - k["x"]).max() > 1.0
