@@ -146,6 +146,37 @@ public:
         status_ = n < 0 ? n : ORBFE_OK;
         return n < 0 ? 0 : n;
     }
+    // The window-search loop of SearchByProjection (ORBmatcher.cc:44-236, :2173-2389, :2391-2510); the caller keeps
+    // the reference's projection lines and emits one orbfe_proj_query per GetFeaturesInArea call.
+    // assign[i]: index of the window whose MapPoint lands in mvpMapPoints[i], -1 untouched, -2 set to NULL.
+    int SearchByProjectionWindows(const orbfe_grid_frame& F, const std::vector<orbfe_proj_query>& windows, int mode, int th,
+                                  bool linkStereo, bool rotHist, std::vector<int32_t>& assign) {
+        assign.assign(F.n > 0 ? F.n : 1, -1);
+        if (!m_) return 0;
+        const int n = orbfe_search_by_projection(m_, &F, windows.data(), (int)windows.size(), mode, th, linkStereo, rotHist,
+                                                 assign.data(), nullptr);
+        assign.resize(F.n > 0 ? F.n : 0);
+        status_ = n < 0 ? n : ORBFE_OK;
+        return n < 0 ? 0 : n;
+    }
+    // Frame::UndistortKeyPoints (Frame.cc:730-763).  K4 = fx, fy, cx, cy; dist = mDistCoef (4 or 5 floats).
+    bool UndistortKeyPoints(const std::vector<cv::KeyPoint>& mvKeys, const float* K4, const float* dist, int ndist,
+                            std::vector<cv::KeyPoint>& mvKeysUn) {
+        mvKeysUn.resize(mvKeys.size());
+        if (!m_) return false;
+        status_ = orbfe_undistort_keypoints(m_, reinterpret_cast<const orbfe_keypoint*>(mvKeys.data()), (int)mvKeys.size(), K4, dist,
+                                            ndist, reinterpret_cast<orbfe_keypoint*>(mvKeysUn.data()));
+        return status_ == ORBFE_OK;
+    }
+    // MapPoint::ComputeDistinctiveDescriptors (MapPoint.cc:349-423) for many map points in one launch: rows
+    // offsets[p]..offsets[p+1] of `observed` are point p's descriptors; best[p] = the row to clone into mDescriptor.
+    bool ComputeDistinctiveDescriptors(const cv::Mat& observed, const std::vector<int32_t>& offsets, std::vector<int32_t>& best) {
+        const int np = offsets.empty() ? 0 : (int)offsets.size() - 1;
+        best.assign(np > 0 ? np : 0, -1);
+        if (!m_ || np <= 0) return m_ != nullptr;
+        status_ = orbfe_distinctive_descriptors(m_, observed.rows ? observed.ptr() : nullptr, offsets.data(), np, best.data());
+        return status_ == ORBFE_OK;
+    }
     // Frame::ComputeStereoFishEyeMatches, whole body (Frame.cc:1116-1156).  cam1 / cam2: mvParameters of the two
     // KannalaBrandt8 cameras (8 floats), Rlr (row-major 3x3) / tlr: Frame::mRlr, mtlr.  Returns nMatches.
     int ComputeStereoFishEyeMatches(const std::vector<cv::KeyPoint>& mvKeys, const cv::Mat& mDescriptors, int monoLeft,

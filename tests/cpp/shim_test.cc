@@ -6,6 +6,7 @@
 // Writes: int32 nL, monoL, nR | nL keypoints (28 B) | nL x 32 descriptors | nL floats mvuRight | nL floats
 // mvDepth | int32 nmatchesBoW | nR int32 (SearchByBoW KF=left, Frame=right with the node function of
 // orbfe/synth.py and every left feature holding a MapPoint) | 8 floats scale factors | pyramid level 1 ROI bytes.
+// Then: nL x (float x, y) undistorted left keypoints | int32 nproj | nR int32 window assignment | 3 int32 distinctive rows.
 // With a vocabulary file: | int32 nwords, nnodes | nwords x (uint32 word, double value) | per node: uint32 id,
 // int32 count, count x uint32 feature (ORBVocabulary::transform of the left descriptors, levelsup 4).
 // Exit code 3 = no CUDA device (the CPU-side test expects exactly that), 0 = ok.
@@ -14,6 +15,7 @@
 #include <algorithm>
 #include <cstdio>
 #include <cstdlib>
+#include <cstring>
 #include <map>
 #include <vector>
 
@@ -96,6 +98,31 @@ int main(int argc, char** argv) {
     int32_t ps[2] = {p1.cols, p1.rows};
     fwrite(ps, 4, 2, o);
     for (int r = 0; r < p1.rows; ++r) fwrite(p1.ptr(r), 1, p1.cols, o);
+    {   // Frame::UndistortKeyPoints with the EuRoC cam0 distortion; SearchByProjection windows around the left keypoints
+        const float K4[4] = {458.654f, 457.296f, 367.215f, 248.375f}, D[4] = {-0.28340811f, 0.07395907f, 0.00019359f, 1.76187114e-05f};
+        std::vector<cv::KeyPoint> kUn;
+        if (!matcher.UndistortKeyPoints(kL, K4, D, 4, kUn)) return 1;
+        for (const auto& k : kUn) { fwrite(&k.pt.x, 4, 1, o); fwrite(&k.pt.y, 4, 1, o); }
+        orbfe_grid_frame F = {};
+        F.kps = reinterpret_cast<const orbfe_keypoint*>(kR.data()); F.desc = dR.ptr(); F.n = dR.rows; F.nleft = -1;
+        F.min_x = 0.f; F.min_y = 0.f; F.grid_w_inv = 64.f / (float)w; F.grid_h_inv = 48.f / (float)h;
+        std::vector<orbfe_proj_query> win(kL.size());
+        for (size_t i = 0; i < kL.size(); ++i) {       // the right image's content sits to the left: search around (x - 12, y)
+            orbfe_proj_query& q = win[i];
+            memset(&q, 0, sizeof(q));
+            q.u = kL[i].pt.x - 12.f; q.v = kL[i].pt.y; q.r = 30.f; q.min_level = (int16_t)(kL[i].octave - 1); q.max_level = (int16_t)(kL[i].octave + 1);
+            q.angle = kL[i].angle; q.obs = 1; q.valid = 1;
+            memcpy(q.desc, dL.ptr((int)i), 32);
+        }
+        std::vector<int32_t> assign;
+        const int32_t np = matcher.SearchByProjectionWindows(F, win, 0, ORBmatcher::TH_HIGH, false, true, assign);
+        if (matcher.lastStatus() != ORBFE_OK) return 1;
+        fwrite(&np, 4, 1, o);
+        fwrite(assign.data(), 4, assign.size(), o);
+        std::vector<int32_t> offs = {0, std::min(5, dL.rows), std::min(5, dL.rows), std::min(40, dL.rows)}, best;
+        if (!matcher.ComputeDistinctiveDescriptors(dL, offs, best) || best.size() != 3 || best[1] != -1) return 1;
+        fwrite(best.data(), 4, 3, o);
+    }
     if (argc == 10) {
         ORBVocabulary voc;
         if (!voc.loadFromTextFile(argv[9]) || voc.empty()) { fprintf(stderr, "vocabulary: %s\n", orbfe_strerror(voc.lastStatus())); return 1; }

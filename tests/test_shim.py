@@ -87,6 +87,10 @@ def test_shim_equals_python_abi_path(tmp_path):
     sf = np.frombuffer(buf, np.float32, 8, o); o += 32
     pw, ph = np.frombuffer(buf, np.int32, 2, o); o += 8
     lvl1 = np.frombuffer(buf, np.uint8, pw * ph, o).reshape(ph, pw); o += pw * ph
+    und = np.frombuffer(buf, np.float32, 2 * nL, o).reshape(nL, 2); o += 8 * nL
+    nproj = int(np.frombuffer(buf, np.int32, 1, o)[0]); o += 4
+    passign = np.frombuffer(buf, np.int32, nR, o); o += 4 * nR
+    pbest = np.frombuffer(buf, np.int32, 3, o); o += 12
     nw, nn = np.frombuffer(buf, np.int32, 2, o); o += 8
     bv = np.frombuffer(buf, np.dtype([("w", "<u4"), ("v", "<f8")]), nw, o); o += 12 * nw
     fv = {}
@@ -114,3 +118,16 @@ def test_shim_equals_python_abi_path(tmp_path):
                                 vc["weight"]).transform(dd, 4)
     assert np.array_equal(bv["w"], rw) and np.array_equal(bv["v"], rv)
     assert sorted(fv) == rn.tolist() and all(fv[int(n)] == ri[ro[i]:ro[i + 1]].tolist() for i, n in enumerate(rn))
+    # undistortion, projection windows and distinctive descriptors through the shim == the oracle
+    import oracle_binding as ob
+    from orbfe import projection as pj
+    ku = ob.undistort_keypoints(k, [458.654, 457.296, 367.215, 248.375], [-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05])
+    assert np.array_equal(und[:, 0], ku["x"]) and np.array_equal(und[:, 1], ku["y"])
+    G = pj.GridFrame(kR, dR, (0, 0, w, h), exL.GetScaleFactors())
+    win = np.zeros(nL, pj.PROJ_QUERY_DTYPE)
+    win["u"], win["v"], win["r"] = k["x"] - np.float32(12), k["y"], 30
+    win["min_level"], win["max_level"], win["angle"], win["obs"], win["valid"], win["desc"] = k["octave"] - 1, k["octave"] + 1, k["angle"], 1, 1, dd
+    rassign, _, rn = ob.search_by_projection(G, win, 0, 100, 0.7, False, True)
+    assert nproj == rn and np.array_equal(passign, rassign) and rn > 200
+    offs = np.array([0, min(5, nL), min(5, nL), min(40, nL)], np.int32)
+    assert np.array_equal(pbest, ob.distinctive_descriptors(dd, offs))
