@@ -360,6 +360,30 @@ def run_projection(args, orbfe, rank, local, world):
     return out
 
 
+def bind_to_gpu_numa_node(torch, local):
+    """Pins this rank's host threads (and therefore its first-touch pinned staging memory) to the NUMA node the
+    GPU hangs off, so that at N > 1 the ranks' host->device streams do not cross the socket interconnect."""
+    try:
+        bus = torch.cuda.get_device_properties(local).pci_bus_id
+        dom = torch.cuda.get_device_properties(local).pci_domain_id
+        dev = torch.cuda.get_device_properties(local).pci_device_id
+        path = f"/sys/bus/pci/devices/{dom:04x}:{bus:02x}:{dev:02x}.0/numa_node"
+        node = int(open(path).read().strip())
+        if node < 0:
+            return None
+        cpus = []
+        for part in open(f"/sys/devices/system/node/node{node}/cpulist").read().strip().split(","):
+            lo, _, hi = part.partition("-")
+            cpus.extend(range(int(lo), int(hi or lo) + 1))
+        allowed = sorted(set(cpus) & os.sched_getaffinity(0))
+        if allowed:
+            os.sched_setaffinity(0, allowed)
+            return node
+    except Exception:
+        pass
+    return None
+
+
 # ---- GPU arm ---------------------------------------------------------------------------------------
 def run_orbfe(args):
     import numpy as np
@@ -375,6 +399,7 @@ def run_orbfe(args):
     if rank == 0:
         g.build()
     torch.cuda.set_device(local)
+    numa = bind_to_gpu_numa_node(torch, local)
     if world > 1:
         os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep NCCL's version banner off stdout (one JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -485,7 +510,7 @@ def run_orbfe(args):
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
         "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "distinct_frames": nd, "lapping": list(LAPPING),
-                   "mean_keypoints_per_frame": n_kp, "parallelism": f"frame-sharded x{world}, no collective",
+                   "mean_keypoints_per_frame": n_kp, "parallelism": f"frame-sharded x{world}, no collective", "numa_node": numa,
                    "l2": f"inputs larger than L2: {B * W * H / 1e6:.0f} MB of frames and a "
                          f"{B * sum((a + 38) * (b + 38) for a, b in level_sizes) / 1e6:.0f} MB pyramid per step vs 126 MB L2"},
         "e2e": {"value": e2e_v, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),

@@ -117,10 +117,13 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 }
 
 #define BLUR_TW 128            // tile width  (one warp, 4 px per lane)
-#define BLUR_TH 32             // tile height (rows walked by a thread)
+#define BLUR_TH ORBFE_BLUR_TH   // tile height (rows walked by a thread); the host counts tiles with the same constant
 
 // grid.x = ceil(total tiles / 4) (4 warps per CTA, each decodes its own tile), grid.y = frame
-__global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
+#ifndef BLUR_MINB
+#define BLUR_MINB 1
+#endif
+__global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
                                               const LevelGeom* __restrict__ geom, int nlevels, int totalTiles, int frame0) {
     const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = frame0 + blockIdx.y;
     if (tile >= totalTiles) return;
@@ -167,7 +170,10 @@ __global__ void __launch_bounds__(128) k_blur(const uint8_t* __restrict__ pyr, u
 
 #define DESC_WARPS 8
 
-__global__ void __launch_bounds__(DESC_WARPS * 32) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
+#ifndef DESC_MINB
+#define DESC_MINB 6
+#endif
+__global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                                                               const LevelGeom* __restrict__ geom,
                                                               const uint32_t* __restrict__ slot, const int* __restrict__ nOut,
                                                               int kpPerFrame, orbfe_keypoint* __restrict__ kps,

@@ -99,7 +99,10 @@ __device__ __forceinline__ int warp_push(bool pred, int* counter) {
     return pred ? base + __popc(m & ((1u << lane) - 1u)) : -1;
 }
 
-__global__ void __launch_bounds__(FAST_THREADS) k_fast_cells(const __grid_constant__ FastMaps maps,
+#ifndef FAST_MINB
+#define FAST_MINB 8
+#endif
+__global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __grid_constant__ FastMaps maps,
                                                              const LevelGeom* __restrict__ geom,
                                                              const CellDesc* __restrict__ cells, uint32_t* __restrict__ cand,
                                                              int* __restrict__ candCount, long long candPerFrame,

@@ -110,9 +110,14 @@ __global__ void __launch_bounds__(128) k_pyr_resize(uint8_t* __restrict__ pyr, L
 // A thread owns one destination word and walks PYR_TH rows with the plan in registers: per row
 // 8 word loads (L1-resident), 4 PRMT, 8 DP2A (the 11-bit horizontal blend), the vertical blend, 1 store.
 // One warp = a 128-byte x PYR_TH-row tile, 4 tiles per CTA.
+#ifndef PYR_TH
 #define PYR_TH 16
+#endif
 
-__global__ void __launch_bounds__(128) k_pyr_resize_plan(uint8_t* __restrict__ pyr, LevelGeom gs, LevelGeom gd,
+#ifndef PYR_MINB
+#define PYR_MINB 1
+#endif
+__global__ void __launch_bounds__(128, PYR_MINB) k_pyr_resize_plan(uint8_t* __restrict__ pyr, LevelGeom gs, LevelGeom gd,
                                                          const ResizeTap* __restrict__ taps, const ColPlan* __restrict__ plans,
                                                          int tilesX, int totalTiles, int frame0) {
     const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = frame0 + blockIdx.y;

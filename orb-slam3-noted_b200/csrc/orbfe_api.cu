@@ -200,7 +200,7 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
         // resize taps (level l from level l-1)
         g.blurTileBase = blurTiles;
         g.blurTilesX = (g.w + 127) / 128;
-        blurTiles += g.blurTilesX * ((g.h + 31) / 32);
+        blurTiles += g.blurTilesX * ((g.h + ORBFE_BLUR_TH - 1) / ORBFE_BLUR_TH);
         g.tabX = tapOff;
         g.tabY = tapOff + g.w;
         tapOff += g.w + g.h;

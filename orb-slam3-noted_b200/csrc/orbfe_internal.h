@@ -10,6 +10,9 @@
 
 #define ORBFE_MAX_LEVELS 16
 #define ORBFE_EDGE 19          // EDGE_THRESHOLD, ORBextractor.cc:71
+#ifndef ORBFE_BLUR_TH
+#define ORBFE_BLUR_TH 32       // rows per k_blur tile (tile = 128 x ORBFE_BLUR_TH, one warp)
+#endif
 #define ORBFE_XO 32            // byte offset of ROI column 0 inside a bordered row (keeps ROI 32B-aligned)
 #define ORBFE_MIN_BORDER 16    // EDGE_THRESHOLD - 3, ORBextractor.cc:771
 #define ORBFE_MAX_NODES 2048
