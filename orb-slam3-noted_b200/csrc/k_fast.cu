@@ -99,6 +99,9 @@ __device__ __forceinline__ int warp_push(bool pred, int* counter) {
     return pred ? base + __popc(m & ((1u << lane) - 1u)) : -1;
 }
 
+#ifndef FAST_CPC
+#define FAST_CPC 1             // cells per CTA (measured on B200: 1 -> 1.56 ms, 2 -> 1.67, 3 -> 1.77, 4 -> 1.91 per 512 frames)
+#endif
 #ifndef FAST_MINB
 #define FAST_MINB 8
 #endif
@@ -106,34 +109,38 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
                                                              const LevelGeom* __restrict__ geom,
                                                              const CellDesc* __restrict__ cells, uint32_t* __restrict__ cand,
                                                              int* __restrict__ candCount, long long candPerFrame,
-                                                             int nlevels, int iniTh, int minTh, int boxW, int boxH, int frame0) {
+                                                             int nlevels, int iniTh, int minTh, int boxW, int boxH, int frame0,
+                                                             int nCells) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t sBar;
+    __shared__ __align__(8) uint64_t sBar[FAST_CPC];
     __shared__ int sCand, sCorners, sKept, sBase;
-    const CellDesc cd = cells[blockIdx.x];
     const int frame = frame0 + blockIdx.y;
-    const LevelGeom& g = geom[cd.level];
-    const int cw = cd.cw, ch = cd.ch;
     const int tp = boxW;                     // dense tile as delivered by TMA
-    // TMA wants the innermost start coordinate on a 16-byte boundary: load from the aligned column below
-    // the cell; tile byte = sh + column.
-    const int sh = (ORBFE_XO + cd.x0) & 15;
-    const int tw = cw - 6, th = ch - 6;      // tested area
-    if (tw <= 0 || th <= 0) return;
     const int tileBytes = boxW * boxH;
-    uint8_t* tile = smem;
-    uint8_t* score = tile + tileBytes;
+    const int tileStride = (tileBytes + 127) & ~127;   // TMA destinations must be 128-byte aligned
+    uint8_t* tiles = smem;                   // FAST_CPC tiles, all requested up front: cell k+1 loads while cell k computes
+    uint8_t* score = tiles + FAST_CPC * tileStride;
     uint16_t* list1 = reinterpret_cast<uint16_t*>(score + tileBytes);        // survivors of the quick test
     const int listCap = ((boxW - 6) * (boxH - 6) + 1) & ~1;
     uint16_t* list2 = list1 + listCap;                                       // corners
     uint32_t* kept = reinterpret_cast<uint32_t*>(list2 + listCap);
     const int tid = threadIdx.x;
     const int nw = tp >> 2;
+    const int cell0 = blockIdx.x * FAST_CPC;
 
     if (tid == 0) {
-        mbar_init(&sBar, 1);
-        mbar_expect_tx(&sBar, (uint32_t)tileBytes);
-        tma_load_3d(tile, &maps.m[cd.level], ORBFE_XO + cd.x0 - sh, ORBFE_EDGE + cd.y0, frame, &sBar);
+#pragma unroll
+        for (int ci = 0; ci < FAST_CPC; ++ci) {
+            if (cell0 + ci >= nCells) break;
+            const CellDesc c = cells[cell0 + ci];
+            if (c.cw - 6 <= 0 || c.ch - 6 <= 0) continue;
+            // TMA wants the innermost start coordinate on a 16-byte boundary: load from the aligned column
+            // below the cell; tile byte = sh + column.
+            const int s = (ORBFE_XO + c.x0) & 15;
+            mbar_init(&sBar[ci], 1);
+            mbar_expect_tx(&sBar[ci], (uint32_t)tileBytes);
+            tma_load_3d(tiles + ci * tileStride, &maps.m[c.level], ORBFE_XO + c.x0 - s, ORBFE_EDGE + c.y0, frame, &sBar[ci]);
+        }
     }
 
     int off[16];
@@ -143,6 +150,15 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
 #pragma unroll
         for (int k = 0; k < 16; ++k) off[k] = dy[k] * tp + dx[k];
     }
+  for (int ci = 0; ci < FAST_CPC; ++ci) {
+    if (cell0 + ci >= nCells) break;
+    const CellDesc cd = cells[cell0 + ci];
+    const LevelGeom& g = geom[cd.level];
+    const int cw = cd.cw, ch = cd.ch;
+    const int sh = (ORBFE_XO + cd.x0) & 15;
+    const int tw = cw - 6, th = ch - 6;      // tested area
+    if (tw <= 0 || th <= 0) continue;
+    const uint8_t* tile = tiles + ci * tileStride;
     // A1 work units: (row r in [3, ch-3)) x (word wi in [wLo, wHi]); word wi holds columns 4wi-sh .. 4wi-sh+3
     const int wLo = (sh + 3) >> 2, wHi = (sh + cw - 4) >> 2, nWordsA1 = wHi - wLo + 1;
     const int units = th * nWordsA1;
@@ -153,7 +169,7 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
         if (tid == 0) { sCand = 0; sCorners = 0; sKept = 0; }
         for (int i = tid; i < tileBytes / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
         __syncthreads();                       // also orders the mbarrier init before everyone's wait
-        if (pass == 0) mbar_wait(&sBar, 0);
+        if (pass == 0) mbar_wait(&sBar[ci], 0);
         // A1: necessary condition on two opposite ring pairs, 4 pixels per step.  A 9-arc covers at least
         // one pixel of every opposite pair, so a corner has |c - v| > t for v0 or v8 AND for v4 or v12.
         {
@@ -235,26 +251,31 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
         __syncthreads();
     }
     const int nk = sKept;
-    if (nk == 0) return;
-    if (tid == 0) sBase = atomicAdd(&candCount[frame * nlevels + cd.level], nk);
-    __syncthreads();
-    uint32_t* out = cand + (long long)frame * candPerFrame + g.candBase + sBase;
-    for (int i = tid; i < nk; i += FAST_THREADS) out[i] = kept[i];
+    if (nk > 0) {
+        if (tid == 0) sBase = atomicAdd(&candCount[frame * nlevels + cd.level], nk);
+        __syncthreads();
+        uint32_t* out = cand + (long long)frame * candPerFrame + g.candBase + sBase;
+        for (int i = tid; i < nk; i += FAST_THREADS) out[i] = kept[i];
+    }
+    __syncthreads();                         // the next cell reuses the score map, the lists and the counters
+  }
 }
 
 cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
     cudaError_t e = cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->stream);
     if (e != cudaSuccess) return e;
     static size_t configured = 0;
-    if ((size_t)h->maxCellBytes > 48 * 1024 && (size_t)h->maxCellBytes > configured) {
-        e = cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, h->maxCellBytes);
+    const size_t tileStride = ((size_t)h->fastBoxW * h->fastBoxH + 127) & ~(size_t)127;
+    const size_t smem = (size_t)h->maxCellBytes + FAST_CPC * tileStride - (size_t)h->fastBoxW * h->fastBoxH;   // maxCellBytes counts one unpadded tile
+    if (smem > 48 * 1024 && smem > configured) {
+        e = cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
-        configured = h->maxCellBytes;
+        configured = smem;
     }
-    dim3 grid(h->nCellsTotal, batch);
-    k_fast_cells<<<grid, FAST_THREADS, h->maxCellBytes, h->stream>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,
-                                                                     h->candPerFrame, h->p.nlevels, h->p.ini_th_fast,
-                                                                     h->p.min_th_fast, h->fastBoxW, h->fastBoxH, frame0);
+    dim3 grid((h->nCellsTotal + FAST_CPC - 1) / FAST_CPC, batch);
+    k_fast_cells<<<grid, FAST_THREADS, smem, h->stream>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,
+                                                          h->candPerFrame, h->p.nlevels, h->p.ini_th_fast, h->p.min_th_fast,
+                                                          h->fastBoxW, h->fastBoxH, frame0, h->nCellsTotal);
     h->launches++;
     return cudaGetLastError();
 }
