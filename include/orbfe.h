@@ -324,6 +324,8 @@ typedef struct orbfe_grid_frame {
     const int32_t* right_to_left;  /* mvRightToLeftMatch [n - nleft]; NULL = all -1 */
     float min_x, min_y;            /* Frame::mnMinX, mnMinY */
     float grid_w_inv, grid_h_inv;  /* mfGridElementWidthInv, mfGridElementHeightInv (64 x 48 grid, Frame.h:45-46) */
+    const float* inv_level_sigma2; /* mvInvLevelSigma2 [n_levels]; only read by windows with chi2 != 0; NULL = none */
+    int n_levels;
 } orbfe_grid_frame;
 
 /* One search window = one GetFeaturesInArea(u, v, r, min_level, max_level, right) call of the reference plus
@@ -340,14 +342,20 @@ typedef struct orbfe_proj_query {
     uint8_t check_ur;
     uint8_t valid;                 /* 0 = the reference `continue`s before searching (not in view, bad, behind the camera ...) */
     uint8_t skip_if_prev_ratio_rejected; /* :135: a failed ratio test also skips the same MapPoint's right-camera search */
-    uint8_t pad[3];
+    uint8_t chi2;                  /* 1 = Fuse's reprojection gate (ORBmatcher.cc:1744-1770): skip a feature when
+                                      ((u-x)^2 + (v-y)^2 [+ (ur-mvuRight)^2 if mvuRight >= 0]) * inv_level_sigma2[octave]
+                                      exceeds 5.99 [7.8] */
+    uint8_t pad[2];
     uint8_t desc[32];              /* pMP->GetDescriptor() */
 } orbfe_proj_query;
 
 /* The loop shared by SearchByProjection(Frame&, const vector<MapPoint*>&, th, ...) (ORBmatcher.cc:44-236: mode 1,
  * th = TH_HIGH, link_stereo = 1, rot_hist = 0) and SearchByProjection(Frame& Current, const Frame& Last, th, bMono)
  * (:2173-2389) / (Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) (:2391-2510) (mode 0, th = TH_HIGH / ORBdist,
- * rot_hist = 1 (applied iff the matcher checks orientation)).
+ * rot_hist = 1 (applied iff the matcher checks orientation)).  The KeyFrame-side searches are the same loop with
+ * windows that never claim (obs = 0) or always claim: SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th,
+ * ratioHamming) :473-585 / :588 (mode 0, th = floor(TH_LOW * ratioHamming), blocked = vpMatched non-NULL, obs = 1),
+ * Fuse :1629-1821 (chi2 = 1) / :1823-1945 and both directions of SearchBySim3 :1947-2171 (obs = 0, read `choice`).
  *   mode 0: keep the nearest descriptor, accept dist <= th.
  *   mode 1: best and second best; accept dist <= th unless both sit on the same pyramid level and
  *           best > mfNNratio * second (:133-139).

@@ -149,13 +149,18 @@ public:
     // The window-search loop of SearchByProjection (ORBmatcher.cc:44-236, :2173-2389, :2391-2510); the caller keeps
     // the reference's projection lines and emits one orbfe_proj_query per GetFeaturesInArea call.
     // assign[i]: index of the window whose MapPoint lands in mvpMapPoints[i], -1 untouched, -2 set to NULL.
+    // choice (optional): the feature each window picked, -1 = none — what the KeyFrame-side callers consume (Fuse
+    // :1629-1945 and SearchBySim3 :1947-2171 use windows that never claim, obs = 0; SearchByProjection(KeyFrame*, Scw,
+    // ...) :473-700 uses claiming windows with blocked = vpMatched non-NULL).
     int SearchByProjectionWindows(const orbfe_grid_frame& F, const std::vector<orbfe_proj_query>& windows, int mode, int th,
-                                  bool linkStereo, bool rotHist, std::vector<int32_t>& assign) {
+                                  bool linkStereo, bool rotHist, std::vector<int32_t>& assign, std::vector<int32_t>* choice = nullptr) {
         assign.assign(F.n > 0 ? F.n : 1, -1);
+        if (choice) choice->assign(windows.empty() ? 1 : windows.size(), -1);
         if (!m_) return 0;
         const int n = orbfe_search_by_projection(m_, &F, windows.data(), (int)windows.size(), mode, th, linkStereo, rotHist,
-                                                 assign.data(), nullptr);
+                                                 assign.data(), choice ? choice->data() : nullptr);
         assign.resize(F.n > 0 ? F.n : 0);
+        if (choice) choice->resize(windows.size());
         status_ = n < 0 ? n : ORBFE_OK;
         return n < 0 ? 0 : n;
     }

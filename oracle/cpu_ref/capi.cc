@@ -248,14 +248,14 @@ long orbref_bow_transform_many(void* voc, const uint8_t* desc, int n, int nframe
 int orbref_search_by_projection(const KeyPoint* kps, const uint8_t* desc, int n, int nleft, const uint8_t* blocked,
                                 const float* uRight, const int32_t* l2r, const int32_t* r2l, float minX, float minY,
                                 float gridWInv, float gridHInv, const void* queries, int nq, int mode, int th, float nnRatio,
-                                int linkStereo, int rotHist, int32_t* assign, int32_t* choice) {
-    GridFrame F{kps, desc, n, nleft, blocked, uRight, l2r, r2l, minX, minY, gridWInv, gridHInv};
+                                int linkStereo, int rotHist, const float* invLevelSigma2, int32_t* assign, int32_t* choice) {
+    GridFrame F{kps, desc, n, nleft, blocked, uRight, l2r, r2l, minX, minY, gridWInv, gridHInv, invLevelSigma2};
     ProjParams p{mode, th, nnRatio, linkStereo, rotHist};
     return searchByProjection(F, (const ProjQuery*)queries, nq, p, assign, choice);
 }
 int orbref_features_in_area(const KeyPoint* kps, int n, int nleft, float minX, float minY, float gridWInv, float gridHInv,
                             float x, float y, float r, int minLevel, int maxLevel, int bRight, int32_t* out) {
-    GridFrame F{kps, nullptr, n, nleft, nullptr, nullptr, nullptr, nullptr, minX, minY, gridWInv, gridHInv};
+    GridFrame F{kps, nullptr, n, nleft, nullptr, nullptr, nullptr, nullptr, minX, minY, gridWInv, gridHInv, nullptr};
     FrameGrid g(F);
     std::vector<int> v;
     g.featuresInArea(x, y, r, minLevel, maxLevel, bRight != 0, v);

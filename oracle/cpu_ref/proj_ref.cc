@@ -70,6 +70,19 @@ int searchByProjection(const GridFrame& F, const ProjQuery* q, int nq, const Pro
                 const float er = std::fabs(Q.ur - F.uRight[idx]);
                 if (er > Q.r) continue;
             }
+            if (Q.chi2 && F.invLevelSigma2) {                                    // Fuse :1744-1770
+                const KeyPoint& kp = F.kps[idx];
+                const float kpr = F.uRight ? F.uRight[Q.right ? idx - F.nleft : idx] : -1.f;     // mvuRight[idx], idx camera-local
+                const float ex = Q.u - kp.x, ey = Q.v - kp.y;
+                if (kpr >= 0) {
+                    const float er = Q.ur - kpr;
+                    const float e2 = ex * ex + ey * ey + er * er;
+                    if (e2 * F.invLevelSigma2[kp.octave] > 7.8) continue;
+                } else {
+                    const float e2 = ex * ex + ey * ey;
+                    if (e2 * F.invLevelSigma2[kp.octave] > 5.99) continue;
+                }
+            }
             const int dist = descriptorDistanceSwar(Q.desc, F.desc + 32 * (size_t)idx);
             if (dist < bestDist) {
                 bestDist2 = bestDist; bestDist = dist; bestLevel2 = bestLevel; bestLevel = F.kps[idx].octave; bestIdx = idx;

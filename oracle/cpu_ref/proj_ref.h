@@ -5,6 +5,9 @@
 // SearchByProjection(Frame&, vector<MapPoint*>&, th, ...) :44-236 (best + second best with the scale-level
 // rule, stereo links) and SearchByProjection(Frame& Current, const Frame& Last, th, bMono) :2173-2389 /
 // SearchByProjection(Frame&, KeyFrame*, sAlreadyFound, th, ORBdist) :2391-2510 (best only, rotation histogram).
+// The KeyFrame-side searches reuse the loop (KeyFrame::GetFeaturesInArea, src/KeyFrame.cc:737-781, is the same cell
+// walk without the level filter, which those callers apply themselves): SearchByProjection(KeyFrame*, Scw, ...)
+// :473-585 / :588-700, Fuse :1629-1821 (with its chi-square gate) / :1823-1945, SearchBySim3 :1947-2171.
 // The part of those functions that differs per overload — projecting a MapPoint with a pose and a camera,
 // predicting its scale level — produces, per MapPoint, a window (u, v, r, level range); everything after that
 // is the same loop, restated here over flattened arrays exactly as at the C ABI (include/orbfe.h).
@@ -27,6 +30,7 @@ struct GridFrame {                // the Frame being searched
     const int32_t* leftToRight;   // mvLeftToRightMatch [nleft] (nullable)
     const int32_t* rightToLeft;   // mvRightToLeftMatch [n - nleft] (nullable)
     float minX, minY, gridWInv, gridHInv;     // mnMinX, mnMinY, mfGridElementWidthInv, mfGridElementHeightInv
+    const float* invLevelSigma2;  // mvInvLevelSigma2 (windows with chi2; nullable)
 };
 
 #pragma pack(push, 1)
@@ -40,7 +44,8 @@ struct ProjQuery {                // one GetFeaturesInArea window + what is matc
     uint8_t checkUr;              // apply |ur - mvuRight[idx]| > r -> skip (only when nleft == -1 && mvuRight > 0)
     uint8_t valid;                // 0: skipped before the window search (not in view, bad, behind the camera ...)
     uint8_t skipIfPrevRatioRejected;   // :135: the `continue` after a failed ratio test also skips the same MapPoint's right-camera search
-    uint8_t pad[3];
+    uint8_t chi2;                 // Fuse's per-candidate reprojection gate (ORBmatcher.cc:1744-1770)
+    uint8_t pad[2];
     uint8_t desc[32];             // pMP->GetDescriptor()
 };
 #pragma pack(pop)

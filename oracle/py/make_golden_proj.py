@@ -51,6 +51,97 @@ def result_of(F, old, mps):
     return out
 
 
+def kf_of(G):
+    K = pp.KeyFrame(G.kps, G.desc, G.scale_factors, (G.min_x, G.min_y, G.max_x, G.max_y), G.nleft, G.u_right, G.left_to_right,
+                    G.right_to_left, G.mbf, G.mb, inv_level_sigma2=G.inv_level_sigma2, log_scale_factor=pc.LOG_SF)
+    return K
+
+
+def kf_points(pts, K=None):
+    out = []
+    for i in range(len(pts["desc"])):
+        if "null" in pts and pts["null"][i]:
+            out.append(None)
+            continue
+        m = pp.MapPointKF(pts["desc"][i], pts["world_pos"][i], pts["normal"][i], pts["min_dist"][i], pts["max_dist"][i], 1, bool(pts["bad"][i]))
+        if K is not None and "in_keyframe" in pts and pts["in_keyframe"][i]:
+            m.in_kf.add(id(K))
+        out.append(m)
+    return out
+
+
+def golden_kf(name):
+    """Returns the arrays stored for one KeyFrame-side case (also used by nothing else: the tests read the file)."""
+    c = pc.kf_inputs(name)
+    K, kind, pts = kf_of(c["KF"]), c["kind"], c["pts"]
+    mps = kf_points(pts, K)
+    if kind in ("sim3", "fuse_sim3"):
+        Rcw, tcw, Ow = pj.decompose_sim3(c["Scw"])
+        T = np.concatenate([Rcw, tcw[:, None]], 1)
+    else:
+        T = c["Tcw"][:3]
+        Ow = pj.camera_centre(T[:, :3], T[:, 3])
+    to_cam = lambda p: pj.transform_point(T, p)
+    if kind == "sim3":
+        old = Old()
+        vpMatched = [old if c["KF"].blocked[i] else None for i in range(K.N)]
+        found = [m for i, m in enumerate(mps) if pts["already_found"][i]]
+        vpMatched = _Matched(vpMatched, found)
+        n = pp.search_by_projection_sim3(K, mps, vpMatched, c["th"], c["ratio"], to_cam, c["project"], Ow)
+        idx = {id(m): i for i, m in enumerate(mps)}
+        res = np.array([idx[id(m)] if (m is not None and m is not old) else -1 for m in list.__iter__(vpMatched)], np.int32)
+        return dict(n=n, point_of_feature=res)
+    if kind == "fuse_sim3":
+        already = {id(m) for i, m in enumerate(mps) if pts["already_found"][i]}
+        n, picks = pp.fuse_sim3(K, mps, c["th"], to_cam, c["project"], Ow, already)
+    else:
+        n, picks = pp.fuse(K, mps, c["th"], to_cam, c["project"], Ow, kind == "fuse_right")
+    ch = np.full(len(mps), -1, np.int32)
+    for i, b in picks:
+        ch[i] = b
+    return dict(n=n, feature_of_point=ch)
+
+
+class _Matched(list):
+    """vpMatched whose iteration (the spAlreadyFound set of :490) also yields the points flagged already-found,
+    which in the reference sit in vpMatched at indices outside this test's keyframe features."""
+    def __init__(self, items, extra):
+        super().__init__(items)
+        self.extra = extra
+
+    def __iter__(self):
+        yield from list.__iter__(self)
+        yield from self.extra
+
+
+def golden_sim3(name):
+    c = pc.sim3_inputs(name)
+    K1, K2 = kf_of(c["KF1"]), kf_of(c["KF2"])
+    for K, P in ((K1, c["mps1"]), (K2, c["mps2"])):
+        pts = kf_points(P)
+        K.mvpMapPoints = [m if P["has_mp"][i] else None for i, m in enumerate(pts)]
+    # vpMatches12: the already-matched KF1 features hold a point that KF2 does not observe (index -1)
+    vpMatches12 = [Old() if c["mps1"]["already_matched"][i] else None for i in range(K1.N)]
+    sR12, sR21, t21 = pj.sim3_relative(c["s12"], c["R12"], c["t12"])
+    T12 = np.concatenate([sR12, c["t12"].reshape(3, 1)], 1)
+    T21 = np.concatenate([sR21, t21.reshape(3, 1)], 1)
+    # vbAlreadyMatched2 comes from GetIndexInKeyFrame in the reference; the scenario sets it directly
+    already2 = c["mps2"]["already_matched"]
+    n, v1, v2 = search_by_sim3_with_mask(K1, K2, vpMatches12, already2, c["th"], T12, T21, c)
+    return dict(n=n, vnMatch1=np.array(v1, np.int32), vnMatch2=np.array(v2, np.int32))
+
+
+def search_by_sim3_with_mask(K1, K2, vpMatches12, already2, th, T12, T21, c):
+    marked = [i for i in range(K2.N) if already2[i]]
+    holders = [m for m in vpMatches12 if m is not None]
+    # each already-matched KF1 entry reports one of the marked KF2 indices (round robin), the rest report -1
+    table = {id(m): (marked[k] if k < len(marked) else -1) for k, m in enumerate(holders)}
+    assert len(holders) >= len(marked), "scenario: more marked KF2 features than already-matched KF1 entries"
+    return pp.search_by_sim3(K1, K2, vpMatches12, lambda m: table[id(m)], th, pc.CAM,
+                             lambda p: pj.transform_point(c["T1w"], p), lambda p: pj.transform_point(c["T2w"], p),
+                             lambda p: pj.transform_point(T21, p), lambda p: pj.transform_point(T12, p))
+
+
 def main():
     out = os.path.join(ROOT, "tests", "golden")
     for name in pc.MP_CASES:
@@ -96,6 +187,17 @@ def main():
         np.savez_compressed(os.path.join(out, f"{name}.npz"), in_crc=crc(c["Cur"].kps, c["Cur"].desc, last["desc"], last["world_pos"]),
                             lastframe_feature_of_feature=res, n=n)
         print(name, "nmatches", n, "assigned", int((res >= 0).sum()))
+    for name in pc.KF_CASES:
+        g = golden_kf(name)
+        c = pc.kf_inputs(name)
+        np.savez_compressed(os.path.join(out, f"{name}.npz"), in_crc=crc(c["KF"].kps, c["KF"].desc, c["pts"]["desc"], c["pts"]["world_pos"]), **g)
+        key = "point_of_feature" if "point_of_feature" in g else "feature_of_point"
+        print(name, "n", g["n"], "assigned", int((g[key] >= 0).sum()))
+    for name in pc.SIM3_CASES:
+        g = golden_sim3(name)
+        c = pc.sim3_inputs(name)
+        np.savez_compressed(os.path.join(out, f"{name}.npz"), in_crc=crc(c["KF1"].kps, c["KF2"].kps, c["mps1"]["desc"], c["mps2"]["world_pos"]), **g)
+        print(name, "nFound", g["n"], "one-way", int((g["vnMatch1"] >= 0).sum()), int((g["vnMatch2"] >= 0).sum()))
 
 
 if __name__ == "__main__":

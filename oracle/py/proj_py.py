@@ -3,7 +3,8 @@
 Follows src/Frame.cc (AssignFeaturesToGrid :380-411, GetFeaturesInArea :640-706, PosInGrid :708-719) and
 src/ORBmatcher.cc: SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints) :44-236,
 RadiusByViewingCos :238-244, SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono)
-:2173-2389.  Frames and MapPoints are small Python objects with the reference's member names; float32
+:2173-2389, and the KeyFrame-side searches SearchByProjection(KeyFrame*, Scw, ...) :473-585, Fuse :1629-1821 /
+:1823-1945, SearchBySim3 :1947-2171.  Frames and MapPoints are small Python objects with the reference's member names; float32
 arithmetic is spelled out with numpy scalars.  Written independently of oracle/cpu_ref/proj_ref.cc (which
 works on the flattened windows); the golden fixtures come from this file.
 """
@@ -294,3 +295,243 @@ def search_by_projection_lastframe(Cur, Last, th, bMono, check_ori, project, x3D
                     Cur.mvpMapPoints[idx] = None
                     nmatches -= 1
     return nmatches
+
+
+# ---- KeyFrame-side searches (loop closing, merging, local mapping) -------------------------------------------------
+class KeyFrame(Frame):
+    """What the searches below read of a KeyFrame: the Frame's grid (KeyFrame.cc:60 copies it), mvInvLevelSigma2,
+    mvpMapPoints.  GetFeaturesInArea (KeyFrame.cc:737-781) has no level filter; IsInImage :783-786."""
+
+    def __init__(self, *a, inv_level_sigma2=None, log_scale_factor=None, **k):
+        super().__init__(*a, **k)
+        self.mvInvLevelSigma2 = None if inv_level_sigma2 is None else np.asarray(inv_level_sigma2, F32)
+        self.mfLogScaleFactor = F32(log_scale_factor)
+        self.mnScaleLevels = len(self.mvScaleFactors)
+
+    def GetFeaturesInAreaKF(self, x, y, r, bRight=False):
+        return Frame.GetFeaturesInArea(self, x, y, r, -1, -1, bRight)
+
+    def IsInImage(self, x, y):
+        return bool(x >= self.mnMinX and x < self.mnMaxX and y >= self.mnMinY and y < self.mnMaxY)
+
+    def GetMapPoint(self, idx):
+        return self.mvpMapPoints[idx]
+
+
+class MapPointKF(MapPoint):
+    def __init__(self, descriptor, world_pos, normal, mf_min, mf_max, n_obs=1, bad=False):
+        super().__init__(descriptor, n_obs, bad, np.asarray(world_pos, F32))
+        self.mNormalVector = np.asarray(normal, F32)
+        self.mfMinDistance, self.mfMaxDistance = F32(mf_min), F32(mf_max)
+        self.in_kf = set()                       # ids of keyframes observing it
+
+    def GetMinDistanceInvariance(self):
+        return F32(F32(0.8) * self.mfMinDistance)
+
+    def GetMaxDistanceInvariance(self):
+        return F32(F32(1.2) * self.mfMaxDistance)
+
+    def PredictScale(self, currentDist, pKF):                    # MapPoint.cc:534-549
+        ratio = F32(self.mfMaxDistance / F32(currentDist))
+        nScale = int(math.ceil(math.log(float(ratio)) / float(pKF.mfLogScaleFactor)))
+        return 0 if nScale < 0 else min(nScale, pKF.mnScaleLevels - 1)
+
+    def IsInKeyFrame(self, pKF):
+        return id(pKF) in self.in_kf
+
+
+def _norm(v):
+    return F32(math.sqrt(sum(float(c) * float(c) for c in v)))
+
+
+def _window_level(pMP, pKF, Ow):
+    """Depth-invariance and viewing-angle gates + PredictScale (:523-541 and its copies)."""
+    PO = (pMP.mWorldPos - Ow).astype(F32)
+    dist = _norm(PO)
+    if dist < pMP.GetMinDistanceInvariance() or dist > pMP.GetMaxDistanceInvariance():
+        return None
+    if sum(float(a) * float(b) for a, b in zip(PO, pMP.mNormalVector)) < 0.5 * float(dist):
+        return None
+    return pMP.PredictScale(dist, pKF)
+
+
+def search_by_projection_sim3(pKF, vpPoints, vpMatched, th, ratioHamming, to_camera, project, Ow):
+    """ORBmatcher.cc:473-585.  to_camera(p3Dw) = Rcw * p3Dw + tcw of the decomposed Scw.  Mutates vpMatched."""
+    spAlreadyFound = {id(m) for m in vpMatched if m is not None}
+    nmatches = 0
+    for pMP in vpPoints:
+        if pMP.isBad() or id(pMP) in spAlreadyFound:
+            continue
+        p3Dc = to_camera(pMP.mWorldPos)
+        if p3Dc[2] < 0.0:
+            continue
+        u, v = project(p3Dc)
+        if not pKF.IsInImage(u, v):
+            continue
+        nPredictedLevel = _window_level(pMP, pKF, Ow)
+        if nPredictedLevel is None:
+            continue
+        radius = F32(F32(th) * pKF.mvScaleFactors[nPredictedLevel])
+        vIndices = pKF.GetFeaturesInAreaKF(u, v, radius)
+        if not vIndices:
+            continue
+        dMP = pMP.GetDescriptor()
+        bestDist, bestIdx = 256, -1
+        for idx in vIndices:
+            if vpMatched[idx] is not None:
+                continue
+            kpLevel = int(pKF.keys[idx]["octave"])
+            if kpLevel < nPredictedLevel - 1 or kpLevel > nPredictedLevel:
+                continue
+            dist = descriptor_distance(dMP, pKF.mDescriptors[idx])
+            if dist < bestDist:
+                bestDist, bestIdx = dist, idx
+        if F32(bestDist) <= F32(F32(TH_LOW) * F32(ratioHamming)):
+            vpMatched[bestIdx] = pMP
+            nmatches += 1
+    return nmatches
+
+
+def fuse(pKF, vpMapPoints, th, to_camera, project, Ow, bRight=False):
+    """ORBmatcher.cc:1629-1821.  Returns (nFused, [(index in vpMapPoints, bestIdx)]): the graph surgery of :1787-1812
+    (Replace / AddObservation) is left to the caller, the searches do not depend on it."""
+    nFused, picks = 0, []
+    for i, pMP in enumerate(vpMapPoints):
+        if pMP is None or pMP.isBad() or pMP.IsInKeyFrame(pKF):
+            continue
+        p3Dc = to_camera(pMP.mWorldPos)
+        if p3Dc[2] < 0.0:
+            continue
+        invz = F32(F32(1) / p3Dc[2])
+        u, v = project(p3Dc)
+        if not pKF.IsInImage(u, v):
+            continue
+        ur = F32(u - F32(pKF.mbf * invz))
+        nPredictedLevel = _window_level(pMP, pKF, Ow)
+        if nPredictedLevel is None:
+            continue
+        radius = F32(F32(th) * pKF.mvScaleFactors[nPredictedLevel])
+        vIndices = pKF.GetFeaturesInAreaKF(u, v, radius, bRight)
+        if not vIndices:
+            continue
+        dMP = pMP.GetDescriptor()
+        bestDist, bestIdx = 256, -1
+        for idx in vIndices:
+            kp = pKF.keys[idx] if (pKF.Nleft == -1 or not bRight) else pKF.keys[idx + pKF.Nleft]
+            kpLevel = int(kp["octave"])
+            if kpLevel < nPredictedLevel - 1 or kpLevel > nPredictedLevel:
+                continue
+            ex, ey = F32(u - kp["x"]), F32(v - kp["y"])
+            if pKF.mvuRight[idx] >= 0:
+                er = F32(ur - pKF.mvuRight[idx])
+                e2 = F32(F32(F32(ex * ex) + F32(ey * ey)) + F32(er * er))
+                if float(F32(e2 * pKF.mvInvLevelSigma2[kpLevel])) > 7.8:
+                    continue
+            else:
+                e2 = F32(F32(ex * ex) + F32(ey * ey))
+                if float(F32(e2 * pKF.mvInvLevelSigma2[kpLevel])) > 5.99:
+                    continue
+            if bRight:
+                idx += pKF.Nleft
+            dist = descriptor_distance(dMP, pKF.mDescriptors[idx])
+            if dist < bestDist:
+                bestDist, bestIdx = dist, idx
+        if bestDist <= TH_LOW:
+            picks.append((i, bestIdx))
+            nFused += 1
+    return nFused, picks
+
+
+def fuse_sim3(pKF, vpPoints, th, to_camera, project, Ow, spAlreadyFound):
+    """ORBmatcher.cc:1823-1945 (searches only, as in fuse())."""
+    nFused, picks = 0, []
+    for i, pMP in enumerate(vpPoints):
+        if pMP.isBad() or id(pMP) in spAlreadyFound:
+            continue
+        p3Dc = to_camera(pMP.mWorldPos)
+        if p3Dc[2] < 0.0:
+            continue
+        u, v = project(p3Dc)
+        if not pKF.IsInImage(u, v):
+            continue
+        nPredictedLevel = _window_level(pMP, pKF, Ow)
+        if nPredictedLevel is None:
+            continue
+        radius = F32(F32(th) * pKF.mvScaleFactors[nPredictedLevel])
+        vIndices = pKF.GetFeaturesInAreaKF(u, v, radius)
+        if not vIndices:
+            continue
+        dMP = pMP.GetDescriptor()
+        bestDist, bestIdx = 2 ** 31 - 1, -1
+        for idx in vIndices:
+            kpLevel = int(pKF.keys[idx]["octave"])
+            if kpLevel < nPredictedLevel - 1 or kpLevel > nPredictedLevel:
+                continue
+            dist = descriptor_distance(dMP, pKF.mDescriptors[idx])
+            if dist < bestDist:
+                bestDist, bestIdx = dist, idx
+        if bestDist <= TH_LOW:
+            picks.append((i, bestIdx))
+            nFused += 1
+    return nFused, picks
+
+
+def search_by_sim3(pKF1, pKF2, vpMatches12, index_in_kf2, th, cam, to_c1, to_c2, c1_to_c2, c2_to_c1):
+    """ORBmatcher.cc:1947-2171.  index_in_kf2(pMP) = get<0>(pMP->GetIndexInKeyFrame(pKF2)); to_c1 / to_c2 = camera
+    from world; c1_to_c2(p) = sR21 * p + t21, c2_to_c1(p) = sR12 * p + t12.  Mutates vpMatches12; returns nFound and
+    (vnMatch1, vnMatch2)."""
+    fx, fy, cx, cy = (F32(c) for c in cam[:4])
+    N1, N2 = pKF1.N, pKF2.N
+    vbAlreadyMatched1, vbAlreadyMatched2 = [False] * N1, [False] * N2
+    for i in range(N1):
+        pMP = vpMatches12[i]
+        if pMP is not None:
+            vbAlreadyMatched1[i] = True
+            idx2 = index_in_kf2(pMP)
+            if 0 <= idx2 < N2:
+                vbAlreadyMatched2[idx2] = True
+
+    def one_way(src, dst, already, to_src, src_to_dst):
+        vnMatch = [-1] * src.N
+        for i in range(src.N):
+            pMP = src.mvpMapPoints[i]
+            if pMP is None or already[i] or pMP.isBad():
+                continue
+            pd = src_to_dst(to_src(pMP.mWorldPos))
+            if pd[2] < 0.0:
+                continue
+            invz = F32(1.0 / float(pd[2]))
+            x, y = F32(pd[0] * invz), F32(pd[1] * invz)
+            u, v = F32(F32(fx * x) + cx), F32(F32(fy * y) + cy)
+            if not dst.IsInImage(u, v):
+                continue
+            dist3D = _norm(pd)
+            if dist3D < pMP.GetMinDistanceInvariance() or dist3D > pMP.GetMaxDistanceInvariance():
+                continue
+            nPredictedLevel = pMP.PredictScale(dist3D, dst)
+            radius = F32(F32(th) * dst.mvScaleFactors[nPredictedLevel])
+            vIndices = dst.GetFeaturesInAreaKF(u, v, radius)
+            if not vIndices:
+                continue
+            dMP = pMP.GetDescriptor()
+            bestDist, bestIdx = 2 ** 31 - 1, -1
+            for idx in vIndices:
+                kpo = int(dst.keys[idx]["octave"])
+                if kpo < nPredictedLevel - 1 or kpo > nPredictedLevel:
+                    continue
+                dist = descriptor_distance(dMP, dst.mDescriptors[idx])
+                if dist < bestDist:
+                    bestDist, bestIdx = dist, idx
+            if bestDist <= TH_HIGH:
+                vnMatch[i] = bestIdx
+        return vnMatch
+
+    vnMatch1 = one_way(pKF1, pKF2, vbAlreadyMatched1, to_c1, c1_to_c2)
+    vnMatch2 = one_way(pKF2, pKF1, vbAlreadyMatched2, to_c2, c2_to_c1)
+    nFound = 0
+    for i1 in range(N1):
+        idx2 = vnMatch1[i1]
+        if idx2 >= 0 and vnMatch2[idx2] == i1:
+            vpMatches12[i1] = pKF2.mvpMapPoints[idx2]
+            nFound += 1
+    return nFound, vnMatch1, vnMatch2

@@ -73,6 +73,7 @@ __device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lan
     const bool bCheckLevels = (minLevel > 0) || (maxLevel >= 0);
     const bool right = Q.right != 0;
     const bool checkUr = !right && Q.checkUr && P.nleft == -1 && P.uRight != nullptr;
+    const bool chi2 = Q.chi2 != 0 && P.invSigma2 != nullptr;
     const uint4 a0 = *reinterpret_cast<const uint4*>(Q.desc), a1 = *(reinterpret_cast<const uint4*>(Q.desc) + 1);
     const int ny = w.maxCY - w.minCY + 1, ncell = (w.maxCX - w.minCX + 1) * ny;
     const int side = right ? GRID_CELLS : 0;
@@ -92,6 +93,18 @@ __device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lan
             if (checkUr) {
                 const float ur = P.uRight[idx];
                 if (ur > 0.f && fabsf(__fsub_rn(Q.ur, ur)) > r) continue;
+            }
+            if (chi2) {             // Fuse :1744-1770 (mvuRight is read with the camera-local index, as the reference does)
+                const float ex = __fsub_rn(x, kp.x), ey = __fsub_rn(y, kp.y);
+                const float kpr = P.uRight ? P.uRight[right ? idx - P.nleft : idx] : -1.f;
+                float e2 = __fadd_rn(__fmul_rn(ex, ex), __fmul_rn(ey, ey));
+                double gate = 5.99;
+                if (kpr >= 0.f) {
+                    const float er = __fsub_rn(Q.ur, kpr);
+                    e2 = __fadd_rn(e2, __fmul_rn(er, er));
+                    gate = 7.8;
+                }
+                if ((double)__fmul_rn(e2, P.invSigma2[oct]) > gate) continue;
             }
             const int dist = ham_q(a0, a1, P.desc + 32ll * idx);
             f((unsigned long long)dist << 40 | (unsigned long long)e << 16 | (unsigned)idx);

@@ -45,7 +45,7 @@ cudaError_t orbfe_launch_distinctive(cudaStream_t st, const uint8_t* dDesc, cons
 struct ProjQueryDev {          // = orbfe_proj_query (include/orbfe.h), 64 bytes
     float u, v, r, ur, angle;
     int16_t minLevel, maxLevel;
-    uint8_t right, obs, checkUr, valid, skipIfPrevRatioRejected, pad[3];
+    uint8_t right, obs, checkUr, valid, skipIfPrevRatioRejected, chi2, pad[2];
     uint8_t desc[32];
 };
 static_assert(sizeof(ProjQueryDev) == 64, "orbfe_proj_query layout");
@@ -59,6 +59,7 @@ struct ProjProblem {
     const int32_t* r2l;        // nullable
     int n, nleft;
     float minX, minY, gridWInv, gridHInv;
+    const float* invSigma2;    // mvInvLevelSigma2 (windows with chi2; nullable)
     const ProjQueryDev* q;
     int nq;
     int32_t* assign;           // n

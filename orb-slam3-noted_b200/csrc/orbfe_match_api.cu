@@ -561,6 +561,12 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     for (int i = 0; i < n; ++i) assign[i] = -1;
     if (choice) for (int i = 0; i < nq; ++i) choice[i] = -1;
     if (n == 0 || nq == 0) return 0;
+    bool anyChi2 = false;
+    for (int i = 0; i < nq && !anyChi2; ++i) anyChi2 = queries[i].chi2 != 0;
+    if (anyChi2) {          // Fuse's gate indexes mvInvLevelSigma2 by the feature's octave
+        if (!F->inv_level_sigma2 || F->n_levels < 1 || F->n_levels > ORBFE_MAX_LEVELS) return ORBFE_ERR_BAD_ARGUMENT;
+        for (int i = 0; i < n; ++i) if (F->kps[i].octave < 0 || F->kps[i].octave >= F->n_levels) return ORBFE_ERR_BAD_ARGUMENT;
+    }
     if (link_stereo && F->nleft != -1) {
         if (F->left_to_right) for (int i = 0; i < F->nleft; ++i) if (F->left_to_right[i] < -1 || F->left_to_right[i] >= n - F->nleft) return ORBFE_ERR_BAD_ARGUMENT;
         if (F->right_to_left) for (int i = 0; i < n - F->nleft; ++i) if (F->right_to_left[i] < -1 || F->right_to_left[i] >= F->nleft) return ORBFE_ERR_BAD_ARGUMENT;
@@ -571,6 +577,7 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     const size_t oKp = stage_take(u, sizeof(float4) * n), oDesc = stage_take(u, 32 * (size_t)n), oBlk = stage_take(u, n);
     const size_t oUr = stage_take(u, sizeof(float) * n), oL2R = stage_take(u, sizeof(int32_t) * std::max(nl, 1));
     const size_t oR2L = stage_take(u, sizeof(int32_t) * std::max(nr, 1)), oQ = stage_take(u, sizeof(ProjQueryDev) * (size_t)nq);
+    const size_t oSig = stage_take(u, sizeof(float) * ORBFE_MAX_LEVELS);
     const size_t oProb = stage_take(u, sizeof(ProjProblem));
     const size_t inBytes = u;
     const size_t oSorted = stage_take(u, sizeof(uint32_t) * n), oCell = stage_take(u, sizeof(int) * 4 * 3072);
@@ -595,6 +602,7 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     if (F->left_to_right && nl) memcpy(hs + oL2R, F->left_to_right, sizeof(int32_t) * nl);
     if (F->right_to_left && nr) memcpy(hs + oR2L, F->right_to_left, sizeof(int32_t) * nr);
     memcpy(hs + oQ, queries, sizeof(ProjQueryDev) * (size_t)nq);
+    if (anyChi2) memcpy(hs + oSig, F->inv_level_sigma2, sizeof(float) * F->n_levels);
     ProjProblem P;
     memset(&P, 0, sizeof(P));
     P.kp = reinterpret_cast<const float4*>(ds + oKp);
@@ -603,6 +611,7 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     P.uRight = F->u_right ? reinterpret_cast<const float*>(ds + oUr) : nullptr;
     P.l2r = (F->left_to_right && nl) ? reinterpret_cast<const int32_t*>(ds + oL2R) : nullptr;
     P.r2l = (F->right_to_left && nr) ? reinterpret_cast<const int32_t*>(ds + oR2L) : nullptr;
+    P.invSigma2 = anyChi2 ? reinterpret_cast<const float*>(ds + oSig) : nullptr;
     P.n = n; P.nleft = F->nleft;
     P.minX = F->min_x; P.minY = F->min_y; P.gridWInv = F->grid_w_inv; P.gridHInv = F->grid_h_inv;
     P.q = reinterpret_cast<const ProjQueryDev*>(ds + oQ);

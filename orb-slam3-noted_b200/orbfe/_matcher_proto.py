@@ -28,7 +28,8 @@ class Kb8Epipolar(C.Structure):
 class GridFrameC(C.Structure):
     """orbfe_grid_frame"""
     _fields_ = [("kps", _P), ("desc", _P), ("n", _I), ("nleft", _I), ("blocked", _P), ("u_right", _P), ("left_to_right", _P),
-                ("right_to_left", _P), ("min_x", _F), ("min_y", _F), ("grid_w_inv", _F), ("grid_h_inv", _F)]
+                ("right_to_left", _P), ("min_x", _F), ("min_y", _F), ("grid_w_inv", _F), ("grid_h_inv", _F),
+                ("inv_level_sigma2", _P), ("n_levels", _I)]
 
 
 PROTO = {

@@ -279,6 +279,8 @@ class ORBmatcher:
         g.blocked, g.u_right = _p(F.blocked), _p(F.u_right)
         g.left_to_right, g.right_to_left = _p(F.left_to_right), _p(F.right_to_left)
         g.min_x, g.min_y, g.grid_w_inv, g.grid_h_inv = float(F.min_x), float(F.min_y), float(F.grid_w_inv), float(F.grid_h_inv)
+        sig = getattr(F, "inv_level_sigma2", None)
+        g.inv_level_sigma2, g.n_levels = _p(sig), 0 if sig is None else len(sig)
         assign, choice = np.full(max(F.n, 1), -1, np.int32), np.full(max(len(q), 1), -1, np.int32)
         n = self._lib.orbfe_search_by_projection(self._m, C.byref(g), _p(q), len(q), int(mode), int(th), int(bool(link_stereo)),
                                                  int(bool(rot_hist)), _p(assign), _p(choice))

@@ -281,14 +281,14 @@ def search_by_projection(F, queries, mode, th, nnratio, link_stereo, rot_hist):
     """oracle/cpu_ref/proj_ref.cc on a projection.GridFrame and an array of PROJ_QUERY_DTYPE records.
     Returns (assign, choice, nmatches)."""
     L_ = lib()
-    L_.orbref_search_by_projection.argtypes = [_P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I, _I, _F, _I, _I, _P, _P]
+    L_.orbref_search_by_projection.argtypes = [_P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I, _I, _F, _I, _I, _P, _P, _P]
     q = np.ascontiguousarray(queries)
     assign, choice = np.zeros(max(F.n, 1), np.int32), np.zeros(max(len(q), 1), np.int32)
     opt = lambda a: None if a is None else _p(a)
     n = L_.orbref_search_by_projection(_p(F.kps), _p(F.desc), F.n, F.nleft, opt(F.blocked), opt(F.u_right), opt(F.left_to_right),
                                        opt(F.right_to_left), float(F.min_x), float(F.min_y), float(F.grid_w_inv),
                                        float(F.grid_h_inv), _p(q), len(q), mode, th, float(nnratio), int(link_stereo),
-                                       int(rot_hist), _p(assign), _p(choice))
+                                       int(rot_hist), opt(F.inv_level_sigma2), _p(assign), _p(choice))
     return assign[:F.n], choice[:len(q)], n
 
 

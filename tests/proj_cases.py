@@ -130,3 +130,149 @@ def lf_inputs(name):
     project = lambda p: pj.pinhole_project(CAM, p)
     project_right = lambda p: pj.pinhole_project(CAM, pj.transform_point(Trl, p))
     return dict(Cur=Cur, last=last, Tcw=Tcw, th=th, fb=fb, ori=ori, project=project, project_right=project_right)
+
+
+# ---- KeyFrame-side searches (SearchByProjection(KeyFrame*, Scw, ...), Fuse, SearchBySim3) -------------------------
+LOG_SF = np.float32(np.log(np.float32(1.2)))
+INV_SIGMA2 = (1.0 / (SCALE.astype(np.float64) ** 2)).astype(np.float32)
+# name -> (seed, features, points, th, kind); kind: "sim3" :473, "fuse" :1629, "fuse_right" :1629 bRight, "fuse_sim3" :1823
+KF_CASES = {
+    "proj_kf_sim3": (4300, 1500, 1300, 4.0, "sim3"),
+    "proj_kf_sim3_ratio": (4301, 1200, 1000, 8.0, "sim3"),
+    "proj_kf_fuse": (4302, 1500, 1400, 3.0, "fuse"),
+    "proj_kf_fuse_right": (4303, 1600, 1200, 3.0, "fuse_right"),
+    "proj_kf_fuse_sim3": (4304, 1400, 1200, 4.0, "fuse_sim3"),
+}
+SIM3_CASES = {"proj_sim3_pair": (4400, 1300, 7.5)}
+
+
+def rodrigues(w):
+    w = np.asarray(w, np.float64)
+    th = np.linalg.norm(w)
+    if th < 1e-12:
+        return np.eye(3)
+    k = w / th
+    K = np.array([[0, -k[2], k[1]], [k[2], 0, -k[0]], [-k[1], k[0], 0]])
+    return np.eye(3) + np.sin(th) * K + (1 - np.cos(th)) * K @ K
+
+
+def pose(rng, rot=0.05, trans=0.3):
+    T = np.eye(4, dtype=np.float32)
+    T[:3, :3] = rodrigues(rng.normal(0, rot, 3)).astype(np.float32)
+    T[:3, 3] = rng.normal(0, trans, 3).astype(np.float32)
+    return T
+
+
+def points_seen_by(rng, KF, m, Tcw, lo_feat, hi_feat, compete=40, px_noise=1.5, flips=60):
+    """m world points whose projections (pinhole CAM, pose Tcw) fall next to features lo_feat..hi_feat of KF; every 5th
+    aims at one of `compete` features.  Returns the per-point arrays the flatteners read."""
+    R, t = Tcw[:3, :3].astype(np.float64), Tcw[:3, 3].astype(np.float64)
+    Ow = -R.T @ t
+    P = dict(bad=rng.random(m) < 0.03, world_pos=np.zeros((m, 3), np.float32), normal=np.zeros((m, 3), np.float32),
+             min_dist=np.zeros(m, np.float32), max_dist=np.zeros(m, np.float32), desc=np.zeros((m, 32), np.uint8),
+             src=np.zeros(m, np.int32))
+    for i in range(m):
+        src = int(rng.integers(lo_feat, hi_feat)) if i % 5 else int(rng.integers(lo_feat, min(hi_feat, lo_feat + compete)))
+        kp = KF.kps[src]
+        z = float(rng.uniform(0.8, 15.0)) if rng.random() < 0.97 else -2.0
+        u, v = kp["x"] + rng.normal(0, px_noise) * SCALE[kp["octave"]], kp["y"] + rng.normal(0, px_noise) * SCALE[kp["octave"]]
+        if rng.random() < 0.04:
+            u += 800
+        pc = np.array([(u - CAM[2]) / CAM[0] * z, (v - CAM[3]) / CAM[1] * z, z])
+        pw = R.T @ (pc - t)
+        P["world_pos"][i] = pw.astype(np.float32)
+        PO = pw - Ow
+        d = np.linalg.norm(PO)
+        nrm = PO / d if rng.random() < 0.9 else rodrigues(rng.normal(0, 1.0, 3)) @ (PO / d)     # some seen from the side
+        P["normal"][i] = nrm.astype(np.float32)
+        mx = d * 1.2 ** (kp["octave"] + rng.uniform(-0.9, 0.9)) if rng.random() < 0.95 else d * rng.uniform(0.3, 0.9)
+        P["max_dist"][i] = mx
+        P["min_dist"][i] = mx / 1.2 ** 7 if rng.random() < 0.95 else d * 1.5
+        P["desc"][i] = noisy_desc(rng, KF.desc[src], flips)
+        P["src"][i] = src
+    return P
+
+
+def kf_inputs(name):
+    seed, n, m, th, kind = KF_CASES[name]
+    rng = np.random.default_rng(seed)
+    rig = kind == "fuse_right"
+    KF = make_frame(rng, n, rig)
+    KF.inv_level_sigma2 = INV_SIGMA2
+    if rig:
+        KF.u_right = np.full(n, -1, np.float32)
+    Tcw = pose(rng)
+    nl = KF.nleft if rig else n
+    c = dict(KF=KF, th=th, kind=kind, Tcw=Tcw, project=lambda p: pj.pinhole_project(CAM, p))
+    if kind in ("sim3", "fuse_sim3"):
+        s = np.float32(1.07)
+        Scw = Tcw.copy()
+        Scw[:3, :] *= s
+        c["Scw"] = Scw
+        # the flatteners see Rcw, tcw after the decomposition; generate the points with exactly those
+        Rcw, tcw, _ = pj.decompose_sim3(Scw)
+        T = np.eye(4, dtype=np.float32)
+        T[:3, :3], T[:3, 3] = Rcw, tcw
+        pts = points_seen_by(rng, KF, m, T, 0, n)
+        pts["already_found"] = rng.random(m) < 0.1
+        if kind == "sim3":
+            KF.blocked = (rng.random(n) < 0.2).astype(np.uint8)           # vpMatched[idx] != NULL
+            c["ratio"] = 1.0 if name == "proj_kf_sim3" else 1.5
+    else:
+        lo, hi = (nl, n) if rig else (0, n)
+        pts = points_seen_by(rng, KF, m, Tcw, lo, hi)
+        pts["null"], pts["in_keyframe"] = rng.random(m) < 0.03, rng.random(m) < 0.1
+    c["pts"] = pts
+    return c
+
+
+def sim3_inputs(name):
+    """Two keyframes seeing a common set of points; KF2's camera = Sim3(s12, R12, t12)^-1 of KF1's."""
+    seed, n, th = SIM3_CASES[name]
+    rng = np.random.default_rng(seed)
+    KF1, KF2 = make_frame(rng, n, False), make_frame(rng, n, False)
+    T1w, T2w = pose(rng), pose(rng)
+    # x1 = s12 R12 x2 + t12 with x_i = T_iw X  =>  for s12 = 1: R12 = R1 R2^T, t12 = t1 - R12 t2
+    R1, R2 = T1w[:3, :3].astype(np.float64), T2w[:3, :3].astype(np.float64)
+    R12 = R1 @ R2.T
+    t12 = T1w[:3, 3].astype(np.float64) - R12 @ T2w[:3, 3].astype(np.float64)
+    out = dict(KF1=KF1, KF2=KF2, T1w=T1w, T2w=T2w, s12=np.float32(1.0), R12=R12.astype(np.float32), t12=t12.astype(np.float32), th=th)
+    # map points of KF1: half of them are also visible in KF2 next to a KF2 feature that carries a similar descriptor
+    m1 = points_seen_by(rng, KF1, n, T1w, 0, n, compete=n, px_noise=0.0, flips=20)
+    m2 = points_seen_by(rng, KF2, n, T2w, 0, n, compete=n, px_noise=0.0, flips=20)
+    for P, KFa, KFb, Tb in ((m1, KF1, KF2, T2w), (m2, KF2, KF1, T1w)):
+        # feature i of KFa observes P[i]: put the point of feature i where feature src[i] sat, then swap roles so that
+        # point i belongs to feature i (a permutation of the generated points)
+        order = np.argsort(P["src"], kind="stable")
+        _, first = np.unique(P["src"][order], return_index=True)
+        keep = order[first]                                   # one point per distinct feature
+        has = np.zeros(n, bool)
+        for k in list(P):
+            if k == "src":
+                continue
+            full = np.zeros((n,) + P[k].shape[1:], P[k].dtype)
+            full[P["src"][keep]] = P[k][keep]
+            P[k] = full
+        has[P.pop("src")[keep]] = True
+        P["has_mp"] = has
+        P["already_matched"] = rng.random(n) < 0.05
+    # make a third of KF1's points visible in KF2 as well: move a KF2 feature onto their projection, similar descriptor
+    proj = lambda T, p: pj.pinhole_project(CAM, pj.transform_point(T, p))
+    idx1 = np.flatnonzero(m1["has_mp"])
+    for i1 in idx1[: len(idx1) // 3 * 2]:
+        u, v = proj(T2w, m1["world_pos"][i1])
+        if not (4 < u < W - 4 and 4 < v < H - 4):
+            continue
+        i2 = int(rng.integers(0, n))
+        KF2.kps["x"][i2], KF2.kps["y"][i2] = snap(u + rng.normal(0, 1.0)), snap(v + rng.normal(0, 1.0))
+        KF2.kps["octave"][i2] = KF1.kps["octave"][i1]
+        KF2.desc[i2] = noisy_desc(rng, m1["desc"][i1], 30)
+        if rng.random() < 0.8:                                 # and KF2's own map point there is the same 3-D point
+            for k in ("world_pos", "normal", "min_dist", "max_dist"):
+                m2[k][i2] = m1[k][i1]
+            m2["desc"][i2], m2["has_mp"][i2], m2["bad"][i2] = noisy_desc(rng, m1["desc"][i1], 10), True, False
+    # vbAlreadyMatched2 is derived from vpMatches12 in the reference (:1977-1987): never more marks than in KF1
+    m2["already_matched"] = np.zeros(n, bool)
+    m2["already_matched"][rng.permutation(n)[: int(m1["already_matched"].sum()) // 2]] = True
+    out["mps1"], out["mps2"] = m1, m2
+    return out

@@ -95,3 +95,35 @@ def test_relocalisation_overload():
         assign, choice, n = orbfe.ORBmatcher(0.9, True).search_by_projection(c["Cur"], q, 0, orbdist, False, True)
         rassign, rchoice, rn = ob.search_by_projection(c["Cur"], q, 0, orbdist, 0.9, False, True)
         assert n == rn and np.array_equal(assign, rassign) and np.array_equal(choice, rchoice) and n > 60
+
+
+@pytest.mark.parametrize("name", list(pc.KF_CASES))
+def test_keyframe_side_searches(name):
+    """SearchByProjection(KeyFrame*, Scw, ...) :473, Fuse :1629 (chi-square gate, bRight) and :1823: GPU == oracle engine
+    on the same windows == object-level golden."""
+    from test_proj_oracle import run_kf
+    c = pc.kf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    res, n, q, choice = run_kf(c, gpu_search(0.9, False))
+    rres, rn, _, rchoice = run_kf(c, ob.search_by_projection)
+    assert n == rn and np.array_equal(choice, rchoice) and np.array_equal(res, rres)
+    key = "point_of_feature" if c["kind"] == "sim3" else "feature_of_point"
+    assert n == int(g["n"]) and np.array_equal(res, g[key])
+
+
+@pytest.mark.parametrize("name", list(pc.SIM3_CASES))
+def test_search_by_sim3(name):
+    from test_proj_oracle import run_sim3
+    c = pc.sim3_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    vn1, vn2, pairs, n = run_sim3(c, gpu_search(0.9, False))
+    assert np.array_equal(vn1, g["vnMatch1"]) and np.array_equal(vn2, g["vnMatch2"]) and n == int(g["n"])
+
+
+def test_chi2_needs_sigma_table():
+    c = pc.kf_inputs("proj_kf_fuse")
+    from test_proj_oracle import kf_windows
+    q, owner, th = kf_windows(c)
+    c["KF"].inv_level_sigma2 = None
+    with pytest.raises(orbfe.OrbfeError):
+        orbfe.ORBmatcher(0.9, False).search_by_projection(c["KF"], q, 0, th)

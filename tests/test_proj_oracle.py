@@ -78,3 +78,78 @@ def test_features_in_area_known_answers():
     assert ob.features_in_area(F, 2000, 100, 10, -1, -1, False).tolist() == []
     # the last feature rounds to grid cell (64, 48): PosInGrid drops it (Frame.cc:714)
     assert ob.features_in_area(F, 751, 479, 5, -1, -1, False).tolist() == []
+
+
+# ---- KeyFrame-side searches ----------------------------------------------------------------------------------------
+def kf_windows(c):
+    KF, pts, kind = c["KF"], c["pts"], c["kind"]
+    if kind in ("sim3", "fuse_sim3"):
+        q, owner = pj.queries_from_sim3_points(KF, pts, c["Scw"], c["th"], c["project"], pc.LOG_SF, claim=kind == "sim3")
+        th = pj.hamming_threshold(50, c["ratio"]) if kind == "sim3" else 50
+        return q, owner, th
+    T = c["Tcw"]
+    q, owner = pj.queries_for_fuse(KF, pts, T[:3, :3], T[:3, 3], pj.camera_centre(T[:3, :3], T[:3, 3]), c["th"], c["project"],
+                                   pc.LOG_SF, kind == "fuse_right")
+    return q, owner, 50
+
+
+def run_kf(c, search):
+    """Returns (what the golden stores, n, queries, choice)."""
+    q, owner, th = kf_windows(c)
+    assign, choice, n = search(c["KF"], q, 0, th, 0.9, False, False)
+    if c["kind"] == "sim3":
+        return owners(assign, owner), n, q, choice
+    out = np.full(len(c["pts"]["desc"]), -1, np.int32)
+    out[owner] = choice
+    return out, n, q, choice
+
+
+@pytest.mark.parametrize("name", list(pc.KF_CASES))
+def test_keyframe_side_searches_match_golden(name):
+    c = pc.kf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    assert crc(c["KF"].kps, c["KF"].desc, c["pts"]["desc"], c["pts"]["world_pos"]) == int(g["in_crc"])
+    res, n, q, choice = run_kf(c, ob.search_by_projection)
+    key = "point_of_feature" if c["kind"] == "sim3" else "feature_of_point"
+    assert n == int(g["n"]) and np.array_equal(res, g[key]) and n > 200
+    if c["kind"] == "sim3":                  # claiming windows: a feature is taken once, never a pre-matched one
+        taken = choice[choice >= 0]
+        assert len(set(taken.tolist())) == len(taken) and not c["KF"].blocked[taken].any()
+    else:                                    # Fuse never claims: several points may pick the same feature
+        taken = choice[choice >= 0]
+        assert len(set(taken.tolist())) < len(taken)
+    if c["kind"] == "fuse_right":
+        assert (choice[choice >= 0] >= c["KF"].nleft).all()
+
+
+def test_fuse_chi_square_gate_matters():
+    """Without the gate of ORBmatcher.cc:1744-1770 the same windows pick more (and different) features."""
+    c = pc.kf_inputs("proj_kf_fuse")
+    q, owner, th = kf_windows(c)
+    _, with_gate, n1 = ob.search_by_projection(c["KF"], q, 0, th, 0.9, False, False)
+    q2 = q.copy()
+    q2["chi2"] = 0
+    _, without, n2 = ob.search_by_projection(c["KF"], q2, 0, th, 0.9, False, False)
+    assert n2 > n1 and (with_gate != without).sum() > 50
+    # stereo features (mvuRight >= 0) use the 3-dof gate: moving `ur` far away rejects exactly those
+    q3 = q.copy()
+    q3["ur"] += 1000
+    _, far, n3 = ob.search_by_projection(c["KF"], q3, 0, th, 0.9, False, False)
+    picked = far[far >= 0]
+    assert n3 < n1 and (c["KF"].u_right[picked] < 0).all()
+
+
+def run_sim3(c, search):
+    f = lambda F, q, mode, th: search(F, q, mode, th, 0.9, False, False)
+    return pj.search_by_sim3(f, c["KF1"], c["KF2"], c["mps1"], c["mps2"], c["T1w"][:3], c["T2w"][:3], c["s12"], c["R12"], c["t12"],
+                             c["th"], pc.CAM, pc.LOG_SF)
+
+
+@pytest.mark.parametrize("name", list(pc.SIM3_CASES))
+def test_search_by_sim3_matches_golden(name):
+    c = pc.sim3_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    assert crc(c["KF1"].kps, c["KF2"].kps, c["mps1"]["desc"], c["mps2"]["world_pos"]) == int(g["in_crc"])
+    vn1, vn2, pairs, n = run_sim3(c, ob.search_by_projection)
+    assert np.array_equal(vn1, g["vnMatch1"]) and np.array_equal(vn2, g["vnMatch2"]) and n == int(g["n"]) and n > 100
+    assert n < (vn1 >= 0).sum()              # the agreement pass rejects some one-way matches
