@@ -366,6 +366,18 @@ typedef struct orbfe_proj_query {
 int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_frame* F, const orbfe_proj_query* queries, int nq, int mode,
                                int th, int link_stereo, int rot_hist, int32_t* assign, int32_t* choice);
 
+/* ORBmatcher::SearchForInitialization(Frame& F1, Frame& F2, vector<cv::Point2f>& vbPrevMatched, vector<int>& vnMatches12,
+ * int windowSize) (ORBmatcher.cc:706-821), the matcher of Tracking::MonocularInitialization (Tracking.cc:2569).
+ * kps1 / desc1 = F1.mvKeysUn / F1.mDescriptors [n1]; F2 = the frame whose grid is searched (kps = mvKeysUn, nleft = -1;
+ * blocked, u_right and the stereo links are not read).  prev_matched [n1][2] = vbPrevMatched: read as the window
+ * centres, and entries of matched features are overwritten with the matched F2 keypoint (:815-817).
+ * matches12 [n1] = vnMatches12 (-1 = none).  Uses the matcher's mfNNratio and mbCheckOrientation.  Only level-0
+ * keypoints of both frames take part; F1 features are processed as if one after another: a later feature with a
+ * strictly smaller distance takes over an F2 feature, one with a larger or equal distance does not see it.
+ * Returns nmatches or a negative status. */
+int orbfe_search_for_initialization(orbfe_matcher* m, const orbfe_keypoint* kps1, const uint8_t* desc1, int n1,
+                                    const orbfe_grid_frame* F2, float* prev_matched, int window_size, int32_t* matches12);
+
 /* ---- BoW transform ------------------------------------------------------------------
  * DBoW2::TemplatedVocabulary<FORB::TDescriptor, FORB> (= ORB_SLAM3::ORBVocabulary) flattened: node 0 is the
  * root, nodes 1.. in the order of the vocabulary text file (saveToTextFile / loadFromTextFile,

@@ -164,6 +164,20 @@ public:
         status_ = n < 0 ? n : ORBFE_OK;
         return n < 0 ? 0 : n;
     }
+    // ORBmatcher::SearchForInitialization (ORBmatcher.cc:706-821) on arrays: F1 = (mvKeysUn1, mDescriptors1), F2 as a grid
+    // frame (kps = mvKeysUn, nleft = -1, mnMinX / mnMinY / grid inverses).  vbPrevMatched and vnMatches12 as in the reference.
+    int SearchForInitializationArrays(const std::vector<cv::KeyPoint>& mvKeysUn1, const cv::Mat& mDescriptors1, const orbfe_grid_frame& F2,
+                                      std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12, int windowSize = 10) {
+        static_assert(sizeof(cv::Point2f) == 8 && sizeof(int) == sizeof(int32_t), "Point2f / int layout");
+        vnMatches12.assign(mvKeysUn1.size(), -1);
+        if (!m_ || mvKeysUn1.empty()) return 0;
+        if (vbPrevMatched.size() != mvKeysUn1.size()) { status_ = ORBFE_ERR_BAD_ARGUMENT; return 0; }
+        const int n = orbfe_search_for_initialization(m_, reinterpret_cast<const orbfe_keypoint*>(mvKeysUn1.data()), mDescriptors1.ptr(),
+                                                      (int)mvKeysUn1.size(), &F2, reinterpret_cast<float*>(vbPrevMatched.data()),
+                                                      windowSize, vnMatches12.data());
+        status_ = n < 0 ? n : ORBFE_OK;
+        return n < 0 ? 0 : n;
+    }
     // Frame::UndistortKeyPoints (Frame.cc:730-763).  K4 = fx, fy, cx, cy; dist = mDistCoef (4 or 5 floats).
     bool UndistortKeyPoints(const std::vector<cv::KeyPoint>& mvKeys, const float* K4, const float* dist, int ndist,
                             std::vector<cv::KeyPoint>& mvKeysUn) {
@@ -259,6 +273,14 @@ public:
         for (size_t i = 0; i < m.size(); ++i)
             if (m[i] >= 0) vpMatches12[i] = mp2[m[i]];
         return n;
+    }
+    int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
+                                int windowSize = 10) {
+        orbfe_grid_frame G = {};
+        G.kps = reinterpret_cast<const orbfe_keypoint*>(F2.mvKeysUn.data()); G.desc = F2.mDescriptors.data; G.n = (int)F2.mvKeysUn.size();
+        G.nleft = -1;
+        G.min_x = F2.mnMinX; G.min_y = F2.mnMinY; G.grid_w_inv = F2.mfGridElementWidthInv; G.grid_h_inv = F2.mfGridElementHeightInv;
+        return SearchForInitializationArrays(F1.mvKeysUn, F1.mDescriptors, G, vbPrevMatched, vnMatches12, windowSize);
     }
 #endif
 

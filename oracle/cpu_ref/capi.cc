@@ -253,6 +253,12 @@ int orbref_search_by_projection(const KeyPoint* kps, const uint8_t* desc, int n,
     ProjParams p{mode, th, nnRatio, linkStereo, rotHist};
     return searchByProjection(F, (const ProjQuery*)queries, nq, p, assign, choice);
 }
+int orbref_search_for_initialization(const KeyPoint* kps1, const uint8_t* desc1, int n1, const KeyPoint* kps2, const uint8_t* desc2,
+                                     int n2, float minX, float minY, float gridWInv, float gridHInv, float* prevMatched,
+                                     int windowSize, float nnRatio, int checkOri, int32_t* matches12) {
+    GridFrame F{kps2, desc2, n2, -1, nullptr, nullptr, nullptr, nullptr, minX, minY, gridWInv, gridHInv, nullptr};
+    return searchForInitialization(kps1, desc1, n1, F, prevMatched, windowSize, nnRatio, checkOri != 0, matches12);
+}
 int orbref_features_in_area(const KeyPoint* kps, int n, int nleft, float minX, float minY, float gridWInv, float gridHInv,
                             float x, float y, float r, int minLevel, int maxLevel, int bRight, int32_t* out) {
     GridFrame F{kps, nullptr, n, nleft, nullptr, nullptr, nullptr, nullptr, minX, minY, gridWInv, gridHInv, nullptr};

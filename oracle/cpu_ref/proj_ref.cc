@@ -2,6 +2,7 @@
 #include "proj_ref.h"
 
 #include <algorithm>
+#include <climits>
 #include <cmath>
 
 #include "match_ref.h"
@@ -115,6 +116,49 @@ int searchByProjection(const GridFrame& F, const ProjQuery* q, int nq, const Pro
             for (int idx : rotHist[i]) { assign[idx] = -2; nmatches--; }
         }
     }
+    return nmatches;
+}
+
+int searchForInitialization(const KeyPoint* kps1, const uint8_t* desc1, int n1, const GridFrame& F2, float* prevMatched,
+                            int windowSize, float nnRatio, bool checkOri, int32_t* matches12) {
+    FrameGrid grid(F2);
+    int nmatches = 0;
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    std::vector<int> rotHist[HISTO_LENGTH];
+    std::vector<int> vMatchedDistance(F2.n, INT_MAX), vnMatches21(F2.n, -1), cand;
+    for (int i1 = 0; i1 < n1; ++i1) {
+        const int level1 = kps1[i1].octave;
+        if (level1 > 0) continue;                                                              // :724-725
+        grid.featuresInArea(prevMatched[2 * i1], prevMatched[2 * i1 + 1], (float)windowSize, level1, level1, false, cand);
+        if (cand.empty()) continue;
+        int bestDist = INT_MAX, bestDist2 = INT_MAX, bestIdx2 = -1;
+        for (int i2 : cand) {
+            const int dist = descriptorDistanceSwar(desc1 + 32 * (size_t)i1, F2.desc + 32 * (size_t)i2);
+            if (vMatchedDistance[i2] <= dist) continue;                                        // :744
+            if (dist < bestDist) { bestDist2 = bestDist; bestDist = dist; bestIdx2 = i2; }
+            else if (dist < bestDist2) bestDist2 = dist;
+        }
+        if (bestDist > TH_LOW) continue;
+        if (!((float)bestDist < (float)bestDist2 * nnRatio)) continue;
+        if (vnMatches21[bestIdx2] >= 0) { matches12[vnMatches21[bestIdx2]] = -1; nmatches--; }
+        matches12[i1] = bestIdx2;
+        vnMatches21[bestIdx2] = i1;
+        vMatchedDistance[bestIdx2] = bestDist;
+        nmatches++;
+        if (checkOri) rotHist[rotBin(kps1[i1].angle, F2.kps[bestIdx2].angle)].push_back(i1);
+    }
+    if (checkOri) {
+        int counts[HISTO_LENGTH], ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < HISTO_LENGTH; ++i) counts[i] = (int)rotHist[i].size();
+        computeThreeMaxima(counts, HISTO_LENGTH, ind1, ind2, ind3);
+        for (int i = 0; i < HISTO_LENGTH; i++) {
+            if (i == ind1 || i == ind2 || i == ind3) continue;
+            for (int idx1 : rotHist[i])
+                if (matches12[idx1] >= 0) { matches12[idx1] = -1; nmatches--; }
+        }
+    }
+    for (int i1 = 0; i1 < n1; ++i1)
+        if (matches12[i1] >= 0) { prevMatched[2 * i1] = F2.kps[matches12[i1]].x; prevMatched[2 * i1 + 1] = F2.kps[matches12[i1]].y; }
     return nmatches;
 }
 

@@ -74,4 +74,11 @@ private:
 // (global index) or -1.  Returns nmatches as the reference counts it.
 int searchByProjection(const GridFrame& F, const ProjQuery* q, int nq, const ProjParams& p, int32_t* assign, int32_t* choice);
 
+// ORBmatcher::SearchForInitialization (src/ORBmatcher.cc:706-821): F1 = (kps1 = mvKeysUn, desc1), F2 = the Frame whose
+// grid is searched; prevMatched [n1][2] = vbPrevMatched, updated in place (:815-817); matches12 [n1] = vnMatches12.
+// Only level-0 features of both frames take part (:721-725).  A later F1 feature with a strictly smaller distance
+// steals an F2 feature (:757-768); candidates whose recorded distance is <= the new one are invisible (:744).
+int searchForInitialization(const KeyPoint* kps1, const uint8_t* desc1, int n1, const GridFrame& F2, float* prevMatched,
+                            int windowSize, float nnRatio, bool checkOri, int32_t* matches12);
+
 }  // namespace orbref

@@ -200,5 +200,26 @@ def main():
         print(name, "nFound", g["n"], "one-way", int((g["vnMatch1"] >= 0).sum()), int((g["vnMatch2"] >= 0).sum()))
 
 
+def golden_init(name):
+    c = pc.init_inputs(name)
+    fr = lambda G: pp.Frame(G.kps, G.desc, G.scale_factors, (G.min_x, G.min_y, G.max_x, G.max_y))
+    prev = [list(p) for p in c["prev"]]
+    n, v12 = pp.search_for_initialization(fr(c["F1"]), fr(c["F2"]), prev, c["win"], c["nnratio"], c["ori"])
+    return dict(n=n, vnMatches12=np.array(v12, np.int32), prev_matched=np.array(prev, np.float32),
+                in_crc=crc(c["F1"].kps, c["F1"].desc, c["F2"].kps, c["F2"].desc, c["prev"]))
+
+
+def main_init():
+    out = os.path.join(ROOT, "tests", "golden")
+    for name in pc.INIT_CASES:
+        g = golden_init(name)
+        np.savez_compressed(os.path.join(out, f"{name}.npz"), **g)
+        print(name, "nmatches", g["n"], "matched", int((g["vnMatches12"] >= 0).sum()))
+
+
 if __name__ == "__main__":
+    if "--init-only" in sys.argv:
+        main_init()
+        sys.exit(0)
     main()
+    main_init()

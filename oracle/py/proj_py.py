@@ -3,7 +3,7 @@
 Follows src/Frame.cc (AssignFeaturesToGrid :380-411, GetFeaturesInArea :640-706, PosInGrid :708-719) and
 src/ORBmatcher.cc: SearchByProjection(Frame&, const vector<MapPoint*>&, th, bFarPoints, thFarPoints) :44-236,
 RadiusByViewingCos :238-244, SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono)
-:2173-2389, and the KeyFrame-side searches SearchByProjection(KeyFrame*, Scw, ...) :473-585, Fuse :1629-1821 /
+:2173-2389, SearchForInitialization :706-821, and the KeyFrame-side searches SearchByProjection(KeyFrame*, Scw, ...) :473-585, Fuse :1629-1821 /
 :1823-1945, SearchBySim3 :1947-2171.  Frames and MapPoints are small Python objects with the reference's member names; float32
 arithmetic is spelled out with numpy scalars.  Written independently of oracle/cpu_ref/proj_ref.cc (which
 works on the flattened windows); the golden fixtures come from this file.
@@ -295,6 +295,59 @@ def search_by_projection_lastframe(Cur, Last, th, bMono, check_ori, project, x3D
                     Cur.mvpMapPoints[idx] = None
                     nmatches -= 1
     return nmatches
+
+
+def search_for_initialization(F1, F2, vbPrevMatched, windowSize, nnratio, check_ori):
+    """ORBmatcher::SearchForInitialization, ORBmatcher.cc:706-821.  F1 / F2: Frames whose `keys` are mvKeysUn.
+    vbPrevMatched: list of [x, y] float32 pairs, updated in place (:815-817).  Returns (nmatches, vnMatches12)."""
+    INT_MAX = 2147483647
+    nmatches = 0
+    vnMatches12 = [-1] * F1.N
+    rotHist = [[] for _ in range(HISTO_LENGTH)]
+    vMatchedDistance = [INT_MAX] * F2.N
+    vnMatches21 = [-1] * F2.N
+    for i1 in range(F1.N):
+        kp1 = F1.keys[i1]
+        level1 = int(kp1["octave"])
+        if level1 > 0:
+            continue
+        vIndices2 = F2.GetFeaturesInArea(vbPrevMatched[i1][0], vbPrevMatched[i1][1], windowSize, level1, level1)
+        if not vIndices2:
+            continue
+        d1 = F1.mDescriptors[i1]
+        bestDist, bestDist2, bestIdx2 = INT_MAX, INT_MAX, -1
+        for i2 in vIndices2:
+            dist = descriptor_distance(d1, F2.mDescriptors[i2])
+            if vMatchedDistance[i2] <= dist:
+                continue
+            if dist < bestDist:
+                bestDist2, bestDist, bestIdx2 = bestDist, dist, i2
+            elif dist < bestDist2:
+                bestDist2 = dist
+        if bestDist <= TH_LOW:
+            if F32(bestDist) < F32(F32(bestDist2) * F32(nnratio)):
+                if vnMatches21[bestIdx2] >= 0:
+                    vnMatches12[vnMatches21[bestIdx2]] = -1
+                    nmatches -= 1
+                vnMatches12[i1] = bestIdx2
+                vnMatches21[bestIdx2] = i1
+                vMatchedDistance[bestIdx2] = bestDist
+                nmatches += 1
+                if check_ori:
+                    rotHist[rot_bin(F1.keys[i1]["angle"], F2.keys[bestIdx2]["angle"])].append(i1)
+    if check_ori:
+        keep = compute_three_maxima([len(h) for h in rotHist])
+        for i in range(HISTO_LENGTH):
+            if i in keep:
+                continue
+            for idx1 in rotHist[i]:
+                if vnMatches12[idx1] >= 0:
+                    vnMatches12[idx1] = -1
+                    nmatches -= 1
+    for i1 in range(F1.N):
+        if vnMatches12[i1] >= 0:
+            vbPrevMatched[i1] = [F2.keys[vnMatches12[i1]]["x"], F2.keys[vnMatches12[i1]]["y"]]
+    return nmatches, vnMatches12
 
 
 # ---- KeyFrame-side searches (loop closing, merging, local mapping) -------------------------------------------------

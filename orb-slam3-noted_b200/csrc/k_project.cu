@@ -63,8 +63,12 @@ __device__ __forceinline__ Window window_cells(const ProjProblem& P, const ProjQ
 
 // Visits the candidates of window i that lane `lane` of `nlanes` owns, in cell order; f(key, idx).
 // blockedAt == nullptr: only the caller's static mask applies.
-template <class F>
-__device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lane, int nlanes, const int* __restrict__ blockedAt, F f) {
+struct AlwaysVisible { __device__ __forceinline__ bool operator()(int, int) const { return true; } };
+
+// vis(idx, dist): evaluated after the distance, false = the candidate is skipped (SearchForInitialization :744).
+template <class F, class V = AlwaysVisible>
+__device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lane, int nlanes, const int* __restrict__ blockedAt, F f,
+                                            V vis = V()) {
     const ProjQueryDev& Q = P.q[i];
     const Window w = window_cells(P, Q);
     if (w.minCX > w.maxCX) return;
@@ -107,6 +111,7 @@ __device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lan
                 if ((double)__fmul_rn(e2, P.invSigma2[oct]) > gate) continue;
             }
             const int dist = ham_q(a0, a1, P.desc + 32ll * idx);
+            if (!vis(idx, dist)) continue;
             f((unsigned long long)dist << 40 | (unsigned long long)e << 16 | (unsigned)idx);
         }
     }
@@ -322,6 +327,142 @@ __global__ void __launch_bounds__(PROJ_T) k_proj_resolve(const ProjProblem* __re
     atomicAdd(&sCount, cnt);
     __syncthreads();
     if (tid == 0) *P.nmatches = sCount;
+}
+
+// ---- 3b. SearchForInitialization (ORBmatcher.cc:706-821): one window per F1 feature, windows in index order.
+// The reference keeps, per F2 feature, the distance of its current match (vMatchedDistance) and hides the feature
+// from any later window whose distance is not strictly smaller (:744); a later, closer window steals it (:757-768).
+// Same Jacobi scheme as k_proj_resolve: in every sweep the accepted windows of the previous sweep are chained per
+// feature (head / next), window i treats a candidate as visible iff no window j < i on that chain has
+// dist_j <= dist, and takes the two smallest visible keys of its list.  Sweep k makes windows < k final.
+// Afterwards: vnMatches12[i] survives iff i is the LAST window that chose its feature; the rotation histogram
+// counts every accepted window, stolen or not (rotHist[bin].push_back(i1) is never undone, :772-781).
+__global__ void __launch_bounds__(PROJ_T) k_init_resolve(const ProjProblem* __restrict__ probs, int th, float nnRatio, int rotHist) {
+    __shared__ int hist[ORBFE_HISTO_LENGTH];
+    __shared__ int keep[3];
+    __shared__ int sChanged, sCount;
+    const ProjProblem P = probs[blockIdx.x];
+    const int tid = threadIdx.x;
+    const int n = P.n, nq = P.nq;
+    int* head = P.scratch;                            // n: newest claimant of each F2 feature (previous sweep)
+    int* chA = head + n;                              // nq: choice
+    int* chB = chA + nq;
+    int* dA = chB + nq;                               // nq: distance of the choice
+    int* dB = dA + nq;
+    int* next = P.assign;                             // nq <= capacity of assign (the API sizes it max(n, nq))
+    for (int i = tid; i < nq; i += PROJ_T) { chA[i] = -1; dA[i] = 0; }
+    __syncthreads();
+    int* chOld = chA; int* chNew = chB; int* dOld = dA; int* dNew = dB;
+    for (int sweep = 0; sweep <= nq; ++sweep) {
+        for (int t = tid; t < n; t += PROJ_T) head[t] = -1;
+        if (tid == 0) sChanged = 0;
+        __syncthreads();
+        for (int i = tid; i < nq; i += PROJ_T) {
+            const int c = chOld[i];
+            if (c >= 0) next[i] = atomicExch(&head[c], i);
+        }
+        __syncthreads();
+        auto visible = [&](int i, int idx, int dist) {
+            for (int j = head[idx]; j >= 0; j = next[j])
+                if (j < i && dOld[j] <= dist) return false;
+            return true;
+        };
+        int changed = 0;
+        for (int i = tid; i < nq; i += PROJ_T) {
+            int res = -1, resDist = 0;
+            if (P.q[i].valid) {
+                const unsigned long long* list = P.cand + (long long)i * PROJ_K;
+                const unsigned long long lim = P.limit[i];
+                unsigned long long k1 = ~0ull, k2 = ~0ull;
+                bool complete = false;
+                for (int s = 0; s < PROJ_K; ++s) {
+                    const unsigned long long k = list[s];
+                    if (k == ~0ull) { complete = lim == ~0ull; break; }
+                    if (k >= lim) break;
+                    if (!visible(i, (int)(k & 0xFFFFu), (int)(k >> 40))) continue;
+                    if (k1 == ~0ull) k1 = k;
+                    else { k2 = k; complete = true; break; }
+                }
+                if (!complete && lim == ~0ull) complete = true;
+                if (!complete) {
+                    k1 = ~0ull; k2 = ~0ull;
+                    scan_window(P, i, 0, 1, nullptr, [&](unsigned long long k) { top2_insert(k1, k2, k); },
+                                [&](int idx, int dist) { return visible(i, idx, dist); });
+                }
+                if (k1 != ~0ull) {
+                    const int bestDist = (int)(k1 >> 40);
+                    const float second = k2 == ~0ull ? 2147483648.0f : (float)(int)(k2 >> 40);      // (float)INT_MAX
+                    if (bestDist <= th && (float)bestDist < __fmul_rn(second, nnRatio)) { res = (int)(k1 & 0xFFFFu); resDist = bestDist; }
+                }
+            }
+            if (res != chOld[i] || resDist != dOld[i]) changed = 1;
+            chNew[i] = res; dNew[i] = resDist;
+        }
+        if (changed) sChanged = 1;
+        __syncthreads();
+        int* t1 = chOld; chOld = chNew; chNew = t1;
+        int* t2 = dOld; dOld = dNew; dNew = t2;
+        const int any = sChanged;
+        __syncthreads();
+        if (!any) break;
+    }
+    // finish: head[f] <- last window that chose f (vnMatches21)
+    for (int t = tid; t < n; t += PROJ_T) head[t] = -1;
+    if (tid < ORBFE_HISTO_LENGTH) hist[tid] = 0;
+    if (tid == 0) sCount = 0;
+    __syncthreads();
+    for (int i = tid; i < nq; i += PROJ_T) {
+        const int c = chOld[i];
+        if (c < 0) continue;
+        atomicMax(&head[c], i);
+        if (rotHist) atomicAdd(&hist[rot_bin_p(P.q[i].angle, P.kp[c].z)], 1);
+    }
+    __syncthreads();
+    if (rotHist && tid == 0) {
+        int max1 = 0, max2 = 0, max3 = 0, ind1 = -1, ind2 = -1, ind3 = -1;
+        for (int i = 0; i < ORBFE_HISTO_LENGTH; i++) {
+            const int s = hist[i];
+            if (s > max1) { max3 = max2; max2 = max1; max1 = s; ind3 = ind2; ind2 = ind1; ind1 = i; }
+            else if (s > max2) { max3 = max2; max2 = s; ind3 = ind2; ind2 = i; }
+            else if (s > max3) { max3 = s; ind3 = i; }
+        }
+        if ((float)max2 < __fmul_rn(0.1f, (float)max1)) { ind2 = -1; ind3 = -1; }
+        else if ((float)max3 < __fmul_rn(0.1f, (float)max1)) { ind3 = -1; }
+        keep[0] = ind1; keep[1] = ind2; keep[2] = ind3;
+    }
+    __syncthreads();
+    int cnt = 0;
+    for (int i = tid; i < nq; i += PROJ_T) {
+        int c = chOld[i];
+        if (c >= 0 && head[c] != i) c = -1;                        // stolen by a later window (:759-763)
+        if (c >= 0 && rotHist) {
+            const int bin = rot_bin_p(P.q[i].angle, P.kp[c].z);
+            if (!(bin == keep[0] || bin == keep[1] || bin == keep[2])) c = -1;
+        }
+        P.choice[i] = c;
+        if (c >= 0) ++cnt;
+    }
+    atomicAdd(&sCount, cnt);
+    __syncthreads();
+    if (tid == 0) *P.nmatches = sCount;
+}
+
+cudaError_t orbfe_launch_search_for_initialization(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int th,
+                                                   float nnRatio, int rotHist, long long* launches) {
+    if (nprob <= 0) return cudaSuccess;
+    int np2 = 1;
+    while (np2 < nMax) np2 <<= 1;
+    const size_t smem = (size_t)np2 * 4;
+    if (smem > 48 * 1024) {
+        cudaError_t e = cudaFuncSetAttribute(k_proj_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+    }
+    k_proj_grid<<<nprob, PROJ_T, smem, st>>>(dProbs);
+    dim3 grid((nqMax + 7) / 8, nprob);
+    k_proj_candidates<<<grid, 256, 0, st>>>(dProbs);
+    k_init_resolve<<<nprob, PROJ_T, 0, st>>>(dProbs, th, nnRatio, rotHist);
+    *launches += 3;
+    return cudaGetLastError();
 }
 
 cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int mode,

@@ -77,6 +77,9 @@ struct ProjProblem {
 cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int mode,
                                               int th, float nnRatio, int linkStereo, int rotHist, long long* launches);
 
+cudaError_t orbfe_launch_search_for_initialization(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int th,
+                                                   float nnRatio, int rotHist, long long* launches);
+
 // SearchForTriangulation with Kannala-Brandt cameras: cameras [0] = mpCamera, [1] = mpCamera2 of each
 // keyframe, relative poses {ll, lr, rl, rr} (x1 = R12 x2 + t12), NLeft of both keyframes (-1: one camera).
 struct TriKb8Geo {

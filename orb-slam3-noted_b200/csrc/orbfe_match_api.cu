@@ -636,6 +636,81 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     return *reinterpret_cast<int*>(hs + oCnt);
 }
 
+// ORBmatcher::SearchForInitialization (ORBmatcher.cc:706-821): one level-0 window per F1 feature around vbPrevMatched.
+extern "C" int orbfe_search_for_initialization(orbfe_matcher* m, const orbfe_keypoint* kps1, const uint8_t* desc1, int n1,
+                                               const orbfe_grid_frame* F2, float* prev_matched, int window_size, int32_t* matches12) {
+    if (!m || !F2 || n1 < 0 || F2->n < 0 || window_size < 0) return ORBFE_ERR_BAD_ARGUMENT;
+    if (n1 > 0 && (!kps1 || !desc1 || !prev_matched || !matches12)) return ORBFE_ERR_BAD_ARGUMENT;
+    if (F2->n > 0 && (!F2->kps || !F2->desc)) return ORBFE_ERR_BAD_ARGUMENT;
+    if (F2->n > 16384 || n1 > (1 << 24)) return ORBFE_ERR_TOO_LARGE;
+    const int n = F2->n, nq = n1;
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    if (n == 0 || nq == 0) return 0;
+    CK(cudaSetDevice(m->device));
+    size_t u = 0;
+    const size_t oKp = stage_take(u, sizeof(float4) * n), oDesc = stage_take(u, 32 * (size_t)n);
+    const size_t oQ = stage_take(u, sizeof(ProjQueryDev) * (size_t)nq), oProb = stage_take(u, sizeof(ProjProblem));
+    const size_t inBytes = u;
+    const size_t oSorted = stage_take(u, sizeof(uint32_t) * n), oCell = stage_take(u, sizeof(int) * 4 * 3072);
+    const size_t oCand = stage_take(u, sizeof(unsigned long long) * (size_t)nq * PROJ_K), oLim = stage_take(u, sizeof(unsigned long long) * (size_t)nq);
+    const size_t oScr = stage_take(u, sizeof(int) * ((size_t)n + 4 * (size_t)nq));
+    const size_t oAsg = stage_take(u, sizeof(int32_t) * (size_t)std::max(n, nq));      // claim chains of k_init_resolve
+    const size_t oOut = stage_take(u, 0);
+    const size_t oCh = stage_take(u, sizeof(int32_t) * (size_t)nq), oCnt = stage_take(u, 4);
+    int st = ensure_stage(m, u);
+    if (st != ORBFE_OK) return st;
+    CK(cudaStreamSynchronize(m->stream));
+    uint8_t* hs = m->hStage;
+    uint8_t* ds = m->dStage;
+    float4* kp = reinterpret_cast<float4*>(hs + oKp);
+    for (int i = 0; i < n; ++i) {
+        float4 v = make_float4(F2->kps[i].x, F2->kps[i].y, F2->kps[i].angle, 0.f);
+        memcpy(&v.w, &F2->kps[i].octave, 4);
+        kp[i] = v;
+    }
+    memcpy(hs + oDesc, F2->desc, 32 * (size_t)n);
+    ProjQueryDev* q = reinterpret_cast<ProjQueryDev*>(hs + oQ);
+    memset(q, 0, sizeof(ProjQueryDev) * (size_t)nq);
+    for (int i = 0; i < nq; ++i) {
+        ProjQueryDev& e = q[i];
+        e.u = prev_matched[2 * i];
+        e.v = prev_matched[2 * i + 1];
+        e.r = (float)window_size;
+        e.angle = kps1[i].angle;
+        e.minLevel = 0;                               // GetFeaturesInArea(x, y, windowSize, level1, level1), level1 == 0 (:721-727)
+        e.maxLevel = 0;
+        e.valid = kps1[i].octave > 0 ? 0 : 1;
+        memcpy(e.desc, desc1 + 32 * (size_t)i, 32);
+    }
+    ProjProblem P;
+    memset(&P, 0, sizeof(P));
+    P.kp = reinterpret_cast<const float4*>(ds + oKp);
+    P.desc = ds + oDesc;
+    P.n = n; P.nleft = -1;
+    P.minX = F2->min_x; P.minY = F2->min_y; P.gridWInv = F2->grid_w_inv; P.gridHInv = F2->grid_h_inv;
+    P.q = reinterpret_cast<const ProjQueryDev*>(ds + oQ);
+    P.nq = nq;
+    P.assign = reinterpret_cast<int32_t*>(ds + oAsg);
+    P.choice = reinterpret_cast<int32_t*>(ds + oCh);
+    P.nmatches = reinterpret_cast<int*>(ds + oCnt);
+    P.sorted = reinterpret_cast<uint32_t*>(ds + oSorted);
+    P.cellStart = reinterpret_cast<int*>(ds + oCell);
+    P.cellEnd = P.cellStart + 2 * 3072;
+    P.cand = reinterpret_cast<unsigned long long*>(ds + oCand);
+    P.limit = reinterpret_cast<unsigned long long*>(ds + oLim);
+    P.scratch = reinterpret_cast<int*>(ds + oScr);
+    memcpy(hs + oProb, &P, sizeof(P));
+    CK(cudaMemcpyAsync(ds, hs, inBytes, cudaMemcpyHostToDevice, m->stream));
+    CK(orbfe_launch_search_for_initialization(m->stream, reinterpret_cast<const ProjProblem*>(ds + oProb), 1, n, nq, ORBFE_TH_LOW,
+                                              m->nnRatio, m->checkOri ? 1 : 0, &m->launches));
+    CK(cudaMemcpyAsync(hs + oOut, ds + oOut, u - oOut, cudaMemcpyDeviceToHost, m->stream));
+    CK(cudaStreamSynchronize(m->stream));
+    memcpy(matches12, hs + oCh, sizeof(int32_t) * (size_t)nq);
+    for (int i = 0; i < nq; ++i)                      // :815-817
+        if (matches12[i] >= 0) { prev_matched[2 * i] = F2->kps[matches12[i]].x; prev_matched[2 * i + 1] = F2->kps[matches12[i]].y; }
+    return *reinterpret_cast<int*>(hs + oCnt);
+}
+
 // ---- Kannala-Brandt fisheye stereo ----------------------------------------------------------------------
 extern "C" int orbfe_fisheye_stereo_match(orbfe_matcher* m, const orbfe_keypoint* kps_left, const uint8_t* desc_left, int n_left,
                                           int mono_left, const orbfe_keypoint* kps_right, const uint8_t* desc_right, int n_right,

@@ -36,6 +36,7 @@ PROTO = {
     "orbfe_undistort_keypoints": (_I, [_P, _P, _I, _P, _P, _I, _P]),
     "orbfe_distinctive_descriptors": (_I, [_P, _P, _P, _I, _P]),
     "orbfe_search_by_projection": (_I, [_P, _P, _P, _I, _I, _I, _I, _I, _P, _P]),
+    "orbfe_search_for_initialization": (_I, [_P, _P, _P, _I, _P, _P, _I, _P]),
     "orbfe_vocabulary_create": (_I, [_I, _I, _I, _I, _I, _P, _P, _P, _P, _I, C.POINTER(_P)]),
     "orbfe_vocabulary_load_text": (_I, [C.c_char_p, _I, _I, C.POINTER(_P)]),
     "orbfe_vocabulary_destroy": (None, [_P]),

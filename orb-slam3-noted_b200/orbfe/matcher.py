@@ -288,6 +288,25 @@ class ORBmatcher:
             raise OrbfeError(n, "orbfe_search_by_projection")
         return assign[:F.n], choice[:len(q)], n
 
+    def SearchForInitialization(self, kps1, desc1, F2, vbPrevMatched, windowSize=10):
+        """ORBmatcher::SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (ORBmatcher.cc:706-821).
+        kps1 / desc1 = F1.mvKeysUn / F1.mDescriptors, F2 = projection.GridFrame of the second frame, vbPrevMatched
+        (n1, 2) float32.  Returns (nmatches, vnMatches12, updated vbPrevMatched)."""
+        from ._lib import KEYPOINT_DTYPE
+        k1 = np.ascontiguousarray(kps1, KEYPOINT_DTYPE)
+        d1 = np.ascontiguousarray(desc1, np.uint8).reshape(-1, 32)
+        prev = np.array(vbPrevMatched, np.float32).reshape(-1, 2).copy()
+        if len(d1) != len(k1) or len(prev) != len(k1):
+            raise ValueError("SearchForInitialization: kps1, desc1 and vbPrevMatched must have one row per F1 feature")
+        g = GridFrameC()
+        g.kps, g.desc, g.n, g.nleft = _p(F2.kps), _p(F2.desc), F2.n, -1
+        g.min_x, g.min_y, g.grid_w_inv, g.grid_h_inv = float(F2.min_x), float(F2.min_y), float(F2.grid_w_inv), float(F2.grid_h_inv)
+        m12 = np.full(max(len(k1), 1), -1, np.int32)
+        n = self._lib.orbfe_search_for_initialization(self._m, _p(k1), _p(d1), len(k1), C.byref(g), _p(prev), int(windowSize), _p(m12))
+        if n < 0:
+            raise OrbfeError(n, "orbfe_search_for_initialization")
+        return n, m12[:len(k1)], prev
+
     def SearchForTriangulationKB8(self, desc1, fv1, has_mp1, kps1, desc2, fv2, has_mp2, kps2, cam_a, cam_b, nleft_a, nleft_b, R12,
                                   t12, epipole, sigma2_a, sigma2_b, scale_b, bOnlyStereo=False, bCoarse=False):
         """ORBmatcher::SearchForTriangulation_ (ORBmatcher.cc:1208-1432) for Kannala-Brandt keyframes

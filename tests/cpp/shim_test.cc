@@ -122,6 +122,15 @@ int main(int argc, char** argv) {
         std::vector<int32_t> offs = {0, std::min(5, dL.rows), std::min(5, dL.rows), std::min(40, dL.rows)}, best;
         if (!matcher.ComputeDistinctiveDescriptors(dL, offs, best) || best.size() != 3 || best[1] != -1) return 1;
         fwrite(best.data(), 4, 3, o);
+        // SearchForInitialization: left frame -> right frame, windows of 40 px around the left positions
+        std::vector<cv::Point2f> prev(kL.size());
+        for (size_t i = 0; i < kL.size(); ++i) prev[i] = kL[i].pt;
+        std::vector<int> m12;
+        const int32_t ni = matcher.SearchForInitializationArrays(kL, dL, F, prev, m12, 40);
+        if (matcher.lastStatus() != ORBFE_OK || m12.size() != kL.size()) return 1;
+        fwrite(&ni, 4, 1, o);
+        fwrite(m12.data(), 4, m12.size(), o);
+        fwrite(prev.data(), 8, prev.size(), o);
     }
     if (argc == 10) {
         ORBVocabulary voc;

@@ -292,6 +292,19 @@ def search_by_projection(F, queries, mode, th, nnratio, link_stereo, rot_hist):
     return assign[:F.n], choice[:len(q)], n
 
 
+def search_for_initialization(kps1, desc1, F2, prev_matched, window_size, nnratio, check_ori):
+    """oracle/cpu_ref/proj_ref.cc searchForInitialization.  Returns (nmatches, vnMatches12, updated vbPrevMatched)."""
+    L_ = lib()
+    L_.orbref_search_for_initialization.argtypes = [_P, _P, _I, _P, _P, _I, _F, _F, _F, _F, _P, _I, _F, _I, _P]
+    kps1, desc1 = np.ascontiguousarray(kps1), np.ascontiguousarray(desc1, np.uint8)
+    prev = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+    m12 = np.zeros(max(len(kps1), 1), np.int32)
+    n = L_.orbref_search_for_initialization(_p(kps1), _p(desc1), len(kps1), _p(F2.kps), _p(F2.desc), F2.n, float(F2.min_x),
+                                            float(F2.min_y), float(F2.grid_w_inv), float(F2.grid_h_inv), _p(prev), int(window_size),
+                                            float(nnratio), int(check_ori), _p(m12))
+    return n, m12[:len(kps1)], prev
+
+
 def features_in_area(F, x, y, r, min_level, max_level, right):
     L_ = lib()
     L_.orbref_features_in_area.argtypes = [_P, _I, _I, _F, _F, _F, _F, _F, _F, _F, _I, _I, _I, _P]

@@ -276,3 +276,38 @@ def sim3_inputs(name):
     m2["already_matched"][rng.permutation(n)[: int(m1["already_matched"].sum()) // 2]] = True
     out["mps1"], out["mps2"] = m1, m2
     return out
+
+
+# SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) :706: name -> (seed, n1, n2, windowSize, nnratio, check_ori)
+INIT_CASES = {
+    "proj_init_w100": (4500, 2000, 2200, 100, 0.9, True),
+    "proj_init_w30_noori": (4501, 1500, 1500, 30, 0.8, False),
+}
+
+
+def init_inputs(name=None, spec=None):
+    """F2's level-0 features are the sources; an F1 feature copies one (position within the window, descriptor with
+    up to 45 flipped bits).  Every 3rd F1 feature competes for one of 60 sources, so matches are stolen by later,
+    closer descriptors, later but farther ones see vMatchedDistance[i2] <= dist and fall back to their next
+    candidate; some sources get a near-duplicate neighbour so the ratio test fires."""
+    seed, n1, n2, win, nnratio, ori = spec if spec is not None else INIT_CASES[name]
+    rng = np.random.default_rng(seed)
+    F2 = make_frame(rng, n2, False)
+    lvl0 = np.flatnonzero(F2.kps["octave"] == 0)
+    for s in lvl0[:: 7]:                                       # near-duplicates: same place, descriptor a few bits away
+        t = int(rng.integers(0, n2))
+        F2.kps["x"][t], F2.kps["y"][t] = snap(F2.kps["x"][s] + rng.normal(0, 2.0)), snap(F2.kps["y"][s] + rng.normal(0, 2.0))
+        F2.kps["octave"][t] = 0
+        F2.desc[t] = noisy_desc(rng, F2.desc[s], 12)
+    lvl0 = np.flatnonzero(F2.kps["octave"] == 0)
+    F1 = make_frame(rng, n1, False)
+    prev = np.zeros((n1, 2), np.float32)
+    for i in range(n1):
+        if rng.random() < 0.75:
+            s = int(lvl0[int(rng.integers(0, len(lvl0))) if i % 3 else int(rng.integers(0, min(60, len(lvl0))))])
+            F1.kps["x"][i] = snap(np.clip(F2.kps["x"][s] + rng.normal(0, win / 4), 1, W - 1))
+            F1.kps["y"][i] = snap(np.clip(F2.kps["y"][s] + rng.normal(0, win / 4), 1, H - 1))
+            F1.desc[i] = noisy_desc(rng, F2.desc[s], 46)
+            F1.kps["angle"][i] = np.float32((F2.kps["angle"][s] + (rng.normal(0, 4) if rng.random() < 0.85 else rng.uniform(0, 360))) % 360)
+        prev[i] = (F1.kps["x"][i], F1.kps["y"][i]) if rng.random() < 0.8 else (snap(rng.uniform(-30, W + 30)), snap(rng.uniform(-30, H + 30)))
+    return dict(F1=F1, F2=F2, prev=prev, win=win, nnratio=nnratio, ori=ori)

@@ -127,3 +127,66 @@ def test_chi2_needs_sigma_table():
     c["KF"].inv_level_sigma2 = None
     with pytest.raises(orbfe.OrbfeError):
         orbfe.ORBmatcher(0.9, False).search_by_projection(c["KF"], q, 0, th)
+
+
+@pytest.mark.parametrize("name", list(pc.INIT_CASES))
+def test_search_for_initialization(name):
+    """ORBmatcher::SearchForInitialization :706: GPU == C++ oracle == object-level golden (vnMatches12, vbPrevMatched, count)."""
+    c = pc.init_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    m = orbfe.ORBmatcher(c["nnratio"], c["ori"])
+    n, m12, prev = m.SearchForInitialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], c["win"])
+    rn, rm12, rprev = ob.search_for_initialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], c["win"], c["nnratio"], c["ori"])
+    assert n == rn and np.array_equal(m12, rm12) and np.array_equal(prev, rprev)
+    assert n == int(g["n"]) and np.array_equal(m12, g["vnMatches12"]) and np.array_equal(prev, g["prev_matched"])
+
+
+@pytest.mark.parametrize("seed,n1,n2,win,ratio,ori", [(4510, 3000, 900, 100, 0.9, True), (4511, 5000, 5000, 100, 0.9, True),
+                                                       (4512, 800, 3000, 15, 0.7, False), (4513, 2500, 400, 200, 1.0, True)])
+def test_search_for_initialization_vs_oracle(seed, n1, n2, win, ratio, ori):
+    """More shapes incl. the initialiser's 5000-feature frames and heavy competition (many F1 features per F2 source)."""
+    c = pc.init_inputs(spec=(seed, n1, n2, win, ratio, ori))
+    m = orbfe.ORBmatcher(ratio, ori)
+    n, m12, prev = m.SearchForInitialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], win)
+    rn, rm12, rprev = ob.search_for_initialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], win, ratio, ori)
+    assert n == rn and np.array_equal(m12, rm12) and np.array_equal(prev, rprev) and n > 20
+
+
+def test_search_for_initialization_steal_chain():
+    """400 F1 features all derived from 3 F2 features with steadily decreasing distance: every window steals from the
+    one before it, so the sweeps need one round per window (worst case), and only the last claimants survive."""
+    rng = np.random.default_rng(9)
+    k2 = np.zeros(3, orbfe.KEYPOINT_DTYPE)
+    k2["x"], k2["y"] = (300, 304, 296), (200, 203, 198)
+    d2 = rng.integers(0, 256, (3, 32), dtype=np.uint8)
+    F2 = pj.GridFrame(k2, d2, (0, 0, pc.W, pc.H), pc.SCALE)
+    n1 = 400
+    k1 = np.zeros(n1, orbfe.KEYPOINT_DTYPE)
+    k1["x"], k1["y"] = 300, 200
+    d1 = np.zeros((n1, 32), np.uint8)
+    for i in range(n1):
+        d = d2[i % 3].copy()
+        for b in rng.choice(256, max(0, 45 - i // 9), replace=False):
+            d[b >> 3] ^= 1 << (b & 7)
+        d1[i] = d
+    prev = np.tile(np.float32([300, 200]), (n1, 1))
+    m = orbfe.ORBmatcher(0.9, False)
+    n, m12, _ = m.SearchForInitialization(k1, d1, F2, prev, 20)
+    rn, rm12, _ = ob.search_for_initialization(k1, d1, F2, prev, 20, 0.9, False)
+    assert n == rn == 3 and np.array_equal(m12, rm12)
+
+
+def test_search_for_initialization_edge_cases():
+    c = pc.init_inputs("proj_init_w30_noori")
+    m = orbfe.ORBmatcher(0.8, False)
+    n, m12, prev = m.SearchForInitialization(c["F1"].kps[:0], c["F1"].desc[:0], c["F2"], c["prev"][:0], 30)
+    assert n == 0 and len(m12) == 0
+    k = c["F1"].kps.copy()
+    k["octave"] = 1                                   # nothing on level 0: every F1 feature is skipped (:724)
+    n, m12, prev = m.SearchForInitialization(k, c["F1"].desc, c["F2"], c["prev"], 30)
+    assert n == 0 and (m12 == -1).all() and np.array_equal(prev, c["prev"])
+    k2 = c["F2"].kps.copy()
+    k2["octave"] = 2                                  # no level-0 candidates in F2
+    F2 = pj.GridFrame(k2, c["F2"].desc, (0, 0, pc.W, pc.H), pc.SCALE)
+    n, m12, _ = m.SearchForInitialization(c["F1"].kps, c["F1"].desc, F2, c["prev"], 30)
+    assert n == 0 and (m12 == -1).all()

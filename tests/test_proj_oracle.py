@@ -153,3 +153,18 @@ def test_search_by_sim3_matches_golden(name):
     vn1, vn2, pairs, n = run_sim3(c, ob.search_by_projection)
     assert np.array_equal(vn1, g["vnMatch1"]) and np.array_equal(vn2, g["vnMatch2"]) and n == int(g["n"]) and n > 100
     assert n < (vn1 >= 0).sum()              # the agreement pass rejects some one-way matches
+
+
+@pytest.mark.parametrize("name", list(pc.INIT_CASES))
+def test_search_for_initialization_matches_golden(name):
+    """oracle/cpu_ref searchForInitialization vs the object-level Python restatement of ORBmatcher.cc:706-821."""
+    c = pc.init_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    assert crc(c["F1"].kps, c["F1"].desc, c["F2"].kps, c["F2"].desc, c["prev"]) == int(g["in_crc"])
+    n, m12, prev = ob.search_for_initialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], c["win"], c["nnratio"], c["ori"])
+    assert n == int(g["n"]) and np.array_equal(m12, g["vnMatches12"]) and np.array_equal(prev, g["prev_matched"])
+    assert n > 100 and n == (m12 >= 0).sum()
+    # one-to-one, level 0 on both sides
+    hit = m12[m12 >= 0]
+    assert len(set(hit.tolist())) == len(hit)
+    assert (c["F1"].kps["octave"][m12 >= 0] == 0).all() and (c["F2"].kps["octave"][hit] == 0).all()

@@ -91,6 +91,9 @@ def test_shim_equals_python_abi_path(tmp_path):
     nproj = int(np.frombuffer(buf, np.int32, 1, o)[0]); o += 4
     passign = np.frombuffer(buf, np.int32, nR, o); o += 4 * nR
     pbest = np.frombuffer(buf, np.int32, 3, o); o += 12
+    ninit = int(np.frombuffer(buf, np.int32, 1, o)[0]); o += 4
+    init12 = np.frombuffer(buf, np.int32, nL, o); o += 4 * nL
+    initprev = np.frombuffer(buf, np.float32, 2 * nL, o).reshape(nL, 2); o += 8 * nL
     nw, nn = np.frombuffer(buf, np.int32, 2, o); o += 8
     bv = np.frombuffer(buf, np.dtype([("w", "<u4"), ("v", "<f8")]), nw, o); o += 12 * nw
     fv = {}
@@ -131,3 +134,5 @@ def test_shim_equals_python_abi_path(tmp_path):
     assert nproj == rn and np.array_equal(passign, rassign) and rn > 200
     offs = np.array([0, min(5, nL), min(5, nL), min(40, nL)], np.int32)
     assert np.array_equal(pbest, ob.distinctive_descriptors(dd, offs))
+    rni, r12, rprev = ob.search_for_initialization(k, dd, G, np.stack([k["x"], k["y"]], 1), 40, 0.7, True)
+    assert ninit == rni and np.array_equal(init12, r12) and np.array_equal(initprev, rprev) and rni > 30
