@@ -109,17 +109,28 @@ def _oracle():
     return oracle_binding
 
 
-def cpu_frames_per_s(frames, nthreads, budget_s):
-    """Times orbref_extract_many (one extractor instance per thread, frame-parallel) for about budget_s."""
+def cpu_extractor():
+    """(kind, extract_many, description): the reference's own ORBextractor.cc when oracle/_ref holds it (compiled here
+    from /root/reference/src by `make -C oracle ref`, prebuilt on the GPU box), else the oracle port."""
     ob = _oracle()
+    if os.path.exists(ob.REF_MT_LIB):
+        return "reference", ob.ref_extract_many, ("ORB_SLAM3::ORBextractor of the reference's own src/ORBextractor.cc (oracle/_ref, "
+                                                  "-O3 -ffp-contract=off, process allocator); its OpenCV calls run the scalar "
+                                                  "restatement oracle/cpu_ref/cvprim.cc, not OpenCV's SIMD kernels")
+    return "port", ob.extract_many, "CPU restatement oracle/cpu_ref (-O3 -march=native) of ORBextractor.cc with OpenCV 4.x arithmetic"
+
+
+def cpu_frames_per_s(frames, nthreads, budget_s, extract_many=None):
+    """Times extract_many (one extractor instance per thread, frame-parallel) for about budget_s."""
+    extract_many = extract_many or cpu_extractor()[1]
     n = len(frames)
     t0 = time.perf_counter()
-    ob.extract_many(ORB_PARAMS, frames, LAPPING, nthreads)          # warm-up + rate estimate
+    extract_many(ORB_PARAMS, frames, LAPPING, nthreads)          # warm-up + rate estimate
     rate = n / (time.perf_counter() - t0)
     reps = max(1, int(budget_s * rate / n))
     t0 = time.perf_counter()
     for _ in range(reps):
-        ob.extract_many(ORB_PARAMS, frames, LAPPING, nthreads)
+        extract_many(ORB_PARAMS, frames, LAPPING, nthreads)
     dt = time.perf_counter() - t0
     return reps * n / dt, reps * n
 
@@ -135,12 +146,12 @@ def run_reference(args):
     cores = os.cpu_count() or 1
     per_step = 16 * cores
     frames = orbfe.synth.frames(1000, per_step, W, H)
-    ob = _oracle()
+    kind, extract_many, what = cpu_extractor()
     for _ in range(args.warmup):
-        ob.extract_many(ORB_PARAMS, frames, LAPPING, cores)
+        extract_many(ORB_PARAMS, frames, LAPPING, cores)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        ob.extract_many(ORB_PARAMS, frames, LAPPING, cores)
+        extract_many(ORB_PARAMS, frames, LAPPING, cores)
     dt = time.perf_counter() - t0
     v = args.steps * per_step / dt
     sample = f"{per_step} frames per step x {args.steps} steps, frame-parallel over {cores} host threads"
@@ -149,9 +160,8 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": WORKLOAD, "frames_per_step": per_step,
-                   "note": "CPU restatement (oracle/cpu_ref, -O3 -march=native) of ORBextractor.cc with OpenCV 4.x "
-                           "arithmetic; the reference's own sources need OpenCV C++ headers, absent here"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                   "note": what},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -528,10 +538,14 @@ def run_orbfe(args):
     if world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         frames = orbfe.synth.frames(1000, 8 * cores, W, H)
-        v, nfr = cpu_frames_per_s(frames, cores, args.cpu_seconds)
-        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port",
-                               "sample": f"{nfr} frames of the same workload, frame-parallel over {cores} host threads "
-                                         "(oracle/cpu_ref, one extractor per thread)"}
+        kind, extract_many, what = cpu_extractor()
+        v, nfr = cpu_frames_per_s(frames, cores, args.cpu_seconds, extract_many)
+        out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+                               "sample": f"{nfr} frames of the same workload, frame-parallel over {cores} host threads, "
+                                         f"one extractor per thread; {what}"}
+        if kind == "reference":      # the oracle port beside it, same frames and threads
+            vp, _ = cpu_frames_per_s(frames, cores, min(args.cpu_seconds, 4.0), _oracle().extract_many)
+            out["cpu_baseline"]["oracle_port_frames_per_s"] = vp
         # what the reference does per image (one thread), and per stereo pair (two threads, Frame.cc:119-122)
         v1, _ = cpu_frames_per_s(frames[:8], 1, 1.0)
         v2, _ = cpu_frames_per_s(frames[:16], 2, 1.0)

@@ -1,0 +1,2 @@
+// Stand-in: see ../opencv.hpp (TEST INFRASTRUCTURE).
+#include "../opencv.hpp"

@@ -1,0 +1,215 @@
+// opencv.hpp — minimal stand-in for the OpenCV C++ API that /root/reference/src/ORBextractor.cc uses, so that the
+// reference's OWN source file compiles here without OpenCV (TEST INFRASTRUCTURE: only oracle/_ref is built with it).
+//
+// What is real and what is restated when oracle/_ref runs:
+//   * real: every line of ORBextractor.cc / ORBextractor.h — constructor tables, ComputePyramid's level sizes,
+//     the FAST cell loop with its retry, DivideNode / DistributeOctTree (std::list, heap pointers and all), IC_Angle,
+//     computeOrbDescriptor, the lapping-area output order of operator();
+//   * restated: the OpenCV primitives behind cv::resize, cv::copyMakeBorder, cv::FAST, cv::GaussianBlur and
+//     cv::fastAtan2, which forward to oracle/cpu_ref/cvprim.cc — each one held bit for bit to cv2 4.13.0 by
+//     tests/test_oracle_vs_cv2.py.  cv::Mat here is a plain ref-counted 8-bit matrix with ROI views.
+// Written from the documented OpenCV interface; no OpenCV source was consulted or copied.
+#pragma once
+#include <algorithm>
+#include <cassert>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+#include "../../cpu_ref/cvprim.h"
+
+typedef unsigned char uchar;
+
+#define CV_8U 0
+#define CV_8UC1 0
+#define CV_PI 3.1415926535897932384626433832795
+
+namespace cv {
+
+typedef ::uchar uchar;
+
+inline int cvRound(float v) { return (int)lrintf(v); }      // round half to even, like cvtss2si
+inline int cvRound(double v) { return (int)lrint(v); }
+inline int cvRound(int v) { return v; }
+inline int cvFloor(double v) { return (int)std::floor(v); }
+inline int cvCeil(double v) { return (int)std::ceil(v); }
+
+template <class T> struct Point_ {
+    T x, y;
+    Point_() : x(0), y(0) {}
+    Point_(T x_, T y_) : x(x_), y(y_) {}
+    template <class S> Point_& operator*=(S s) { x = (T)(x * s); y = (T)(y * s); return *this; }
+};
+typedef Point_<int> Point2i;
+typedef Point2i Point;
+typedef Point_<float> Point2f;
+
+struct Size {
+    int width, height;
+    Size() : width(0), height(0) {}
+    Size(int w, int h) : width(w), height(h) {}
+};
+struct Rect {
+    int x, y, width, height;
+    Rect(int x_, int y_, int w, int h) : x(x_), y(y_), width(w), height(h) {}
+};
+
+struct KeyPoint {          // 28 bytes, the layout of cv::KeyPoint
+    Point2f pt;
+    float size, angle, response;
+    int octave, class_id;
+    KeyPoint() : pt(0, 0), size(0), angle(-1), response(0), octave(0), class_id(-1) {}
+    KeyPoint(float x, float y, float size_, float angle_ = -1, float response_ = 0, int octave_ = 0, int class_id_ = -1)
+        : pt(x, y), size(size_), angle(angle_), response(response_), octave(octave_), class_id(class_id_) {}
+};
+static_assert(sizeof(KeyPoint) == 28, "cv::KeyPoint layout");
+
+class Mat;
+class _OutputArray;
+
+class Mat {
+public:
+    int rows = 0, cols = 0;
+    size_t step = 0;                 // bytes per row of the underlying buffer
+    uchar* data = nullptr;
+
+    Mat() {}
+    Mat(int r, int c, int type) { create(r, c, type); }
+    Mat(Size s, int type) { create(s.height, s.width, type); }
+    // user-allocated data (not owned)
+    Mat(int r, int c, int type, void* d, size_t st) : rows(r), cols(c), step(st), data((uchar*)d) { assert(type == CV_8U); }
+
+    void create(int r, int c, int type) {
+        assert(type == CV_8U);
+        if (data && r == rows && c == cols) return;       // like OpenCV: a matching header is kept (ROI views stay views)
+        rows = r; cols = c; step = (size_t)c;
+        buf_.reset(new uchar[(size_t)r * c + 1], std::default_delete<uchar[]>());
+        data = buf_.get();
+    }
+    void release() { buf_.reset(); data = nullptr; rows = cols = 0; step = 0; }
+    static Mat zeros(int r, int c, int type) { Mat m(r, c, type); std::memset(m.data, 0, (size_t)r * c); return m; }
+
+    int type() const { return CV_8U; }
+    bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
+    size_t step1() const { return step; }
+
+    Mat operator()(const Rect& r) const { return view(r.y, r.y + r.height, r.x, r.x + r.width); }
+    Mat rowRange(int a, int b) const { return view(a, b, 0, cols); }
+    Mat colRange(int a, int b) const { return view(0, rows, a, b); }
+    Mat row(int i) const { return view(i, i + 1, 0, cols); }
+
+    template <class T> T& at(int y, int x) { return *reinterpret_cast<T*>(data + (size_t)y * step + x * sizeof(T)); }
+    template <class T> const T& at(int y, int x) const { return *reinterpret_cast<const T*>(data + (size_t)y * step + x * sizeof(T)); }
+    uchar* ptr(int y = 0) { return data + (size_t)y * step; }
+    const uchar* ptr(int y = 0) const { return data + (size_t)y * step; }
+    template <class T> T* ptr(int y = 0) { return reinterpret_cast<T*>(data + (size_t)y * step); }
+    template <class T> const T* ptr(int y = 0) const { return reinterpret_cast<const T*>(data + (size_t)y * step); }
+
+    Mat clone() const {
+        Mat m;
+        if (empty()) return m;
+        m.create(rows, cols, CV_8U);
+        for (int y = 0; y < rows; ++y) std::memcpy(m.ptr(y), ptr(y), (size_t)cols);
+        return m;
+    }
+    inline void copyTo(const _OutputArray& dst) const;
+
+private:
+    Mat view(int y0, int y1, int x0, int x1) const {
+        assert(y0 >= 0 && y1 <= rows && x0 >= 0 && x1 <= cols && y0 <= y1 && x0 <= x1);
+        Mat m;
+        m.rows = y1 - y0; m.cols = x1 - x0; m.step = step; m.data = data + (size_t)y0 * step + x0; m.buf_ = buf_;
+        return m;
+    }
+    std::shared_ptr<uchar> buf_;     // keeps the allocation alive for every view
+};
+
+class _InputArray {
+public:
+    _InputArray(const Mat& m) : m_(&m) {}
+    bool empty() const { return m_->empty(); }
+    Mat getMat() const { return *m_; }
+private:
+    const Mat* m_;
+};
+class _OutputArray {
+public:
+    _OutputArray(const Mat& m) : m_(const_cast<Mat*>(&m)) {}
+    void release() const { m_->release(); }
+    void create(int r, int c, int type) const { m_->create(r, c, type); }
+    Mat getMat() const { return *m_; }
+    Mat& ref() const { return *m_; }
+private:
+    Mat* m_;
+};
+typedef const _InputArray& InputArray;
+typedef const _OutputArray& OutputArray;
+
+inline void Mat::copyTo(const _OutputArray& dst) const {
+    dst.create(rows, cols, CV_8U);
+    Mat& d = dst.ref();
+    for (int y = 0; y < rows; ++y) std::memmove(d.ptr(y), ptr(y), (size_t)cols);
+}
+
+enum { BORDER_REFLECT_101 = 4, BORDER_ISOLATED = 16 };
+enum { INTER_LINEAR = 1 };
+
+inline float fastAtan2(float y, float x) { return orbref::fastAtan2(y, x); }
+
+// cv::FAST(image, keypoints, threshold, nonmaxSuppression): type 9_16, keypoints in row-major order,
+// KeyPoint(x, y, 7.f, -1, score).
+inline void FAST(InputArray image, std::vector<KeyPoint>& keypoints, int threshold, bool nonmaxSuppression = true) {
+    assert(nonmaxSuppression);
+    (void)nonmaxSuppression;
+    const Mat img = image.getMat();
+    std::vector<orbref::FastKp> out;
+    orbref::fast9_16(img.data, img.cols, img.rows, (ptrdiff_t)img.step, threshold, out);
+    keypoints.clear();
+    keypoints.reserve(out.size());
+    for (const orbref::FastKp& k : out) keypoints.push_back(KeyPoint((float)k.x, (float)k.y, 7.f, -1, (float)k.score));
+}
+
+// cv::resize(src, dst, dsize, 0, 0, INTER_LINEAR), 8-bit single channel.
+inline void resize(InputArray src_, OutputArray dst_, Size dsize, double fx = 0, double fy = 0, int interpolation = INTER_LINEAR) {
+    assert(fx == 0 && fy == 0 && interpolation == INTER_LINEAR);
+    (void)fx; (void)fy; (void)interpolation;
+    const Mat src = src_.getMat();
+    dst_.create(dsize.height, dsize.width, CV_8U);
+    Mat dst = dst_.getMat();
+    orbref::resizeLinearU8(src.data, src.cols, src.rows, (ptrdiff_t)src.step, dst.data, dst.cols, dst.rows, (ptrdiff_t)dst.step);
+}
+
+// cv::copyMakeBorder(src, dst, b, b, b, b, BORDER_REFLECT_101 [+ BORDER_ISOLATED]).
+inline void copyMakeBorder(InputArray src_, OutputArray dst_, int top, int bottom, int left, int right, int borderType) {
+    assert((borderType & ~BORDER_ISOLATED) == BORDER_REFLECT_101 && top == bottom && top == left && top == right);
+    (void)bottom; (void)left; (void)right; (void)borderType;
+    const Mat src = src_.getMat();
+    dst_.create(src.rows + 2 * top, src.cols + 2 * top, CV_8U);
+    Mat dst = dst_.getMat();
+    for (int y = 0; y < src.rows; ++y) {
+        uchar* d = dst.ptr(y + top) + top;
+        if (d != src.ptr(y)) std::memmove(d, src.ptr(y), (size_t)src.cols);
+    }
+    orbref::fillBorderReflect101(dst.data, src.cols, src.rows, top, (ptrdiff_t)dst.step);
+}
+
+// cv::GaussianBlur(src, dst, Size(7, 7), 2, 2, BORDER_REFLECT_101), 8-bit; src and dst may be the same matrix.
+inline void GaussianBlur(InputArray src_, OutputArray dst_, Size ksize, double sigmaX, double sigmaY = 0, int borderType = BORDER_REFLECT_101) {
+    assert(ksize.width == 7 && ksize.height == 7 && sigmaX == 2 && sigmaY == 2 && borderType == BORDER_REFLECT_101);
+    (void)ksize; (void)sigmaX; (void)sigmaY; (void)borderType;
+    const Mat src = src_.getMat().clone();
+    dst_.create(src.rows, src.cols, CV_8U);
+    Mat dst = dst_.getMat();
+    orbref::gaussianBlur7x7(src.data, src.cols, src.rows, (ptrdiff_t)src.step, dst.data, (ptrdiff_t)dst.step);
+}
+
+// Only referenced by ORBextractor::ComputeKeyPointsOld, which the reference never calls (ORBextractor.cc:1083).
+struct KeyPointsFilter {
+    static void retainBest(std::vector<KeyPoint>& keypoints, int npoints) {
+        if (npoints >= 0 && (int)keypoints.size() > npoints) keypoints.resize(npoints);
+    }
+};
+
+}  // namespace cv

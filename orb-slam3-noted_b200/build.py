@@ -64,3 +64,16 @@ def build_all(force=False):
 
 if __name__ == "__main__":
     print(build_all(force="--force" in sys.argv))
+
+
+REFERENCE_SRC = "/root/reference/src/ORBextractor.cc"
+REF_LIBS = [os.path.join(ROOT, "oracle", "_ref", n) for n in ("liborbslam3_orbextractor.so", "liborbslam3_orbextractor_mt.so")]
+
+
+def build_reference(force=False):
+    """oracle/_ref: the reference's own ORBextractor.cc compiled where it lies (make -C oracle ref).  Only possible in the
+    container that has /root/reference; elsewhere the prebuilt libraries (they travel with the snapshot) are used as is."""
+    if not os.path.exists(REFERENCE_SRC):
+        return [p for p in REF_LIBS if os.path.exists(p)]
+    _run(["make", "-C", os.path.join(ROOT, "oracle"), "ref"] + (["-B"] if force else []))
+    return REF_LIBS

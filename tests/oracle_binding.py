@@ -331,3 +331,92 @@ def undistort_keypoints(kps, K4, dist):
     L_.orbref_undistort_keypoints.argtypes = [_P, _I, _P, _P, _I, _P]
     L_.orbref_undistort_keypoints(_p(kps), len(kps), _p(K4), _p(dist), len(dist), _p(out))
     return out
+
+
+# ---- the reference's own ORBextractor.cc, compiled against the OpenCV stand-in (oracle/_ref, see oracle/Makefile) ----
+REF_LIB = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "oracle", "_ref", "liborbslam3_orbextractor.so")
+_ref_lib = None
+
+
+def ref_available():
+    return os.path.exists(REF_LIB)
+
+
+def ref_lib():
+    global _ref_lib
+    if _ref_lib is None:
+        L = C.CDLL(REF_LIB)
+        L.orbslam3_extractor_create.restype = C.c_void_p
+        L.orbslam3_extractor_create.argtypes = [_I, _F, _I, _I, _I]
+        L.orbslam3_extractor_destroy.argtypes = [C.c_void_p]
+        L.orbslam3_extractor_extract.restype = _I
+        L.orbslam3_extractor_extract.argtypes = [C.c_void_p, _P, _I, _I, C.c_long, _I, _I, _P, _P, _I, _P]
+        L.orbslam3_extractor_pyramid.restype = _I
+        L.orbslam3_extractor_pyramid.argtypes = [C.c_void_p, _I, _P, _I, _P, _P]
+        L.orbslam3_extractor_tables.argtypes = [C.c_void_p, _P, _P, _P, _P]
+        L.orbslam3_extractor_pyramid_bordered.restype = _I
+        L.orbslam3_extractor_pyramid_bordered.argtypes = [C.c_void_p, _I, _P, _I, _P, _P]
+        _ref_lib = L
+    return _ref_lib
+
+
+class OrbSlam3Extractor:
+    """ORB_SLAM3::ORBextractor of /root/reference/src/ORBextractor.cc itself (its OpenCV calls go to the stand-in
+    in oracle/refshim, whose primitives are oracle/cpu_ref/cvprim.cc)."""
+
+    def __init__(self, nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST):
+        self.L = ref_lib()
+        self.h = self.L.orbslam3_extractor_create(nfeatures, scaleFactor, nlevels, iniThFAST, minThFAST)
+        self.nlevels = nlevels
+        self.cap = nfeatures + 64 * nlevels + 4096
+
+    def __del__(self):
+        try:
+            self.L.orbslam3_extractor_destroy(self.h)
+        except Exception:
+            pass
+
+    def __call__(self, image, lapping=(0, 0)):
+        image = np.ascontiguousarray(image)
+        h, w = image.shape
+        kps = np.zeros(self.cap, KEYPOINT_DTYPE)
+        desc = np.zeros((self.cap, 32), np.uint8)
+        mono = C.c_int(0)
+        n = self.L.orbslam3_extractor_extract(self.h, _p(image), w, h, w, int(lapping[0]), int(lapping[1]), _p(kps), _p(desc),
+                                              self.cap, C.byref(mono))
+        assert n >= 0, "reference capacity"
+        return mono.value, kps[:n].copy(), desc[:n].copy()
+
+    def level(self, l):
+        w, h = C.c_int(), C.c_int()
+        buf = np.zeros(4096 * 4096, np.uint8)
+        assert self.L.orbslam3_extractor_pyramid(self.h, l, _p(buf), buf.size, C.byref(w), C.byref(h)) == 0
+        return buf[:w.value * h.value].reshape(h.value, w.value).copy()
+
+    def level_bordered(self, l):
+        w, h = C.c_int(), C.c_int()
+        buf = np.zeros(4096 * 4096, np.uint8)
+        assert self.L.orbslam3_extractor_pyramid_bordered(self.h, l, _p(buf), buf.size, C.byref(w), C.byref(h)) == 0
+        return buf[:w.value * h.value].reshape(h.value, w.value).copy()
+
+    def tables(self):
+        t = [np.zeros(self.nlevels, np.float32) for _ in range(4)]
+        self.L.orbslam3_extractor_tables(self.h, *[_p(a) for a in t])
+        return t
+
+
+REF_MT_LIB = REF_LIB.replace(".so", "_mt.so")
+_ref_mt = None
+
+
+def ref_extract_many(orb_params, frames, lapping, nthreads):
+    """Frame-parallel run of the reference's ORBextractor (process allocator build), one instance per thread."""
+    global _ref_mt
+    if _ref_mt is None:
+        _ref_mt = C.CDLL(REF_MT_LIB)
+        _ref_mt.orbslam3_extract_many.restype = C.c_long
+        _ref_mt.orbslam3_extract_many.argtypes = [_I, _F, _I, _I, _I, _P, _I, _I, _I, _I, _I, _I]
+    frames = np.ascontiguousarray(frames)
+    n, h, w = frames.shape
+    nf, sf, nl, ini, mn = orb_params
+    return _ref_mt.orbslam3_extract_many(nf, sf, nl, ini, mn, _p(frames), n, w, h, int(lapping[0]), int(lapping[1]), int(nthreads))

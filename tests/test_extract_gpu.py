@@ -59,6 +59,26 @@ def test_extract_parity(name, w, h, nf, lap):
     assert ok >= 0.9999 * tot, (ok, tot)
 
 
+@pytest.mark.parametrize("name,w,h,nf,lap", SHAPES, ids=[s[0] for s in SHAPES])
+def test_cuda_equals_reference_source(name, w, h, nf, lap):
+    """The CUDA path against the reference's own src/ORBextractor.cc (oracle/_ref, prebuilt; see
+    tests/test_reference_orbextractor.py for what that library is)."""
+    import oracle_binding as ob
+    if not ob.ref_available():
+        pytest.skip("oracle/_ref not built")
+    ex = orbfe.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    ref = ob.OrbSlam3Extractor(nf, 1.2, 8, 20, 7)
+    ok = tot = 0
+    for seed in range(2):
+        img = orbfe.synth.frame(2000 + 100 * SHAPES.index((name, w, h, nf, lap)) + seed, w, h)
+        a, b = check_frame(ex, ref, img, lap, stages=False)
+        for l in range(ex.nlevels):
+            assert np.array_equal(ex.image_pyramid(l, 0)[0], ref.level_bordered(l)), f"pyramid level {l}"
+        ok += a
+        tot += b
+    assert tot > 0.9 * 2 * nf and ok >= 0.9999 * tot, (ok, tot)
+
+
 def test_batch_equals_single():
     w, h, nf = 752, 480, 1000
     imgs = orbfe.synth.frames(2000, 6, w, h)
