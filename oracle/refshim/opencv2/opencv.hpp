@@ -15,7 +15,10 @@
 #include <cmath>
 #include <cstdint>
 #include <cstring>
+#include <iostream>
 #include <memory>
+#include <sstream>
+#include <string>
 #include <vector>
 
 #include "../../cpu_ref/cvprim.h"
@@ -24,6 +27,7 @@ typedef unsigned char uchar;
 
 #define CV_8U 0
 #define CV_8UC1 0
+#define CV_32F 5        // only named by FORB::toMat32F, which nothing on the path calls
 #define CV_PI 3.1415926535897932384626433832795
 
 namespace cv {
@@ -211,5 +215,29 @@ struct KeyPointsFilter {
         if (npoints >= 0 && (int)keypoints.size() > npoints) keypoints.resize(npoints);
     }
 };
+
+// cv::FileStorage / cv::FileNode: TemplatedVocabulary's virtual save(fs) / load(fs) (YAML) must compile; ORB-SLAM3 only
+// uses loadFromTextFile (System.cc:118), so these never open anything.
+class FileNode {
+public:
+    FileNode operator[](const std::string&) const { return FileNode(); }
+    FileNode operator[](const char*) const { return FileNode(); }
+    FileNode operator[](int) const { return FileNode(); }
+    size_t size() const { return 0; }
+    operator int() const { return 0; }
+    operator float() const { return 0.f; }
+    operator double() const { return 0.0; }
+    operator std::string() const { return std::string(); }
+};
+class FileStorage {
+public:
+    enum { READ = 0, WRITE = 1 };
+    FileStorage() {}
+    FileStorage(const std::string&, int) {}
+    bool isOpened() const { return false; }
+    FileNode operator[](const std::string&) const { return FileNode(); }
+    FileNode operator[](const char*) const { return FileNode(); }
+};
+template <class T> inline FileStorage& operator<<(FileStorage& fs, const T&) { return fs; }
 
 }  // namespace cv

@@ -420,3 +420,49 @@ def ref_extract_many(orb_params, frames, lapping, nthreads):
     n, h, w = frames.shape
     nf, sf, nl, ini, mn = orb_params
     return _ref_mt.orbslam3_extract_many(nf, sf, nl, ini, mn, _p(frames), n, w, h, int(lapping[0]), int(lapping[1]), int(nthreads))
+
+
+# ---- the reference's own vendored DBoW2 (oracle/_ref/libdbow2_orbvoc.so, see oracle/Makefile) ----
+REF_VOC_LIB = os.path.join(os.path.dirname(REF_LIB), "libdbow2_orbvoc.so")
+_ref_voc = None
+
+
+def ref_voc_available():
+    return os.path.exists(REF_VOC_LIB)
+
+
+class DBoW2Vocabulary:
+    """ORBVocabulary (TemplatedVocabulary<FORB::TDescriptor, FORB>) of Thirdparty/DBoW2 itself, loaded with its own
+    loadFromTextFile from an ORBvoc-format text file."""
+
+    def __init__(self, path):
+        global _ref_voc
+        if _ref_voc is None:
+            L = C.CDLL(REF_VOC_LIB)
+            L.orbslam3_voc_load_text.restype = C.c_void_p
+            L.orbslam3_voc_load_text.argtypes = [C.c_char_p]
+            L.orbslam3_voc_destroy.argtypes = [C.c_void_p]
+            L.orbslam3_voc_words.restype = _I
+            L.orbslam3_voc_words.argtypes = [C.c_void_p]
+            L.orbslam3_voc_transform.argtypes = [C.c_void_p, _P, _I, _I, _P, _P, _P, _P, _P, _P, _P]
+            _ref_voc = L
+        self.L = _ref_voc
+        self.h = self.L.orbslam3_voc_load_text(str(path).encode())
+        assert self.h, "DBoW2 loadFromTextFile failed"
+        self.nwords = self.L.orbslam3_voc_words(self.h)
+
+    def __del__(self):
+        try:
+            self.L.orbslam3_voc_destroy(self.h)
+        except Exception:
+            pass
+
+    def transform(self, desc, levelsup):
+        desc = np.ascontiguousarray(desc, np.uint8).reshape(-1, 32)
+        n = len(desc)
+        words, values = np.zeros(max(n, 1), np.uint32), np.zeros(max(n, 1), np.float64)
+        nodes, off, idx = np.zeros(max(n, 1), np.uint32), np.zeros(n + 1, np.int32), np.zeros(max(n, 1), np.int32)
+        nw, nn = C.c_int(0), C.c_int(0)
+        self.L.orbslam3_voc_transform(self.h, _p(desc), n, int(levelsup), _p(words), _p(values), C.byref(nw), _p(nodes), _p(off),
+                                      _p(idx), C.byref(nn))
+        return words[:nw.value], values[:nw.value], nodes[:nn.value], off[:nn.value + 1], idx[:off[nn.value]]

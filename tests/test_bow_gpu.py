@@ -101,3 +101,28 @@ def test_load_text_file(tmp_path):
     assert np.array_equal(words, g["words"]) and np.array_equal(values, g["values"]) and np.array_equal(fv.indices, g["indices"])
     with pytest.raises(orbfe.OrbfeError):
         orbfe.ORBVocabulary.loadFromTextFile(str(tmp_path / "missing.txt"))
+
+
+@pytest.mark.parametrize("name", ["voc_k10_L4", "voc_k6_L4_idf_l2"])
+def test_cuda_equals_dbow2_source(name, tmp_path):
+    """The CUDA transform (vocabulary loaded by orbfe's ORBvoc text loader) against the reference's own vendored DBoW2
+    (oracle/_ref/libdbow2_orbvoc.so, prebuilt; see tests/test_reference_dbow2.py) reading the same text file."""
+    import oracle_binding as ob
+    if not ob.ref_voc_available():
+        pytest.skip("oracle/_ref not built")
+    from test_reference_dbow2 import write_text
+    c = bc.voc_inputs(name)
+    write_text(c, tmp_path / "voc.txt")
+    ref = ob.DBoW2Vocabulary(tmp_path / "voc.txt")
+    v = orbfe.ORBVocabulary.loadFromTextFile(str(tmp_path / "voc.txt"), c["norm"])
+    assert v.size() == ref.nwords
+    for levelsup in (c["levelsup"], 0, 4):
+        (words, values), fv = v.transform(c["feat"], levelsup)
+        rw, rv, rn, ro, ri = ref.transform(c["feat"], levelsup)
+        assert np.array_equal(words, rw) and np.array_equal(values, rv)
+        if levelsup == 0:
+            # an early leaf (above level L - levelsup) leaves DBoW2's `NodeId nid` uninitialised (TemplatedVocabulary.h:1162,
+            # :1259-1260): the FeatureVector entry of such a feature is undefined in the reference; include/orbfe.h defines it
+            # as the leaf's own id.  Only the BowVector is comparable here.
+            continue
+        assert np.array_equal(fv.node_ids, rn) and np.array_equal(fv.offsets, ro) and np.array_equal(fv.indices, ri)
