@@ -83,26 +83,37 @@ public:
     Mat(int r, int c, int type) { create(r, c, type); }
     Mat(Size s, int type) { create(s.height, s.width, type); }
     // user-allocated data (not owned)
-    Mat(int r, int c, int type, void* d, size_t st) : rows(r), cols(c), step(st), data((uchar*)d) { assert(type == CV_8U); }
+    Mat(int r, int c, int type, void* d, size_t st) : rows(r), cols(c), step(st), data((uchar*)d), esz_(type == CV_32F ? 4 : 1) {
+        assert(type == CV_8U || type == CV_32F);
+    }
 
     void create(int r, int c, int type) {
-        assert(type == CV_8U);
-        if (data && r == rows && c == cols) return;       // like OpenCV: a matching header is kept (ROI views stay views)
-        rows = r; cols = c; step = (size_t)c;
-        buf_.reset(new uchar[(size_t)r * c + 1], std::default_delete<uchar[]>());
+        assert(type == CV_8U || type == CV_32F);
+        const int e = type == CV_32F ? 4 : 1;
+        if (data && r == rows && c == cols && e == esz_) return;   // like OpenCV: a matching header is kept (ROI views stay views)
+        rows = r; cols = c; esz_ = e; step = (size_t)c * e;
+        buf_.reset(new uchar[(size_t)r * c * e + 1], std::default_delete<uchar[]>());
         data = buf_.get();
     }
     void release() { buf_.reset(); data = nullptr; rows = cols = 0; step = 0; }
-    static Mat zeros(int r, int c, int type) { Mat m(r, c, type); std::memset(m.data, 0, (size_t)r * c); return m; }
+    static Mat zeros(int r, int c, int type) { Mat m(r, c, type); std::memset(m.data, 0, (size_t)r * m.step); return m; }
 
-    int type() const { return CV_8U; }
+    int type() const { return esz_ == 4 ? CV_32F : CV_8U; }
+    size_t elemSize() const { return (size_t)esz_; }
     bool empty() const { return data == nullptr || rows == 0 || cols == 0; }
-    size_t step1() const { return step; }
+    size_t step1() const { return step / esz_; }
 
     Mat operator()(const Rect& r) const { return view(r.y, r.y + r.height, r.x, r.x + r.width); }
     Mat rowRange(int a, int b) const { return view(a, b, 0, cols); }
     Mat colRange(int a, int b) const { return view(0, rows, a, b); }
     Mat row(int i) const { return view(i, i + 1, 0, cols); }
+    Mat col(int j) const { return view(0, rows, j, j + 1); }
+    // single index: element i of a row or column vector
+    template <class T> T& at(int i) { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
+    template <class T> const T& at(int i) const { return cols == 1 ? at<T>(i, 0) : at<T>(i / cols, i % cols); }
+    // float algebra (CV_32F), evaluated eagerly; see the operators below the class
+    inline Mat t() const;
+    inline double dot(const Mat& b) const;
 
     template <class T> T& at(int y, int x) { return *reinterpret_cast<T*>(data + (size_t)y * step + x * sizeof(T)); }
     template <class T> const T& at(int y, int x) const { return *reinterpret_cast<const T*>(data + (size_t)y * step + x * sizeof(T)); }
@@ -114,8 +125,8 @@ public:
     Mat clone() const {
         Mat m;
         if (empty()) return m;
-        m.create(rows, cols, CV_8U);
-        for (int y = 0; y < rows; ++y) std::memcpy(m.ptr(y), ptr(y), (size_t)cols);
+        m.create(rows, cols, type());
+        for (int y = 0; y < rows; ++y) std::memcpy(m.ptr(y), ptr(y), (size_t)cols * esz_);
         return m;
     }
     inline void copyTo(const _OutputArray& dst) const;
@@ -124,9 +135,10 @@ private:
     Mat view(int y0, int y1, int x0, int x1) const {
         assert(y0 >= 0 && y1 <= rows && x0 >= 0 && x1 <= cols && y0 <= y1 && x0 <= x1);
         Mat m;
-        m.rows = y1 - y0; m.cols = x1 - x0; m.step = step; m.data = data + (size_t)y0 * step + x0; m.buf_ = buf_;
+        m.rows = y1 - y0; m.cols = x1 - x0; m.step = step; m.esz_ = esz_; m.data = data + (size_t)y0 * step + (size_t)x0 * esz_; m.buf_ = buf_;
         return m;
     }
+    int esz_ = 1;
     std::shared_ptr<uchar> buf_;     // keeps the allocation alive for every view
 };
 
@@ -152,10 +164,94 @@ typedef const _InputArray& InputArray;
 typedef const _OutputArray& OutputArray;
 
 inline void Mat::copyTo(const _OutputArray& dst) const {
-    dst.create(rows, cols, CV_8U);
+    dst.create(rows, cols, type());
     Mat& d = dst.ref();
-    for (int y = 0; y < rows; ++y) std::memmove(d.ptr(y), ptr(y), (size_t)cols);
+    for (int y = 0; y < rows; ++y) std::memmove(d.ptr(y), ptr(y), (size_t)cols * esz_);
 }
+
+// ---- float matrices (CV_32F): the small dense algebra ORBmatcher.cc writes with cv::Mat.  Products and dot products
+// accumulate in double and round once to float, like OpenCV's float GEMM; expressions are evaluated operator by
+// operator (OpenCV fuses A*B+C into one GEMM call, which can differ in the last bit).
+inline Mat operator*(const Mat& a, const Mat& b) {
+    assert(a.type() == CV_32F && b.type() == CV_32F && a.cols == b.rows);
+    Mat c(a.rows, b.cols, CV_32F);
+    for (int i = 0; i < a.rows; ++i)
+        for (int j = 0; j < b.cols; ++j) {
+            double s = 0;
+            for (int k = 0; k < a.cols; ++k) s += (double)a.at<float>(i, k) * (double)b.at<float>(k, j);
+            c.at<float>(i, j) = (float)s;
+        }
+    return c;
+}
+#define ORBREF_MAT_EW(OP)                                                                          \
+    inline Mat operator OP(const Mat& a, const Mat& b) {                                           \
+        assert(a.type() == CV_32F && b.type() == CV_32F && a.rows == b.rows && a.cols == b.cols);  \
+        Mat c(a.rows, a.cols, CV_32F);                                                             \
+        for (int i = 0; i < a.rows; ++i)                                                           \
+            for (int j = 0; j < a.cols; ++j) c.at<float>(i, j) = a.at<float>(i, j) OP b.at<float>(i, j); \
+        return c;                                                                                  \
+    }
+ORBREF_MAT_EW(+)
+ORBREF_MAT_EW(-)
+#undef ORBREF_MAT_EW
+inline Mat operator*(const Mat& a, double s) {
+    Mat c(a.rows, a.cols, CV_32F);
+    for (int i = 0; i < a.rows; ++i)
+        for (int j = 0; j < a.cols; ++j) c.at<float>(i, j) = (float)(a.at<float>(i, j) * s);
+    return c;
+}
+inline Mat operator*(double s, const Mat& a) { return a * s; }
+inline Mat operator/(const Mat& a, double s) { return a * (1.0 / s); }
+inline Mat operator-(const Mat& a) { return a * -1.0; }
+inline Mat Mat::t() const {
+    Mat c(cols, rows, CV_32F);
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < cols; ++j) c.at<float>(j, i) = at<float>(i, j);
+    return c;
+}
+inline double Mat::dot(const Mat& b) const {
+    double s = 0;
+    for (int i = 0; i < rows; ++i)
+        for (int j = 0; j < cols; ++j) s += (double)at<float>(i, j) * (double)b.at<float>(i, j);
+    return s;
+}
+inline double norm(const Mat& a) { return std::sqrt(a.dot(a)); }
+
+template <class T> struct Point3_ {
+    T x, y, z;
+    Point3_() : x(0), y(0), z(0) {}
+    Point3_(T x_, T y_, T z_) : x(x_), y(y_), z(z_) {}
+};
+typedef Point3_<float> Point3f;
+
+// cv::Matx: plain fixed-size arrays, products accumulate in the element type, k ascending
+template <class T, int M, int N> struct Matx {
+    T val[M * N];
+    Matx() { for (int i = 0; i < M * N; ++i) val[i] = T(0); }
+    T& operator()(int i, int j) { return val[i * N + j]; }
+    const T& operator()(int i, int j) const { return val[i * N + j]; }
+    T& operator()(int i) { return val[i]; }
+    const T& operator()(int i) const { return val[i]; }
+    Matx<T, N, M> t() const { Matx<T, N, M> r; for (int i = 0; i < M; ++i) for (int j = 0; j < N; ++j) r(j, i) = (*this)(i, j); return r; }
+};
+template <class T, int M, int K, int N> inline Matx<T, M, N> operator*(const Matx<T, M, K>& a, const Matx<T, K, N>& b) {
+    Matx<T, M, N> c;
+    for (int i = 0; i < M; ++i)
+        for (int j = 0; j < N; ++j) { T s = 0; for (int k = 0; k < K; ++k) s += a(i, k) * b(k, j); c(i, j) = s; }
+    return c;
+}
+template <class T, int M, int N> inline Matx<T, M, N> operator+(const Matx<T, M, N>& a, const Matx<T, M, N>& b) {
+    Matx<T, M, N> c; for (int i = 0; i < M * N; ++i) c.val[i] = a.val[i] + b.val[i]; return c;
+}
+template <class T, int M, int N> inline Matx<T, M, N> operator-(const Matx<T, M, N>& a, const Matx<T, M, N>& b) {
+    Matx<T, M, N> c; for (int i = 0; i < M * N; ++i) c.val[i] = a.val[i] - b.val[i]; return c;
+}
+template <class T, int M, int N> inline Matx<T, M, N> operator-(const Matx<T, M, N>& a) {
+    Matx<T, M, N> c; for (int i = 0; i < M * N; ++i) c.val[i] = -a.val[i]; return c;
+}
+typedef Matx<float, 3, 3> Matx33f;
+typedef Matx<float, 3, 1> Matx31f;
+typedef Matx<float, 4, 4> Matx44f;
 
 enum { BORDER_REFLECT_101 = 4, BORDER_ISOLATED = 16 };
 enum { INTER_LINEAR = 1 };

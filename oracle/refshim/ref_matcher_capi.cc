@@ -1,0 +1,169 @@
+// ref_matcher_capi.cc — C entry points around the reference's own ORB_SLAM3::ORBmatcher, compiled from
+// /root/reference/src/ORBmatcher.cc + include/ORBmatcher.h (unmodified) against the stand-ins of oracle/refshim
+// (opencv2/opencv.hpp, orbslam3_standin.h) (TEST INFRASTRUCTURE).  Each wrapper builds the stand-in Frame / KeyFrame /
+// MapPoint objects from flat arrays (the layout of include/orbfe.h) and calls the reference's member function.
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+#include "ORBmatcher.h"
+
+using namespace ORB_SLAM3;
+
+namespace {
+struct KpPod { float x, y, size, angle, response; int32_t octave, class_id; };
+static_assert(sizeof(KpPod) == sizeof(cv::KeyPoint), "KeyPoint layout");
+
+std::vector<cv::KeyPoint> keys(const KpPod* k, int n) {
+    std::vector<cv::KeyPoint> v(n);
+    if (n) memcpy(v.data(), k, sizeof(KpPod) * (size_t)n);
+    return v;
+}
+cv::Mat descs(const uint8_t* d, int n) {
+    cv::Mat m(n > 0 ? n : 1, 32, CV_8U);
+    if (n > 0) memcpy(m.data, d, 32 * (size_t)n);
+    return n > 0 ? m : m.rowRange(0, 0);
+}
+DBoW2::FeatureVector featvec(const uint32_t* nodeIds, const int32_t* off, const int32_t* idx, int nnodes) {
+    DBoW2::FeatureVector fv;
+    for (int k = 0; k < nnodes; ++k)
+        for (int j = off[k]; j < off[k + 1]; ++j) fv.addFeature(nodeIds[k], (unsigned)idx[j]);
+    return fv;
+}
+struct Matcher : ORBmatcher {
+    using ORBmatcher::ORBmatcher;
+    void threeMaxima(std::vector<int>* histo, int L, int& a, int& b, int& c) { ComputeThreeMaxima(histo, L, a, b, c); }
+};
+}  // namespace
+
+extern "C" {
+int orbslam3_descriptor_distance(const uint8_t* a, const uint8_t* b) {
+    return ORBmatcher::DescriptorDistance(descs(a, 1), descs(b, 1));
+}
+void orbslam3_three_maxima(const int32_t* counts, int L, int32_t* ind) {
+    std::vector<std::vector<int>> h(L);
+    for (int i = 0; i < L; ++i) h[i].assign(counts[i], 0);
+    int a = -1, b = -1, c = -1;
+    Matcher m(0.6f, true);
+    m.threeMaxima(h.data(), L, a, b, c);
+    ind[0] = a; ind[1] = b; ind[2] = c;
+}
+
+// SearchByBoW.  form 0: (KeyFrame* A, Frame& B, vpMapPointMatches) :269-471;  form 1: (KeyFrame* A, KeyFrame* B, vpMatches12) :823-963.
+// maskA / maskB: the feature holds a good MapPoint.  a2b[nA], b2a[nB]: matched partner or -1.  Returns nmatches.
+int orbslam3_search_bow(int form, float nnratio, int checkOri, const KpPod* kpsA, const uint8_t* descA, int nA, const uint8_t* maskA,
+                        const uint32_t* nodesA, const int32_t* offA, const int32_t* idxA, int nnodesA, const KpPod* kpsB,
+                        const uint8_t* descB, int nB, const uint8_t* maskB, const uint32_t* nodesB, const int32_t* offB, const int32_t* idxB,
+                        int nnodesB, int nleftB, int32_t* a2b, int32_t* b2a) {
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    std::vector<std::unique_ptr<MapPoint>> pool;
+    auto points = [&](const uint8_t* mask, int n) {
+        std::vector<MapPoint*> v(n, nullptr);
+        for (int i = 0; i < n; ++i)
+            if (mask && mask[i]) { pool.emplace_back(new MapPoint()); v[i] = pool.back().get(); }
+        return v;
+    };
+    KeyFrame A;
+    A.N = nA; A.mvKeysUn = keys(kpsA, nA); A.mvKeys = A.mvKeysUn; A.mDescriptors = descs(descA, nA);
+    A.mFeatVec = featvec(nodesA, offA, idxA, nnodesA); A.mvpMapPoints = points(maskA, nA);
+    for (int i = 0; i < nA; ++i) a2b[i] = -1;
+    for (int i = 0; i < nB; ++i) b2a[i] = -1;
+    int n;
+    Pinhole rig(1.f, 1.f, 0.f, 0.f);       // a second camera only has to exist: it switches the keypoint accessors to mvKeys / mvKeysRight
+    if (form == 0) {
+        Frame B;
+        if (nleftB != -1) { A.mpCamera2 = &rig; A.NLeft = nA; B.mpCamera2 = &rig; }
+        B.N = nB; B.Nleft = nleftB; B.mDescriptors = descs(descB, nB); B.mFeatVec = featvec(nodesB, offB, idxB, nnodesB);
+        std::vector<cv::KeyPoint> all = keys(kpsB, nB);
+        if (nleftB == -1) { B.mvKeys = all; B.mvKeysUn = all; }
+        else { B.mvKeys.assign(all.begin(), all.begin() + nleftB); B.mvKeysRight.assign(all.begin() + nleftB, all.end()); B.mvKeysUn = B.mvKeys; }
+        std::vector<MapPoint*> out;
+        n = matcher.SearchByBoW(&A, B, out);
+        for (int j = 0; j < (int)out.size() && j < nB; ++j)
+            if (out[j])
+                for (int i = 0; i < nA; ++i)
+                    if (A.mvpMapPoints[i] == out[j]) { b2a[j] = i; a2b[i] = j; break; }
+    } else {
+        KeyFrame B;
+        B.N = nB; B.mvKeysUn = keys(kpsB, nB); B.mvKeys = B.mvKeysUn; B.mDescriptors = descs(descB, nB);
+        B.mFeatVec = featvec(nodesB, offB, idxB, nnodesB); B.mvpMapPoints = points(maskB, nB);
+        std::vector<MapPoint*> out;
+        n = matcher.SearchByBoW(&A, &B, out);
+        for (int i = 0; i < (int)out.size() && i < nA; ++i)
+            if (out[i])
+                for (int j = 0; j < nB; ++j)
+                    if (B.mvpMapPoints[j] == out[i]) { a2b[i] = j; b2a[j] = i; break; }
+    }
+    return n;
+}
+
+// SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) :706-821.
+int orbslam3_search_for_initialization(float nnratio, int checkOri, const KpPod* kps1, const uint8_t* desc1, int n1, const KpPod* kps2,
+                                       const uint8_t* desc2, int n2, float minX, float minY, float maxX, float maxY, float* prevMatched,
+                                       int windowSize, int32_t* matches12) {
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    Frame F1, F2;
+    F1.N = n1; F1.mvKeysUn = keys(kps1, n1); F1.mvKeys = F1.mvKeysUn; F1.mDescriptors = descs(desc1, n1);
+    F2.N = n2; F2.mvKeysUn = keys(kps2, n2); F2.mvKeys = F2.mvKeysUn; F2.mDescriptors = descs(desc2, n2);
+    F2.setBounds(minX, minY, maxX, maxY);
+    F2.AssignFeaturesToGrid();
+    std::vector<cv::Point2f> prev(n1);
+    for (int i = 0; i < n1; ++i) prev[i] = cv::Point2f(prevMatched[2 * i], prevMatched[2 * i + 1]);
+    std::vector<int> m12;
+    const int n = matcher.SearchForInitialization(F1, F2, prev, m12, windowSize);
+    for (int i = 0; i < n1; ++i) { matches12[i] = m12[i]; prevMatched[2 * i] = prev[i].x; prevMatched[2 * i + 1] = prev[i].y; }
+    return n;
+}
+
+// SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, th, bFarPoints, thFarPoints) :44-236.
+// Frame: kps = mvKeysUn (nleft == -1) or mvKeys ++ mvKeysRight; blocked[i]: mvpMapPoints[i] holds a MapPoint with observations.
+// MapPoints: one array per member the function reads.  mpOfFeature[n]: index of the MapPoint that ends up in
+// F.mvpMapPoints[i] (-1: entry untouched).  Returns nmatches.
+int orbslam3_search_by_projection_mappoints(float nnratio, const KpPod* kps, const uint8_t* desc, int n, int nleft, const uint8_t* blocked,
+                                            const float* uRight, const int32_t* l2r, const int32_t* r2l, float minX, float minY, float maxX,
+                                            float maxY, const float* scaleFactors, int nlevels, int m, const uint8_t* inView,
+                                            const uint8_t* inViewR, const uint8_t* bad, const float* depth, const float* projX,
+                                            const float* projY, const float* projXR, const float* projYR, const int32_t* level,
+                                            const int32_t* levelR, const float* viewCos, const float* viewCosR, const uint8_t* mpDesc,
+                                            const int32_t* obs, float th, int bFarPoints, float thFarPoints, int32_t* mpOfFeature) {
+    ORBmatcher matcher(nnratio, true);
+    Frame F;
+    F.N = n; F.Nleft = nleft; F.mDescriptors = descs(desc, n);
+    std::vector<cv::KeyPoint> all = keys(kps, n);
+    Pinhole rig(1.f, 1.f, 0.f, 0.f);
+    if (nleft == -1) { F.mvKeysUn = all; F.mvKeys = all; }
+    else { F.mvKeys.assign(all.begin(), all.begin() + nleft); F.mvKeysRight.assign(all.begin() + nleft, all.end()); F.mvKeysUn = F.mvKeys; F.mpCamera2 = &rig; F.Nright = n - nleft; }
+    F.mvuRight.assign(n, -1.f);
+    if (uRight) F.mvuRight.assign(uRight, uRight + n);
+    if (nleft != -1) {
+        F.mvLeftToRightMatch.assign(nleft, -1);
+        F.mvRightToLeftMatch.assign(n - nleft, -1);
+        if (l2r) F.mvLeftToRightMatch.assign(l2r, l2r + nleft);
+        if (r2l) F.mvRightToLeftMatch.assign(r2l, r2l + (n - nleft));
+    }
+    F.mvScaleFactors.assign(scaleFactors, scaleFactors + nlevels);
+    F.setBounds(minX, minY, maxX, maxY);
+    F.AssignFeaturesToGrid();
+    MapPoint old;
+    old.nObs = 1;
+    F.mvpMapPoints.assign(n, nullptr);
+    for (int i = 0; i < n; ++i) if (blocked && blocked[i]) F.mvpMapPoints[i] = &old;
+    std::vector<MapPoint> mps(m);
+    std::vector<MapPoint*> vp(m);
+    for (int i = 0; i < m; ++i) {
+        MapPoint& p = mps[i];
+        p.mbTrackInView = inView[i]; p.mbTrackInViewR = inViewR[i]; p.mbBad = bad[i]; p.mTrackDepth = depth[i];
+        p.mTrackProjX = projX[i]; p.mTrackProjY = projY[i]; p.mTrackProjXR = projXR[i]; p.mTrackProjYR = projYR[i];
+        p.mnTrackScaleLevel = level[i]; p.mnTrackScaleLevelR = levelR[i]; p.mTrackViewCos = viewCos[i]; p.mTrackViewCosR = viewCosR[i];
+        p.mDescriptor = descs(mpDesc + 32 * (size_t)i, 1).clone(); p.nObs = obs[i];
+        vp[i] = &p;
+    }
+    const int nm = matcher.SearchByProjection(F, vp, th, bFarPoints != 0, thFarPoints);
+    for (int i = 0; i < n; ++i) {
+        MapPoint* p = F.mvpMapPoints[i];
+        mpOfFeature[i] = (p && p != &old) ? (int32_t)(p - mps.data()) : -1;
+    }
+    return nm;
+}
+}

@@ -466,3 +466,85 @@ class DBoW2Vocabulary:
         self.L.orbslam3_voc_transform(self.h, _p(desc), n, int(levelsup), _p(words), _p(values), C.byref(nw), _p(nodes), _p(off),
                                       _p(idx), C.byref(nn))
         return words[:nw.value], values[:nw.value], nodes[:nn.value], off[:nn.value + 1], idx[:off[nn.value]]
+
+
+# ---- the reference's own ORBmatcher.cc (oracle/_ref/liborbslam3_orbmatcher.so, see oracle/Makefile) ----
+REF_MATCHER_LIB = os.path.join(os.path.dirname(REF_LIB), "liborbslam3_orbmatcher.so")
+_ref_matcher = None
+
+
+def ref_matcher_available():
+    return os.path.exists(REF_MATCHER_LIB)
+
+
+def ref_matcher():
+    global _ref_matcher
+    if _ref_matcher is None:
+        L = C.CDLL(REF_MATCHER_LIB)
+        L.orbslam3_search_bow.argtypes = [_I, _F, _I, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _I, _P, _P, _P, _P, _I, _I, _P, _P]
+        L.orbslam3_search_for_initialization.argtypes = [_F, _I, _P, _P, _I, _P, _P, _I, _F, _F, _F, _F, _P, _I, _P]
+        L.orbslam3_search_by_projection_mappoints.argtypes = [_F, _P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I] + [_P] * 14 + \
+            [_F, _I, _F, _P]
+        _ref_matcher = L
+    return _ref_matcher
+
+
+def _kp_with_angle(angles):
+    k = np.zeros(len(angles), KEYPOINT_DTYPE)
+    k["angle"] = angles
+    return k
+
+
+def ref_descriptor_distance(a, b):
+    a, b = np.ascontiguousarray(a, np.uint8), np.ascontiguousarray(b, np.uint8)
+    return ref_matcher().orbslam3_descriptor_distance(_p(a), _p(b))
+
+
+def ref_three_maxima(counts):
+    c = np.ascontiguousarray(counts, np.int32)
+    out = np.zeros(3, np.int32)
+    ref_matcher().orbslam3_three_maxima(_p(c), len(c), _p(out))
+    return tuple(int(v) for v in out)
+
+
+def ref_search_bow(form, descA, fvA, maskA, angA, descB, fvB, maskB, angB, ratio, check_ori, nleft=-1):
+    """ORBmatcher::SearchByBoW of the reference itself.  form 0: (KeyFrame*, Frame&), form 1: (KeyFrame*, KeyFrame*)."""
+    descA, descB = np.ascontiguousarray(descA, np.uint8), np.ascontiguousarray(descB, np.uint8)
+    maskA = np.ascontiguousarray(maskA).astype(np.uint8)
+    maskB = None if maskB is None else np.ascontiguousarray(maskB).astype(np.uint8)
+    kA, kB = _kp_with_angle(angA), _kp_with_angle(angB)
+    a2b, b2a = np.zeros(max(len(descA), 1), np.int32), np.zeros(max(len(descB), 1), np.int32)
+    n = ref_matcher().orbslam3_search_bow(form, ratio, int(check_ori), _p(kA), _p(descA), len(descA), _p(maskA), _p(fvA.node_ids),
+                                          _p(fvA.offsets), _p(fvA.indices), len(fvA.node_ids), _p(kB), _p(descB), len(descB), _pn(maskB),
+                                          _p(fvB.node_ids), _p(fvB.offsets), _p(fvB.indices), len(fvB.node_ids), nleft, _p(a2b), _p(b2a))
+    return a2b[:len(descA)], b2a[:len(descB)], n
+
+
+def ref_search_for_initialization(kps1, desc1, F2, prev_matched, window_size, nnratio, check_ori):
+    kps1, desc1 = np.ascontiguousarray(kps1), np.ascontiguousarray(desc1, np.uint8)
+    prev = np.array(prev_matched, np.float32).reshape(-1, 2).copy()
+    m12 = np.zeros(max(len(kps1), 1), np.int32)
+    n = ref_matcher().orbslam3_search_for_initialization(float(nnratio), int(check_ori), _p(kps1), _p(desc1), len(kps1), _p(F2.kps),
+                                                         _p(F2.desc), F2.n, float(F2.min_x), float(F2.min_y), float(F2.max_x),
+                                                         float(F2.max_y), _p(prev), int(window_size), _p(m12))
+    return n, m12[:len(kps1)], prev
+
+
+def ref_search_by_projection_mappoints(F, mp, th, nnratio, far, th_far):
+    """ORBmatcher::SearchByProjection(Frame&, vpMapPoints, th, bFarPoints, thFarPoints) of the reference itself on a
+    projection.GridFrame and the MapPoint member arrays of tests/proj_cases.mp_inputs."""
+    m = len(mp["desc"])
+    u8 = lambda a: np.ascontiguousarray(a).astype(np.uint8)
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    i32 = lambda a: np.ascontiguousarray(a, np.int32)
+    arrs = [u8(mp["in_view"]), u8(mp["in_view_r"]), u8(mp["bad"]), f32(mp["depth"]), f32(mp["proj_x"]), f32(mp["proj_y"]),
+            f32(mp["proj_xr"]), f32(mp["proj_yr"]), i32(mp["level"]), i32(mp["level_r"]), f32(mp["view_cos"]), f32(mp["view_cos_r"]),
+            np.ascontiguousarray(mp["desc"], np.uint8), i32(mp["obs"])]
+    out = np.zeros(max(F.n, 1), np.int32)
+    sf = f32(F.scale_factors)
+    opt = lambda a: None if a is None else _p(a)
+    n = ref_matcher().orbslam3_search_by_projection_mappoints(
+        float(nnratio), _p(F.kps), _p(F.desc), F.n, F.nleft, opt(F.blocked), opt(F.u_right), opt(F.left_to_right), opt(F.right_to_left),
+        float(F.min_x), float(F.min_y), float(F.max_x), float(F.max_y), _p(sf), len(sf), m, *[_p(a) for a in arrs], float(th), int(far),
+        float(th_far), _p(out))
+    return n, out[:F.n]

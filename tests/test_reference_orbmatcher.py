@@ -1,0 +1,66 @@
+"""CPU: the reference's OWN src/ORBmatcher.cc + include/ORBmatcher.h, compiled unmodified into
+oracle/_ref/liborbslam3_orbmatcher.so (the include guards of Frame.h / KeyFrame.h / MapPoint.h are pre-defined and the
+data-holder stand-ins of oracle/refshim/orbslam3_standin.h force-included), against the C++ oracle and the golden
+vectors of the Python restatements: DescriptorDistance, ComputeThreeMaxima, both SearchByBoW overloads,
+SearchForInitialization and SearchByProjection(Frame&, vpMapPoints, ...)."""
+import os
+
+import numpy as np
+import pytest
+
+import match_cases as mc
+import oracle_binding as ob
+import orbfe
+import proj_cases as pc
+from common import GOLDEN
+from test_match_oracle import extract
+
+pytestmark = pytest.mark.skipif(not ob.ref_matcher_available(), reason="oracle/_ref not built (needs /root/reference; make -C oracle ref)")
+
+
+def test_descriptor_distance_and_three_maxima():
+    d = orbfe.synth.descriptors(11, 200)
+    for i in range(0, 200, 2):
+        assert ob.ref_descriptor_distance(d[i], d[i + 1]) == ob.descriptor_distance(d[i], d[i + 1]) == int(np.unpackbits(d[i] ^ d[i + 1]).sum())
+    rng = np.random.default_rng(5)
+    for _ in range(300):
+        h = rng.integers(0, 12, 30) * (rng.random(30) < rng.random())
+        if rng.random() < 0.3:
+            h[rng.integers(0, 30, 3)] = h.max()                     # ties between the maxima
+        assert ob.ref_three_maxima(h) == ob.three_maxima(h)
+
+
+@pytest.mark.parametrize("name", list(mc.BOW_CASES))
+def test_search_by_bow(name):
+    c = mc.bow_inputs(name, extract)
+    g = np.load(os.path.join(GOLDEN, f"match_{name}.npz"))
+    ang1, ang2 = c["k1"]["angle"], c["k2"]["angle"]
+    # SearchByBoW(KeyFrame*, Frame&, ...)
+    a2b, b2a, n = ob.ref_search_bow(0, c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], None, ang2, 0.7, c["check_ori"], c["nleft"])
+    oa2b, ob2a, on = ob.search_bow(c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], None, ang2, 0.7, c["check_ori"], strict=False,
+                                   nleft=c["nleft"])
+    assert n == on == int(g["n_kf_f"]) and np.array_equal(b2a, ob2a) and np.array_equal(b2a, g["kf_f"]) and n > 100
+    # SearchByBoW(KeyFrame*, KeyFrame*, ...)
+    a2b, b2a, n = ob.ref_search_bow(1, c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], c["mp2"], ang2, 0.8, c["check_ori"])
+    oa2b, ob2a, on = ob.search_bow(c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], c["mp2"], ang2, 0.8, c["check_ori"], strict=True)
+    assert n == on == int(g["n_kf_kf"]) and np.array_equal(a2b, oa2b) and np.array_equal(a2b, g["kf_kf"])
+
+
+@pytest.mark.parametrize("name", list(pc.INIT_CASES))
+def test_search_for_initialization(name):
+    c = pc.init_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    n, m12, prev = ob.ref_search_for_initialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], c["win"], c["nnratio"], c["ori"])
+    on, om12, oprev = ob.search_for_initialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], c["win"], c["nnratio"], c["ori"])
+    assert n == on == int(g["n"]) and np.array_equal(m12, om12) and np.array_equal(m12, g["vnMatches12"])
+    assert np.array_equal(prev, oprev) and np.array_equal(prev, g["prev_matched"])
+
+
+@pytest.mark.parametrize("name", list(pc.MP_CASES))
+def test_search_by_projection_local_points(name):
+    from test_proj_oracle import run_mp
+    c = pc.mp_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    n, res = ob.ref_search_by_projection_mappoints(c["F"], c["mp"], c["th"], c["nnratio"], c["far"], c["th_far"])
+    ores, on, _, _ = run_mp(c, ob.search_by_projection)
+    assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["mappoint_of_feature"])
