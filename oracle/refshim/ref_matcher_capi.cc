@@ -166,4 +166,44 @@ int orbslam3_search_by_projection_mappoints(float nnratio, const KpPod* kps, con
     }
     return nm;
 }
+
+// SearchForTriangulation_(pKF1, pKF2, F12, vMatchedPairs, bOnlyStereo, bCoarse) :1208-1432 with pinhole cameras.
+// hasMp*: the feature already holds a MapPoint; uRight*: mvuRight; F12 row-major; (ex, ey): the epipole in image 2.
+// matches12[n1]: partner in keyframe 2 or -1 (what vMatchedPairs lists in ascending idx1).  Returns nmatches.
+int orbslam3_search_for_triangulation(float nnratio, int checkOri, const KpPod* kps1, const uint8_t* desc1, int n1, const uint8_t* hasMp1,
+                                      const float* uRight1, const uint32_t* nodes1, const int32_t* off1, const int32_t* idx1, int nnodes1,
+                                      const KpPod* kps2, const uint8_t* desc2, int n2, const uint8_t* hasMp2, const float* uRight2,
+                                      const uint32_t* nodes2, const int32_t* off2, const int32_t* idx2, int nnodes2, const float* sigma2,
+                                      const float* scale, int nlevels, const float* F12, float ex, float ey, int onlyStereo, int coarse,
+                                      int32_t* matches12) {
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    MapPoint some;
+    Pinhole cam1(1.f, 1.f, 0.f, 0.f), cam2(1.f, 1.f, 0.f, 0.f);
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) cam1.F12(i, j) = F12[3 * i + j];
+    cam2.fixedEpipole = true;
+    cam2.epipole = cv::Point2f(ex, ey);
+    auto fill = [&](KeyFrame& K, const KpPod* kps, const uint8_t* desc, int n, const uint8_t* hasMp, const float* ur, const uint32_t* nodes,
+                    const int32_t* off, const int32_t* idx, int nnodes, Pinhole* cam) {
+        K.N = n; K.mvKeysUn = keys(kps, n); K.mvKeys = K.mvKeysUn; K.mDescriptors = descs(desc, n);
+        K.mFeatVec = featvec(nodes, off, idx, nnodes);
+        K.mvpMapPoints.assign(n, nullptr);
+        for (int i = 0; i < n; ++i) if (hasMp[i]) K.mvpMapPoints[i] = &some;
+        K.mvuRight.assign(ur, ur + n);
+        K.mvLevelSigma2.assign(sigma2, sigma2 + nlevels);
+        K.mvScaleFactors.assign(scale, scale + nlevels);
+        K.mpCamera = cam;
+        K.Tcw = cv::Mat::zeros(4, 4, CV_32F);
+        for (int i = 0; i < 4; ++i) K.Tcw.at<float>(i, i) = 1.f;
+    };
+    KeyFrame K1, K2;
+    fill(K1, kps1, desc1, n1, hasMp1, uRight1, nodes1, off1, idx1, nnodes1, &cam1);
+    fill(K2, kps2, desc2, n2, hasMp2, uRight2, nodes2, off2, idx2, nnodes2, &cam2);
+    cv::Matx33f F;
+    for (int i = 0; i < 3; ++i) for (int j = 0; j < 3; ++j) F(i, j) = F12[3 * i + j];
+    std::vector<std::pair<size_t, size_t>> pairs;
+    const int n = matcher.SearchForTriangulation_(&K1, &K2, F, pairs, onlyStereo != 0, coarse != 0);
+    for (int i = 0; i < n1; ++i) matches12[i] = -1;
+    for (const auto& pr : pairs) matches12[pr.first] = (int32_t)pr.second;
+    return n;
+}
 }

@@ -548,3 +548,24 @@ def ref_search_by_projection_mappoints(F, mp, th, nnratio, far, th_far):
         float(F.min_x), float(F.min_y), float(F.max_x), float(F.max_y), _p(sf), len(sf), m, *[_p(a) for a in arrs], float(th), int(far),
         float(th_far), _p(out))
     return n, out[:F.n]
+
+
+def ref_search_triangulation(kpA, descA, fvA, mpA, urA, kpB, descB, fvB, mpB, urB, sigma2, scale, F12, ep, nnratio, check_ori,
+                             only_stereo, coarse):
+    """ORBmatcher::SearchForTriangulation_ of the reference itself (pinhole; F12 and the epipole as the C ABI receives them)."""
+    L = ref_matcher()
+    L.orbslam3_search_for_triangulation.argtypes = [_F, _I, _P, _P, _I, _P, _P, _P, _P, _P, _I, _P, _P, _I, _P, _P, _P, _P, _P, _I, _P, _P,
+                                                    _I, _P, _F, _F, _I, _I, _P]
+    kpA, kpB = np.ascontiguousarray(kpA), np.ascontiguousarray(kpB)
+    descA, descB = np.ascontiguousarray(descA, np.uint8), np.ascontiguousarray(descB, np.uint8)
+    mpA, mpB = np.ascontiguousarray(mpA).astype(np.uint8), np.ascontiguousarray(mpB).astype(np.uint8)
+    urA, urB = np.ascontiguousarray(urA, np.float32), np.ascontiguousarray(urB, np.float32)
+    sigma2, scale = np.ascontiguousarray(sigma2, np.float32), np.ascontiguousarray(scale, np.float32)
+    F12 = np.ascontiguousarray(F12, np.float32).reshape(9)
+    m12 = np.zeros(max(len(descA), 1), np.int32)
+    n = L.orbslam3_search_for_triangulation(float(nnratio), int(check_ori), _p(kpA), _p(descA), len(descA), _p(mpA), _p(urA),
+                                            _p(fvA.node_ids), _p(fvA.offsets), _p(fvA.indices), len(fvA.node_ids), _p(kpB), _p(descB),
+                                            len(descB), _p(mpB), _p(urB), _p(fvB.node_ids), _p(fvB.offsets), _p(fvB.indices),
+                                            len(fvB.node_ids), _p(sigma2), _p(scale), len(sigma2), _p(F12), float(ep[0]), float(ep[1]),
+                                            int(only_stereo), int(coarse), _p(m12))
+    return m12[:len(descA)], n

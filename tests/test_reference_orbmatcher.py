@@ -64,3 +64,17 @@ def test_search_by_projection_local_points(name):
     n, res = ob.ref_search_by_projection_mappoints(c["F"], c["mp"], c["th"], c["nnratio"], c["far"], c["th_far"])
     ores, on, _, _ = run_mp(c, ob.search_by_projection)
     assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["mappoint_of_feature"])
+
+
+@pytest.mark.parametrize("name", list(mc.TRI_CASES))
+def test_search_for_triangulation(name):
+    from test_match_oracle import tables
+    sc, isc, s2, is2, per, umax = tables()
+    c = mc.tri_inputs(name, extract, sc, s2)
+    g = np.load(os.path.join(GOLDEN, f"match_{name}.npz"))
+    m12, n = ob.ref_search_triangulation(c["k1"], c["d1"], c["fv1"], c["mp1"], c["ur1"], c["k2"], c["d2"], c["fv2"], c["mp2"], c["ur2"],
+                                         s2, sc, c["F12"], c["ep"], 0.6, c["check_ori"], c["only_stereo"], c["coarse"])
+    om12, on = ob.search_triangulation(c["k1"], c["d1"], c["fv1"], c["mp1"], c["ur1"], c["k2"], c["d2"], c["fv2"], c["mp2"], c["ur2"],
+                                       s2, sc, c["F12"], c["ep"], c["check_ori"], c["only_stereo"], c["coarse"])
+    assert n == on and np.array_equal(m12, om12)
+    assert n == int(g["n"]) and np.array_equal(m12, g["m12"])
