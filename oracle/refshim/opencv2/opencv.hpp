@@ -169,17 +169,19 @@ inline void Mat::copyTo(const _OutputArray& dst) const {
     for (int y = 0; y < rows; ++y) std::memmove(d.ptr(y), ptr(y), (size_t)cols * esz_);
 }
 
-// ---- float matrices (CV_32F): the small dense algebra ORBmatcher.cc writes with cv::Mat.  Products and dot products
-// accumulate in double and round once to float, like OpenCV's float GEMM; expressions are evaluated operator by
-// operator (OpenCV fuses A*B+C into one GEMM call, which can differ in the last bit).
+// ---- float matrices (CV_32F): the small dense algebra ORBmatcher.cc writes with cv::Mat.  OpenCV evaluates A*B (+C) of
+// such sizes in plain float, products summed left to right, C added last (checked against cv2.gemm 4.13 on 20 000 random
+// 3x3 * 3x1 + 3x1 and 3x3 * 3x3 cases: identical every time; a double accumulator matches only 14-19 % of them);
+// cv::norm accumulates squares in double.  Expressions are evaluated operator by operator, which for A*B+C gives the
+// same float operations in the same order as the fused GEMM.
 inline Mat operator*(const Mat& a, const Mat& b) {
     assert(a.type() == CV_32F && b.type() == CV_32F && a.cols == b.rows);
     Mat c(a.rows, b.cols, CV_32F);
     for (int i = 0; i < a.rows; ++i)
         for (int j = 0; j < b.cols; ++j) {
-            double s = 0;
-            for (int k = 0; k < a.cols; ++k) s += (double)a.at<float>(i, k) * (double)b.at<float>(k, j);
-            c.at<float>(i, j) = (float)s;
+            float s = a.at<float>(i, 0) * b.at<float>(0, j);
+            for (int k = 1; k < a.cols; ++k) s += a.at<float>(i, k) * b.at<float>(k, j);
+            c.at<float>(i, j) = s;
         }
     return c;
 }

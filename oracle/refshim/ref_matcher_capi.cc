@@ -206,4 +206,74 @@ int orbslam3_search_for_triangulation(float nnratio, int checkOri, const KpPod* 
     for (const auto& pr : pairs) matches12[pr.first] = (int32_t)pr.second;
     return n;
 }
+
+namespace {
+cv::Mat mat44(const float* t) {
+    cv::Mat m(4, 4, CV_32F);
+    memcpy(m.data, t, 64);
+    return m;
+}
+cv::Mat vec3(const float* v) {
+    cv::Mat m(3, 1, CV_32F);
+    memcpy(m.data, v, 12);
+    return m;
+}
+// A Frame from the arrays of orbfe_grid_frame (kps = mvKeysUn, or mvKeys ++ mvKeysRight when nleft != -1).
+void fillFrame(Frame& F, Pinhole* cam, Pinhole* rig, MapPoint* old, const KpPod* kps, const uint8_t* desc, int n, int nleft, const uint8_t* blocked,
+               const float* uRight, float minX, float minY, float maxX, float maxY, const float* scaleFactors, int nlevels) {
+    F.N = n; F.Nleft = nleft; F.mDescriptors = descs(desc, n);
+    std::vector<cv::KeyPoint> all = keys(kps, n);
+    if (nleft == -1) { F.mvKeysUn = all; F.mvKeys = all; }
+    else { F.mvKeys.assign(all.begin(), all.begin() + nleft); F.mvKeysRight.assign(all.begin() + nleft, all.end()); F.mvKeysUn = F.mvKeys; F.mpCamera2 = rig; F.Nright = n - nleft; }
+    F.mpCamera = cam;
+    F.mvuRight.assign(n, -1.f);
+    if (uRight) F.mvuRight.assign(uRight, uRight + n);
+    F.mvScaleFactors.assign(scaleFactors, scaleFactors + nlevels);
+    F.mnScaleLevels = nlevels;
+    F.setBounds(minX, minY, maxX, maxY);
+    F.AssignFeaturesToGrid();
+    F.mvpMapPoints.assign(n, nullptr);
+    for (int i = 0; i < n; ++i) if (blocked && blocked[i]) F.mvpMapPoints[i] = old;
+}
+}  // namespace
+
+extern "C" {
+// SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono) :2173-2389.  cam: fx, fy, cx, cy of mpCamera;
+// Tcw / Tlw: 4x4 row-major poses of the current / last frame; Trl: CurrentFrame.mTrl (3x4 used) or NULL.
+// lastOfFeature[n]: LastFrame feature whose MapPoint ends up in CurrentFrame.mvpMapPoints[i], -1 otherwise.
+int orbslam3_search_by_projection_lastframe(int checkOri, const KpPod* kps, const uint8_t* desc, int n, int nleft, const uint8_t* blocked,
+                                            const float* uRight, float minX, float minY, float maxX, float maxY, const float* scaleFactors,
+                                            int nlevels, float mbf, float mb, const float* cam, const float* Tcw, const float* Tlw,
+                                            const float* Trl, int m, const uint8_t* hasMp, const uint8_t* outlier, const int32_t* octave,
+                                            const float* angle, const float* worldPos, const uint8_t* mpDesc, const int32_t* obs, float th,
+                                            int bMono, int32_t* lastOfFeature) {
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    Pinhole camera(cam[0], cam[1], cam[2], cam[3]), rig(1.f, 1.f, 0.f, 0.f);
+    MapPoint old;
+    Frame Cur, Last;
+    fillFrame(Cur, &camera, &rig, &old, kps, desc, n, nleft, blocked, uRight, minX, minY, maxX, maxY, scaleFactors, nlevels);
+    Cur.mbf = mbf; Cur.mb = mb; Cur.mTcw = mat44(Tcw);
+    if (Trl) Cur.mTrl = mat44(Trl).rowRange(0, 3).clone();       // Frame::mTrl is 3 x 4
+    Last.N = m; Last.mTcw = mat44(Tlw);
+    Last.mvKeys.resize(m);
+    for (int i = 0; i < m; ++i) { Last.mvKeys[i].octave = octave[i]; Last.mvKeys[i].angle = angle[i]; }
+    Last.mvKeysUn = Last.mvKeys;
+    Last.mvbOutlier.resize(m);
+    std::vector<MapPoint> mps(m);
+    Last.mvpMapPoints.assign(m, nullptr);
+    for (int i = 0; i < m; ++i) {
+        Last.mvbOutlier[i] = outlier[i] != 0;
+        mps[i].mWorldPos = vec3(worldPos + 3 * (size_t)i);
+        mps[i].mDescriptor = descs(mpDesc + 32 * (size_t)i, 1).clone();
+        mps[i].nObs = obs[i];
+        if (hasMp[i]) Last.mvpMapPoints[i] = &mps[i];
+    }
+    const int nm = matcher.SearchByProjection(Cur, Last, th, bMono != 0);
+    for (int i = 0; i < n; ++i) {
+        MapPoint* p = Cur.mvpMapPoints[i];
+        lastOfFeature[i] = (p && p != &old) ? (int32_t)(p - mps.data()) : -1;
+    }
+    return nm;
+}
+}
 }

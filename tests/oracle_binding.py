@@ -569,3 +569,30 @@ def ref_search_triangulation(kpA, descA, fvA, mpA, urA, kpB, descB, fvB, mpB, ur
                                             len(fvB.node_ids), _p(sigma2), _p(scale), len(sigma2), _p(F12), float(ep[0]), float(ep[1]),
                                             int(only_stereo), int(coarse), _p(m12))
     return m12[:len(descA)], n
+
+
+def ref_search_by_projection_lastframe(Cur, last, Tcw, th, fb, cam, Trl, check_ori):
+    """ORBmatcher::SearchByProjection(CurrentFrame, LastFrame, th, bMono) of the reference itself.  fb = (bForward,
+    bBackward): LastFrame's pose is the current one moved +-1 m along z (or not at all) so that the reference derives
+    those flags itself (:2184-2194) with mb = 0.11."""
+    L = ref_matcher()
+    L.orbslam3_search_by_projection_lastframe.argtypes = [_I, _P, _P, _I, _I, _P, _P, _F, _F, _F, _F, _P, _I, _F, _F, _P, _P, _P, _P, _I,
+                                                          _P, _P, _P, _P, _P, _P, _P, _F, _I, _P]
+    f32 = lambda a: np.ascontiguousarray(a, np.float32)
+    u8 = lambda a: np.ascontiguousarray(a).astype(np.uint8)
+    Tcw = f32(Tcw).reshape(4, 4)
+    Tlw = Tcw.copy()
+    Tlw[2, 3] += np.float32(1.0 if fb[0] else -1.0 if fb[1] else 0.0)
+    sf = f32(Cur.scale_factors)
+    cam = f32(cam[:4])
+    m = len(last["has_mp"])
+    arrs = [u8(last["has_mp"]), u8(last["outlier"]), np.ascontiguousarray(last["octave"], np.int32), f32(last["angle"]),
+            f32(last["world_pos"]), np.ascontiguousarray(last["desc"], np.uint8), np.ascontiguousarray(last["obs"], np.int32)]
+    out = np.zeros(max(Cur.n, 1), np.int32)
+    opt = lambda a: None if a is None else _p(a)
+    trl = None if Trl is None else f32(Trl).reshape(4, 4)
+    n = L.orbslam3_search_by_projection_lastframe(int(check_ori), _p(Cur.kps), _p(Cur.desc), Cur.n, Cur.nleft, opt(Cur.blocked),
+                                                  opt(Cur.u_right), float(Cur.min_x), float(Cur.min_y), float(Cur.max_x), float(Cur.max_y),
+                                                  _p(sf), len(sf), float(Cur.mbf), 0.11, _p(cam), _p(Tcw), _p(Tlw), opt(trl), m,
+                                                  *[_p(a) for a in arrs], float(th), 0, _p(out))
+    return n, out[:Cur.n]

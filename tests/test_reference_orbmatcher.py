@@ -78,3 +78,17 @@ def test_search_for_triangulation(name):
                                        s2, sc, c["F12"], c["ep"], c["check_ori"], c["only_stereo"], c["coarse"])
     assert n == on and np.array_equal(m12, om12)
     assert n == int(g["n"]) and np.array_equal(m12, g["m12"])
+
+
+@pytest.mark.parametrize("name", list(pc.LF_CASES))
+def test_search_by_projection_last_frame(name):
+    """SearchByProjection(CurrentFrame, LastFrame, th, bMono) :2173: the reference projects with its own cv::Mat lines."""
+    from test_proj_oracle import run_lf
+    c = pc.lf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    Trl = np.eye(4, dtype=np.float32)
+    Trl[:3, 3] = (-0.101, 0.0, 0.0)
+    n, res = ob.ref_search_by_projection_lastframe(c["Cur"], c["last"], c["Tcw"], c["th"], c["fb"], pc.CAM, Trl, c["ori"])
+    ores, on, _, _ = run_lf(c, ob.search_by_projection)
+    assert n == on == int(g["n"])
+    assert np.array_equal(res, np.where(ores >= 0, ores, -1)) and np.array_equal(res, np.where(g["lastframe_feature_of_feature"] >= 0, g["lastframe_feature_of_feature"], -1))
