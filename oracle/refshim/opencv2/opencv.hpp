@@ -196,10 +196,12 @@ inline Mat operator*(const Mat& a, const Mat& b) {
 ORBREF_MAT_EW(+)
 ORBREF_MAT_EW(-)
 #undef ORBREF_MAT_EW
+// A * s, A / s: OpenCV scales with convertTo, whose scale factor is narrowed to float for CV_32F (A / s multiplies by (float)(1 / s))
 inline Mat operator*(const Mat& a, double s) {
     Mat c(a.rows, a.cols, CV_32F);
+    const float f = (float)s;
     for (int i = 0; i < a.rows; ++i)
-        for (int j = 0; j < a.cols; ++j) c.at<float>(i, j) = (float)(a.at<float>(i, j) * s);
+        for (int j = 0; j < a.cols; ++j) c.at<float>(i, j) = a.at<float>(i, j) * f;
     return c;
 }
 inline Mat operator*(double s, const Mat& a) { return a * s; }

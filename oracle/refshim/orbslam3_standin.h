@@ -107,8 +107,11 @@ public:
         auto it = mObservations.find(pKF);
         return it != mObservations.end() ? it->second : std::tuple<int, int>(-1, -1);
     }
-    void AddObservation(KeyFrame* pKF, int idx) { mObservations[pKF] = std::tuple<int, int>(idx, -1); ++nObs; }
-    void Replace(MapPoint* pMP) { mpReplaced = pMP; mbBad = true; }
+    // Test tap: every (MapPoint, feature index) that Fuse joins — AddObservation from the matcher, and both parties of a Replace.
+    static std::vector<std::pair<MapPoint*, int>>& fuseLog() { static std::vector<std::pair<MapPoint*, int>> v; return v; }
+    void AddObservation(KeyFrame* pKF, int idx) { fuseLog().push_back(std::make_pair(this, idx)); observe(pKF, idx); }
+    void observe(KeyFrame* pKF, int idx) { mObservations[pKF] = std::tuple<int, int>(idx, -1); ++nObs; }
+    inline void Replace(MapPoint* pMP);                                    // src/MapPoint.cc:226-283
 };
 
 // The 64 x 48 feature grid of Frame::AssignFeaturesToGrid / PosInGrid (src/Frame.cc:380-411, 708-719), shared by Frame and
@@ -203,8 +206,9 @@ public:
 
     std::vector<MapPoint*> GetMapPointMatches() { return mvpMapPoints; }
     MapPoint* GetMapPoint(const std::size_t& idx) { return mvpMapPoints[idx]; }
+    std::set<MapPoint*> mspExtra;          // test hook: MapPoints the keyframe observes at features outside the test's arrays
     std::set<MapPoint*> GetMapPoints() {
-        std::set<MapPoint*> s;
+        std::set<MapPoint*> s(mspExtra);
         for (MapPoint* p : mvpMapPoints) if (p && !p->isBad()) s.insert(p);
         return s;
     }
@@ -262,6 +266,25 @@ public:
     cv::Matx31f GetRightTranslation_() { return m31(GetRightTranslation()); }
     cv::Matx31f GetRightCameraCenter_() { return m31(GetRightCameraCenter()); }
 };
+
+// src/MapPoint.cc:226-283: this point goes bad, its observations move to pMP (or are erased where pMP is already seen).
+inline void MapPoint::Replace(MapPoint* pMP) {
+    if (pMP == this) return;
+    std::map<KeyFrame*, std::tuple<int, int>> obs = mObservations;
+    for (auto& o : pMP->mObservations)                                      // the feature where the two points met
+        if (!obs.count(o.first)) { fuseLog().push_back(std::make_pair(this, std::get<0>(o.second))); fuseLog().push_back(std::make_pair(pMP, std::get<0>(o.second))); }
+    mObservations.clear();
+    mbBad = true;
+    mpReplaced = pMP;
+    for (auto& o : obs) {
+        KeyFrame* pKF = o.first;
+        const int idx = std::get<0>(o.second);
+        fuseLog().push_back(std::make_pair(this, idx));
+        fuseLog().push_back(std::make_pair(pMP, idx));
+        if (!pMP->IsInKeyFrame(pKF)) { pKF->mvpMapPoints[idx] = pMP; pMP->observe(pKF, idx); }
+        else pKF->mvpMapPoints[idx] = nullptr;
+    }
+}
 
 inline int MapPoint::PredictScale(const float& currentDist, KeyFrame* pKF) {
     float ratio = mfMaxDistance / currentDist;

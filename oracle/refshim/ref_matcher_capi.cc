@@ -277,3 +277,108 @@ int orbslam3_search_by_projection_lastframe(int checkOri, const KpPod* kps, cons
 }
 }
 }
+
+namespace {
+struct KfInput {             // a KeyFrame in the arrays of orbfe_grid_frame + what the KeyFrame-side searches read besides
+    const KpPod* kps; const uint8_t* desc; int n, nleft; const uint8_t* blocked; const float* uRight;
+    float minX, minY, maxX, maxY; const float* scaleFactors; const float* invLevelSigma2; int nlevels;
+    float cam[4]; float mbf; float logScaleFactor; const float* Tcw;
+};
+struct KfPoints {            // vpPoints as arrays
+    int m; const uint8_t* null; const uint8_t* bad; const uint8_t* flagged; const float* worldPos; const float* normal;
+    const float* minDist; const float* maxDist; const uint8_t* desc;
+};
+void fillKeyFrame(KeyFrame& K, Pinhole* cam, std::vector<MapPoint>& occupants, const KfInput& in) {
+    const int n = in.n;
+    K.N = n; K.NLeft = in.nleft; K.mDescriptors = descs(in.desc, n);
+    std::vector<cv::KeyPoint> all = keys(in.kps, n);
+    if (in.nleft == -1) { K.mvKeysUn = all; K.mvKeys = all; }
+    else { K.mvKeys.assign(all.begin(), all.begin() + in.nleft); K.mvKeysRight.assign(all.begin() + in.nleft, all.end()); K.mvKeysUn = K.mvKeys; K.mpCamera2 = cam; K.NRight = n - in.nleft; }
+    K.mpCamera = cam;
+    K.fx = in.cam[0]; K.fy = in.cam[1]; K.cx = in.cam[2]; K.cy = in.cam[3]; K.mbf = in.mbf; K.mfLogScaleFactor = in.logScaleFactor;
+    K.mvuRight.assign(n, -1.f);
+    if (in.uRight) K.mvuRight.assign(in.uRight, in.uRight + n);
+    K.mvScaleFactors.assign(in.scaleFactors, in.scaleFactors + in.nlevels);
+    if (in.invLevelSigma2) K.mvInvLevelSigma2.assign(in.invLevelSigma2, in.invLevelSigma2 + in.nlevels);
+    K.mnScaleLevels = in.nlevels;
+    K.setBounds(in.minX, in.minY, in.maxX, in.maxY);
+    K.AssignFeaturesToGrid();
+    K.Tcw = mat44(in.Tcw);
+    K.Tcr = cv::Mat::zeros(4, 4, CV_32F);
+    for (int i = 0; i < 4; ++i) K.Tcr.at<float>(i, i) = 1.f;
+    K.mvpMapPoints.assign(n, nullptr);
+    occupants.assign(n, MapPoint());
+    for (int i = 0; i < n; ++i)
+        if (in.blocked && in.blocked[i]) { occupants[i].observe(&K, i); occupants[i].nObs = 1; K.mvpMapPoints[i] = &occupants[i]; }
+}
+void fillPoints(std::vector<MapPoint>& mps, std::vector<MapPoint*>& vp, const KfPoints& P) {
+    mps.assign(P.m, MapPoint());
+    vp.assign(P.m, nullptr);
+    for (int i = 0; i < P.m; ++i) {
+        MapPoint& p = mps[i];
+        p.mbBad = P.bad && P.bad[i];
+        p.mWorldPos = vec3(P.worldPos + 3 * (size_t)i);
+        p.mNormalVector = vec3(P.normal + 3 * (size_t)i);
+        p.mfMinDistance = P.minDist[i]; p.mfMaxDistance = P.maxDist[i];
+        p.mDescriptor = descs(P.desc + 32 * (size_t)i, 1).clone();
+        p.nObs = 1;
+        if (!(P.null && P.null[i])) vp[i] = &p;
+    }
+}
+}  // namespace
+
+extern "C" {
+// SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, th, ratioHamming) :473-585.  blocked = vpMatched[idx] != NULL;
+// P.flagged = the point is in spAlreadyFound (it sits in vpMatched beyond the keyframe's own features).
+// pointOfFeature[n]: index of the point written to vpMatched[idx], -1 elsewhere.
+int orbslam3_search_by_projection_sim3(const KfInput* in, const float* Scw, const KfPoints* P, int th, float ratioHamming, int32_t* pointOfFeature) {
+    ORBmatcher matcher(0.9f, true);
+    Pinhole cam(in->cam[0], in->cam[1], in->cam[2], in->cam[3]);
+    KeyFrame K;
+    std::vector<MapPoint> occ, mps;
+    std::vector<MapPoint*> vp;
+    fillKeyFrame(K, &cam, occ, *in);
+    fillPoints(mps, vp, *P);
+    std::vector<MapPoint*> vpMatched(K.mvpMapPoints);
+    for (int i = 0; i < P->m; ++i) if (P->flagged && P->flagged[i]) vpMatched.push_back(&mps[i]);
+    const int nm = matcher.SearchByProjection(&K, mat44(Scw), vp, vpMatched, th, ratioHamming);
+    for (int i = 0; i < in->n; ++i) {
+        MapPoint* p = vpMatched[i];
+        pointOfFeature[i] = (p && p >= mps.data() && p < mps.data() + mps.size()) ? (int32_t)(p - mps.data()) : -1;
+    }
+    return nm;
+}
+
+// Fuse(KeyFrame* pKF, vpMapPoints, th, bRight) :1629-1821 (scw == NULL; P.flagged = the point is already observed by pKF) and
+// Fuse(KeyFrame* pKF, cv::Mat Scw, vpPoints, th, vpReplacePoint) :1823-1945 (P.flagged = the point is among pKF's MapPoints).
+// featureOfPoint[m]: the feature each point was fused with (added, replaced or replacing), -1 = not fused.  Returns nFused.
+int orbslam3_fuse(const KfInput* in, const float* Scw, const KfPoints* P, float th, int bRight, int32_t* featureOfPoint) {
+    ORBmatcher matcher(0.9f, true);
+    Pinhole cam(in->cam[0], in->cam[1], in->cam[2], in->cam[3]);
+    KeyFrame K;
+    std::vector<MapPoint> occ, mps;
+    std::vector<MapPoint*> vp;
+    fillKeyFrame(K, &cam, occ, *in);
+    fillPoints(mps, vp, *P);
+    MapPoint::fuseLog().clear();
+    int nFused;
+    std::vector<MapPoint*> vpReplace(P->m, nullptr);
+    if (Scw) {
+        for (int i = 0; i < P->m; ++i) if (P->flagged && P->flagged[i]) K.mspExtra.insert(&mps[i]);
+        nFused = matcher.Fuse(&K, mat44(Scw), vp, th, vpReplace);
+    } else {
+        KeyFrame elsewhere;                  // "already in this keyframe": an observation at a feature outside the arrays
+        for (int i = 0; i < P->m; ++i) if (P->flagged && P->flagged[i]) mps[i].mObservations[&K] = std::tuple<int, int>(-1, -1);
+        nFused = matcher.Fuse(&K, vp, th, bRight != 0);
+    }
+    for (int i = 0; i < P->m; ++i) featureOfPoint[i] = -1;
+    for (const auto& e : MapPoint::fuseLog())
+        if (e.first >= mps.data() && e.first < mps.data() + mps.size() && e.second >= 0) featureOfPoint[e.first - mps.data()] = e.second;
+    for (int i = 0; i < P->m; ++i)           // Fuse(Scw): a point that met an occupied feature is only reported through vpReplacePoint
+        if (vpReplace[i] && featureOfPoint[i] < 0) {
+            auto it = vpReplace[i]->mObservations.find(&K);
+            if (it != vpReplace[i]->mObservations.end()) featureOfPoint[i] = std::get<0>(it->second);
+        }
+    return nFused;
+}
+}

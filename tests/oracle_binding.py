@@ -596,3 +596,65 @@ def ref_search_by_projection_lastframe(Cur, last, Tcw, th, fb, cam, Trl, check_o
                                                   _p(sf), len(sf), float(Cur.mbf), 0.11, _p(cam), _p(Tcw), _p(Tlw), opt(trl), m,
                                                   *[_p(a) for a in arrs], float(th), 0, _p(out))
     return n, out[:Cur.n]
+
+
+class _KfInput(C.Structure):
+    _fields_ = [("kps", _P), ("desc", _P), ("n", _I), ("nleft", _I), ("blocked", _P), ("uRight", _P), ("minX", _F), ("minY", _F),
+                ("maxX", _F), ("maxY", _F), ("scaleFactors", _P), ("invLevelSigma2", _P), ("nlevels", _I), ("cam", _F * 4), ("mbf", _F),
+                ("logScaleFactor", _F), ("Tcw", _P)]
+
+
+class _KfPoints(C.Structure):
+    _fields_ = [("m", _I), ("null", _P), ("bad", _P), ("flagged", _P), ("worldPos", _P), ("normal", _P), ("minDist", _P),
+                ("maxDist", _P), ("desc", _P)]
+
+
+def _kf_structs(KF, pts, cam, Tcw, log_sf, flagged_key):
+    keep = []                                           # arrays must outlive the call
+
+    def arr(a, dt):
+        if a is None:
+            return None
+        a = np.ascontiguousarray(np.asarray(a).astype(dt) if dt == np.uint8 else a, dt)
+        keep.append(a)
+        return C.cast(_p(a), _P)
+    k = _KfInput()
+    k.kps, k.desc, k.n, k.nleft = arr(KF.kps, KF.kps.dtype), arr(KF.desc, np.uint8), KF.n, KF.nleft
+    k.blocked, k.uRight = arr(KF.blocked, np.uint8), arr(KF.u_right, np.float32)
+    k.minX, k.minY, k.maxX, k.maxY = float(KF.min_x), float(KF.min_y), float(KF.max_x), float(KF.max_y)
+    k.scaleFactors, k.invLevelSigma2 = arr(KF.scale_factors, np.float32), arr(getattr(KF, "inv_level_sigma2", None), np.float32)
+    k.nlevels = len(KF.scale_factors)
+    k.cam = (_F * 4)(*[float(c) for c in cam[:4]])
+    k.mbf, k.logScaleFactor = float(KF.mbf), float(log_sf)
+    T = np.eye(4, dtype=np.float32)
+    T[:np.asarray(Tcw).shape[0]] = np.asarray(Tcw, np.float32)
+    k.Tcw = arr(T, np.float32)
+    p = _KfPoints()
+    p.m = len(pts["desc"])
+    p.null, p.bad = arr(pts.get("null"), np.uint8), arr(pts.get("bad"), np.uint8)
+    p.flagged = arr(pts.get(flagged_key), np.uint8)
+    p.worldPos, p.normal = arr(pts["world_pos"], np.float32), arr(pts["normal"], np.float32)
+    p.minDist, p.maxDist, p.desc = arr(pts["min_dist"], np.float32), arr(pts["max_dist"], np.float32), arr(pts["desc"], np.uint8)
+    return k, p, keep
+
+
+def ref_search_by_projection_sim3(KF, pts, Scw, th, ratio, cam, log_sf):
+    """ORBmatcher::SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming) of the reference itself."""
+    L = ref_matcher()
+    L.orbslam3_search_by_projection_sim3.argtypes = [_P, _P, _P, _I, _F, _P]
+    k, p, keep = _kf_structs(KF, pts, cam, np.eye(4), log_sf, "already_found")
+    S = np.ascontiguousarray(Scw, np.float32)
+    out = np.zeros(max(KF.n, 1), np.int32)
+    n = L.orbslam3_search_by_projection_sim3(C.byref(k), _p(S), C.byref(p), int(th), float(ratio), _p(out))
+    return n, out[:KF.n]
+
+
+def ref_fuse(KF, pts, Tcw, Scw, th, right, cam, log_sf):
+    """ORBmatcher::Fuse of the reference itself: (pKF, vpMapPoints, th, bRight) when Scw is None, else (pKF, Scw, vpPoints, th, ...)."""
+    L = ref_matcher()
+    L.orbslam3_fuse.argtypes = [_P, _P, _P, _F, _I, _P]
+    k, p, keep = _kf_structs(KF, pts, cam, np.eye(4) if Tcw is None else Tcw, log_sf, "in_keyframe" if Scw is None else "already_found")
+    S = None if Scw is None else np.ascontiguousarray(Scw, np.float32)
+    out = np.zeros(max(len(pts["desc"]), 1), np.int32)
+    n = L.orbslam3_fuse(C.byref(k), None if S is None else _p(S), C.byref(p), float(th), int(right), _p(out))
+    return n, out[:len(pts["desc"])]

@@ -92,3 +92,21 @@ def test_search_by_projection_last_frame(name):
     ores, on, _, _ = run_lf(c, ob.search_by_projection)
     assert n == on == int(g["n"])
     assert np.array_equal(res, np.where(ores >= 0, ores, -1)) and np.array_equal(res, np.where(g["lastframe_feature_of_feature"] >= 0, g["lastframe_feature_of_feature"], -1))
+
+
+@pytest.mark.parametrize("name", list(pc.KF_CASES))
+def test_keyframe_side_searches(name):
+    """SearchByProjection(KeyFrame*, Scw, ...) :473, Fuse :1629 (incl. bRight) and Fuse(Scw) :1823 of the reference itself: the
+    Sim3 decomposition, projection, distance / viewing-angle gates, PredictScale and the chi-square gate are its own lines."""
+    from test_proj_oracle import run_kf
+    c = pc.kf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    ores, on, _, _ = run_kf(c, ob.search_by_projection)
+    if c["kind"] == "sim3":
+        n, res = ob.ref_search_by_projection_sim3(c["KF"], c["pts"], c["Scw"], c["th"], c["ratio"], pc.CAM, pc.LOG_SF)
+        assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["point_of_feature"])
+    else:
+        sim3 = c["kind"] == "fuse_sim3"
+        n, res = ob.ref_fuse(c["KF"], c["pts"], None if sim3 else c["Tcw"], c["Scw"] if sim3 else None, c["th"], c["kind"] == "fuse_right",
+                             pc.CAM, pc.LOG_SF)
+        assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["feature_of_point"])
