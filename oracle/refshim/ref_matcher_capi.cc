@@ -382,3 +382,75 @@ int orbslam3_fuse(const KfInput* in, const float* Scw, const KfPoints* P, float 
     return nFused;
 }
 }
+
+extern "C" {
+// SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) :1947-2171.  P1 / P2: the keyframes' own MapPoints (null[i] = no MapPoint
+// at feature i; flagged = vpMatches12[i] already holds a point (P1) / that point is observed by pKF2 at this feature (P2)).
+// matches12[n1]: feature of pKF2 whose MapPoint the call wrote into vpMatches12[i], -1 elsewhere.  Returns nFound.
+int orbslam3_search_by_sim3(const KfInput* in1, const KfInput* in2, const KfPoints* P1, const KfPoints* P2, float s12, const float* R12,
+                            const float* t12, float th, int32_t* matches12) {
+    ORBmatcher matcher(0.9f, true);
+    Pinhole cam(in1->cam[0], in1->cam[1], in1->cam[2], in1->cam[3]);
+    KeyFrame K1, K2;
+    std::vector<MapPoint> occ1, occ2, mps1, mps2;
+    std::vector<MapPoint*> vp1, vp2;
+    fillKeyFrame(K1, &cam, occ1, *in1);
+    fillKeyFrame(K2, &cam, occ2, *in2);
+    fillPoints(mps1, vp1, *P1);
+    fillPoints(mps2, vp2, *P2);
+    K1.mvpMapPoints = vp1;
+    K2.mvpMapPoints = vp2;
+    std::vector<int> marked;
+    for (int i = 0; i < in2->n; ++i) if (P2->flagged && P2->flagged[i]) marked.push_back(i);
+    std::vector<MapPoint> holders(in1->n);
+    std::vector<MapPoint*> vpMatches12(in1->n, nullptr);
+    size_t k = 0;
+    for (int i = 0; i < in1->n; ++i)
+        if (P1->flagged && P1->flagged[i]) {
+            if (k < marked.size()) holders[i].mObservations[&K2] = std::tuple<int, int>(marked[k], -1);
+            ++k;
+            vpMatches12[i] = &holders[i];
+        }
+    cv::Mat R(3, 3, CV_32F);
+    memcpy(R.data, R12, 36);
+    const int nFound = matcher.SearchBySim3(&K1, &K2, vpMatches12, s12, R, vec3(t12), th);
+    for (int i = 0; i < in1->n; ++i) {
+        MapPoint* p = vpMatches12[i];
+        matches12[i] = (p && p >= mps2.data() && p < mps2.data() + mps2.size()) ? (int32_t)(p - mps2.data()) : -1;
+    }
+    return nFound;
+}
+}
+
+extern "C" {
+// SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const set<MapPoint*>& sAlreadyFound, th, ORBdist) :2391-2510 (relocalisation).
+// cur: the frame (blocked = mvpMapPoints[i] != NULL); P: pKF's MapPoints by feature (null, bad, flagged = in sAlreadyFound);
+// kfAngle[m]: pKF->mvKeysUn[i].angle.  pointOfFeature[n]: keyframe feature whose MapPoint landed in mvpMapPoints[i], -1 elsewhere.
+int orbslam3_search_by_projection_reloc(int checkOri, const KfInput* cur, const KfPoints* P, const float* kfAngle, float th, int ORBdist,
+                                        int32_t* pointOfFeature) {
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    Pinhole cam(cur->cam[0], cur->cam[1], cur->cam[2], cur->cam[3]), rig(1.f, 1.f, 0.f, 0.f);
+    MapPoint old;
+    Frame F;
+    fillFrame(F, &cam, &rig, &old, cur->kps, cur->desc, cur->n, cur->nleft, cur->blocked, cur->uRight, cur->minX, cur->minY, cur->maxX,
+              cur->maxY, cur->scaleFactors, cur->nlevels);
+    F.mTcw = mat44(cur->Tcw);
+    F.mfLogScaleFactor = cur->logScaleFactor;
+    KeyFrame K;
+    std::vector<MapPoint> mps;
+    std::vector<MapPoint*> vp;
+    fillPoints(mps, vp, *P);
+    K.N = P->m;
+    K.mvpMapPoints = vp;
+    K.mvKeysUn.resize(P->m);
+    for (int i = 0; i < P->m; ++i) K.mvKeysUn[i].angle = kfAngle[i];
+    std::set<MapPoint*> found;
+    for (int i = 0; i < P->m; ++i) if (P->flagged && P->flagged[i]) found.insert(&mps[i]);
+    const int nm = matcher.SearchByProjection(F, &K, found, th, ORBdist);
+    for (int i = 0; i < cur->n; ++i) {
+        MapPoint* p = F.mvpMapPoints[i];
+        pointOfFeature[i] = (p && p != &old) ? (int32_t)(p - mps.data()) : -1;
+    }
+    return nm;
+}
+}

@@ -658,3 +658,41 @@ def ref_fuse(KF, pts, Tcw, Scw, th, right, cam, log_sf):
     out = np.zeros(max(len(pts["desc"]), 1), np.int32)
     n = L.orbslam3_fuse(C.byref(k), None if S is None else _p(S), C.byref(p), float(th), int(right), _p(out))
     return n, out[:len(pts["desc"])]
+
+
+def ref_search_by_sim3(c, cam, log_sf):
+    """ORBmatcher::SearchBySim3 of the reference itself on a tests/proj_cases.sim3_inputs scenario.
+    Returns (nFound, vpMatches12 as keyframe-2 feature indices)."""
+    L = ref_matcher()
+    L.orbslam3_search_by_sim3.argtypes = [_P, _P, _P, _P, _F, _P, _P, _F, _P]
+    keep = []
+
+    def side(KF, mps, T):
+        pts = dict(mps)
+        pts["null"] = ~np.asarray(mps["has_mp"], bool)
+        k, p, kp = _kf_structs(KF, pts, cam, T, log_sf, "already_matched")
+        keep.append(kp)
+        return k, p
+    k1, p1 = side(c["KF1"], c["mps1"], c["T1w"])
+    k2, p2 = side(c["KF2"], c["mps2"], c["T2w"])
+    R12, t12 = np.ascontiguousarray(c["R12"], np.float32), np.ascontiguousarray(c["t12"], np.float32).reshape(3)
+    out = np.zeros(max(c["KF1"].n, 1), np.int32)
+    n = L.orbslam3_search_by_sim3(C.byref(k1), C.byref(k2), C.byref(p1), C.byref(p2), float(c["s12"]), _p(R12), _p(t12), float(c["th"]),
+                                  _p(out))
+    return n, out[:c["KF1"].n]
+
+
+def ref_search_by_projection_reloc(Cur, kf, Tcw, th, orb_dist, cam, log_sf, check_ori=True):
+    """ORBmatcher::SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) of the reference itself; `kf` as for
+    projection.queries_from_keyframe.  Returns (nmatches, keyframe feature per frame feature)."""
+    L = ref_matcher()
+    L.orbslam3_search_by_projection_reloc.argtypes = [_I, _P, _P, _P, _F, _I, _P]
+    pts = dict(kf)
+    m = len(kf["has_mp"])
+    pts["null"] = ~np.asarray(kf["has_mp"], bool)
+    pts["normal"] = np.zeros((m, 3), np.float32)
+    k, p, keep = _kf_structs(Cur, pts, cam, Tcw, log_sf, "already_found")
+    ang = np.ascontiguousarray(kf["angle"], np.float32)
+    out = np.zeros(max(Cur.n, 1), np.int32)
+    n = L.orbslam3_search_by_projection_reloc(int(check_ori), C.byref(k), C.byref(p), _p(ang), float(th), int(orb_dist), _p(out))
+    return n, out[:Cur.n]

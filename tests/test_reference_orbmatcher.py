@@ -110,3 +110,35 @@ def test_keyframe_side_searches(name):
         n, res = ob.ref_fuse(c["KF"], c["pts"], None if sim3 else c["Tcw"], c["Scw"] if sim3 else None, c["th"], c["kind"] == "fuse_right",
                              pc.CAM, pc.LOG_SF)
         assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["feature_of_point"])
+
+
+@pytest.mark.parametrize("name", list(pc.SIM3_CASES))
+def test_search_by_sim3(name):
+    from test_proj_oracle import run_sim3
+    c = pc.sim3_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    n, m12 = ob.ref_search_by_sim3(c, pc.CAM, pc.LOG_SF)
+    vn1, vn2, pairs, on = run_sim3(c, ob.search_by_projection)
+    want = np.full(c["KF1"].n, -1, np.int32)
+    for i1, i2 in pairs:
+        want[i1] = i2
+    assert n == on == int(g["n"]) and np.array_equal(m12, want) and n > 100
+
+
+def test_search_by_projection_relocalisation():
+    """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) :2391 of the reference itself vs the engine on the
+    windows of projection.queries_from_keyframe (same scenario as tests/test_proj_gpu.py::test_relocalisation_overload)."""
+    from orbfe import projection as pj
+    from test_proj_oracle import owners
+    c = pc.lf_inputs("proj_last_mono")
+    rng = np.random.default_rng(77)
+    last, m = c["last"], len(c["last"]["has_mp"])
+    dist = np.sqrt((last["world_pos"].astype(np.float64) ** 2).sum(1)).astype(np.float32)
+    kf = dict(has_mp=last["has_mp"], bad=rng.random(m) < 0.03, already_found=rng.random(m) < 0.2, world_pos=last["world_pos"],
+              min_dist=(dist * rng.uniform(0.3, 1.05, m)).astype(np.float32), max_dist=(dist * rng.uniform(0.95, 4.0, m)).astype(np.float32),
+              angle=last["angle"], desc=last["desc"])
+    q, owner = pj.queries_from_keyframe(c["Cur"], kf, c["Tcw"], 10.0, c["project"], np.float32(np.log(1.2)))
+    for orbdist in (100, 64):
+        n, res = ob.ref_search_by_projection_reloc(c["Cur"], kf, c["Tcw"], 10.0, orbdist, pc.CAM, np.float32(np.log(1.2)))
+        assign, choice, on = ob.search_by_projection(c["Cur"], q, 0, orbdist, 0.9, False, True)
+        assert n == on and n > 60 and np.array_equal(res, np.where(assign >= 0, owners(assign, owner), -1))
