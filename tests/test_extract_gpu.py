@@ -173,3 +173,25 @@ def test_colour_input_equals_cvtcolor_then_extract(fmt):
     ex.set_input_format("gray")
     mono2, k2, d2 = ex(want_grey, None, (0, 0))
     assert k2.tobytes() == k0.tobytes()
+
+
+def _random_configs():
+    from test_reference_orbextractor import random_configs
+    return random_configs(20261106, 8)
+
+
+@pytest.mark.parametrize("cfg", _random_configs(), ids=lambda c: f"{c[0]}x{c[1]}_n{c[2]}_s{c[3]}_l{c[4]}_t{c[5]}-{c[6]}")
+def test_cuda_equals_reference_source_random_configs(cfg):
+    """Random image sizes, level counts, scale factors, budgets and thresholds: CUDA vs the reference's own ORBextractor.cc."""
+    import oracle_binding as ob
+    if not ob.ref_available():
+        pytest.skip("oracle/_ref not built")
+    w, h, nf, sf, nl, ini, mn = cfg
+    ex = orbfe.ORBextractor(nf, sf, nl, ini, mn, max_width=w, max_height=h)
+    ref = ob.OrbSlam3Extractor(nf, sf, nl, ini, mn)
+    img = orbfe.synth.frame(8000 + w + h, w, h)
+    lap = (w // 3, 2 * w // 3)
+    ok, tot = check_frame(ex, ref, img, lap, stages=False)
+    for l in range(nl):
+        assert np.array_equal(ex.image_pyramid(l, 0)[0], ref.level_bordered(l)), f"pyramid level {l}"
+    assert ok >= 0.9999 * tot and tot > 0.5 * nf, (ok, tot)

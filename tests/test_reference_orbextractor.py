@@ -86,3 +86,30 @@ def test_timing_build_agrees_in_count():
     ref = ob.OrbSlam3Extractor(1000, *ORB)
     want = sum(len(ref(f, (0, 1000))[1]) for f in frames)
     assert abs(total - want) <= 0.005 * want
+
+
+def random_configs(seed, count):
+    rng = np.random.default_rng(seed)
+    out = []
+    for _ in range(count):
+        nl = int(rng.integers(3, 9))
+        sf = float(rng.choice([1.15, 1.2, 1.25, 1.3, 1.41]))
+        lo = int(np.ceil(120 * sf ** (nl - 1)))                      # the smallest level must still hold a FAST cell row
+        w, h = int(rng.integers(max(lo, 200), max(lo, 200) + 700)), int(rng.integers(max(lo, 160), max(lo, 160) + 500))
+        if w < h:                 # portrait frames narrower than ~1:2 make DistributeOctTree's nIni = round(width / height) zero
+            w, h = h, w           # (a division by zero in the reference, ORBextractor.cc:541-543; orbfe_create refuses them)
+        nf = int(rng.integers(200, 2500))
+        ini = int(rng.integers(10, 41))
+        out.append((w, h, nf, sf, nl, ini, int(rng.integers(3, ini))))
+    return out
+
+
+@pytest.mark.parametrize("cfg", random_configs(20261105, 12), ids=lambda c: f"{c[0]}x{c[1]}_n{c[2]}_s{c[3]}_l{c[4]}_t{c[5]}-{c[6]}")
+def test_oracle_equals_reference_source_random_configs(cfg):
+    """Odd image sizes, level counts, scale factors, feature budgets and FAST thresholds drawn at random."""
+    w, h, nf, sf, nl, ini, mn = cfg
+    ref, orc = ob.OrbSlam3Extractor(nf, sf, nl, ini, mn), ob.OrbRef(nf, sf, nl, ini, mn)
+    for seed in (7000 + w, 7001 + h):
+        img = orbfe.synth.frame(seed, w, h)
+        lap = (0, 0) if seed & 1 else (w // 4, 3 * w // 4)
+        same_result(ref(img, lap), orc(img, lap))
