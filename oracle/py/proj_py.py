@@ -386,7 +386,9 @@ class MapPointKF(MapPoint):
 
     def PredictScale(self, currentDist, pKF):                    # MapPoint.cc:534-549
         ratio = F32(self.mfMaxDistance / F32(currentDist))
-        nScale = int(math.ceil(math.log(float(ratio)) / float(pKF.mfLogScaleFactor)))
+        # float log / float division (std::log(float) under `using namespace std`); the correctly rounded float log agrees
+        # with glibc's logf wherever the ceiling is concerned (tests/test_reference_mappoint.py)
+        nScale = int(math.ceil(float(F32(F32(math.log(float(ratio))) / F32(pKF.mfLogScaleFactor)))))
         return 0 if nScale < 0 else min(nScale, pKF.mnScaleLevels - 1)
 
     def IsInKeyFrame(self, pKF):

@@ -232,6 +232,8 @@ typedef Point3_<float> Point3f;
 template <class T, int M, int N> struct Matx {
     T val[M * N];
     Matx() { for (int i = 0; i < M * N; ++i) val[i] = T(0); }
+    Matx(T a, T b, T c) { static_assert(M * N == 3, "three-element Matx"); val[0] = a; val[1] = b; val[2] = c; }
+    static Matx zeros() { return Matx(); }
     T& operator()(int i, int j) { return val[i * N + j]; }
     const T& operator()(int i, int j) const { return val[i * N + j]; }
     T& operator()(int i) { return val[i]; }

@@ -143,11 +143,29 @@ def queries_from_lastframe(Cur, last, Tcw, th, fwd_bwd, project=None, project_ri
     return (np.array(q, PROJ_QUERY_DTYPE) if q else np.zeros(0, PROJ_QUERY_DTYPE)), np.array(owner, np.int32)
 
 
+_libm_logf = None
+
+
+def logf(x):
+    """log() of a float argument as the reference's translation units see it: `using namespace std` puts std::log(float) in
+    scope, so `log(ratio)` and `log(mfScaleFactor)` (src/Frame.cc:109) are the C library's logf, not the double log."""
+    global _libm_logf
+    if _libm_logf is None:
+        import ctypes.util
+        f = C.CDLL(ctypes.util.find_library("m") or "libm.so.6").logf
+        f.restype, f.argtypes = C.c_float, [C.c_float]
+        _libm_logf = f
+    return F32(_libm_logf(float(F32(x))))
+
+
 def predict_scale(max_distance, current_dist, log_scale_factor, n_levels):
-    """MapPoint::PredictScale (src/MapPoint.cc:551-566): log() of a float ratio in double, ceil, clamp."""
+    """MapPoint::PredictScale (src/MapPoint.cc:534-566): `ceil(log(ratio) / mfLogScaleFactor)` is evaluated entirely in
+    float (logf, float division, ceilf) - checked against the reference's own object code in tests/test_reference_mappoint.py."""
     import math
     ratio = F32(F32(max_distance) / F32(current_dist))
-    n = int(math.ceil(math.log(float(ratio)) / float(F32(log_scale_factor))))
+    if not (ratio > 0 and np.isfinite(ratio)):          # log(0) = -inf, x / 0 = inf, nan: the int conversion gives INT_MIN on x86 -> level 0
+        return 0
+    n = int(math.ceil(float(F32(logf(ratio) / F32(log_scale_factor)))))
     return 0 if n < 0 else min(n, n_levels - 1)
 
 

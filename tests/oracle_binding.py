@@ -696,3 +696,41 @@ def ref_search_by_projection_reloc(Cur, kf, Tcw, th, orb_dist, cam, log_sf, chec
     out = np.zeros(max(Cur.n, 1), np.int32)
     n = L.orbslam3_search_by_projection_reloc(int(check_ori), C.byref(k), C.byref(p), _p(ang), float(th), int(orb_dist), _p(out))
     return n, out[:Cur.n]
+
+
+# ---- the reference's own src/MapPoint.cc (oracle/_ref/liborbslam3_mappoint.so, see oracle/Makefile) ----
+REF_MAPPOINT_LIB = os.path.join(os.path.dirname(REF_LIB), "liborbslam3_mappoint.so")
+_ref_mappoint = None
+
+
+def ref_mappoint_available():
+    return os.path.exists(REF_MAPPOINT_LIB) and ref_matcher_available()
+
+
+def ref_mappoint():
+    global _ref_mappoint
+    if _ref_mappoint is None:
+        L = C.CDLL(REF_MAPPOINT_LIB)
+        L.orbslam3_distinctive_descriptors.argtypes = [_P, _P, _I, _I, _P]
+        L.orbslam3_mappoint_nobs.argtypes = [_I, _I]
+        L.orbslam3_mappoint_predict_scale.argtypes = [_P, _P, _I, _F, _I, _I, _P]
+        _ref_mappoint = L
+    return _ref_mappoint
+
+
+def ref_distinctive_descriptors(desc, offsets, stereo=False):
+    """MapPoint::ComputeDistinctiveDescriptors (src/MapPoint.cc:349-423), the reference's own object code."""
+    desc = np.ascontiguousarray(desc, np.uint8)
+    offsets = np.ascontiguousarray(offsets, np.int32)
+    best = np.full(len(offsets) - 1, -2, np.int32)
+    ref_mappoint().orbslam3_distinctive_descriptors(_p(desc), _p(offsets), len(offsets) - 1, int(stereo), _p(best))
+    return best
+
+
+def ref_predict_scale(max_distance, current_dist, log_scale_factor, n_levels, via_frame=False):
+    """MapPoint::PredictScale (src/MapPoint.cc:534-566), the reference's own object code."""
+    md = np.ascontiguousarray(max_distance, np.float32)
+    cd = np.ascontiguousarray(current_dist, np.float32)
+    out = np.empty(len(md), np.int32)
+    ref_mappoint().orbslam3_mappoint_predict_scale(_p(md), _p(cd), len(md), float(log_scale_factor), int(n_levels), int(via_frame), _p(out))
+    return out

@@ -78,3 +78,14 @@ def test_keyframe_side_vs_reference_source(name):
         rn, rres = ob.ref_fuse(c["KF"], c["pts"], None if sim3 else c["Tcw"], c["Scw"] if sim3 else None, c["th"], c["kind"] == "fuse_right",
                                pc.CAM, pc.LOG_SF)
     assert n == rn and np.array_equal(res, rres)
+
+
+@pytest.mark.skipif(not ob.ref_mappoint_available(), reason="oracle/_ref/liborbslam3_mappoint.so not built")
+@pytest.mark.parametrize("seed,npoints", [(5200, 400), (5203, 4000)])
+def test_distinctive_descriptors_vs_reference_source(seed, npoints):
+    """k_distinctive == MapPoint::ComputeDistinctiveDescriptors of the reference's own MapPoint.cc (mono keyframes and
+    fisheye keyframes that contribute a left and a right row)."""
+    d, off = mc.distinctive_inputs(seed, npoints)
+    best = orbfe.ORBmatcher().ComputeDistinctiveDescriptors(d, off)
+    assert np.array_equal(best, ob.ref_distinctive_descriptors(d, off, False))
+    assert np.array_equal(best, ob.ref_distinctive_descriptors(d, off, True))
