@@ -1,0 +1,149 @@
+// TEST INFRASTRUCTURE (oracle/_ref): C entry points over the reference's own src/Frame.cc, src/MapPoint.cc,
+// src/CameraModels/{Pinhole,KannalaBrandt8}.cpp and src/ORBextractor.cc, all compiled unmodified against
+// refshim/frame_standin.h + refshim/opencv2.  ORBmatcher::DescriptorDistance / TH_HIGH / TH_LOW come from
+// liborbslam3_orbmatcher.so (the reference's own ORBmatcher.cc).  Nothing here is linked into the product.
+#define private public        // Frame::UndistortKeyPoints / AssignFeaturesToGrid / ComputeImageBounds are private members
+#include "Frame.h"
+#undef private
+#include "KannalaBrandt8.h"
+#include "MapPoint.h"
+#include "ORBextractor.h"
+#include "Pinhole.h"
+
+#include <cstdint>
+#include <cstring>
+
+#include "../cpu_ref/match_ref.h"
+
+using namespace ORB_SLAM3;
+
+// cv::undistortPoints of the stand-in forwards here: oracle/cpu_ref's restatement, bit-identical to cv2.undistortPoints 4.13
+namespace cv {
+void orbref_undistort_points_hook(const float* xy, int n, const float K4[4], const float* dist, int ndist, const float P4[4], float* out) {
+    assert(!std::memcmp(K4, P4, 4 * sizeof(float)));      // Frame.cc:749 passes the same intrinsics as camera matrix and as P
+    std::vector<orbref::KeyPoint> in(n), o(n);
+    for (int i = 0; i < n; ++i) { in[i].x = xy[2 * i]; in[i].y = xy[2 * i + 1]; }
+    orbref::undistortKeyPoints(in.data(), n, K4, dist, ndist, o.data());
+    for (int i = 0; i < n; ++i) { out[2 * i] = o[i].x; out[2 * i + 1] = o[i].y; }
+}
+}  // namespace cv
+
+namespace {
+
+std::vector<cv::KeyPoint> keypoints(const void* kps, int n) {
+    std::vector<cv::KeyPoint> v(n);
+    if (n) std::memcpy(v.data(), kps, (size_t)n * sizeof(cv::KeyPoint));
+    return v;
+}
+cv::Mat descriptors(const uint8_t* d, int n) { return n ? cv::Mat(n, 32, CV_8U, const_cast<uint8_t*>(d), 32).clone() : cv::Mat(0, 32, CV_8U); }
+
+// The tables a Frame copies from its extractor (Frame.cc:107-113)
+void scaleTables(Frame& F, ORBextractor& ex) {
+    F.mnScaleLevels = ex.GetLevels();
+    F.mfScaleFactor = ex.GetScaleFactor();
+    F.mfLogScaleFactor = log(F.mfScaleFactor);
+    F.mvScaleFactors = ex.GetScaleFactors();
+    F.mvInvScaleFactors = ex.GetInverseScaleFactors();
+    F.mvLevelSigma2 = ex.GetScaleSigmaSquares();
+    F.mvInvLevelSigma2 = ex.GetInverseScaleSigmaSquares();
+}
+
+// bordered level buffers (19 px each side, as ORBextractor::ComputePyramid leaves them) -> mvImagePyramid ROI views
+void setPyramid(ORBextractor& ex, const uint8_t* const* levels, const int32_t* w, const int32_t* h) {
+    for (int l = 0; l < ex.GetLevels(); ++l) {
+        const size_t stride = (size_t)w[l] + 38;
+        ex.mvImagePyramid[l] = cv::Mat(h[l], w[l], CV_8U, const_cast<uint8_t*>(levels[l]) + 19 * stride + 19, stride);
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+// Frame::ComputeStereoMatches (Frame.cc:794-964) on a Frame holding the two key point sets and extractors whose mvImagePyramid
+// are the given levels.  u_right / depth: mvuRight / mvDepth (N floats).
+void orbslam3_frame_stereo_matches(int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th,
+                                   const uint8_t* const* levelsL, const uint8_t* const* levelsR, const int32_t* w, const int32_t* h,
+                                   const void* kpL, const uint8_t* descL, int nL, const void* kpR, const uint8_t* descR, int nR,
+                                   float bf, float b, float* u_right, float* depth) {
+    ORBextractor exL(nfeatures, scale_factor, nlevels, ini_th, min_th), exR(nfeatures, scale_factor, nlevels, ini_th, min_th);
+    setPyramid(exL, levelsL, w, h);
+    setPyramid(exR, levelsR, w, h);
+    Frame F;
+    F.mpORBextractorLeft = &exL;
+    F.mpORBextractorRight = &exR;
+    scaleTables(F, exL);
+    F.mvKeys = keypoints(kpL, nL);
+    F.mvKeysRight = keypoints(kpR, nR);
+    F.mDescriptors = descriptors(descL, nL);
+    F.mDescriptorsRight = descriptors(descR, nR);
+    F.N = nL;
+    F.mbf = bf;
+    F.mb = b;
+    F.ComputeStereoMatches();
+    for (int i = 0; i < nL; ++i) { u_right[i] = F.mvuRight[i]; depth[i] = F.mvDepth[i]; }
+}
+
+// Frame::ComputeStereoFishEyeMatches (Frame.cc:1116-1156) with the reference's own KannalaBrandt8::TriangulateMatches
+// (KannalaBrandt8.cpp:338-407).  cam1 / cam2: fx fy cx cy k1 k2 k3 k4.  R12 / t12 = mRlr / mtlr.  Returns the match count.
+int orbslam3_frame_fisheye_matches(const float* cam1, const float* cam2, const void* kpL, const uint8_t* descL, int nL, int mono_left,
+                                   const void* kpR, const uint8_t* descR, int nR, int mono_right, const float* R12, const float* t12,
+                                   const float* sigma2, int nlevels, int32_t* l2r, int32_t* r2l, float* depth, float* p3d) {
+    KannalaBrandt8 c1(std::vector<float>(cam1, cam1 + 8)), c2(std::vector<float>(cam2, cam2 + 8));
+    Frame F;
+    F.mpCamera = &c1;
+    F.mpCamera2 = &c2;
+    F.mvKeys = keypoints(kpL, nL);
+    F.mvKeysRight = keypoints(kpR, nR);
+    F.mDescriptors = descriptors(descL, nL);
+    F.mDescriptorsRight = descriptors(descR, nR);
+    F.Nleft = nL;
+    F.Nright = nR;
+    F.monoLeft = mono_left;
+    F.monoRight = mono_right;
+    F.mvLevelSigma2.assign(sigma2, sigma2 + nlevels);
+    F.mRlr = cv::Mat(3, 3, CV_32F, const_cast<float*>(R12), 12).clone();
+    F.mtlr = cv::Mat(3, 1, CV_32F, const_cast<float*>(t12), 4).clone();
+    F.ComputeStereoFishEyeMatches();
+    int n = 0;
+    for (int i = 0; i < nL; ++i) {
+        l2r[i] = F.mvLeftToRightMatch[i];
+        depth[i] = F.mvDepth[i];
+        const cv::Mat& p = F.mvStereo3Dpoints[i];
+        for (int k = 0; k < 3; ++k) p3d[3 * i + k] = p.empty() ? 0.f : p.at<float>(k);
+        n += l2r[i] >= 0;
+    }
+    for (int i = 0; i < nR; ++i) r2l[i] = F.mvRightToLeftMatch[i];
+    return n;
+}
+
+// Frame::UndistortKeyPoints (Frame.cc:730-763) with a Pinhole camera: mvKeys -> mvKeysUn.
+void orbslam3_frame_undistort_keypoints(const void* kps, int n, const float* K4, const float* dist, int ndist, void* out) {
+    Pinhole cam(std::vector<float>(K4, K4 + 4));
+    Frame F;
+    F.mpCamera = &cam;
+    F.mK = cam.toK();
+    F.mDistCoef = cv::Mat(ndist, 1, CV_32F, const_cast<float*>(dist), 4).clone();
+    F.mvKeys = keypoints(kps, n);
+    F.N = n;
+    F.UndistortKeyPoints();
+    if (n) std::memcpy(out, F.mvKeysUn.data(), (size_t)n * sizeof(cv::KeyPoint));
+}
+
+// KannalaBrandt8::project / unproject (KannalaBrandt8.cpp:24-41, 96-123) on n points.
+void orbslam3_kb8_project(const float* cam, const float* p3d, int n, float* uv) {
+    KannalaBrandt8 c(std::vector<float>(cam, cam + 8));
+    for (int i = 0; i < n; ++i) {
+        const cv::Point2f q = c.project(cv::Point3f(p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2]));
+        uv[2 * i] = q.x; uv[2 * i + 1] = q.y;
+    }
+}
+void orbslam3_kb8_unproject(const float* cam, const float* uv, int n, float* ray) {
+    KannalaBrandt8 c(std::vector<float>(cam, cam + 8));
+    for (int i = 0; i < n; ++i) {
+        const cv::Point3f r = c.unproject(cv::Point2f(uv[2 * i], uv[2 * i + 1]));
+        ray[3 * i] = r.x; ray[3 * i + 1] = r.y; ray[3 * i + 2] = r.z;
+    }
+}
+
+}  // extern "C"

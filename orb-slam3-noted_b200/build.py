@@ -67,7 +67,7 @@ if __name__ == "__main__":
 
 
 REFERENCE_SRC = "/root/reference/src/ORBextractor.cc"
-REF_LIBS = [os.path.join(ROOT, "oracle", "_ref", n) for n in ("liborbslam3_orbextractor.so", "liborbslam3_orbextractor_mt.so", "libdbow2_orbvoc.so", "liborbslam3_orbmatcher.so", "liborbslam3_mappoint.so")]
+REF_LIBS = [os.path.join(ROOT, "oracle", "_ref", n) for n in ("liborbslam3_orbextractor.so", "liborbslam3_orbextractor_mt.so", "libdbow2_orbvoc.so", "liborbslam3_orbmatcher.so", "liborbslam3_mappoint.so", "liborbslam3_frame.so")]
 
 
 def build_reference(force=False):

@@ -734,3 +734,83 @@ def ref_predict_scale(max_distance, current_dist, log_scale_factor, n_levels, vi
     out = np.empty(len(md), np.int32)
     ref_mappoint().orbslam3_mappoint_predict_scale(_p(md), _p(cd), len(md), float(log_scale_factor), int(n_levels), int(via_frame), _p(out))
     return out
+
+
+# ---- the reference's own src/Frame.cc + camera models (oracle/_ref/liborbslam3_frame.so, see oracle/Makefile) ----
+REF_FRAME_LIB = os.path.join(os.path.dirname(REF_LIB), "liborbslam3_frame.so")
+_ref_frame = None
+
+
+def ref_frame_available():
+    return os.path.exists(REF_FRAME_LIB) and ref_matcher_available()
+
+
+def ref_frame():
+    global _ref_frame
+    if _ref_frame is None:
+        L = C.CDLL(REF_FRAME_LIB)
+        L.orbslam3_frame_stereo_matches.argtypes = [_I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _F, _F, _P, _P]
+        L.orbslam3_frame_fisheye_matches.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _I, _P, _P, _P, _P]
+        L.orbslam3_frame_undistort_keypoints.argtypes = [_P, _I, _P, _P, _I, _P]
+        L.orbslam3_kb8_project.argtypes = [_P, _P, _I, _P]
+        L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
+        _ref_frame = L
+    return _ref_frame
+
+
+def ref_stereo_matches(params, levelsL, levelsR, kpL, descL, kpR, descR, bf, b):
+    """Frame::ComputeStereoMatches (src/Frame.cc:794-964), the reference's own object code.  levelsL / levelsR: the
+    bordered pyramid levels ((h + 38) x (w + 38) uint8 arrays) of the two extractors."""
+    nf, sf, nl, ini, mn = params
+    levelsL = [np.ascontiguousarray(a, np.uint8) for a in levelsL]
+    levelsR = [np.ascontiguousarray(a, np.uint8) for a in levelsR]
+    w = np.array([a.shape[1] - 38 for a in levelsL], np.int32)
+    h = np.array([a.shape[0] - 38 for a in levelsL], np.int32)
+    pL = (C.c_void_p * nl)(*[a.ctypes.data for a in levelsL])
+    pR = (C.c_void_p * nl)(*[a.ctypes.data for a in levelsR])
+    kpL, kpR = np.ascontiguousarray(kpL), np.ascontiguousarray(kpR)
+    descL, descR = np.ascontiguousarray(descL, np.uint8), np.ascontiguousarray(descR, np.uint8)
+    u, d = np.zeros(max(len(kpL), 1), np.float32), np.zeros(max(len(kpL), 1), np.float32)
+    ref_frame().orbslam3_frame_stereo_matches(nf, sf, nl, ini, mn, pL, pR, _p(w), _p(h), _p(kpL), _p(descL), len(kpL), _p(kpR), _p(descR),
+                                              len(kpR), bf, b, _p(u), _p(d))
+    return u[:len(kpL)], d[:len(kpL)]
+
+
+def ref_fisheye_stereo(cam1, cam2, kpL, descL, mono_left, kpR, descR, mono_right, R12, t12, sigma2):
+    """Frame::ComputeStereoFishEyeMatches (src/Frame.cc:1116-1156) + KannalaBrandt8::TriangulateMatches, the reference's own
+    object code (its cv::SVD is the stand-in's double-precision Jacobi).  Returns (l2r, r2l, depth, p3d, n)."""
+    cam1, cam2 = np.ascontiguousarray(cam1, np.float32), np.ascontiguousarray(cam2, np.float32)
+    kpL, kpR = np.ascontiguousarray(kpL), np.ascontiguousarray(kpR)
+    descL, descR = np.ascontiguousarray(descL, np.uint8), np.ascontiguousarray(descR, np.uint8)
+    R12, t12 = np.ascontiguousarray(R12, np.float32).reshape(9), np.ascontiguousarray(t12, np.float32).reshape(3)
+    sigma2 = np.ascontiguousarray(sigma2, np.float32)
+    nL, nR = len(kpL), len(kpR)
+    l2r, r2l = np.zeros(max(nL, 1), np.int32), np.zeros(max(nR, 1), np.int32)
+    depth, p3d = np.zeros(max(nL, 1), np.float32), np.zeros((max(nL, 1), 3), np.float32)
+    n = ref_frame().orbslam3_frame_fisheye_matches(_p(cam1), _p(cam2), _p(kpL), _p(descL), nL, mono_left, _p(kpR), _p(descR), nR,
+                                                   mono_right, _p(R12), _p(t12), _p(sigma2), len(sigma2), _p(l2r), _p(r2l), _p(depth), _p(p3d))
+    return l2r[:nL], r2l[:nR], depth[:nL], p3d[:nL], n
+
+
+def ref_undistort_keypoints(kps, K4, dist):
+    """Frame::UndistortKeyPoints (src/Frame.cc:730-763), the reference's own object code (cv::undistortPoints = the restatement
+    that tests/test_oracle_vs_cv2.py holds to cv2)."""
+    kps = np.ascontiguousarray(kps)
+    K4, dist = np.ascontiguousarray(K4, np.float32), np.ascontiguousarray(dist, np.float32)
+    out = np.zeros_like(kps)
+    ref_frame().orbslam3_frame_undistort_keypoints(_p(kps), len(kps), _p(K4), _p(dist), len(dist), _p(out))
+    return out
+
+
+def ref_kb8_project(cam, p3d):
+    cam, p3d = np.ascontiguousarray(cam, np.float32), np.ascontiguousarray(p3d, np.float32)
+    uv = np.zeros((len(p3d), 2), np.float32)
+    ref_frame().orbslam3_kb8_project(_p(cam), _p(p3d), len(p3d), _p(uv))
+    return uv
+
+
+def ref_kb8_unproject(cam, uv):
+    cam, uv = np.ascontiguousarray(cam, np.float32), np.ascontiguousarray(uv, np.float32)
+    ray = np.zeros((len(uv), 3), np.float32)
+    ref_frame().orbslam3_kb8_unproject(_p(cam), _p(uv), len(uv), _p(ray))
+    return ray

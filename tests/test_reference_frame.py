@@ -1,0 +1,110 @@
+"""The reference's own src/Frame.cc, src/CameraModels/KannalaBrandt8.cpp and Pinhole.cpp (compiled unmodified into
+oracle/_ref/liborbslam3_frame.so, recipe in oracle/Makefile) against the C++ oracle and the golden fixtures:
+Frame::ComputeStereoMatches (Frame.cc:794-964), Frame::ComputeStereoFishEyeMatches (:1116-1156) with
+KannalaBrandt8::TriangulateMatches, Frame::UndistortKeyPoints (:730-763)."""
+import os
+
+import numpy as np
+import pytest
+
+import match_cases as mc
+import oracle_binding as ob
+from common import GOLDEN
+from test_match_oracle import extract, tables
+
+pytestmark = pytest.mark.skipif(not ob.ref_frame_available(), reason="oracle/_ref/liborbslam3_frame.so not built")
+
+
+def gold(name):
+    return np.load(os.path.join(GOLDEN, f"match_{name}.npz"))
+
+
+def levels(ref, n=8):
+    return [ref.level(l) for l in range(n)]
+
+
+@pytest.mark.parametrize("name", list(mc.STEREO_CASES))
+def test_stereo_matches_oracle_equals_reference_source(name):
+    c = mc.stereo_inputs(name, extract)
+    (_, kL, dL, rL), (_, kR, dR, rR) = c["L"], c["R"]
+    u, d = ob.ref_stereo_matches((c["nf"],) + mc.ORB, levels(rL), levels(rR), kL, dL, kR, dR, c["bf"], c["b"])
+    uo, do, _ = ob.stereo_match(rL, rR, kL, dL, kR, dR, c["bf"], c["b"])
+    g = gold(name)
+    assert np.array_equal(u, uo) and np.array_equal(d, do)                      # float32-exact
+    assert np.array_equal(u, g["u_right"]) and np.array_equal(d, g["depth"])
+    assert (d > 0).sum() > 0.4 * len(kL)
+
+
+@pytest.mark.parametrize("name", list(mc.FISHEYE_CASES))
+def test_fisheye_stereo_oracle_vs_reference_source(name):
+    """The reference's own knnMatch / Lowe / TriangulateMatches control flow.  Its cv::SVD is a stand-in (double Jacobi), the
+    oracle's is its own double Jacobi, the golden's is the real cv2.SVDecomp: decisions compared away from the thresholds."""
+    c = mc.fisheye_inputs(name)
+    s2 = tables()[2]
+    args = (c["cam1"], c["cam2"], c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], c["mono_r"], c["R12"], c["t12"], s2)
+    l2r, r2l, depth, p3d, n = ob.ref_fisheye_stereo(*args)
+    ol2r, or2l, odepth, op3d, mg, on = ob.fisheye_stereo(*args)
+    g = gold(name)
+    safe = np.minimum(mg, g["margins"]) > 1e-3
+    assert safe.sum() > 0.95 * (g["margins"] < 1e29).sum()
+    assert np.array_equal(l2r[safe], ol2r[safe]) and np.array_equal(l2r[safe], g["l2r"][safe])
+    ok = safe & (l2r >= 0)
+    assert ok.sum() > 200
+    assert np.allclose(depth[ok], odepth[ok], rtol=2e-3, atol=1e-5) and np.allclose(depth[ok], g["depth"][ok], rtol=2e-3, atol=1e-5)
+    assert np.allclose(p3d[ok], op3d[ok], rtol=2e-3, atol=2e-4)
+    assert abs(n - on) <= (~safe & (g["margins"] < 1e29)).sum()
+    # unmatched rows keep the reference's defaults
+    assert (depth[l2r < 0] == -1).all()
+    m = l2r[l2r >= 0]
+    assert (r2l[m] >= 0).all()
+
+
+def und_points(n=3000, seed=77):
+    import orbfe
+    rng = np.random.default_rng(seed)
+    k = np.zeros(n, orbfe.KEYPOINT_DTYPE)
+    k["x"], k["y"] = rng.uniform(0, 752, n).astype(np.float32), rng.uniform(0, 480, n).astype(np.float32)
+    k["octave"], k["angle"], k["size"], k["class_id"] = rng.integers(0, 8, n), rng.uniform(0, 360, n), 31, -1
+    return k
+
+
+UND_K = np.array([458.654, 457.296, 367.215, 248.375], np.float32)
+UND_CASES = [np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], np.float32),
+             np.array([-0.3, 0.1, 0.001, -0.0005, -0.02], np.float32),
+             np.array([0.0, 0.07, 0.0, 0.0], np.float32)]
+
+
+@pytest.mark.parametrize("ci", range(len(UND_CASES)))
+def test_undistort_keypoints_oracle_equals_reference_source(ci):
+    """Frame::UndistortKeyPoints' own lines (the k1 == 0 early exit, the N x 2 matrix, reshape, the copy back that keeps
+    octave / angle / size) on top of the undistortPoints restatement that is held to cv2."""
+    k = und_points()
+    out = ob.ref_undistort_keypoints(k, UND_K, UND_CASES[ci])
+    assert out.tobytes() == ob.undistort_keypoints(k, UND_K, UND_CASES[ci]).tobytes()
+    if UND_CASES[ci][0] == 0:
+        assert out.tobytes() == k.tobytes()             # Frame.cc:732-736
+    else:
+        assert np.abs(out["x"] - k["x"]).max() > 1.0
+
+
+def test_kb8_project_unproject_oracle_equals_reference_source():
+    """KannalaBrandt8::unproject (KannalaBrandt8.cpp:96-123, Newton iterations with the precision stop) of the reference's own
+    object code == oracle/cpu_ref/kb8_ref.cc bit for bit.  project (:24-41) ends in `fx * r * cos(psi) + cx` with a float
+    psi: whether that is cosf or the double cos depends on which <math.h> / `using namespace std` the translation unit happens
+    to see through the OpenCV headers (the stand-in build sees std::cos(float), the oracle and the GPU take the double one);
+    the two differ by at most one float ulp of the pixel coordinate, which is the tolerance here."""
+    rng = np.random.default_rng(5)
+    P = np.stack([rng.uniform(-3, 3, 4000), rng.uniform(-2, 2, 4000), rng.uniform(0.2, 10, 4000)], 1).astype(np.float32)
+    L = ob.lib()
+    for cam in (mc.KB8_LEFT, mc.KB8_RIGHT):
+        cam = np.ascontiguousarray(cam, np.float32)
+        uv = ob.ref_kb8_project(cam, P)
+        ray = ob.ref_kb8_unproject(cam, uv)
+        ouv, oray = np.zeros_like(uv), np.zeros_like(ray)
+        for i in range(len(P)):
+            L.orbref_kb8_project(ob._p(cam), ob._p(P[i]), ob._p(ouv[i]))
+            L.orbref_kb8_unproject(ob._p(cam), float(ouv[i, 0]), float(ouv[i, 1]), ob._p(oray[i]))
+        assert np.abs(uv - ouv).max() <= 6.2e-5 and (uv == ouv).mean() > 0.8       # ulp(512) = 6.1e-5
+        ray_o = ob.ref_kb8_unproject(cam, ouv)
+        assert np.array_equal(ray_o, oray)
+        assert np.allclose(ray[:, :2] * P[:, 2:3], P[:, :2], atol=2e-3)

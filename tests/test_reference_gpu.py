@@ -89,3 +89,58 @@ def test_distinctive_descriptors_vs_reference_source(seed, npoints):
     best = orbfe.ORBmatcher().ComputeDistinctiveDescriptors(d, off)
     assert np.array_equal(best, ob.ref_distinctive_descriptors(d, off, False))
     assert np.array_equal(best, ob.ref_distinctive_descriptors(d, off, True))
+
+
+frame_lib = pytest.mark.skipif(not ob.ref_frame_available(), reason="oracle/_ref/liborbslam3_frame.so not built")
+
+
+@frame_lib
+@pytest.mark.parametrize("name", list(mc.STEREO_CASES))
+def test_stereo_match_vs_reference_source(name):
+    """k_stereo_search / k_stereo_filter == Frame::ComputeStereoMatches of the reference's own Frame.cc, float32-exact, on
+    the features and pyramids the device extracted."""
+    from oracle_binding import OrbRef
+    cam, nf, seed = mc.STEREO_CASES[name]
+    w, h = cam["w"], cam["h"]
+    imL, imR = orbfe.synth.stereo_pair(seed, w, h)
+    bf = float(np.float32(cam["bf"]))
+    b = float(np.float32(np.float32(cam["bf"]) / np.float32(cam["fx"])))
+    ex = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h, max_batch=2)
+    (_, kL, dL), (_, kR, dR) = ex.extract_batch(np.stack([imL, imR]), (0, 0))
+    u, d, n = orbfe.ORBmatcher().stereo_match(ex, ex, bf, b, 0, 1)
+    levL = [ex.image_pyramid(l, 0)[0] for l in range(8)]
+    levR = [ex.image_pyramid(l, 1)[0] for l in range(8)]
+    ru, rd = ob.ref_stereo_matches((nf,) + mc.ORB, levL, levR, kL, dL, kR, dR, bf, b)
+    assert np.array_equal(u[:len(kL)], ru) and np.array_equal(d[:len(kL)], rd)
+    assert n == (rd > 0).sum() > 0.4 * len(kL)
+
+
+@frame_lib
+@pytest.mark.parametrize("name", list(mc.FISHEYE_CASES))
+def test_fisheye_stereo_vs_reference_source(name):
+    """ComputeStereoFishEyeMatches on the GPU vs the reference's own Frame.cc + KannalaBrandt8.cpp (decisions away from the
+    thresholds: both sides end in their own 4x4 null-vector solve)."""
+    c = mc.fisheye_inputs(name)
+    s2 = tables()[2]
+    l2r, r2l, depth, p3d, n = orbfe.ORBmatcher(0.7, True).ComputeStereoFishEyeMatches(
+        c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], c["mono_r"], c["cam1"], c["cam2"], c["R12"], c["t12"], s2)
+    args = (c["cam1"], c["cam2"], c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], c["mono_r"], c["R12"], c["t12"], s2)
+    rl2r, rr2l, rdepth, rp3d, rn = ob.ref_fisheye_stereo(*args)
+    mg = ob.fisheye_stereo(*args)[4]
+    safe = mg > 1e-3
+    assert np.array_equal(l2r[safe], rl2r[safe])
+    ok = safe & (rl2r >= 0)
+    assert ok.sum() > 200
+    assert np.allclose(depth[ok], rdepth[ok], rtol=2e-3, atol=1e-5) and np.allclose(p3d[ok], rp3d[ok], rtol=2e-3, atol=2e-4)
+    assert abs(n - rn) <= ((mg < 1e29) & ~safe).sum()
+    both = (l2r >= 0) & (rl2r >= 0)
+    assert np.array_equal(r2l[l2r[both]] >= 0, rr2l[rl2r[both]] >= 0)
+
+
+@frame_lib
+def test_undistort_keypoints_vs_reference_source():
+    from test_reference_frame import UND_CASES, UND_K, und_points
+    k = und_points()
+    m = orbfe.ORBmatcher()
+    for D in UND_CASES:
+        assert m.UndistortKeyPoints(k, UND_K, D).tobytes() == ob.ref_undistort_keypoints(k, UND_K, D).tobytes()
