@@ -130,9 +130,43 @@ void orbslam3_frame_undistort_keypoints(const void* kps, int n, const float* K4,
     if (n) std::memcpy(out, F.mvKeysUn.data(), (size_t)n * sizeof(cv::KeyPoint));
 }
 
+// Frame::AssignFeaturesToGrid (Frame.cc:380-411) + PosInGrid (:708-719) + GetFeaturesInArea (:640-706).  kps: mvKeysUn (nleft ==
+// -1) or mvKeys ++ mvKeysRight.  Window q = win[6q .. 6q+5] = (x, y, r, minLevel, maxLevel, bRight); the indices it returns are
+// appended to `out` (right-camera indices as the reference returns them: relative to Nleft), counts[q] = how many.
+int orbslam3_frame_features_in_area(const void* kps, int n, int nleft, float min_x, float min_y, float grid_w_inv, float grid_h_inv,
+                                    const float* win, int nwin, int32_t* out, int out_cap, int32_t* counts) {
+    Frame F;
+    Frame::mnMinX = min_x;
+    Frame::mnMinY = min_y;
+    Frame::mfGridElementWidthInv = grid_w_inv;
+    Frame::mfGridElementHeightInv = grid_h_inv;
+    const std::vector<cv::KeyPoint> all = keypoints(kps, n);
+    F.N = n;
+    F.Nleft = nleft;
+    if (nleft == -1) F.mvKeysUn = all;
+    else { F.mvKeys.assign(all.begin(), all.begin() + nleft); F.mvKeysRight.assign(all.begin() + nleft, all.end()); F.Nright = n - nleft; }
+    F.AssignFeaturesToGrid();
+    int total = 0;
+    for (int q = 0; q < nwin; ++q) {
+        const float* w = win + 6 * q;
+        const std::vector<size_t> v = F.GetFeaturesInArea(w[0], w[1], w[2], (int)w[3], (int)w[4], w[5] != 0.f);
+        counts[q] = (int)v.size();
+        for (size_t i : v) { if (total < out_cap) out[total] = (int32_t)i; ++total; }
+    }
+    return total;
+}
+
 // KannalaBrandt8::project / unproject (KannalaBrandt8.cpp:24-41, 96-123) on n points.
 void orbslam3_kb8_project(const float* cam, const float* p3d, int n, float* uv) {
     KannalaBrandt8 c(std::vector<float>(cam, cam + 8));
+    for (int i = 0; i < n; ++i) {
+        const cv::Point2f q = c.project(cv::Point3f(p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2]));
+        uv[2 * i] = q.x; uv[2 * i + 1] = q.y;
+    }
+}
+// Pinhole::project (Pinhole.cpp:34-42) / unproject (:68-71) on n points.
+void orbslam3_pinhole_project(const float* K4, const float* p3d, int n, float* uv) {
+    Pinhole c(std::vector<float>(K4, K4 + 4));
     for (int i = 0; i < n; ++i) {
         const cv::Point2f q = c.project(cv::Point3f(p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2]));
         uv[2 * i] = q.x; uv[2 * i + 1] = q.y;

@@ -752,7 +752,9 @@ def ref_frame():
         L.orbslam3_frame_stereo_matches.argtypes = [_I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _F, _F, _P, _P]
         L.orbslam3_frame_fisheye_matches.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _I, _P, _P, _P, _P]
         L.orbslam3_frame_undistort_keypoints.argtypes = [_P, _I, _P, _P, _I, _P]
+        L.orbslam3_frame_features_in_area.argtypes = [_P, _I, _I, _F, _F, _F, _F, _P, _I, _P, _I, _P]
         L.orbslam3_kb8_project.argtypes = [_P, _P, _I, _P]
+        L.orbslam3_pinhole_project.argtypes = [_P, _P, _I, _P]
         L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
         _ref_frame = L
     return _ref_frame
@@ -814,3 +816,30 @@ def ref_kb8_unproject(cam, uv):
     ray = np.zeros((len(uv), 3), np.float32)
     ref_frame().orbslam3_kb8_unproject(_p(cam), _p(uv), len(uv), _p(ray))
     return ray
+
+
+def ref_features_in_area(F, windows):
+    """Frame::AssignFeaturesToGrid + GetFeaturesInArea (src/Frame.cc:380-411, 640-719), the reference's own object code.
+    windows: (nq, 6) float32 rows (x, y, r, minLevel, maxLevel, bRight).  Returns a list of index arrays; right-camera
+    indices are global (+ nleft) like the oracle's."""
+    win = np.ascontiguousarray(windows, np.float32).reshape(-1, 6)
+    cap = max(1, len(win) * max(F.n, 1))
+    out, counts = np.zeros(cap, np.int32), np.zeros(max(len(win), 1), np.int32)
+    total = ref_frame().orbslam3_frame_features_in_area(_p(F.kps), F.n, F.nleft, float(F.min_x), float(F.min_y), float(F.grid_w_inv),
+                                                        float(F.grid_h_inv), _p(win), len(win), _p(out), cap, _p(counts))
+    assert total <= cap
+    res, o = [], 0
+    for q in range(len(win)):
+        idx = out[o:o + counts[q]].copy()
+        if win[q, 5] != 0:
+            idx += F.nleft
+        res.append(idx)
+        o += counts[q]
+    return res
+
+
+def ref_pinhole_project(K4, p3d):
+    K4, p3d = np.ascontiguousarray(K4, np.float32), np.ascontiguousarray(p3d, np.float32)
+    uv = np.zeros((len(p3d), 2), np.float32)
+    ref_frame().orbslam3_pinhole_project(_p(K4), _p(p3d), len(p3d), _p(uv))
+    return uv

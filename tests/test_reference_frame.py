@@ -108,3 +108,49 @@ def test_kb8_project_unproject_oracle_equals_reference_source():
         ray_o = ob.ref_kb8_unproject(cam, ouv)
         assert np.array_equal(ray_o, oray)
         assert np.allclose(ray[:, :2] * P[:, 2:3], P[:, :2], atol=2e-3)
+
+
+@pytest.mark.parametrize("nleft_frac", [None, 0.55], ids=["mono", "fisheye_rig"])
+def test_features_in_area_oracle_equals_reference_source(nleft_frac):
+    """Frame::AssignFeaturesToGrid / PosInGrid / GetFeaturesInArea of the reference's own Frame.cc: same indices in the same
+    (cell-major, push) order as the oracle's grid, for random windows incl. level ranges, undistorted points outside the image
+    bounds (dropped by PosInGrid) and windows hanging over the border."""
+    import orbfe
+    import proj_cases as pc
+    from orbfe import projection as pj
+    rng = np.random.default_rng(11)
+    n = 3000
+    k = np.zeros(n, orbfe.KEYPOINT_DTYPE)
+    k["x"] = rng.uniform(-30, 780, n).astype(np.float32)           # some outside (-12.5, 760) x (-8, 490)
+    k["y"] = rng.uniform(-20, 500, n).astype(np.float32)
+    k["octave"] = rng.integers(0, 8, n)
+    nleft = -1 if nleft_frac is None else int(n * nleft_frac)
+    F = pj.GridFrame(k, np.zeros((n, 32), np.uint8), (-12.5, -8.0, 760.25, 490.5), pc.SCALE, nleft=nleft)
+    nq = 1500
+    win = np.zeros((nq, 6), np.float32)
+    win[:, 0], win[:, 1] = rng.uniform(-60, 820, nq), rng.uniform(-50, 540, nq)
+    win[:, 2] = rng.choice([2.5, 4.0, 7.2, 15.0, 40.0, 100.0], nq)
+    lo = rng.integers(-1, 6, nq)
+    hi = np.where(rng.random(nq) < 0.5, -1, lo + rng.integers(0, 4, nq))
+    win[:, 3], win[:, 4] = lo, hi
+    if nleft != -1:
+        win[:, 5] = rng.random(nq) < 0.5
+    got = ob.ref_features_in_area(F, win)
+    total = 0
+    for q in range(nq):
+        want = ob.features_in_area(F, win[q, 0], win[q, 1], win[q, 2], int(win[q, 3]), int(win[q, 4]), bool(win[q, 5]))
+        assert np.array_equal(got[q], want), q
+        total += len(want)
+    assert total > 8 * nq
+
+
+def test_pinhole_project_equals_reference_source():
+    """Pinhole::project of the reference's own Pinhole.cpp == the float32 restatement the window construction uses
+    (orbfe/projection.py pinhole_project)."""
+    from orbfe import projection as pj
+    rng = np.random.default_rng(3)
+    P = np.stack([rng.uniform(-4, 4, 5000), rng.uniform(-3, 3, 5000), rng.uniform(0.1, 30, 5000)], 1).astype(np.float32)
+    K4 = np.array([458.654, 457.296, 367.215, 248.375], np.float32)
+    uv = ob.ref_pinhole_project(K4, P)
+    got = np.array([pj.pinhole_project(K4, p) for p in P], np.float32)
+    assert np.array_equal(uv, got)
