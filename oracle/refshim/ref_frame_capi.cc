@@ -17,6 +17,51 @@
 
 using namespace ORB_SLAM3;
 
+// ---- a monotonic heap for this library only (linked -Bsymbolic), as in ref_capi.cc and for the same reason: DistributeOctTree
+// orders equal-size nodes by their address (ORBextractor.cc:682) and the oracle / CUDA path define that tie as "created later
+// compares greater".  Thread-safe (Frame's stereo constructor extracts the two eyes on two threads: each thread's own nodes
+// still get increasing addresses); every C entry point below rewinds to where it started, all of its allocations being dead.
+#include <sys/mman.h>
+
+#include <atomic>
+#include <new>
+namespace {
+const size_t kArena = (size_t)48 << 30;      // virtual; pages are touched on demand
+char* arenaBase() {
+    static char* base = [] {
+        void* p = mmap(nullptr, kArena, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS | MAP_NORESERVE, -1, 0);
+        return p == MAP_FAILED ? nullptr : (char*)p;
+    }();
+    return base;
+}
+std::atomic<size_t> g_top{0};
+void* bump(size_t n) {
+    char* base = arenaBase();
+    const size_t need = ((n ? n : 1) + 15) & ~(size_t)15;
+    const size_t at = g_top.fetch_add(need);
+    if (!base || at + need > kArena) throw std::bad_alloc();
+    return base + at;
+}
+struct HeapScope {
+    size_t mark;
+    HeapScope() : mark(g_top.load()) {}
+    ~HeapScope() {
+        const size_t top = g_top.load();
+        if (top > mark) {
+            const size_t a = (mark + 4095) & ~(size_t)4095, b = (top + 4095) & ~(size_t)4095;
+            if (b > a) madvise(arenaBase() + a, b - a, MADV_DONTNEED);
+            g_top.store(mark);
+        }
+    }
+};
+}  // namespace
+void* operator new(size_t n) { return bump(n); }
+void* operator new[](size_t n) { return bump(n); }
+void operator delete(void*) noexcept {}
+void operator delete[](void*) noexcept {}
+void operator delete(void*, size_t) noexcept {}
+void operator delete[](void*, size_t) noexcept {}
+
 // cv::undistortPoints of the stand-in forwards here: oracle/cpu_ref's restatement, bit-identical to cv2.undistortPoints 4.13
 namespace cv {
 void orbref_undistort_points_hook(const float* xy, int n, const float K4[4], const float* dist, int ndist, const float P4[4], float* out) {
@@ -66,6 +111,7 @@ void orbslam3_frame_stereo_matches(int nfeatures, float scale_factor, int nlevel
                                    const uint8_t* const* levelsL, const uint8_t* const* levelsR, const int32_t* w, const int32_t* h,
                                    const void* kpL, const uint8_t* descL, int nL, const void* kpR, const uint8_t* descR, int nR,
                                    float bf, float b, float* u_right, float* depth) {
+    HeapScope heap_scope;
     ORBextractor exL(nfeatures, scale_factor, nlevels, ini_th, min_th), exR(nfeatures, scale_factor, nlevels, ini_th, min_th);
     setPyramid(exL, levelsL, w, h);
     setPyramid(exR, levelsR, w, h);
@@ -89,6 +135,7 @@ void orbslam3_frame_stereo_matches(int nfeatures, float scale_factor, int nlevel
 int orbslam3_frame_fisheye_matches(const float* cam1, const float* cam2, const void* kpL, const uint8_t* descL, int nL, int mono_left,
                                    const void* kpR, const uint8_t* descR, int nR, int mono_right, const float* R12, const float* t12,
                                    const float* sigma2, int nlevels, int32_t* l2r, int32_t* r2l, float* depth, float* p3d) {
+    HeapScope heap_scope;
     KannalaBrandt8 c1(std::vector<float>(cam1, cam1 + 8)), c2(std::vector<float>(cam2, cam2 + 8));
     Frame F;
     F.mpCamera = &c1;
@@ -119,6 +166,7 @@ int orbslam3_frame_fisheye_matches(const float* cam1, const float* cam2, const v
 
 // Frame::UndistortKeyPoints (Frame.cc:730-763) with a Pinhole camera: mvKeys -> mvKeysUn.
 void orbslam3_frame_undistort_keypoints(const void* kps, int n, const float* K4, const float* dist, int ndist, void* out) {
+    HeapScope heap_scope;
     Pinhole cam(std::vector<float>(K4, K4 + 4));
     Frame F;
     F.mpCamera = &cam;
@@ -135,6 +183,7 @@ void orbslam3_frame_undistort_keypoints(const void* kps, int n, const float* K4,
 // appended to `out` (right-camera indices as the reference returns them: relative to Nleft), counts[q] = how many.
 int orbslam3_frame_features_in_area(const void* kps, int n, int nleft, float min_x, float min_y, float grid_w_inv, float grid_h_inv,
                                     const float* win, int nwin, int32_t* out, int out_cap, int32_t* counts) {
+    HeapScope heap_scope;
     Frame F;
     Frame::mnMinX = min_x;
     Frame::mnMinY = min_y;
@@ -158,14 +207,57 @@ int orbslam3_frame_features_in_area(const void* kps, int n, int nleft, float min
 
 // KannalaBrandt8::project / unproject (KannalaBrandt8.cpp:24-41, 96-123) on n points.
 void orbslam3_kb8_project(const float* cam, const float* p3d, int n, float* uv) {
+    HeapScope heap_scope;
     KannalaBrandt8 c(std::vector<float>(cam, cam + 8));
     for (int i = 0; i < n; ++i) {
         const cv::Point2f q = c.project(cv::Point3f(p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2]));
         uv[2 * i] = q.x; uv[2 * i + 1] = q.y;
     }
 }
+// The stereo constructor Frame(imLeft, imRight, ts, extractorLeft, extractorRight, voc, K, distCoef, bf, thDepth, pCamera)
+// (Frame.cc:98-200) from two images: two extraction threads, UndistortKeyPoints, ComputeStereoMatches, image bounds, grid.
+// `mb` is read by ComputeStereoMatches (:838) before the constructor assigns it (:176) and no initialiser mentions it: its value
+// there is whatever the object's storage held.  The Frame is therefore constructed in storage where that member already
+// holds bf / fx, the value the constructor itself assigns a few lines later.
+// kps / kps_un / desc / u_right / depth: capacity cap (left eye); kps_r / desc_r: capacity cap (right eye).
+// out_n[0] = N, out_n[1] = right key points.  bounds: mnMinX, mnMinY, mnMaxX, mnMaxY.  Returns 0, or -1 if cap is too small.
+int orbslam3_frame_stereo_construct(const uint8_t* im_left, const uint8_t* im_right, int w, int h, int nfeatures, float scale_factor,
+                                    int nlevels, int ini_th, int min_th, const float* K4, const float* dist, int ndist, float bf,
+                                    float th_depth, int cap, void* kps, void* kps_un, uint8_t* desc, float* u_right, float* depth,
+                                    void* kps_r, uint8_t* desc_r, int32_t* out_n, float* bounds) {
+    HeapScope heap_scope;
+    ORBextractor exL(nfeatures, scale_factor, nlevels, ini_th, min_th), exR(nfeatures, scale_factor, nlevels, ini_th, min_th);
+    Pinhole cam(std::vector<float>(K4, K4 + 4));
+    cv::Mat K = cam.toK();
+    cv::Mat D = cv::Mat(ndist, 1, CV_32F, const_cast<float*>(dist), 4).clone();
+    cv::Mat imL(h, w, CV_8UC1, const_cast<uint8_t*>(im_left), (size_t)w), imR(h, w, CV_8UC1, const_cast<uint8_t*>(im_right), (size_t)w);
+    Frame::mbInitialComputations = true;
+    alignas(64) static unsigned char storage[sizeof(Frame)];
+    Frame* seed = new (storage) Frame();
+    seed->mb = bf / K4[0];
+    seed->~Frame();
+    Frame* F = new (storage) Frame(imL, imR, 0.0, &exL, &exR, nullptr, K, D, bf, th_depth, &cam);
+    int rc = 0;
+    const int n = F->N, nr = (int)F->mvKeysRight.size();
+    out_n[0] = n; out_n[1] = nr;
+    if (n > cap || nr > cap) rc = -1;
+    else {
+        if (n) {
+            std::memcpy(kps, F->mvKeys.data(), (size_t)n * sizeof(cv::KeyPoint));
+            std::memcpy(kps_un, F->mvKeysUn.data(), (size_t)n * sizeof(cv::KeyPoint));
+            for (int i = 0; i < n; ++i) { std::memcpy(desc + 32 * (size_t)i, F->mDescriptors.ptr(i), 32); u_right[i] = F->mvuRight[i]; depth[i] = F->mvDepth[i]; }
+        }
+        if (nr) std::memcpy(kps_r, F->mvKeysRight.data(), (size_t)nr * sizeof(cv::KeyPoint));
+        for (int i = 0; i < nr; ++i) std::memcpy(desc_r + 32 * (size_t)i, F->mDescriptorsRight.ptr(i), 32);
+        bounds[0] = Frame::mnMinX; bounds[1] = Frame::mnMinY; bounds[2] = Frame::mnMaxX; bounds[3] = Frame::mnMaxY;
+    }
+    F->~Frame();
+    return rc;
+}
+
 // Pinhole::project (Pinhole.cpp:34-42) / unproject (:68-71) on n points.
 void orbslam3_pinhole_project(const float* K4, const float* p3d, int n, float* uv) {
+    HeapScope heap_scope;
     Pinhole c(std::vector<float>(K4, K4 + 4));
     for (int i = 0; i < n; ++i) {
         const cv::Point2f q = c.project(cv::Point3f(p3d[3 * i], p3d[3 * i + 1], p3d[3 * i + 2]));
@@ -173,6 +265,7 @@ void orbslam3_pinhole_project(const float* K4, const float* p3d, int n, float* u
     }
 }
 void orbslam3_kb8_unproject(const float* cam, const float* uv, int n, float* ray) {
+    HeapScope heap_scope;
     KannalaBrandt8 c(std::vector<float>(cam, cam + 8));
     for (int i = 0; i < n; ++i) {
         const cv::Point3f r = c.unproject(cv::Point2f(uv[2 * i], uv[2 * i + 1]));

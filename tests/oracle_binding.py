@@ -755,6 +755,7 @@ def ref_frame():
         L.orbslam3_frame_features_in_area.argtypes = [_P, _I, _I, _F, _F, _F, _F, _P, _I, _P, _I, _P]
         L.orbslam3_kb8_project.argtypes = [_P, _P, _I, _P]
         L.orbslam3_pinhole_project.argtypes = [_P, _P, _I, _P]
+        L.orbslam3_frame_stereo_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, _F, _F, _I] + [_P] * 9
         L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
         _ref_frame = L
     return _ref_frame
@@ -843,3 +844,23 @@ def ref_pinhole_project(K4, p3d):
     uv = np.zeros((len(p3d), 2), np.float32)
     ref_frame().orbslam3_pinhole_project(_p(K4), _p(p3d), len(p3d), _p(uv))
     return uv
+
+
+def ref_stereo_frame(im_left, im_right, params, K4, dist, bf, th_depth=40.0):
+    """The reference's stereo Frame constructor (src/Frame.cc:98-200) on two images, its own object code end to end: two
+    extraction threads, UndistortKeyPoints, ComputeStereoMatches, ComputeImageBounds.  Returns a dict."""
+    import orbfe
+    nf, sf, nl, ini, mn = params
+    imL, imR = np.ascontiguousarray(im_left, np.uint8), np.ascontiguousarray(im_right, np.uint8)
+    h, w = imL.shape
+    K4, dist = np.ascontiguousarray(K4, np.float32), np.ascontiguousarray(dist, np.float32)
+    cap = nf + 64
+    kps, kun, kr = (np.zeros(cap, orbfe.KEYPOINT_DTYPE) for _ in range(3))
+    desc, descr = np.zeros((cap, 32), np.uint8), np.zeros((cap, 32), np.uint8)
+    u, d = np.zeros(cap, np.float32), np.zeros(cap, np.float32)
+    n, bounds = np.zeros(2, np.int32), np.zeros(4, np.float32)
+    rc = ref_frame().orbslam3_frame_stereo_construct(_p(imL), _p(imR), w, h, nf, sf, nl, ini, mn, _p(K4), _p(dist), len(dist), bf, th_depth,
+                                                     cap, _p(kps), _p(kun), _p(desc), _p(u), _p(d), _p(kr), _p(descr), _p(n), _p(bounds))
+    assert rc == 0, (rc, n)
+    N, NR = int(n[0]), int(n[1])
+    return dict(kps=kps[:N], kps_un=kun[:N], desc=desc[:N], u_right=u[:N], depth=d[:N], kps_r=kr[:NR], desc_r=descr[:NR], bounds=bounds)

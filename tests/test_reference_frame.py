@@ -154,3 +154,26 @@ def test_pinhole_project_equals_reference_source():
     uv = ob.ref_pinhole_project(K4, P)
     got = np.array([pj.pinhole_project(K4, p) for p in P], np.float32)
     assert np.array_equal(uv, got)
+
+
+@pytest.mark.parametrize("name", list(mc.STEREO_CASES))
+def test_stereo_frame_constructor_end_to_end(name):
+    """Two images -> the reference's own stereo Frame constructor (its ORBextractor on two threads, UndistortKeyPoints,
+    ComputeStereoMatches) == the oracle's extraction + stereo matching + undistortion: key points, descriptors, mvuRight,
+    mvDepth, mvKeysUn and the image bounds byte for byte."""
+    c = mc.stereo_inputs(name, extract)
+    (_, kL, dL, rL), (_, kR, dR, rR) = c["L"], c["R"]
+    cam = c["cam"]
+    K4 = np.array([cam["fx"], cam.get("fy", cam["fx"]), cam.get("cx", cam["w"] / 2), cam.get("cy", cam["h"] / 2)], np.float32)
+    for D in (np.zeros(4, np.float32), np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], np.float32)):
+        F = ob.ref_stereo_frame(c["imL"], c["imR"], (c["nf"],) + mc.ORB, K4, D, c["bf"])
+        assert F["kps"].tobytes() == kL.tobytes() and np.array_equal(F["desc"], dL)
+        assert F["kps_r"].tobytes() == kR.tobytes() and np.array_equal(F["desc_r"], dR)
+        b = float(np.float32(np.float32(c["bf"]) / K4[0]))
+        u, d, _ = ob.stereo_match(rL, rR, kL, dL, kR, dR, c["bf"], b)
+        assert np.array_equal(F["u_right"], u) and np.array_equal(F["depth"], d)
+        assert F["kps_un"].tobytes() == ob.undistort_keypoints(kL, K4, D).tobytes()
+        if D[0] == 0:
+            assert F["bounds"].tolist() == [0.0, 0.0, float(cam["w"]), float(cam["h"])]      # Frame.cc:765-792
+        else:
+            assert F["bounds"][0] < 0 and F["bounds"][2] > cam["w"]

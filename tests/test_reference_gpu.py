@@ -144,3 +144,29 @@ def test_undistort_keypoints_vs_reference_source():
     m = orbfe.ORBmatcher()
     for D in UND_CASES:
         assert m.UndistortKeyPoints(k, UND_K, D).tobytes() == ob.ref_undistort_keypoints(k, UND_K, D).tobytes()
+
+
+@frame_lib
+@pytest.mark.parametrize("name", list(mc.STEREO_CASES))
+def test_stereo_frame_end_to_end_vs_reference_constructor(name):
+    """Two images -> the product (batched extraction of both eyes, stereo matcher, undistortion) vs the reference's own stereo
+    Frame constructor (Frame.cc:98-200: its ORBextractor on two threads, UndistortKeyPoints, ComputeStereoMatches) run from the
+    same two images: mvKeys, mvKeysRight, descriptors, mvuRight, mvDepth, mvKeysUn byte for byte."""
+    cam, nf, seed = mc.STEREO_CASES[name]
+    w, h = cam["w"], cam["h"]
+    imL, imR = orbfe.synth.stereo_pair(seed, w, h)
+    bf = float(np.float32(cam["bf"]))
+    K4 = np.array([cam["fx"], cam.get("fy", cam["fx"]), cam.get("cx", w / 2), cam.get("cy", h / 2)], np.float32)
+    D = np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], np.float32)
+    b = float(np.float32(np.float32(bf) / K4[0]))
+    ex = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h, max_batch=2)
+    (_, kL, dL), (_, kR, dR) = ex.extract_batch(np.stack([imL, imR]), (0, 0))
+    m = orbfe.ORBmatcher()
+    u, d, n = m.stereo_match(ex, ex, bf, b, 0, 1)
+    kun = m.UndistortKeyPoints(kL, K4, D)
+    F = ob.ref_stereo_frame(imL, imR, (nf,) + mc.ORB, K4, D, bf)
+    assert F["kps"].tobytes() == kL.tobytes() and F["kps_r"].tobytes() == kR.tobytes()
+    assert np.array_equal(F["desc"], dL) and np.array_equal(F["desc_r"], dR)
+    assert np.array_equal(F["u_right"], u[:len(kL)]) and np.array_equal(F["depth"], d[:len(kL)])
+    assert F["kps_un"].tobytes() == kun.tobytes()
+    assert n == (F["depth"] > 0).sum()
