@@ -255,6 +255,43 @@ int orbslam3_frame_stereo_construct(const uint8_t* im_left, const uint8_t* im_ri
     return rc;
 }
 
+// The stereo-fisheye constructor Frame(imLeft, imRight, ts, extractorLeft, extractorRight, voc, K, distCoef, bf, thDepth, pCamera,
+// pCamera2, Tlr) (Frame.cc:1017-1114): extraction of both eyes with their lapping areas on two threads, ComputeStereoFishEyeMatches,
+// descriptors stacked, grid, UndistortKeyPoints (zero distortion: a copy).  kps: mvKeys ++ mvKeysRight, desc: the stacked matrix
+// (capacity cap rows each); out_n = Nleft, Nright, monoLeft, monoRight; l2r / depth / p3d: Nleft entries, r2l: Nright.
+int orbslam3_frame_fisheye_construct(const uint8_t* im_left, const uint8_t* im_right, int w, int h, int nfeatures, float scale_factor,
+                                     int nlevels, int ini_th, int min_th, const float* cam1, const float* cam2, const int32_t* lap_left,
+                                     const int32_t* lap_right, const float* Tlr34, float bf, float th_depth, int cap, void* kps, uint8_t* desc,
+                                     int32_t* out_n, int32_t* l2r, int32_t* r2l, float* depth, float* p3d) {
+    HeapScope heap_scope;
+    ORBextractor exL(nfeatures, scale_factor, nlevels, ini_th, min_th), exR(nfeatures, scale_factor, nlevels, ini_th, min_th);
+    KannalaBrandt8 c1(std::vector<float>(cam1, cam1 + 8)), c2(std::vector<float>(cam2, cam2 + 8));
+    c1.mvLappingArea[0] = lap_left[0]; c1.mvLappingArea[1] = lap_left[1];
+    c2.mvLappingArea[0] = lap_right[0]; c2.mvLappingArea[1] = lap_right[1];
+    cv::Mat K = c1.toK();
+    cv::Mat D = cv::Mat::zeros(4, 1, CV_32F);                    // Tracking.cc: fisheye rigs carry zero mDistCoef
+    cv::Mat Tlr = cv::Mat(3, 4, CV_32F, const_cast<float*>(Tlr34), 16).clone();
+    cv::Mat imL(h, w, CV_8UC1, const_cast<uint8_t*>(im_left), (size_t)w), imR(h, w, CV_8UC1, const_cast<uint8_t*>(im_right), (size_t)w);
+    Frame::mbInitialComputations = true;
+    Frame F(imL, imR, 0.0, &exL, &exR, nullptr, K, D, bf, th_depth, &c1, &c2, Tlr);
+    const int nl = F.Nleft, nr = F.Nright;
+    out_n[0] = nl; out_n[1] = nr; out_n[2] = F.monoLeft; out_n[3] = F.monoRight;
+    if (nl + nr > cap) return -1;
+    if (nl) std::memcpy(kps, F.mvKeys.data(), (size_t)nl * sizeof(cv::KeyPoint));
+    if (nr) std::memcpy((char*)kps + (size_t)nl * sizeof(cv::KeyPoint), F.mvKeysRight.data(), (size_t)nr * sizeof(cv::KeyPoint));
+    for (int i = 0; i < F.mDescriptors.rows; ++i) std::memcpy(desc + 32 * (size_t)i, F.mDescriptors.ptr(i), 32);
+    for (int i = 0; i < nl; ++i) {
+        l2r[i] = F.mvLeftToRightMatch[i];
+        depth[i] = F.mvDepth[i];
+        const cv::Mat& p = F.mvStereo3Dpoints[i];
+        for (int k = 0; k < 3; ++k) p3d[3 * i + k] = p.empty() ? 0.f : p.at<float>(k);
+    }
+    for (int i = 0; i < nr; ++i) r2l[i] = F.mvRightToLeftMatch[i];
+    // the undistorted copy and the stacked descriptor matrix must be what the constructor promises
+    if ((int)F.mvKeysUn.size() != nl || F.mDescriptors.rows != nl + nr) return -2;
+    return 0;
+}
+
 // Pinhole::project (Pinhole.cpp:34-42) / unproject (:68-71) on n points.
 void orbslam3_pinhole_project(const float* K4, const float* p3d, int n, float* uv) {
     HeapScope heap_scope;

@@ -755,6 +755,7 @@ def ref_frame():
         L.orbslam3_frame_features_in_area.argtypes = [_P, _I, _I, _F, _F, _F, _F, _P, _I, _P, _I, _P]
         L.orbslam3_kb8_project.argtypes = [_P, _P, _I, _P]
         L.orbslam3_pinhole_project.argtypes = [_P, _P, _I, _P]
+        L.orbslam3_frame_fisheye_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _F, _F, _I] + [_P] * 7
         L.orbslam3_frame_stereo_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, _F, _F, _I] + [_P] * 9
         L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
         _ref_frame = L
@@ -864,3 +865,25 @@ def ref_stereo_frame(im_left, im_right, params, K4, dist, bf, th_depth=40.0):
     assert rc == 0, (rc, n)
     N, NR = int(n[0]), int(n[1])
     return dict(kps=kps[:N], kps_un=kun[:N], desc=desc[:N], u_right=u[:N], depth=d[:N], kps_r=kr[:NR], desc_r=descr[:NR], bounds=bounds)
+
+
+def ref_fisheye_frame(im_left, im_right, params, cam1, cam2, lap_left, lap_right, Tlr, bf=0.0, th_depth=40.0):
+    """The reference's stereo-fisheye Frame constructor (src/Frame.cc:1017-1114) on two images, its own object code."""
+    import orbfe
+    nf, sf, nl, ini, mn = params
+    imL, imR = np.ascontiguousarray(im_left, np.uint8), np.ascontiguousarray(im_right, np.uint8)
+    h, w = imL.shape
+    cam1, cam2 = np.ascontiguousarray(cam1, np.float32), np.ascontiguousarray(cam2, np.float32)
+    lapL, lapR = np.ascontiguousarray(lap_left, np.int32), np.ascontiguousarray(lap_right, np.int32)
+    Tlr = np.ascontiguousarray(Tlr, np.float32).reshape(3, 4)
+    cap = 2 * (nf + 64)
+    kps, desc = np.zeros(cap, orbfe.KEYPOINT_DTYPE), np.zeros((cap, 32), np.uint8)
+    n = np.zeros(4, np.int32)
+    l2r, r2l = np.zeros(cap, np.int32), np.zeros(cap, np.int32)
+    depth, p3d = np.zeros(cap, np.float32), np.zeros((cap, 3), np.float32)
+    rc = ref_frame().orbslam3_frame_fisheye_construct(_p(imL), _p(imR), w, h, nf, sf, nl, ini, mn, _p(cam1), _p(cam2), _p(lapL), _p(lapR),
+                                                      _p(Tlr), bf, th_depth, cap, _p(kps), _p(desc), _p(n), _p(l2r), _p(r2l), _p(depth), _p(p3d))
+    assert rc == 0, (rc, n)
+    NL, NR = int(n[0]), int(n[1])
+    return dict(kps=kps[:NL + NR], desc=desc[:NL + NR], nleft=NL, nright=NR, mono_left=int(n[2]), mono_right=int(n[3]),
+                l2r=l2r[:NL], r2l=r2l[:NR], depth=depth[:NL], p3d=p3d[:NL])

@@ -177,3 +177,34 @@ def test_stereo_frame_constructor_end_to_end(name):
             assert F["bounds"].tolist() == [0.0, 0.0, float(cam["w"]), float(cam["h"])]      # Frame.cc:765-792
         else:
             assert F["bounds"][0] < 0 and F["bounds"][2] > cam["w"]
+
+
+def fisheye_frame_case():
+    w, h, nf, seed, lapL, lapR = mc.LAP_CASES["lap_tumvi"]
+    import orbfe
+    imL, imR = orbfe.synth.stereo_pair(seed, w, h)
+    return imL, imR, nf, lapL, lapR
+
+
+def test_fisheye_frame_constructor_end_to_end():
+    """Two images -> the reference's own stereo-fisheye Frame constructor (extraction with the lapping areas on two threads,
+    ComputeStereoFishEyeMatches, stacked descriptors) vs the oracle pipeline: key points (mono part first, lapping part last),
+    monoLeft / monoRight and the stacked descriptors byte for byte; matches where no threshold is within 1e-3."""
+    imL, imR, nf, lapL, lapR = fisheye_frame_case()
+    F = ob.ref_fisheye_frame(imL, imR, (nf,) + mc.ORB, mc.KB8_LEFT, mc.KB8_RIGHT, lapL, lapR, mc.TLR)
+    monoL, kL, dL, _ = extract(imL, nf, lapL)
+    monoR, kR, dR, _ = extract(imR, nf, lapR)
+    assert (F["nleft"], F["nright"], F["mono_left"], F["mono_right"]) == (len(kL), len(kR), monoL, monoR)
+    assert F["kps"][:len(kL)].tobytes() == kL.tobytes() and F["kps"][len(kL):].tobytes() == kR.tobytes()
+    assert np.array_equal(F["desc"], np.concatenate([dL, dR]))
+    assert 0 < monoL < len(kL) and 0 < monoR < len(kR)
+    s2 = tables()[2]
+    l2r, r2l, depth, p3d, mg, n = ob.fisheye_stereo(mc.KB8_LEFT, mc.KB8_RIGHT, kL, dL, monoL, kR, dR, monoR, mc.TLR[:, :3], mc.TLR[:, 3], s2)
+    tried = mg < 1e29
+    assert tried.sum() > 100                       # Lowe-ratio survivors that reached the triangulation
+    safe = mg > 1e-3
+    assert np.array_equal(F["l2r"][safe], l2r[safe])
+    assert (F["l2r"][~tried] == -1).all()
+    ok = safe & (l2r >= 0)
+    if ok.any():
+        assert np.allclose(F["depth"][ok], depth[ok], rtol=2e-3, atol=1e-5) and np.allclose(F["p3d"][ok], p3d[ok], rtol=2e-3, atol=2e-4)

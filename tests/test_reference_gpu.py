@@ -170,3 +170,29 @@ def test_stereo_frame_end_to_end_vs_reference_constructor(name):
     assert np.array_equal(F["u_right"], u[:len(kL)]) and np.array_equal(F["depth"], d[:len(kL)])
     assert F["kps_un"].tobytes() == kun.tobytes()
     assert n == (F["depth"] > 0).sum()
+
+
+@frame_lib
+def test_fisheye_frame_end_to_end_vs_reference_constructor():
+    """Two images -> the product (extraction of each eye with its lapping area, fisheye stereo matcher) vs the reference's own
+    stereo-fisheye Frame constructor (Frame.cc:1017-1114) run from the same images."""
+    from test_reference_frame import fisheye_frame_case
+    imL, imR, nf, lapL, lapR = fisheye_frame_case()
+    h, w = imL.shape
+    F = ob.ref_fisheye_frame(imL, imR, (nf,) + mc.ORB, mc.KB8_LEFT, mc.KB8_RIGHT, lapL, lapR, mc.TLR)
+    ex = orbfe.ORBextractor(nf, *mc.ORB, max_width=w, max_height=h)
+    monoL, kL, dL = ex(imL, None, lapL)
+    monoR, kR, dR = ex(imR, None, lapR)
+    assert (F["nleft"], F["nright"], F["mono_left"], F["mono_right"]) == (len(kL), len(kR), monoL, monoR)
+    assert F["kps"][:len(kL)].tobytes() == kL.tobytes() and F["kps"][len(kL):].tobytes() == kR.tobytes()
+    assert np.array_equal(F["desc"], np.concatenate([dL, dR]))
+    s2 = tables()[2]
+    l2r, r2l, depth, p3d, n = orbfe.ORBmatcher(0.7, True).ComputeStereoFishEyeMatches(kL, dL, monoL, kR, dR, monoR, mc.KB8_LEFT, mc.KB8_RIGHT,
+                                                                                      mc.TLR[:, :3], mc.TLR[:, 3], s2)
+    mg = ob.fisheye_stereo(mc.KB8_LEFT, mc.KB8_RIGHT, kL, dL, monoL, kR, dR, monoR, mc.TLR[:, :3], mc.TLR[:, 3], s2)[4]
+    safe = mg > 1e-3
+    assert (mg < 1e29).sum() > 100
+    assert np.array_equal(l2r[safe], F["l2r"][safe])
+    ok = safe & (F["l2r"] >= 0)
+    if ok.any():
+        assert np.allclose(depth[ok], F["depth"][ok], rtol=2e-3, atol=1e-5) and np.allclose(p3d[ok], F["p3d"][ok], rtol=2e-3, atol=2e-4)
