@@ -8,6 +8,7 @@
 #include "KannalaBrandt8.h"
 #include "MapPoint.h"
 #include "ORBextractor.h"
+#include "ORBVocabulary.h"
 #include "Pinhole.h"
 
 #include <cstdint>
@@ -289,6 +290,48 @@ int orbslam3_frame_fisheye_construct(const uint8_t* im_left, const uint8_t* im_r
     for (int i = 0; i < nr; ++i) r2l[i] = F.mvRightToLeftMatch[i];
     // the undistorted copy and the stacked descriptor matrix must be what the constructor promises
     if ((int)F.mvKeysUn.size() != nl || F.mDescriptors.rows != nl + nr) return -2;
+    return 0;
+}
+
+// The monocular constructor Frame(imGray, ts, extractor, voc, pCamera, distCoef, bf, thDepth) (Frame.cc:284-378): ExtractORB with the
+// lapping range (0, 1000), UndistortKeyPoints, bounds, grid; then Frame::ComputeBoW (:721-728) when voc_path names an ORBvoc text
+// file (DBoW2's own loadFromTextFile + transform(features, mBowVec, mFeatVec, 4)).
+// out_n: N, mono index, BowVector size, FeatureVector size.  words / values: capacity cap; nodes / offsets (+1) / indices: cap.
+int orbslam3_frame_mono_construct(const uint8_t* im, int w, int h, int nfeatures, float scale_factor, int nlevels, int ini_th, int min_th,
+                                  const float* K4, const float* dist, int ndist, const char* voc_path, int cap, void* kps, void* kps_un,
+                                  uint8_t* desc, int32_t* out_n, uint32_t* words, double* values, uint32_t* nodes, int32_t* offsets,
+                                  int32_t* indices) {
+    HeapScope heap_scope;
+    ORBextractor ex(nfeatures, scale_factor, nlevels, ini_th, min_th);
+    Pinhole cam(std::vector<float>(K4, K4 + 4));
+    cv::Mat D = cv::Mat(ndist, 1, CV_32F, const_cast<float*>(dist), 4).clone();
+    cv::Mat img(h, w, CV_8UC1, const_cast<uint8_t*>(im), (size_t)w);
+    ORBVocabulary voc;
+    if (voc_path && !voc.loadFromTextFile(voc_path)) return -3;
+    Frame::mbInitialComputations = true;
+    Frame F(img, 0.0, &ex, voc_path ? &voc : nullptr, &cam, D, 0.f, 0.f);
+    const int n = F.N;
+    out_n[0] = n; out_n[1] = F.monoLeft; out_n[2] = out_n[3] = 0;
+    if (n > cap) return -1;
+    if (n) {
+        std::memcpy(kps, F.mvKeys.data(), (size_t)n * sizeof(cv::KeyPoint));
+        std::memcpy(kps_un, F.mvKeysUn.data(), (size_t)n * sizeof(cv::KeyPoint));
+        for (int i = 0; i < n; ++i) std::memcpy(desc + 32 * (size_t)i, F.mDescriptors.ptr(i), 32);
+    }
+    if (voc_path && n) {
+        F.ComputeBoW();
+        int k = 0;
+        for (const auto& wv : F.mBowVec) { words[k] = wv.first; values[k] = wv.second; ++k; }
+        out_n[2] = k;
+        int nn = 0, at = 0;
+        offsets[0] = 0;
+        for (const auto& nf : F.mFeatVec) {
+            nodes[nn] = nf.first;
+            for (unsigned i : nf.second) indices[at++] = (int32_t)i;
+            offsets[++nn] = at;
+        }
+        out_n[3] = nn;
+    }
     return 0;
 }
 

@@ -756,6 +756,7 @@ def ref_frame():
         L.orbslam3_kb8_project.argtypes = [_P, _P, _I, _P]
         L.orbslam3_pinhole_project.argtypes = [_P, _P, _I, _P]
         L.orbslam3_frame_fisheye_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _F, _F, _I] + [_P] * 7
+        L.orbslam3_frame_mono_construct.argtypes = [_P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, C.c_char_p, _I] + [_P] * 9
         L.orbslam3_frame_stereo_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, _F, _F, _I] + [_P] * 9
         L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
         _ref_frame = L
@@ -887,3 +888,25 @@ def ref_fisheye_frame(im_left, im_right, params, cam1, cam2, lap_left, lap_right
     NL, NR = int(n[0]), int(n[1])
     return dict(kps=kps[:NL + NR], desc=desc[:NL + NR], nleft=NL, nright=NR, mono_left=int(n[2]), mono_right=int(n[3]),
                 l2r=l2r[:NL], r2l=r2l[:NR], depth=depth[:NL], p3d=p3d[:NL])
+
+
+def ref_mono_frame(image, params, K4, dist, voc_path=None):
+    """The reference's monocular Frame constructor (src/Frame.cc:284-378) + Frame::ComputeBoW (:721-728), its own object code
+    (ORBextractor.cc, Frame.cc, Pinhole.cpp, DBoW2).  Returns a dict; bow = (words, values, node ids, offsets, indices)."""
+    import orbfe
+    nf, sf, nl, ini, mn = params
+    im = np.ascontiguousarray(image, np.uint8)
+    h, w = im.shape
+    K4, dist = np.ascontiguousarray(K4, np.float32), np.ascontiguousarray(dist, np.float32)
+    cap = nf + 64
+    kps, kun, desc = np.zeros(cap, orbfe.KEYPOINT_DTYPE), np.zeros(cap, orbfe.KEYPOINT_DTYPE), np.zeros((cap, 32), np.uint8)
+    n = np.zeros(4, np.int32)
+    words, values = np.zeros(cap, np.uint32), np.zeros(cap, np.float64)
+    nodes, off, idx = np.zeros(cap, np.uint32), np.zeros(cap + 1, np.int32), np.zeros(cap, np.int32)
+    rc = ref_frame().orbslam3_frame_mono_construct(_p(im), w, h, nf, sf, nl, ini, mn, _p(K4), _p(dist), len(dist),
+                                                   None if voc_path is None else str(voc_path).encode(), cap, _p(kps), _p(kun), _p(desc),
+                                                   _p(n), _p(words), _p(values), _p(nodes), _p(off), _p(idx))
+    assert rc == 0, (rc, n)
+    N, nw, nn = int(n[0]), int(n[2]), int(n[3])
+    return dict(kps=kps[:N], kps_un=kun[:N], desc=desc[:N], mono=int(n[1]),
+                bow=(words[:nw], values[:nw], nodes[:nn], off[:nn + 1], idx[:off[nn]]))

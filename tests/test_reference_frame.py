@@ -208,3 +208,28 @@ def test_fisheye_frame_constructor_end_to_end():
     ok = safe & (l2r >= 0)
     if ok.any():
         assert np.allclose(F["depth"][ok], depth[ok], rtol=2e-3, atol=1e-5) and np.allclose(F["p3d"][ok], p3d[ok], rtol=2e-3, atol=2e-4)
+
+
+def test_mono_frame_constructor_and_bow_end_to_end(tmp_path):
+    """BASELINE config 0 as the reference runs it: one 752x480 image -> the reference's own monocular Frame constructor
+    (ORBextractor(1000, 1.2, 8, 20, 7) with the lapping range (0, 1000), UndistortKeyPoints) -> Frame::ComputeBoW with a k = 10
+    vocabulary loaded by DBoW2's own loader == the oracle's extraction, undistortion and BoW transform, byte for byte
+    (BowVector values: float64 bit patterns)."""
+    import orbfe
+    from test_bow_oracle import voc_of
+    from test_reference_dbow2 import write_text
+    img = orbfe.synth.frame(1000, 752, 480)
+    K4 = np.array([458.654, 457.296, 367.215, 248.375], np.float32)
+    D = np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], np.float32)
+    parent, leaf, desc, weight = orbfe.synth.vocabulary(4242, 10, 5, 1)      # L = 5: levelsup 4 groups features by the 10 level-1 nodes
+    c = dict(k=10, L=5, weighting=0, norm=1, parent=parent, leaf=leaf, desc=desc, weight=weight)
+    write_text(c, tmp_path / "voc.txt")
+    F = ob.ref_mono_frame(img, (1000,) + mc.ORB, K4, D, tmp_path / "voc.txt")
+    mono, k, d, _ = extract(img, 1000, (0, 1000))
+    assert F["mono"] == -1                      # the constructor resets monoLeft after the extraction (Frame.cc:356)
+    assert F["kps"].tobytes() == k.tobytes() and np.array_equal(F["desc"], d)
+    assert F["kps_un"].tobytes() == ob.undistort_keypoints(k, K4, D).tobytes()
+    want = voc_of(c).transform(d, 4)
+    for a, b, what in zip(F["bow"], want, ("words", "values", "node ids", "offsets", "indices")):
+        assert np.array_equal(a, b), what
+    assert len(F["bow"][0]) > 300 and len(F["bow"][2]) == 10

@@ -196,3 +196,28 @@ def test_fisheye_frame_end_to_end_vs_reference_constructor():
     ok = safe & (F["l2r"] >= 0)
     if ok.any():
         assert np.allclose(depth[ok], F["depth"][ok], rtol=2e-3, atol=1e-5) and np.allclose(p3d[ok], F["p3d"][ok], rtol=2e-3, atol=2e-4)
+
+
+@frame_lib
+def test_mono_frame_and_bow_end_to_end_vs_reference_constructor(tmp_path):
+    """BASELINE config 0 end to end: one 752x480 image -> the product (extraction with the lapping range (0, 1000), undistortion,
+    BoW transform with the vocabulary read by orbfe's ORBvoc loader) vs the reference's own monocular Frame constructor +
+    Frame::ComputeBoW (Frame.cc:284-378, 721-728; DBoW2 reading the same text file): mvKeys, descriptors, mvKeysUn, mBowVec (float64
+    bit patterns) and mFeatVec byte for byte."""
+    from test_reference_dbow2 import write_text
+    img = orbfe.synth.frame(1000, 752, 480)
+    K4 = np.array([458.654, 457.296, 367.215, 248.375], np.float32)
+    D = np.array([-0.28340811, 0.07395907, 0.00019359, 1.76187114e-05], np.float32)
+    parent, leaf, desc, weight = orbfe.synth.vocabulary(4242, 10, 5, 1)
+    c = dict(k=10, L=5, weighting=0, norm=1, parent=parent, leaf=leaf, desc=desc, weight=weight)
+    write_text(c, tmp_path / "voc.txt")
+    F = ob.ref_mono_frame(img, (1000,) + mc.ORB, K4, D, tmp_path / "voc.txt")
+    ex = orbfe.ORBextractor(1000, *mc.ORB, max_width=752, max_height=480)
+    mono, k, d = ex(img, None, (0, 1000))
+    assert F["kps"].tobytes() == k.tobytes() and np.array_equal(F["desc"], d) and len(k) >= 1000
+    assert F["kps_un"].tobytes() == orbfe.ORBmatcher().UndistortKeyPoints(k, K4, D).tobytes()
+    v = orbfe.ORBVocabulary.loadFromTextFile(str(tmp_path / "voc.txt"), 1)
+    (words, values), fv = v.transform(d, 4)
+    rw, rv, rn, ro, ri = F["bow"]
+    assert np.array_equal(words, rw) and np.array_equal(values, rv)
+    assert np.array_equal(fv.node_ids, rn) and np.array_equal(fv.offsets, ro) and np.array_equal(fv.indices, ri)
