@@ -173,6 +173,12 @@ extern "C" {
 // ---- KB8 fisheye (kb8_ref.cc)
 void orbref_kb8_project(const float* cam, const float* p, float* uv) { kb8Project(*(const Kb8*)cam, p, uv); }
 void orbref_kb8_unproject(const float* cam, float u, float v, float* ray) { kb8Unproject(*(const Kb8*)cam, u, v, ray); }
+// KannalaBrandt8::TriangulateMatches_ per pair (the predicate behind epipolarConstrain_, KannalaBrandt8.cpp:423-426, 409-480)
+void orbref_kb8_triangulate_pairs(const float* cam1, const float* cam2, const KeyPoint* kp1, const KeyPoint* kp2, int n, const float* R12,
+                                  const float* t12, const float* sigma, const float* unc, float* depth, float* p3d, float* margins) {
+    for (int i = 0; i < n; ++i)
+        depth[i] = kb8TriangulateMatches(*(const Kb8*)cam1, *(const Kb8*)cam2, kp1[i], kp2[i], R12, t12, sigma[i], unc[i], p3d + 3 * i, margins + i);
+}
 int orbref_fisheye_stereo(const float* cam1, const float* cam2, const KeyPoint* kpL, const uint8_t* descL, int nL, int monoLeft,
                           const KeyPoint* kpR, const uint8_t* descR, int nR, int monoRight, const float* R12, const float* t12,
                           const float* sigma2, int32_t* l2r, int32_t* r2l, float* depth, float* p3d, float* margins) {

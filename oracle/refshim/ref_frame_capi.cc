@@ -335,6 +335,23 @@ int orbslam3_frame_mono_construct(const uint8_t* im, int w, int h, int nfeatures
     return 0;
 }
 
+// KannalaBrandt8::epipolarConstrain_ (KannalaBrandt8.cpp:423-426) = TriangulateMatches_ (:409-480, the Matx code path that
+// SearchForTriangulation_ reaches) > 0.0001, and the point it triangulates, per key point pair.
+void orbslam3_kb8_epipolar_constrain_(const float* cam1, const float* cam2, const void* kps1, const void* kps2, int n, const float* R12,
+                                      const float* t12, const float* sigma, const float* unc, uint8_t* ok, float* depth, float* p3d) {
+    HeapScope heap_scope;
+    KannalaBrandt8 c1(std::vector<float>(cam1, cam1 + 8)), c2(std::vector<float>(cam2, cam2 + 8));
+    const std::vector<cv::KeyPoint> k1 = keypoints(kps1, n), k2 = keypoints(kps2, n);
+    cv::Matx33f R(R12[0], R12[1], R12[2], R12[3], R12[4], R12[5], R12[6], R12[7], R12[8]);
+    cv::Matx31f t(t12[0], t12[1], t12[2]);
+    for (int i = 0; i < n; ++i) {
+        ok[i] = c1.epipolarConstrain_(&c2, k1[i], k2[i], R, t, sigma[i], unc[i]) ? 1 : 0;
+        cv::Matx31f p;
+        depth[i] = c1.TriangulateMatches_(&c2, k1[i], k2[i], R, t, sigma[i], unc[i], p);
+        for (int k = 0; k < 3; ++k) p3d[3 * i + k] = depth[i] > 0 ? p(k) : 0.f;
+    }
+}
+
 // Pinhole::project (Pinhole.cpp:34-42) / unproject (:68-71) on n points.
 void orbslam3_pinhole_project(const float* K4, const float* p3d, int n, float* uv) {
     HeapScope heap_scope;

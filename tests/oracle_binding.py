@@ -757,6 +757,7 @@ def ref_frame():
         L.orbslam3_pinhole_project.argtypes = [_P, _P, _I, _P]
         L.orbslam3_frame_fisheye_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _F, _F, _I] + [_P] * 7
         L.orbslam3_frame_mono_construct.argtypes = [_P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, C.c_char_p, _I] + [_P] * 9
+        L.orbslam3_kb8_epipolar_constrain_.argtypes = [_P] * 4 + [_I] + [_P] * 7
         L.orbslam3_frame_stereo_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, _F, _F, _I] + [_P] * 9
         L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
         _ref_frame = L
@@ -910,3 +911,30 @@ def ref_mono_frame(image, params, K4, dist, voc_path=None):
     N, nw, nn = int(n[0]), int(n[2]), int(n[3])
     return dict(kps=kps[:N], kps_un=kun[:N], desc=desc[:N], mono=int(n[1]),
                 bow=(words[:nw], values[:nw], nodes[:nn], off[:nn + 1], idx[:off[nn]]))
+
+
+def _pair_args(cam1, cam2, kp1, kp2, R12, t12, sigma, unc):
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    return f(cam1), f(cam2), np.ascontiguousarray(kp1), np.ascontiguousarray(kp2), f(R12).reshape(9), f(t12).reshape(3), f(sigma), f(unc)
+
+
+def ref_kb8_epipolar_constrain(cam1, cam2, kp1, kp2, R12, t12, sigma, unc):
+    """KannalaBrandt8::epipolarConstrain_ / TriangulateMatches_ (KannalaBrandt8.cpp:409-480), the reference's own object code.
+    Returns (ok, depth, p3d)."""
+    cam1, cam2, kp1, kp2, R12, t12, sigma, unc = _pair_args(cam1, cam2, kp1, kp2, R12, t12, sigma, unc)
+    n = len(kp1)
+    ok, depth, p3d = np.zeros(n, np.uint8), np.zeros(n, np.float32), np.zeros((n, 3), np.float32)
+    ref_frame().orbslam3_kb8_epipolar_constrain_(_p(cam1), _p(cam2), _p(kp1), _p(kp2), n, _p(R12), _p(t12), _p(sigma), _p(unc), _p(ok),
+                                                 _p(depth), _p(p3d))
+    return ok.astype(bool), depth, p3d
+
+
+def kb8_triangulate_pairs(cam1, cam2, kp1, kp2, R12, t12, sigma, unc):
+    """The oracle's per-pair KB8 predicate (oracle/cpu_ref/kb8_ref.cc).  Returns (depth, p3d, margins)."""
+    cam1, cam2, kp1, kp2, R12, t12, sigma, unc = _pair_args(cam1, cam2, kp1, kp2, R12, t12, sigma, unc)
+    n = len(kp1)
+    depth, p3d, mg = np.zeros(n, np.float32), np.zeros((n, 3), np.float32), np.zeros(n, np.float32)
+    L_ = lib()
+    L_.orbref_kb8_triangulate_pairs.argtypes = [_P] * 4 + [_I] + [_P] * 7
+    L_.orbref_kb8_triangulate_pairs(_p(cam1), _p(cam2), _p(kp1), _p(kp2), n, _p(R12), _p(t12), _p(sigma), _p(unc), _p(depth), _p(p3d), _p(mg))
+    return depth, p3d, mg

@@ -233,3 +233,26 @@ def test_mono_frame_constructor_and_bow_end_to_end(tmp_path):
     for a, b, what in zip(F["bow"], want, ("words", "values", "node ids", "offsets", "indices")):
         assert np.array_equal(a, b), what
     assert len(F["bow"][0]) > 300 and len(F["bow"][2]) == 10
+
+
+def test_kb8_epipolar_constrain_oracle_vs_reference_source():
+    """KannalaBrandt8::epipolarConstrain_ (the Matx code path SearchForTriangulation_ reaches with fisheye cameras:
+    TriangulateMatches_ / Triangulate_, KannalaBrandt8.cpp:409-480, 514-537) vs the oracle's per-pair predicate, on the matched
+    pairs of a fisheye fixture plus mismatched pairs: same decision wherever no threshold is within 1e-3, same point."""
+    c = mc.fisheye_inputs("fisheye_tumvi")
+    s2 = tables()[2]
+    l2r = ob.fisheye_stereo(c["cam1"], c["cam2"], c["kL"], c["dL"], c["mono_l"], c["kR"], c["dR"], c["mono_r"], c["R12"], c["t12"], s2)[0]
+    rng = np.random.default_rng(8)
+    iL = np.concatenate([np.flatnonzero(l2r >= 0), rng.integers(c["mono_l"], len(c["kL"]), 1500)])
+    iR = np.concatenate([l2r[l2r >= 0], rng.integers(c["mono_r"], len(c["kR"]), 1500)])
+    k1, k2 = c["kL"][iL], c["kR"][iR]
+    sig, unc = s2[k1["octave"]], s2[k2["octave"]]
+    ok, depth, p3d = ob.ref_kb8_epipolar_constrain(c["cam1"], c["cam2"], k1, k2, c["R12"], c["t12"], sig, unc)
+    odepth, op3d, mg = ob.kb8_triangulate_pairs(c["cam1"], c["cam2"], k1, k2, c["R12"], c["t12"], sig, unc)
+    safe = mg > 1e-3
+    assert safe.mean() > 0.95
+    assert np.array_equal(ok[safe], odepth[safe] > 0.0001)
+    assert np.array_equal(ok, depth > 0.0001)
+    both = safe & ok
+    assert both.sum() > 300 and (~ok & safe).sum() > 300
+    assert np.allclose(depth[both], odepth[both], rtol=2e-3, atol=1e-5) and np.allclose(p3d[both], op3d[both], rtol=2e-3, atol=2e-4)
