@@ -256,3 +256,35 @@ def test_kb8_epipolar_constrain_oracle_vs_reference_source():
     both = safe & ok
     assert both.sum() > 300 and (~ok & safe).sum() > 300
     assert np.allclose(depth[both], odepth[both], rtol=2e-3, atol=1e-5) and np.allclose(p3d[both], op3d[both], rtol=2e-3, atol=2e-4)
+
+
+def _stereo_random_configs(seed, count):
+    from test_reference_orbextractor import random_configs
+    return [c for c in random_configs(seed, 3 * count) if c[4] >= 3][:count]
+
+
+def _cfg_id(c):
+    return "%dx%d_n%d_s%.2f_l%d_t%d-%d" % c
+
+
+@pytest.mark.parametrize("cfg", _stereo_random_configs(20261107, 6), ids=_cfg_id)
+def test_stereo_frame_constructor_random_configs(cfg):
+    """Random image shapes, feature budgets, scale factors, level counts and FAST thresholds: the reference's stereo Frame
+    constructor from two images == the oracle's extraction + stereo matcher + undistortion, byte for byte."""
+    import orbfe
+    w, h, nf, sf, nl, ini, mn = cfg
+    imL, imR = orbfe.synth.stereo_pair(9000 + w + h, w, h)
+    K4 = np.array([0.6 * w, 0.6 * w, w / 2 - 3.25, h / 2 + 1.5], np.float32)
+    D = np.array([-0.21, 0.05, 0.0004, -0.0003], np.float32)
+    bf = float(np.float32(0.11 * K4[0]))
+    F = ob.ref_stereo_frame(imL, imR, (nf, sf, nl, ini, mn), K4, D, bf)
+    rL, rR = ob.OrbRef(nf, sf, nl, ini, mn), ob.OrbRef(nf, sf, nl, ini, mn)
+    _, kL, dL = rL(imL, (0, 0))
+    _, kR, dR = rR(imR, (0, 0))
+    assert F["kps"].tobytes() == kL.tobytes() and np.array_equal(F["desc"], dL)
+    assert F["kps_r"].tobytes() == kR.tobytes() and np.array_equal(F["desc_r"], dR)
+    b = float(np.float32(np.float32(bf) / K4[0]))
+    u, d, _ = ob.stereo_match(rL, rR, kL, dL, kR, dR, bf, b)
+    assert np.array_equal(F["u_right"], u) and np.array_equal(F["depth"], d)
+    assert F["kps_un"].tobytes() == ob.undistort_keypoints(kL, K4, D).tobytes()
+    assert (d > 0).sum() > 0.2 * len(kL)

@@ -221,3 +221,32 @@ def test_mono_frame_and_bow_end_to_end_vs_reference_constructor(tmp_path):
     rw, rv, rn, ro, ri = F["bow"]
     assert np.array_equal(words, rw) and np.array_equal(values, rv)
     assert np.array_equal(fv.node_ids, rn) and np.array_equal(fv.offsets, ro) and np.array_equal(fv.indices, ri)
+
+
+def _gpu_stereo_configs():
+    from test_reference_frame import _stereo_random_configs
+    return _stereo_random_configs(20261108, 5)
+
+
+@frame_lib
+@pytest.mark.parametrize("cfg", _gpu_stereo_configs(), ids=lambda c: "%dx%d_n%d_s%.2f_l%d_t%d-%d" % c)
+def test_stereo_frame_random_configs_vs_reference_constructor(cfg):
+    """Random shapes / budgets / scale factors / level counts / thresholds: product (batched extraction + stereo matcher +
+    undistortion) vs the reference's own stereo Frame constructor run from the same two images, byte for byte."""
+    w, h, nf, sf, nl, ini, mn = cfg
+    imL, imR = orbfe.synth.stereo_pair(9100 + w + h, w, h)
+    K4 = np.array([0.6 * w, 0.6 * w, w / 2 - 3.25, h / 2 + 1.5], np.float32)
+    D = np.array([-0.21, 0.05, 0.0004, -0.0003], np.float32)
+    bf = float(np.float32(0.11 * K4[0]))
+    b = float(np.float32(np.float32(bf) / K4[0]))
+    F = ob.ref_stereo_frame(imL, imR, (nf, sf, nl, ini, mn), K4, D, bf)
+    ex = orbfe.ORBextractor(nf, sf, nl, ini, mn, max_width=w, max_height=h, max_batch=2)
+    (_, kL, dL), (_, kR, dR) = ex.extract_batch(np.stack([imL, imR]), (0, 0))
+    m = orbfe.ORBmatcher()
+    u, d, n = m.stereo_match(ex, ex, bf, b, 0, 1)
+    assert F["kps"].tobytes() == kL.tobytes() and F["kps_r"].tobytes() == kR.tobytes()
+    same = (F["desc"] == dL).all(1).sum() + (F["desc_r"] == dR).all(1).sum()
+    assert same >= 0.9999 * (len(dL) + len(dR))
+    if same == len(dL) + len(dR):
+        assert np.array_equal(F["u_right"], u[:len(kL)]) and np.array_equal(F["depth"], d[:len(kL)])
+    assert F["kps_un"].tobytes() == m.UndistortKeyPoints(kL, K4, D).tobytes()
