@@ -185,6 +185,10 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
                 c.ox = (short)(j * g.wCell); c.oy = (short)(i * g.hCell); c.pad = 0;
                 const int tw = c.cw - 6, th = c.ch - 6;
                 if (tw <= 0 || th <= 0) continue;   // FAST on a < 7 px ROI finds nothing
+                {   // words per tested row as k_fast_cells counts them (tile byte = sh + column)
+                    const int sh = (ORBFE_XO + c.x0) & 15, wLo = (sh + 3) >> 2, wHi = (sh + c.cw - 4) >> 2, nWords = wHi - wLo + 1;
+                    c.inv = ((1u << 20) + nWords - 1) / nWords;
+                }
                 sp.cells.push_back(c);
                 const int keptCap = ((tw + 1) / 2) * ((th + 1) / 2);
                 cap += keptCap;

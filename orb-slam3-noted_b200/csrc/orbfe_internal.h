@@ -52,6 +52,7 @@ struct CellDesc {
     short level, x0, y0, cw, ch;   // ROI-relative origin (iniX, iniY) and size (maxX-iniX, maxY-iniY)
     short ox, oy;                  // j*wCell, i*hCell
     short pad;
+    unsigned inv;                  // ceil(2^20 / words per tested row): k_fast_cells splits a work unit index without dividing
 };
 
 // Bilinear resize coefficients of one destination column/row (OpenCV 11-bit fixed point).
