@@ -48,12 +48,13 @@ __device__ __forceinline__ int fast_score_packed(const uint8_t* __restrict__ til
     return (int)max(best & 0xFFFFu, best >> 16) - 257;
 }
 
-// Per-byte unsigned "a > b" of two packed u8x4 words; the answer is bit 7 of each byte (other bits are
-// garbage, mask with 0x80808080).  With a = a7:al, b = b7:bl:  a > b  <=>  (a7 & ~b7) | (a7 == b7 & al > bl),
-// and bit 7 of (b | 0x80) - (a & 0x7f) is "bl >= al" (128 + bl - al never borrows across bytes).
-__device__ __forceinline__ uint32_t gtu4_bit7(uint32_t a, uint32_t b) {
-    const uint32_t ge_ba = (b | 0x80808080u) - (a & 0x7F7F7F7Fu);
-    return (a & ~b) | (~(a ^ b) & ~ge_ba);
+// Per-byte unsigned "a > t" of a packed u8x4 word against ONE threshold t (the same in all four bytes); the answer is
+// bit 7 of each byte (other bits are garbage, mask with 0x80808080).  With a = a7:al and t = t7:tl, bit 7 of
+// x = al + (127 - tl) is "al > tl" (the sum never carries across bytes), and  a > t  <=>  t7 ? (a7 & x7) : (a7 | x7).
+// k127 = (127 - tl) in every byte, lowT = t < 128 ? ~0 : 0.  Three instructions: LOP3, IADD, LOP3.
+__device__ __forceinline__ uint32_t gtu4_bit7(uint32_t a, uint32_t k127, uint32_t lowT) {
+    const uint32_t x = (a & 0x7F7F7F7Fu) + k127;
+    return (x & a) | ((x | a) & lowT);
 }
 
 // ---- TMA + mbarrier helpers (sm_100a PTX) -----------------------------------------------------------
@@ -163,18 +164,18 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
         // A1: necessary condition on two opposite ring pairs, 4 pixels per step.  A 9-arc covers at least
         // one pixel of every opposite pair, so a corner has |c - v| > t for v0 or v8 AND for v4 or v12.
         {
-            const uint32_t t4 = (uint32_t)t * 0x01010101u;
+            const uint32_t k127 = (uint32_t)(127 - (t & 127)) * 0x01010101u, lowT = t < 128 ? 0xFFFFFFFFu : 0u;
             const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(tile);
             for (int u = tid; u < units; u += FAST_THREADS) {
                 const int rr = (int)(((uint32_t)u * inv) >> 20), wi = wLo + u - rr * nWordsA1, r = rr + 3;
                 const uint32_t c = tw32[r * nw + wi];
                 const uint32_t up = tw32[(r - 3) * nw + wi], dn = tw32[(r + 3) * nw + wi];
-                uint32_t m = (gtu4_bit7(__vabsdiffu4(c, up), t4) | gtu4_bit7(__vabsdiffu4(c, dn), t4)) & 0x80808080u;
+                uint32_t m = (gtu4_bit7(__vabsdiffu4(c, up), k127, lowT) | gtu4_bit7(__vabsdiffu4(c, dn), k127, lowT)) & 0x80808080u;
                 if (m == 0) continue;
                 const uint32_t lf = tw32[r * nw + wi - 1], rt = tw32[r * nw + wi + 1];
                 const uint32_t vl = __byte_perm(lf, c, 0x4321);      // bytes at column - 3
                 const uint32_t vr = __byte_perm(c, rt, 0x6543);      // bytes at column + 3
-                m &= gtu4_bit7(__vabsdiffu4(c, vl), t4) | gtu4_bit7(__vabsdiffu4(c, vr), t4);
+                m &= gtu4_bit7(__vabsdiffu4(c, vl), k127, lowT) | gtu4_bit7(__vabsdiffu4(c, vr), k127, lowT);
                 // nibble of survivors, restricted to tested columns [3, cw-3)
                 uint32_t vb = (m >> 7 & 1u) | (m >> 14 & 2u) | (m >> 21 & 4u) | (m >> 28 & 8u);
                 const int c0 = 4 * wi - sh;                      // column of byte 0 (may be < 0)

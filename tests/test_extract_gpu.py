@@ -195,3 +195,22 @@ def test_cuda_equals_reference_source_random_configs(cfg):
     for l in range(nl):
         assert np.array_equal(ex.image_pyramid(l, 0)[0], ref.level_bordered(l)), f"pyramid level {l}"
     assert ok >= 0.9999 * tot and tot > 0.5 * nf, (ok, tot)
+
+
+@pytest.mark.parametrize("ini,mn", [(150, 130), (200, 127), (128, 5), (127, 126), (254, 253)])
+def test_cuda_equals_reference_source_high_thresholds(ini, mn):
+    """FAST thresholds on both sides of 128 (the packed byte compare of k_fast_cells switches form there) on a black / white
+    checker pattern with noise: CUDA vs the reference's own ORBextractor.cc."""
+    import oracle_binding as ob
+    if not ob.ref_available():
+        pytest.skip("oracle/_ref not built")
+    w, h, nf = 640, 480, 800
+    rng = np.random.default_rng(ini * 1000 + mn)
+    yy, xx = np.mgrid[0:h, 0:w]
+    img = (((xx // 23 + yy // 17) % 2) * 235 + 10 + rng.integers(-10, 11, (h, w))).astype(np.uint8)
+    img[rng.random((h, w)) < 0.002] = 255                      # isolated bright dots: corners at any threshold below 235
+    ex = orbfe.ORBextractor(nf, 1.2, 8, ini, mn, max_width=w, max_height=h)
+    ref = ob.OrbSlam3Extractor(nf, 1.2, 8, ini, mn)
+    ok, tot = check_frame(ex, ref, img, (0, 0), stages=False)
+    assert ok >= 0.9999 * tot
+    assert tot > 50 or ini > 235, tot
