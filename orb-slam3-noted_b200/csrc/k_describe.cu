@@ -200,13 +200,16 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
         const int lim = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;
         const uint8_t* c = pyr + centre + u;
         const int pitch = g.pitch;
-        int sum = 0;
+        // rows v and -v together (m01 += v * (I(v) - I(-v)), as IC_Angle itself does); the loads are unconditional - every
+        // row of the 31 x 31 window lies inside the 19-px border and touches the same lines whichever lanes are inside the
+        // disc - so only the three accumulations are predicated and the unrolled loop has no branches
+        int sum = lane < 31 ? (int)__ldg(c) : 0;
 #pragma unroll
-        for (int v = -15; v <= 15; ++v) {
-            if ((v < 0 ? -v : v) <= lim) {
-                const int I = __ldg(c + v * pitch);
-                sum += I;
-                m01 += v * I;
+        for (int v = 1; v <= 15; ++v) {
+            const int Ip = __ldg(c + v * pitch), Im = __ldg(c - v * pitch);
+            if (v <= lim) {
+                sum += Ip + Im;
+                m01 += v * (Ip - Im);
             }
         }
         m10 = u * sum;
