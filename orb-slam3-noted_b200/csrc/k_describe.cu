@@ -223,7 +223,9 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     if (lane == 0) kps[(long long)frame * kpPerFrame + i].angle = angle;
     // a = cosf(angle * factorPI), b = sinf(...): float argument, result rounded from double precision
     const float rad = __fmul_rn(angle, (float)(3.14159265358979323846 / 180.f));
-    const float a = (float)cos((double)rad), b = (float)sin((double)rad);
+    double sd, cd;                                  // one shared argument reduction for both
+    sincos((double)rad, &sd, &cd);
+    const float a = (float)cd, b = (float)sd;
     // ---- lane computes descriptor byte `lane`: tests 8*lane .. 8*lane+7
     const uint8_t* Bc = blur + centre;
     const int pitch = g.pitch;
