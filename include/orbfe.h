@@ -112,11 +112,27 @@ int orbfe_get_pyramid_level(orbfe_handle* h, int frame, int level, uint8_t* dst,
  * (ORBextractor.cc:843-851).  Returns the count (may exceed cap; only cap triples are written). */
 int orbfe_get_candidates(orbfe_handle* h, int frame, int level, int32_t* xyr, int cap);
 
-/* The CUDA stream the handle enqueues on (a cudaStream_t), for callers that time with events. */
+/* The handle's public CUDA stream (a cudaStream_t): every call is ordered on it — internally an extraction forks
+ * into side compute streams and joins back — so events recorded on it bracket whole calls. */
 void* orbfe_stream(orbfe_handle* h);
 int orbfe_synchronize(orbfe_handle* h);
-/* Number of kernels this handle has launched since creation. */
+/* Number of kernels this handle has launched since creation (kernels inside a replayed CUDA graph included), and the
+ * number of cudaGraphLaunch calls among them. */
 long long orbfe_launch_count(const orbfe_handle* h);
+long long orbfe_graph_launch_count(const orbfe_handle* h);
+
+/* Ordering against streams the handle does not own.  Matchers and vocabularies enqueue on their own streams; a
+ * consumer that reads an extractor's DEVICE results without a host synchronise in between must be ordered after
+ * the extraction, and the next extraction (which overwrites those results and the pyramid) after the consumer:
+ *   orbfe_stream_wait_extractor(h, s)  work enqueued on stream `s` from now on waits for everything enqueued on h so far;
+ *   orbfe_extractor_wait_stream(h, s)  work enqueued on h from now on waits for everything enqueued on `s` so far.
+ * The entry points that take an orbfe_handle* themselves (orbfe_stereo_match*) do both internally. */
+int orbfe_stream_wait_extractor(orbfe_handle* h, void* stream);
+int orbfe_extractor_wait_stream(orbfe_handle* h, void* stream);
+
+/* Tuning of the device-side pipeline (defaults: 32-frame chunks over 3 compute streams, CUDA graphs on).
+ * chunk_frames / compute_streams <= 0 and use_graphs < 0 keep the current value.  Synchronises the handle. */
+int orbfe_set_pipeline(orbfe_handle* h, int chunk_frames, int compute_streams, int use_graphs);
 
 /* Per-stage device timing (the REGISTER_TIMES switch of include/Config.h:4 / Frame.cc:116-127, done
  * with CUDA events on the handle's stream).  While enabled every extract call brackets its stages

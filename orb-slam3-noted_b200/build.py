@@ -31,15 +31,32 @@ def _run(cmd, **kw):
     return r.stdout
 
 
-def build_cuda(force=False):
+def build_cuda(force=False, defines=(), out=None):
+    """One object per .cu file (compiled in parallel, only the stale ones), then one link.  `defines` / `out` build a
+    variant library (tools/variant_sweep.sh); variants always recompile everything into their own object directory."""
+    from concurrent.futures import ThreadPoolExecutor
     srcs = sorted(glob.glob(os.path.join(CSRC, "*.cu")))
-    deps = srcs + glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.inc")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
+    hdrs = glob.glob(os.path.join(CSRC, "*.h")) + glob.glob(os.path.join(CSRC, "*.inc")) + glob.glob(os.path.join(CSRC, "*.cuh")) + \
         glob.glob(os.path.join(ROOT, "include", "*.h"))
-    if not force and _newer(LIB, deps):
+    lib = out or LIB
+    variant = bool(defines) or out is not None
+    if not force and not variant and _newer(LIB, srcs + hdrs):
         return LIB
     nvcc = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
-    _run([nvcc] + NVCC_FLAGS + ["-o", LIB] + srcs)
-    return LIB
+    objdir = os.path.join(HERE, "_build", "obj" + ("_" + os.path.basename(lib) if variant else ""))
+    os.makedirs(objdir, exist_ok=True)
+    flags = [f for f in NVCC_FLAGS if f != "-shared"] + ["-D" + d for d in defines]
+
+    def one(src):
+        obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
+        if force or variant or not _newer(obj, [src] + hdrs):
+            _run([nvcc] + flags + ["-c", "-o", obj, src])
+        return obj
+
+    with ThreadPoolExecutor(max_workers=min(8, os.cpu_count() or 1)) as pool:
+        objs = list(pool.map(one, srcs))
+    _run([nvcc, "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", lib] + objs)
+    return lib
 
 
 def build_synth(force=False):

@@ -210,11 +210,9 @@ cudaError_t orbfe_launch_bow_assemble(cudaStream_t st, const VocDev& v, const in
                                       int* dNNodes, long long* launches) {
     if (batch <= 0) return cudaSuccess;
     const size_t smem = orbfe_bow_assemble_smem(nMax > 0 ? nMax : 1);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_bow_assemble, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
+    {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_bow_assemble), smem);
+        if (ea != cudaSuccess) return ea;
     }
     k_bow_assemble<<<batch, ASM_T, smem, st>>>(v, dN, nHost, nMax, dWord, dNode, dW, dWords, dValues, dNWords, dNodeIds, dOffsets,
                                               dIndices, dNNodes);

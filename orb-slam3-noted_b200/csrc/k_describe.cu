@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
 }
 
 cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int lap0, int lap1) {
-    k_assemble<<<batch, ASM_THREADS, 0, h->stream>>>(h->dGeom, h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, lap0, lap1,
+    k_assemble<<<batch, ASM_THREADS, 0, h->cur>>>(h->dGeom, h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, lap0, lap1,
                                                      h->dKps, h->dSlot, h->dN, h->dMono, frame0);
     h->launches++;
     return cudaGetLastError();
@@ -257,11 +257,11 @@ cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int la
 cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch) {
     {
         dim3 grid((h->blurTiles + 3) / 4, batch);
-        k_blur<<<grid, 128, 0, h->stream>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles, frame0);
+        k_blur<<<grid, 128, 0, h->cur>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles, frame0);
         h->launches++;
     }
     dim3 grid((h->kpPerFrame + DESC_WARPS - 1) / DESC_WARPS, batch);
-    k_describe<<<grid, DESC_WARPS * 32, 0, h->stream>>>(h->dPyr, h->dBlur, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps,
+    k_describe<<<grid, DESC_WARPS * 32, 0, h->cur>>>(h->dPyr, h->dBlur, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps,
                                                        h->dDesc, frame0);
     h->launches++;
     return cudaGetLastError();

@@ -243,18 +243,16 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
 }
 
 cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
-    cudaError_t e = cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->stream);
+    cudaError_t e = cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->cur);
     if (e != cudaSuccess) return e;
-    static size_t configured = 0;
     const size_t tileStride = ((size_t)h->fastBoxW * h->fastBoxH + 127) & ~(size_t)127;
     const size_t smem = (size_t)h->maxCellBytes + FAST_CPC * tileStride - (size_t)h->fastBoxW * h->fastBoxH;   // maxCellBytes counts one unpadded tile
-    if (smem > 48 * 1024 && smem > configured) {
-        e = cudaFuncSetAttribute(k_fast_cells, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
+    {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_fast_cells), smem);
+        if (ea != cudaSuccess) return ea;
     }
     dim3 grid((h->nCellsTotal + FAST_CPC - 1) / FAST_CPC, batch);
-    k_fast_cells<<<grid, FAST_THREADS, smem, h->stream>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,
+    k_fast_cells<<<grid, FAST_THREADS, smem, h->cur>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,
                                                           h->candPerFrame, h->p.nlevels, h->p.ini_th_fast, h->p.min_th_fast,
                                                           h->fastBoxW, h->fastBoxH, frame0, h->nCellsTotal);
     h->launches++;

@@ -331,14 +331,12 @@ cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch) {
     int sortCap = 1;
     while (sortCap < Lcap) sortCap <<= 1;
     const size_t smem = octree_smem_bytes(Lcap, sortCap);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_octree, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
+    {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_octree), smem);
+        if (ea != cudaSuccess) return ea;
     }
     dim3 grid(h->p.nlevels, batch);
-    k_octree<<<grid, OCT_THREADS, smem, h->stream>>>(h->dGeom, h->dCand, h->dNodeOf, h->dCandCount, h->candPerFrame,
+    k_octree<<<grid, OCT_THREADS, smem, h->cur>>>(h->dGeom, h->dCand, h->dNodeOf, h->dCandCount, h->candPerFrame,
                                                      h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, Lcap, sortCap, frame0);
     h->launches++;
     return cudaGetLastError();

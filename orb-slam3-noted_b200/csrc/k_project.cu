@@ -471,11 +471,9 @@ cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem
     int np2 = 1;
     while (np2 < nMax) np2 <<= 1;
     const size_t smem = (size_t)np2 * 4;
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_proj_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
+    {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_proj_grid), smem);
+        if (ea != cudaSuccess) return ea;
     }
     k_proj_grid<<<nprob, PROJ_T, smem, st>>>(dProbs);
     if (nqMax > 0) {

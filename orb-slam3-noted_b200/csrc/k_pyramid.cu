@@ -171,14 +171,14 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int fr
         const LevelGeom& g = h->geom[0];
         if (h->inFormat == ORBFE_FORMAT_GRAY8) {
             dim3 grid(((g.pitch >> 4) + 7) / 8, batch, (g.rows + 31) / 32);
-            k_pyr_level0<<<grid, 256, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
+            k_pyr_level0<<<grid, 256, 0, h->cur>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
         } else {
             dim3 grid((g.pitch / 4 + 127) / 128, g.rows, batch);
             const int rFirst = h->inFormat == ORBFE_FORMAT_RGB8 || h->inFormat == ORBFE_FORMAT_RGBA8;
             if (h->inFormat <= ORBFE_FORMAT_BGR8)
-                k_pyr_level0_color<3><<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
+                k_pyr_level0_color<3><<<grid, 128, 0, h->cur>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
             else
-                k_pyr_level0_color<4><<<grid, 128, 0, h->stream>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
+                k_pyr_level0_color<4><<<grid, 128, 0, h->cur>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
         }
         h->launches++;
     }
@@ -187,10 +187,10 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int fr
         if (gd.planBase >= 0) {
             const int tilesX = gd.pitch / 128, total = tilesX * ((gd.rows + PYR_TH - 1) / PYR_TH);
             dim3 grid((total + 3) / 4, batch);
-            k_pyr_resize_plan<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total, frame0);
+            k_pyr_resize_plan<<<grid, 128, 0, h->cur>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total, frame0);
         } else {   // scale factors whose 2-column source window exceeds 8 bytes: generic kernel
             dim3 grid((gd.pitch / 4 + 127) / 128, gd.rows, batch);
-            k_pyr_resize<<<grid, 128, 0, h->stream>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, frame0);
+            k_pyr_resize<<<grid, 128, 0, h->cur>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, frame0);
         }
         h->launches++;
     }

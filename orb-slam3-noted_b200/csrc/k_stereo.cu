@@ -229,11 +229,9 @@ cudaError_t orbfe_launch_stereo(cudaStream_t st, const orbfe_handle* hl, int fra
         tb.invScale[l] = l < hl->p.nlevels ? hl->invScale[l] : 1.f;
     }
     const size_t smem = (size_t)hr->kpPerFrame * 8;
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_stereo_search, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
+    {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_stereo_search), smem);
+        if (ea != cudaSuccess) return ea;
     }
     dim3 grid((hl->kpPerFrame + ST_THREADS - 1) / ST_THREADS, npairs);
     k_stereo_search<<<grid, ST_THREADS, smem, st>>>(L, R, tb, bf, b, dURight, dDepth, dSad, outStride);

@@ -7,7 +7,9 @@
 #include <string.h>
 
 #include <algorithm>
+#include <map>
 #include <mutex>
+#include <utility>
 #include <vector>
 
 #include "orbfe_internal.h"
@@ -26,6 +28,21 @@ int orbfe_set_cuda_error(cudaError_t e, const char* what) { return cuda_fail(e, 
     } while (0)
 
 static inline int cvRoundF(float v) { return (int)lrintf(v); }   // half-to-even
+
+cudaError_t orbfe_ensure_dyn_smem(const void* func, size_t bytes) {
+    if (bytes <= 48 * 1024) return cudaSuccess;
+    static std::mutex mu;
+    static std::map<std::pair<int, const void*>, size_t> granted;   // high-water mark per (device, kernel)
+    int dev = 0;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return e;
+    std::lock_guard<std::mutex> lock(mu);
+    size_t& g = granted[std::make_pair(dev, func)];
+    if (bytes <= g) return cudaSuccess;
+    e = cudaFuncSetAttribute(func, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    if (e == cudaSuccess) g = bytes;
+    return e;
+}
 
 // ---- reference tables, ORBextractor.cc:413-444 ----------------------------------------------------
 static void build_tables(orbfe_handle* h) {
@@ -234,7 +251,10 @@ static void free_handle(orbfe_handle* h) {
     cudaSetDevice(h->device);
     cudaFree(h->dIn); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dCand); cudaFree(h->dNodeOf); cudaFree(h->dCandCount);
     cudaFree(h->dLvlKp); cudaFree(h->dLvlCount); cudaFree(h->dGeom); cudaFree(h->dCells); cudaFree(h->dTaps); cudaFree(h->dPlans);
-    cudaFree(h->dKps); cudaFree(h->dDesc); cudaFree(h->dSlot); cudaFree(h->dN); cudaFree(h->dMono);
+    cudaFree(h->dRes); cudaFree(h->dSlot);
+    if (h->hRes) cudaFreeHost(h->hRes);
+    for (int i = 0; i < ORBFE_GRAPH_SLOTS; ++i)
+        if (h->graphs[i].exec) cudaGraphExecDestroy(h->graphs[i].exec);
     if (h->hN) cudaFreeHost(h->hN);
     if (h->hMono) cudaFreeHost(h->hMono);
     if (h->profEv) {
@@ -245,9 +265,14 @@ static void free_handle(orbfe_handle* h) {
     for (int c = 0; c < ORBFE_PIPE_MAX_CHUNKS; ++c)
         for (int k = 0; k < 3; ++k)
             if (h->evPipe[c][k]) cudaEventDestroy(h->evPipe[c][k]);
+    if (h->evFork) cudaEventDestroy(h->evFork);
+    if (h->evOrder) cudaEventDestroy(h->evOrder);
+    for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
+        if (h->evJoin[i]) cudaEventDestroy(h->evJoin[i]);
     if (h->sIn) cudaStreamDestroy(h->sIn);
     if (h->sOut) cudaStreamDestroy(h->sOut);
-    if (h->sAlt) cudaStreamDestroy(h->sAlt);
+    for (int i = 1; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
+        if (h->sComp[i]) cudaStreamDestroy(h->sComp[i]);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
 }
@@ -284,6 +309,8 @@ static int encode_fast_maps(orbfe_handle* h) {
     return ORBFE_OK;
 }
 
+static void drop_graphs(orbfe_handle* h);
+
 // Upload the geometry of a new image shape (no-op when the shape is unchanged).
 static int configure_shape(orbfe_handle* h, int W, int H) {
     if (W == h->curW && H == h->curH) return ORBFE_OK;
@@ -312,6 +339,7 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     h->kpPerFrame = sp.kpPerFrame;
     h->blurTiles = sp.blurTiles;
     CK(cudaStreamSynchronize(h->stream));   // previous work may still read the old tables
+    drop_graphs(h);                         // captured launches carry the old geometry and tensor maps
     CK(cudaMemcpyAsync(h->dGeom, h->geom, sizeof(LevelGeom) * h->p.nlevels, cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->dCells, sp.cells.data(), sizeof(CellDesc) * sp.cells.size(), cudaMemcpyHostToDevice, h->stream));
     CK(cudaMemcpyAsync(h->dTaps, sp.taps.data(), sizeof(ResizeTap) * sp.taps.size(), cudaMemcpyHostToDevice, h->stream));
@@ -362,7 +390,20 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&h->sIn, cudaStreamNonBlocking));
     CKC(cudaStreamCreateWithFlags(&h->sOut, cudaStreamNonBlocking));
-    CKC(cudaStreamCreateWithFlags(&h->sAlt, cudaStreamNonBlocking));
+    h->sComp[0] = h->stream;
+    h->cur = h->stream;
+    for (int i = 1; i < ORBFE_MAX_COMPUTE_STREAMS; ++i) CKC(cudaStreamCreateWithFlags(&h->sComp[i], cudaStreamNonBlocking));
+    CKC(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
+    CKC(cudaEventCreateWithFlags(&h->evOrder, cudaEventDisableTiming));
+    for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i) CKC(cudaEventCreateWithFlags(&h->evJoin[i], cudaEventDisableTiming));
+    {   // device-resident pipeline tuning (see run_device_pipeline); the environment overrides are for sweeps
+        const char* e1 = getenv("ORBFE_DEV_CHUNK");
+        const char* e2 = getenv("ORBFE_DEV_STREAMS");
+        const char* e3 = getenv("ORBFE_GRAPHS");
+        h->devChunk = e1 && atoi(e1) > 0 ? atoi(e1) : ORBFE_DEV_CHUNK;
+        h->devStreams = e2 && atoi(e2) > 0 ? std::min(atoi(e2), ORBFE_MAX_COMPUTE_STREAMS) : ORBFE_DEV_STREAMS;
+        h->useGraphs = e3 ? atoi(e3) != 0 : 1;
+    }
     for (int c = 0; c < ORBFE_PIPE_MAX_CHUNKS; ++c)
         for (int k = 0; k < 3; ++k) CKC(cudaEventCreateWithFlags(&h->evPipe[c][k], cudaEventDisableTiming));
     CKC(cudaMalloc(&h->dIn, h->inBytes));
@@ -377,11 +418,19 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaMalloc(&h->dCells, sizeof(CellDesc) * h->cellCap));
     CKC(cudaMalloc(&h->dTaps, sizeof(ResizeTap) * h->tabCap));
     CKC(cudaMalloc(&h->dPlans, sizeof(ColPlan) * h->planCap));
-    CKC(cudaMalloc(&h->dKps, sizeof(orbfe_keypoint) * B * h->kpCapPerFrame));
-    CKC(cudaMalloc(&h->dDesc, (size_t)32 * B * h->kpCapPerFrame));
+    {   // one result arena: counts | mono | keypoints | descriptors
+        h->resKpsOff = (2 * sizeof(int) * B + 255) & ~(size_t)255;
+        h->resDescOff = (h->resKpsOff + sizeof(orbfe_keypoint) * B * h->kpCapPerFrame + 255) & ~(size_t)255;
+        h->resBytes = h->resDescOff + (size_t)32 * B * h->kpCapPerFrame;
+        CKC(cudaMalloc(&h->dRes, h->resBytes));
+        CKC(cudaMemset(h->dRes, 0, h->resBytes));
+        h->dN = reinterpret_cast<int*>(h->dRes);
+        h->dMono = h->dN + B;
+        h->dKps = reinterpret_cast<orbfe_keypoint*>(h->dRes + h->resKpsOff);
+        h->dDesc = h->dRes + h->resDescOff;
+        if (p.max_batch <= ORBFE_SMALL_BATCH) CKC(cudaMallocHost(&h->hRes, h->resBytes));
+    }
     CKC(cudaMalloc(&h->dSlot, sizeof(uint32_t) * B * h->kpCapPerFrame));
-    CKC(cudaMalloc(&h->dN, sizeof(int) * B));
-    CKC(cudaMalloc(&h->dMono, sizeof(int) * B));
     CKC(cudaMallocHost(&h->hN, sizeof(int) * B));
     CKC(cudaMallocHost(&h->hMono, sizeof(int) * B));
     CKC(cudaMemset(h->dPyr, 0, h->pyrBytes));
@@ -424,7 +473,7 @@ static int prof_fold_oldest(orbfe_handle* h) {
     return ORBFE_OK;
 }
 
-// Enqueues the five stages for frames [frame0, frame0 + batch) of the arenas; dImages = first of those frames.
+// Enqueues the five stages for frames [frame0, frame0 + batch) of the arenas on h->cur; dImages = first of those frames.
 static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int W, int H, long long stride,
                            long long frameStride, int lap0, int lap1) {
     cudaError_t e;
@@ -432,19 +481,117 @@ static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int frame0, 
     if (h->profiling) {
         if (h->profCount == ORBFE_PROF_RING) { int st = prof_fold_oldest(h); if (st != ORBFE_OK) return st; }
         ev = h->profEv[(h->profHead + h->profCount) % ORBFE_PROF_RING];
-        CK(cudaEventRecord(ev[0], h->stream));
+        CK(cudaEventRecord(ev[0], h->cur));
     }
     if ((e = orbfe_launch_pyramid(h, dImages, frame0, batch, W, H, stride, frameStride)) != cudaSuccess) return cuda_fail(e, "pyramid");
-    if (ev) CK(cudaEventRecord(ev[1], h->stream));
+    if (ev) CK(cudaEventRecord(ev[1], h->cur));
     if ((e = orbfe_launch_fast(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "fast");
-    if (ev) CK(cudaEventRecord(ev[2], h->stream));
+    if (ev) CK(cudaEventRecord(ev[2], h->cur));
     if ((e = orbfe_launch_octree(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "octree");
-    if (ev) CK(cudaEventRecord(ev[3], h->stream));
+    if (ev) CK(cudaEventRecord(ev[3], h->cur));
     if ((e = orbfe_launch_assemble(h, frame0, batch, lap0, lap1)) != cudaSuccess) return cuda_fail(e, "assemble");
-    if (ev) CK(cudaEventRecord(ev[4], h->stream));
+    if (ev) CK(cudaEventRecord(ev[4], h->cur));
     if ((e = orbfe_launch_describe(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "describe");
-    if (ev) { CK(cudaEventRecord(ev[5], h->stream)); h->profCount++; }
+    if (ev) { CK(cudaEventRecord(ev[5], h->cur)); h->profCount++; }
     h->lastBatch = std::max(h->lastBatch, frame0 + batch);
+    return ORBFE_OK;
+}
+
+// The device-resident pipeline.  A batch is cut into chunks of about h->devChunk frames and every chunk runs all five
+// stages before the next one starts on its stream: the chunk's pyramid (1.7 MB per 752x480 frame) and its blurred copy
+// are still in the 126 MB L2 when FAST, the blur and the descriptors read them, instead of making one HBM round trip per
+// stage as a whole-batch launch does.  Chunks go round-robin over h->devStreams compute streams, so the narrow launches
+// of one chunk (small pyramid levels, one quadtree CTA per level) run under the wide launches of its neighbours.  The
+// side streams fork from and join back into the handle's public stream: callers see one ordered stream.  With stage
+// profiling on, everything stays on the public stream (events between stages need a single timeline).
+static int run_device_pipeline(orbfe_handle* h, const uint8_t* dImages, int batch, int W, int H, long long stride,
+                               long long frameStride, int lap0, int lap1) {
+    const int want = std::max(1, h->devChunk);
+    const int nchunks = (batch + want - 1) / want;
+    const int chunk = (batch + nchunks - 1) / nchunks;     // even chunks
+    const int ns = h->profiling ? 1 : std::max(1, std::min(h->devStreams, nchunks));
+    if (ns > 1) {
+        CK(cudaEventRecord(h->evFork, h->stream));
+        for (int i = 1; i < ns; ++i) CK(cudaStreamWaitEvent(h->sComp[i], h->evFork, 0));
+    }
+    int st = ORBFE_OK;
+    for (int c = 0, f0 = 0; f0 < batch && st == ORBFE_OK; ++c, f0 += chunk) {
+        h->cur = h->sComp[c % ns];
+        st = enqueue_extract(h, dImages + (long long)f0 * frameStride, f0, std::min(chunk, batch - f0), W, H, stride, frameStride, lap0, lap1);
+    }
+    h->cur = h->stream;
+    if (ns > 1)     // join even after an error: a capture must see every forked stream come back
+        for (int i = 1; i < ns; ++i) {
+            CK(cudaEventRecord(h->evJoin[i], h->sComp[i]));
+            CK(cudaStreamWaitEvent(h->stream, h->evJoin[i], 0));
+        }
+    return st;
+}
+
+static void drop_graphs(orbfe_handle* h) {
+    for (int i = 0; i < ORBFE_GRAPH_SLOTS; ++i) {
+        if (h->graphs[i].exec) cudaGraphExecDestroy(h->graphs[i].exec);
+        memset(&h->graphs[i], 0, sizeof(h->graphs[i]));
+    }
+}
+
+// run_device_pipeline through a CUDA graph.  The first call with a given argument set runs eagerly (it also sets the
+// per-device kernel attributes), the second one is captured (all chunks, all compute streams) and instantiated, later ones
+// are a single cudaGraphLaunch on the public stream.  Keyed by the device image pointer and every argument that reaches a
+// kernel; configure_shape drops the cache when the image shape changes.
+static int device_pipeline(orbfe_handle* h, const uint8_t* dImages, int batch, int W, int H, long long stride,
+                           long long frameStride, int lap0, int lap1) {
+    h->lastBatch = 0;
+    if (!h->useGraphs || h->profiling) return run_device_pipeline(h, dImages, batch, W, H, stride, frameStride, lap0, lap1);
+    OrbfeGraphSlot* slot = nullptr;
+    OrbfeGraphSlot* lru = &h->graphs[0];
+    for (int i = 0; i < ORBFE_GRAPH_SLOTS; ++i) {
+        OrbfeGraphSlot& g = h->graphs[i];
+        if (g.seen && g.images == dImages && g.batch == batch && g.W == W && g.H == H && g.lap0 == lap0 && g.lap1 == lap1 &&
+            g.format == h->inFormat && g.stride == stride && g.frameStride == frameStride) { slot = &g; break; }
+        if (g.lastUse < lru->lastUse) lru = &g;
+    }
+    ++h->graphClock;
+    if (slot && slot->exec) {
+        slot->lastUse = h->graphClock;
+        CK(cudaGraphLaunch(slot->exec, h->stream));
+        h->launches += slot->kernels;
+        h->graphLaunches++;
+        h->lastBatch = batch;
+        return ORBFE_OK;
+    }
+    if (!slot) {
+        if (lru->exec) cudaGraphExecDestroy(lru->exec);
+        memset(lru, 0, sizeof(*lru));
+        lru->images = dImages; lru->batch = batch; lru->W = W; lru->H = H; lru->lap0 = lap0; lru->lap1 = lap1;
+        lru->format = h->inFormat; lru->stride = stride; lru->frameStride = frameStride; lru->seen = 1;
+        lru->lastUse = h->graphClock;
+        return run_device_pipeline(h, dImages, batch, W, H, stride, frameStride, lap0, lap1);
+    }
+    slot->lastUse = h->graphClock;
+    if (slot->seen < 0) return run_device_pipeline(h, dImages, batch, W, H, stride, frameStride, lap0, lap1);   // capture failed before
+    const long long l0 = h->launches;
+    cudaGraph_t graph = nullptr;
+    cudaError_t e = cudaStreamBeginCapture(h->stream, cudaStreamCaptureModeRelaxed);
+    int st = ORBFE_OK;
+    if (e == cudaSuccess) {
+        st = run_device_pipeline(h, dImages, batch, W, H, stride, frameStride, lap0, lap1);
+        e = cudaStreamEndCapture(h->stream, &graph);
+    }
+    if (e == cudaSuccess && st == ORBFE_OK) e = cudaGraphInstantiate(&slot->exec, graph, 0);
+    if (graph) cudaGraphDestroy(graph);
+    if (e != cudaSuccess || st != ORBFE_OK) {          // nothing ran: fall back to the eager pipeline for this argument set
+        cudaGetLastError();
+        slot->exec = nullptr;
+        slot->seen = -1;
+        h->launches = l0;
+        if (st != ORBFE_OK) return st;
+        return run_device_pipeline(h, dImages, batch, W, H, stride, frameStride, lap0, lap1);
+    }
+    slot->kernels = h->launches - l0;
+    CK(cudaGraphLaunch(slot->exec, h->stream));
+    h->graphLaunches++;
+    h->lastBatch = batch;
     return ORBFE_OK;
 }
 
@@ -502,11 +649,11 @@ extern "C" int orbfe_extract_batch_device(orbfe_handle* h, const uint8_t* d_imag
     if (!h) return ORBFE_ERR_BAD_ARGUMENT;
     if (!d_images || width <= 0 || height <= 0 || batch <= 0) return ORBFE_ERR_EMPTY_IMAGE;
     if (stride < (ptrdiff_t)width * format_bpp(h->inFormat) || batch > h->p.max_batch) return batch > h->p.max_batch ? ORBFE_ERR_TOO_LARGE : ORBFE_ERR_BAD_ARGUMENT;
+    if (batch > 1 && frame_stride < stride * (ptrdiff_t)height) return ORBFE_ERR_BAD_ARGUMENT;
     CK(cudaSetDevice(h->device));
     int st = configure_shape(h, width, height);
     if (st != ORBFE_OK) return st;
-    h->lastBatch = 0;
-    return enqueue_extract(h, d_images, 0, batch, width, height, stride, frame_stride, lap0, lap1);
+    return device_pipeline(h, d_images, batch, width, height, stride, frame_stride, lap0, lap1);
 }
 
 extern "C" int orbfe_fetch_results(orbfe_handle* h, int batch, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n_out,
@@ -543,6 +690,46 @@ extern "C" int orbfe_fetch_results(orbfe_handle* h, int batch, orbfe_keypoint* k
     return ORBFE_OK;
 }
 
+// The drop-in call sizes (one image, or the two eyes of a stereo frame): one H2D copy, one graph launch, ONE D2H copy of
+// the whole result arena into its pinned mirror, one synchronise; the rows go to the caller's buffers by memcpy.
+static int extract_small(orbfe_handle* h, const uint8_t* images, int batch, int width, int height, ptrdiff_t stride,
+                         ptrdiff_t frame_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap, int* n_out,
+                         int* mono_out) {
+    const ptrdiff_t rowBytes = (ptrdiff_t)width * format_bpp(h->inFormat);
+    const size_t fbytes = (size_t)rowBytes * height;
+    if (stride == rowBytes && (batch == 1 || frame_stride == (ptrdiff_t)fbytes)) {
+        CK(cudaMemcpyAsync(h->dIn, images, fbytes * batch, cudaMemcpyHostToDevice, h->stream));
+    } else {
+        for (int b = 0; b < batch; ++b)
+            CK(cudaMemcpy2DAsync(h->dIn + b * fbytes, rowBytes, images + (size_t)b * frame_stride, stride, rowBytes, height,
+                                 cudaMemcpyHostToDevice, h->stream));
+    }
+    int st = device_pipeline(h, h->dIn, batch, width, height, rowBytes, (long long)fbytes, lap0, lap1);
+    if (st != ORBFE_OK) { cudaStreamSynchronize(h->stream); return st; }
+    const int kpf = h->kpPerFrame, B = h->p.max_batch;
+    const size_t kpsBytes = sizeof(orbfe_keypoint) * (size_t)batch * kpf, descBytes = (size_t)32 * batch * kpf;
+    if (batch == B) {
+        CK(cudaMemcpyAsync(h->hRes, h->dRes, h->resDescOff + descBytes, cudaMemcpyDeviceToHost, h->stream));
+    } else {
+        CK(cudaMemcpyAsync(h->hRes, h->dRes, 2 * sizeof(int) * B, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(h->hRes + h->resKpsOff, h->dRes + h->resKpsOff, kpsBytes, cudaMemcpyDeviceToHost, h->stream));
+        CK(cudaMemcpyAsync(h->hRes + h->resDescOff, h->dRes + h->resDescOff, descBytes, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    const int* hn = reinterpret_cast<const int*>(h->hRes);
+    const int* hm = hn + B;
+    for (int b = 0; b < batch; ++b) {
+        n_out[b] = hn[b];
+        if (mono_out) mono_out[b] = hm[b];
+        if (hn[b] > cap) return ORBFE_ERR_CAPACITY;
+    }
+    for (int b = 0; b < batch; ++b) {
+        memcpy(kps + (size_t)b * cap, h->hRes + h->resKpsOff + sizeof(orbfe_keypoint) * (size_t)b * kpf, sizeof(orbfe_keypoint) * (size_t)hn[b]);
+        memcpy(desc + (size_t)b * cap * 32, h->hRes + h->resDescOff + (size_t)32 * b * kpf, (size_t)32 * hn[b]);
+    }
+    return ORBFE_OK;
+}
+
 extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int batch, int width, int height, ptrdiff_t stride,
                                    ptrdiff_t frame_stride, int lap0, int lap1, orbfe_keypoint* kps, uint8_t* desc, int cap,
                                    int* n_out, int* mono_out) {
@@ -551,15 +738,19 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
     const int bpp = format_bpp(h->inFormat);
     const ptrdiff_t rowBytes = (ptrdiff_t)width * bpp;
     if (stride < rowBytes) return ORBFE_ERR_BAD_ARGUMENT;
+    if (batch > 1 && frame_stride < stride * (ptrdiff_t)height) return ORBFE_ERR_BAD_ARGUMENT;
     if (batch > h->p.max_batch || width > h->p.max_width || height > h->p.max_height) return ORBFE_ERR_TOO_LARGE;
     CK(cudaSetDevice(h->device));
     int st = configure_shape(h, width, height);
     if (st != ORBFE_OK) return st;
     if (!kps || !desc || !n_out) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->hRes) return extract_small(h, images, batch, width, height, stride, frame_stride, lap0, lap1, kps, desc, cap, n_out, mono_out);
     // Chunked pipeline: the H2D copy of chunk k+1 (copy-in stream) overlaps the kernels of chunk k (main
     // stream) and the D2H copy of chunk k-1's results (copy-out stream).  Frames are staged densely
     // (row stride = width) in the input arena.
-    static const int pipeChunk = [] { const char* e = getenv("ORBFE_PIPE_CHUNK"); int v = e ? atoi(e) : 0; return v > 0 ? v : ORBFE_PIPE_CHUNK; }();
+    static const int pipeChunkEnv = [] { const char* e = getenv("ORBFE_PIPE_CHUNK"); int v = e ? atoi(e) : 0; return v > 0 ? v : ORBFE_PIPE_CHUNK; }();
+    int pipeChunk = pipeChunkEnv;
+    while ((batch + pipeChunk - 1) / pipeChunk + 2 > ORBFE_PIPE_MAX_CHUNKS) pipeChunk *= 2;    // very long batches: larger chunks, never a refusal
     // chunk boundaries: a short first chunk (its copy-in is the only one nothing overlaps), then full chunks
     int bounds[ORBFE_PIPE_MAX_CHUNKS + 1];
     int nchunks = 0;
@@ -570,51 +761,65 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
         int f = std::min(pipeChunk / 4 > 0 ? pipeChunk / 4 : 1, batch);
         bounds[++nchunks] = f;
         while (f < batch) {
-            if (nchunks >= ORBFE_PIPE_MAX_CHUNKS) return ORBFE_ERR_TOO_LARGE;
-            f = batch - f <= pipeChunk + pipeChunk / 2 ? batch : f + pipeChunk;
+            f = (batch - f <= pipeChunk + pipeChunk / 2 || nchunks + 1 >= ORBFE_PIPE_MAX_CHUNKS) ? batch : f + pipeChunk;
             bounds[++nchunks] = f;
         }
     }
     const int kpf = h->kpPerFrame;
     const size_t fbytes = (size_t)rowBytes * height;
     h->lastBatch = 0;
-    cudaStream_t mainStream = h->stream;
-    CK(cudaEventRecord(h->evPipe[0][0], h->stream));          // copy-in / the second compute stream must not overtake earlier work
-    CK(cudaStreamWaitEvent(h->sIn, h->evPipe[0][0], 0));
-    CK(cudaStreamWaitEvent(h->sAlt, h->evPipe[0][0], 0));
+    cudaStream_t sAlt = h->sComp[1];
+    // an error in the middle must not return while copies into the caller's buffers are still in flight
+    auto fail = [&](int code) {
+        h->cur = h->stream;
+        cudaStreamSynchronize(h->sIn); cudaStreamSynchronize(sAlt); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->sOut);
+        return code;
+    };
+#define CKP(call)                                                   \
+    do {                                                            \
+        cudaError_t e_ = (call);                                    \
+        if (e_ != cudaSuccess) return fail(cuda_fail(e_, #call));   \
+    } while (0)
+    CKP(cudaEventRecord(h->evPipe[0][0], h->stream));          // copy-in / the second compute stream must not overtake earlier work
+    CKP(cudaStreamWaitEvent(h->sIn, h->evPipe[0][0], 0));
+    CKP(cudaStreamWaitEvent(sAlt, h->evPipe[0][0], 0));
     for (int c = 0; c < nchunks; ++c) {
         const int f0 = bounds[c], nb = bounds[c + 1] - f0;
         if (stride == rowBytes && frame_stride == (ptrdiff_t)fbytes) {
-            CK(cudaMemcpyAsync(h->dIn + f0 * fbytes, images + f0 * fbytes, fbytes * nb, cudaMemcpyHostToDevice, h->sIn));
+            CKP(cudaMemcpyAsync(h->dIn + f0 * fbytes, images + f0 * fbytes, fbytes * nb, cudaMemcpyHostToDevice, h->sIn));
         } else {
             for (int b = f0; b < f0 + nb; ++b)
-                CK(cudaMemcpy2DAsync(h->dIn + b * fbytes, rowBytes, images + (size_t)b * frame_stride, stride, rowBytes, height,
-                                     cudaMemcpyHostToDevice, h->sIn));
+                CKP(cudaMemcpy2DAsync(h->dIn + b * fbytes, rowBytes, images + (size_t)b * frame_stride, stride, rowBytes, height,
+                                      cudaMemcpyHostToDevice, h->sIn));
         }
-        CK(cudaEventRecord(h->evPipe[c][1], h->sIn));
+        CKP(cudaEventRecord(h->evPipe[c][1], h->sIn));
         // chunks alternate between two compute streams, so the latency-bound stages of one chunk (small
         // pyramid levels, quadtree) run under the wide stages of its neighbour
-        cudaStream_t compute = (c & 1) ? h->sAlt : mainStream;
-        CK(cudaStreamWaitEvent(compute, h->evPipe[c][1], 0));
-        h->stream = compute;
+        cudaStream_t compute = (c & 1) ? sAlt : h->stream;
+        CKP(cudaStreamWaitEvent(compute, h->evPipe[c][1], 0));
+        h->cur = compute;
         st = enqueue_extract(h, h->dIn + f0 * fbytes, f0, nb, width, height, rowBytes, (long long)fbytes, lap0, lap1);
-        h->stream = mainStream;
-        if (st != ORBFE_OK) return st;
-        CK(cudaEventRecord(h->evPipe[c][2], compute));
-        CK(cudaStreamWaitEvent(h->sOut, h->evPipe[c][2], 0));
-        CK(cudaMemcpyAsync(h->hN + f0, h->dN + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
-        CK(cudaMemcpyAsync(h->hMono + f0, h->dMono + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
+        h->cur = h->stream;
+        if (st != ORBFE_OK) return fail(st);
+        CKP(cudaEventRecord(h->evPipe[c][2], compute));
+        CKP(cudaStreamWaitEvent(h->sOut, h->evPipe[c][2], 0));
+        CKP(cudaMemcpyAsync(h->hN + f0, h->dN + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
+        CKP(cudaMemcpyAsync(h->hMono + f0, h->dMono + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
         if (cap >= kpf) {
-            CK(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, sizeof(orbfe_keypoint) * (size_t)cap, h->dKps + (size_t)f0 * kpf,
-                                 sizeof(orbfe_keypoint) * (size_t)kpf, sizeof(orbfe_keypoint) * (size_t)kpf, nb,
-                                 cudaMemcpyDeviceToHost, h->sOut));
-            CK(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, 32 * (size_t)cap, h->dDesc + (size_t)f0 * kpf * 32, 32 * (size_t)kpf,
-                                 32 * (size_t)kpf, nb, cudaMemcpyDeviceToHost, h->sOut));
+            CKP(cudaMemcpy2DAsync(kps + (size_t)f0 * cap, sizeof(orbfe_keypoint) * (size_t)cap, h->dKps + (size_t)f0 * kpf,
+                                  sizeof(orbfe_keypoint) * (size_t)kpf, sizeof(orbfe_keypoint) * (size_t)kpf, nb,
+                                  cudaMemcpyDeviceToHost, h->sOut));
+            CKP(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, 32 * (size_t)cap, h->dDesc + (size_t)f0 * kpf * 32, 32 * (size_t)kpf,
+                                  32 * (size_t)kpf, nb, cudaMemcpyDeviceToHost, h->sOut));
         }
     }
-    CK(cudaStreamSynchronize(h->sOut));
-    CK(cudaStreamSynchronize(h->sAlt));
-    CK(cudaStreamSynchronize(h->stream));
+    // the public stream ends up ordered after everything this call enqueued (device results are valid on it)
+    CKP(cudaEventRecord(h->evJoin[1], sAlt));
+    CKP(cudaStreamWaitEvent(h->stream, h->evJoin[1], 0));
+    CKP(cudaStreamSynchronize(h->sOut));
+    CKP(cudaStreamSynchronize(sAlt));
+    CKP(cudaStreamSynchronize(h->stream));
+#undef CKP
     if (cap >= kpf) {
         for (int b = 0; b < batch; ++b) { n_out[b] = h->hN[b]; if (mono_out) mono_out[b] = h->hMono[b]; }
         return ORBFE_OK;
@@ -628,6 +833,33 @@ extern "C" int orbfe_extract(orbfe_handle* h, const uint8_t* image, int width, i
     int st = orbfe_extract_batch(h, image, 1, width, height, stride, (ptrdiff_t)stride * height, lap0, lap1, kps, desc, cap, &n, &mono);
     if (n_out) *n_out = n;
     return st < 0 ? st : mono;
+}
+
+// ---- ordering against other streams (the matchers and the vocabulary own their streams) ---------------------------
+extern "C" int orbfe_stream_wait_extractor(orbfe_handle* h, void* stream) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    CK(cudaEventRecord(h->evOrder, h->stream));
+    CK(cudaStreamWaitEvent((cudaStream_t)stream, h->evOrder, 0));
+    return ORBFE_OK;
+}
+extern "C" int orbfe_extractor_wait_stream(orbfe_handle* h, void* stream) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    CK(cudaEventRecord(h->evOrder, (cudaStream_t)stream));
+    CK(cudaStreamWaitEvent(h->stream, h->evOrder, 0));
+    return ORBFE_OK;
+}
+extern "C" long long orbfe_graph_launch_count(const orbfe_handle* h) { return h ? h->graphLaunches : 0; }
+extern "C" int orbfe_set_pipeline(orbfe_handle* h, int chunk_frames, int compute_streams, int use_graphs) {
+    if (!h) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    if (chunk_frames > 0) h->devChunk = chunk_frames;
+    if (compute_streams > 0) h->devStreams = std::min(compute_streams, ORBFE_MAX_COMPUTE_STREAMS);
+    if (use_graphs >= 0) h->useGraphs = use_graphs != 0;
+    drop_graphs(h);
+    return ORBFE_OK;
 }
 
 extern "C" int orbfe_device_results(orbfe_handle* h, const orbfe_keypoint** d_kps, const uint8_t** d_desc, const int** d_n,

@@ -17,7 +17,12 @@
 #define ORBFE_MIN_BORDER 16    // EDGE_THRESHOLD - 3, ORBextractor.cc:771
 #define ORBFE_MAX_NODES 2048
 #define ORBFE_PIPE_CHUNK 64        // frames per chunk of the pipelined host path (orbfe_extract_batch)
-#define ORBFE_PIPE_MAX_CHUNKS 64   // per-level quota ceiling of the on-chip quadtree
+#define ORBFE_PIPE_MAX_CHUNKS 64
+#define ORBFE_MAX_COMPUTE_STREAMS 4
+#define ORBFE_GRAPH_SLOTS 4
+#define ORBFE_DEV_CHUNK 32         // frames per chunk of the device-resident pipeline: pyramid + blurred copy of a chunk stay in L2
+#define ORBFE_DEV_STREAMS 3
+#define ORBFE_SMALL_BATCH 8        // handles up to this max_batch mirror the whole result arena in pinned memory (one D2H per call)
 
 // Packed FAST candidate: x | y << 11 | response << 22, (x, y) relative to (minBorderX, minBorderY).
 #define ORBFE_CAND_X(c) ((int)((c) & 0x7FFu))
@@ -73,13 +78,28 @@ struct FastMaps {
     CUtensorMap m[ORBFE_MAX_LEVELS];
 };
 
+// One captured extraction (all chunks, all compute streams) for one set of call arguments.
+struct OrbfeGraphSlot {
+    const uint8_t* images;
+    int batch, W, H, lap0, lap1, format, seen;
+    long long stride, frameStride, lastUse;
+    cudaGraphExec_t exec;
+    long long kernels;      // kernel nodes in the graph (launch accounting)
+};
+
 struct orbfe_handle {
     orbfe_params p;
     int device;
-    cudaStream_t stream;
+    cudaStream_t stream;                             // the handle's public stream: every call is ordered on it
+    cudaStream_t cur;                                // stream the launchers enqueue on (stream or one of the side streams)
     cudaStream_t sIn, sOut;                          // copy-in / copy-out streams of the pipelined host path
-    cudaStream_t sAlt;                               // second compute stream: odd chunks of the pipelined host path
+    cudaStream_t sComp[ORBFE_MAX_COMPUTE_STREAMS];   // compute streams of the chunked pipelines; sComp[0] == stream
     cudaEvent_t evPipe[ORBFE_PIPE_MAX_CHUNKS][3];    // per chunk: [0][0] fence, [c][1] frames landed, [c][2] results ready
+    cudaEvent_t evFork, evJoin[ORBFE_MAX_COMPUTE_STREAMS], evOrder;
+    int devChunk, devStreams;                        // device-resident pipeline: frames per chunk, compute streams used
+    int useGraphs;
+    OrbfeGraphSlot graphs[ORBFE_GRAPH_SLOTS];
+    long long graphLaunches, graphClock;
     long long launches;
     // reference tables (ORBextractor.cc:413-444)
     float scale[ORBFE_MAX_LEVELS], invScale[ORBFE_MAX_LEVELS], sigma2[ORBFE_MAX_LEVELS], invSigma2[ORBFE_MAX_LEVELS];
@@ -113,6 +133,9 @@ struct orbfe_handle {
     ResizeTap* dTaps;
     ColPlan* dPlans;
     int planCap;
+    uint8_t* dRes;          // result arena: dN | dMono | dKps | dDesc, contiguous (small-batch handles fetch it with one copy)
+    uint8_t* hRes;          // pinned mirror of the result arena (max_batch <= ORBFE_SMALL_BATCH), else NULL
+    size_t resBytes, resKpsOff, resDescOff;
     orbfe_keypoint* dKps;   // [frame][kpPerFrame]
     uint8_t* dDesc;         // [frame][kpPerFrame][32]
     uint32_t* dSlot;        // [frame][kpPerFrame] : level << 28 | y << 14 | x (level coords) of the keypoint at dst slot
@@ -130,9 +153,13 @@ struct orbfe_handle {
 };
 #define ORBFE_PROF_RING 64
 
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) is a per-device setting: raises it to `bytes` for the current device if this
+// (device, kernel) pair has not been given that much yet.  Thread-safe; no-op up to 48 KB.
+cudaError_t orbfe_ensure_dyn_smem(const void* func, size_t bytes);
+
 // ---- launchers (each returns cudaGetLastError()) -------------------------------------------------
-// Every launcher processes frames [frame0, frame0 + batch) of the handle's arenas (chunked pipelining of
-// the host path); dImages points at the first of those frames.
+// Every launcher processes frames [frame0, frame0 + batch) of the handle's arenas on h->cur (chunked pipelines of
+// the host and device paths); dImages points at the first of those frames.
 cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int width, int height,
                                  long long stride, long long frameStride);
 cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch);

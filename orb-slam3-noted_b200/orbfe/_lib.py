@@ -64,6 +64,10 @@ def lib():
         "orbfe_stream": (_P, [_P]),
         "orbfe_synchronize": (_I, [_P]),
         "orbfe_launch_count": (C.c_longlong, [_P]),
+        "orbfe_graph_launch_count": (C.c_longlong, [_P]),
+        "orbfe_stream_wait_extractor": (_I, [_P, _P]),
+        "orbfe_extractor_wait_stream": (_I, [_P, _P]),
+        "orbfe_set_pipeline": (_I, [_P, _I, _I, _I]),
         "orbfe_set_profiling": (_I, [_P, _I]),
         "orbfe_set_input_format": (_I, [_P, _I]),
         "orbfe_get_stage_times": (_I, [_P, _P, C.POINTER(C.c_longlong)]),
@@ -88,7 +92,8 @@ def exported_symbols():
     return ["orbfe_create", "orbfe_destroy", "orbfe_get_tables", "orbfe_max_keypoints", "orbfe_extract",
             "orbfe_extract_batch", "orbfe_extract_batch_device", "orbfe_device_results", "orbfe_fetch_results",
             "orbfe_get_pyramid_level", "orbfe_get_candidates", "orbfe_stream", "orbfe_synchronize",
-            "orbfe_launch_count", "orbfe_set_profiling", "orbfe_set_input_format", "orbfe_get_stage_times", "orbfe_stage_name", "orbfe_strerror", "orbfe_last_cuda_error", "orbfe_version"] + list(_matcher_proto.PROTO)
+            "orbfe_launch_count", "orbfe_graph_launch_count", "orbfe_stream_wait_extractor", "orbfe_extractor_wait_stream",
+            "orbfe_set_pipeline", "orbfe_set_profiling", "orbfe_set_input_format", "orbfe_get_stage_times", "orbfe_stage_name", "orbfe_strerror", "orbfe_last_cuda_error", "orbfe_version"] + list(_matcher_proto.PROTO)
 
 
 def strerror(status):

@@ -184,6 +184,26 @@ class ORBextractor:
     def launch_count(self):
         return int(self._lib.orbfe_launch_count(self._h))
 
+    def graph_launch_count(self):
+        return int(self._lib.orbfe_graph_launch_count(self._h))
+
+    def order_consumer(self, stream):
+        """Work enqueued on `stream` (a matcher's or vocabulary's cudaStream_t) from now on waits for this extractor."""
+        st = self._lib.orbfe_stream_wait_extractor(self._h, C.c_void_p(stream))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_stream_wait_extractor")
+
+    def wait_consumer(self, stream):
+        """The next extraction waits for everything already enqueued on `stream` (it overwrites what that work reads)."""
+        st = self._lib.orbfe_extractor_wait_stream(self._h, C.c_void_p(stream))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_extractor_wait_stream")
+
+    def set_pipeline(self, chunk_frames=0, compute_streams=0, use_graphs=-1):
+        st = self._lib.orbfe_set_pipeline(self._h, int(chunk_frames), int(compute_streams), int(use_graphs))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_set_pipeline")
+
     STAGES = ("pyramid", "fast", "octree", "assemble", "describe")
 
     def set_profiling(self, enabled=True):
