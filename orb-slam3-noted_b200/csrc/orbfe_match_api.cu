@@ -195,6 +195,13 @@ static int wait_for(orbfe_matcher* m, orbfe_handle* h) {
     return ORBFE_OK;
 }
 
+// ... and the reverse: the extractor's next call (which overwrites its results and pyramid) waits for what the matcher enqueued.
+static int release_to(orbfe_matcher* m, orbfe_handle* h) {
+    CK(cudaEventRecord(m->ev, m->stream));
+    CK(cudaStreamWaitEvent(h->stream, m->ev, 0));
+    return ORBFE_OK;
+}
+
 extern "C" int orbfe_stereo_match_batch_device(orbfe_matcher* m, orbfe_handle* h, int npairs, float bf, float b, float* d_u_right,
                                                float* d_depth) {
     if (!m || !h || !d_u_right || !d_depth || npairs <= 0 || !(b > 0.f)) return ORBFE_ERR_BAD_ARGUMENT;
@@ -207,7 +214,7 @@ extern "C" int orbfe_stereo_match_batch_device(orbfe_matcher* m, orbfe_handle* h
     int* dSad = reinterpret_cast<int*>(m->dScratch);
     int* dCount = dSad + (size_t)npairs * h->kpCapPerFrame;
     CK(orbfe_launch_stereo(m->stream, h, 0, 2, h, 1, 2, npairs, bf, b, d_u_right, d_depth, dSad, dCount, h->kpCapPerFrame, &m->launches));
-    return ORBFE_OK;
+    return release_to(m, h);
 }
 
 extern "C" int orbfe_stereo_match(orbfe_matcher* m, orbfe_handle* left, int frame_l, orbfe_handle* right, int frame_r, float bf,
