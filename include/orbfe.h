@@ -198,6 +198,20 @@ int orbfe_hamming_knn2(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t
 int orbfe_hamming_knn2_batch_device(orbfe_matcher* m, const uint8_t* d_q, ptrdiff_t q_stride, const int* d_nq, int nq_max,
                                     const uint8_t* d_t, ptrdiff_t t_stride, const int* d_nt, int nt_max, int batch,
                                     int32_t* d_idx2, int32_t* d_dist2);
+/* Allocation-free form of orbfe_hamming_knn2 on DEVICE buffers.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Needs no orbfe_matcher; calls no cudaMalloc / cudaFree / allocating routine.  The kernels'
+ * scratch (per-split partial results) lives in a static device array of ORBFE_NOALLOC_SCRATCH_BYTES that every GPU loading
+ * the library holds until exit; hence the limits nq <= ORBFE_NOALLOC_MAX_QUERIES and nt <= ORBFE_NOALLOC_MAX_TRAIN
+ * (larger sizes return ORBFE_ERR_TOO_LARGE, text in orbfe_last_cuda_error()).  d_q (nq x 32), d_t (nt x 32): device
+ * descriptors; d_idx2 / d_dist2: device int32 [nq][2], same contents as orbfe_hamming_knn2.  Asynchronous on `stream`
+ * (a cudaStream_t of `device`, NULL = the default stream).  All calls share the one scratch array: calls that may overlap
+ * on the GPU (different streams without ordering between them) race; calls on one stream are safe. */
+#define ORBFE_NOALLOC_MAX_QUERIES 8192
+#define ORBFE_NOALLOC_MAX_TRAIN 65536
+#define ORBFE_NOALLOC_SCRATCH_BYTES (1u << 20)
+int orbfe_hamming_knn2_noalloc(int device, void* stream, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt, int32_t* d_idx2,
+                               int32_t* d_dist2);
 /* Frame::ComputeStereoFishEyeMatches up to the descriptor test (Frame.cc:1134-1141): 2-NN + Lowe
  * ratio (d0 < d1 * ratio in double precision, ratio = the double literal 0.7 there).  match[nq] = train index or -1.  Returns the number
  * of matches. */

@@ -137,6 +137,68 @@ cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStr
     return cudaGetLastError();
 }
 
+// ---- allocation-free 2-NN (no counterpart in the reference) -----------------
+// For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
+// the same k_knn2 / k_knn2_merge pair, with the per-split partial keys in a file-scope device array instead of the matcher's
+// growable scratch.  Every GPU that loads the library holds the array (1 MiB) until exit.  All calls share it and it keeps the
+// last call's contents; nothing in it has to start at zero (k_knn2 writes every (split, query) slot k_knn2_merge reads), so it
+// is never cleared — but two calls that overlap on the GPU (different streams, no ordering) race on it.
+#include <mutex>
+
+#include "../../include/orbfe.h"
+int orbfe_set_cuda_error(cudaError_t e, const char* what);   // orbfe_api.cu
+
+#define NOALLOC_MAX_SPLIT 16
+static __device__ __align__(256) uint2 g_knnScratch[(size_t)NOALLOC_MAX_SPLIT * ORBFE_NOALLOC_MAX_QUERIES];
+static_assert(sizeof(uint2) * NOALLOC_MAX_SPLIT * ORBFE_NOALLOC_MAX_QUERIES == ORBFE_NOALLOC_SCRATCH_BYTES, "declared scratch size");
+
+#define NOALLOC_MAX_DEVICES 64
+static std::mutex g_noallocMu;
+static uint2* g_knnScratchPtr[NOALLOC_MAX_DEVICES];    // device address of g_knnScratch on each device (the name itself is a host stand-in)
+static int g_noallocSms[NOALLOC_MAX_DEVICES];
+
+extern "C" int orbfe_hamming_knn2_noalloc(int device, void* stream, const uint8_t* d_q, int nq, const uint8_t* d_t, int nt,
+                                          int32_t* d_idx2, int32_t* d_dist2) {
+    if (device < 0 || device >= NOALLOC_MAX_DEVICES || nq < 0 || nt < 0 || (nq > 0 && (!d_q || !d_idx2 || !d_dist2)) || (nt > 0 && !d_t))
+        return ORBFE_ERR_BAD_ARGUMENT;
+    if (nq > ORBFE_NOALLOC_MAX_QUERIES || nt > ORBFE_NOALLOC_MAX_TRAIN) {
+        orbfe_set_cuda_error(cudaErrorInvalidValue, nq > ORBFE_NOALLOC_MAX_QUERIES
+                                                        ? "orbfe_hamming_knn2_noalloc: nq exceeds ORBFE_NOALLOC_MAX_QUERIES (8192), the static scratch is sized for that"
+                                                        : "orbfe_hamming_knn2_noalloc: nt exceeds ORBFE_NOALLOC_MAX_TRAIN (65536)");
+        return ORBFE_ERR_TOO_LARGE;
+    }
+    if (nq == 0) return ORBFE_OK;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) return orbfe_set_cuda_error(e, "orbfe_hamming_knn2_noalloc: cudaSetDevice");
+    uint2* scratch;
+    int sms;
+    {   // once per device, with that device current: the device address of the static array
+        std::lock_guard<std::mutex> lock(g_noallocMu);
+        if (!g_knnScratchPtr[device]) {
+            uint2* p = nullptr;
+            e = cudaGetSymbolAddress((void**)&p, g_knnScratch);
+            if (e != cudaSuccess || !p) return orbfe_set_cuda_error(e != cudaSuccess ? e : cudaErrorUnknown, "orbfe_hamming_knn2_noalloc: cudaGetSymbolAddress(g_knnScratch)");
+            int n = 0;
+            e = cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device);
+            if (e != cudaSuccess) return orbfe_set_cuda_error(e, "orbfe_hamming_knn2_noalloc: cudaDeviceGetAttribute");
+            g_noallocSms[device] = n;
+            g_knnScratchPtr[device] = p;
+        }
+        scratch = g_knnScratchPtr[device];
+        sms = g_noallocSms[device];
+    }
+    int nsplit = 1, splitLen = nt;
+    orbfe_knn2_plan(nq, nt, 1, sms, &nsplit, &splitLen);
+    if (nsplit > NOALLOC_MAX_SPLIT) {      // fewer, longer splits: the scratch holds NOALLOC_MAX_SPLIT partial results per query
+        splitLen = ((nt + NOALLOC_MAX_SPLIT - 1) / NOALLOC_MAX_SPLIT + KNN_TILE - 1) / KNN_TILE * KNN_TILE;
+        nsplit = (nt + splitLen - 1) / splitLen;
+    }
+    long long launches = 0;
+    e = orbfe_launch_knn2((cudaStream_t)stream, d_q, 0, nullptr, nq, d_t, 0, nullptr, nt, 1, nsplit, splitLen, scratch, d_idx2, d_dist2, &launches);
+    if (e != cudaSuccess) return orbfe_set_cuda_error(e, "orbfe_hamming_knn2_noalloc: launch");
+    return ORBFE_OK;
+}
+
 // Frame::UndistortKeyPoints (src/Frame.cc:730-763) = cv::undistortPoints with P = K: thread per keypoint, OpenCV's five
 // fixed-point iterations in double, every product and sum rounded separately (no FMA contraction) so the float
 // result is bit-identical to the library's.
