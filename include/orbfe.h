@@ -130,7 +130,7 @@ long long orbfe_graph_launch_count(const orbfe_handle* h);
 int orbfe_stream_wait_extractor(orbfe_handle* h, void* stream);
 int orbfe_extractor_wait_stream(orbfe_handle* h, void* stream);
 
-/* Tuning of the device-side pipeline (defaults: 32-frame chunks over 3 compute streams, CUDA graphs on).
+/* Tuning of the device-side pipeline (defaults: chunks of up to 512 frames over 2 compute streams, CUDA graphs on).
  * chunk_frames / compute_streams <= 0 and use_graphs < 0 keep the current value.  Synchronises the handle. */
 int orbfe_set_pipeline(orbfe_handle* h, int chunk_frames, int compute_streams, int use_graphs);
 
@@ -375,7 +375,10 @@ typedef struct orbfe_proj_query {
     uint8_t chi2;                  /* 1 = Fuse's reprojection gate (ORBmatcher.cc:1744-1770): skip a feature when
                                       ((u-x)^2 + (v-y)^2 [+ (ur-mvuRight)^2 if mvuRight >= 0]) * inv_level_sigma2[octave]
                                       exceeds 5.99 [7.8] */
-    uint8_t pad[2];
+    uint8_t skip_if_prev_empty;    /* skip this window when the PREVIOUS window's GetFeaturesInArea returned nothing: in
+                                      SearchByProjection(Current, Last, ...) that `continue` (:2236-2237) also skips the same
+                                      MapPoint's right-camera window */
+    uint8_t pad;
     uint8_t desc[32];              /* pMP->GetDescriptor() */
 } orbfe_proj_query;
 

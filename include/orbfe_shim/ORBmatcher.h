@@ -4,10 +4,11 @@
 // HISTO_LENGTH (include/ORBmatcher.h:35-111).  The searches come in two layers:
 //   * array layer (always available): the reference's inputs already flattened — descriptors,
 //     keypoints, a FeatureVector as CSR, MapPoint-validity masks.  This is what the tests drive.
-//   * object layer (#ifdef ORBFE_WITH_ORBSLAM3, needs the reference's Frame.h / KeyFrame.h /
-//     MapPoint.h): SearchByBoW(KeyFrame*, Frame&, ...), SearchByBoW(KeyFrame*, KeyFrame*, ...),
-//     SearchForTriangulation_(...) with the reference's signatures; they flatten the objects and
-//     call the array layer.  Not compiled in this repository (ORB-SLAM3's headers need OpenCV/Eigen).
+//   * object layer (#ifdef ORBFE_WITH_ORBSLAM3, needs the reference's Frame.h / KeyFrame.h / MapPoint.h): every
+//     Search* / Fuse member of the reference's class with the reference's signature (ORBmatcherObjects.h); they flatten
+//     the objects, call the C ABI and write the results back into the objects.  Compiled and run in this repository
+//     against the data-holder stand-ins of oracle/refshim (tests/test_shim_objects_gpu.py: every method equals the
+//     reference's own ORBmatcher.cc on the same objects).
 #ifndef ORBMATCHER_H
 #define ORBMATCHER_H
 
@@ -25,9 +26,12 @@
 #include "../orbfe.h"
 
 #ifdef ORBFE_WITH_ORBSLAM3
+#include <set>
+#ifndef ORBFE_ORBSLAM3_TYPES_PROVIDED     // tests force-include stand-ins for these three (they pull in Eigen, g2o, boost)
 #include "Frame.h"
 #include "KeyFrame.h"
 #include "MapPoint.h"
+#endif
 #endif
 
 namespace ORB_SLAM3 {
@@ -242,46 +246,42 @@ public:
     }
 
 #ifdef ORBFE_WITH_ORBSLAM3
-    // ---- object layer: the reference's signatures ------------------------------------------------------
-    int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches) {
-        const std::vector<MapPoint*> vpMapPointsKF = pKF->GetMapPointMatches();
-        std::vector<uint8_t> mask(vpMapPointsKF.size());
-        for (size_t i = 0; i < mask.size(); ++i) mask[i] = vpMapPointsKF[i] && !vpMapPointsKF[i]->isBad();
-        orbfe_shim::FeatureVectorCsr fvKF(pKF->mFeatVec), fvF(F.mFeatVec);
-        orbfe_shim::Side a, b;
-        a.desc = pKF->mDescriptors.data; a.n = pKF->mDescriptors.rows; a.fv = &fvKF; a.mask = mask.data(); a.kps = pKF->mvKeysUn.data();
-        b.desc = F.mDescriptors.data; b.n = F.mDescriptors.rows; b.fv = &fvF; b.kps = F.mvKeys.data();
-        std::vector<int32_t> m;
-        const int n = SearchByBoWArrays(a, b, F.Nleft, m);
-        vpMapPointMatches.assign(F.N, static_cast<MapPoint*>(NULL));
-        for (int j = 0; j < (int)m.size(); ++j)
-            if (m[j] >= 0) vpMapPointMatches[j] = vpMapPointsKF[m[j]];
-        return n;
-    }
-    int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12) {
-        const std::vector<MapPoint*> mp1 = pKF1->GetMapPointMatches(), mp2 = pKF2->GetMapPointMatches();
-        std::vector<uint8_t> k1(mp1.size()), k2(mp2.size());
-        for (size_t i = 0; i < k1.size(); ++i) k1[i] = mp1[i] && !mp1[i]->isBad();
-        for (size_t i = 0; i < k2.size(); ++i) k2[i] = mp2[i] && !mp2[i]->isBad();
-        orbfe_shim::FeatureVectorCsr fv1(pKF1->mFeatVec), fv2(pKF2->mFeatVec);
-        orbfe_shim::Side a, b;
-        a.desc = pKF1->mDescriptors.data; a.n = pKF1->mDescriptors.rows; a.fv = &fv1; a.mask = k1.data(); a.kps = pKF1->mvKeysUn.data();
-        b.desc = pKF2->mDescriptors.data; b.n = pKF2->mDescriptors.rows; b.fv = &fv2; b.mask = k2.data(); b.kps = pKF2->mvKeysUn.data();
-        std::vector<int32_t> m;
-        const int n = SearchByBoWArrays(a, b, m);
-        vpMatches12.assign(mp1.size(), static_cast<MapPoint*>(NULL));
-        for (size_t i = 0; i < m.size(); ++i)
-            if (m[i] >= 0) vpMatches12[i] = mp2[m[i]];
-        return n;
-    }
+    // ---- object layer: the reference's signatures (include/ORBmatcher.h:44-91), defined in ORBmatcherObjects.h.  Each one
+    // flattens the objects it is given into the arrays of the C ABI, runs the search on the GPU and writes the results
+    // back into the objects exactly where the reference does.
+    int SearchByProjection(Frame& F, const std::vector<MapPoint*>& vpMapPoints, const float th = 3, const bool bFarPoints = false,
+                           const float thFarPoints = 50.0f);                                                         // :46
+    int SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, const float th, const bool bMono);          // :50
+    int SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, const std::set<MapPoint*>& sAlreadyFound, const float th,
+                           const int ORBdist);                                                                       // :54
+    int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, std::vector<MapPoint*>& vpMatched,
+                           int th, float ratioHamming = 1.0);                                                        // :58
+    int SearchByProjection(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, const std::vector<KeyFrame*>& vpPointsKFs,
+                           std::vector<MapPoint*>& vpMatched, std::vector<KeyFrame*>& vpMatchedKF, int th, float ratioHamming = 1.0);   // :62
+    int SearchByBoW(KeyFrame* pKF, Frame& F, std::vector<MapPoint*>& vpMapPointMatches);                             // :67
+    int SearchByBoW(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12);                            // :68
     int SearchForInitialization(Frame& F1, Frame& F2, std::vector<cv::Point2f>& vbPrevMatched, std::vector<int>& vnMatches12,
-                                int windowSize = 10) {
-        orbfe_grid_frame G = {};
-        G.kps = reinterpret_cast<const orbfe_keypoint*>(F2.mvKeysUn.data()); G.desc = F2.mDescriptors.data; G.n = (int)F2.mvKeysUn.size();
-        G.nleft = -1;
-        G.min_x = F2.mnMinX; G.min_y = F2.mnMinY; G.grid_w_inv = F2.mfGridElementWidthInv; G.grid_h_inv = F2.mfGridElementHeightInv;
-        return SearchForInitializationArrays(F1.mvKeysUn, F1.mDescriptors, G, vbPrevMatched, vnMatches12, windowSize);
-    }
+                                int windowSize = 10);                                                                // :71
+    int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                               const bool bOnlyStereo, const bool bCoarse = false);                                  // :74
+    int SearchForTriangulation_(KeyFrame* pKF1, KeyFrame* pKF2, cv::Matx33f F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                                const bool bOnlyStereo, const bool bCoarse = false);                                 // :77
+    int SearchForTriangulation(KeyFrame* pKF1, KeyFrame* pKF2, cv::Mat F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                               const bool bOnlyStereo, std::vector<cv::Mat>& vMatchedPoints);                        // :80
+    int SearchBySim3(KeyFrame* pKF1, KeyFrame* pKF2, std::vector<MapPoint*>& vpMatches12, const float& s12, const cv::Mat& R12,
+                     const cv::Mat& t12, const float th);                                                            // :85
+    int Fuse(KeyFrame* pKF, const std::vector<MapPoint*>& vpMapPoints, const float th = 3.0, const bool bRight = false);   // :88
+    int Fuse(KeyFrame* pKF, cv::Mat Scw, const std::vector<MapPoint*>& vpPoints, float th, std::vector<MapPoint*>& vpReplacePoint);   // :91
+
+protected:
+    float RadiusByViewingCos(const float& viewCos) { return viewCos > 0.998 ? 2.5f : 4.0f; }                        // ORBmatcher.cc:238-244
+    void ComputeThreeMaxima(std::vector<int>* histo, const int L, int& ind1, int& ind2, int& ind3);                  // :2515-2556
+    int triangulationSearch(KeyFrame* pKF1, KeyFrame* pKF2, const cv::Matx33f& F12, std::vector<std::pair<size_t, size_t> >& vMatchedPairs,
+                            bool bOnlyStereo, bool bCoarse, std::vector<cv::Mat>* vMatchedPoints);
+    int sim3Projection(KeyFrame* pKF, const cv::Mat& Scw, const std::vector<MapPoint*>& vpPoints, const std::vector<KeyFrame*>* vpPointsKFs,
+                       std::vector<MapPoint*>& vpMatched, std::vector<KeyFrame*>* vpMatchedKF, int th, float ratioHamming);
+
+public:
 #endif
 
     static const int TH_LOW = ORBFE_TH_LOW;
@@ -301,5 +301,9 @@ private:
 };
 
 }  // namespace ORB_SLAM3
+
+#ifdef ORBFE_WITH_ORBSLAM3
+#include "ORBmatcherObjects.h"
+#endif
 
 #endif  // ORBMATCHER_H

@@ -55,15 +55,17 @@ int searchByProjection(const GridFrame& F, const ProjQuery* q, int nq, const Pro
     };
     std::vector<int> rotHist[HISTO_LENGTH];
     std::vector<int> cand;
-    bool prevRatioRejected = false;
+    bool prevRatioRejected = false, prevEmpty = true;
     for (int i = 0; i < nq; ++i) {
         choice[i] = -1;
         const ProjQuery& Q = q[i];
-        const bool skip = Q.skipIfPrevRatioRejected && prevRatioRejected;
+        const bool skip = (Q.skipIfPrevRatioRejected && prevRatioRejected) || (Q.skipIfPrevEmpty && prevEmpty);
         prevRatioRejected = false;
-        if (!Q.valid || skip) continue;
+        prevEmpty = true;                 // of an invalid window: the reference `continue`d before searching
+        if (!Q.valid) continue;
         grid.featuresInArea(Q.u, Q.v, Q.r, Q.minLevel, Q.maxLevel, Q.right != 0, cand);
-        if (cand.empty()) continue;
+        prevEmpty = cand.empty();         // SearchByProjection(Current, Last) :2236-2237 leaves the MapPoint, right camera included
+        if (skip || cand.empty()) continue;
         int bestDist = 256, bestLevel = -1, bestDist2 = 256, bestLevel2 = -1, bestIdx = -1;
         for (int idx : cand) {
             if (isBlocked(idx)) continue;

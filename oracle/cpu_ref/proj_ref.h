@@ -45,7 +45,8 @@ struct ProjQuery {                // one GetFeaturesInArea window + what is matc
     uint8_t valid;                // 0: skipped before the window search (not in view, bad, behind the camera ...)
     uint8_t skipIfPrevRatioRejected;   // :135: the `continue` after a failed ratio test also skips the same MapPoint's right-camera search
     uint8_t chi2;                 // Fuse's per-candidate reprojection gate (ORBmatcher.cc:1744-1770)
-    uint8_t pad[2];
+    uint8_t skipIfPrevEmpty;      // :2236-2237: an empty left window skips the same MapPoint's right-camera window too
+    uint8_t pad;
     uint8_t desc[32];             // pMP->GetDescriptor()
 };
 #pragma pack(pop)

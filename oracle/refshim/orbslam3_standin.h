@@ -35,6 +35,12 @@ class MapPoint;
 class GeometricCamera {
 public:
     virtual ~GeometricCamera() {}
+    // include/CameraModels/GeometricCamera.h:86-93: camera kind and raw parameters (read by the orbfe shim to pick the pinhole
+    // or the Kannala-Brandt search); the stand-in only has pinhole cameras
+    const unsigned int CAM_PINHOLE = 0;
+    const unsigned int CAM_FISHEYE = 1;
+    virtual unsigned int GetType() { return CAM_PINHOLE; }
+    virtual float getParameter(const int i) { return 0.f; }
     virtual cv::Point2f project(const cv::Point3f& p3D) = 0;
     virtual cv::Point2f project(const cv::Matx31f& m3D) = 0;
     virtual cv::Point2f project(const cv::Mat& m3D) = 0;
@@ -250,6 +256,13 @@ public:
     }
     // poses: src/KeyFrame.cc:126-170, :1101-1170.  Float blocks of Tcw; camera centre Ow = -Rcw^T tcw.
     cv::Mat GetPose() { return Tcw.clone(); }
+    cv::Mat GetPoseInverse() {                                       // src/KeyFrame.cc:160-164 (Twc), from Rwc = Rcw^T and Ow
+        cv::Mat Twc = cv::Mat::zeros(4, 4, CV_32F);
+        const cv::Mat Rwc = GetRotation().t(), Ow = GetCameraCenter();
+        for (int i = 0; i < 3; ++i) { for (int j = 0; j < 3; ++j) Twc.at<float>(i, j) = Rwc.at<float>(i, j); Twc.at<float>(i, 3) = Ow.at<float>(i); }
+        Twc.at<float>(3, 3) = 1.f;
+        return Twc;
+    }
     cv::Mat GetRotation() { return Tcw.rowRange(0, 3).colRange(0, 3).clone(); }
     cv::Mat GetTranslation() { return Tcw.rowRange(0, 3).col(3).clone(); }
     cv::Mat GetCameraCenter() { return -GetRotation().t() * GetTranslation(); }

@@ -93,4 +93,6 @@ def build_reference(force=False):
     if not os.path.exists(REFERENCE_SRC):
         return [p for p in REF_LIBS if os.path.exists(p)]
     _run(["make", "-C", os.path.join(ROOT, "oracle"), "ref"] + (["-B"] if force else []))
+    # the shim's ORBmatcher object layer behind the reference wrappers' C entry points (test artefact; links liborbfe.so)
+    _run(["make", "-C", os.path.join(ROOT, "oracle"), "shim"] + (["-B"] if force else []))
     return REF_LIBS

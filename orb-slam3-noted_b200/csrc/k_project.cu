@@ -68,7 +68,7 @@ struct AlwaysVisible { __device__ __forceinline__ bool operator()(int, int) cons
 // vis(idx, dist): evaluated after the distance, false = the candidate is skipped (SearchForInitialization :744).
 template <class F, class V = AlwaysVisible>
 __device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lane, int nlanes, const int* __restrict__ blockedAt, F f,
-                                            V vis = V()) {
+                                            V vis = V(), int* areaHits = nullptr) {
     const ProjQueryDev& Q = P.q[i];
     const Window w = window_cells(P, Q);
     if (w.minCX > w.maxCX) return;
@@ -93,6 +93,7 @@ __device__ __forceinline__ void scan_window(const ProjProblem& P, int i, int lan
                 if (maxLevel >= 0 && oct > maxLevel) continue;
             }
             if (!(fabsf(__fsub_rn(kp.x, x)) < r && fabsf(__fsub_rn(kp.y, y)) < r)) continue;
+            if (areaHits) ++*areaHits;          // the feature is in GetFeaturesInArea's result, whatever the loop does with it
             if (blockedAt ? blockedAt[idx] < i : (P.blocked && P.blocked[idx])) continue;
             if (checkUr) {
                 const float ur = P.uRight[idx];
@@ -190,17 +191,23 @@ __global__ void __launch_bounds__(256) k_proj_candidates(const ProjProblem* __re
     const int i = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (i >= P.nq) return;
     unsigned long long* list = P.cand + (long long)i * PROJ_K;
+    int* areaEmpty = P.scratch + P.n + 4 * P.nq;                    // nq flags: GetFeaturesInArea returned nothing
     if (!P.q[i].valid) {
         if (lane < PROJ_K) list[lane] = ~0ull;
-        if (lane == 0) P.limit[i] = ~0ull;
+        if (lane == 0) { P.limit[i] = ~0ull; areaEmpty[i] = 1; }
         return;
     }
     unsigned long long k1 = ~0ull, k2 = ~0ull, dropped = ~0ull;     // lane-local best two + smallest key let go
+    int hits = 0;
     scan_window(P, i, lane, 32, nullptr, [&](unsigned long long k) {
         if (k < k1) { dropped = min(dropped, k2); k2 = k1; k1 = k; }
         else if (k < k2) { dropped = min(dropped, k2); k2 = k; }
         else dropped = min(dropped, k);
-    });
+    }, AlwaysVisible(), &hits);
+    {
+        const unsigned any = __ballot_sync(0xffffffffu, hits > 0);
+        if (lane == 0) areaEmpty[i] = any == 0u;
+    }
     // the PROJ_K smallest of the 64 kept keys: repeated warp-min extraction
     unsigned long long lim = dropped;
 #pragma unroll
@@ -234,6 +241,7 @@ __global__ void __launch_bounds__(PROJ_T) k_proj_resolve(const ProjProblem* __re
     int* chB = chA + nq;
     int* rjA = chB + nq;                              // nq   (ratio-rejected flag, previous sweep)
     int* rjB = rjA + nq;
+    const int* areaEmpty = rjB + nq;                  // nq   (written by k_proj_candidates)
     for (int i = tid; i < nq; i += PROJ_T) { chA[i] = -1; rjA[i] = 0; }
     __syncthreads();
     int* chOld = chA; int* chNew = chB; int* rjOld = rjA; int* rjNew = rjB;
@@ -253,7 +261,8 @@ __global__ void __launch_bounds__(PROJ_T) k_proj_resolve(const ProjProblem* __re
         for (int i = tid; i < nq; i += PROJ_T) {
             int2 res = make_int2(-1, 0);
             const ProjQueryDev& Q = P.q[i];
-            const bool skip = !Q.valid || (Q.skipIfPrevRatioRejected && i > 0 && rjOld[i - 1]);
+            const bool skip = !Q.valid || (Q.skipIfPrevRatioRejected && i > 0 && rjOld[i - 1]) ||
+                              (Q.skipIfPrevEmpty && i > 0 && areaEmpty[i - 1]);
             if (!skip) {
                 const unsigned long long* list = P.cand + (long long)i * PROJ_K;
                 const unsigned long long lim = P.limit[i];

@@ -497,13 +497,14 @@ static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int frame0, 
     return ORBFE_OK;
 }
 
-// The device-resident pipeline.  A batch is cut into chunks of about h->devChunk frames and every chunk runs all five
-// stages before the next one starts on its stream: the chunk's pyramid (1.7 MB per 752x480 frame) and its blurred copy
-// are still in the 126 MB L2 when FAST, the blur and the descriptors read them, instead of making one HBM round trip per
-// stage as a whole-batch launch does.  Chunks go round-robin over h->devStreams compute streams, so the narrow launches
-// of one chunk (small pyramid levels, one quadtree CTA per level) run under the wide launches of its neighbours.  The
-// side streams fork from and join back into the handle's public stream: callers see one ordered stream.  With stage
-// profiling on, everything stays on the public stream (events between stages need a single timeline).
+// The device-resident pipeline.  A batch is cut into chunks of at most h->devChunk frames; every chunk runs all five stages
+// on one of h->devStreams compute streams (round-robin), so the narrow launches of one chunk (small pyramid levels, one
+// quadtree CTA per level) run under the wide launches of its neighbours.  The side streams fork from and join back into
+// the handle's public stream: callers see one ordered stream.  Measured on B200 (profiles/r02a_pipeline_sweep.txt, 512
+// frames of 752x480): chunks small enough to keep a chunk's pyramid in the 126 MB L2 (16-64 frames) LOSE to whole-batch
+// launches (150-157 k vs 158 k frames/s) - the stages are instruction-bound, not DRAM-bound, and short launches pay their
+// tails - so the default chunk is 512 frames and chunking only matters for longer batches.  With stage profiling on,
+// everything stays on the public stream (events between stages need a single timeline).
 static int run_device_pipeline(orbfe_handle* h, const uint8_t* dImages, int batch, int W, int H, long long stride,
                                long long frameStride, int lap0, int lap1) {
     const int want = std::max(1, h->devChunk);

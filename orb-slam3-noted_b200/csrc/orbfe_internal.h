@@ -20,8 +20,8 @@
 #define ORBFE_PIPE_MAX_CHUNKS 64
 #define ORBFE_MAX_COMPUTE_STREAMS 4
 #define ORBFE_GRAPH_SLOTS 4
-#define ORBFE_DEV_CHUNK 32         // frames per chunk of the device-resident pipeline: pyramid + blurred copy of a chunk stay in L2
-#define ORBFE_DEV_STREAMS 3
+#define ORBFE_DEV_CHUNK 512        // frames per chunk of the device-resident pipeline (profiles/r02a_pipeline_sweep.txt: L2-sized chunks lose)
+#define ORBFE_DEV_STREAMS 2
 #define ORBFE_SMALL_BATCH 8        // handles up to this max_batch mirror the whole result arena in pinned memory (one D2H per call)
 
 // Packed FAST candidate: x | y << 11 | response << 22, (x, y) relative to (minBorderX, minBorderY).

@@ -45,7 +45,7 @@ cudaError_t orbfe_launch_distinctive(cudaStream_t st, const uint8_t* dDesc, cons
 struct ProjQueryDev {          // = orbfe_proj_query (include/orbfe.h), 64 bytes
     float u, v, r, ur, angle;
     int16_t minLevel, maxLevel;
-    uint8_t right, obs, checkUr, valid, skipIfPrevRatioRejected, chi2, pad[2];
+    uint8_t right, obs, checkUr, valid, skipIfPrevRatioRejected, chi2, skipIfPrevEmpty, pad;
     uint8_t desc[32];
 };
 static_assert(sizeof(ProjQueryDev) == 64, "orbfe_proj_query layout");
@@ -71,7 +71,7 @@ struct ProjProblem {
     int* cellEnd;              // 2 * 3072
     unsigned long long* cand;  // nq * PROJ_K smallest candidate keys per window
     unsigned long long* limit; // nq: keys below it are a correct prefix of the window's sorted candidates
-    int* scratch;              // n + 4 * nq ints
+    int* scratch;              // n + 5 * nq ints
 };
 #define PROJ_K 8
 cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int mode,

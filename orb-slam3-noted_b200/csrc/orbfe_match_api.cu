@@ -589,7 +589,7 @@ extern "C" int orbfe_search_by_projection(orbfe_matcher* m, const orbfe_grid_fra
     const size_t inBytes = u;
     const size_t oSorted = stage_take(u, sizeof(uint32_t) * n), oCell = stage_take(u, sizeof(int) * 4 * 3072);
     const size_t oCand = stage_take(u, sizeof(unsigned long long) * (size_t)nq * PROJ_K), oLim = stage_take(u, sizeof(unsigned long long) * (size_t)nq);
-    const size_t oScr = stage_take(u, sizeof(int) * ((size_t)n + 4 * (size_t)nq));
+    const size_t oScr = stage_take(u, sizeof(int) * ((size_t)n + 5 * (size_t)nq));
     const size_t oOut = stage_take(u, 0);
     const size_t oAsg = stage_take(u, sizeof(int32_t) * n), oCh = stage_take(u, sizeof(int32_t) * (size_t)nq), oCnt = stage_take(u, 4);
     int st = ensure_stage(m, u);
@@ -660,7 +660,7 @@ extern "C" int orbfe_search_for_initialization(orbfe_matcher* m, const orbfe_key
     const size_t inBytes = u;
     const size_t oSorted = stage_take(u, sizeof(uint32_t) * n), oCell = stage_take(u, sizeof(int) * 4 * 3072);
     const size_t oCand = stage_take(u, sizeof(unsigned long long) * (size_t)nq * PROJ_K), oLim = stage_take(u, sizeof(unsigned long long) * (size_t)nq);
-    const size_t oScr = stage_take(u, sizeof(int) * ((size_t)n + 4 * (size_t)nq));
+    const size_t oScr = stage_take(u, sizeof(int) * ((size_t)n + 5 * (size_t)nq));
     const size_t oAsg = stage_take(u, sizeof(int32_t) * (size_t)std::max(n, nq));      // claim chains of k_init_resolve
     const size_t oOut = stage_take(u, 0);
     const size_t oCh = stage_take(u, sizeof(int32_t) * (size_t)nq), oCnt = stage_take(u, 4);

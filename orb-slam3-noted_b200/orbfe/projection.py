@@ -19,7 +19,8 @@ FRAME_GRID_ROWS, FRAME_GRID_COLS = 48, 64
 # include/orbfe.h: orbfe_proj_query (64 bytes)
 PROJ_QUERY_DTYPE = np.dtype([("u", "<f4"), ("v", "<f4"), ("r", "<f4"), ("ur", "<f4"), ("angle", "<f4"), ("min_level", "<i2"),
                              ("max_level", "<i2"), ("right", "u1"), ("obs", "u1"), ("check_ur", "u1"), ("valid", "u1"),
-                             ("skip_if_prev_ratio_rejected", "u1"), ("chi2", "u1"), ("pad", "u1", 2), ("desc", "u1", 32)])
+                             ("skip_if_prev_ratio_rejected", "u1"), ("chi2", "u1"), ("skip_if_prev_empty", "u1"), ("pad", "u1"),
+                             ("desc", "u1", 32)])
 assert PROJ_QUERY_DTYPE.itemsize == 64
 
 
@@ -139,6 +140,7 @@ def queries_from_lastframe(Cur, last, Tcw, th, fwd_bwd, project=None, project_ri
             e = np.zeros((), PROJ_QUERY_DTYPE)
             e["u"], e["v"], e["r"], e["min_level"], e["max_level"], e["right"] = u, v, radius, lo, hi, 1
             e["angle"], e["obs"], e["valid"], e["desc"] = last["angle"][i], last["obs"][i] > 0, 1, last["desc"][i]
+            e["skip_if_prev_empty"] = 1         # :2236-2237: an empty left window `continue`s past the right camera too
             q.append(e); owner.append(i)
     return (np.array(q, PROJ_QUERY_DTYPE) if q else np.zeros(0, PROJ_QUERY_DTYPE)), np.array(owner, np.int32)
 

@@ -477,16 +477,47 @@ def ref_matcher_available():
     return os.path.exists(REF_MATCHER_LIB)
 
 
+def _load_matcher(path):
+    L = C.CDLL(path)
+    L.orbslam3_search_bow.argtypes = [_I, _F, _I, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _I, _P, _P, _P, _P, _I, _I, _P, _P]
+    L.orbslam3_search_for_initialization.argtypes = [_F, _I, _P, _P, _I, _P, _P, _I, _F, _F, _F, _F, _P, _I, _P]
+    L.orbslam3_search_by_projection_mappoints.argtypes = [_F, _P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I] + [_P] * 14 + \
+        [_F, _I, _F, _P]
+    return L
+
+
 def ref_matcher():
     global _ref_matcher
     if _ref_matcher is None:
-        L = C.CDLL(REF_MATCHER_LIB)
-        L.orbslam3_search_bow.argtypes = [_I, _F, _I, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _I, _P, _P, _P, _P, _I, _I, _P, _P]
-        L.orbslam3_search_for_initialization.argtypes = [_F, _I, _P, _P, _I, _P, _P, _I, _F, _F, _F, _F, _P, _I, _P]
-        L.orbslam3_search_by_projection_mappoints.argtypes = [_F, _P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I] + [_P] * 14 + \
-            [_F, _I, _F, _P]
-        _ref_matcher = L
+        _ref_matcher = _load_matcher(REF_MATCHER_LIB)
     return _ref_matcher
+
+
+# The orbfe shim's ORBmatcher object layer behind the same C entry points (make -C oracle shim): GPU-backed.
+SHIM_MATCHER_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "liborbfe_shim_orbmatcher.so")
+_shim_matcher = None
+
+
+def shim_matcher_available():
+    return os.path.exists(SHIM_MATCHER_LIB)
+
+
+class shim_matcher_library:
+    """with shim_matcher_library(): every ref_* matcher call below runs ORB_SLAM3::ORBmatcher of include/orbfe_shim instead of the
+    reference's ORBmatcher.cc (same stand-in Frame / KeyFrame / MapPoint objects, same C wrappers)."""
+
+    def __enter__(self):
+        global _ref_matcher, _shim_matcher
+        if _shim_matcher is None:
+            _shim_matcher = _load_matcher(SHIM_MATCHER_LIB)
+        self.saved = ref_matcher() if ref_matcher_available() else None
+        _ref_matcher = _shim_matcher
+        return self
+
+    def __exit__(self, *exc):
+        global _ref_matcher
+        _ref_matcher = self.saved
+        return False
 
 
 def _kp_with_angle(angles):
