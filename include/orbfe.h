@@ -107,6 +107,13 @@ int orbfe_fetch_results(orbfe_handle* h, int batch, orbfe_keypoint* kps, uint8_t
  * query the size only.  *w, *h receive the ROI size. */
 int orbfe_get_pyramid_level(orbfe_handle* h, int frame, int level, uint8_t* dst, ptrdiff_t dst_stride, int* w, int* hgt);
 
+/* The whole mvImagePyramid of one frame of the last extract with ONE synchronise: dst[l] receives the bordered level l
+ * ((h_l + 38) rows of w_l + 38 bytes, dst_stride[l] bytes apart); sizes from orbfe_get_level_size (valid once an image of
+ * the current shape has been extracted).  What the C++ shim calls after operator() so that unmodified host readers of
+ * ORBextractor::mvImagePyramid (Frame::ComputeStereoMatches, Frame.cc:801,891-906) keep working. */
+int orbfe_get_pyramid(orbfe_handle* h, int frame, uint8_t* const* dst, const ptrdiff_t* dst_stride);
+int orbfe_get_level_size(const orbfe_handle* h, int level, int* w, int* hgt);
+
 /* Debug / parity taps of the last extract: FAST candidates of (frame, level) as int32 triples
  * (x, y, response) relative to (minBorderX, minBorderY), sorted into the reference's push order
  * (ORBextractor.cc:843-851).  Returns the count (may exceed cap; only cap triples are written). */

@@ -67,6 +67,9 @@ public:
         pyramidValid_ = false;
         if (mono < 0) { lastStatus_ = mono; _keypoints.clear(); orbfe_shim::release_out(_descriptors); return -1; }
         lastStatus_ = ORBFE_OK;
+        // the reference leaves mvImagePyramid filled after every call and Frame::ComputeStereoMatches (Frame.cc:801,891-906)
+        // reads it on the host: by default so do we (one batched copy, ~1.3 MB for a 752x480 image)
+        if (hostPyramid_ && !FetchImagePyramid()) { _keypoints.clear(); orbfe_shim::release_out(_descriptors); return -1; }
         static_assert(sizeof(cv::KeyPoint) == sizeof(orbfe_keypoint), "cv::KeyPoint must be 28 bytes");
         _keypoints.resize(n);
         if (n == 0) { orbfe_shim::release_out(_descriptors); return mono; }
@@ -83,24 +86,30 @@ public:
     std::vector<float> inline GetScaleSigmaSquares() { tables(); return mvLevelSigma2; }
     std::vector<float> inline GetInverseScaleSigmaSquares() { tables(); return mvInvLevelSigma2; }
 
-    // Public member of the reference (ORBextractor.h:83), read by Frame::ComputeStereoMatches on the
-    // host.  The pyramid lives on the GPU; call FetchImagePyramid() before reading it on the host
-    // (orbfe_stereo_match does not need it).
+    // Public member of the reference (ORBextractor.h:83), read by Frame::ComputeStereoMatches on the host.  The pyramid is
+    // computed and kept on the GPU; after every operator() its bordered levels are copied to the host and mvImagePyramid[l]
+    // points at the ROI inside each, exactly like the reference's cv::Mat views (ORBextractor.cc:1160-1163), so unmodified
+    // host readers work.  An integration that routes Frame::ComputeStereoMatches to orbfe_stereo_match (which reads the
+    // device-resident pyramid) switches the copy off with SetHostPyramid(false) and may still call FetchImagePyramid().
     std::vector<cv::Mat> mvImagePyramid;
+    void SetHostPyramid(bool on) { hostPyramid_ = on; }
 
-    // Copies the bordered levels of the last extraction to the host and points mvImagePyramid[l] at
-    // the ROI inside each, exactly like the reference's cv::Mat views (ORBextractor.cc:1160-1163).
     bool FetchImagePyramid() {
         if (!h_) return false;
         if (pyramidValid_) return true;
         parents_.resize(nlevels);
+        std::vector<uint8_t*> dst(nlevels);
+        std::vector<ptrdiff_t> strides(nlevels);
+        std::vector<int> w(nlevels), h(nlevels);
         for (int l = 0; l < nlevels; ++l) {
-            int w = 0, h = 0;
-            if (orbfe_get_pyramid_level(h_, 0, l, nullptr, 0, &w, &h) < 0) return false;
-            parents_[l].create(h + 38, w + 38, CV_8U);
-            if (orbfe_get_pyramid_level(h_, 0, l, parents_[l].ptr(), (ptrdiff_t)parents_[l].step, &w, &h) < 0) return false;
-            mvImagePyramid[l] = orbfe_shim::roi_view(parents_[l], 19, 19, w, h);
+            if (orbfe_get_level_size(h_, l, &w[l], &h[l]) < 0) return false;
+            parents_[l].create(h[l] + 38, w[l] + 38, CV_8U);
+            dst[l] = parents_[l].ptr();
+            strides[l] = (ptrdiff_t)parents_[l].step;
         }
+        lastStatus_ = orbfe_get_pyramid(h_, 0, dst.data(), strides.data());
+        if (lastStatus_ < 0) return false;
+        for (int l = 0; l < nlevels; ++l) mvImagePyramid[l] = orbfe_shim::roi_view(parents_[l], 19, 19, w[l], h[l]);
         pyramidValid_ = true;
         return true;
     }
@@ -148,7 +157,7 @@ private:
     int device_;
     orbfe_handle* h_ = nullptr;
     int maxW_ = 0, maxH_ = 0, lastStatus_ = ORBFE_OK;
-    bool pyramidValid_ = false;
+    bool pyramidValid_ = false, hostPyramid_ = true;
     std::vector<orbfe_keypoint> kps_;
     std::vector<uint8_t> desc_;
     std::vector<cv::Mat> parents_;

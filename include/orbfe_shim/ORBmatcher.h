@@ -284,9 +284,9 @@ protected:
 public:
 #endif
 
-    static const int TH_LOW = ORBFE_TH_LOW;
-    static const int TH_HIGH = ORBFE_TH_HIGH;
-    static const int HISTO_LENGTH = ORBFE_HISTO_LENGTH;
+    static constexpr int TH_LOW = ORBFE_TH_LOW;       // constexpr: implicitly inline, so odr-uses need no definition elsewhere
+    static constexpr int TH_HIGH = ORBFE_TH_HIGH;
+    static constexpr int HISTO_LENGTH = ORBFE_HISTO_LENGTH;
 
     orbfe_matcher* handle() { return m_; }
     int lastStatus() const { return status_; }

@@ -26,6 +26,9 @@ using namespace ORB_SLAM3;
 
 #include <atomic>
 #include <new>
+#ifdef ORBSLAM3_REF_SYSTEM_HEAP     // the build against the orbfe shim: no reference quadtree in this library, nothing to pin
+namespace { struct HeapScope {}; }
+#else
 namespace {
 const size_t kArena = (size_t)48 << 30;      // virtual; pages are touched on demand
 char* arenaBase() {
@@ -62,6 +65,7 @@ void operator delete(void*) noexcept {}
 void operator delete[](void*) noexcept {}
 void operator delete(void*, size_t) noexcept {}
 void operator delete[](void*, size_t) noexcept {}
+#endif
 
 // cv::undistortPoints of the stand-in forwards here: oracle/cpu_ref's restatement, bit-identical to cv2.undistortPoints 4.13
 namespace cv {

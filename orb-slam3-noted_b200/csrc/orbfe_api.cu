@@ -893,6 +893,31 @@ extern "C" int orbfe_get_pyramid_level(orbfe_handle* h, int frame, int level, ui
     return ORBFE_OK;
 }
 
+// All levels of one frame with one synchronise (what the shim's mvImagePyramid needs after every operator() when the host
+// reads the pyramid, as the unmodified Frame::ComputeStereoMatches does).
+extern "C" int orbfe_get_pyramid(orbfe_handle* h, int frame, uint8_t* const* dst, const ptrdiff_t* dst_stride) {
+    if (!h || !dst || !dst_stride) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->lastBatch <= 0) return ORBFE_ERR_NOT_READY;
+    if (frame < 0 || frame >= h->lastBatch) return ORBFE_ERR_BAD_ARGUMENT;
+    for (int l = 0; l < h->p.nlevels; ++l)
+        if (!dst[l] || dst_stride[l] < h->geom[l].w + 2 * ORBFE_EDGE) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    for (int l = 0; l < h->p.nlevels; ++l) {
+        const LevelGeom& g = h->geom[l];
+        const uint8_t* src = h->dPyr + g.base + (long long)frame * g.plane + (ORBFE_XO - ORBFE_EDGE);
+        CK(cudaMemcpy2DAsync(dst[l], dst_stride[l], src, g.pitch, g.w + 2 * ORBFE_EDGE, g.rows, cudaMemcpyDeviceToHost, h->stream));
+    }
+    CK(cudaStreamSynchronize(h->stream));
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_get_level_size(const orbfe_handle* h, int level, int* w, int* hgt) {
+    if (!h || level < 0 || level >= h->p.nlevels || h->curW <= 0) return h && h->curW <= 0 ? ORBFE_ERR_NOT_READY : ORBFE_ERR_BAD_ARGUMENT;
+    if (w) *w = h->geom[level].w;
+    if (hgt) *hgt = h->geom[level].h;
+    return ORBFE_OK;
+}
+
 extern "C" int orbfe_get_candidates(orbfe_handle* h, int frame, int level, int32_t* xyr, int cap) {
     if (!h || level < 0 || level >= h->p.nlevels) return ORBFE_ERR_BAD_ARGUMENT;
     if (h->lastBatch <= 0) return ORBFE_ERR_NOT_READY;

@@ -80,7 +80,9 @@ int main(int argc, char** argv) {
     if (ORBmatcher::DescriptorDistance(dL.row(0), dL.row(0)) != 0) return 1;
 
     std::vector<float> sf = exL.GetScaleFactors();
-    if (!exL.FetchImagePyramid()) return 1;
+    // like the reference's, the shim leaves mvImagePyramid filled after operator() (no explicit fetch): an unmodified
+    // Frame::ComputeStereoMatches reads it right away (Frame.cc:801)
+    if (exL.mvImagePyramid[0].rows != H || exL.mvImagePyramid[0].cols != W || exR.mvImagePyramid[0].rows != H) return 1;
     const cv::Mat& p1 = exL.mvImagePyramid[1];
 
     FILE* o = fopen(argv[8], "wb");

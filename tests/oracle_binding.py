@@ -776,23 +776,55 @@ def ref_frame_available():
     return os.path.exists(REF_FRAME_LIB) and ref_matcher_available()
 
 
+def _load_frame(path):
+    L = C.CDLL(path)
+    L.orbslam3_frame_stereo_matches.argtypes = [_I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _F, _F, _P, _P]
+    L.orbslam3_frame_fisheye_matches.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _I, _P, _P, _P, _P]
+    L.orbslam3_frame_undistort_keypoints.argtypes = [_P, _I, _P, _P, _I, _P]
+    L.orbslam3_frame_features_in_area.argtypes = [_P, _I, _I, _F, _F, _F, _F, _P, _I, _P, _I, _P]
+    L.orbslam3_kb8_project.argtypes = [_P, _P, _I, _P]
+    L.orbslam3_pinhole_project.argtypes = [_P, _P, _I, _P]
+    L.orbslam3_frame_fisheye_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _F, _F, _I] + [_P] * 7
+    L.orbslam3_frame_mono_construct.argtypes = [_P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, C.c_char_p, _I] + [_P] * 9
+    L.orbslam3_kb8_epipolar_constrain_.argtypes = [_P] * 4 + [_I] + [_P] * 7
+    L.orbslam3_frame_stereo_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, _F, _F, _I] + [_P] * 9
+    L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
+    return L
+
+
 def ref_frame():
     global _ref_frame
     if _ref_frame is None:
-        L = C.CDLL(REF_FRAME_LIB)
-        L.orbslam3_frame_stereo_matches.argtypes = [_I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _P, _I, _P, _P, _I, _F, _F, _P, _P]
-        L.orbslam3_frame_fisheye_matches.argtypes = [_P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _P, _P, _P, _I, _P, _P, _P, _P]
-        L.orbslam3_frame_undistort_keypoints.argtypes = [_P, _I, _P, _P, _I, _P]
-        L.orbslam3_frame_features_in_area.argtypes = [_P, _I, _I, _F, _F, _F, _F, _P, _I, _P, _I, _P]
-        L.orbslam3_kb8_project.argtypes = [_P, _P, _I, _P]
-        L.orbslam3_pinhole_project.argtypes = [_P, _P, _I, _P]
-        L.orbslam3_frame_fisheye_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _P, _P, _P, _F, _F, _I] + [_P] * 7
-        L.orbslam3_frame_mono_construct.argtypes = [_P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, C.c_char_p, _I] + [_P] * 9
-        L.orbslam3_kb8_epipolar_constrain_.argtypes = [_P] * 4 + [_I] + [_P] * 7
-        L.orbslam3_frame_stereo_construct.argtypes = [_P, _P, _I, _I, _I, _F, _I, _I, _I, _P, _P, _I, _F, _F, _I] + [_P] * 9
-        L.orbslam3_kb8_unproject.argtypes = [_P, _P, _I, _P]
-        _ref_frame = L
+        _ref_frame = _load_frame(REF_FRAME_LIB)
     return _ref_frame
+
+
+# The reference's own Frame.cc compiled against the orbfe shim headers + liborbfe.so (make -C oracle shim): its Frame constructors
+# extract on the GPU.
+SHIM_FRAME_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "liborbfe_shim_frame.so")
+_shim_frame = None
+
+
+def shim_frame_available():
+    return os.path.exists(SHIM_FRAME_LIB)
+
+
+class shim_frame_library:
+    """with shim_frame_library(): ref_stereo_frame / ref_fisheye_frame / ref_mono_frame / ref_stereo_matches run the reference's
+    Frame.cc whose ORBextractor is the orbfe shim class (GPU) instead of the reference's ORBextractor.cc."""
+
+    def __enter__(self):
+        global _ref_frame, _shim_frame
+        if _shim_frame is None:
+            _shim_frame = _load_frame(SHIM_FRAME_LIB)
+        self.saved = ref_frame() if ref_frame_available() else None
+        _ref_frame = _shim_frame
+        return self
+
+    def __exit__(self, *exc):
+        global _ref_frame
+        _ref_frame = self.saved
+        return False
 
 
 def ref_stereo_matches(params, levelsL, levelsR, kpL, descL, kpR, descR, bf, b):
