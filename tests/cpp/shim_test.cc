@@ -82,7 +82,7 @@ int main(int argc, char** argv) {
     std::vector<float> sf = exL.GetScaleFactors();
     // like the reference's, the shim leaves mvImagePyramid filled after operator() (no explicit fetch): an unmodified
     // Frame::ComputeStereoMatches reads it right away (Frame.cc:801)
-    if (exL.mvImagePyramid[0].rows != H || exL.mvImagePyramid[0].cols != W || exR.mvImagePyramid[0].rows != H) return 1;
+    if (exL.mvImagePyramid[0].rows != h || exL.mvImagePyramid[0].cols != w || exR.mvImagePyramid[0].rows != h) return 1;
     const cv::Mat& p1 = exL.mvImagePyramid[1];
 
     FILE* o = fopen(argv[8], "wb");
