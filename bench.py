@@ -11,8 +11,9 @@ keypoints + descriptors inside the timed region).  Under torchrun each rank driv
 its own frames (no data-path collective: frames are independent); the timed region
 is bracketed by barrier + synchronize and the max over ranks is reported.
 
-`--impl reference` times the CPU restatement of the reference path (oracle/, the reference's own
-C++ cannot be compiled here: it needs OpenCV C++ headers) on all host cores, rank 0 only.
+`--impl reference` times the reference's own src/ORBextractor.cc (oracle/_ref, compiled from /root/reference against
+the OpenCV stand-in of oracle/refshim; the oracle port only if that library is missing) on all host cores, rank 0 only.
+The `shapes` object of the line holds one leg per other BASELINE config (bench_legs.py) and the drop-in latency.
 """
 import argparse
 import json
@@ -159,8 +160,9 @@ def run_reference(args):
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step": per_step,
-                   "note": what},
+        "config": {"workload": WORKLOAD, "lapping": list(LAPPING)},
+        "config_detail": {"frames_per_step": per_step, "note": what, "primitives": "scalar restatement of OpenCV's resize / FAST / GaussianBlur "
+                          "(bit-identical to cv2 4.13, not its SIMD kernels)"},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
@@ -483,6 +485,22 @@ def run_orbfe(args):
     barrier()
     e2e_s = time.perf_counter() - t0
 
+    # outside the timed regions: frames of the timed 512-batch (as the e2e call left them in the host buffers) against the
+    # reference's own ORBextractor.cc (oracle/_ref) or, without it, the oracle port
+    parity_frames = None
+    if rank == 0 and not args.no_cpu:
+        ob = _oracle()
+        ref = ob.OrbSlam3Extractor(*ORB_PARAMS) if ob.ref_available() else ob.OrbRef(*ORB_PARAMS)
+        parity_frames = {"against": "oracle/_ref (reference ORBextractor.cc)" if ob.ref_available() else "oracle/cpu_ref", "frames": [], "ok": True}
+        for fi in sorted({0, 1, B // 2, B - 1}):
+            rmono, rk, rd = ref(hnp[fi], LAPPING)
+            k, d = kps[fi, :n_out[fi]], desc[fi, :n_out[fi]]
+            ok = bool(rmono == mono[fi] and len(rk) == len(k) and all(np.array_equal(rk[f], k[f]) for f in ("x", "y", "size", "response", "octave")) and
+                      np.max(np.abs(rk["angle"] - k["angle"]), initial=0) <= 1e-4 * 180 / np.pi and (rd == d).all(1).mean() >= 0.9999)
+            parity_frames["frames"].append(fi)
+            parity_frames["ok"] = parity_frames["ok"] and ok
+        if not parity_frames["ok"]:
+            raise SystemExit("bench.py: the timed batch does not reproduce the reference extractor: " + json.dumps(parity_frames))
     if world > 1:
         t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -494,6 +512,26 @@ def run_orbfe(args):
     matching = None if args.no_match else run_matching(args, torch, orbfe, rank, local, world, barrier, dist)
     proj = None if args.no_match else run_projection(args, orbfe, rank, local, world)
     clk = clocks.stop()
+    level_sizes = []
+    for l in range(ex.nlevels):
+        _, roi = ex.image_pyramid(l, 0)
+        level_sizes.append((roi.shape[1], roi.shape[0]))
+    legs = {}
+    if rank == 0 and world == 1 and not args.no_legs:      # the scaling runs (N > 1) carry the headline only
+        import bench_legs as bl
+        peak_l, _ = measured_peaks()
+        ex.close()                      # the headline handle's arenas (2 GB) are not needed any more
+        del dev
+        torch.cuda.empty_cache()
+        for name, fn in (("config1_stereo_euroc", lambda: bl.run_stereo(args, torch, orbfe, local, peak_l)),
+                         ("config2_fisheye_tumvi", lambda: bl.run_fisheye(args, torch, orbfe, local, peak_l)),
+                         ("config3_kitti_bow", lambda: bl.run_kitti_bow(args, torch, orbfe, local, peak_l)),
+                         ("config4_hd_1080p", lambda: bl.run_hd(args, torch, orbfe, local, peak_l)),
+                         ("latency", lambda: bl.run_latency(args, torch, orbfe, local))):
+            try:
+                legs[name] = fn()
+            except Exception as e:      # a leg must not take the headline down
+                legs[name] = {"error": f"{type(e).__name__}: {e}"}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -502,10 +540,6 @@ def run_orbfe(args):
     value = world * K * B / (ms / 1e3)
     e2e_v = world * K * B / e2e_s
     # roofline of the dominant stage (per launch of that stage = one batch of B frames)
-    level_sizes = []
-    for l in range(ex.nlevels):
-        _, roi = ex.image_pyramid(l, 0)
-        level_sizes.append((roi.shape[1], roi.shape[0]))
     b_alg = algorithmic_bytes_per_frame(W, H, n_kp, level_sizes)
     top = max(stage_ms, key=stage_ms.get)
     # profiling counts one "call" per chunk of the device pipeline: a launch of a stage processes B * K / calls frames
@@ -526,10 +560,12 @@ def run_orbfe(args):
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": Wm,
         "ms_per_step": ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": WORKLOAD, "frames_per_step_per_gpu": B, "distinct_frames": nd, "lapping": list(LAPPING),
-                   "mean_keypoints_per_frame": n_kp, "parallelism": f"frame-sharded x{world}, no collective", "numa_node": numa,
-                   "l2": f"inputs larger than L2: {B * W * H / 1e6:.0f} MB of frames and a "
-                         f"{B * sum((a + 38) * (b + 38) for a, b in level_sizes) / 1e6:.0f} MB pyramid per step vs 126 MB L2"},
+        "config": {"workload": WORKLOAD, "lapping": list(LAPPING)},
+        "config_detail": {"frames_per_step_per_gpu": B, "distinct_frames": nd, "mean_keypoints_per_frame": n_kp,
+                          "parallelism": f"frame-sharded x{world}, no collective", "numa_node": numa,
+                          "l2": f"inputs larger than L2: {B * W * H / 1e6:.0f} MB of frames and a "
+                                f"{B * sum((a + 38) * (b + 38) for a, b in level_sizes) / 1e6:.0f} MB pyramid per step vs 126 MB L2",
+                          "parity_checked_frames": parity_frames},
         "e2e": {"value": e2e_v, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),
                 "d2h_bytes_per_step": int(B * ex.cap * 60 + 8 * B), "ms_per_step": 1e3 * e2e_s / K,
                 "api": "orbfe_extract_batch (pinned host buffers; 64-frame chunks pipelined over copy-in / 2 compute / copy-out streams)"},
@@ -566,6 +602,8 @@ def run_orbfe(args):
         out["bow_transform"] = bow
     if proj is not None:
         out["projection_search"] = proj
+    if legs:
+        out["shapes"] = legs
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -583,6 +621,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-match", action="store_true", help="skip the matching and BoW legs")
     ap.add_argument("--match-frames", type=int, default=24, help="1920x1080 frames per matching step per GPU")
+    ap.add_argument("--no-legs", action="store_true", help="skip the legs for BASELINE configs 1-4 and the latency leg")
+    ap.add_argument("--stereo-pairs", type=int, default=128, help="stereo pairs per step of the config-1 leg")
+    ap.add_argument("--hd-frames", type=int, default=32, help="1920x1080 frames per step of the config-4 leg")
     args = ap.parse_args()
     if args.warmup < 3:
         args.warmup = 3

@@ -1,7 +1,7 @@
 // k_fast.cu — grid FAST: the cell loop of ORBextractor::ComputeKeyPointsOctTree
 // (ORBextractor.cc:787-853) with cv::FAST(cell, keys, th, nonmaxSuppression=true), type 9_16.
 //
-// One CTA per (cell, frame).  The cell ROI (core + 6 px, clamped at the level's max border) is brought
+// One CTA per (cell, frame) (two to four cells per CTA were measured and lost: 1.56 -> 1.67 / 1.77 / 1.91 ms per 512 frames).  The cell ROI (core + 6 px, clamped at the level's max border) is brought
 // into shared memory by ONE TMA tiled load (cp.async.bulk.tensor.3d over a per-level tensor map of the
 // pyramid arena, completion on an mbarrier) issued by thread 0 while the other threads clear the score
 // map; the reference never lets FAST read outside the cell ROI, and neither do we (the TMA box may be
@@ -89,49 +89,41 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, i
         : "memory");
 }
 
-#ifndef FAST_CPC
-#define FAST_CPC 1             // cells per CTA (measured on B200: 1 -> 1.56 ms, 2 -> 1.67, 3 -> 1.77, 4 -> 1.91 per 512 frames)
-#endif
 #ifndef FAST_MINB
 #define FAST_MINB 8
 #endif
+// TPC = tile pitch known at compile time (64: every BASELINE shape, cells up to 49 px wide) or 0 = runtime boxW.  With a constant
+// pitch the 16 ring offsets, the +-3-row word offsets of stage A and the index -> (x, y) split are immediates / shifts.
+// Everything that depends only on the cell (tested-word range, edge masks, TMA coordinates) or only on the launch (list
+// capacities, reciprocal of the pitch) comes precomputed from the host (CellDesc, kernel parameters): the prologue of a
+// CTA that lives for ~3000 warp instructions used to spend 14 % of them on this arithmetic (profiles/r01o_*).
+template <int TPC>
 __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __grid_constant__ FastMaps maps,
                                                              const LevelGeom* __restrict__ geom,
                                                              const CellDesc* __restrict__ cells, uint32_t* __restrict__ cand,
                                                              int* __restrict__ candCount, long long candPerFrame,
-                                                             int nlevels, int iniTh, int minTh, int boxW, int boxH, int frame0,
-                                                             int nCells) {
+                                                             int nlevels, int iniTh, int minTh, int boxW, int tileBytes, int listCap,
+                                                             uint32_t invTp, int frame0) {
     extern __shared__ __align__(128) uint8_t smem[];
-    __shared__ __align__(8) uint64_t sBar[FAST_CPC];
+    __shared__ __align__(8) uint64_t sBar;
     __shared__ int sCand, sCorners, sKept, sBase;
     const int frame = frame0 + blockIdx.y;
-    const int tp = boxW;                     // dense tile as delivered by TMA
-    const int tileBytes = boxW * boxH;
-    const int tileStride = (tileBytes + 127) & ~127;   // TMA destinations must be 128-byte aligned
-    uint8_t* tiles = smem;                   // FAST_CPC tiles, all requested up front: cell k+1 loads while cell k computes
-    uint8_t* score = tiles + FAST_CPC * tileStride;
+    const int tp = TPC ? TPC : boxW;         // dense tile as delivered by TMA
+    uint8_t* tile = smem;
+    uint8_t* score = tile + ((tileBytes + 127) & ~127);   // TMA destinations must be 128-byte aligned
     uint16_t* list1 = reinterpret_cast<uint16_t*>(score + tileBytes);        // survivors of the quick test
-    const int listCap = ((boxW - 6) * (boxH - 6) + 1) & ~1;
     uint16_t* list2 = list1 + listCap;                                       // corners
     uint32_t* kept = reinterpret_cast<uint32_t*>(list2 + listCap);
     const int tid = threadIdx.x;
     const int nw = tp >> 2;
-    const uint32_t invTp = ((1u << 20) + tp - 1) / tp;   // idx / tp == (idx * invTp) >> 20 for idx * tp < 2^20 (a tile has < 2^14 bytes)
-    const int cell0 = blockIdx.x * FAST_CPC;
+    const CellDesc cd = cells[blockIdx.x];
 
     if (tid == 0) {
-#pragma unroll
-        for (int ci = 0; ci < FAST_CPC; ++ci) {
-            if (cell0 + ci >= nCells) break;
-            const CellDesc c = cells[cell0 + ci];
-            if (c.cw - 6 <= 0 || c.ch - 6 <= 0) continue;
-            // TMA wants the innermost start coordinate on a 16-byte boundary: load from the aligned column
-            // below the cell; tile byte = sh + column.
-            const int s = (ORBFE_XO + c.x0) & 15;
-            mbar_init(&sBar[ci], 1);
-            mbar_expect_tx(&sBar[ci], (uint32_t)tileBytes);
-            tma_load_3d(tiles + ci * tileStride, &maps.m[c.level], ORBFE_XO + c.x0 - s, ORBFE_EDGE + c.y0, frame, &sBar[ci]);
-        }
+        mbar_init(&sBar, 1);
+        mbar_expect_tx(&sBar, (uint32_t)tileBytes);
+        // TMA wants the innermost start coordinate on a 16-byte boundary: the box starts at the aligned column below the
+        // cell (cd.tx); tile byte = cd.sh + column.
+        tma_load_3d(tile, &maps.m[cd.level], cd.tx, cd.ty, frame, &sBar);
     }
 
     int off[16];
@@ -141,55 +133,44 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
 #pragma unroll
         for (int k = 0; k < 16; ++k) off[k] = dy[k] * tp + dx[k];
     }
-  for (int ci = 0; ci < FAST_CPC; ++ci) {
-    if (cell0 + ci >= nCells) break;
-    const CellDesc cd = cells[cell0 + ci];
-    const LevelGeom& g = geom[cd.level];
-    const int cw = cd.cw, ch = cd.ch;
-    const int sh = (ORBFE_XO + cd.x0) & 15;
-    const int tw = cw - 6, th = ch - 6;      // tested area
-    if (tw <= 0 || th <= 0) continue;
-    const uint8_t* tile = tiles + ci * tileStride;
-    // A1 work units: (row r in [3, ch-3)) x (word wi in [wLo, wHi]); word wi holds columns 4wi-sh .. 4wi-sh+3
-    const int wLo = (sh + 3) >> 2, wHi = (sh + cw - 4) >> 2, nWordsA1 = wHi - wLo + 1;
-    const int units = th * nWordsA1;
-    const uint32_t inv = cd.inv;             // host: ceil(2^20 / nWordsA1); u / nWordsA1 == (u * inv) >> 20 for u < 2^20 / nWordsA1
+    const int nWords = cd.nWords, units = cd.units;
+    const uint32_t inv = cd.inv;             // host: ceil(2^20 / nWords); u / nWords == (u * inv) >> 20 for u < 2^20 / nWords
+    const int w0 = 3 * nw + cd.wLo;          // first tested word: row 3, word wLo
+    const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(tile);
 
     int t = iniTh;
     for (int pass = 0; pass < 2; ++pass) {
         if (tid == 0) { sCand = 0; sCorners = 0; sKept = 0; }
         for (int i = tid; i < tileBytes / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
         __syncthreads();                       // also orders the mbarrier init before everyone's wait
-        if (pass == 0) mbar_wait(&sBar[ci], 0);
-        // A1: necessary condition on two opposite ring pairs, 4 pixels per step.  A 9-arc covers at least
-        // one pixel of every opposite pair, so a corner has |c - v| > t for v0 or v8 AND for v4 or v12.
+        if (pass == 0) mbar_wait(&sBar, 0);
+        // A: necessary condition on two opposite ring pairs, 4 pixels per step.  A 9-arc covers at least one pixel of every
+        // opposite pair, so a corner has |c - v| > t for v0 or v8 AND for v4 or v12.  Bit 7 of every byte of m = "may be a corner".
         {
             const uint32_t k127 = (uint32_t)(127 - (t & 127)) * 0x01010101u, lowT = t < 128 ? 0xFFFFFFFFu : 0u;
-            const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(tile);
             for (int u = tid; u < units; u += FAST_THREADS) {
-                const int rr = (int)(((uint32_t)u * inv) >> 20), wi = wLo + u - rr * nWordsA1, r = rr + 3;
-                const uint32_t c = tw32[r * nw + wi];
-                const uint32_t up = tw32[(r - 3) * nw + wi], dn = tw32[(r + 3) * nw + wi];
+                const int rr = (int)(((uint32_t)u * inv) >> 20), wj = u - rr * nWords;
+                const int w = w0 + rr * nw + wj;
+                const uint32_t c = tw32[w];
+                const uint32_t up = tw32[w - 3 * nw], dn = tw32[w + 3 * nw];
                 uint32_t m = (gtu4_bit7(__vabsdiffu4(c, up), k127, lowT) | gtu4_bit7(__vabsdiffu4(c, dn), k127, lowT)) & 0x80808080u;
+                if (wj == 0) m &= cd.firstMask;                  // tested columns are [3, cw - 3): edge words carry fewer than 4
+                if (wj == nWords - 1) m &= cd.lastMask;
                 if (m == 0) continue;
-                const uint32_t lf = tw32[r * nw + wi - 1], rt = tw32[r * nw + wi + 1];
+                const uint32_t lf = tw32[w - 1], rt = tw32[w + 1];
                 const uint32_t vl = __byte_perm(lf, c, 0x4321);      // bytes at column - 3
                 const uint32_t vr = __byte_perm(c, rt, 0x6543);      // bytes at column + 3
                 m &= gtu4_bit7(__vabsdiffu4(c, vl), k127, lowT) | gtu4_bit7(__vabsdiffu4(c, vr), k127, lowT);
-                // nibble of survivors, restricted to tested columns [3, cw-3)
-                uint32_t vb = (m >> 7 & 1u) | (m >> 14 & 2u) | (m >> 21 & 4u) | (m >> 28 & 8u);
-                const int c0 = 4 * wi - sh;                      // column of byte 0 (may be < 0)
-                const int kLo = max(3 - c0, 0), kHi = min(cw - 3 - c0, 4);   // valid bytes [kLo, kHi)
-                vb &= ((1u << kHi) - 1u) & ~((1u << kLo) - 1u);
-                if (vb == 0u) continue;
+                if (m == 0u) continue;
                 // survivors are sparse (a few lanes per warp): each lane reserves its own slots with one shared-memory atomic.
                 // Measured against the warp-aggregated form (5 ballots + prefix popcounts + one atomic per warp) on B200:
                 // FAST 1.56 -> 1.42 ms per 512 frames; the same change in stages B and C: -> 1.31 ms.
-                int base = atomicAdd(&sCand, __popc(vb));
-                const int idx = r * tp + 4 * wi;
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (vb >> k & 1u) list1[base++] = (uint16_t)(idx + k);
+                int base = atomicAdd(&sCand, __popc(m));
+                const int idx = 4 * w;
+                if (m & 0x00000080u) list1[base++] = (uint16_t)idx;
+                if (m & 0x00008000u) list1[base++] = (uint16_t)(idx + 1);
+                if (m & 0x00800000u) list1[base++] = (uint16_t)(idx + 2);
+                if (m & 0x80000000u) list1[base] = (uint16_t)(idx + 3);
             }
         }
         __syncthreads();
@@ -222,7 +203,7 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
             }
             const int slot = keep ? atomicAdd(&sKept, 1) : -1;
             if (slot >= 0) {
-                const int y = (int)(((uint32_t)idx * invTp) >> 20), x = idx - y * tp - sh;
+                const int y = TPC ? idx / TPC : (int)(((uint32_t)idx * invTp) >> 20), x = idx - y * tp - cd.sh;
                 kept[slot] = (uint32_t)(x + cd.ox) | (uint32_t)(y + cd.oy) << 11 | (uint32_t)s << 22;
             }
         }
@@ -235,26 +216,31 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
     if (nk > 0) {
         if (tid == 0) sBase = atomicAdd(&candCount[frame * nlevels + cd.level], nk);
         __syncthreads();
-        uint32_t* out = cand + (long long)frame * candPerFrame + g.candBase + sBase;
+        uint32_t* out = cand + (long long)frame * candPerFrame + geom[cd.level].candBase + sBase;
         for (int i = tid; i < nk; i += FAST_THREADS) out[i] = kept[i];
     }
-    __syncthreads();                         // the next cell reuses the score map, the lists and the counters
-  }
 }
 
 cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
     cudaError_t e = cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->cur);
     if (e != cudaSuccess) return e;
-    const size_t tileStride = ((size_t)h->fastBoxW * h->fastBoxH + 127) & ~(size_t)127;
-    const size_t smem = (size_t)h->maxCellBytes + FAST_CPC * tileStride - (size_t)h->fastBoxW * h->fastBoxH;   // maxCellBytes counts one unpadded tile
-    {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
-        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_fast_cells), smem);
-        if (ea != cudaSuccess) return ea;
-    }
-    dim3 grid((h->nCellsTotal + FAST_CPC - 1) / FAST_CPC, batch);
-    k_fast_cells<<<grid, FAST_THREADS, smem, h->cur>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,
-                                                          h->candPerFrame, h->p.nlevels, h->p.ini_th_fast, h->p.min_th_fast,
-                                                          h->fastBoxW, h->fastBoxH, frame0, h->nCellsTotal);
+    const int tileBytes = h->fastBoxW * h->fastBoxH;
+    const size_t tileStride = ((size_t)tileBytes + 127) & ~(size_t)127;
+    const size_t smem = (size_t)h->maxCellBytes + tileStride - (size_t)tileBytes;   // maxCellBytes counts one unpadded tile
+    const int listCap = ((h->fastBoxW - 6) * (h->fastBoxH - 6) + 1) & ~1;
+    const uint32_t invTp = ((1u << 20) + h->fastBoxW - 1) / h->fastBoxW;   // idx / tp == (idx * invTp) >> 20 (a tile has < 2^14 bytes)
+    dim3 grid(h->nCellsTotal, batch);
+#define ORBFE_FAST_LAUNCH(TPC)                                                                                                   \
+    do {                                                                                                                         \
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_fast_cells<TPC>), smem);                    \
+        if (ea != cudaSuccess) return ea;                                                                                        \
+        k_fast_cells<TPC><<<grid, FAST_THREADS, smem, h->cur>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,       \
+                                                                h->candPerFrame, h->p.nlevels, h->p.ini_th_fast, h->p.min_th_fast, \
+                                                                h->fastBoxW, tileBytes, listCap, invTp, frame0);                 \
+    } while (0)
+    if (h->fastBoxW == 64) ORBFE_FAST_LAUNCH(64);
+    else ORBFE_FAST_LAUNCH(0);
+#undef ORBFE_FAST_LAUNCH
     h->launches++;
     return cudaGetLastError();
 }

@@ -197,14 +197,21 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
                 if (iniX >= g.maxBX - 6) continue;
                 if (maxX > g.maxBX) maxX = g.maxBX;
                 CellDesc c;
+                memset(&c, 0, sizeof(c));
                 c.level = (short)l; c.x0 = (short)iniX; c.y0 = (short)iniY;
                 c.cw = (short)(maxX - iniX); c.ch = (short)(maxY - iniY);
-                c.ox = (short)(j * g.wCell); c.oy = (short)(i * g.hCell); c.pad = 0;
+                c.ox = (short)(j * g.wCell); c.oy = (short)(i * g.hCell);
                 const int tw = c.cw - 6, th = c.ch - 6;
                 if (tw <= 0 || th <= 0) continue;   // FAST on a < 7 px ROI finds nothing
-                {   // words per tested row as k_fast_cells counts them (tile byte = sh + column)
+                {   // stage A of k_fast_cells walks the tile in 32-bit words (tile byte = sh + column), tested columns [3, cw - 3)
                     const int sh = (ORBFE_XO + c.x0) & 15, wLo = (sh + 3) >> 2, wHi = (sh + c.cw - 4) >> 2, nWords = wHi - wLo + 1;
+                    c.sh = (short)sh; c.wLo = (short)wLo; c.nWords = (short)nWords; c.units = (short)(th * nWords);
                     c.inv = ((1u << 20) + nWords - 1) / nWords;
+                    c.tx = (short)(ORBFE_XO + c.x0 - sh); c.ty = (short)(ORBFE_EDGE + c.y0);
+                    const int kLo = std::max(3 - (4 * wLo - sh), 0), kHi = std::min(c.cw - 3 - (4 * wHi - sh), 4);
+                    c.firstMask = kLo >= 4 ? 0u : 0x80808080u << (8 * kLo);
+                    c.lastMask = kHi <= 0 ? 0u : 0x80808080u >> (8 * (4 - kHi));
+                    if (nWords == 1) { c.firstMask &= c.lastMask; c.lastMask = c.firstMask; }
                 }
                 sp.cells.push_back(c);
                 const int keptCap = ((tw + 1) / 2) * ((th + 1) / 2);
@@ -749,8 +756,11 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
     // Chunked pipeline: the H2D copy of chunk k+1 (copy-in stream) overlaps the kernels of chunk k (main
     // stream) and the D2H copy of chunk k-1's results (copy-out stream).  Frames are staged densely
     // (row stride = width) in the input arena.
-    static const int pipeChunkEnv = [] { const char* e = getenv("ORBFE_PIPE_CHUNK"); int v = e ? atoi(e) : 0; return v > 0 ? v : ORBFE_PIPE_CHUNK; }();
-    int pipeChunk = pipeChunkEnv;
+    static const int pipeChunkEnv = [] { const char* e = getenv("ORBFE_PIPE_CHUNK"); int v = e ? atoi(e) : 0; return v > 0 ? v : 0; }();
+    // chunk = what overlaps: sized in BYTES (64 frames of 752x480 = 23 MB, measured best on B200, tools/sweep_chunk.sh), so larger
+    // frames get proportionally fewer per chunk (11 at 1920x1080) and a 32-frame HD batch still pipelines its copies
+    int pipeChunk = pipeChunkEnv ? pipeChunkEnv
+                                 : (int)std::max<size_t>(2, std::min<size_t>(ORBFE_PIPE_CHUNK, (size_t)ORBFE_PIPE_CHUNK * 752 * 480 / ((size_t)rowBytes * height)));
     while ((batch + pipeChunk - 1) / pipeChunk + 2 > ORBFE_PIPE_MAX_CHUNKS) pipeChunk *= 2;    // very long batches: larger chunks, never a refusal
     // chunk boundaries: a short first chunk (its copy-in is the only one nothing overlaps), then full chunks
     int bounds[ORBFE_PIPE_MAX_CHUNKS + 1];

@@ -52,13 +52,20 @@ struct LevelGeom {
     int planBase;          // first ColPlan of this level (pitch/4 entries), -1: no plan (generic resize kernel)
 };
 
-// One FAST cell = one CTA of k_fast (ORBextractor.cc:787-853).
-struct CellDesc {
+// One FAST cell = one CTA of k_fast (ORBextractor.cc:787-853), with everything the kernel would otherwise derive per CTA.
+struct __align__(16) CellDesc {
     short level, x0, y0, cw, ch;   // ROI-relative origin (iniX, iniY) and size (maxX-iniX, maxY-iniY)
     short ox, oy;                  // j*wCell, i*hCell
-    short pad;
-    unsigned inv;                  // ceil(2^20 / words per tested row): k_fast_cells splits a work unit index without dividing
+    short sh;                      // (ORBFE_XO + x0) & 15: tile byte = sh + column
+    short wLo, nWords;             // stage A: first tested word of a tile row, tested words per row
+    short units;                   // (ch - 6) * nWords
+    short tx, ty;                  // TMA box origin inside the bordered level (tx 16-byte aligned)
+    short pad[3];
+    unsigned inv;                  // ceil(2^20 / nWords): k_fast_cells splits a work unit index without dividing
+    unsigned firstMask, lastMask;  // 0x80 in the bytes of the first / last tested word of a row that are tested columns
+    unsigned pad2;
 };
+static_assert(sizeof(CellDesc) == 48, "CellDesc layout");
 
 // Bilinear resize coefficients of one destination column/row (OpenCV 11-bit fixed point).
 struct ResizeTap {
