@@ -214,3 +214,21 @@ def test_cuda_equals_reference_source_high_thresholds(ini, mn):
     ok, tot = check_frame(ex, ref, img, (0, 0), stages=False)
     assert ok >= 0.9999 * tot
     assert tot > 50 or ini > 235, tot
+
+
+@pytest.mark.parametrize("params", [(1000, 1.2, 8, 20, 7), (1200, 1.2, 8, 20, 7), (2000, 1.25, 5, 26, 6), (777, 1.5, 4, 18, 9),
+                                    (1500, 2.0, 3, 20, 7), (4000, 1.2, 8, 20, 7), (500, 1.1, 12, 20, 7)])
+def test_tables_equal_reference_constructor(params):
+    """orbfe_get_tables (row a1) straight against the tables the reference's own constructor builds (ORBextractor.cc:413-444,
+    read out of oracle/_ref's ORB_SLAM3::ORBextractor object) and the oracle's per-level quotas: float bit patterns."""
+    import oracle_binding as ob
+    w, h = 752, 480
+    ex = orbfe.ORBextractor(*params, max_width=w, max_height=h)
+    sc, isc, s2, is2, per, umax = OrbRef(*params).tables()
+    got = (ex.GetScaleFactors(), ex.GetInverseScaleFactors(), ex.GetScaleSigmaSquares(), ex.GetInverseScaleSigmaSquares())
+    for a, b in zip(got, (sc, isc, s2, is2)):
+        assert a.dtype == np.float32 and a.tobytes() == b.tobytes()
+    assert np.array_equal(ex.features_per_level(), per) and per.sum() >= min(params[0], per.sum())
+    if ob.ref_available():
+        for a, b in zip(got, ob.OrbSlam3Extractor(*params).tables()):
+            assert a.tobytes() == b.tobytes()

@@ -91,8 +91,8 @@ def test_lapping_match(name):
     m = orbfe.ORBmatcher()
     match, n = m.match_lapping(c["q"], c["t"], 0.7)
     assert np.array_equal(match, ob.knn2_ratio(c["q"], c["t"], 0.7))
-    if crc(c["q"], c["t"]) == int(g["in_crc"]):
-        assert np.array_equal(match, g["match"])
+    assert crc(c["q"], c["t"]) == int(g["in_crc"]), "inputs drifted from the committed fixture"
+    assert np.array_equal(match, g["match"])
     assert n == (match >= 0).sum() > 100
 
 
@@ -125,8 +125,8 @@ def test_stereo_match(name, mode):
     assert np.array_equal(u, ru) and np.array_equal(d, rd)
     assert n == (rd > 0).sum() > 0.4 * len(kL)
     g = gold(name)
-    if crc(kL, dL, kR, dR) == int(g["in_crc"]):
-        assert np.array_equal(u, g["u_right"]) and np.array_equal(d, g["depth"])
+    assert crc(kL, dL, kR, dR) == int(g["in_crc"]), "inputs drifted from the committed fixture"
+    assert np.array_equal(u, g["u_right"]) and np.array_equal(d, g["depth"])
 
 
 def test_stereo_batch_device():
@@ -160,6 +160,7 @@ def test_search_by_bow(name, matcher):
     c = mc.bow_inputs(name, extract_ref)
     g = gold(name)
     same_inputs = crc(c["d1"], c["d2"], c["mp1"], c["mp2"]) == int(g["in_crc"])
+    assert same_inputs, "inputs drifted from the committed fixture"
     m7 = orbfe.ORBmatcher(0.7, c["check_ori"])
     m8 = orbfe.ORBmatcher(0.8, c["check_ori"])
     b2a, n = m7.SearchByBoW_KF_F(c["d1"], c["fv1"], c["mp1"], c["k1"], c["d2"], c["fv2"], c["k2"], c["nleft"])
@@ -211,8 +212,8 @@ def test_search_for_triangulation(name):
                                        c["ur2"], s2, sc, c["F12"], c["ep"], c["check_ori"], c["only_stereo"], c["coarse"])
     assert n == rn and np.array_equal(m12, rm12)
     assert len(pairs) == n and np.all(np.diff(pairs[:, 0]) > 0)
-    if crc(c["d1"], c["d2"], c["mp1"], c["mp2"], c["F12"]) == int(g["in_crc"]):
-        assert n == int(g["n"]) and np.array_equal(m12, g["m12"])
+    assert crc(c["d1"], c["d2"], c["mp1"], c["mp2"], c["F12"]) == int(g["in_crc"]), "inputs drifted from the committed fixture"
+    assert n == int(g["n"]) and np.array_equal(m12, g["m12"])
 
 
 def test_empty_and_disjoint_feature_vectors():
@@ -295,13 +296,17 @@ def test_search_for_triangulation_kb8(name):
                                                      c["ep"], c["check_ori"], False, c["coarse"])
     assert n == (m12 >= 0).sum() == len(pairs) and n > 60
     for ref, refn, refp, margins in ((rm12, rn, rpts, mg), (g["m12"], int(g["n"]), g["points"], np.minimum(mg, g["margins"]))):
+        # match indices are in the bit-exact class: a row may differ only where some accept / reject threshold of its
+        # candidate pairs lies within 1e-3 (relative) of the computed value (4x4 SVD: Jacobi in double here, cv::SVD in the
+        # golden).  With the rotation check such a flip can move a histogram bin across the 10 % rule and with it rows that
+        # are themselves safe: that cascade is accepted only when an unsafe row really flipped.
         safe = margins > 1e-3
-        if safe.all():
-            assert np.array_equal(m12, ref) and n == refn
-        elif not c["check_ori"]:
-            assert np.array_equal(m12[safe], ref[safe])
+        differs = m12 != ref
+        if not (c["check_ori"] and (differs & ~safe).any()):
+            assert not (differs & safe).any(), np.flatnonzero(differs & safe)
+            assert n == refn or (differs & ~safe).any()
         else:
-            assert np.mean(m12 == ref) > 0.99
+            assert differs.mean() < 0.01
         ok = (m12 >= 0) & (m12 == ref)
         if not c["coarse"]:
             assert np.allclose(pts[ok], refp[ok], rtol=2e-3, atol=2e-4)
