@@ -372,6 +372,43 @@ def run_projection(args, orbfe, rank, local, world):
     return out
 
 
+def host_link_probe(torch, dist, world, host, dev, seconds=0.4):
+    """What the box's host memory system can feed: every rank copies its pinned batch host->device and a device buffer of the
+    result size device->host AT THE SAME TIME (two streams), all ranks concurrently, for ~`seconds`.  Returns aggregate GB/s
+    per direction (sum over ranks).  The e2e leg can not beat this: it is the ceiling the N-GPU end-to-end curve is judged on."""
+    s_in, s_out = torch.cuda.Stream(), torch.cuda.Stream()
+    out_dev = torch.empty(host.numel() // 5 + 1, dtype=torch.uint8, device="cuda")     # results are ~19 % of the input bytes
+    out_host = torch.empty(out_dev.numel(), dtype=torch.uint8).pin_memory()
+
+    def run(n_in, n_out):
+        with torch.cuda.stream(s_in):
+            for _ in range(n_in):
+                dev.copy_(host, non_blocking=True)
+        with torch.cuda.stream(s_out):
+            for _ in range(n_out):
+                out_host.copy_(out_dev, non_blocking=True)
+        s_in.synchronize()
+        s_out.synchronize()
+    res = {}
+    for name, a, b in (("h2d_alone", 1, 0), ("d2h_alone", 0, 1), ("both", 1, 1)):     # "both": the path's own mix, D2H = 1/5 of the H2D bytes
+        run(a, b)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        reps = 0
+        t0 = time.perf_counter()
+        while time.perf_counter() - t0 < seconds:
+            run(a, b)
+            reps += 1
+        dt = time.perf_counter() - t0
+        t = torch.tensor([reps * a * host.numel() / dt / 1e9, reps * b * out_dev.numel() / dt / 1e9], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t)          # sum of the ranks' rates, all measured while every rank was copying
+            dist.barrier()
+        res[name] = {"h2d_gbs": float(t[0]), "d2h_gbs": float(t[1])}
+    return res
+
+
 def bind_to_gpu_numa_node(torch, local):
     """Pins this rank's host threads (and therefore its first-touch pinned staging memory) to the NUMA node the
     GPU hangs off, so that at N > 1 the ranks' host->device streams do not cross the socket interconnect."""
@@ -485,6 +522,7 @@ def run_orbfe(args):
     barrier()
     e2e_s = time.perf_counter() - t0
 
+    link = host_link_probe(torch, dist, world, host, dev)
     # outside the timed regions: frames of the timed 512-batch (as the e2e call left them in the host buffers) against the
     # reference's own ORBextractor.cc (oracle/_ref) or, without it, the oracle port
     parity_frames = None
@@ -568,6 +606,9 @@ def run_orbfe(args):
                           "parity_checked_frames": parity_frames},
         "e2e": {"value": e2e_v, "unit": UNIT, "h2d_bytes_per_step": int(B * W * H),
                 "d2h_bytes_per_step": int(B * ex.cap * 60 + 8 * B), "ms_per_step": 1e3 * e2e_s / K,
+                "host_ceiling_gbs": link, "host_ceiling_frames_per_s": link["both"]["h2d_gbs"] * 1e9 / (W * H),
+                "host_ceiling_note": "pinned H2D of the frame batch and D2H of a result-sized buffer on two streams, all ranks at once "
+                                     "(aggregate over ranks); frames/s ceiling = concurrent H2D rate / bytes per frame",
                 "api": "orbfe_extract_batch (pinned host buffers; 64-frame chunks pipelined over copy-in / 2 compute / copy-out streams)"},
         "gpu_launches": int(launches), "graph_launches": int(graph_launches),
         "clocks": clk,

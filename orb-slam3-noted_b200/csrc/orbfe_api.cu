@@ -775,6 +775,13 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
             f = (batch - f <= pipeChunk + pipeChunk / 2 || nchunks + 1 >= ORBFE_PIPE_MAX_CHUNKS) ? batch : f + pipeChunk;
             bounds[++nchunks] = f;
         }
+        // ... and a short last chunk: its kernels and its copy-out are the tail nothing overlaps either
+        const int last = bounds[nchunks] - bounds[nchunks - 1], tail = pipeChunk / 4;
+        if (tail > 0 && last >= 3 * tail && nchunks < ORBFE_PIPE_MAX_CHUNKS) {
+            bounds[nchunks + 1] = bounds[nchunks];
+            bounds[nchunks] -= tail;
+            ++nchunks;
+        }
     }
     const int kpf = h->kpPerFrame;
     const size_t fbytes = (size_t)rowBytes * height;
