@@ -121,7 +121,10 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 
 // grid.x = ceil(total tiles / 4) (4 warps per CTA, each decodes its own tile), grid.y = frame
 #ifndef BLUR_MINB
-#define BLUR_MINB 1
+#define BLUR_MINB 4             // with the unconditional row loop the compiler hoists every load (198 registers, 2 CTAs / SM) unless capped:
+#endif                         // describe stage 1.114 ms uncapped, 1.001 at 3, 0.951 at 4 (128 registers) - profiles/r02g_variant_sweep.txt
+#ifndef BLUR_PTR
+#define BLUR_PTR 1
 #endif
 __global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
                                               const LevelGeom* __restrict__ geom, int nlevels, int totalTiles, int frame0) {
@@ -141,13 +144,19 @@ __global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restri
     const uint32_t* src = reinterpret_cast<const uint32_t*>(pyr + lvl + (long long)(y0 - 3 + ORBFE_EDGE) * g.pitch + ORBFE_XO + x0);
     uint32_t* dst = reinterpret_cast<uint32_t*>(blur + lvl + (long long)(y0 + ORBFE_EDGE) * g.pitch + ORBFE_XO + x0);
     const uint32_t qa = 18u | 34u << 8 | 48u << 16 | 56u << 24, qb = 48u | 34u << 8 | 18u << 16;
-    // The row loop is fully unrolled and its body unconditional (rows past a short last tile re-read the
-    // tile's last row, only the store is predicated), so the 7-row window rotates by register renaming.
+    // The row loop is fully unrolled and its body unconditional, so the 7-row window rotates by register renaming.  Rows
+    // past a short last tile are simply read (the level's own bottom border and, beyond it, the arena's slack: the results
+    // of those rows are never stored) - only the store is predicated, and source / destination advance by one pitch per
+    // row (a clamped row index cost a 64-bit multiply-add per row: 12.6 % of the kernel's instructions, profiles/r01o_*).
     uint32_t h[7][4];
-    const int lastRow = rows + 5;
 #pragma unroll
     for (int r = 0; r < BLUR_TH + 6; ++r) {
-        const uint32_t* p = src + (long long)min(r, lastRow) * pw;
+#if BLUR_PTR
+        const uint32_t* p = src;
+        src += pw;
+#else
+        const uint32_t* p = src + (long long)min(r, rows + 5) * pw;
+#endif
         const uint32_t wm = __ldg(p - 1), w0 = __ldg(p), wp = __ldg(p + 1);
 #pragma unroll
         for (int j = 0; j < 6; ++j)
@@ -163,7 +172,12 @@ __global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restri
             for (int k = 0; k < 4; ++k)     // < 2^24: the rounded result is byte 2
                 v[k] = 18u * (h[0][k] + h[6][k]) + 34u * (h[1][k] + h[5][k]) + 48u * (h[2][k] + h[4][k]) + 56u * h[3][k] + 32768u;
             const uint32_t o = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+#if BLUR_PTR
+            if (r - 6 < rows) *dst = o;
+            dst += pw;
+#else
             if (r - 6 < rows) dst[(long long)(r - 6) * pw] = o;
+#endif
         }
     }
 }

@@ -92,6 +92,9 @@ __device__ __forceinline__ void tma_load_3d(void* dst, const CUtensorMap* map, i
 #ifndef FAST_MINB
 #define FAST_MINB 8
 #endif
+#ifndef FAST_PAD
+#define FAST_PAD 0             // measured on B200 (profiles/r02g_variant_sweep.txt): 1.287 ms with the re-pitch vs 1.243 without - the extra pass and
+#endif                         // barrier cost more than the bank conflicts they remove; kept selectable
 // TPC = tile pitch known at compile time (64: every BASELINE shape, cells up to 49 px wide) or 0 = runtime boxW.  With a constant
 // pitch the 16 ring offsets, the +-3-row word offsets of stage A and the index -> (x, y) split are immediates / shifts.
 // Everything that depends only on the cell (tested-word range, edge masks, TMA coordinates) or only on the launch (list
@@ -108,12 +111,19 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
     __shared__ __align__(8) uint64_t sBar;
     __shared__ int sCand, sCorners, sKept, sBase;
     const int frame = frame0 + blockIdx.y;
-    const int tp = TPC ? TPC : boxW;         // dense tile as delivered by TMA
+    // FAST_PAD (TPC = 64 only): TMA delivers a dense 64-byte-pitch tile, which puts rows r and r + 2 on the same banks - a
+    // vertical edge (survivors at one column of consecutive rows) then makes every ring load a 16-way bank conflict, and stage
+    // A's three-row word loads conflict 2-way.  The tile is re-pitched once to 68 bytes (17 words, odd) right after it lands;
+    // the dense TMA destination aliases the two lists (written only after the re-pitch).
+    constexpr bool kPad = FAST_PAD && TPC == 64;
+    const int tp = kPad ? 68 : TPC ? TPC : boxW;         // pitch of the tile and of the score map the stages work on
+    const int mapBytes = kPad ? (tileBytes >> 6) * 68 : tileBytes;
     uint8_t* tile = smem;
-    uint8_t* score = tile + ((tileBytes + 127) & ~127);   // TMA destinations must be 128-byte aligned
-    uint16_t* list1 = reinterpret_cast<uint16_t*>(score + tileBytes);        // survivors of the quick test
+    uint8_t* score = tile + ((mapBytes + 127) & ~127);   // TMA destinations must be 128-byte aligned
+    uint16_t* list1 = reinterpret_cast<uint16_t*>(score + ((mapBytes + 127) & ~127));      // survivors of the quick test
     uint16_t* list2 = list1 + listCap;                                       // corners
     uint32_t* kept = reinterpret_cast<uint32_t*>(list2 + listCap);
+    uint8_t* landing = kPad ? reinterpret_cast<uint8_t*>(list1) : tile;      // where TMA writes
     const int tid = threadIdx.x;
     const int nw = tp >> 2;
     const CellDesc cd = cells[blockIdx.x];
@@ -123,7 +133,7 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
         mbar_expect_tx(&sBar, (uint32_t)tileBytes);
         // TMA wants the innermost start coordinate on a 16-byte boundary: the box starts at the aligned column below the
         // cell (cd.tx); tile byte = cd.sh + column.
-        tma_load_3d(tile, &maps.m[cd.level], cd.tx, cd.ty, frame, &sBar);
+        tma_load_3d(landing, &maps.m[cd.level], cd.tx, cd.ty, frame, &sBar);
     }
 
     int off[16];
@@ -141,9 +151,17 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
     int t = iniTh;
     for (int pass = 0; pass < 2; ++pass) {
         if (tid == 0) { sCand = 0; sCorners = 0; sKept = 0; }
-        for (int i = tid; i < tileBytes / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
+        for (int i = tid; i < (mapBytes + 15) / 16; i += FAST_THREADS) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
         __syncthreads();                       // also orders the mbarrier init before everyone's wait
-        if (pass == 0) mbar_wait(&sBar, 0);
+        if (pass == 0) {
+            mbar_wait(&sBar, 0);
+            if (kPad) {                        // dense 16-word rows -> 17-word rows; both sides conflict-free
+                const uint32_t* src = reinterpret_cast<const uint32_t*>(landing);
+                uint32_t* dst = reinterpret_cast<uint32_t*>(tile);
+                for (int i = tid; i < tileBytes / 4; i += FAST_THREADS) dst[i + (i >> 4)] = src[i];
+                __syncthreads();               // the lists reuse the landing area
+            }
+        }
         // A: necessary condition on two opposite ring pairs, 4 pixels per step.  A 9-arc covers at least one pixel of every
         // opposite pair, so a corner has |c - v| > t for v0 or v8 AND for v4 or v12.  Bit 7 of every byte of m = "may be a corner".
         {
@@ -203,7 +221,8 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
             }
             const int slot = keep ? atomicAdd(&sKept, 1) : -1;
             if (slot >= 0) {
-                const int y = TPC ? idx / TPC : (int)(((uint32_t)idx * invTp) >> 20), x = idx - y * tp - cd.sh;
+                const int y = kPad ? (int)(((uint32_t)idx * 15421u) >> 20) : TPC ? idx / TPC : (int)(((uint32_t)idx * invTp) >> 20);
+                const int x = idx - y * tp - cd.sh;
                 kept[slot] = (uint32_t)(x + cd.ox) | (uint32_t)(y + cd.oy) << 11 | (uint32_t)s << 22;
             }
         }
@@ -226,7 +245,8 @@ cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
     if (e != cudaSuccess) return e;
     const int tileBytes = h->fastBoxW * h->fastBoxH;
     const size_t tileStride = ((size_t)tileBytes + 127) & ~(size_t)127;
-    const size_t smem = (size_t)h->maxCellBytes + tileStride - (size_t)tileBytes;   // maxCellBytes counts one unpadded tile
+    // maxCellBytes counts two unpadded maps; FAST_PAD re-pitches both to 68 bytes and 128-byte-aligns them
+    const size_t smem = (size_t)h->maxCellBytes + 2 * (tileStride - (size_t)tileBytes) + (FAST_PAD && h->fastBoxW == 64 ? 2 * ((size_t)h->fastBoxH * 4 + 128) : 0);
     const int listCap = ((h->fastBoxW - 6) * (h->fastBoxH - 6) + 1) & ~1;
     const uint32_t invTp = ((1u << 20) + h->fastBoxW - 1) / h->fastBoxW;   // idx / tp == (idx * invTp) >> 20 (a tile has < 2^14 bytes)
     dim3 grid(h->nCellsTotal, batch);

@@ -326,7 +326,7 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     plan_shape(h, W, H, sp);
     if (sp.status != ORBFE_OK) return sp.status;
     const size_t B = (size_t)h->p.max_batch;
-    if (sp.pyrBytesPerFrame * B > h->pyrBytes || (size_t)sp.candPerFrame * B > h->candEntries ||
+    if (sp.pyrBytesPerFrame * B + (size_t)(ORBFE_BLUR_TH + 8) * sp.geom[0].pitch > h->pyrBytes || (size_t)sp.candPerFrame * B > h->candEntries ||
         (int)sp.cells.size() > h->cellCap || (int)sp.taps.size() > h->tabCap || sp.kpPerFrame > h->kpCapPerFrame ||
         (int)sp.plans.size() > h->planCap)
         return ORBFE_ERR_TOO_LARGE;
@@ -379,7 +379,9 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     if (sp.status != ORBFE_OK) { delete h; return sp.status; }
     const size_t B = (size_t)p.max_batch;
     // a little slack so that smaller shapes whose rounding goes the other way still fit
-    h->pyrBytes = sp.pyrBytesPerFrame * B + 4096;
+    // slack: smaller shapes whose rounding goes the other way, and k_blur's unconditional reads of up to ORBFE_BLUR_TH rows past a
+    // short last tile of the last level plane
+    h->pyrBytes = sp.pyrBytesPerFrame * B + 4096 + (size_t)(ORBFE_BLUR_TH + 8) * sp.geom[0].pitch;
     h->candEntries = ((size_t)sp.candPerFrame + 256) * B;
     h->cellCap = (int)sp.cells.size() + 64;
     h->tabCap = (int)sp.taps.size() + 64;
@@ -775,13 +777,7 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
             f = (batch - f <= pipeChunk + pipeChunk / 2 || nchunks + 1 >= ORBFE_PIPE_MAX_CHUNKS) ? batch : f + pipeChunk;
             bounds[++nchunks] = f;
         }
-        // ... and a short last chunk: its kernels and its copy-out are the tail nothing overlaps either
-        const int last = bounds[nchunks] - bounds[nchunks - 1], tail = pipeChunk / 4;
-        if (tail > 0 && last >= 3 * tail && nchunks < ORBFE_PIPE_MAX_CHUNKS) {
-            bounds[nchunks + 1] = bounds[nchunks];
-            bounds[nchunks] -= tail;
-            ++nchunks;
-        }
+        // (a tapering tail - shorter last chunks - was measured in round 1 and had no effect: the path sits on the PCIe link)
     }
     const int kpf = h->kpPerFrame;
     const size_t fbytes = (size_t)rowBytes * height;
