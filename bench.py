@@ -211,19 +211,24 @@ def run_matching(args, torch, orbfe, rank, local, world, barrier, dist):
         m.knn2_batch_device(d_desc, cap * 32, d_n, cap, d_desc + cap * 32, cap * 32, d_n + 4, cap, B - 1, idx.data_ptr(),
                             dst.data_ptr())
 
-    for _ in range(Wm):
-        step()
-    m.synchronize()
-    barrier()
-    l0 = m.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record(stream)
-    for _ in range(K):
-        step()
-    e1.record(stream)
-    barrier()
-    ms = e0.elapsed_time(e1)
-    launches = m.launch_count() - l0
+    def timed(backend):
+        m.set_knn2_backend(backend)
+        for _ in range(Wm):
+            step()
+        m.synchronize()
+        barrier()
+        l0 = m.launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(K):
+            step()
+        e1.record(stream)
+        barrier()
+        return e0.elapsed_time(e1), m.launch_count() - l0, (idx.cpu().numpy().copy(), dst.cpu().numpy().copy())
+
+    ms_popc, launches_popc, out_popc = timed(m.KNN2_POPC)
+    ms, launches, out_tc = timed(m.KNN2_TENSOR)           # the headline backend; it stays selected for the e2e leg below
+    same = bool(all(np.array_equal(a[b, :n[b]], c[b, :n[b]]) for a, c in zip(out_popc, out_tc) for b in range(B - 1)))
     # end to end: the host-buffer call, one frame pair per call
     descs = [r[2] for r in res]
     for _ in range(Wm):
@@ -236,13 +241,19 @@ def run_matching(args, torch, orbfe, rank, local, world, barrier, dist):
     barrier()
     e2e_s = time.perf_counter() - t0
     if world > 1:
-        t = torch.tensor([ms, e2e_s * 1e3], dtype=torch.float64, device="cuda")
+        t = torch.tensor([ms, e2e_s * 1e3, ms_popc], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_s = float(t[0]), float(t[1]) / 1e3
+        ms, e2e_s, ms_popc = float(t[0]), float(t[1]) / 1e3, float(t[2])
     if rank != 0:
         return None
     value = world * K * pairs_per_step / (ms / 1e3)
+    value_popc = world * K * pairs_per_step / (ms_popc / 1e3)
     popc = orbfe.measure_popc_peak(local)
+    try:
+        bf16 = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops"])
+        i8_peak, i8_src = 2 * bf16, "2 x MEASURED_PEAKS.json bf16_tflops (int8 dense = 2 x bf16 dense on B200; no int8 figure is measured)"
+    except Exception:
+        i8_peak, i8_src = 4500.0, "nominal 4.5 POP/s dense int8 (no MEASURED_PEAKS.json)"
     out = {
         "metric": "Hamming matches/s (descriptor pairs evaluated per second)", "value": value, "unit": "pairs/s",
         "ms_per_step": ms / K, "gpu_launches": int(launches),
@@ -251,9 +262,15 @@ def run_matching(args, torch, orbfe, rank, local, world, barrier, dist):
         "e2e": {"value": world * K * pairs_per_step / e2e_s, "unit": "pairs/s",
                 "h2d_bytes_per_step": int(32 * (n[:-1] + n[1:]).sum()), "d2h_bytes_per_step": int(16 * n[:-1].sum()),
                 "api": "orbfe_hamming_knn2 (host buffers), one call per frame pair"},
-        "roofline": {"bound": "int-popc", "kernel": "k_knn2", "achieved": value / world * 8 / 1e12, "peak": popc / 1e12,
-                     "unit": "Tpopc/s", "frac": value / world * 8 / popc, "peak_source": "measured (orbfe_measure_popc_peak)",
-                     "popc_per_pair": 8},
+        "backend": "tensor (tcgen05.mma kind::i8, csrc/k_knn2_tc.cu); results identical to the POPC kernel: " + str(same),
+        "roofline": {"bound": "tensor", "kernel": "k_knn2_tc", "achieved": value / world * 576 / 1e12, "peak": i8_peak, "unit": "TOP/s",
+                     "frac": value / world * 576 / 1e12 / i8_peak, "peak_source": i8_src, "traffic": None,
+                     "ops_per_pair": 576, "note": "2 x 288 int8 multiply-adds per descriptor pair (256 descriptor bits + a 32-wide K slice that "
+                                                  "carries the train index); the XOR + POPC form of the same pair is 8 POPC"},
+        "popc_backend": {"value": value_popc, "unit": "pairs/s", "ms_per_step": ms_popc / K, "gpu_launches": int(launches_popc),
+                         "roofline": {"bound": "int-popc", "kernel": "k_knn2", "achieved": value_popc / world * 8 / 1e12, "peak": popc / 1e12,
+                                      "unit": "Tpopc/s", "frac": value_popc / world * 8 / popc,
+                                      "peak_source": "measured (orbfe_measure_popc_peak)", "popc_per_pair": 8}},
     }
     if world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1

@@ -205,6 +205,14 @@ int orbfe_hamming_knn2(orbfe_matcher* m, const uint8_t* q, int nq, const uint8_t
 int orbfe_hamming_knn2_batch_device(orbfe_matcher* m, const uint8_t* d_q, ptrdiff_t q_stride, const int* d_nq, int nq_max,
                                     const uint8_t* d_t, ptrdiff_t t_stride, const int* d_nt, int nt_max, int batch,
                                     int32_t* d_idx2, int32_t* d_dist2);
+/* The brute-force 2-NN has two exact implementations: XOR + POPC on the integer pipe, and the tensor cores (tcgen05.mma
+ * kind::i8 on descriptors expanded to signed bytes; the accumulator is 256 * hamming + index).  Both give
+ * identical indices and distances.  Default: ORBFE_KNN2_DEFAULT, overridden per process by the environment variable
+ * ORBFE_KNN2=popc|tensor and per matcher by this call. */
+enum { ORBFE_KNN2_POPC = 0, ORBFE_KNN2_TENSOR = 1 };
+#define ORBFE_KNN2_DEFAULT ORBFE_KNN2_TENSOR
+int orbfe_matcher_set_knn2_backend(orbfe_matcher* m, int backend);
+
 /* Allocation-free form of orbfe_hamming_knn2 on DEVICE buffers.  No counterpart in the reference: added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Needs no orbfe_matcher; calls no cudaMalloc / cudaFree / allocating routine.  The kernels'

@@ -1,0 +1,297 @@
+// k_knn2_tc.cu — brute-force Hamming 2-NN on the 5th-generation tensor cores (tcgen05.mma kind::i8, TMEM accumulators).
+//
+// Same contract as k_knn2 (k_match.cu): cv::BFMatcher(NORM_HAMMING).knnMatch(k = 2) as Frame::ComputeStereoFishEyeMatches
+// uses it (Frame.cc:43,1134), distances of ORBmatcher::DescriptorDistance (ORBmatcher.cc:2561-2577), ties to the lowest
+// train index.  Integer arithmetic end to end, so indices and distances are bit-identical to the POPC kernel.
+//
+// All-pairs Hamming IS a dense contraction: with descriptor bits expanded to signed bytes, a_k = +-64 for the query and
+// b_k = -+2 for the train row, a_k * b_k = -128 where the bits agree and +128 where they differ, so
+//     sum_k a_k b_k = 256 * hamming - 32768.
+// A 17th-and-18th 16-byte K chunk carries (2, 1, 0, ...) on the query side and (j >> 1, j & 1, 0, ...) on the train side,
+// j = the row's position inside its 256-row tile, which adds exactly j.  The accumulator therefore holds
+//     D = 256 * hamming + j - 32768,
+// whose signed minimum over a tile IS "smallest distance, ties to the lowest index": the epilogue is a two-smallest
+// reduction over raw accumulators (2.5 instructions per pair instead of the 27 of the XOR + POPC form) and the distance
+// and index are unpacked from the two survivors only.
+//
+// One CTA = 128 queries (the 128 TMEM lanes) x one split of the train set, streamed in tiles of 256 rows:
+//   warps 4-7  producers: expand the tile's descriptors (32 B each) to 288-byte K-major rows of signed bytes through a 256-entry
+//              byte -> 8-byte table, into the canonical no-swizzle UMMA layout (8-row x 16-byte core matrices), two stages;
+//   warp 8     one elected thread issues 9 x tcgen05.mma (M 128, N 256, K 32) per tile into one of two 256-column TMEM
+//              accumulators and commits to mbarriers (frees the smem stage, publishes the accumulator);
+//   warps 0-3  epilogue: tcgen05.ld 32 columns at a time (thread = query row), two-smallest update, then release the accumulator.
+// Roles meet only through mbarriers; generic-proxy writes are fenced (fence.proxy.async) before the tensor core reads them.
+#include <limits.h>
+
+#include "orbfe_internal.h"
+#include "orbfe_match.h"
+
+#define TC_M 128                 // queries per CTA = TMEM lanes
+#define TC_N 256                 // train rows per tile = accumulator columns
+#define TC_CHUNKS 18             // 16-byte K chunks per row: 16 of descriptor bits + 2 carrying the row index
+#define TC_THREADS 288
+#define TC_A_BYTES (TC_M * 16 * TC_CHUNKS)        // 36864
+#define TC_B_BYTES (TC_N * 16 * TC_CHUNKS)        // 73728
+#define TC_SMEM (TC_A_BYTES + 2 * TC_B_BYTES + 2 * 2048 + 256)
+#define KNN_IDX_BITS 20
+#define KNN_IDX_MASK ((1u << KNN_IDX_BITS) - 1u)
+#define KNN_NONE 0xFFFFFFFFu
+
+namespace {
+
+__device__ __forceinline__ uint32_t s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void bar_init(uint64_t* bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count));
+}
+__device__ __forceinline__ void bar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(bar)) : "memory");
+}
+__device__ __forceinline__ void bar_wait(uint64_t* bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "W_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra D_%=;\n"
+        "bra W_%=;\n"
+        "D_%=:\n"
+        "}\n" ::"r"(s32(bar)),
+        "r"(parity)
+        : "memory");
+}
+__device__ __forceinline__ void fence_async_proxy() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// Shared-memory matrix descriptor, K-major, no swizzle: 8-row x 16-byte core matrices of 128 contiguous bytes; LBO = distance
+// between the two 16-byte K chunks of one MMA, SBO = distance between 8-row groups (both in 16-byte units); version 1 (sm_100).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t smemAddr, uint32_t lbo16, uint32_t sbo16) {
+    return (uint64_t)((smemAddr >> 4) & 0x3FFFu) | (uint64_t)(lbo16 & 0x3FFFu) << 16 | (uint64_t)(sbo16 & 0x3FFFu) << 32 | 1ull << 46;
+}
+// Instruction descriptor of kind::i8: D = S32, A = B = signed 8-bit, both K-major, N = 256, M = 128.
+__device__ constexpr uint32_t kIdesc = 2u << 4 | 1u << 7 | 1u << 10 | (uint32_t)(TC_N >> 3) << 17 | (uint32_t)(TC_M >> 4) << 24;
+
+__device__ __forceinline__ void umma_i8(uint32_t tmemD, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::i8 [%0], %1, %2, %3, {%5, %5, %5, %5}, p;\n"
+        "}\n" ::"r"(tmemD),
+        "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate), "r"(0u)
+        : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, int (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, "
+        "%21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]),
+          "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+          "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]),
+          "=r"(v[31])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Two smallest of {m0 <= m1} and two new values (5 instructions per two accumulators).
+__device__ __forceinline__ void two_min2(int& m0, int& m1, int a, int b) {
+    const int lo = min(a, b), hi = max(a, b);
+    m1 = __vimin3_s32(max(m0, lo), m1, hi);
+    m0 = min(m0, lo);
+}
+__device__ __forceinline__ void key_update(uint32_t& k0, uint32_t& k1, uint32_t k) {
+    const uint32_t hi = max(k0, k);
+    k0 = min(k0, k);
+    k1 = min(k1, hi);
+}
+
+// One descriptor row (32 bytes, `words`) -> 18 K chunks of signed bytes at row `r` of a tile of R rows; extra = the two
+// bytes of the index-carrying chunk.
+__device__ __forceinline__ void expand_row(uint8_t* tile, int R, int r, const uint4& w0, const uint4& w1, const uint2* __restrict__ lut,
+                                           uint32_t extra) {
+    uint8_t* row = tile + (r >> 3) * 128 + (r & 7) * 16;
+    const uint32_t w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+    const int cstride = R * 16;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const uint2 a = lut[w[i] & 0xFFu], b = lut[(w[i] >> 8) & 0xFFu], c = lut[(w[i] >> 16) & 0xFFu], d = lut[w[i] >> 24];
+        *reinterpret_cast<uint4*>(row + (2 * i) * cstride) = make_uint4(a.x, a.y, b.x, b.y);
+        *reinterpret_cast<uint4*>(row + (2 * i + 1) * cstride) = make_uint4(c.x, c.y, d.x, d.y);
+    }
+    *reinterpret_cast<uint4*>(row + 16 * cstride) = make_uint4(extra, 0u, 0u, 0u);
+    *reinterpret_cast<uint4*>(row + 17 * cstride) = make_uint4(0u, 0u, 0u, 0u);
+}
+
+}  // namespace
+
+// grid = (query tiles of 128, train splits, batch)
+__global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __restrict__ q, long long qStride, const int* __restrict__ nqArr,
+                                                          int nqMax, const uint8_t* __restrict__ t, long long tStride,
+                                                          const int* __restrict__ ntArr, int ntMax, int splitLen,
+                                                          uint2* __restrict__ partial, int32_t* __restrict__ idx2, int32_t* __restrict__ dist2) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    __shared__ __align__(8) uint64_t aFull, bFull[2], bEmpty[2], accFull[2], accEmpty[2];
+    __shared__ uint32_t sTmem;
+    const int b = blockIdx.z, split = blockIdx.y, nsplit = gridDim.y;
+    const int nq = nqArr ? min(nqArr[b], nqMax) : nqMax;
+    const int nt = ntArr ? min(ntArr[b], ntMax) : ntMax;
+    const int q0 = blockIdx.x * TC_M;
+    if (q0 >= nq) return;
+    const int t0 = split * splitLen, t1 = min(t0 + splitLen, nt);
+    const int ntiles = t1 > t0 ? (t1 - t0 + TC_N - 1) / TC_N : 0;
+    uint8_t* sA = smem;
+    uint8_t* sB = smem + TC_A_BYTES;
+    uint2* lutA = reinterpret_cast<uint2*>(smem + TC_A_BYTES + 2 * TC_B_BYTES);
+    uint2* lutB = lutA + 256;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+
+    if (tid == 0) {
+        bar_init(&aFull, 128);
+        for (int s = 0; s < 2; ++s) { bar_init(&bFull[s], 128); bar_init(&bEmpty[s], 1); bar_init(&accFull[s], 1); bar_init(&accEmpty[s], 128); }
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (tid < 256) {            // byte -> 8 signed bytes: query +-64, train -+2 (bit i of the byte -> output byte i)
+        uint32_t a[2] = {0u, 0u}, c[2] = {0u, 0u};
+        for (int i = 0; i < 8; ++i) {
+            const uint32_t bit = (tid >> i) & 1u;
+            a[i >> 2] |= (bit ? 0x40u : 0xC0u) << (8 * (i & 3));
+            c[i >> 2] |= (bit ? 0xFEu : 0x02u) << (8 * (i & 3));
+        }
+        lutA[tid] = make_uint2(a[0], a[1]);
+        lutB[tid] = make_uint2(c[0], c[1]);
+    }
+    if (warp == 8) {            // the whole TMEM of the SM: two accumulators of 256 columns (one CTA per SM by shared memory)
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&sTmem)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = sTmem;
+
+    if (warp >= 4 && warp < 8) {
+        // ---- producers
+        const int p = tid - 128;
+        {
+            uint4 w0 = make_uint4(0u, 0u, 0u, 0u), w1 = w0;
+            if (q0 + p < nq) {
+                const uint4* src = reinterpret_cast<const uint4*>(q + (long long)b * qStride) + 2 * (long long)(q0 + p);
+                w0 = __ldg(src); w1 = __ldg(src + 1);
+            }
+            expand_row(sA, TC_M, p, w0, w1, lutA, 0x00000102u);
+            fence_async_proxy();
+            bar_arrive(&aFull);
+        }
+        const uint4* tp = reinterpret_cast<const uint4*>(t + (long long)b * tStride);
+        for (int i = 0; i < ntiles; ++i) {
+            const int s = i & 1;
+            bar_wait(&bEmpty[s], ((i >> 1) & 1) ^ 1);
+            uint8_t* tile = sB + s * TC_B_BYTES;
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const int r = p + 128 * h, g = t0 + i * TC_N + r;
+                uint4 w0 = make_uint4(0u, 0u, 0u, 0u), w1 = w0;
+                if (g < t1) { w0 = __ldg(tp + 2 * (long long)g); w1 = __ldg(tp + 2 * (long long)g + 1); }
+                expand_row(tile, TC_N, r, w0, w1, lutB, (uint32_t)(r >> 1) | (uint32_t)(r & 1) << 8);
+            }
+            fence_async_proxy();
+            bar_arrive(&bFull[s]);
+        }
+    } else if (warp == 8) {
+        // ---- MMA issuer: one thread
+        if (lane == 0 && ntiles > 0) {
+            bar_wait(&aFull, 0);
+            const uint32_t aBase = s32(sA), bBase = s32(sB);
+            for (int i = 0; i < ntiles; ++i) {
+                const int s = i & 1;
+                bar_wait(&bFull[s], (i >> 1) & 1);
+                bar_wait(&accEmpty[s], ((i >> 1) & 1) ^ 1);
+                tc_fence_after();
+#pragma unroll
+                for (int k = 0; k < TC_CHUNKS / 2; ++k) {
+                    const uint64_t ad = umma_desc(aBase + 2 * k * TC_M * 16, TC_M, 8);
+                    const uint64_t bd = umma_desc(bBase + s * TC_B_BYTES + 2 * k * TC_N * 16, TC_N, 8);
+                    umma_i8(tmem + s * TC_N, ad, bd, k > 0);
+                }
+                umma_commit(&bEmpty[s]);       // the stage may be overwritten once these MMAs have read it
+                umma_commit(&accFull[s]);      // ... and the accumulator is complete
+            }
+        }
+    } else {
+        // ---- epilogue: thread = query row = TMEM lane
+        uint32_t k0 = KNN_NONE, k1 = KNN_NONE;
+        const uint32_t laneBase = tmem + ((uint32_t)(warp * 32) << 16);
+        for (int i = 0; i < ntiles; ++i) {
+            const int s = i & 1;
+            bar_wait(&accFull[s], (i >> 1) & 1);
+            tc_fence_after();
+            const int base = t0 + i * TC_N, valid = min(TC_N, t1 - base);
+            int m0 = INT_MAX, m1 = INT_MAX;
+#pragma unroll 1
+            for (int cb = 0; cb < TC_N; cb += 32) {
+                int v[32];
+                tmem_ld32(laneBase + s * TC_N + cb, v);
+                tmem_ld_wait();
+                if (cb + 32 > valid) {         // the last tile of a split: rows past the end do not exist
+#pragma unroll
+                    for (int j = 0; j < 32; ++j)
+                        if (cb + j >= valid) v[j] = INT_MAX;
+                }
+#pragma unroll
+                for (int j = 0; j < 32; j += 2) two_min2(m0, m1, v[j], v[j + 1]);
+            }
+            tc_fence_before();
+            bar_arrive(&accEmpty[s]);
+            // D = 256 * hamming + j - 32768  ->  packed key  hamming << 20 | train index
+            if (m0 != INT_MAX) { const uint32_t x = (uint32_t)(m0 + 32768); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
+            if (m1 != INT_MAX) { const uint32_t x = (uint32_t)(m1 + 32768); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
+        }
+        const int qi = q0 + tid;
+        if (qi < nq) {
+            if (nsplit == 1) {
+                const long long o = ((long long)b * nqMax + qi) * 2;
+                idx2[o] = k0 == KNN_NONE ? -1 : (int)(k0 & KNN_IDX_MASK);
+                dist2[o] = k0 == KNN_NONE ? -1 : (int)(k0 >> KNN_IDX_BITS);
+                idx2[o + 1] = k1 == KNN_NONE ? -1 : (int)(k1 & KNN_IDX_MASK);
+                dist2[o + 1] = k1 == KNN_NONE ? -1 : (int)(k1 >> KNN_IDX_BITS);
+            } else {
+                partial[((long long)b * nsplit + split) * nqMax + qi] = make_uint2(k0, k1);
+            }
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+}
+
+// Train splits for the tensor-core kernel: tiles of 256 rows, about two CTAs' worth of work per SM.
+void orbfe_knn2_tc_plan(int nqMax, int ntMax, int batch, int smCount, int* nsplit, int* splitLen) {
+    const long long ctas = (long long)((nqMax + TC_M - 1) / TC_M) * batch;
+    const int tiles = (ntMax + TC_N - 1) / TC_N;
+    long long s = ctas > 0 ? (2LL * smCount + ctas - 1) / ctas : 1;
+    s = s < 1 ? 1 : s > tiles ? tiles : s;
+    if (s > 64) s = 64;
+    const int per = (int)((tiles + s - 1) / (s > 0 ? s : 1));
+    *splitLen = (per < 1 ? 1 : per) * TC_N;
+    const int n = (ntMax + *splitLen - 1) / *splitLen;
+    *nsplit = n < 1 ? 1 : n;
+}
+
+cudaError_t orbfe_launch_knn2_tc(cudaStream_t st, const uint8_t* dq, long long qStride, const int* dNq, int nqMax, const uint8_t* dt,
+                                 long long tStride, const int* dNt, int ntMax, int batch, int nsplit, int splitLen, uint2* dPartial,
+                                 int32_t* dIdx2, int32_t* dDist2, long long* launches) {
+    if (nqMax <= 0 || batch <= 0) return cudaSuccess;
+    if (ntMax > (int)KNN_IDX_MASK || splitLen % TC_N != 0) return cudaErrorInvalidValue;
+    const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_knn2_tc), TC_SMEM);
+    if (ea != cudaSuccess) return ea;
+    dim3 grid((nqMax + TC_M - 1) / TC_M, nsplit, batch);
+    k_knn2_tc<<<grid, TC_THREADS, TC_SMEM, st>>>(dq, qStride, dNq, nqMax, dt, tStride, dNt, ntMax, splitLen, dPartial, dIdx2, dDist2);
+    ++*launches;
+    if (nsplit > 1) return orbfe_launch_knn2_merge(st, dPartial, dNq, nqMax, nsplit, batch, dIdx2, dDist2, launches);
+    return cudaGetLastError();
+}

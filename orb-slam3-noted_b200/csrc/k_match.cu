@@ -137,6 +137,14 @@ cudaError_t orbfe_launch_knn2(cudaStream_t st, const uint8_t* dq, long long qStr
     return cudaGetLastError();
 }
 
+cudaError_t orbfe_launch_knn2_merge(cudaStream_t st, const uint2* dPartial, const int* dNq, int nqMax, int nsplit, int batch, int32_t* dIdx2,
+                                    int32_t* dDist2, long long* launches) {
+    dim3 g2((nqMax + KNN_THREADS - 1) / KNN_THREADS, batch);
+    k_knn2_merge<<<g2, KNN_THREADS, 0, st>>>(dPartial, dNq, nqMax, nsplit, dIdx2, dDist2);
+    ++*launches;
+    return cudaGetLastError();
+}
+
 // ---- allocation-free 2-NN (no counterpart in the reference) -----------------
 // For callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it):
 // the same k_knn2 / k_knn2_merge pair, with the per-split partial keys in a file-scope device array instead of the matcher's

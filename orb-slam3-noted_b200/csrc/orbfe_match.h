@@ -37,6 +37,13 @@ struct TriGeo {
 };
 
 struct UndistortGeo { double fx, fy, cx, cy, k1, k2, p1, p2, k3; };
+// brute-force 2-NN: the POPC kernel (k_match.cu) and the tensor-core kernel (k_knn2_tc.cu), same arguments and results
+cudaError_t orbfe_launch_knn2_merge(cudaStream_t st, const uint2* dPartial, const int* dNq, int nqMax, int nsplit, int batch, int32_t* dIdx2,
+                                    int32_t* dDist2, long long* launches);
+void orbfe_knn2_tc_plan(int nqMax, int ntMax, int batch, int smCount, int* nsplit, int* splitLen);
+cudaError_t orbfe_launch_knn2_tc(cudaStream_t st, const uint8_t* dq, long long qStride, const int* dNq, int nqMax, const uint8_t* dt,
+                                 long long tStride, const int* dNt, int ntMax, int batch, int nsplit, int splitLen, uint2* dPartial,
+                                 int32_t* dIdx2, int32_t* dDist2, long long* launches);
 cudaError_t orbfe_launch_undistort(cudaStream_t st, orbfe_keypoint* dKps, int n, const UndistortGeo& g, long long* launches);
 cudaError_t orbfe_launch_distinctive(cudaStream_t st, const uint8_t* dDesc, const int32_t* dOffsets, int npoints, int32_t* dBest,
                                      long long* launches);

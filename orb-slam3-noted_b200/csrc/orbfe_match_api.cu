@@ -3,6 +3,7 @@
 // all grown on demand), host-side flattening of the reference's inputs and the launches.
 // No CPU fallback: every entry point needs the CUDA device the matcher was created on.
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -24,6 +25,7 @@ struct orbfe_matcher {
     int checkOri;
     int device;
     int smCount;
+    int knnBackend;              // ORBFE_KNN2_POPC / ORBFE_KNN2_TENSOR
     cudaStream_t stream;
     cudaEvent_t ev;
     long long launches;
@@ -79,6 +81,10 @@ extern "C" int orbfe_matcher_create(float nnratio, int check_orientation, int de
     m->nnRatio = nnratio;
     m->checkOri = check_orientation ? 1 : 0;
     m->device = device;
+    {
+        const char* env = getenv("ORBFE_KNN2");
+        m->knnBackend = env && !strcmp(env, "popc") ? ORBFE_KNN2_POPC : env && !strcmp(env, "tensor") ? ORBFE_KNN2_TENSOR : ORBFE_KNN2_DEFAULT;
+    }
     cudaError_t e = cudaSetDevice(device);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&m->stream, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaEventCreateWithFlags(&m->ev, cudaEventDisableTiming);
@@ -117,16 +123,28 @@ extern "C" int orbfe_hamming_knn2_batch_device(orbfe_matcher* m, const uint8_t* 
     if (nt_max >= (1 << 20)) return ORBFE_ERR_TOO_LARGE;
     if (nq_max == 0 || batch == 0) return ORBFE_OK;
     CK(cudaSetDevice(m->device));
+    const bool tensor = m->knnBackend == ORBFE_KNN2_TENSOR;
     int nsplit = 1, splitLen = nt_max;
-    orbfe_knn2_plan(nq_max, nt_max, batch, m->smCount, &nsplit, &splitLen);
+    if (tensor) orbfe_knn2_tc_plan(nq_max, nt_max, batch, m->smCount, &nsplit, &splitLen);
+    else orbfe_knn2_plan(nq_max, nt_max, batch, m->smCount, &nsplit, &splitLen);
     uint2* partial = nullptr;
     if (nsplit > 1) {
         int st = ensure_scratch(m, sizeof(uint2) * (size_t)batch * nsplit * nq_max);
         if (st != ORBFE_OK) return st;
         partial = reinterpret_cast<uint2*>(m->dScratch);
     }
-    CK(orbfe_launch_knn2(m->stream, d_q, q_stride, d_nq, nq_max, d_t, t_stride, d_nt, nt_max, batch, nsplit, splitLen, partial,
-                         d_idx2, d_dist2, &m->launches));
+    if (tensor)
+        CK(orbfe_launch_knn2_tc(m->stream, d_q, q_stride, d_nq, nq_max, d_t, t_stride, d_nt, nt_max, batch, nsplit, splitLen, partial, d_idx2,
+                                d_dist2, &m->launches));
+    else
+        CK(orbfe_launch_knn2(m->stream, d_q, q_stride, d_nq, nq_max, d_t, t_stride, d_nt, nt_max, batch, nsplit, splitLen, partial, d_idx2,
+                             d_dist2, &m->launches));
+    return ORBFE_OK;
+}
+
+extern "C" int orbfe_matcher_set_knn2_backend(orbfe_matcher* m, int backend) {
+    if (!m || (backend != ORBFE_KNN2_POPC && backend != ORBFE_KNN2_TENSOR)) return ORBFE_ERR_BAD_ARGUMENT;
+    m->knnBackend = backend;
     return ORBFE_OK;
 }
 

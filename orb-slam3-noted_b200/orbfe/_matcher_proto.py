@@ -53,6 +53,7 @@ PROTO = {
     "orbfe_matcher_stream": (_P, [_P]),
     "orbfe_matcher_synchronize": (_I, [_P]),
     "orbfe_matcher_launch_count": (C.c_longlong, [_P]),
+    "orbfe_matcher_set_knn2_backend": (_I, [_P, _I]),
     "orbfe_hamming_knn2_noalloc": (_I, [_I, _P, _P, _I, _P, _I, _P, _P]),
     "orbfe_hamming_knn2": (_I, [_P, _P, _I, _P, _I, _P, _P]),
     "orbfe_hamming_knn2_batch_device": (_I, [_P, _P, _PD, _P, _I, _P, _PD, _P, _I, _I, _P, _P]),

@@ -121,6 +121,14 @@ class ORBmatcher:
         return int(np.unpackbits(x).sum())
 
     # ---- brute force (cv::BFMatcher(NORM_HAMMING).knnMatch(k=2), Frame.cc:1134)
+    KNN2_POPC, KNN2_TENSOR = 0, 1
+
+    def set_knn2_backend(self, backend):
+        """KNN2_POPC (integer pipe) or KNN2_TENSOR (tcgen05 kind::i8): identical results."""
+        st = self._lib.orbfe_matcher_set_knn2_backend(self._m, int(backend))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_matcher_set_knn2_backend")
+
     def knn2(self, q, t):
         q = np.ascontiguousarray(q, np.uint8).reshape(-1, 32)
         t = np.ascontiguousarray(t, np.uint8).reshape(-1, 32)
