@@ -4,22 +4,27 @@
 // uses it (Frame.cc:43,1134), distances of ORBmatcher::DescriptorDistance (ORBmatcher.cc:2561-2577), ties to the lowest
 // train index.  Integer arithmetic end to end, so indices and distances are bit-identical to the POPC kernel.
 //
-// All-pairs Hamming IS a dense contraction: with descriptor bits expanded to signed bytes, a_k = +-64 for the query and
-// b_k = -+2 for the train row, a_k * b_k = -128 where the bits agree and +128 where they differ, so
-//     sum_k a_k b_k = 256 * hamming - 32768.
-// A 17th-and-18th 16-byte K chunk carries (2, 1, 0, ...) on the query side and (j >> 1, j & 1, 0, ...) on the train side,
-// j = the row's position inside its 256-row tile, which adds exactly j.  The accumulator therefore holds
-//     D = 256 * hamming + j - 32768,
+// All-pairs Hamming IS a dense contraction.  Expand the descriptor bits to signed bytes, a_k = +2 / -2 for a set / clear
+// query bit and b_k = -128 / 0 for a set / clear train bit: a_k * b_k is -256 where both bits are set, +256 where only the
+// train bit is, 0 elsewhere, so
+//     sum_k a_k b_k = 256 * (n01 - n11) = 256 * (hamming - popcount(query)).
+// popcount(query) is a constant of the accumulator ROW (one query per TMEM lane), so it does not move the row's minima and
+// is added back only when a survivor is unpacked.  One more 32-byte K slice carries (2, 1, 0, ...) on the query side and
+// (j >> 1, j & 1, 0, ...) on the train side, j = the row's position inside its 256-row tile, which adds exactly j.  The
+// accumulator therefore holds
+//     D = 256 * (hamming - popcount(query)) + j,
 // whose signed minimum over a tile IS "smallest distance, ties to the lowest index": the epilogue is a two-smallest
-// reduction over raw accumulators (2.5 instructions per pair instead of the 27 of the XOR + POPC form) and the distance
-// and index are unpacked from the two survivors only.
+// reduction over raw accumulators (2.5 instructions per pair instead of the 27 of the XOR + POPC form); distance and
+// index are unpacked from the two survivors of a tile only.
 //
 // One CTA = 128 queries (the 128 TMEM lanes) x one split of the train set, streamed in tiles of 256 rows:
-//   warps 4-7  producers: expand the tile's descriptors (32 B each) to 288-byte K-major rows of signed bytes through a 256-entry
-//              byte -> 8-byte table, into the canonical no-swizzle UMMA layout (8-row x 16-byte core matrices), two stages;
-//   warp 8     one elected thread issues 9 x tcgen05.mma (M 128, N 256, K 32) per tile into one of two 256-column TMEM
+//   warps 8-11 producers: expand the tile's descriptors (32 B each) to 288-byte K-major rows (shift + mask per 4 bytes: a bit
+//              moved to bit 7 of its byte IS the byte -128 / 0) in the canonical no-swizzle UMMA layout (8-row x 16-byte
+//              core matrices), two stages;
+//   warp 12    one elected thread issues 9 x tcgen05.mma (M 128, N 256, K 32) per tile into one of two 256-column TMEM
 //              accumulators and commits to mbarriers (frees the smem stage, publishes the accumulator);
-//   warps 0-3  epilogue: tcgen05.ld 32 columns at a time (thread = query row), two-smallest update, then release the accumulator.
+//   warps 0-7  epilogue: thread = query row; warps 0-3 take columns 0-127, warps 4-7 columns 128-255 of the same lanes;
+//              tcgen05.ld 32 columns at a time, two in flight, four independent two-smallest chains per thread.
 // Roles meet only through mbarriers; generic-proxy writes are fenced (fence.proxy.async) before the tensor core reads them.
 #include <limits.h>
 
@@ -29,10 +34,12 @@
 #define TC_M 128                 // queries per CTA = TMEM lanes
 #define TC_N 256                 // train rows per tile = accumulator columns
 #define TC_CHUNKS 18             // 16-byte K chunks per row: 16 of descriptor bits + 2 carrying the row index
-#define TC_THREADS 288
+#define TC_THREADS 416
+#define TC_PRODUCER_WARP0 8
+#define TC_MMA_WARP 12
 #define TC_A_BYTES (TC_M * 16 * TC_CHUNKS)        // 36864
 #define TC_B_BYTES (TC_N * 16 * TC_CHUNKS)        // 73728
-#define TC_SMEM (TC_A_BYTES + 2 * TC_B_BYTES + 2 * 2048 + 256)
+#define TC_SMEM (TC_A_BYTES + 2 * TC_B_BYTES + TC_M * 8 + 256)
 #define KNN_IDX_BITS 20
 #define KNN_IDX_MASK ((1u << KNN_IDX_BITS) - 1u)
 #define KNN_NONE 0xFFFFFFFFu
@@ -96,7 +103,16 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, int (&v)[32]) {
           "=r"(v[31])
         : "r"(taddr));
 }
-__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+// The loaded registers are valid only after tcgen05.wait::ld; naming them as in-out operands keeps every use behind the wait.
+__device__ __forceinline__ void tmem_ld_wait(int (&v)[32]) {
+    asm volatile("tcgen05.wait::ld.sync.aligned;"
+                 : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]),
+                   "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]),
+                   "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]),
+                   "+r"(v[31])
+                 :
+                 : "memory");
+}
 
 // Two smallest of {m0 <= m1} and two new values (5 instructions per two accumulators).
 __device__ __forceinline__ void two_min2(int& m0, int& m1, int a, int b) {
@@ -110,18 +126,26 @@ __device__ __forceinline__ void key_update(uint32_t& k0, uint32_t& k1, uint32_t 
     k1 = min(k1, hi);
 }
 
-// One descriptor row (32 bytes, `words`) -> 18 K chunks of signed bytes at row `r` of a tile of R rows; extra = the two
-// bytes of the index-carrying chunk.
-__device__ __forceinline__ void expand_row(uint8_t* tile, int R, int r, const uint4& w0, const uint4& w1, const uint2* __restrict__ lut,
-                                           uint32_t extra) {
+// One descriptor row (32 bytes) -> 18 K chunks of signed bytes at row `r` of a tile of R rows.  Output word (i, p) holds bit p
+// of the four bytes of descriptor word i: the word shifted left by 7 - p has those bits at bit 7 of each byte.  kTrain: the
+// byte is -128 / 0 (mask only); query: +2 / -2 (a few more operations, once per CTA).  Any fixed order of the K elements
+// serves, as long as both operands use the same one.  extra = the two bytes of the index-carrying chunk.
+template <bool kTrain>
+__device__ __forceinline__ void expand_row(uint8_t* tile, int R, int r, const uint4& w0, const uint4& w1, uint32_t extra) {
     uint8_t* row = tile + (r >> 3) * 128 + (r & 7) * 16;
     const uint32_t w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
     const int cstride = R * 16;
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-        const uint2 a = lut[w[i] & 0xFFu], b = lut[(w[i] >> 8) & 0xFFu], c = lut[(w[i] >> 16) & 0xFFu], d = lut[w[i] >> 24];
-        *reinterpret_cast<uint4*>(row + (2 * i) * cstride) = make_uint4(a.x, a.y, b.x, b.y);
-        *reinterpret_cast<uint4*>(row + (2 * i + 1) * cstride) = make_uint4(c.x, c.y, d.x, d.y);
+        uint32_t o[8];
+#pragma unroll
+        for (int p = 0; p < 8; ++p) {
+            const uint32_t sh = w[i] << (7 - p);
+            const uint32_t m = sh & 0x80808080u;                                   // 0x80 = -128 where the bit is set
+            o[p] = kTrain ? m : ((((m >> 7) ^ 0x01010101u) * 0xFEu) | (m >> 6));    // query: 0x02 = +2 where set, 0xFE = -2 where clear
+        }
+        *reinterpret_cast<uint4*>(row + (2 * i) * cstride) = make_uint4(o[0], o[1], o[2], o[3]);
+        *reinterpret_cast<uint4*>(row + (2 * i + 1) * cstride) = make_uint4(o[4], o[5], o[6], o[7]);
     }
     *reinterpret_cast<uint4*>(row + 16 * cstride) = make_uint4(extra, 0u, 0u, 0u);
     *reinterpret_cast<uint4*>(row + 17 * cstride) = make_uint4(0u, 0u, 0u, 0u);
@@ -146,26 +170,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __rest
     const int ntiles = t1 > t0 ? (t1 - t0 + TC_N - 1) / TC_N : 0;
     uint8_t* sA = smem;
     uint8_t* sB = smem + TC_A_BYTES;
-    uint2* lutA = reinterpret_cast<uint2*>(smem + TC_A_BYTES + 2 * TC_B_BYTES);
-    uint2* lutB = lutA + 256;
+    uint2* sKeys = reinterpret_cast<uint2*>(smem + TC_A_BYTES + 2 * TC_B_BYTES);     // the upper column half's result per query
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
 
     if (tid == 0) {
         bar_init(&aFull, 128);
-        for (int s = 0; s < 2; ++s) { bar_init(&bFull[s], 128); bar_init(&bEmpty[s], 1); bar_init(&accFull[s], 1); bar_init(&accEmpty[s], 128); }
+        for (int s = 0; s < 2; ++s) { bar_init(&bFull[s], 128); bar_init(&bEmpty[s], 1); bar_init(&accFull[s], 1); bar_init(&accEmpty[s], 256); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    if (tid < 256) {            // byte -> 8 signed bytes: query +-64, train -+2 (bit i of the byte -> output byte i)
-        uint32_t a[2] = {0u, 0u}, c[2] = {0u, 0u};
-        for (int i = 0; i < 8; ++i) {
-            const uint32_t bit = (tid >> i) & 1u;
-            a[i >> 2] |= (bit ? 0x40u : 0xC0u) << (8 * (i & 3));
-            c[i >> 2] |= (bit ? 0xFEu : 0x02u) << (8 * (i & 3));
-        }
-        lutA[tid] = make_uint2(a[0], a[1]);
-        lutB[tid] = make_uint2(c[0], c[1]);
-    }
-    if (warp == 8) {            // the whole TMEM of the SM: two accumulators of 256 columns (one CTA per SM by shared memory)
+    if (warp == TC_MMA_WARP) {  // the whole TMEM of the SM: two accumulators of 256 columns (one CTA per SM by shared memory)
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s32(&sTmem)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
@@ -174,35 +187,40 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __rest
     tc_fence_after();
     const uint32_t tmem = sTmem;
 
-    if (warp >= 4 && warp < 8) {
+    if (warp >= TC_PRODUCER_WARP0 && warp < TC_MMA_WARP) {
         // ---- producers
-        const int p = tid - 128;
+        const int p = tid - TC_PRODUCER_WARP0 * 32;
         {
             uint4 w0 = make_uint4(0u, 0u, 0u, 0u), w1 = w0;
             if (q0 + p < nq) {
                 const uint4* src = reinterpret_cast<const uint4*>(q + (long long)b * qStride) + 2 * (long long)(q0 + p);
                 w0 = __ldg(src); w1 = __ldg(src + 1);
             }
-            expand_row(sA, TC_M, p, w0, w1, lutA, 0x00000102u);
+            expand_row<false>(sA, TC_M, p, w0, w1, 0x00000102u);
             fence_async_proxy();
             bar_arrive(&aFull);
         }
         const uint4* tp = reinterpret_cast<const uint4*>(t + (long long)b * tStride);
         for (int i = 0; i < ntiles; ++i) {
             const int s = i & 1;
+            uint4 w[4];
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {      // the loads do not depend on the stage: issue them before waiting for it
+                const int g = t0 + i * TC_N + p + 128 * h;
+                w[2 * h] = w[2 * h + 1] = make_uint4(0u, 0u, 0u, 0u);
+                if (g < t1) { w[2 * h] = __ldg(tp + 2 * (long long)g); w[2 * h + 1] = __ldg(tp + 2 * (long long)g + 1); }
+            }
             bar_wait(&bEmpty[s], ((i >> 1) & 1) ^ 1);
             uint8_t* tile = sB + s * TC_B_BYTES;
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
-                const int r = p + 128 * h, g = t0 + i * TC_N + r;
-                uint4 w0 = make_uint4(0u, 0u, 0u, 0u), w1 = w0;
-                if (g < t1) { w0 = __ldg(tp + 2 * (long long)g); w1 = __ldg(tp + 2 * (long long)g + 1); }
-                expand_row(tile, TC_N, r, w0, w1, lutB, (uint32_t)(r >> 1) | (uint32_t)(r & 1) << 8);
+                const int r = p + 128 * h;
+                expand_row<true>(tile, TC_N, r, w[2 * h], w[2 * h + 1], (uint32_t)(r >> 1) | (uint32_t)(r & 1) << 8);
             }
             fence_async_proxy();
             bar_arrive(&bFull[s]);
         }
-    } else if (warp == 8) {
+    } else if (warp == TC_MMA_WARP) {
         // ---- MMA issuer: one thread
         if (lane == 0 && ntiles > 0) {
             bar_wait(&aFull, 0);
@@ -223,50 +241,74 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __rest
             }
         }
     } else {
-        // ---- epilogue: thread = query row = TMEM lane
+        // ---- epilogue: thread = query row = TMEM lane; `half` = which 128 columns of every tile
+        const int half = warp >> 2, row = (warp & 3) * 32 + lane;
+        const int qi = q0 + row;
+        int popq = 0;
+        if (qi < nq) {
+            const uint4* src = reinterpret_cast<const uint4*>(q + (long long)b * qStride) + 2 * (long long)qi;
+            const uint4 a = __ldg(src), c = __ldg(src + 1);
+            popq = __popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w) + __popc(c.x) + __popc(c.y) + __popc(c.z) + __popc(c.w);
+        }
         uint32_t k0 = KNN_NONE, k1 = KNN_NONE;
-        const uint32_t laneBase = tmem + ((uint32_t)(warp * 32) << 16);
+        const uint32_t laneBase = tmem + ((uint32_t)((warp & 3) * 32) << 16) + half * 128;
         for (int i = 0; i < ntiles; ++i) {
             const int s = i & 1;
             bar_wait(&accFull[s], (i >> 1) & 1);
             tc_fence_after();
-            const int base = t0 + i * TC_N, valid = min(TC_N, t1 - base);
-            int m0 = INT_MAX, m1 = INT_MAX;
-#pragma unroll 1
-            for (int cb = 0; cb < TC_N; cb += 32) {
-                int v[32];
-                tmem_ld32(laneBase + s * TC_N + cb, v);
-                tmem_ld_wait();
-                if (cb + 32 > valid) {         // the last tile of a split: rows past the end do not exist
+            const int base = t0 + i * TC_N, valid = min(TC_N, t1 - base) - half * 128;      // valid columns of this half
+            int m0[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX}, m1[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX};
+            int v[2][32];
+            tmem_ld32(laneBase + s * TC_N, v[0]);
+#pragma unroll
+            for (int cb = 0; cb < 4; ++cb) {
+                int (&x)[32] = v[cb & 1];
+                tmem_ld_wait(x);
+                if (cb < 3) tmem_ld32(laneBase + s * TC_N + (cb + 1) * 32, v[(cb + 1) & 1]);      // in flight while this block is reduced
+                if (cb * 32 + 32 > valid) {    // the last tile of a split: rows past the end do not exist
 #pragma unroll
                     for (int j = 0; j < 32; ++j)
-                        if (cb + j >= valid) v[j] = INT_MAX;
+                        if (cb * 32 + j >= valid) x[j] = INT_MAX;
                 }
 #pragma unroll
-                for (int j = 0; j < 32; j += 2) two_min2(m0, m1, v[j], v[j + 1]);
+                for (int j = 0; j < 32; j += 8) {
+                    two_min2(m0[0], m1[0], x[j], x[j + 1]);
+                    two_min2(m0[1], m1[1], x[j + 2], x[j + 3]);
+                    two_min2(m0[2], m1[2], x[j + 4], x[j + 5]);
+                    two_min2(m0[3], m1[3], x[j + 6], x[j + 7]);
+                }
             }
             tc_fence_before();
             bar_arrive(&accEmpty[s]);
-            // D = 256 * hamming + j - 32768  ->  packed key  hamming << 20 | train index
-            if (m0 != INT_MAX) { const uint32_t x = (uint32_t)(m0 + 32768); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
-            if (m1 != INT_MAX) { const uint32_t x = (uint32_t)(m1 + 32768); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
+            two_min2(m0[0], m1[0], m0[1], m1[1]);
+            two_min2(m0[2], m1[2], m0[3], m1[3]);
+            two_min2(m0[0], m1[0], m0[2], m1[2]);
+            // D = 256 * (hamming - popcount(query)) + j  ->  packed key  hamming << 20 | train index
+            if (m0[0] != INT_MAX) { const uint32_t x = (uint32_t)(m0[0] + 256 * popq); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
+            if (m1[0] != INT_MAX) { const uint32_t x = (uint32_t)(m1[0] + 256 * popq); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
         }
-        const int qi = q0 + tid;
-        if (qi < nq) {
+        if (half == 1) sKeys[row] = make_uint2(k0, k1);
+        tc_fence_before();
+        __syncthreads();
+        if (half == 0 && qi < nq) {
+            const uint2 o = sKeys[row];
+            key_update(k0, k1, o.x);
+            key_update(k0, k1, o.y);           // KNN_NONE entries never displace a real key
             if (nsplit == 1) {
-                const long long o = ((long long)b * nqMax + qi) * 2;
-                idx2[o] = k0 == KNN_NONE ? -1 : (int)(k0 & KNN_IDX_MASK);
-                dist2[o] = k0 == KNN_NONE ? -1 : (int)(k0 >> KNN_IDX_BITS);
-                idx2[o + 1] = k1 == KNN_NONE ? -1 : (int)(k1 & KNN_IDX_MASK);
-                dist2[o + 1] = k1 == KNN_NONE ? -1 : (int)(k1 >> KNN_IDX_BITS);
+                const long long at = ((long long)b * nqMax + qi) * 2;
+                idx2[at] = k0 == KNN_NONE ? -1 : (int)(k0 & KNN_IDX_MASK);
+                dist2[at] = k0 == KNN_NONE ? -1 : (int)(k0 >> KNN_IDX_BITS);
+                idx2[at + 1] = k1 == KNN_NONE ? -1 : (int)(k1 & KNN_IDX_MASK);
+                dist2[at + 1] = k1 == KNN_NONE ? -1 : (int)(k1 >> KNN_IDX_BITS);
             } else {
                 partial[((long long)b * nsplit + split) * nqMax + qi] = make_uint2(k0, k1);
             }
         }
+        return;
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 8) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
+    if (warp == TC_MMA_WARP) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512u) : "memory");
 }
 
 // Train splits for the tensor-core kernel: tiles of 256 rows, about two CTAs' worth of work per SM.
