@@ -4,18 +4,18 @@
 // uses it (Frame.cc:43,1134), distances of ORBmatcher::DescriptorDistance (ORBmatcher.cc:2561-2577), ties to the lowest
 // train index.  Integer arithmetic end to end, so indices and distances are bit-identical to the POPC kernel.
 //
-// All-pairs Hamming IS a dense contraction.  Expand the descriptor bits to signed bytes, a_k = +2 / -2 for a set / clear
-// query bit and b_k = -128 / 0 for a set / clear train bit: a_k * b_k is -256 where both bits are set, +256 where only the
+// All-pairs Hamming IS a dense contraction.  Expand the descriptor bits to signed bytes, a_k = +1 / -1 for a set / clear
+// query bit and b_k = -128 / 0 for a set / clear train bit: a_k * b_k is -128 where both bits are set, +128 where only the
 // train bit is, 0 elsewhere, so
-//     sum_k a_k b_k = 256 * (n01 - n11) = 256 * (hamming - popcount(query)).
-// popcount(query) is a constant of the accumulator ROW (one query per TMEM lane), so it does not move the row's minima and
-// is added back only when a survivor is unpacked.  One more 32-byte K slice carries (2, 1, 0, ...) on the query side and
-// (j >> 1, j & 1, 0, ...) on the train side, j = the row's position inside its 256-row tile, which adds exactly j.  The
-// accumulator therefore holds
-//     D = 256 * (hamming - popcount(query)) + j,
-// whose signed minimum over a tile IS "smallest distance, ties to the lowest index": the epilogue is a two-smallest
-// reduction over raw accumulators (2.5 instructions per pair instead of the 27 of the XOR + POPC form); distance and
-// index are unpacked from the two survivors of a tile only.
+//     sum_k a_k b_k = 128 * (n01 - n11) = 128 * (hamming - popcount(query)).
+// One more 32-byte K slice carries (2, 1, u0, u1, u2, u3, 0, ...) on the query side and (j >> 1, j & 1, 64, 64, 64, 64, 0, ...)
+// on the train side, with j = the train row's position inside its 128-row half tile and u0 + u1 + u2 + u3 =
+// 2 * (popcount(query) - 128): it adds j + 128 * (popcount(query) - 128).  The accumulator therefore holds
+//     D = 128 * (hamming - 128) + j,     -16384 <= D <= 16511,
+// a 16-bit quantity whose signed minimum over a half tile IS "smallest distance, ties to the lowest index".  The epilogue
+// reads the accumulators two columns per register (tcgen05.ld ... pack::16b) and keeps the two smallest per 16-bit lane
+// with packed DPX min / max: 1.25 integer instructions per descriptor pair instead of the 27 of the XOR + POPC form;
+// distance and index are unpacked from the survivors of a tile only.
 //
 // One CTA = 128 queries (the 128 TMEM lanes) x one split of the train set, streamed in tiles of 256 rows:
 //   warps 8-11 producers: expand the tile's descriptors (32 B each) to 288-byte K-major rows (shift + mask per 4 bytes: a bit
@@ -93,32 +93,34 @@ __device__ __forceinline__ void umma_commit(uint64_t* bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(s32(bar)) : "memory");
 }
 
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, int (&v)[32]) {
+// 32 accumulator columns of this thread's lane as 16 registers: the low 16 bits of two adjacent columns per register.
+__device__ __forceinline__ void tmem_ld32p(uint32_t taddr, uint32_t (&v)[16]) {
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, "
-        "%21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        "tcgen05.ld.sync.aligned.32x32b.x16.pack::16b.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]),
-          "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
-          "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]),
-          "=r"(v[31])
+          "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
         : "r"(taddr));
 }
 // The loaded registers are valid only after tcgen05.wait::ld; naming them as in-out operands keeps every use behind the wait.
-__device__ __forceinline__ void tmem_ld_wait(int (&v)[32]) {
+__device__ __forceinline__ void tmem_ld_wait(uint32_t (&v)[16]) {
     asm volatile("tcgen05.wait::ld.sync.aligned;"
                  : "+r"(v[0]), "+r"(v[1]), "+r"(v[2]), "+r"(v[3]), "+r"(v[4]), "+r"(v[5]), "+r"(v[6]), "+r"(v[7]), "+r"(v[8]), "+r"(v[9]), "+r"(v[10]),
-                   "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15]), "+r"(v[16]), "+r"(v[17]), "+r"(v[18]), "+r"(v[19]), "+r"(v[20]),
-                   "+r"(v[21]), "+r"(v[22]), "+r"(v[23]), "+r"(v[24]), "+r"(v[25]), "+r"(v[26]), "+r"(v[27]), "+r"(v[28]), "+r"(v[29]), "+r"(v[30]),
-                   "+r"(v[31])
+                   "+r"(v[11]), "+r"(v[12]), "+r"(v[13]), "+r"(v[14]), "+r"(v[15])
                  :
                  : "memory");
 }
 
-// Two smallest of {m0 <= m1} and two new values (5 instructions per two accumulators).
-__device__ __forceinline__ void two_min2(int& m0, int& m1, int a, int b) {
-    const int lo = min(a, b), hi = max(a, b);
-    m1 = __vimin3_s32(max(m0, lo), m1, hi);
-    m0 = min(m0, lo);
+// Per 16-bit lane: the two smallest of {m0 <= m1} and two new values (5 DPX instructions per four accumulators).
+__device__ __forceinline__ void two_min2(uint32_t& m0, uint32_t& m1, uint32_t a, uint32_t b) {
+    // (the two-input packed min / max intrinsics are emulated on sm_100a; the three-input DPX forms are one instruction)
+    const uint32_t lo = __vimin3_s16x2(a, b, b), hi = __vimax3_s16x2(a, b, b);
+    m1 = __vimin3_s16x2(__vimax3_s16x2(m0, lo, lo), m1, hi);
+    m0 = __vimin3_s16x2(m0, lo, lo);
+}
+__device__ __forceinline__ void two_min_scalar(int& m0, int& m1, int a) {
+    const int hi = max(m0, a);
+    m0 = min(m0, a);
+    m1 = min(m1, hi);
 }
 __device__ __forceinline__ void key_update(uint32_t& k0, uint32_t& k1, uint32_t k) {
     const uint32_t hi = max(k0, k);
@@ -128,10 +130,10 @@ __device__ __forceinline__ void key_update(uint32_t& k0, uint32_t& k1, uint32_t 
 
 // One descriptor row (32 bytes) -> 18 K chunks of signed bytes at row `r` of a tile of R rows.  Output word (i, p) holds bit p
 // of the four bytes of descriptor word i: the word shifted left by 7 - p has those bits at bit 7 of each byte.  kTrain: the
-// byte is -128 / 0 (mask only); query: +2 / -2 (a few more operations, once per CTA).  Any fixed order of the K elements
+// byte is -128 / 0 (mask only); query: +1 / -1 (a few more operations, once per CTA).  Any fixed order of the K elements
 // serves, as long as both operands use the same one.  extra = the two bytes of the index-carrying chunk.
 template <bool kTrain>
-__device__ __forceinline__ void expand_row(uint8_t* tile, int R, int r, const uint4& w0, const uint4& w1, uint32_t extra) {
+__device__ __forceinline__ void expand_row(uint8_t* tile, int R, int r, const uint4& w0, const uint4& w1, uint32_t extra0, uint32_t extra1) {
     uint8_t* row = tile + (r >> 3) * 128 + (r & 7) * 16;
     const uint32_t w[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
     const int cstride = R * 16;
@@ -140,14 +142,14 @@ __device__ __forceinline__ void expand_row(uint8_t* tile, int R, int r, const ui
         uint32_t o[8];
 #pragma unroll
         for (int p = 0; p < 8; ++p) {
-            const uint32_t sh = w[i] << (7 - p);
+            const uint32_t sh = w[i] * (1u << (7 - p));      // a multiply: the FMA pipe is idle here, the integer ALU is what this kernel runs out of
             const uint32_t m = sh & 0x80808080u;                                   // 0x80 = -128 where the bit is set
-            o[p] = kTrain ? m : ((((m >> 7) ^ 0x01010101u) * 0xFEu) | (m >> 6));    // query: 0x02 = +2 where set, 0xFE = -2 where clear
+            o[p] = kTrain ? m : ((((m >> 7) ^ 0x01010101u) * 0xFFu) | (m >> 7));    // query: 0x01 = +1 where set, 0xFF = -1 where clear
         }
         *reinterpret_cast<uint4*>(row + (2 * i) * cstride) = make_uint4(o[0], o[1], o[2], o[3]);
         *reinterpret_cast<uint4*>(row + (2 * i + 1) * cstride) = make_uint4(o[4], o[5], o[6], o[7]);
     }
-    *reinterpret_cast<uint4*>(row + 16 * cstride) = make_uint4(extra, 0u, 0u, 0u);
+    *reinterpret_cast<uint4*>(row + 16 * cstride) = make_uint4(extra0, extra1, 0u, 0u);
     *reinterpret_cast<uint4*>(row + 17 * cstride) = make_uint4(0u, 0u, 0u, 0u);
 }
 
@@ -196,7 +198,12 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __rest
                 const uint4* src = reinterpret_cast<const uint4*>(q + (long long)b * qStride) + 2 * (long long)(q0 + p);
                 w0 = __ldg(src); w1 = __ldg(src + 1);
             }
-            expand_row<false>(sA, TC_M, p, w0, w1, 0x00000102u);
+            // bytes 2, 1 (they weigh the train side's index bytes) and four bytes that sum to 2 * (popcount - 128)
+            const int pop = __popc(w0.x) + __popc(w0.y) + __popc(w0.z) + __popc(w0.w) + __popc(w1.x) + __popc(w1.y) + __popc(w1.z) + __popc(w1.w);
+            const int two = 2 * pop - 256, q4 = two >> 2, rem = two & 3;       // floor division: two == 4 * q4 + rem
+            const uint32_t u = (uint32_t)((q4 + (rem > 0)) & 0xFF) | (uint32_t)((q4 + (rem > 1)) & 0xFF) << 8 |
+                               (uint32_t)((q4 + (rem > 2)) & 0xFF) << 16 | (uint32_t)(q4 & 0xFF) << 24;
+            expand_row<false>(sA, TC_M, p, w0, w1, 0x00000102u | u << 16, u >> 16);
             fence_async_proxy();
             bar_arrive(&aFull);
         }
@@ -215,7 +222,8 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __rest
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                 const int r = p + 128 * h;
-                expand_row<true>(tile, TC_N, r, w[2 * h], w[2 * h + 1], (uint32_t)(r >> 1) | (uint32_t)(r & 1) << 8);
+                const uint32_t j = (uint32_t)(r & 127);         // position inside its 128-row half tile
+                expand_row<true>(tile, TC_N, r, w[2 * h], w[2 * h + 1], (j >> 1) | (j & 1u) << 8 | 0x40400000u, 0x00004040u);
             }
             fence_async_proxy();
             bar_arrive(&bFull[s]);
@@ -244,34 +252,32 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __rest
         // ---- epilogue: thread = query row = TMEM lane; `half` = which 128 columns of every tile
         const int half = warp >> 2, row = (warp & 3) * 32 + lane;
         const int qi = q0 + row;
-        int popq = 0;
-        if (qi < nq) {
-            const uint4* src = reinterpret_cast<const uint4*>(q + (long long)b * qStride) + 2 * (long long)qi;
-            const uint4 a = __ldg(src), c = __ldg(src + 1);
-            popq = __popc(a.x) + __popc(a.y) + __popc(a.z) + __popc(a.w) + __popc(c.x) + __popc(c.y) + __popc(c.z) + __popc(c.w);
-        }
         uint32_t k0 = KNN_NONE, k1 = KNN_NONE;
         const uint32_t laneBase = tmem + ((uint32_t)((warp & 3) * 32) << 16) + half * 128;
+        const uint32_t kBig = 0x7FFF7FFFu;     // above every real accumulator in both lanes
         for (int i = 0; i < ntiles; ++i) {
             const int s = i & 1;
             bar_wait(&accFull[s], (i >> 1) & 1);
             tc_fence_after();
-            const int base = t0 + i * TC_N, valid = min(TC_N, t1 - base) - half * 128;      // valid columns of this half
-            int m0[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX}, m1[4] = {INT_MAX, INT_MAX, INT_MAX, INT_MAX};
-            int v[2][32];
-            tmem_ld32(laneBase + s * TC_N, v[0]);
+            const int base = t0 + i * TC_N + half * 128, valid = min(128, t1 - base);      // this half's rows: [base, base + valid)
+            uint32_t m0[4] = {kBig, kBig, kBig, kBig}, m1[4] = {kBig, kBig, kBig, kBig};
+            uint32_t v[2][16];
+            tmem_ld32p(laneBase + s * TC_N, v[0]);
 #pragma unroll
             for (int cb = 0; cb < 4; ++cb) {
-                int (&x)[32] = v[cb & 1];
+                uint32_t (&x)[16] = v[cb & 1];
                 tmem_ld_wait(x);
-                if (cb < 3) tmem_ld32(laneBase + s * TC_N + (cb + 1) * 32, v[(cb + 1) & 1]);      // in flight while this block is reduced
+                if (cb < 3) tmem_ld32p(laneBase + s * TC_N + (cb + 1) * 32, v[(cb + 1) & 1]);      // in flight while this block is reduced
                 if (cb * 32 + 32 > valid) {    // the last tile of a split: rows past the end do not exist
 #pragma unroll
-                    for (int j = 0; j < 32; ++j)
-                        if (cb * 32 + j >= valid) x[j] = INT_MAX;
+                    for (int j = 0; j < 16; ++j) {
+                        const int c = cb * 32 + 2 * j;
+                        if (c >= valid) x[j] = kBig;
+                        else if (c + 1 >= valid) x[j] = (x[j] & 0xFFFFu) | 0x7FFF0000u;
+                    }
                 }
 #pragma unroll
-                for (int j = 0; j < 32; j += 8) {
+                for (int j = 0; j < 16; j += 8) {
                     two_min2(m0[0], m1[0], x[j], x[j + 1]);
                     two_min2(m0[1], m1[1], x[j + 2], x[j + 3]);
                     two_min2(m0[2], m1[2], x[j + 4], x[j + 5]);
@@ -283,9 +289,15 @@ __global__ void __launch_bounds__(TC_THREADS, 1) k_knn2_tc(const uint8_t* __rest
             two_min2(m0[0], m1[0], m0[1], m1[1]);
             two_min2(m0[2], m1[2], m0[3], m1[3]);
             two_min2(m0[0], m1[0], m0[2], m1[2]);
-            // D = 256 * (hamming - popcount(query)) + j  ->  packed key  hamming << 20 | train index
-            if (m0[0] != INT_MAX) { const uint32_t x = (uint32_t)(m0[0] + 256 * popq); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
-            if (m1[0] != INT_MAX) { const uint32_t x = (uint32_t)(m1[0] + 256 * popq); key_update(k0, k1, (x >> 8) << KNN_IDX_BITS | (uint32_t)(base + (int)(x & 255u))); }
+            // the two lanes hold disjoint columns: the tile's two smallest are among their four survivors
+            int a0 = INT_MAX, a1 = INT_MAX;
+            two_min_scalar(a0, a1, (int)(short)(m0[0] & 0xFFFFu));
+            two_min_scalar(a0, a1, (int)(short)(m0[0] >> 16));
+            two_min_scalar(a0, a1, (int)(short)(m1[0] & 0xFFFFu));
+            two_min_scalar(a0, a1, (int)(short)(m1[0] >> 16));
+            // D = 128 * (hamming - 128) + j  ->  packed key  hamming << 20 | train index
+            if (a0 != 0x7FFF) key_update(k0, k1, (uint32_t)((a0 >> 7) + 128) << KNN_IDX_BITS | (uint32_t)(base + (a0 & 127)));
+            if (a1 != 0x7FFF) key_update(k0, k1, (uint32_t)((a1 >> 7) + 128) << KNN_IDX_BITS | (uint32_t)(base + (a1 & 127)));
         }
         if (half == 1) sKeys[row] = make_uint2(k0, k1);
         tc_fence_before();
