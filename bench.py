@@ -35,6 +35,9 @@ ORB_PARAMS = (NFEAT, 1.2, 8, 20, 7)
 LAPPING = (0, 1000)           # what the mono Frame ctor passes (Frame.cc:306)
 METRIC = "ORB extract+describe frames/s (752x480, 1000 kp)"
 UNIT = "frames/s"
+# what "kind": "reference" runs underneath the reference's own ORBextractor.cc in this image (no OpenCV C++ here)
+CPU_PRIMITIVES = ("scalar restatement of OpenCV's resize / FAST / GaussianBlur (bit-identical to cv2 4.13, "
+                  "not its SIMD kernels)")
 WORKLOAD = "ORBextractor 752x480 nFeatures=1000 nLevels=8 scale=1.2 iniThFAST=20 minThFAST=7, synthetic textured frames"
 
 
@@ -161,9 +164,9 @@ def run_reference(args):
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": WORKLOAD, "lapping": list(LAPPING)},
-        "config_detail": {"frames_per_step": per_step, "note": what, "primitives": "scalar restatement of OpenCV's resize / FAST / GaussianBlur "
-                          "(bit-identical to cv2 4.13, not its SIMD kernels)"},
-        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+        "config_detail": {"frames_per_step": per_step, "note": what, "primitives": CPU_PRIMITIVES},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
+                         "primitives": CPU_PRIMITIVES},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -645,7 +648,8 @@ def run_orbfe(args):
         v, nfr = cpu_frames_per_s(frames, cores, args.cpu_seconds, extract_many)
         out["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                                "sample": f"{nfr} frames of the same workload, frame-parallel over {cores} host threads, "
-                                         f"one extractor per thread; {what}"}
+                                         f"one extractor per thread; {what}",
+                               "primitives": CPU_PRIMITIVES}
         if kind == "reference":      # the oracle port beside it, same frames and threads
             vp, _ = cpu_frames_per_s(frames, cores, min(args.cpu_seconds, 4.0), _oracle().extract_many)
             out["cpu_baseline"]["oracle_port_frames_per_s"] = vp
