@@ -183,6 +183,9 @@ __global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restri
 }
 
 #define DESC_WARPS 8
+#ifndef DESC_STAGE
+#define DESC_STAGE 0       // measured (profiles/r02m_variants.txt): 0.962 ms with the staged window vs 0.955 without
+#endif
 
 #ifndef DESC_MINB
 #define DESC_MINB 6
@@ -206,6 +209,24 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     const int level = s >> 28, cy = (s >> 14) & 0x3FFF, cx = s & 0x3FFF;
     const LevelGeom& g = geom[level];
     const long long centre = g.base + (long long)frame * g.plane + (long long)(cy + ORBFE_EDGE) * g.pitch + ORBFE_XO + cx;
+#if DESC_STAGE
+    // The 512 samples of a key point fall anywhere in a 37 x 37 window of the blurred level (pattern radius 18.4): read
+    // straight from global memory, every one of the 16 gathers of a warp touches ~20 different lines and the kernel sat on
+    // the L1 tag stage (l1tex 91 %, profiles/r02k_*).  The window is staged once with coalesced aligned words (37 rows x 10
+    // words; the pitch is a multiple of 128, so all rows share the byte shift sh) and the gathers hit shared memory.
+    __shared__ uint32_t sWin[DESC_WARPS][37 * 10];
+    const int sh = (int)((centre - 18) & 3);
+    {
+        const uint32_t* wbase = reinterpret_cast<const uint32_t*>(blur + (centre - 18 - sh)) - 18 * (g.pitch >> 2);
+        const int pw = g.pitch >> 2;
+        uint32_t* dstw = sWin[threadIdx.x >> 5];
+#pragma unroll 4
+        for (int u = lane; u < 370; u += 32) {
+            const int r = (u * 6554) >> 16, j = u - 10 * r;      // u / 10 for u < 16384
+            dstw[u] = __ldg(wbase + r * pw + j);
+        }
+    }
+#endif
     // ---- intensity centroid (IC_Angle): lane = column u = lane - 15, rows v = -15..15 clipped to the disc
     int m10 = 0, m01 = 0;
     {
@@ -241,16 +262,24 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     sincos((double)rad, &sd, &cd);
     const float a = (float)cd, b = (float)sd;
     // ---- lane computes descriptor byte `lane`: tests 8*lane .. 8*lane+7
+#if DESC_STAGE
+    __syncwarp();
+    const uint8_t* Bc = reinterpret_cast<const uint8_t*>(sWin[threadIdx.x >> 5]) + 18 * 40 + 18 + sh;
+    const int pitch = 40;
+#define DESC_LD(p) (*(p))
+#else
     const uint8_t* Bc = blur + centre;
     const int pitch = g.pitch;
+#define DESC_LD(p) __ldg(p)
+#endif
     uint32_t byte = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
         const float4 pt = sPat[k * 32 + lane];   // test 8*lane + k
         const float x0 = pt.x, y0 = pt.y, x1 = pt.z, y1 = pt.w;
-        const int t0 = __ldg(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * pitch +
+        const int t0 = DESC_LD(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * pitch +
                              __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b))));
-        const int t1 = __ldg(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a))) * pitch +
+        const int t1 = DESC_LD(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a))) * pitch +
                              __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b))));
         byte |= (uint32_t)(t0 < t1) << k;
     }

@@ -17,6 +17,10 @@
 // Survivors are appended to the level's candidate array as packed (x, y, response) words.  Their
 // memory order is arbitrary; the reference's push order (cell-row-major, then FAST row-major) is a
 // pure function of (x, y) and is re-derived where it matters (quadtree tie-break, debug tap).
+#include <stdlib.h>
+
+#include <algorithm>
+
 #include "orbfe_internal.h"
 
 #ifndef FAST_THREADS
@@ -128,9 +132,10 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
     const int nw = tp >> 2;
     const CellDesc cd = cells[blockIdx.x];
 
+    const int myTileBytes = (TPC ? TPC : boxW) * geom[cd.level].fastBoxH;     // this level's TMA box
     if (tid == 0) {
         mbar_init(&sBar, 1);
-        mbar_expect_tx(&sBar, (uint32_t)tileBytes);
+        mbar_expect_tx(&sBar, (uint32_t)myTileBytes);
         // TMA wants the innermost start coordinate on a 16-byte boundary: the box starts at the aligned column below the
         // cell (cd.tx); tile byte = cd.sh + column.
         tma_load_3d(landing, &maps.m[cd.level], cd.tx, cd.ty, frame, &sBar);
@@ -158,7 +163,7 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
             if (kPad) {                        // dense 16-word rows -> 17-word rows; both sides conflict-free
                 const uint32_t* src = reinterpret_cast<const uint32_t*>(landing);
                 uint32_t* dst = reinterpret_cast<uint32_t*>(tile);
-                for (int i = tid; i < tileBytes / 4; i += FAST_THREADS) dst[i + (i >> 4)] = src[i];
+                for (int i = tid; i < myTileBytes / 4; i += FAST_THREADS) dst[i + (i >> 4)] = src[i];
                 __syncthreads();               // the lists reuse the landing area
             }
         }
@@ -240,9 +245,242 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
     }
 }
 
+// ---- warp-per-cell form ---------------------------------------------------------------------------------
+// The same stages with ONE WARP per cell and no CTA-wide barrier at all: each warp owns a slice of the dynamic shared
+// memory (tile, score map, corner list, a small survivor queue, its own mbarrier) and issues its own TMA load.  What this
+// buys over the CTA-per-cell form (ncu, profiles/r02k_*): a cell has ~300 four-pixel units, ~170 survivors and ~40 corners,
+// so 128 threads ran stage B at 66 % and stage C at 30 % lane occupancy, repeated the cell prologue in four warps and
+// drained at six __syncthreads per cell.  Here stage A feeds a queue and the exact score runs only on FULL warps of 32
+// survivors (plus one flush), stage C on 32-wide slices, the prologue once, and kept candidates go straight to the level's
+// array (one global atomic per 32-wide NMS slice that kept something; the retry rule only needs the running count).
+#ifndef FAST_WARP
+#define FAST_WARP 1
+#endif
+#ifndef FAST_WARPS
+#define FAST_WARPS 1       // measured (profiles/r02l_*, r02m_*): 1.22 / 1.36 / 1.58 / 1.72 ms per 512 frames with 1 / 2 / 4 / 8 warps per CTA - a CTA's
+#endif                     // shared memory is only released when its slowest cell is done
+#ifndef FAST_WMINB
+#define FAST_WMINB 32
+#endif
+#define FAST_QCAP 192      // survivor queue: < 32 left over + at most 4 x 32 new entries per step
+#ifndef FAST_L2CAP
+#define FAST_L2CAP 512     // corner list; a cell with more corners takes the map-scan form of stage C.  Measured (profiles/r02p_*, r02q_*):
+#endif                     // 128 / 192 / 256 / 384 / 512 entries -> 1.19 / 1.15 / 1.10 / 1.08 / 1.07 ms per 512 frames (the scan is slow, textured cells overflow)
+// Slots from ballots + prefix popcounts instead of the two shared-memory atomics were measured and lost (1.138 vs 1.122 ms,
+// profiles/r02o_variants.txt), as did a tile pitch of 80 bytes for the bank spread (1.30 vs 1.24, profiles/r02m_variants.txt).
+//
+// Shared memory per cell decides how many cells an SM works on at once (the kernel is latency-bound: 1.22 ms at 24 cells per
+// SM, 1.10 at 29), so the score map is NOT tile-shaped: it covers the tested area plus a one-pixel zero frame, at its own
+// pitch sp: score index = (y - 2) * sp + (x - 2) for cell-relative (x, y).
+template <int TPC>
+__global__ void __launch_bounds__(32 * FAST_WARPS, FAST_WMINB) k_fast_warp(const __grid_constant__ FastMaps maps,
+                                                             const LevelGeom* __restrict__ geom,
+                                                             const CellDesc* __restrict__ cells, uint32_t* __restrict__ cand,
+                                                             int* __restrict__ candCount, long long candPerFrame,
+                                                             int nlevels, int iniTh, int minTh, int boxW, int tileBytes, int listCap,
+                                                             uint32_t invTp, int frame0, int cell0, int cellEnd, int warpBytes,
+                                                             int sp, uint32_t invSp, int scoreStride) {
+    extern __shared__ __align__(128) uint8_t smem[];
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    const int cell = cell0 + blockIdx.x * FAST_WARPS + wid;
+    if (cell >= cellEnd) return;                       // whole warps leave; nothing below synchronises the CTA
+    const int frame = frame0 + blockIdx.y;
+    const int tp = TPC ? TPC : boxW;
+    const int tileStride = (tileBytes + 127) & ~127;
+    uint8_t* tile = smem + (size_t)wid * warpBytes;   // TMA destination, 128-byte aligned (warpBytes is a multiple of 128)
+    uint8_t* score = tile + tileStride;
+    uint16_t* list2 = reinterpret_cast<uint16_t*>(score + scoreStride);  // corners (score indices)
+    uint16_t* queue = list2 + listCap;                                     // survivors of the quick test waiting for a full warp
+    uint64_t* bar = reinterpret_cast<uint64_t*>(queue + FAST_QCAP);
+    int* cnt = reinterpret_cast<int*>(bar + 1);                            // [0] queue fill, [1] corners
+    const int nw = tp >> 2;
+    const CellDesc cd = cells[cell];
+    const int myBoxH = geom[cd.level].fastBoxH;                // this level's TMA box (tileBytes = the largest of the launch)
+    const int myScoreWords = (sp * (myBoxH - 4) + 3) >> 2;
+
+    if (lane == 0) {
+        mbar_init(bar, 1);
+        mbar_expect_tx(bar, (uint32_t)(tp * myBoxH));
+        tma_load_3d(tile, &maps.m[cd.level], cd.tx, cd.ty, frame, bar);
+    }
+    int off[16];
+    {
+        const int dx[16] = {0, 1, 2, 3, 3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1};
+        const int dy[16] = {3, 3, 2, 1, 0, -1, -2, -3, -3, -3, -2, -1, 0, 1, 2, 3};
+#pragma unroll
+        for (int k = 0; k < 16; ++k) off[k] = dy[k] * tp + dx[k];
+    }
+    const int nWords = cd.nWords, units = cd.units;
+    const uint32_t inv = cd.inv;
+    const int w0 = 3 * nw + cd.wLo;
+    const int sOff = 2 * sp + cd.sh + 2;           // score index = y * sp + (tile column) - sOff
+    const uint32_t* tw32 = reinterpret_cast<const uint32_t*>(tile);
+    uint32_t* out = cand + (long long)frame * candPerFrame + geom[cd.level].candBase;
+    int* outCount = candCount + frame * nlevels + cd.level;
+    const uint32_t ltMask = (1u << lane) - 1u;
+    const uint32_t outBase = (uint32_t)(cd.ox + 2) | (uint32_t)(cd.oy + 2) << 11;
+
+    // exact score of one queued survivor; a corner goes into the score map and onto the corner list
+#define FAST_SCORE_ONE(idxExpr)                                                                              \
+    {                                                                                                        \
+        const int idx = (idxExpr);                                                                           \
+        const int s = fast_score_packed(tile, idx, off);                                                     \
+        if (s >= t) {                                                                                        \
+            const int y = TPC ? idx / TPC : (int)(((uint32_t)idx * invTp) >> 20);                            \
+            const int sidx = y * sp + (idx - y * tp) - sOff;                                                 \
+            const int slot = atomicAdd(&cnt[1], 1);                                                          \
+            if (slot < listCap) list2[slot] = (uint16_t)sidx;                                                \
+            score[sidx] = (uint8_t)s;                                                                        \
+        }                                                                                                    \
+    }
+#define FAST_NMS(sidx, s)                                                                                    \
+    ((s) > score[(sidx) - 1] && (s) > score[(sidx) + 1] && (s) > score[(sidx) - sp - 1] && (s) > score[(sidx) - sp] && \
+     (s) > score[(sidx) - sp + 1] && (s) > score[(sidx) + sp - 1] && (s) > score[(sidx) + sp] && (s) > score[(sidx) + sp + 1])
+
+    int t = iniTh;
+    for (int pass = 0; pass < 2; ++pass) {
+        if (lane == 0) { cnt[0] = 0; cnt[1] = 0; }
+        for (int i = lane; i < (myScoreWords + 3) >> 2; i += 32) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
+        __syncwarp();                          // also orders lane 0's mbarrier init before the other lanes' wait
+        if (pass == 0) mbar_wait(bar, 0);
+        const uint32_t k127 = (uint32_t)(127 - (t & 127)) * 0x01010101u, lowT = t < 128 ? 0xFFFFFFFFu : 0u;
+        // A + B: quick test over the cell, exact score whenever 32 survivors are waiting
+        for (int u0 = 0; u0 < units; u0 += 32) {
+            const int u = u0 + lane;
+            if (u < units) {
+                const int rr = (int)(((uint32_t)u * inv) >> 20), wj = u - rr * nWords;
+                const int w = w0 + rr * nw + wj;
+                const uint32_t c = tw32[w];
+                const uint32_t up = tw32[w - 3 * nw], dn = tw32[w + 3 * nw];
+                uint32_t m = (gtu4_bit7(__vabsdiffu4(c, up), k127, lowT) | gtu4_bit7(__vabsdiffu4(c, dn), k127, lowT)) & 0x80808080u;
+                if (wj == 0) m &= cd.firstMask;
+                if (wj == nWords - 1) m &= cd.lastMask;
+                if (m != 0u) {
+                    const uint32_t lf = tw32[w - 1], rt = tw32[w + 1];
+                    const uint32_t vl = __byte_perm(lf, c, 0x4321);
+                    const uint32_t vr = __byte_perm(c, rt, 0x6543);
+                    m &= gtu4_bit7(__vabsdiffu4(c, vl), k127, lowT) | gtu4_bit7(__vabsdiffu4(c, vr), k127, lowT);
+                    if (m != 0u) {
+                        int base = atomicAdd(&cnt[0], __popc(m));
+                        const int idx = 4 * w;
+                        if (m & 0x00000080u) queue[base++] = (uint16_t)idx;
+                        if (m & 0x00008000u) queue[base++] = (uint16_t)(idx + 1);
+                        if (m & 0x00800000u) queue[base++] = (uint16_t)(idx + 2);
+                        if (m & 0x80000000u) queue[base] = (uint16_t)(idx + 3);
+                    }
+                }
+            }
+            __syncwarp();
+            int qn = *reinterpret_cast<volatile int*>(&cnt[0]);
+            if (qn >= 32) {
+                do {
+                    qn -= 32;
+                    FAST_SCORE_ONE(queue[qn + lane])
+                } while (qn >= 32);
+                __syncwarp();                  // every lane has read its queue entry before the fill count drops
+                if (lane == 0) cnt[0] = qn;
+                __syncwarp();
+            }
+        }
+        if (lane < *reinterpret_cast<volatile int*>(&cnt[0])) FAST_SCORE_ONE(queue[lane])     // flush: fewer than 32 left
+        __syncwarp();
+        // C: non-max suppression; kept candidates go to the level's array in 32-wide slices
+        const int nc = *reinterpret_cast<volatile int*>(&cnt[1]);
+        int keptTotal = 0;
+        if (nc > listCap) {                    // rare: the list overflowed, walk the score map itself
+            int mine = 0;
+            for (int wi = lane; wi < myScoreWords; wi += 32) {
+                const uint32_t sw = reinterpret_cast<const uint32_t*>(score)[wi];
+                if (sw == 0u) continue;
+                for (int k = 0; k < 4; ++k) {
+                    const int s = (int)((sw >> (8 * k)) & 0xFFu), sidx = 4 * wi + k;
+                    if (s == 0 || !FAST_NMS(sidx, s)) continue;
+                    const int ys = (int)(((uint32_t)sidx * invSp) >> 20), xs = sidx - ys * sp;
+                    out[atomicAdd(outCount, 1)] = (outBase + (uint32_t)xs + ((uint32_t)ys << 11)) | (uint32_t)s << 22;
+                    ++mine;
+                }
+            }
+            keptTotal = __reduce_add_sync(0xffffffffu, mine);
+        } else {
+            for (int i0 = 0; i0 < nc; i0 += 32) {
+                const int i = i0 + lane;
+                bool keep = false;
+                int sidx = 0, s = 0;
+                if (i < nc) {
+                    sidx = list2[i];
+                    s = score[sidx];
+                    keep = FAST_NMS(sidx, s);
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, keep);
+                if (bal != 0u) {
+                    int gbase = 0;
+                    if (lane == 0) gbase = atomicAdd(outCount, __popc(bal));
+                    gbase = __shfl_sync(0xffffffffu, gbase, 0);
+                    if (keep) {
+                        const int ys = (int)(((uint32_t)sidx * invSp) >> 20), xs = sidx - ys * sp;
+                        out[gbase + __popc(bal & ltMask)] = (outBase + (uint32_t)xs + ((uint32_t)ys << 11)) | (uint32_t)s << 22;
+                    }
+                    keptTotal += __popc(bal);
+                }
+            }
+        }
+        if (keptTotal > 0 || pass == 1) break;
+        t = minTh;   // D: retry at the lower threshold
+        __syncwarp();
+    }
+#undef FAST_SCORE_ONE
+#undef FAST_NMS
+}
+
+#ifndef FAST_SMALL_ROWS
+#define FAST_SMALL_ROWS 48     // levels whose cells are at most this tall share a launch with a small shared-memory footprint
+#endif
+static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
+    // ORBFE_FAST_L2CAP (environment, tests only) shrinks the corner list so that ordinary frames take the overflow path
+    static const int capEnv = [] { const char* e = getenv("ORBFE_FAST_L2CAP"); const int v = e ? atoi(e) : 0; return v >= 4 ? (v & ~3) : FAST_L2CAP; }();
+    const uint32_t invTp = ((1u << 20) + h->fastBoxW - 1) / h->fastBoxW;
+    const int nl = h->p.nlevels;
+    // Cells are stored level by level.  Almost all of them are ~44 rows tall, but the coarsest levels have a few of up to ~60
+    // rows; sizing every CTA's shared memory for those costs a quarter of the occupancy, so consecutive levels of the same
+    // class (small / tall) go out as one launch with the footprint of their own tallest box.
+    for (int l = 0; l < nl;) {
+        const bool small = h->geom[l].fastBoxH <= FAST_SMALL_ROWS;
+        int l1 = l, maxH = 0;
+        while (l1 < nl && (h->geom[l1].fastBoxH <= FAST_SMALL_ROWS) == small) { maxH = std::max(maxH, h->geom[l1].fastBoxH); ++l1; }
+        const int cell0 = h->geom[l].cellBase, cellEnd = h->geom[l1 - 1].cellBase + h->geom[l1 - 1].nCells;
+        l = l1;
+        if (cellEnd <= cell0) continue;
+        const int tileBytes = h->fastBoxW * maxH;
+        const int tileStride = (tileBytes + 127) & ~127;
+        const int listCap = std::min(((h->fastMaxCw - 6) * (maxH - 6) + 3) & ~3, capEnv);     // at most: every tested pixel a corner
+        const int sp = (h->fastMaxCw - 4 + 3) & ~3;                       // score map: tested area + a one-pixel frame
+        const int scoreStride = (sp * (maxH - 4) + 15) & ~15;
+        const uint32_t invSp = ((1u << 20) + sp - 1) / sp;               // sidx / sp == (sidx * invSp) >> 20 for sidx < 2^14
+        const int warpBytes = (tileStride + scoreStride + 2 * listCap + 2 * FAST_QCAP + 16 + 127) & ~127;
+        const size_t smem = (size_t)warpBytes * FAST_WARPS;
+        dim3 grid((cellEnd - cell0 + FAST_WARPS - 1) / FAST_WARPS, batch);
+#define ORBFE_FAST_WLAUNCH(TPC)                                                                                                  \
+        do {                                                                                                                     \
+            const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_fast_warp<TPC>), smem);                 \
+            if (ea != cudaSuccess) return ea;                                                                                    \
+            k_fast_warp<TPC><<<grid, 32 * FAST_WARPS, smem, h->cur>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount, \
+                                                                      h->candPerFrame, nl, h->p.ini_th_fast, h->p.min_th_fast,   \
+                                                                      h->fastBoxW, tileBytes, listCap, invTp, frame0, cell0, cellEnd, warpBytes, \
+                                                                      sp, invSp, scoreStride);                                     \
+        } while (0)
+        if (h->fastBoxW == 64) ORBFE_FAST_WLAUNCH(64);
+        else if (h->fastBoxW == 80) ORBFE_FAST_WLAUNCH(80);
+        else ORBFE_FAST_WLAUNCH(0);
+#undef ORBFE_FAST_WLAUNCH
+        h->launches++;
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
     cudaError_t e = cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->cur);
     if (e != cudaSuccess) return e;
+    if (FAST_WARP) return launch_fast_warp(h, frame0, batch);
     const int tileBytes = h->fastBoxW * h->fastBoxH;
     const size_t tileStride = ((size_t)tileBytes + 127) & ~(size_t)127;
     // maxCellBytes counts two unpadded maps; FAST_PAD re-pitches both to 68 bytes and 128-byte-aligns them
@@ -259,6 +497,7 @@ cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
                                                                 h->fastBoxW, tileBytes, listCap, invTp, frame0);                 \
     } while (0)
     if (h->fastBoxW == 64) ORBFE_FAST_LAUNCH(64);
+    else if (h->fastBoxW == 80) ORBFE_FAST_LAUNCH(80);
     else ORBFE_FAST_LAUNCH(0);
 #undef ORBFE_FAST_LAUNCH
     h->launches++;

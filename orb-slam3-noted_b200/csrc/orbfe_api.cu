@@ -13,6 +13,9 @@
 #include <vector>
 
 #include "orbfe_internal.h"
+#ifndef ORBFE_FAST_BOX80
+#define ORBFE_FAST_BOX80 0     // FAST tile pitch 80 instead of 64 bytes (bank spread of the tile rows); see k_fast.cu
+#endif
 
 static thread_local char g_cudaErr[256] = "";
 
@@ -185,6 +188,7 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
         kpOff += g.kpCap;
         // cells, in the reference's loop order
         g.cellBase = (int)sp.cells.size();
+        int lvlMaxCh = 8;
         int cap = 0;
         for (int i = 0; i < g.nRows; i++) {
             const int iniY = ORBFE_MIN_BORDER + i * g.hCell;
@@ -218,10 +222,12 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
                 cap += keptCap;
                 sp.maxCw = std::max(sp.maxCw, (int)c.cw);
                 sp.maxCh = std::max(sp.maxCh, (int)c.ch);
+                lvlMaxCh = std::max(lvlMaxCh, (int)c.ch);
                 sp.maxKept = std::max(sp.maxKept, keptCap);
             }
         }
         g.nCells = (int)sp.cells.size() - g.cellBase;
+        g.fastBoxH = lvlMaxCh;
         g.candCap = (cap + 3) & ~3;
         g.candBase = candOff;
         candOff += g.candCap;
@@ -246,6 +252,9 @@ static void plan_shape(const orbfe_handle* h, int W, int H, ShapePlan& sp) {
     sp.blurTiles = blurTiles;
     // FAST tile = TMA box: inner extent a multiple of 16 bytes; layout of k_fast_cells' dynamic smem
     sp.boxW = (sp.maxCw + 15 + 15) & ~15;   // + up to 15 bytes of alignment shift (TMA start column is 16-byte aligned)
+#if ORBFE_FAST_BOX80
+    if (sp.boxW == 64) sp.boxW = 80;        // 20-word rows: rows r and r + 1 sit 20 banks apart, only rows 8 apart share banks
+#endif
     sp.boxH = sp.maxCh;
     const int listCap = ((sp.boxW - 6) * (sp.boxH - 6) + 1) & ~1;
     sp.maxCellBytes = 2 * sp.boxW * sp.boxH + 2 * 2 * listCap + 4 * sp.maxKept + 16;
@@ -303,7 +312,7 @@ static int encode_fast_maps(orbfe_handle* h) {
         const LevelGeom& g = h->geom[l];
         const cuuint64_t dims[3] = {(cuuint64_t)g.pitch, (cuuint64_t)g.rows, (cuuint64_t)B};
         const cuuint64_t strides[2] = {(cuuint64_t)g.pitch, (cuuint64_t)g.plane};   // bytes, dims 1 and 2
-        const cuuint32_t box[3] = {(cuuint32_t)h->fastBoxW, (cuuint32_t)h->fastBoxH, 1};
+        const cuuint32_t box[3] = {(cuuint32_t)h->fastBoxW, (cuuint32_t)g.fastBoxH, 1};   // per-level rows: most cells are ~44 rows, the coarsest levels up to ~60
         const cuuint32_t estr[3] = {1, 1, 1};
         CUresult r = encode(&h->fastMaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->dPyr + g.base, dims, strides, box, estr,
                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
@@ -338,6 +347,7 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     h->maxCellBytes = sp.maxCellBytes;
     h->fastBoxW = sp.boxW;
     h->fastBoxH = sp.boxH;
+    h->fastMaxCw = sp.maxCw;
     {
         int st = encode_fast_maps(h);
         if (st != ORBFE_OK) return st;

@@ -39,6 +39,7 @@ struct LevelGeom {
     // FAST grid, ORBextractor.cc:771-785
     int maxBX, maxBY, nCols, nRows, wCell, hCell;
     int cellBase, nCells;  // slice of the flattened cell table
+    int fastBoxH;          // rows of this level's FAST TMA box = its tallest cell ROI (the box width is common, fastBoxW)
     // quadtree, ORBextractor.cc:541-543 and :433-444
     int nfeat, nIni;
     float hX;
@@ -118,6 +119,7 @@ struct orbfe_handle {
     int nCellsTotal;
     int maxCellBytes;       // dynamic smem of k_fast_cells
     int fastBoxW, fastBoxH; // TMA box of the FAST tile (>= the largest cell, width a multiple of 16)
+    int fastMaxCw;          // widest cell ROI (core + 6 px)
     FastMaps fastMaps;
     long long candPerFrame; // candidate entries per frame (all levels)
     int kpPerFrame;         // output slots per frame (= cap of device results)

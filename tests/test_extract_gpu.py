@@ -232,3 +232,30 @@ def test_tables_equal_reference_constructor(params):
     if ob.ref_available():
         for a, b in zip(got, ob.OrbSlam3Extractor(*params).tables()):
             assert a.tobytes() == b.tobytes()
+
+
+def test_fast_corner_list_overflow_path():
+    """k_fast_warp keeps a bounded corner list per cell and walks the score map when a cell has more corners than that.
+    ORBFE_FAST_L2CAP (read once per process) shrinks the bound to 8, so almost every cell of an ordinary frame overflows;
+    the candidates and key points must not change.  Runs in a child process because of the read-once knob."""
+    import os
+    import subprocess
+    import sys
+    here = os.path.dirname(os.path.abspath(__file__))
+    code = (
+        "import sys, numpy as np\n"
+        f"sys.path[:0] = [{here!r}, {os.path.join(os.path.dirname(here), 'orb-slam3-noted_b200')!r}]\n"
+        "import orbfe\n"
+        "from oracle_binding import OrbRef\n"
+        "ex = orbfe.ORBextractor(1000, 1.2, 8, 20, 7, max_width=752, max_height=480)\n"
+        "ref = OrbRef(1000, 1.2, 8, 20, 7)\n"
+        "for seed in (4100, 4101):\n"
+        "    img = orbfe.synth.frame(seed, 752, 480)\n"
+        "    rmono, rk, rd = ref(img, (0, 1000)); mono, k, d = ex(img, None, (0, 1000))\n"
+        "    for l in range(8): assert np.array_equal(ex.candidates(l, 0), ref.candidates(l)), l\n"
+        "    assert mono == rmono and all(np.array_equal(k[f], rk[f]) for f in ('octave', 'x', 'y', 'response'))\n"
+        "    assert np.array_equal(d, rd)\n"
+        "print('overflow path ok')\n")
+    env = dict(os.environ, ORBFE_FAST_L2CAP="8")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "overflow path ok" in r.stdout, r.stdout + r.stderr
