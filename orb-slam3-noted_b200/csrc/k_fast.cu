@@ -267,7 +267,8 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
 #define FAST_L2CAP 512     // corner list; a cell with more corners takes the map-scan form of stage C.  Measured (profiles/r02p_*, r02q_*):
 #endif                     // 128 / 192 / 256 / 384 / 512 entries -> 1.19 / 1.15 / 1.10 / 1.08 / 1.07 ms per 512 frames (the scan is slow, textured cells overflow)
 // Slots from ballots + prefix popcounts instead of the two shared-memory atomics were measured and lost (1.138 vs 1.122 ms,
-// profiles/r02o_variants.txt), as did a tile pitch of 80 bytes for the bank spread (1.30 vs 1.24, profiles/r02m_variants.txt).
+// profiles/r02o_variants.txt), as did a tile pitch of 80 bytes for the bank spread (1.30 vs 1.24, profiles/r02m_variants.txt)
+// and two units / two survivors per lane and step for more independent work per warp (1.047 vs 1.025, profiles/r02s_variants.txt).
 //
 // Shared memory per cell decides how many cells an SM works on at once (the kernel is latency-bound: 1.22 ms at 24 cells per
 // SM, 1.10 at 29), so the score map is NOT tile-shaped: it covers the tested area plus a one-pixel zero frame, at its own
