@@ -233,15 +233,18 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
         // the disc is symmetric: |u| <= umax[|v|]  <=>  |v| <= umax[|u|], one limit per lane
         const int u = lane - 15;
         const int lim = lane < 31 ? c_umax[u < 0 ? -u : u] : -1;
-        const uint8_t* c = pyr + centre + u;
-        const int pitch = g.pitch;
+        // addresses = one per-lane 64-bit pointer to the TOP row of the window + an unsigned 32-bit offset (one IMAD.WIDE.U32
+        // per load); signed row offsets from the centre cost a multiply, a sign extension and a three-input 64-bit add each
+        const unsigned upitch = (unsigned)g.pitch;
+        const uint8_t* cTop = pyr + (centre + u - 15ll * g.pitch);
+        asm volatile("" : "+l"(cTop));      // keep it ONE register pair (else the uniform arena base is re-added at every load)
         // rows v and -v together (m01 += v * (I(v) - I(-v)), as IC_Angle itself does); the loads are unconditional - every
         // row of the 31 x 31 window lies inside the 19-px border and touches the same lines whichever lanes are inside the
         // disc - so only the three accumulations are predicated and the unrolled loop has no branches
-        int sum = lane < 31 ? (int)__ldg(c) : 0;
+        int sum = lane < 31 ? (int)__ldg(cTop + 15ull * upitch) : 0;
 #pragma unroll
         for (int v = 1; v <= 15; ++v) {
-            const int Ip = __ldg(c + v * pitch), Im = __ldg(c - v * pitch);
+            const int Ip = __ldg(cTop + (unsigned long long)upitch * (unsigned)(15 + v)), Im = __ldg(cTop + (unsigned long long)upitch * (unsigned)(15 - v));
             if (v <= lim) {
                 sum += Ip + Im;
                 m01 += v * (Ip - Im);
@@ -264,12 +267,16 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     // ---- lane computes descriptor byte `lane`: tests 8*lane .. 8*lane+7
 #if DESC_STAGE
     __syncwarp();
-    const uint8_t* Bc = reinterpret_cast<const uint8_t*>(sWin[threadIdx.x >> 5]) + 18 * 40 + 18 + sh;
+    const uint8_t* Bc = reinterpret_cast<const uint8_t*>(sWin[threadIdx.x >> 5]) + sh;
     const int pitch = 40;
+    const int kOff = 18 * 40 + 18;
 #define DESC_LD(p) (*(p))
 #else
+    // one per-lane 64-bit pointer to the centre + a signed 32-bit offset
     const uint8_t* Bc = blur + centre;
+    asm volatile("" : "+l"(Bc));
     const int pitch = g.pitch;
+    const int kOff = 0;
 #define DESC_LD(p) __ldg(p)
 #endif
     uint32_t byte = 0;
@@ -277,10 +284,10 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     for (int k = 0; k < 8; ++k) {
         const float4 pt = sPat[k * 32 + lane];   // test 8*lane + k
         const float x0 = pt.x, y0 = pt.y, x1 = pt.z, y1 = pt.w;
-        const int t0 = DESC_LD(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * pitch +
-                             __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b))));
-        const int t1 = DESC_LD(Bc + __float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a))) * pitch +
-                             __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b))));
+        const int t0 = DESC_LD(Bc + (long long)(__float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * pitch +
+                                                __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b))) + kOff));
+        const int t1 = DESC_LD(Bc + (long long)(__float2int_rn(__fadd_rn(__fmul_rn(x1, b), __fmul_rn(y1, a))) * pitch +
+                                                __float2int_rn(__fsub_rn(__fmul_rn(x1, a), __fmul_rn(y1, b))) + kOff));
         byte |= (uint32_t)(t0 < t1) << k;
     }
     // gather 4 bytes per word: lanes 4j..4j+3 -> word j, written by lane 4j

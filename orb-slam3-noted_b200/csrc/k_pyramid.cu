@@ -129,27 +129,34 @@ __global__ void __launch_bounds__(128, PYR_MINB) k_pyr_resize_plan(uint8_t* __re
     const uint32_t* sbase = reinterpret_cast<const uint32_t*>(pyr + gs.base + (long long)frame * gs.plane +
                                                               (long long)ORBFE_EDGE * gs.pitch + ORBFE_XO);
     const int spw = gs.pitch >> 2;
-    uint32_t* dst = reinterpret_cast<uint32_t*>(pyr + gd.base + (long long)frame * gd.plane) + word;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(pyr + gd.base + (long long)frame * gd.plane);     // uniform; the word goes into the offset
     const int dpw = gd.pitch >> 2;
     // lane j prepares the vertical tap of row0 + j once (reflection, table read, word offsets of the two
     // source rows, weights pre-shifted so that (a * x) >> 16 is one IMAD.HI); the row loop broadcasts it
-    int myOff0 = 0, myOff1 = 0;
+    // All addresses below are a uniform 64-bit base plus an UNSIGNED 32-bit word offset (one IMAD.WIDE.U32 each): with signed
+    // ints the compiler sign-extended and rebuilt every pointer in four instructions, a quarter of the row loop (r02 SASS).
+    unsigned myOff0 = 0, myOff1 = 0;
     uint32_t myA0 = 0, myA1 = 0;
     if (lane < PYR_TH && row0 + lane < row1) {
         const ResizeTap t = taps[gd.tabY + reflect101(row0 + lane - ORBFE_EDGE, gd.h)];
-        myOff0 = (int)t.s0 * spw; myOff1 = (int)t.s1 * spw;
+        myOff0 = (unsigned)t.s0 * (unsigned)spw; myOff1 = (unsigned)t.s1 * (unsigned)spw;
         myA0 = (uint32_t)t.a0 << 16; myA1 = (uint32_t)t.a1 << 16;
     }
+    const unsigned b01 = (unsigned)cp.base01, b23 = (unsigned)cp.base23;
+    unsigned doff = (unsigned)row0 * (unsigned)dpw + (unsigned)word;
 #pragma unroll 4
     for (int row = row0; row < row1; ++row) {
         const int j = row - row0;
-        const uint32_t* S0 = sbase + __shfl_sync(0xffffffffu, myOff0, j);
-        const uint32_t* S1 = sbase + __shfl_sync(0xffffffffu, myOff1, j);
+        const unsigned o0 = __shfl_sync(0xffffffffu, myOff0, j), o1 = __shfl_sync(0xffffffffu, myOff1, j);
         const uint32_t a0s = __shfl_sync(0xffffffffu, myA0, j), a1s = __shfl_sync(0xffffffffu, myA1, j);
-        const uint32_t p0a = __byte_perm(S0[cp.base01], S0[cp.base01 + 1], cp.sel & 0xFFFF);
-        const uint32_t p0b = __byte_perm(S0[cp.base23], S0[cp.base23 + 1], cp.sel >> 16);
-        const uint32_t p1a = __byte_perm(S1[cp.base01], S1[cp.base01 + 1], cp.sel & 0xFFFF);
-        const uint32_t p1b = __byte_perm(S1[cp.base23], S1[cp.base23 + 1], cp.sel >> 16);
+        const uint32_t* q0a = sbase + (o0 + b01);
+        const uint32_t* q0b = sbase + (o0 + b23);
+        const uint32_t* q1a = sbase + (o1 + b01);
+        const uint32_t* q1b = sbase + (o1 + b23);
+        const uint32_t p0a = __byte_perm(__ldg(q0a), __ldg(q0a + 1), cp.sel & 0xFFFF);
+        const uint32_t p0b = __byte_perm(__ldg(q0b), __ldg(q0b + 1), cp.sel >> 16);
+        const uint32_t p1a = __byte_perm(__ldg(q1a), __ldg(q1a + 1), cp.sel & 0xFFFF);
+        const uint32_t p1b = __byte_perm(__ldg(q1b), __ldg(q1b + 1), cp.sel >> 16);
         int r0[4], r1[4];
         r0[0] = __dp2a_lo(cp.a[0], p0a, 0u); r0[1] = __dp2a_hi(cp.a[1], p0a, 0u);
         r0[2] = __dp2a_lo(cp.a[2], p0b, 0u); r0[3] = __dp2a_hi(cp.a[3], p0b, 0u);
@@ -159,7 +166,8 @@ __global__ void __launch_bounds__(128, PYR_MINB) k_pyr_resize_plan(uint8_t* __re
 #pragma unroll
         for (int k = 0; k < 4; ++k) o[k] = (__umulhi(a0s, (uint32_t)r0[k] >> 4) + __umulhi(a1s, (uint32_t)r1[k] >> 4) + 2u) >> 2;
         const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
-        dst[(long long)row * dpw] = v & cp.keep;
+        dst[doff] = v & cp.keep;
+        doff += (unsigned)dpw;
     }
 }
 
