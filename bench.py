@@ -629,7 +629,7 @@ def run_orbfe(args):
                 "host_ceiling_gbs": link, "host_ceiling_frames_per_s": link["both"]["h2d_gbs"] * 1e9 / (W * H),
                 "host_ceiling_note": "pinned H2D of the frame batch and D2H of a result-sized buffer on two streams, all ranks at once "
                                      "(aggregate over ranks); frames/s ceiling = concurrent H2D rate / bytes per frame",
-                "api": "orbfe_extract_batch (pinned host buffers; 64-frame chunks pipelined over copy-in / 2 compute / copy-out streams)"},
+                "api": "orbfe_extract_batch (pinned host buffers; chunks of 64 752x480 frames' worth of bytes pipelined over copy-in / 2 compute / copy-out streams)"},
         "gpu_launches": int(launches), "graph_launches": int(graph_launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
