@@ -15,6 +15,8 @@
 //               the 31 disc rows are read straight from the (L1/L2-resident) level, lanes = columns,
 //               butterfly reduction of m10/m01; then lane i evaluates tests 8i..8i+7 on the blurred level
 //               and owns byte i of the descriptor, exactly the reference's inner loop.
+#include <algorithm>
+
 #include "orbfe_internal.h"
 
 #define ASM_THREADS 256
@@ -126,10 +128,11 @@ __device__ __forceinline__ float fast_atan2_deg(float y, float x) {
 #ifndef BLUR_PTR
 #define BLUR_PTR 1
 #endif
-__global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
-                                              const LevelGeom* __restrict__ geom, int nlevels, int totalTiles, int frame0) {
-    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5), lane = threadIdx.x & 31, frame = frame0 + blockIdx.y;
-    if (tile >= totalTiles) return;
+#ifndef BLUR_DP2A
+#define BLUR_DP2A 1
+#endif
+__device__ __forceinline__ void blur_tile(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur, const LevelGeom* __restrict__ geom,
+                                          int nlevels, int tile, int frame, int lane) {
     int level = 0;
     while (level + 1 < nlevels && tile >= geom[level + 1].blurTileBase) ++level;
     const LevelGeom& g = geom[level];
@@ -148,6 +151,42 @@ __global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restri
     // past a short last tile are simply read (the level's own bottom border and, beyond it, the arena's slack: the results
     // of those rows are never stored) - only the store is predicated, and source / destination advance by one pitch per
     // row (a clamped row index cost a 64-bit multiply-add per row: 12.6 % of the kernel's instructions, profiles/r01o_*).
+#if BLUR_DP2A
+    // Vertical pass on PAIRS of rows: the horizontal sums are 16-bit (<= 255 * 256), two rows share a register as packed
+    // halves and one IDP.2A applies two taps: per pixel column and row one PRMT (new pair), three IDP.2A and one IMAD instead
+    // of three adds and four multiply-adds.  When row r + 6 arrives pr[j] = (h(r + j), h(r + j + 1)), j = 0..4: output row r
+    // uses pr[0], pr[2], pr[4] and the new row on its own.
+    uint32_t pr[5][4], hp[4] = {0u, 0u, 0u, 0u};
+    const uint32_t w01 = 18u | 34u << 8, w23 = 48u | 56u << 8, w45 = 48u | 34u << 8;
+#pragma unroll
+    for (int r = 0; r < BLUR_TH + 6; ++r) {
+        const uint32_t* p = src;
+        src += pw;
+        const uint32_t wm = __ldg(p - 1), w0 = __ldg(p), wp = __ldg(p + 1);
+        uint32_t hn[4];
+        hn[0] = __dp4a(__byte_perm(wm, w0, 0x4321), qa, __dp4a(__byte_perm(w0, wp, 0x4321), qb, 0u));
+        hn[1] = __dp4a(__byte_perm(wm, w0, 0x5432), qa, __dp4a(__byte_perm(w0, wp, 0x5432), qb, 0u));
+        hn[2] = __dp4a(__byte_perm(wm, w0, 0x6543), qa, __dp4a(__byte_perm(w0, wp, 0x6543), qb, 0u));
+        hn[3] = __dp4a(w0, qa, __dp4a(wp, qb, 0u));
+        if (r >= 6) {
+            uint32_t v[4];
+#pragma unroll
+            for (int k = 0; k < 4; ++k)     // < 2^24: the rounded result is byte 2
+                v[k] = __dp2a_lo(pr[0][k], w01, __dp2a_lo(pr[2][k], w23, __dp2a_lo(pr[4][k], w45, 18u * hn[k] + 32768u)));
+            const uint32_t o = __byte_perm(__byte_perm(v[0], v[1], 0x0062), __byte_perm(v[2], v[3], 0x0062), 0x5410);
+            if (r - 6 < rows) *dst = o;
+            dst += pw;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) pr[j][k] = pr[j + 1][k];
+            pr[4][k] = __byte_perm(hp[k], hn[k], 0x5410);
+            hp[k] = hn[k];
+        }
+    }
+}
+#else
     uint32_t h[7][4];
 #pragma unroll
     for (int r = 0; r < BLUR_TH + 6; ++r) {
@@ -179,6 +218,24 @@ __global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restri
             if (r - 6 < rows) dst[(long long)(r - 6) * pw] = o;
 #endif
         }
+    }
+}
+#endif
+
+__global__ void __launch_bounds__(128, BLUR_MINB) k_blur(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
+                                              const LevelGeom* __restrict__ geom, int nlevels, int totalTiles, int frame0) {
+    const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+    if (tile < totalTiles) blur_tile(pyr, blur, geom, nlevels, tile, frame0 + blockIdx.y, threadIdx.x & 31);
+}
+// The same tiles walked by a fixed number of resident CTAs (grid = SMs x CTAs per SM): the form that runs beside FAST.
+__global__ void __launch_bounds__(128, BLUR_MINB) k_blur_resident(const uint8_t* __restrict__ pyr, uint8_t* __restrict__ blur,
+                                                       const LevelGeom* __restrict__ geom, int nlevels, int totalTiles, int frame0,
+                                                       int batch) {
+    const int lane = threadIdx.x & 31;
+    const long long all = (long long)totalTiles * batch;
+    for (long long g = (long long)blockIdx.x * 4 + (threadIdx.x >> 5); g < all; g += (long long)gridDim.x * 4) {
+        const int f = (int)(g / totalTiles);
+        blur_tile(pyr, blur, geom, nlevels, (int)(g - (long long)f * totalTiles), frame0 + f, lane);
     }
 }
 
@@ -304,12 +361,20 @@ cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int la
     return cudaGetLastError();
 }
 
-cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch) {
-    {
+cudaError_t orbfe_launch_blur(orbfe_handle* h, int frame0, int batch, cudaStream_t st, int persistPerSm) {
+    if (persistPerSm > 0) {
+        const long long groups = ((long long)h->blurTiles * batch + 3) / 4;
+        const int grid = (int)std::min<long long>(groups, (long long)h->smCount * persistPerSm);
+        k_blur_resident<<<grid, 128, 0, st>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles, frame0, batch);
+    } else {
         dim3 grid((h->blurTiles + 3) / 4, batch);
-        k_blur<<<grid, 128, 0, h->cur>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles, frame0);
-        h->launches++;
+        k_blur<<<grid, 128, 0, st>>>(h->dPyr, h->dBlur, h->dGeom, h->p.nlevels, h->blurTiles, frame0);
     }
+    h->launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch) {
     dim3 grid((h->kpPerFrame + DESC_WARPS - 1) / DESC_WARPS, batch);
     k_describe<<<grid, DESC_WARPS * 32, 0, h->cur>>>(h->dPyr, h->dBlur, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps,
                                                        h->dDesc, frame0);

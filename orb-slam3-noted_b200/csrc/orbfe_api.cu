@@ -13,6 +13,16 @@
 #include <vector>
 
 #include "orbfe_internal.h"
+// Measured (profiles/r02v_blur_sweep.txt): the blur on a side stream under FAST + quadtree gains nothing - 184.3 k frames/s
+// serial, 184.5 k with the ordinary grid on the side stream (the block scheduler runs the two kernels one after the other),
+// 149 / 173 / 179 / 180.5 k with 1 / 2 / 3 / 4 resident blur CTAs per SM (four blur warps per SM are too slow, more take the
+// registers FAST needs).  Off by default; the knobs stay for other shapes.
+#ifndef ORBFE_BLUR_OVERLAP
+#define ORBFE_BLUR_OVERLAP 0
+#endif
+#ifndef ORBFE_BLUR_PERSIST
+#define ORBFE_BLUR_PERSIST 4
+#endif
 #ifndef ORBFE_FAST_BOX80
 #define ORBFE_FAST_BOX80 0     // FAST tile pitch 80 instead of 64 bytes (bank spread of the tile rows); see k_fast.cu
 #endif
@@ -283,8 +293,12 @@ static void free_handle(orbfe_handle* h) {
             if (h->evPipe[c][k]) cudaEventDestroy(h->evPipe[c][k]);
     if (h->evFork) cudaEventDestroy(h->evFork);
     if (h->evOrder) cudaEventDestroy(h->evOrder);
-    for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
+    for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i) {
         if (h->evJoin[i]) cudaEventDestroy(h->evJoin[i]);
+        if (h->evPyr[i]) cudaEventDestroy(h->evPyr[i]);
+        if (h->evBlur[i]) cudaEventDestroy(h->evBlur[i]);
+        if (h->sSide[i]) cudaStreamDestroy(h->sSide[i]);
+    }
     if (h->sIn) cudaStreamDestroy(h->sIn);
     if (h->sOut) cudaStreamDestroy(h->sOut);
     for (int i = 1; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
@@ -415,6 +429,12 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaEventCreateWithFlags(&h->evFork, cudaEventDisableTiming));
     CKC(cudaEventCreateWithFlags(&h->evOrder, cudaEventDisableTiming));
     for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i) CKC(cudaEventCreateWithFlags(&h->evJoin[i], cudaEventDisableTiming));
+    for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i) {
+        CKC(cudaStreamCreateWithFlags(&h->sSide[i], cudaStreamNonBlocking));
+        CKC(cudaEventCreateWithFlags(&h->evPyr[i], cudaEventDisableTiming));
+        CKC(cudaEventCreateWithFlags(&h->evBlur[i], cudaEventDisableTiming));
+    }
+    CKC(cudaDeviceGetAttribute(&h->smCount, cudaDevAttrMultiProcessorCount, h->device));
     {   // device-resident pipeline tuning (see run_device_pipeline); the environment overrides are for sweeps
         const char* e1 = getenv("ORBFE_DEV_CHUNK");
         const char* e2 = getenv("ORBFE_DEV_STREAMS");
@@ -422,6 +442,10 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
         h->devChunk = e1 && atoi(e1) > 0 ? atoi(e1) : ORBFE_DEV_CHUNK;
         h->devStreams = e2 && atoi(e2) > 0 ? std::min(atoi(e2), ORBFE_MAX_COMPUTE_STREAMS) : ORBFE_DEV_STREAMS;
         h->useGraphs = e3 ? atoi(e3) != 0 : 1;
+        const char* e4 = getenv("ORBFE_BLUR_OVERLAP");
+        const char* e5 = getenv("ORBFE_BLUR_PERSIST");
+        h->blurOverlap = e4 ? atoi(e4) != 0 : ORBFE_BLUR_OVERLAP;
+        h->blurPersist = e5 ? std::max(0, atoi(e5)) : ORBFE_BLUR_PERSIST;
     }
     for (int c = 0; c < ORBFE_PIPE_MAX_CHUNKS; ++c)
         for (int k = 0; k < 3; ++k) CKC(cudaEventCreateWithFlags(&h->evPipe[c][k], cudaEventDisableTiming));
@@ -504,12 +528,27 @@ static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int frame0, 
     }
     if ((e = orbfe_launch_pyramid(h, dImages, frame0, batch, W, H, stride, frameStride)) != cudaSuccess) return cuda_fail(e, "pyramid");
     if (ev) CK(cudaEventRecord(ev[1], h->cur));
+    // The blur needs the pyramid and nothing else, FAST + quadtree + assemble do not need the blur: it goes to a side stream
+    // (forked from and joined back into h->cur, so a capture sees one graph) as a few RESIDENT CTAs per SM that walk the
+    // tiles - FAST is latency-bound at two thirds of the issue slots and leaves registers free, the blur is pure ALU work.
+    int side = -1;
+    if (!h->profiling && h->blurOverlap)
+        for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
+            if (h->sComp[i] == h->cur) side = i;
+    if (side >= 0) {
+        CK(cudaEventRecord(h->evPyr[side], h->cur));
+        CK(cudaStreamWaitEvent(h->sSide[side], h->evPyr[side], 0));
+        if ((e = orbfe_launch_blur(h, frame0, batch, h->sSide[side], h->blurPersist)) != cudaSuccess) return cuda_fail(e, "blur");
+        CK(cudaEventRecord(h->evBlur[side], h->sSide[side]));
+    }
     if ((e = orbfe_launch_fast(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "fast");
     if (ev) CK(cudaEventRecord(ev[2], h->cur));
     if ((e = orbfe_launch_octree(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "octree");
     if (ev) CK(cudaEventRecord(ev[3], h->cur));
     if ((e = orbfe_launch_assemble(h, frame0, batch, lap0, lap1)) != cudaSuccess) return cuda_fail(e, "assemble");
     if (ev) CK(cudaEventRecord(ev[4], h->cur));
+    if (side >= 0) CK(cudaStreamWaitEvent(h->cur, h->evBlur[side], 0));
+    else if ((e = orbfe_launch_blur(h, frame0, batch, h->cur, 0)) != cudaSuccess) return cuda_fail(e, "blur");
     if ((e = orbfe_launch_describe(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "describe");
     if (ev) { CK(cudaEventRecord(ev[5], h->cur)); h->profCount++; }
     h->lastBatch = std::max(h->lastBatch, frame0 + batch);

@@ -104,6 +104,10 @@ struct orbfe_handle {
     cudaStream_t sComp[ORBFE_MAX_COMPUTE_STREAMS];   // compute streams of the chunked pipelines; sComp[0] == stream
     cudaEvent_t evPipe[ORBFE_PIPE_MAX_CHUNKS][3];    // per chunk: [0][0] fence, [c][1] frames landed, [c][2] results ready
     cudaEvent_t evFork, evJoin[ORBFE_MAX_COMPUTE_STREAMS], evOrder;
+    // the blur of a chunk only needs its pyramid: it runs on a side stream under FAST + quadtree + assemble (enqueue_extract)
+    cudaStream_t sSide[ORBFE_MAX_COMPUTE_STREAMS];
+    cudaEvent_t evPyr[ORBFE_MAX_COMPUTE_STREAMS], evBlur[ORBFE_MAX_COMPUTE_STREAMS];
+    int blurOverlap, blurPersist, smCount;         // overlap on/off; resident blur CTAs per SM (0: one CTA per four tiles)
     int devChunk, devStreams;                        // device-resident pipeline: frames per chunk, compute streams used
     int useGraphs;
     OrbfeGraphSlot graphs[ORBFE_GRAPH_SLOTS];
@@ -174,4 +178,5 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int fr
 cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch);
 cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch);
 cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int lap0, int lap1);
+cudaError_t orbfe_launch_blur(orbfe_handle* h, int frame0, int batch, cudaStream_t st, int persistPerSm);
 cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch);
