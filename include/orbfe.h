@@ -141,6 +141,16 @@ int orbfe_extractor_wait_stream(orbfe_handle* h, void* stream);
  * chunk_frames / compute_streams <= 0 and use_graphs < 0 keep the current value.  Synchronises the handle. */
 int orbfe_set_pipeline(orbfe_handle* h, int chunk_frames, int compute_streams, int use_graphs);
 
+/* Which kernel computes GaussianBlur(7x7, 2, 2) (ORBextractor.cc:1114-1115): the integer-ALU kernel (k_blur) or the tensor-core
+ * kernel (k_blur_tc: the two passes as banded int8 GEMMs on tcgen05.mma).  Same bytes either way; no counterpart in the
+ * reference.  ORBFE_BLUR=alu|tensor in the environment sets the initial value.  Synchronises the handle. */
+enum { ORBFE_BLUR_ALU = 0, ORBFE_BLUR_TENSOR = 1 };
+int orbfe_set_blur_backend(orbfe_handle* h, int backend);
+
+/* Tap: the blurred level the descriptors of the last call were sampled from (the reference's `workingMat` after GaussianBlur),
+ * ROI only, w x h bytes (sizes from orbfe_get_pyramid_level) into dst with dst_stride >= w. */
+int orbfe_get_blurred_level(orbfe_handle* h, int frame, int level, uint8_t* dst, ptrdiff_t dst_stride);
+
 /* Per-stage device timing (the REGISTER_TIMES switch of include/Config.h:4 / Frame.cc:116-127, done
  * with CUDA events on the handle's stream).  While enabled every extract call brackets its stages
  * with events; orbfe_get_stage_times synchronises, adds up the elapsed milliseconds per stage since

@@ -362,6 +362,7 @@ cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int la
 }
 
 cudaError_t orbfe_launch_blur(orbfe_handle* h, int frame0, int batch, cudaStream_t st, int persistPerSm) {
+    if (h->blurBackend == ORBFE_BLUR_TENSOR) return orbfe_launch_blur_tc(h, frame0, batch, st);
     if (persistPerSm > 0) {
         const long long groups = ((long long)h->blurTiles * batch + 3) / 4;
         const int grid = (int)std::min<long long>(groups, (long long)h->smCount * persistPerSm);

@@ -17,6 +17,9 @@
 // serial, 184.5 k with the ordinary grid on the side stream (the block scheduler runs the two kernels one after the other),
 // 149 / 173 / 179 / 180.5 k with 1 / 2 / 3 / 4 resident blur CTAs per SM (four blur warps per SM are too slow, more take the
 // registers FAST needs).  Off by default; the knobs stay for other shapes.
+#ifndef ORBFE_BLUR_DEFAULT
+#define ORBFE_BLUR_DEFAULT ORBFE_BLUR_ALU
+#endif
 #ifndef ORBFE_BLUR_OVERLAP
 #define ORBFE_BLUR_OVERLAP 0
 #endif
@@ -444,6 +447,8 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
         h->useGraphs = e3 ? atoi(e3) != 0 : 1;
         const char* e4 = getenv("ORBFE_BLUR_OVERLAP");
         const char* e5 = getenv("ORBFE_BLUR_PERSIST");
+        const char* e6 = getenv("ORBFE_BLUR");
+        h->blurBackend = e6 ? (strcmp(e6, "alu") == 0 ? ORBFE_BLUR_ALU : ORBFE_BLUR_TENSOR) : ORBFE_BLUR_DEFAULT;
         h->blurOverlap = e4 ? atoi(e4) != 0 : ORBFE_BLUR_OVERLAP;
         h->blurPersist = e5 ? std::max(0, atoi(e5)) : ORBFE_BLUR_PERSIST;
     }
@@ -925,6 +930,15 @@ extern "C" int orbfe_set_pipeline(orbfe_handle* h, int chunk_frames, int compute
     return ORBFE_OK;
 }
 
+extern "C" int orbfe_set_blur_backend(orbfe_handle* h, int backend) {
+    if (!h || (backend != ORBFE_BLUR_ALU && backend != ORBFE_BLUR_TENSOR)) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    CK(cudaStreamSynchronize(h->stream));
+    h->blurBackend = backend;
+    drop_graphs(h);
+    return ORBFE_OK;
+}
+
 extern "C" int orbfe_device_results(orbfe_handle* h, const orbfe_keypoint** d_kps, const uint8_t** d_desc, const int** d_n,
                                     const int** d_mono, int* cap) {
     if (!h) return ORBFE_ERR_BAD_ARGUMENT;
@@ -951,6 +965,20 @@ extern "C" int orbfe_get_pyramid_level(orbfe_handle* h, int frame, int level, ui
     CK(cudaSetDevice(h->device));
     const uint8_t* src = h->dPyr + g.base + (long long)frame * g.plane + (ORBFE_XO - ORBFE_EDGE);
     CK(cudaMemcpy2DAsync(dst, dst_stride, src, g.pitch, bw, g.rows, cudaMemcpyDeviceToHost, h->stream));
+    CK(cudaStreamSynchronize(h->stream));
+    return ORBFE_OK;
+}
+
+// The blurred level descriptors are sampled from (the reference's `workingMat` after GaussianBlur, ORBextractor.cc:1114-1115): ROI only.
+extern "C" int orbfe_get_blurred_level(orbfe_handle* h, int frame, int level, uint8_t* dst, ptrdiff_t dst_stride) {
+    if (!h || !dst || level < 0 || level >= h->p.nlevels) return ORBFE_ERR_BAD_ARGUMENT;
+    if (h->lastBatch <= 0) return ORBFE_ERR_NOT_READY;
+    if (frame < 0 || frame >= h->lastBatch) return ORBFE_ERR_BAD_ARGUMENT;
+    const LevelGeom& g = h->geom[level];
+    if (dst_stride < g.w) return ORBFE_ERR_BAD_ARGUMENT;
+    CK(cudaSetDevice(h->device));
+    const uint8_t* src = h->dBlur + g.base + (long long)frame * g.plane + (long long)ORBFE_EDGE * g.pitch + ORBFE_XO;
+    CK(cudaMemcpy2DAsync(dst, dst_stride, src, g.pitch, g.w, g.h, cudaMemcpyDeviceToHost, h->stream));
     CK(cudaStreamSynchronize(h->stream));
     return ORBFE_OK;
 }

@@ -107,6 +107,7 @@ struct orbfe_handle {
     // the blur of a chunk only needs its pyramid: it runs on a side stream under FAST + quadtree + assemble (enqueue_extract)
     cudaStream_t sSide[ORBFE_MAX_COMPUTE_STREAMS];
     cudaEvent_t evPyr[ORBFE_MAX_COMPUTE_STREAMS], evBlur[ORBFE_MAX_COMPUTE_STREAMS];
+    int blurBackend;                               // ORBFE_BLUR_ALU / ORBFE_BLUR_TENSOR (include/orbfe.h)
     int blurOverlap, blurPersist, smCount;         // overlap on/off; resident blur CTAs per SM (0: one CTA per four tiles)
     int devChunk, devStreams;                        // device-resident pipeline: frames per chunk, compute streams used
     int useGraphs;
@@ -179,4 +180,5 @@ cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch);
 cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch);
 cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int lap0, int lap1);
 cudaError_t orbfe_launch_blur(orbfe_handle* h, int frame0, int batch, cudaStream_t st, int persistPerSm);
+cudaError_t orbfe_launch_blur_tc(orbfe_handle* h, int frame0, int batch, cudaStream_t st);     // k_blur_tc.cu
 cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch);

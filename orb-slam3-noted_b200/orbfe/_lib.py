@@ -61,6 +61,8 @@ def lib():
         "orbfe_fetch_results": (_I, [_P, _I, _P, _P, _I, _P, _P]),
         "orbfe_get_pyramid_level": (_I, [_P, _I, _I, _P, _PD, C.POINTER(_I), C.POINTER(_I)]),
         "orbfe_get_candidates": (_I, [_P, _I, _I, _P, _I]),
+        "orbfe_get_blurred_level": (_I, [_P, _I, _I, _P, _PD]),
+        "orbfe_set_blur_backend": (_I, [_P, _I]),
         "orbfe_get_pyramid": (_I, [_P, _I, _P, _P]),
         "orbfe_get_level_size": (_I, [_P, _I, C.POINTER(_I), C.POINTER(_I)]),
         "orbfe_stream": (_P, [_P]),
@@ -93,7 +95,7 @@ def exported_symbols():
     from . import _matcher_proto
     return ["orbfe_create", "orbfe_destroy", "orbfe_get_tables", "orbfe_max_keypoints", "orbfe_extract",
             "orbfe_extract_batch", "orbfe_extract_batch_device", "orbfe_device_results", "orbfe_fetch_results",
-            "orbfe_get_pyramid_level", "orbfe_get_pyramid", "orbfe_get_level_size", "orbfe_get_candidates", "orbfe_stream", "orbfe_synchronize",
+            "orbfe_get_pyramid_level", "orbfe_get_pyramid", "orbfe_get_level_size", "orbfe_get_candidates", "orbfe_get_blurred_level", "orbfe_set_blur_backend", "orbfe_stream", "orbfe_synchronize",
             "orbfe_launch_count", "orbfe_graph_launch_count", "orbfe_stream_wait_extractor", "orbfe_extractor_wait_stream",
             "orbfe_set_pipeline", "orbfe_set_profiling", "orbfe_set_input_format", "orbfe_get_stage_times", "orbfe_stage_name", "orbfe_strerror", "orbfe_last_cuda_error", "orbfe_version"] + list(_matcher_proto.PROTO)
 

@@ -199,6 +199,26 @@ class ORBextractor:
         if st < 0:
             raise OrbfeError(st, "orbfe_extractor_wait_stream")
 
+    BLUR_ALU, BLUR_TENSOR = 0, 1
+
+    def set_blur_backend(self, backend):
+        """k_blur (integer ALU) or k_blur_tc (tcgen05 int8 GEMMs); same bytes either way."""
+        st = self._lib.orbfe_set_blur_backend(self._h, int(backend))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_set_blur_backend")
+
+    def blurred_level(self, level, frame=0):
+        """The blurred level the descriptors were sampled from (the reference's workingMat after GaussianBlur), ROI only."""
+        w, h = C.c_int(), C.c_int()
+        st = self._lib.orbfe_get_pyramid_level(self._h, frame, level, None, 0, C.byref(w), C.byref(h))
+        if st < 0:
+            raise OrbfeError(st, "orbfe_get_pyramid_level")
+        buf = np.zeros((h.value, w.value), np.uint8)
+        st = self._lib.orbfe_get_blurred_level(self._h, frame, level, ptr(buf), buf.strides[0])
+        if st < 0:
+            raise OrbfeError(st, "orbfe_get_blurred_level")
+        return buf
+
     def set_pipeline(self, chunk_frames=0, compute_streams=0, use_graphs=-1):
         st = self._lib.orbfe_set_pipeline(self._h, int(chunk_frames), int(compute_streams), int(use_graphs))
         if st < 0:
