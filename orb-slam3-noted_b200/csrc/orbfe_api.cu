@@ -17,6 +17,9 @@
 // serial, 184.5 k with the ordinary grid on the side stream (the block scheduler runs the two kernels one after the other),
 // 149 / 173 / 179 / 180.5 k with 1 / 2 / 3 / 4 resident blur CTAs per SM (four blur warps per SM are too slow, more take the
 // registers FAST needs).  Off by default; the knobs stay for other shapes.
+#ifndef ORBFE_PIPE_STREAMS
+#define ORBFE_PIPE_STREAMS 2       // compute streams of the host-buffer pipeline (orbfe_extract_batch)
+#endif
 #ifndef ORBFE_BLUR_DEFAULT
 #define ORBFE_BLUR_DEFAULT ORBFE_BLUR_ALU
 #endif
@@ -827,20 +830,35 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
     } else {
         int f = std::min(pipeChunk / 4 > 0 ? pipeChunk / 4 : 1, batch);
         bounds[++nchunks] = f;
-        while (f < batch) {
-            f = (batch - f <= pipeChunk + pipeChunk / 2 || nchunks + 1 >= ORBFE_PIPE_MAX_CHUNKS) ? batch : f + pipeChunk;
+        // ... and optionally a tapering tail (half, then a quarter chunk; ORBFE_PIPE_TAPER=1).  Measured twice, no effect either
+        // time (124.6 k vs 124.1 k frames/s, round 2): the timeline (ORBFE_PIPE_TRACE=1, tools/probe/pipe_trace.py) shows the
+        // copy-in stream busy back to back for 3.48 of the 4.13 ms and every chunk's kernels finishing ~0.7 ms after its bytes
+        // arrive - a chunk is a chain of fourteen dependent launches with a latency floor of 0.3-0.5 ms however small it is -
+        // so what follows the last copy-in is that lag, not the size of the last chunk.
+        static const int taper = [] { const char* e = getenv("ORBFE_PIPE_TAPER"); return e ? atoi(e) : 0; }();
+        const int t2 = taper && pipeChunk >= 8 ? pipeChunk / 2 : 0, t4 = taper && pipeChunk >= 8 ? pipeChunk / 4 : 0;
+        int body = batch - f - t2 - t4;                       // frames between the short first chunk and the tail
+        int tail2 = t2, tail4 = t4;
+        if (body < pipeChunk / 2) { body = batch - f; tail2 = tail4 = 0; }     // too short to taper
+        int nbody = (body + pipeChunk - 1) / pipeChunk;
+        if (nchunks + nbody + 2 > ORBFE_PIPE_MAX_CHUNKS) nbody = ORBFE_PIPE_MAX_CHUNKS - nchunks - 2;
+        for (int k = 0; k < nbody; ++k) {                     // even body chunks
+            f += body / nbody + (k < body % nbody ? 1 : 0);
             bounds[++nchunks] = f;
         }
-        // (a tapering tail - shorter last chunks - was measured in round 1 and had no effect: the path sits on the PCIe link)
+        if (tail2) { f += tail2; bounds[++nchunks] = f; }
+        if (tail4) { f += tail4; bounds[++nchunks] = f; }
     }
     const int kpf = h->kpPerFrame;
     const size_t fbytes = (size_t)rowBytes * height;
     h->lastBatch = 0;
-    cudaStream_t sAlt = h->sComp[1];
+    static const int pipeStreams = [] { const char* e = getenv("ORBFE_PIPE_STREAMS"); int v = e ? atoi(e) : 0; return v > 0 ? std::min(v, ORBFE_MAX_COMPUTE_STREAMS) : ORBFE_PIPE_STREAMS; }();
     // an error in the middle must not return while copies into the caller's buffers are still in flight
     auto fail = [&](int code) {
         h->cur = h->stream;
-        cudaStreamSynchronize(h->sIn); cudaStreamSynchronize(sAlt); cudaStreamSynchronize(h->stream); cudaStreamSynchronize(h->sOut);
+        cudaStreamSynchronize(h->sIn);
+        for (int i = 0; i < pipeStreams; ++i) cudaStreamSynchronize(h->sComp[i]);
+        cudaStreamSynchronize(h->sOut);
         return code;
     };
 #define CKP(call)                                                   \
@@ -848,9 +866,16 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
         cudaError_t e_ = (call);                                    \
         if (e_ != cudaSuccess) return fail(cuda_fail(e_, #call));   \
     } while (0)
+    // ORBFE_PIPE_TRACE=1 (debug): timed events after every copy-in, chunk of kernels and copy-out, printed to stderr
+    static const int trace = [] { const char* e = getenv("ORBFE_PIPE_TRACE"); return e ? atoi(e) : 0; }();
+    std::vector<cudaEvent_t> tev;
+    auto mark = [&](cudaStream_t s_) { if (trace) { cudaEvent_t e_; cudaEventCreate(&e_); cudaEventRecord(e_, s_); tev.push_back(e_); } };
+    mark(h->stream);
     CKP(cudaEventRecord(h->evPipe[0][0], h->stream));          // copy-in / the second compute stream must not overtake earlier work
     CKP(cudaStreamWaitEvent(h->sIn, h->evPipe[0][0], 0));
-    CKP(cudaStreamWaitEvent(sAlt, h->evPipe[0][0], 0));
+    for (int i = 1; i < pipeStreams; ++i) CKP(cudaStreamWaitEvent(h->sComp[i], h->evPipe[0][0], 0));
+    // every copy-in is enqueued before the first kernel: the copy stream then runs back to back whatever the host needs to
+    // enqueue a chunk's fourteen launches (the short first chunk is copied faster than its kernels are enqueued)
     for (int c = 0; c < nchunks; ++c) {
         const int f0 = bounds[c], nb = bounds[c + 1] - f0;
         if (stride == rowBytes && frame_stride == (ptrdiff_t)fbytes) {
@@ -861,15 +886,20 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
                                       cudaMemcpyHostToDevice, h->sIn));
         }
         CKP(cudaEventRecord(h->evPipe[c][1], h->sIn));
-        // chunks alternate between two compute streams, so the latency-bound stages of one chunk (small
-        // pyramid levels, quadtree) run under the wide stages of its neighbour
-        cudaStream_t compute = (c & 1) ? sAlt : h->stream;
+        mark(h->sIn);
+    }
+    for (int c = 0; c < nchunks; ++c) {
+        const int f0 = bounds[c], nb = bounds[c + 1] - f0;
+        // chunks go round the compute streams, so the latency-bound stages of one chunk (small pyramid levels, quadtree)
+        // run under the wide stages of its neighbours
+        cudaStream_t compute = h->sComp[c % pipeStreams];
         CKP(cudaStreamWaitEvent(compute, h->evPipe[c][1], 0));
         h->cur = compute;
         st = enqueue_extract(h, h->dIn + f0 * fbytes, f0, nb, width, height, rowBytes, (long long)fbytes, lap0, lap1);
         h->cur = h->stream;
         if (st != ORBFE_OK) return fail(st);
         CKP(cudaEventRecord(h->evPipe[c][2], compute));
+        mark(compute);
         CKP(cudaStreamWaitEvent(h->sOut, h->evPipe[c][2], 0));
         CKP(cudaMemcpyAsync(h->hN + f0, h->dN + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
         CKP(cudaMemcpyAsync(h->hMono + f0, h->dMono + f0, sizeof(int) * nb, cudaMemcpyDeviceToHost, h->sOut));
@@ -880,13 +910,30 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
             CKP(cudaMemcpy2DAsync(desc + (size_t)f0 * cap * 32, 32 * (size_t)cap, h->dDesc + (size_t)f0 * kpf * 32, 32 * (size_t)kpf,
                                   32 * (size_t)kpf, nb, cudaMemcpyDeviceToHost, h->sOut));
         }
+        mark(h->sOut);
     }
+    {
     // the public stream ends up ordered after everything this call enqueued (device results are valid on it)
-    CKP(cudaEventRecord(h->evJoin[1], sAlt));
-    CKP(cudaStreamWaitEvent(h->stream, h->evJoin[1], 0));
+    for (int i = 1; i < pipeStreams; ++i) {
+        CKP(cudaEventRecord(h->evJoin[i], h->sComp[i]));
+        CKP(cudaStreamWaitEvent(h->stream, h->evJoin[i], 0));
+    }
     CKP(cudaStreamSynchronize(h->sOut));
-    CKP(cudaStreamSynchronize(sAlt));
     CKP(cudaStreamSynchronize(h->stream));
+    }
+    if (trace && !tev.empty()) {       // t0, copy-in x nchunks, then (kernels, copy-out) x nchunks
+        fprintf(stderr, "[orbfe pipe trace] %d chunks:", nchunks);
+        for (int c = 0; c < nchunks; ++c) fprintf(stderr, " %d", bounds[c + 1] - bounds[c]);
+        fprintf(stderr, "\n");
+        for (size_t i = 1; i < tev.size(); ++i) {
+            float ms = 0.f;
+            cudaEventElapsedTime(&ms, tev[0], tev[i]);
+            const int c = (int)i - 1;
+            if (c < nchunks) fprintf(stderr, "  copy-in %2d done %.3f ms\n", c, ms);
+            else fprintf(stderr, "  %s %2d done %.3f ms\n", (c - nchunks) % 2 ? "copy-out" : "kernels ", (c - nchunks) / 2, ms);
+        }
+        for (cudaEvent_t e_ : tev) cudaEventDestroy(e_);
+    }
 #undef CKP
     if (cap >= kpf) {
         for (int b = 0; b < batch; ++b) { n_out[b] = h->hN[b]; if (mono_out) mono_out[b] = h->hMono[b]; }
