@@ -171,6 +171,86 @@ __global__ void __launch_bounds__(128, PYR_MINB) k_pyr_resize_plan(uint8_t* __re
     }
 }
 
+// ---- the same arithmetic with the source staged by TMA (the default since round 2) ---------------------------------------
+// north_star prescribes "staged through shared memory with TMA tile loads" for the pyramid.  A CTA of four warps covers 128
+// destination bytes x 64 destination rows; every source row / column its taps touch lies in one box of the parent level
+// (PyrTmaLevel: per tile column the first source word, per row group the first source row), which thread 0 fetches with one
+// cp.async.bulk.tensor.3d; the row loop then reads the two source rows from shared memory instead of L1.  Stores are the same
+// full-line 32-bit stores (a warp writes 128 contiguous bytes per row).  Measured against k_pyr_resize_plan: see
+// profiles/r03m_pyr_tma.txt - 0.659 -> 0.581 ms per 512 frames, so this is the default; ORBFE_PYR_TMA=0 selects the plain kernel.
+namespace {
+__device__ __forceinline__ uint32_t pyr_s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+}
+#define PYRTMA_THREADS (ORBFE_PYRTMA_ROWS / PYR_TH * 32)
+__global__ void __launch_bounds__(PYRTMA_THREADS) k_pyr_resize_tma(const __grid_constant__ FastMaps maps, uint8_t* __restrict__ pyr, LevelGeom gd,
+                                                        const ResizeTap* __restrict__ taps, const ColPlan* __restrict__ plans,
+                                                        const PyrTmaPlan* __restrict__ plan, int level, int frame0) {
+    extern __shared__ __align__(128) uint8_t tileBytes[];
+    __shared__ __align__(8) uint64_t bar;
+    const PyrTmaLevel& L = plan->lv[level];
+    const int tx = blockIdx.x, ty = blockIdx.y, frame = frame0 + blockIdx.z;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int boxWords = L.boxWords, colLo = L.colLo[tx], rowLo = L.rowLo[ty];
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pyr_s32(&bar)), "r"(1));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pyr_s32(&bar)), "r"((uint32_t)(boxWords * 4 * L.boxH)) : "memory");
+        asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];" ::"r"(
+                         pyr_s32(tileBytes)),
+                     "l"(&maps.m[level]), "r"(ORBFE_XO + colLo * 4), "r"(ORBFE_EDGE + rowLo), "r"(frame), "r"(pyr_s32(&bar))
+                     : "memory");
+    }
+    const int word = tx * 32 + lane;
+    const ColPlan cp = plans[gd.planBase + word];
+    const int row0 = ty * ORBFE_PYRTMA_ROWS + warp * PYR_TH, row1 = min(row0 + PYR_TH, gd.rows);
+    unsigned myOff0 = 0, myOff1 = 0;
+    uint32_t myA0 = 0, myA1 = 0;
+    if (lane < PYR_TH && row0 + lane < row1) {
+        const ResizeTap t = taps[gd.tabY + reflect101(row0 + lane - ORBFE_EDGE, gd.h)];
+        myOff0 = (unsigned)(t.s0 - rowLo) * (unsigned)boxWords; myOff1 = (unsigned)(t.s1 - rowLo) * (unsigned)boxWords;
+        myA0 = (uint32_t)t.a0 << 16; myA1 = (uint32_t)t.a1 << 16;
+    }
+    const unsigned b01 = (unsigned)(cp.base01 - colLo), b23 = (unsigned)(cp.base23 - colLo);
+    const uint32_t* S = reinterpret_cast<const uint32_t*>(tileBytes);
+    uint32_t* dst = reinterpret_cast<uint32_t*>(pyr + gd.base + (long long)frame * gd.plane);
+    const unsigned dpw = (unsigned)(gd.pitch >> 2);
+    unsigned doff = (unsigned)row0 * dpw + (unsigned)word;
+    __syncthreads();                   // the barrier is initialised before anyone polls it
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "PW_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra PD_%=;\n"
+        "bra PW_%=;\n"
+        "PD_%=:\n"
+        "}\n" ::"r"(pyr_s32(&bar)),
+        "r"(0)
+        : "memory");
+    if (row0 >= gd.rows) return;
+#pragma unroll 4
+    for (int row = row0; row < row1; ++row) {
+        const int j = row - row0;
+        const unsigned o0 = __shfl_sync(0xffffffffu, myOff0, j), o1 = __shfl_sync(0xffffffffu, myOff1, j);
+        const uint32_t a0s = __shfl_sync(0xffffffffu, myA0, j), a1s = __shfl_sync(0xffffffffu, myA1, j);
+        const uint32_t p0a = __byte_perm(S[o0 + b01], S[o0 + b01 + 1], cp.sel & 0xFFFF);
+        const uint32_t p0b = __byte_perm(S[o0 + b23], S[o0 + b23 + 1], cp.sel >> 16);
+        const uint32_t p1a = __byte_perm(S[o1 + b01], S[o1 + b01 + 1], cp.sel & 0xFFFF);
+        const uint32_t p1b = __byte_perm(S[o1 + b23], S[o1 + b23 + 1], cp.sel >> 16);
+        int r0[4], r1[4];
+        r0[0] = __dp2a_lo(cp.a[0], p0a, 0u); r0[1] = __dp2a_hi(cp.a[1], p0a, 0u);
+        r0[2] = __dp2a_lo(cp.a[2], p0b, 0u); r0[3] = __dp2a_hi(cp.a[3], p0b, 0u);
+        r1[0] = __dp2a_lo(cp.a[0], p1a, 0u); r1[1] = __dp2a_hi(cp.a[1], p1a, 0u);
+        r1[2] = __dp2a_lo(cp.a[2], p1b, 0u); r1[3] = __dp2a_hi(cp.a[3], p1b, 0u);
+        uint32_t o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) o[k] = (__umulhi(a0s, (uint32_t)r0[k] >> 4) + __umulhi(a1s, (uint32_t)r1[k] >> 4) + 2u) >> 2;
+        const uint32_t v = __byte_perm(__byte_perm(o[0], o[1], 0x0040), __byte_perm(o[2], o[3], 0x0040), 0x5410);
+        dst[doff] = v & cp.keep;
+        doff += dpw;
+    }
+}
+
 cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int width, int height,
                                  long long stride, long long frameStride) {
     (void)width; (void)height;
@@ -192,7 +272,12 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int fr
     }
     for (int l = 1; l < nl; ++l) {
         const LevelGeom& gd = h->geom[l];
-        if (gd.planBase >= 0) {
+        if (gd.planBase >= 0 && h->pyrUseTma && h->pyrTma.lv[l].ok) {
+            const PyrTmaLevel& L = h->pyrTma.lv[l];
+            const size_t smem = (size_t)L.boxWords * 4 * L.boxH;
+            dim3 grid(L.tilesX, L.groupsY, batch);
+            k_pyr_resize_tma<<<grid, PYRTMA_THREADS, smem, h->cur>>>(h->pyrMaps, h->dPyr, gd, h->dTaps, h->dPlans, h->dPyrTma, l, frame0);
+        } else if (gd.planBase >= 0) {
             const int tilesX = gd.pitch / 128, total = tilesX * ((gd.rows + PYR_TH - 1) / PYR_TH);
             dim3 grid((total + 3) / 4, batch);
             k_pyr_resize_plan<<<grid, 128, 0, h->cur>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total, frame0);

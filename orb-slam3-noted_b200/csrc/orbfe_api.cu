@@ -17,6 +17,9 @@
 // serial, 184.5 k with the ordinary grid on the side stream (the block scheduler runs the two kernels one after the other),
 // 149 / 173 / 179 / 180.5 k with 1 / 2 / 3 / 4 resident blur CTAs per SM (four blur warps per SM are too slow, more take the
 // registers FAST needs).  Off by default; the knobs stay for other shapes.
+#ifndef ORBFE_PYR_TMA_DEFAULT
+#define ORBFE_PYR_TMA_DEFAULT 1    // resize levels through k_pyr_resize_tma (TMA-staged source): 0.659 -> 0.581 ms per 512 frames
+#endif
 #ifndef ORBFE_PIPE_STREAMS
 #define ORBFE_PIPE_STREAMS 2       // compute streams of the host-buffer pipeline (orbfe_extract_batch)
 #endif
@@ -282,7 +285,7 @@ static void free_handle(orbfe_handle* h) {
     if (!h) return;
     cudaSetDevice(h->device);
     cudaFree(h->dIn); cudaFree(h->dPyr); cudaFree(h->dBlur); cudaFree(h->dCand); cudaFree(h->dNodeOf); cudaFree(h->dCandCount);
-    cudaFree(h->dLvlKp); cudaFree(h->dLvlCount); cudaFree(h->dGeom); cudaFree(h->dCells); cudaFree(h->dTaps); cudaFree(h->dPlans);
+    cudaFree(h->dLvlKp); cudaFree(h->dLvlCount); cudaFree(h->dGeom); cudaFree(h->dCells); cudaFree(h->dTaps); cudaFree(h->dPlans); cudaFree(h->dPyrTma);
     cudaFree(h->dRes); cudaFree(h->dSlot);
     if (h->hRes) cudaFreeHost(h->hRes);
     for (int i = 0; i < ORBFE_GRAPH_SLOTS; ++i)
@@ -345,6 +348,70 @@ static int encode_fast_maps(orbfe_handle* h) {
     return ORBFE_OK;
 }
 
+// Source boxes and tensor maps of k_pyr_resize_tma (see orbfe_internal.h); sp still holds the host copies of taps and plans.
+static int encode_pyr_maps(orbfe_handle* h, const ShapePlan& sp) {
+    memset(&h->pyrTma, 0, sizeof(h->pyrTma));
+    if (!h->pyrUseTma) return ORBFE_OK;
+    static EncodeTiledFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres);
+        if (e != cudaSuccess || qres != cudaDriverEntryPointSuccess || !fn) return cuda_fail(e != cudaSuccess ? e : cudaErrorUnknown, "cuTensorMapEncodeTiled entry point");
+        encode = (EncodeTiledFn)fn;
+    }
+    const size_t B = (size_t)h->p.max_batch;
+    for (int l = 1; l < h->p.nlevels; ++l) {
+        const LevelGeom& gd = h->geom[l];
+        const LevelGeom& gs = h->geom[l - 1];
+        PyrTmaLevel& L = h->pyrTma.lv[l];
+        if (gd.planBase < 0) continue;
+        L.tilesX = gd.pitch / 128;
+        L.groupsY = (gd.rows + ORBFE_PYRTMA_ROWS - 1) / ORBFE_PYRTMA_ROWS;
+        if (L.tilesX > 24 || L.groupsY > 96) continue;
+        int spanW = 0, spanH = 0;
+        for (int tx = 0; tx < L.tilesX; ++tx) {
+            int lo = 1 << 30, hi = 0;
+            for (int w = tx * 32; w < tx * 32 + 32; ++w) {
+                const ColPlan& cp = sp.plans[gd.planBase + w];
+                lo = std::min(lo, std::min(cp.base01, cp.base23));
+                hi = std::max(hi, std::max(cp.base01, cp.base23) + 1);
+            }
+            L.colLo[tx] = lo & ~3;
+            spanW = std::max(spanW, hi - L.colLo[tx] + 1);
+        }
+        for (int ty = 0; ty < L.groupsY; ++ty) {
+            int lo = 1 << 30, hi = 0;
+            for (int r = ty * ORBFE_PYRTMA_ROWS; r < std::min((ty + 1) * ORBFE_PYRTMA_ROWS, gd.rows); ++r) {
+                int y = r - ORBFE_EDGE;
+                y = y < 0 ? -y : y;
+                if (y >= gd.h) y = 2 * gd.h - 2 - y;
+                const ResizeTap& t = sp.taps[gd.tabY + y];
+                lo = std::min(lo, (int)t.s0);
+                hi = std::max(hi, (int)t.s1);
+            }
+            L.rowLo[ty] = lo;
+            spanH = std::max(spanH, hi - lo + 1);
+        }
+        L.boxWords = (spanW + 3) & ~3;
+        L.boxH = spanH;
+        if (L.boxWords * 4 > 256 || L.boxH > 256) continue;
+        const cuuint64_t dims[3] = {(cuuint64_t)gs.pitch, (cuuint64_t)gs.rows, (cuuint64_t)B};
+        const cuuint64_t strides[2] = {(cuuint64_t)gs.pitch, (cuuint64_t)gs.plane};
+        const cuuint32_t box[3] = {(cuuint32_t)(L.boxWords * 4), (cuuint32_t)L.boxH, 1};
+        const cuuint32_t estr[3] = {1, 1, 1};
+        CUresult r = encode(&h->pyrMaps.m[l], CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, h->dPyr + gs.base, dims, strides, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+        if (r != CUDA_SUCCESS) {
+            snprintf(g_cudaErr, sizeof(g_cudaErr), "cuTensorMapEncodeTiled(pyramid level %d) failed: CUresult %d", l, (int)r);
+            return ORBFE_ERR_CUDA;
+        }
+        L.ok = 1;
+    }
+    return ORBFE_OK;
+}
+
 static void drop_graphs(orbfe_handle* h);
 
 // Upload the geometry of a new image shape (no-op when the shape is unchanged).
@@ -370,6 +437,7 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     h->fastMaxCw = sp.maxCw;
     {
         int st = encode_fast_maps(h);
+        if (st == ORBFE_OK) st = encode_pyr_maps(h, sp);
         if (st != ORBFE_OK) return st;
     }
     h->candPerFrame = sp.candPerFrame;
@@ -382,6 +450,7 @@ static int configure_shape(orbfe_handle* h, int W, int H) {
     CK(cudaMemcpyAsync(h->dTaps, sp.taps.data(), sizeof(ResizeTap) * sp.taps.size(), cudaMemcpyHostToDevice, h->stream));
     if (!sp.plans.empty())
         CK(cudaMemcpyAsync(h->dPlans, sp.plans.data(), sizeof(ColPlan) * sp.plans.size(), cudaMemcpyHostToDevice, h->stream));
+    CK(cudaMemcpyAsync(h->dPyrTma, &h->pyrTma, sizeof(PyrTmaPlan), cudaMemcpyHostToDevice, h->stream));
     CK(cudaStreamSynchronize(h->stream));   // sp's vectors die at return
     h->curW = W;
     h->curH = H;
@@ -450,6 +519,8 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
         h->useGraphs = e3 ? atoi(e3) != 0 : 1;
         const char* e4 = getenv("ORBFE_BLUR_OVERLAP");
         const char* e5 = getenv("ORBFE_BLUR_PERSIST");
+        const char* e7 = getenv("ORBFE_PYR_TMA");
+        h->pyrUseTma = e7 ? atoi(e7) != 0 : ORBFE_PYR_TMA_DEFAULT;
         const char* e6 = getenv("ORBFE_BLUR");
         h->blurBackend = e6 ? (strcmp(e6, "alu") == 0 ? ORBFE_BLUR_ALU : ORBFE_BLUR_TENSOR) : ORBFE_BLUR_DEFAULT;
         h->blurOverlap = e4 ? atoi(e4) != 0 : ORBFE_BLUR_OVERLAP;
@@ -469,6 +540,7 @@ extern "C" int orbfe_create(const orbfe_params* params, orbfe_handle** out) {
     CKC(cudaMalloc(&h->dCells, sizeof(CellDesc) * h->cellCap));
     CKC(cudaMalloc(&h->dTaps, sizeof(ResizeTap) * h->tabCap));
     CKC(cudaMalloc(&h->dPlans, sizeof(ColPlan) * h->planCap));
+    CKC(cudaMalloc(&h->dPyrTma, sizeof(PyrTmaPlan)));
     {   // one result arena: counts | mono | keypoints | descriptors
         h->resKpsOff = (2 * sizeof(int) * B + 255) & ~(size_t)255;
         h->resDescOff = (h->resKpsOff + sizeof(orbfe_keypoint) * B * h->kpCapPerFrame + 255) & ~(size_t)255;

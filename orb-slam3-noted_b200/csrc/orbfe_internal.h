@@ -81,6 +81,22 @@ struct ColPlan {
     uint32_t keep;         // 0xFF per byte inside [-19, w + 19)
 };
 
+// TMA-staged form of the resize (k_pyr_resize_tma, an A/B experiment against k_pyr_resize_plan): a CTA covers 128 destination
+// bytes x 64 destination rows; the source rows / columns its taps touch are one TMA box of the parent level.
+#ifndef ORBFE_PYRTMA_ROWS
+#define ORBFE_PYRTMA_ROWS 64
+#endif
+struct PyrTmaLevel {
+    int ok;                // 0: this level keeps the plain kernel (no column plan, or a box beyond 256)
+    int boxWords, boxH;    // TMA box: source words per row, source rows
+    int tilesX, groupsY;
+    int colLo[24];         // first source word (from ROI column 0, a multiple of 4) per destination tile column
+    int rowLo[96];         // first source row (ROI row) per group of ORBFE_PYRTMA_ROWS destination rows
+};
+struct PyrTmaPlan {
+    PyrTmaLevel lv[ORBFE_MAX_LEVELS];
+};
+
 // One tiled tensor map per pyramid level: dims (pitch, rows, frames) of the bordered level, box = FAST tile.
 struct FastMaps {
     CUtensorMap m[ORBFE_MAX_LEVELS];
@@ -126,6 +142,10 @@ struct orbfe_handle {
     int fastBoxW, fastBoxH; // TMA box of the FAST tile (>= the largest cell, width a multiple of 16)
     int fastMaxCw;          // widest cell ROI (core + 6 px)
     FastMaps fastMaps;
+    FastMaps pyrMaps;       // k_pyr_resize_tma: map [l] = the PARENT of level l with level l's source box
+    PyrTmaPlan pyrTma;
+    PyrTmaPlan* dPyrTma;
+    int pyrUseTma;          // ORBFE_PYR_TMA=1 (experiment; default off, see k_pyramid.cu)
     long long candPerFrame; // candidate entries per frame (all levels)
     int kpPerFrame;         // output slots per frame (= cap of device results)
     // capacities fixed at create
