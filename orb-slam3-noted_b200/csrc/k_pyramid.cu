@@ -21,30 +21,41 @@ __device__ __forceinline__ int reflect101(int i, int n) {
 // warps over the left / right border columns diverge into the per-byte reflected path.  Chunks inside the
 // ROI (ROI column 0 sits on a 32-byte boundary, so they start at a multiple of 16 source bytes) are one
 // 128-bit load + store when the source row is 16-byte aligned, four 32-bit loads when 4-byte aligned.
+#ifndef PYR_L0_ROWS
+#define PYR_L0_ROWS 4          // rows per thread (32 apart): the chunk classification and the column arithmetic are shared
+#endif
 __global__ void __launch_bounds__(256) k_pyr_level0(const uint8_t* __restrict__ in, long long stride,
                                                     long long frameStride, uint8_t* __restrict__ out, LevelGeom g, int frame0) {
-    const int chunk = blockIdx.x * 8 + (threadIdx.x & 7), row = blockIdx.z * 32 + (threadIdx.x >> 3);
-    if (chunk >= (g.pitch >> 4) || row >= g.rows) return;
-    const int y = reflect101(row - ORBFE_EDGE, g.h);
-    const uint8_t* src = in + (long long)blockIdx.y * frameStride + (long long)y * stride;
+    const int chunk = blockIdx.x * 8 + (threadIdx.x & 7), rowA = blockIdx.z * (32 * PYR_L0_ROWS) + (threadIdx.x >> 3);
+    if (chunk >= (g.pitch >> 4)) return;
     const int x0 = chunk * 16 - ORBFE_XO;
-    uint4 v;
-    if (x0 >= 0 && x0 + 16 <= g.w && ((reinterpret_cast<uintptr_t>(src + x0) & 15) == 0)) {
-        v = __ldg(reinterpret_cast<const uint4*>(src + x0));
-    } else if (x0 >= 0 && x0 + 16 <= g.w && ((reinterpret_cast<uintptr_t>(src + x0) & 3) == 0)) {
-        const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src + x0);
-        v = make_uint4(__ldg(s4), __ldg(s4 + 1), __ldg(s4 + 2), __ldg(s4 + 3));
-    } else {
-        uint32_t w[4] = {0u, 0u, 0u, 0u};
+    const uint8_t* frame = in + (long long)blockIdx.y * frameStride;
+    uint8_t* dst = out + g.base + (long long)(frame0 + blockIdx.y) * g.plane;
+    const bool inside = x0 >= 0 && x0 + 16 <= g.w;
+    const int al = (int)((reinterpret_cast<uintptr_t>(frame) | (uintptr_t)stride) & 15);     // every row start shares this alignment
 #pragma unroll
-        for (int k = 0; k < 16; ++k) {
-            const int x = x0 + k;
-            if (x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE) w[k >> 2] |= (uint32_t)__ldg(src + reflect101(x, g.w)) << (8 * (k & 3));
+    for (int k = 0; k < PYR_L0_ROWS; ++k) {
+        const int row = rowA + 32 * k;
+        if (row >= g.rows) break;
+        const int y = reflect101(row - ORBFE_EDGE, g.h);
+        const uint8_t* src = frame + (long long)y * stride;
+        uint4 v;
+        if (inside && al == 0) {
+            v = __ldg(reinterpret_cast<const uint4*>(src + x0));
+        } else if (inside && (al & 3) == 0) {
+            const uint32_t* s4 = reinterpret_cast<const uint32_t*>(src + x0);
+            v = make_uint4(__ldg(s4), __ldg(s4 + 1), __ldg(s4 + 2), __ldg(s4 + 3));
+        } else {
+            uint32_t w[4] = {0u, 0u, 0u, 0u};
+#pragma unroll
+            for (int b = 0; b < 16; ++b) {
+                const int x = x0 + b;
+                if (x >= -ORBFE_EDGE && x < g.w + ORBFE_EDGE) w[b >> 2] |= (uint32_t)__ldg(src + reflect101(x, g.w)) << (8 * (b & 3));
+            }
+            v = make_uint4(w[0], w[1], w[2], w[3]);
         }
-        v = make_uint4(w[0], w[1], w[2], w[3]);
+        reinterpret_cast<uint4*>(dst + (long long)row * g.pitch)[chunk] = v;
     }
-    uint8_t* dst = out + g.base + (long long)(frame0 + blockIdx.y) * g.plane + (long long)row * g.pitch;
-    reinterpret_cast<uint4*>(dst)[chunk] = v;
 }
 
 // Colour input: cv::cvtColor(..., RGB2GRAY / BGR2GRAY / RGBA2GRAY / BGRA2GRAY) of OpenCV 4.x for 8-bit images,
@@ -258,7 +269,7 @@ cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int fr
     {
         const LevelGeom& g = h->geom[0];
         if (h->inFormat == ORBFE_FORMAT_GRAY8) {
-            dim3 grid(((g.pitch >> 4) + 7) / 8, batch, (g.rows + 31) / 32);
+            dim3 grid(((g.pitch >> 4) + 7) / 8, batch, (g.rows + 32 * PYR_L0_ROWS - 1) / (32 * PYR_L0_ROWS));
             k_pyr_level0<<<grid, 256, 0, h->cur>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
         } else {
             dim3 grid((g.pitch / 4 + 127) / 128, g.rows, batch);
