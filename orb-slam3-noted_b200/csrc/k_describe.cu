@@ -244,14 +244,36 @@ __global__ void __launch_bounds__(128, BLUR_MINB) k_blur_resident(const uint8_t*
 #define DESC_STAGE 0       // measured (profiles/r02m_variants.txt): 0.962 ms with the staged window vs 0.955 without
 #endif
 
+#ifndef DESC_KPW
+#define DESC_KPW 1         // key points per warp.  > 1 keeps the lane's part of the pattern in registers across key points: measured
+#endif                     // (profiles/r03q_variants.txt) 0.921 ms at 8 (85 or 51 registers), 1.09 at 4-8 with 64 registers, vs 0.914 at 1
 #ifndef DESC_MINB
-#define DESC_MINB 6
+#define DESC_MINB (DESC_KPW > 1 ? 4 : 6)
 #endif
 __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                                                               const LevelGeom* __restrict__ geom,
                                                               const uint32_t* __restrict__ slot, const int* __restrict__ nOut,
                                                               int kpPerFrame, orbfe_keypoint* __restrict__ kps,
                                                               uint8_t* __restrict__ desc, int frame0) {
+#if DESC_KPW > 1
+    // A warp describes DESC_KPW key points one after the other and keeps ITS part of the pattern - the eight tests of
+    // descriptor byte `lane` - in registers for all of them: the per-key-point reads of the pattern from shared memory were
+    // a quarter of the wavefronts of the data pipe this kernel is bound by (l1tex__data_pipe_lsu_wavefronts 91 %, shared 25 %).
+    const int frame = frame0 + blockIdx.y, lane = threadIdx.x & 31;
+    float4 pat[8];
+    {
+        const uint4* pp = reinterpret_cast<const uint4*>(d_pattern) + 2 * lane;      // tests 8 * lane .. 8 * lane + 7, four bytes each
+        const uint4 p0 = __ldg(pp), p1 = __ldg(pp + 1);
+        const uint32_t w[8] = {p0.x, p0.y, p0.z, p0.w, p1.x, p1.y, p1.z, p1.w};
+#pragma unroll
+        for (int k = 0; k < 8; ++k)
+            pat[k] = make_float4((float)(int8_t)(w[k] & 0xFF), (float)(int8_t)(w[k] >> 8 & 0xFF), (float)(int8_t)(w[k] >> 16 & 0xFF),
+                                 (float)(int8_t)(w[k] >> 24));
+    }
+    const int nKp = nOut[frame];
+    const int iFirst = (blockIdx.x * DESC_WARPS + (threadIdx.x >> 5)) * DESC_KPW;
+    for (int i = iFirst; i < min(iFirst + DESC_KPW, nKp); ++i) {
+#else
     __shared__ float4 sPat[256];     // (x0, y0, x1, y1) of test T at [(T & 7) * 32 + (T >> 3)]
     {
         const int T = threadIdx.x;   // DESC_WARPS * 32 == 256 tests
@@ -262,6 +284,8 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     __syncthreads();
     const int frame = frame0 + blockIdx.y, i = blockIdx.x * DESC_WARPS + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (i >= nOut[frame]) return;
+    {
+#endif
     const uint32_t s = slot[(long long)frame * kpPerFrame + i];
     const int level = s >> 28, cy = (s >> 14) & 0x3FFF, cx = s & 0x3FFF;
     const LevelGeom& g = geom[level];
@@ -339,7 +363,11 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     uint32_t byte = 0;
 #pragma unroll
     for (int k = 0; k < 8; ++k) {
+#if DESC_KPW > 1
+        const float4 pt = pat[k];                // test 8*lane + k
+#else
         const float4 pt = sPat[k * 32 + lane];   // test 8*lane + k
+#endif
         const float x0 = pt.x, y0 = pt.y, x1 = pt.z, y1 = pt.w;
         const int t0 = DESC_LD(Bc + (long long)(__float2int_rn(__fadd_rn(__fmul_rn(x0, b), __fmul_rn(y0, a))) * pitch +
                                                 __float2int_rn(__fsub_rn(__fmul_rn(x0, a), __fmul_rn(y0, b))) + kOff));
@@ -352,6 +380,7 @@ __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const u
     w |= __shfl_xor_sync(0xffffffffu, w, 1);
     w |= __shfl_xor_sync(0xffffffffu, w, 2);
     if ((lane & 3) == 0) reinterpret_cast<uint32_t*>(desc + ((long long)frame * kpPerFrame + i) * 32)[lane >> 2] = w;
+    }
 }
 
 cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int lap0, int lap1) {
@@ -376,7 +405,7 @@ cudaError_t orbfe_launch_blur(orbfe_handle* h, int frame0, int batch, cudaStream
 }
 
 cudaError_t orbfe_launch_describe(orbfe_handle* h, int frame0, int batch) {
-    dim3 grid((h->kpPerFrame + DESC_WARPS - 1) / DESC_WARPS, batch);
+    dim3 grid((h->kpPerFrame + DESC_WARPS * DESC_KPW - 1) / (DESC_WARPS * DESC_KPW), batch);
     k_describe<<<grid, DESC_WARPS * 32, 0, h->cur>>>(h->dPyr, h->dBlur, h->dGeom, h->dSlot, h->dN, h->kpPerFrame, h->dKps,
                                                        h->dDesc, frame0);
     h->launches++;

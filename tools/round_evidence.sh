@@ -24,7 +24,7 @@ cat $out/${tag}_launches_summary.txt
 
 # --set full: extraction kernels of one step (skip the warm-up launches), then the matching kernels
 timeout 1200 ncu --set full --clock-control none --import-source on \
-    -k regex:'k_fast_cells|k_pyr|k_describe|k_blur|k_octree|k_assemble' --launch-skip 39 --launch-count 13 \
+    -k regex:'k_fast|k_pyr|k_describe|k_blur|k_octree|k_assemble' --launch-skip 42 --launch-count 14 \
     -f -o $out/${tag}_extract python bench.py --steps 1 --warmup 3 --no-cpu --no-match --no-legs > $out/${tag}_ncu_extract.log 2>&1
 ncu -i $out/${tag}_extract.ncu-rep --page raw --csv > $out/${tag}_extract_raw.csv 2>/dev/null
 python tools/summarize_ncu_full.py $out/${tag}_extract_raw.csv $out/${tag}_extract_summary.json > $out/${tag}_extract_summary.txt 2>&1
