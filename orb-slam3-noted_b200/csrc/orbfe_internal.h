@@ -81,7 +81,7 @@ struct ColPlan {
     uint32_t keep;         // 0xFF per byte inside [-19, w + 19)
 };
 
-// TMA-staged form of the resize (k_pyr_resize_tma, an A/B experiment against k_pyr_resize_plan): a CTA covers 128 destination
+// TMA-staged form of the resize (k_pyr_resize_tma, the default; k_pyr_resize_plan is the L1 form): a CTA covers 128 destination
 // bytes x 64 destination rows; the source rows / columns its taps touch are one TMA box of the parent level.
 #ifndef ORBFE_PYRTMA_ROWS
 #define ORBFE_PYRTMA_ROWS 64
@@ -145,7 +145,7 @@ struct orbfe_handle {
     FastMaps pyrMaps;       // k_pyr_resize_tma: map [l] = the PARENT of level l with level l's source box
     PyrTmaPlan pyrTma;
     PyrTmaPlan* dPyrTma;
-    int pyrUseTma;          // ORBFE_PYR_TMA=1 (experiment; default off, see k_pyramid.cu)
+    int pyrUseTma;          // resize levels through k_pyr_resize_tma (default; ORBFE_PYR_TMA=0 selects the L1 form, see k_pyramid.cu)
     long long candPerFrame; // candidate entries per frame (all levels)
     int kpPerFrame;         // output slots per frame (= cap of device results)
     // capacities fixed at create
