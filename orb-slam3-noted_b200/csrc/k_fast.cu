@@ -444,10 +444,13 @@ static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
     // Cells are stored level by level.  Almost all of them are ~44 rows tall, but the coarsest levels have a few of up to ~60
     // rows; sizing every CTA's shared memory for those costs a quarter of the occupancy, so consecutive levels of the same
     // class (small / tall) go out as one launch with the footprint of their own tallest box.
+    // ... unless the whole launch fits the GPU at once anyway (single frames, stereo pairs): then occupancy is not the issue,
+    // the second launch's ~15 us of cell latency is, and everything goes out together with the largest footprint.
+    const bool oneLaunch = (long long)h->nCellsTotal * batch <= 24LL * h->smCount;
     for (int l = 0; l < nl;) {
-        const bool small = h->geom[l].fastBoxH <= FAST_SMALL_ROWS;
+        const bool small = oneLaunch || h->geom[l].fastBoxH <= FAST_SMALL_ROWS;
         int l1 = l, maxH = 0;
-        while (l1 < nl && (h->geom[l1].fastBoxH <= FAST_SMALL_ROWS) == small) { maxH = std::max(maxH, h->geom[l1].fastBoxH); ++l1; }
+        while (l1 < nl && (oneLaunch || (h->geom[l1].fastBoxH <= FAST_SMALL_ROWS) == small)) { maxH = std::max(maxH, h->geom[l1].fastBoxH); ++l1; }
         const int cell0 = h->geom[l].cellBase, cellEnd = h->geom[l1 - 1].cellBase + h->geom[l1 - 1].nCells;
         l = l1;
         if (cellEnd <= cell0) continue;
