@@ -542,6 +542,40 @@ def run_orbfe(args):
     barrier()
     e2e_s = time.perf_counter() - t0
 
+    # Information only (not the headline): the same call from TWO host threads, each with its own handle and pinned buffers -
+    # what a caller with more than one stream of frames does (the reference itself extracts a stereo pair on two threads,
+    # Frame.cc:119-122).  One caller leaves the link idle while the kernels of its last chunk drain; two keep it busy.
+    two = None
+    if world == 1 and not args.no_legs:
+        import threading
+        ex2 = orbfe.ORBextractor(*ORB_PARAMS, device=local, max_width=W, max_height=H, max_batch=B)
+        kps2 = torch.empty((B, ex2.cap, 28), dtype=torch.uint8).pin_memory().numpy()
+        desc2 = torch.empty((B, ex2.cap, 32), dtype=torch.uint8).pin_memory().numpy()
+        host2 = host.clone().pin_memory()
+        n2, m2 = np.zeros(B, np.int32), np.zeros(B, np.int32)
+        callers = [(ex.handle, hnp.ctypes.data, kps.ctypes.data, desc.ctypes.data, n_out.ctypes.data, mono.ctypes.data, ex.cap),
+                   (ex2.handle, host2.data_ptr(), kps2.ctypes.data, desc2.ctypes.data, n2.ctypes.data, m2.ctypes.data, ex2.cap)]
+
+        def caller(c, steps):
+            for _ in range(steps):
+                st = L.orbfe_extract_batch(c[0], c[1], B, W, H, W, W * H, LAPPING[0], LAPPING[1], c[2], c[3], c[6], c[4], c[5])
+                if st < 0:
+                    raise orbfe.OrbfeError(st, "orbfe_extract_batch")
+
+        for c in callers:
+            caller(c, 2)
+        th = [threading.Thread(target=caller, args=(c, K)) for c in callers]
+        t0 = time.perf_counter()
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        dt2 = time.perf_counter() - t0
+        two = {"callers": 2, "value": 2 * K * B / dt2, "unit": UNIT, "identical_results": bool((n2 == n_out).all() and (desc2 == desc).all()),
+               "note": "two host threads, two handles on the same GPU, each step = its own H2D + kernels + D2H; information only"}
+        ex2.close()
+        del ex2
+
     link = host_link_probe(torch, dist, world, host, dev)
     # outside the timed regions: frames of the timed 512-batch (as the e2e call left them in the host buffers) against the
     # reference's own ORBextractor.cc (oracle/_ref) or, without it, the oracle port
@@ -629,7 +663,8 @@ def run_orbfe(args):
                 "host_ceiling_gbs": link, "host_ceiling_frames_per_s": link["both"]["h2d_gbs"] * 1e9 / (W * H),
                 "host_ceiling_note": "pinned H2D of the frame batch and D2H of a result-sized buffer on two streams, all ranks at once "
                                      "(aggregate over ranks); frames/s ceiling = concurrent H2D rate / bytes per frame",
-                "api": "orbfe_extract_batch (pinned host buffers; chunks of 64 752x480 frames' worth of bytes pipelined over copy-in / 2 compute / copy-out streams)"},
+                "api": "orbfe_extract_batch (pinned host buffers; chunks of 64 752x480 frames' worth of bytes pipelined over copy-in / 2 compute / copy-out streams)",
+                "two_callers": two},
         "gpu_launches": int(launches), "graph_launches": int(graph_launches),
         "clocks": clk,
         "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",

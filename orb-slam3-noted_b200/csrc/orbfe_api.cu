@@ -897,7 +897,22 @@ extern "C" int orbfe_extract_batch(orbfe_handle* h, const uint8_t* images, int b
     int bounds[ORBFE_PIPE_MAX_CHUNKS + 1];
     int nchunks = 0;
     bounds[0] = 0;
-    if (batch <= pipeChunk + pipeChunk / 2) {
+    // ORBFE_PIPE_SCHEDULE="16,64,64,..." (debug / sweeps): explicit chunk sizes, used when they add up to the batch
+    static const char* schedEnv = getenv("ORBFE_PIPE_SCHEDULE");
+    if (schedEnv && *schedEnv) {
+        int sum = 0, n = 0, tmp[ORBFE_PIPE_MAX_CHUNKS];
+        for (const char* q = schedEnv; *q && n < ORBFE_PIPE_MAX_CHUNKS;) {
+            const int v = atoi(q);
+            if (v <= 0) break;
+            tmp[n++] = v; sum += v;
+            while (*q && *q != ',') ++q;
+            if (*q == ',') ++q;
+        }
+        if (sum == batch)
+            for (int i = 0; i < n; ++i) { bounds[nchunks + 1] = bounds[nchunks] + tmp[i]; ++nchunks; }
+    }
+    if (nchunks > 0) {
+    } else if (batch <= pipeChunk + pipeChunk / 2) {
         bounds[++nchunks] = batch;
     } else {
         int f = std::min(pipeChunk / 4 > 0 ? pipeChunk / 4 : 1, batch);
