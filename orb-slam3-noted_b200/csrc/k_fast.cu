@@ -262,6 +262,9 @@ __global__ void __launch_bounds__(FAST_THREADS, FAST_MINB) k_fast_cells(const __
 #ifndef FAST_WMINB
 #define FAST_WMINB 32
 #endif
+#ifndef FAST_CORNER_BALLOT
+#define FAST_CORNER_BALLOT 1
+#endif
 #define FAST_QCAP 192      // survivor queue: < 32 left over + at most 4 x 32 new entries per step
 #ifndef FAST_L2CAP
 #define FAST_L2CAP 512     // corner list; a cell with more corners takes the map-scan form of stage C.  Measured (profiles/r02p_*, r02q_*):
@@ -322,8 +325,30 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, FAST_WMINB) k_fast_warp(const
     const uint32_t outBase = (uint32_t)(cd.ox + 2) | (uint32_t)(cd.oy + 2) << 11;
 
     // exact score of one queued survivor; a corner goes into the score map and onto the corner list
-#define FAST_SCORE_ONE(idxExpr)                                                                              \
+#if FAST_CORNER_BALLOT
+    // corner slots from one ballot (the count lives in a register, warp-uniform): the compiler turns atomicAdd(&cnt[1], 1)
+    // into a match / elect / popc / shfl sequence of a dozen instructions around the shared-memory atomic
+#define FAST_SCORE_ONE(idxExpr, active)                                                                      \
     {                                                                                                        \
+        int idx = 0, s = -1;                                                                                 \
+        if (active) {                                                                                        \
+            idx = (idxExpr);                                                                                 \
+            s = fast_score_packed(tile, idx, off);                                                           \
+        }                                                                                                    \
+        const bool corner = s >= t;                                                                          \
+        const uint32_t cb = __ballot_sync(0xffffffffu, corner);                                              \
+        if (corner) {                                                                                        \
+            const int y = TPC ? idx / TPC : (int)(((uint32_t)idx * invTp) >> 20);                            \
+            const int sidx = y * sp + (idx - y * tp) - sOff;                                                 \
+            const int slot = ncr + __popc(cb & ltMask);                                                      \
+            if (slot < listCap) list2[slot] = (uint16_t)sidx;                                                \
+            score[sidx] = (uint8_t)s;                                                                        \
+        }                                                                                                    \
+        ncr += __popc(cb);                                                                                   \
+    }
+#else
+#define FAST_SCORE_ONE(idxExpr, active)                                                                      \
+    if (active) {                                                                                            \
         const int idx = (idxExpr);                                                                           \
         const int s = fast_score_packed(tile, idx, off);                                                     \
         if (s >= t) {                                                                                        \
@@ -334,6 +359,7 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, FAST_WMINB) k_fast_warp(const
             score[sidx] = (uint8_t)s;                                                                        \
         }                                                                                                    \
     }
+#endif
 #define FAST_NMS(sidx, s)                                                                                    \
     ((s) > score[(sidx) - 1] && (s) > score[(sidx) + 1] && (s) > score[(sidx) - sp - 1] && (s) > score[(sidx) - sp] && \
      (s) > score[(sidx) - sp + 1] && (s) > score[(sidx) + sp - 1] && (s) > score[(sidx) + sp] && (s) > score[(sidx) + sp + 1])
@@ -341,6 +367,8 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, FAST_WMINB) k_fast_warp(const
     int t = iniTh;
     for (int pass = 0; pass < 2; ++pass) {
         if (lane == 0) { cnt[0] = 0; cnt[1] = 0; }
+        int ncr = 0;
+        (void)ncr;
         for (int i = lane; i < (myScoreWords + 3) >> 2; i += 32) reinterpret_cast<uint4*>(score)[i] = make_uint4(0u, 0u, 0u, 0u);
         __syncwarp();                          // also orders lane 0's mbarrier init before the other lanes' wait
         if (pass == 0) mbar_wait(bar, 0);
@@ -376,17 +404,24 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, FAST_WMINB) k_fast_warp(const
             if (qn >= 32) {
                 do {
                     qn -= 32;
-                    FAST_SCORE_ONE(queue[qn + lane])
+                    FAST_SCORE_ONE(queue[qn + lane], true)
                 } while (qn >= 32);
                 __syncwarp();                  // every lane has read its queue entry before the fill count drops
                 if (lane == 0) cnt[0] = qn;
                 __syncwarp();
             }
         }
-        if (lane < *reinterpret_cast<volatile int*>(&cnt[0])) FAST_SCORE_ONE(queue[lane])     // flush: fewer than 32 left
+        {
+            const bool act = lane < *reinterpret_cast<volatile int*>(&cnt[0]);     // flush: fewer than 32 left
+            FAST_SCORE_ONE(queue[lane], act)
+        }
         __syncwarp();
         // C: non-max suppression; kept candidates go to the level's array in 32-wide slices
+#if FAST_CORNER_BALLOT
+        const int nc = ncr;
+#else
         const int nc = *reinterpret_cast<volatile int*>(&cnt[1]);
+#endif
         int keptTotal = 0;
         if (nc > listCap) {                    // rare: the list overflowed, walk the score map itself
             int mine = 0;
