@@ -291,3 +291,23 @@ def test_selectable_paths_give_the_same_result(env):
         "print('selectable path ok')\n")
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True, timeout=300)
     assert r.returncode == 0 and "selectable path ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_largest_supported_image_and_refusal_beyond():
+    """Level-0 ROI up to 2063 px per side (11-bit packed coordinates, INTEGRATION.md "Limits"): the widest frame the
+    library takes is extracted exactly; a wider handle or image is refused with ORBFE_ERR_TOO_LARGE (not a crash, not a wrong
+    result), and the handle stays usable."""
+    w, h, nf = 2063, 600, 3000
+    ex = orbfe.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w, max_height=h)
+    ref = OrbRef(nf, 1.2, 8, 20, 7)
+    img = orbfe.synth.frame(6100, w, h)
+    ok, tot = check_frame(ex, ref, img, (0, 0), stages=True)
+    assert tot > 0.9 * nf and ok >= 0.9999 * tot
+    with pytest.raises(orbfe.OrbfeError) as e:
+        ex(orbfe.synth.frame(6101, w + 1, h), None, (0, 0))
+    assert e.value.status == -3, e.value            # ORBFE_ERR_TOO_LARGE
+    with pytest.raises(orbfe.OrbfeError) as e:
+        orbfe.ORBextractor(nf, 1.2, 8, 20, 7, max_width=w + 1, max_height=h)
+    assert e.value.status == -3, e.value
+    ok2, tot2 = check_frame(ex, ref, img, (0, 0), stages=False)
+    assert (ok2, tot2) == (ok, tot)
