@@ -4,8 +4,8 @@
 // overloads (Frame&, const Frame& LastFrame, ...) :2173-2389, (Frame&, KeyFrame*, ...) :2391-2510.
 //
 // Three kernels per call (any number of problems = Frames with their ordered windows per launch):
-//   k_proj_grid (one CTA per problem): every feature's cell by PosInGrid's round() rule; a shared-memory bitonic
-//      sort of (side, cell, index) keys gives each cell's features in ascending index = the reference's push order.
+//   k_proj_grid (one CTA per problem): every feature's cell by PosInGrid's round() rule; a shared-memory counting
+//      sort by (side, cell) with every cell's segment in ascending index = the reference's push order.
 //   k_proj_candidates (one warp per window, CTAs over all SMs): lanes take the window's cells in
 //      GetFeaturesInArea's order (x outer, y inner); a candidate's key is dist << 40 | position of its cell << 16 |
 //      index, so ascending keys are exactly the order in which the reference's strict '<' updates prefer
@@ -143,46 +143,86 @@ __device__ __forceinline__ int stereo_link(const ProjProblem& P, int idx) {
 }
 
 // ---- 1. grid
+// Counting sort (round 2; the bitonic sort of 2048 keys took 27 us of a 100 us call): a histogram of the 2 x 3072 cells in shared
+// memory, an exclusive scan, a scatter with per-cell fill counters, and - because the scatter's order within a cell is whatever
+// the atomics made it - an insertion sort of every cell's short segment by feature index (= the reference's push order).
+#define GRID_TOTAL (2 * GRID_CELLS)
+#define GRID_PER_THREAD (GRID_TOTAL / PROJ_T)      // 12 cells per thread
 __global__ void __launch_bounds__(PROJ_T) k_proj_grid(const ProjProblem* __restrict__ probs) {
-    extern __shared__ __align__(16) uint32_t sKeys[];
+    extern __shared__ __align__(16) uint32_t sGrid[];
+    int* sCount = reinterpret_cast<int*>(sGrid);                    // GRID_TOTAL: histogram, then fill cursor
+    uint32_t* sKeys = sGrid + GRID_TOTAL;                           // n sorted keys
+    __shared__ int sWarp[PROJ_T / 32];
     const ProjProblem P = probs[blockIdx.x];
-    const int tid = threadIdx.x, n = P.n;
-    int np2 = 1;
-    while (np2 < n) np2 <<= 1;
-    for (int t = tid; t < 2 * GRID_CELLS; t += PROJ_T) { P.cellStart[t] = 0; P.cellEnd[t] = 0; }
-    for (int t = tid; t < np2; t += PROJ_T) {
-        uint32_t key = 0xFFFFFFFFu;
-        if (t < n) {
-            const float4 kp = P.kp[t];
-            const int px = (int)roundf(__fmul_rn(__fsub_rn(kp.x, P.minX), P.gridWInv));
-            const int py = (int)roundf(__fmul_rn(__fsub_rn(kp.y, P.minY), P.gridHInv));
-            if (px >= 0 && px < GRID_COLS && py >= 0 && py < GRID_ROWS) {
-                const int side = (P.nleft == -1 || t < P.nleft) ? 0 : GRID_CELLS;
-                key = (uint32_t)(side + px * GRID_ROWS + py) << 16 | (uint32_t)t;
-            }
-        }
-        sKeys[t] = key;
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5, n = P.n;
+    for (int t = tid; t < GRID_TOTAL; t += PROJ_T) sCount[t] = 0;
+    __syncthreads();
+    // the cell of every feature (PosInGrid's round() rule), -1 outside the grid
+    auto cell_of = [&](int t) -> int {
+        const float4 kp = P.kp[t];
+        const int px = (int)roundf(__fmul_rn(__fsub_rn(kp.x, P.minX), P.gridWInv));
+        const int py = (int)roundf(__fmul_rn(__fsub_rn(kp.y, P.minY), P.gridHInv));
+        if (px < 0 || px >= GRID_COLS || py < 0 || py >= GRID_ROWS) return -1;
+        return ((P.nleft == -1 || t < P.nleft) ? 0 : GRID_CELLS) + px * GRID_ROWS + py;
+    };
+    for (int t = tid; t < n; t += PROJ_T) {
+        const int c = cell_of(t);
+        if (c >= 0) atomicAdd(&sCount[c], 1);
     }
     __syncthreads();
-    for (int k = 2; k <= np2; k <<= 1)
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            for (int t = tid; t < np2; t += PROJ_T) {
-                const int p = t ^ j;
-                if (p > t) {
-                    const uint32_t a = sKeys[t], b = sKeys[p];
-                    if ((a > b) == ((t & k) == 0)) { sKeys[t] = b; sKeys[p] = a; }
-                }
-            }
-            __syncthreads();
-        }
-    for (int t = tid; t < n; t += PROJ_T) {
-        const uint32_t key = sKeys[t];
-        P.sorted[t] = key;
-        if (key == 0xFFFFFFFFu) continue;
-        const int c = (int)(key >> 16);
-        if (t == 0 || (int)(sKeys[t - 1] >> 16) != c) P.cellStart[c] = t;
-        if (t == n - 1 || sKeys[t + 1] == 0xFFFFFFFFu || (int)(sKeys[t + 1] >> 16) != c) P.cellEnd[c] = t + 1;
+    // exclusive scan over the cells: thread = 12 consecutive cells
+    int cnt[GRID_PER_THREAD], sum = 0;
+#pragma unroll
+    for (int k = 0; k < GRID_PER_THREAD; ++k) { cnt[k] = sCount[tid * GRID_PER_THREAD + k]; sum += cnt[k]; }
+    int inc = sum;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= o) inc += v;
     }
+    if (lane == 31) sWarp[wid] = inc;
+    __syncthreads();
+    if (wid == 0) {
+        int w = lane < PROJ_T / 32 ? sWarp[lane] : 0;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const int v = __shfl_up_sync(0xffffffffu, w, o);
+            if (lane >= o) w += v;
+        }
+        if (lane < PROJ_T / 32) sWarp[lane] = w;          // inclusive over warps
+    }
+    __syncthreads();
+    int run = (wid > 0 ? sWarp[wid - 1] : 0) + inc - sum;   // first slot of this thread's first cell
+    int start[GRID_PER_THREAD];
+#pragma unroll
+    for (int k = 0; k < GRID_PER_THREAD; ++k) {
+        start[k] = run;
+        const int c = tid * GRID_PER_THREAD + k;
+        P.cellStart[c] = cnt[k] ? run : 0;                  // (empty cells read 0 / 0, as before)
+        P.cellEnd[c] = cnt[k] ? run + cnt[k] : 0;
+        sCount[c] = run;                                    // fill cursor
+        run += cnt[k];
+    }
+    __syncthreads();
+    for (int t = tid; t < n; t += PROJ_T) {
+        const int c = cell_of(t);
+        if (c >= 0) sKeys[atomicAdd(&sCount[c], 1)] = (uint32_t)c << 16 | (uint32_t)t;
+    }
+    __syncthreads();
+    // ascending feature index inside every cell
+#pragma unroll
+    for (int k = 0; k < GRID_PER_THREAD; ++k) {
+        const int b0 = start[k], e0 = b0 + cnt[k];
+        for (int i = b0 + 1; i < e0; ++i) {
+            const uint32_t key = sKeys[i];
+            int j = i - 1;
+            while (j >= b0 && sKeys[j] > key) { sKeys[j + 1] = sKeys[j]; --j; }
+            sKeys[j + 1] = key;
+        }
+    }
+    __syncthreads();
+    const int valid = sWarp[PROJ_T / 32 - 1];
+    for (int t = tid; t < n; t += PROJ_T) P.sorted[t] = t < valid ? sKeys[t] : 0xFFFFFFFFu;
 }
 
 // ---- 2. candidate lists: blockIdx.y = problem, one warp per window
@@ -459,12 +499,10 @@ __global__ void __launch_bounds__(PROJ_T) k_init_resolve(const ProjProblem* __re
 cudaError_t orbfe_launch_search_for_initialization(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int th,
                                                    float nnRatio, int rotHist, long long* launches) {
     if (nprob <= 0) return cudaSuccess;
-    int np2 = 1;
-    while (np2 < nMax) np2 <<= 1;
-    const size_t smem = (size_t)np2 * 4;
-    if (smem > 48 * 1024) {
-        cudaError_t e = cudaFuncSetAttribute(k_proj_grid, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
+    const size_t smem = ((size_t)2 * 64 * 48 + (size_t)nMax) * 4;      // cell counters + one key per feature
+    {
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_proj_grid), smem);
+        if (ea != cudaSuccess) return ea;
     }
     k_proj_grid<<<nprob, PROJ_T, smem, st>>>(dProbs);
     dim3 grid((nqMax + 7) / 8, nprob);
@@ -477,9 +515,7 @@ cudaError_t orbfe_launch_search_for_initialization(cudaStream_t st, const ProjPr
 cudaError_t orbfe_launch_search_by_projection(cudaStream_t st, const ProjProblem* dProbs, int nprob, int nMax, int nqMax, int mode,
                                               int th, float nnRatio, int linkStereo, int rotHist, long long* launches) {
     if (nprob <= 0) return cudaSuccess;
-    int np2 = 1;
-    while (np2 < nMax) np2 <<= 1;
-    const size_t smem = (size_t)np2 * 4;
+    const size_t smem = ((size_t)2 * 64 * 48 + (size_t)nMax) * 4;      // cell counters + one key per feature
     {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
         const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_proj_grid), smem);
         if (ea != cudaSuccess) return ea;
