@@ -17,7 +17,10 @@
 // folded into the 64-bit atomicMax key instead of being materialised.
 #include "orbfe_internal.h"
 
-#define OCT_THREADS 256
+// Threads per CTA are a template parameter chosen per launch: a level of a 1000-feature frame keeps <= ~250 nodes and 128 threads are
+// fastest (barriers dominate: 0.160 -> 0.147 ms per 512 frames of 752x480), the 4000-feature levels of 1920x1080 frames want 256
+// (27.5 k vs 30.7 k frames/s).  profiles/r04i_variants.txt, r04j_variants.txt.
+#define OCT_MAX_THREADS 256
 
 struct NodeS {
     short x0, x1, y0, y1;
@@ -25,6 +28,7 @@ struct NodeS {
 };
 
 // In-place exclusive scan of data[0..n) by the whole CTA; returns the total to every thread.
+template <int OCT_THREADS>
 __device__ int block_exclusive_scan(int* data, int n, int* warpSums) {
     const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
     const int per = (n + OCT_THREADS - 1) / OCT_THREADS;
@@ -63,6 +67,7 @@ __device__ int block_exclusive_scan(int* data, int n, int* warpSums) {
 }
 
 // Ascending bitonic sort of n2 (power of two) 64-bit keys in shared memory.
+template <int OCT_THREADS>
 __device__ void block_bitonic_sort(unsigned long long* k, int n2) {
     for (int size = 2; size <= n2; size <<= 1)
         for (int stride = size >> 1; stride > 0; stride >>= 1) {
@@ -95,6 +100,7 @@ __device__ __forceinline__ NodeS child_box(const NodeS& nd, int q, int cnt) {
     return c;
 }
 
+template <int OCT_THREADS>
 __global__ void __launch_bounds__(OCT_THREADS) k_octree(const LevelGeom* __restrict__ geom, const uint32_t* __restrict__ cand,
                                                         uint32_t* __restrict__ nodeOfAll, const int* __restrict__ candCount,
                                                         long long candPerFrame, uint32_t* __restrict__ lvlKp,
@@ -144,7 +150,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(const LevelGeom* __restr
     // drop empty initial nodes, keep order (:570-586)
     for (int i = tid; i < nIni; i += OCT_THREADS) scanA[i] = cur[i].cnt > 0;
     __syncthreads();
-    int L = block_exclusive_scan(scanA, nIni, warpSums);
+    int L = block_exclusive_scan<OCT_THREADS>(scanA, nIni, warpSums);
     for (int i = tid; i < nIni; i += OCT_THREADS) {
         upos[i] = (short)scanA[i];
         if (cur[i].cnt > 0) nxt[scanA[i]] = cur[i];
@@ -182,8 +188,8 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(const LevelGeom* __restr
                 scanB[p] = nex;
             }
             __syncthreads();
-            const int tot = block_exclusive_scan(scanA, L, warpSums);
-            nToExpand = block_exclusive_scan(scanB, L, warpSums);
+            const int tot = block_exclusive_scan<OCT_THREADS>(scanA, L, warpSums);
+            nToExpand = block_exclusive_scan<OCT_THREADS>(scanB, L, warpSums);
             TC = tot & 0xFFFF;
             newL = TC + (tot >> 16);
             for (int p = tid; p < L; p += OCT_THREADS) {
@@ -217,7 +223,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(const LevelGeom* __restr
                 skey[p] = key;
             }
             __syncthreads();
-            block_bitonic_sort(skey, n2);
+            block_bitonic_sort<OCT_THREADS>(skey, n2);
             // growth of the list if sorted entry j is split: (#non-empty children - 1)
             for (int j = tid; j < L; j += OCT_THREADS) {
                 int grow = 0;
@@ -231,7 +237,7 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(const LevelGeom* __restr
                 scanA[j] = grow;
             }
             __syncthreads();
-            const int tot = block_exclusive_scan(scanA, L, warpSums);
+            const int tot = block_exclusive_scan<OCT_THREADS>(scanA, L, warpSums);
             const int E = tot >> 16;
             // entry j is split iff the list was still short before it: L + growth of entries < j  < N
             // (the reference breaks right after the split that reaches N, :728-729)
@@ -249,10 +255,10 @@ __global__ void __launch_bounds__(OCT_THREADS) k_octree(const LevelGeom* __restr
                 }
             }
             __syncthreads();
-            TC = block_exclusive_scan(scanB, L, warpSums);            // creation index over sorted order
+            TC = block_exclusive_scan<OCT_THREADS>(scanB, L, warpSums);            // creation index over sorted order
             for (int p = tid; p < L; p += OCT_THREADS) scanA[p] = upos[p] != -1;
             __syncthreads();
-            const int nKeep = block_exclusive_scan(scanA, L, warpSums);   // survivors keep list order
+            const int nKeep = block_exclusive_scan<OCT_THREADS>(scanA, L, warpSums);   // survivors keep list order
             newL = TC + nKeep;
             for (int j = tid; j < E; j += OCT_THREADS) {
                 const int p = (int)(skey[j] & 0xFFFFFFFFu);
@@ -331,13 +337,17 @@ cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch) {
     int sortCap = 1;
     while (sortCap < Lcap) sortCap <<= 1;
     const size_t smem = octree_smem_bytes(Lcap, sortCap);
-    {   // the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem
-        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_octree), smem);
-        if (ea != cudaSuccess) return ea;
-    }
     dim3 grid(h->p.nlevels, batch);
-    k_octree<<<grid, OCT_THREADS, smem, h->cur>>>(h->dGeom, h->dCand, h->dNodeOf, h->dCandCount, h->candPerFrame,
-                                                     h->dLvlKp, h->dLvlCount, h->kpPerFrame, h->p.nlevels, Lcap, sortCap, frame0);
+#define ORBFE_OCT_LAUNCH(NT)                                                                                                     \
+    do {    /* the attribute is per device: one high-water mark per (device, kernel), see orbfe_ensure_dyn_smem */              \
+        const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_octree<NT>), smem);                         \
+        if (ea != cudaSuccess) return ea;                                                                                        \
+        k_octree<NT><<<grid, NT, smem, h->cur>>>(h->dGeom, h->dCand, h->dNodeOf, h->dCandCount, h->candPerFrame, h->dLvlKp,      \
+                                                 h->dLvlCount, h->kpPerFrame, h->p.nlevels, Lcap, sortCap, frame0);             \
+    } while (0)
+    if (Lcap <= 320) ORBFE_OCT_LAUNCH(128);     // up to ~1400 features per frame
+    else ORBFE_OCT_LAUNCH(256);
+#undef ORBFE_OCT_LAUNCH
     h->launches++;
     return cudaGetLastError();
 }
