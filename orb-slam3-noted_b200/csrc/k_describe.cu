@@ -248,7 +248,7 @@ __global__ void __launch_bounds__(128, BLUR_MINB) k_blur_resident(const uint8_t*
 #define DESC_KPW 1         // key points per warp.  > 1 keeps the lane's part of the pattern in registers across key points: measured
 #endif                     // (profiles/r03q_variants.txt) 0.921 ms at 8 (85 or 51 registers), 1.09 at 4-8 with 64 registers, vs 0.914 at 1
 #ifndef DESC_MINB
-#define DESC_MINB (DESC_KPW > 1 ? 4 : 6)
+#define DESC_MINB (DESC_KPW > 1 ? 4 : 8)      // 8 CTAs of 8 warps = every warp slot of the SM at 32 registers: describe stage 0.916 -> 0.881 ms (profiles/r04p_variants.txt)
 #endif
 __global__ void __launch_bounds__(DESC_WARPS * 32, DESC_MINB) k_describe(const uint8_t* __restrict__ pyr, const uint8_t* __restrict__ blur,
                                                               const LevelGeom* __restrict__ geom,

@@ -193,7 +193,10 @@ namespace {
 __device__ __forceinline__ uint32_t pyr_s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 }
 #define PYRTMA_THREADS (ORBFE_PYRTMA_ROWS / PYR_TH * 32)
-__global__ void __launch_bounds__(PYRTMA_THREADS) k_pyr_resize_tma(const __grid_constant__ FastMaps maps, uint8_t* __restrict__ pyr, LevelGeom gd,
+#ifndef PYRTMA_MINB
+#define PYRTMA_MINB 1
+#endif
+__global__ void __launch_bounds__(PYRTMA_THREADS, PYRTMA_MINB) k_pyr_resize_tma(const __grid_constant__ FastMaps maps, uint8_t* __restrict__ pyr, LevelGeom gd,
                                                         const ResizeTap* __restrict__ taps, const ColPlan* __restrict__ plans,
                                                         const PyrTmaPlan* __restrict__ plan, int level, int frame0) {
     extern __shared__ __align__(128) uint8_t tileBytes[];
