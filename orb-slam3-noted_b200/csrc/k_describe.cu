@@ -19,7 +19,9 @@
 
 #include "orbfe_internal.h"
 
-#define ASM_THREADS 256
+#ifndef ASM_THREADS
+#define ASM_THREADS 1024       // 128 / 256 / 512 / 1024 threads: 0.034 / 0.029 / 0.025 / 0.021 ms per 512 frames (profiles/r04s_variants.txt, r04t)
+#endif
 
 // bit_pattern_31_ (ORBextractor.cc:147-406) as 256 tests x (x0, y0, x1, y1) int8; staged per CTA into
 // shared memory in [test & 7][test >> 3] order so that lane i's k-th test is a conflict-free word read.

@@ -345,7 +345,10 @@ cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch) {
         k_octree<NT><<<grid, NT, smem, h->cur>>>(h->dGeom, h->dCand, h->dNodeOf, h->dCandCount, h->candPerFrame, h->dLvlKp,      \
                                                  h->dLvlCount, h->kpPerFrame, h->p.nlevels, Lcap, sortCap, frame0);             \
     } while (0)
-    if (Lcap <= 320) ORBFE_OCT_LAUNCH(128);     // up to ~1400 features per frame
+    // 128 threads win on throughput (fewer lanes per barrier, more CTAs per SM); a launch that does not fill the GPU anyway
+    // (single frames: 8 CTAs) is a matter of one CTA's latency, and that is shorter with 256 (28 vs 35 us)
+    const bool fewCtas = (long long)batch * h->p.nlevels <= 2LL * h->smCount;
+    if (Lcap <= 320 && !fewCtas) ORBFE_OCT_LAUNCH(128);     // up to ~1400 features per frame
     else ORBFE_OCT_LAUNCH(256);
 #undef ORBFE_OCT_LAUNCH
     h->launches++;
