@@ -21,7 +21,7 @@ else
     cp $so $CSRC/liborbfe.so; touch $CSRC/liborbfe.so
     echo "== $(basename $so .so)"
     python -m pytest $ROOT/tests/test_extract_gpu.py -x -q 2>&1 | tail -1
-    python $ROOT/bench.py --no-cpu --no-match --no-legs --steps 100 2>/dev/null | python -c "
+    python $ROOT/bench.py --no-cpu --no-match --no-legs --steps 60 2>/dev/null | python -c "
 import sys,json
 d=json.loads(sys.stdin.read()); print(round(d['value']), round(d['e2e']['value']), {k: round(v,3) for k,v in d['roofline']['stage_ms_per_step'].items()})"
   done
