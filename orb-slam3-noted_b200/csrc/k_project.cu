@@ -209,7 +209,8 @@ __global__ void __launch_bounds__(PROJ_T) k_proj_grid(const ProjProblem* __restr
         if (c >= 0) sKeys[atomicAdd(&sCount[c], 1)] = (uint32_t)c << 16 | (uint32_t)t;
     }
     __syncthreads();
-    // ascending feature index inside every cell
+    // ascending feature index inside every cell (segments are a handful of entries: 3072 cells for a few thousand features; a
+    // frame with hundreds of features in ONE 12 x 10 px cell would make this quadratic for that thread - slow, still correct)
 #pragma unroll
     for (int k = 0; k < GRID_PER_THREAD; ++k) {
         const int b0 = start[k], e0 = b0 + cnt[k];
