@@ -33,6 +33,20 @@ __global__ void __launch_bounds__(256) k_pyr_level0(const uint8_t* __restrict__ 
     uint8_t* dst = out + g.base + (long long)(frame0 + blockIdx.y) * g.plane;
     const bool inside = x0 >= 0 && x0 + 16 <= g.w;
     const int al = (int)((reinterpret_cast<uintptr_t>(frame) | (uintptr_t)stride) & 15);     // every row start shares this alignment
+    if (inside && al == 0) {      // the common case: every load of the thread issued before its first store
+        uint4 v[PYR_L0_ROWS];
+#pragma unroll
+        for (int k = 0; k < PYR_L0_ROWS; ++k) {
+            const int y = reflect101(min(rowA + 32 * k, g.rows - 1) - ORBFE_EDGE, g.h);
+            v[k] = __ldg(reinterpret_cast<const uint4*>(frame + (long long)y * stride + x0));
+        }
+#pragma unroll
+        for (int k = 0; k < PYR_L0_ROWS; ++k) {
+            const int row = rowA + 32 * k;
+            if (row < g.rows) reinterpret_cast<uint4*>(dst + (long long)row * g.pitch)[chunk] = v[k];
+        }
+        return;
+    }
 #pragma unroll
     for (int k = 0; k < PYR_L0_ROWS; ++k) {
         const int row = rowA + 32 * k;
