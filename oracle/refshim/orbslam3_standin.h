@@ -32,6 +32,24 @@ class Frame;
 class KeyFrame;
 class MapPoint;
 
+#ifdef ORBSLAM3_REAL_CAMERAS
+}  // namespace ORB_SLAM3
+// liborbslam3_orbmatcher_cam.so: the reference's OWN include/CameraModels/{GeometricCamera,Pinhole,KannalaBrandt8}.h and their .cpp
+// files instead of the stand-in camera below (TwoViewReconstruction.h stays out through its include guard: it belongs to monocular
+// initialisation, not to the matcher).
+namespace ORB_SLAM3 {
+class TwoViewReconstruction {
+public:
+    TwoViewReconstruction(cv::Mat&, float sigma = 1.0, int iterations = 200) { (void)sigma; (void)iterations; }
+    bool Reconstruct(const std::vector<cv::KeyPoint>&, const std::vector<cv::KeyPoint>&, const std::vector<int>&, cv::Mat&, cv::Mat&,
+                     std::vector<cv::Point3f>&, std::vector<bool>&) { return false; }
+};
+}  // namespace ORB_SLAM3
+#include "CameraModels/GeometricCamera.h"
+#include "CameraModels/Pinhole.h"
+#include "CameraModels/KannalaBrandt8.h"
+namespace ORB_SLAM3 {
+#else
 class GeometricCamera {
 public:
     virtual ~GeometricCamera() {}
@@ -83,6 +101,8 @@ public:
         return epipolarConstrain_(o, kp1, kp2, cv::Matx33f(), cv::Matx31f(), s, unc);
     }
 };
+
+#endif  // ORBSLAM3_REAL_CAMERAS
 
 class MapPoint {
 public:

@@ -249,7 +249,11 @@ def tri_kb8_inputs(name):
     return dict(k1=k1, d1=d1, fv1=fv_of(d1), mp1=orbfe.synth.mask(seed * 7 + 1, len(d1), 40), k2=k2, d2=d2, fv2=fv_of(d2),
                 mp2=orbfe.synth.mask(seed * 7 + 2, len(d2), 40), cam_a=cam, cam_b=cam, nleft_a=nleft1, nleft_b=nleft2, R12=R12,
                 t12=t12, ep=(float(np.float32(ep[0])), float(np.float32(ep[1]))), check_ori=ori, only_stereo=False,
-                coarse=coarse, nlevels=nlev)
+                coarse=coarse, nlevels=nlev,
+                # the same geometry as keyframe poses (what the reference's SearchForTriangulation_ starts from): Tcw of the
+                # two left cameras and KeyFrame::mTrl (right camera from left)
+                Tcw1=np.linalg.inv(T_w_l1).astype(np.float32), Tcw2=np.linalg.inv(T_w_l2).astype(np.float32),
+                Trl=np.linalg.inv(Tlr).astype(np.float32))
 
 
 def distinctive_inputs(seed=5200, npoints=400):

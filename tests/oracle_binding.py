@@ -493,6 +493,49 @@ def ref_matcher():
     return _ref_matcher
 
 
+# ---- the reference's ORBmatcher.cc TOGETHER WITH its own camera models (oracle/_ref/liborbslam3_orbmatcher_cam.so) ----
+REF_MATCHER_CAM_LIB = os.path.join(os.path.dirname(REF_LIB), "liborbslam3_orbmatcher_cam.so")
+_ref_matcher_cam = None
+
+
+def ref_matcher_cam_available():
+    return os.path.exists(REF_MATCHER_CAM_LIB)
+
+
+class _KfArrays(C.Structure):
+    _fields_ = [("kps", _P), ("desc", _P), ("n", _I), ("nleft", _I), ("hasMp", _P), ("uRight", _P), ("nodes", _P), ("off", _P),
+                ("idx", _P), ("nnodes", _I), ("sigma2", _P), ("scale", _P), ("nlevels", _I), ("cam", _P), ("Tcw", _P), ("Trl", _P)]
+
+
+def ref_search_for_triangulation_cam(fisheye, A, B, nnratio, check_ori, only_stereo, coarse):
+    """SearchForTriangulation_ of the reference on its own Pinhole / KannalaBrandt8 classes, from keyframe POSES.
+    A, B: dicts with kps, desc, fv, mp, nleft, u_right (or None), sigma2, scale, cam (2 x 8), Tcw (4 x 4), Trl (4 x 4).
+    Returns (matches12, nmatches)."""
+    global _ref_matcher_cam
+    if _ref_matcher_cam is None:
+        _ref_matcher_cam = C.CDLL(REF_MATCHER_CAM_LIB)
+        _ref_matcher_cam.orbslam3_search_for_triangulation_cam.argtypes = [_F, _I, _I, _P, _P, _I, _I, _P]
+    keep = []
+
+    def side(d):
+        f = lambda a: np.ascontiguousarray(a, np.float32)
+        arrs = dict(kps=np.ascontiguousarray(d["kps"]), desc=np.ascontiguousarray(d["desc"], np.uint8),
+                    hasMp=np.ascontiguousarray(d["mp"]).astype(np.uint8),
+                    uRight=None if d.get("u_right") is None else f(d["u_right"]), nodes=np.ascontiguousarray(d["fv"].node_ids),
+                    off=np.ascontiguousarray(d["fv"].offsets), idx=np.ascontiguousarray(d["fv"].indices), sigma2=f(d["sigma2"]),
+                    scale=f(d["scale"]), cam=f(d["cam"]), Tcw=f(d["Tcw"]), Trl=f(d["Trl"]))
+        assert arrs["cam"].size == 16 and arrs["Tcw"].size == 16 and arrs["Trl"].size == 16
+        keep.append(arrs)
+        ptr = {k: (_pn(v) if v is None else _p(v)) for k, v in arrs.items()}
+        return _KfArrays(n=len(arrs["desc"]), nleft=int(d["nleft"]), nnodes=len(arrs["nodes"]), nlevels=len(arrs["sigma2"]), **ptr)
+
+    a, b = side(A), side(B)
+    m12 = np.zeros(max(a.n, 1), np.int32)
+    n = _ref_matcher_cam.orbslam3_search_for_triangulation_cam(float(nnratio), int(check_ori), int(fisheye), C.byref(a), C.byref(b),
+                                                               int(only_stereo), int(coarse), _p(m12))
+    return m12[:a.n], n
+
+
 # The orbfe shim's ORBmatcher object layer behind the same C entry points (make -C oracle shim): GPU-backed.
 SHIM_MATCHER_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "liborbfe_shim_orbmatcher.so")
 _shim_matcher = None
