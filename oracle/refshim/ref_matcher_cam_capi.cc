@@ -45,7 +45,7 @@ GeometricCamera* makeCamera(int fisheye, const float* p) {
 
 void fill(KeyFrame& K, const KfArrays& a, int fisheye, std::vector<std::unique_ptr<GeometricCamera>>& cams, MapPoint* some) {
     std::vector<cv::KeyPoint> all(a.n);
-    if (a.n) memcpy(all.data(), a.kps, sizeof(KpPod) * (size_t)a.n);
+    if (a.n) memcpy((void*)all.data(), a.kps, sizeof(KpPod) * (size_t)a.n);
     K.N = a.n;
     K.NLeft = a.nleft;
     if (a.nleft < 0) { K.mvKeysUn = all; K.mvKeys = all; }
@@ -75,6 +75,16 @@ void fill(KeyFrame& K, const KfArrays& a, int fisheye, std::vector<std::unique_p
     }
     K.Tcw = mat44(a.Tcw);
 }
+
+// The F12 argument as the reference's caller forms it (LocalMapping::CreateNewMapPoints, src/LocalMapping.cc:477, through
+// ComputeF12_ :886-903): K1^-T [t12]x R12 K2^-1 of the two left cameras.  The reference's matcher ignores the argument
+// (Pinhole::epipolarConstrain_ rebuilds the same product per pair); the orbfe shim uses it.
+cv::Matx33f callerF12(KeyFrame& K1, KeyFrame& K2) {
+    const cv::Matx33f R12 = K1.GetRotation_() * K2.GetRotation_().t();
+    const cv::Matx31f t12 = -K1.GetRotation_() * K2.GetRotation_().t() * K2.GetTranslation_() + K1.GetTranslation_();
+    const cv::Matx33f cross{0.f, -t12(2), t12(1), t12(2), 0.f, -t12(0), -t12(1), t12(0), 0.f};
+    return K1.mpCamera->toK_().t().inv() * cross * R12 * K2.mpCamera->toK_().inv();
+}
 }  // namespace
 
 extern "C" {
@@ -89,7 +99,7 @@ int orbslam3_search_for_triangulation_cam(float nnratio, int checkOri, int fishe
     fill(K1, *A, fisheye, cams, &some);
     fill(K2, *B, fisheye, cams, &some);
     std::vector<std::pair<size_t, size_t>> pairs;
-    const int n = matcher.SearchForTriangulation_(&K1, &K2, cv::Matx33f(), pairs, onlyStereo != 0, coarse != 0);
+    const int n = matcher.SearchForTriangulation_(&K1, &K2, callerF12(K1, K2), pairs, onlyStereo != 0, coarse != 0);
     for (int i = 0; i < A->n; ++i) matches12[i] = -1;
     for (const auto& pr : pairs) matches12[pr.first] = (int32_t)pr.second;
     return n;

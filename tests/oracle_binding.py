@@ -507,14 +507,27 @@ class _KfArrays(C.Structure):
                 ("idx", _P), ("nnodes", _I), ("sigma2", _P), ("scale", _P), ("nlevels", _I), ("cam", _P), ("Tcw", _P), ("Trl", _P)]
 
 
-def ref_search_for_triangulation_cam(fisheye, A, B, nnratio, check_ori, only_stereo, coarse):
+SHIM_MATCHER_CAM_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "liborbfe_shim_orbmatcher_cam.so")
+_shim_matcher_cam = None
+
+
+def shim_matcher_cam_available():
+    return os.path.exists(SHIM_MATCHER_CAM_LIB)
+
+
+def ref_search_for_triangulation_cam(fisheye, A, B, nnratio, check_ori, only_stereo, coarse, shim=False):
     """SearchForTriangulation_ of the reference on its own Pinhole / KannalaBrandt8 classes, from keyframe POSES.
     A, B: dicts with kps, desc, fv, mp, nleft, u_right (or None), sigma2, scale, cam (2 x 8), Tcw (4 x 4), Trl (4 x 4).
+    shim=True: the same call on ORB_SLAM3::ORBmatcher of include/orbfe_shim (GPU-backed), same objects, same real cameras.
     Returns (matches12, nmatches)."""
-    global _ref_matcher_cam
-    if _ref_matcher_cam is None:
+    global _ref_matcher_cam, _shim_matcher_cam
+    if shim and _shim_matcher_cam is None:
+        _shim_matcher_cam = C.CDLL(SHIM_MATCHER_CAM_LIB)
+        _shim_matcher_cam.orbslam3_search_for_triangulation_cam.argtypes = [_F, _I, _I, _P, _P, _I, _I, _P]
+    if not shim and _ref_matcher_cam is None:
         _ref_matcher_cam = C.CDLL(REF_MATCHER_CAM_LIB)
         _ref_matcher_cam.orbslam3_search_for_triangulation_cam.argtypes = [_F, _I, _I, _P, _P, _I, _I, _P]
+    library = _shim_matcher_cam if shim else _ref_matcher_cam
     keep = []
 
     def side(d):
@@ -531,7 +544,7 @@ def ref_search_for_triangulation_cam(fisheye, A, B, nnratio, check_ori, only_ste
 
     a, b = side(A), side(B)
     m12 = np.zeros(max(a.n, 1), np.int32)
-    n = _ref_matcher_cam.orbslam3_search_for_triangulation_cam(float(nnratio), int(check_ori), int(fisheye), C.byref(a), C.byref(b),
+    n = library.orbslam3_search_for_triangulation_cam(float(nnratio), int(check_ori), int(fisheye), C.byref(a), C.byref(b),
                                                                int(only_stereo), int(coarse), _p(m12))
     return m12[:a.n], n
 

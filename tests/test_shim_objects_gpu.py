@@ -121,3 +121,53 @@ def test_relocalisation_objects(orbdist):
     w, g = both(ob.ref_search_by_projection_reloc, c["Cur"], kf, c["Tcw"], 10.0, orbdist, pc.CAM, np.float32(np.log(1.2)))
     same(w, g)
     assert w[0] > 60
+
+
+# ---- the same object layer on the reference's OWN camera classes (liborbslam3_orbmatcher_cam.so vs liborbfe_shim_orbmatcher_cam.so) ----
+cam_libs = pytest.mark.skipif(not (ob.ref_matcher_cam_available() and ob.shim_matcher_cam_available()),
+                              reason="the *_cam libraries are not built (make -C oracle ref shim)")
+
+
+@cam_libs
+@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES))
+def test_search_for_triangulation_objects_kannala_brandt(name):
+    """SearchForTriangulation_ on keyframes that hold real KannalaBrandt8 objects: the shim reads GetType() / getParameter(), forms the
+    relative poses of the four camera pairings from the keyframes' poses and runs orbfe_search_triangulation_kb8; the reference
+    runs KannalaBrandt8::epipolarConstrain_ per pair.  Rows may differ only where a threshold of the triangulation test lies within
+    1e-3 (relative) of the computed value (the oracle reports that margin per row)."""
+    from oracle_binding import OrbRef
+    from test_reference_matcher_cameras import _sides
+    sc, isc, s2 = OrbRef(1000, *mc.ORB).tables()[:3]
+    c = mc.tri_kb8_inputs(name)
+    A, B = _sides(c, s2, sc, c["cam_a"], c["cam_b"])
+    want, wn = ob.ref_search_for_triangulation_cam(1, A, B, 0.6, c["check_ori"], False, c["coarse"])
+    got, gn = ob.ref_search_for_triangulation_cam(1, A, B, 0.6, c["check_ori"], False, c["coarse"], shim=True)
+    mg = ob.search_triangulation_kb8(c["k1"], c["d1"], c["fv1"], c["mp1"], s2, c["k2"], c["d2"], c["fv2"], c["mp2"], s2, sc, c["cam_a"],
+                                     c["cam_b"], c["nleft_a"], c["nleft_b"], c["R12"], c["t12"], c["ep"], c["check_ori"], False,
+                                     c["coarse"])[3]
+    assert gn == (got >= 0).sum() and gn > 60
+    safe, differs = mg > 1e-3, got != want
+    if not (c["check_ori"] and (differs & ~safe).any()):
+        assert not (differs & safe).any(), np.flatnonzero(differs & safe)
+        assert gn == wn or (differs & ~safe).any()
+    else:
+        assert differs.mean() < 0.01
+    assert ob.ref_search_for_triangulation_cam(1, A, B, 0.6, c["check_ori"], True, c["coarse"], shim=True)[1] == 0
+
+
+@cam_libs
+@pytest.mark.parametrize("name", [k for k, v in mc.TRI_CASES.items() if v[7] is None])
+def test_search_for_triangulation_objects_real_pinhole(name):
+    """Keyframes that hold real Pinhole objects, F12 as LocalMapping::ComputeF12_ forms it from the poses: identical pairs."""
+    from test_reference_matcher_cameras import _sides
+    sc, isc, s2, is2, per, umax = tables()
+    c = mc.tri_inputs(name, extract, sc, s2)
+    cam = mc.TRI_CASES[name][0]
+    K = np.zeros((2, 8), np.float32)
+    K[:, :4] = (cam["fx"], cam["fy"], cam["cx"], cam["cy"])
+    c["Tcw1"], c["Tcw2"], c["Trl"] = np.eye(4, dtype=np.float32), np.eye(4, dtype=np.float32), np.eye(4, dtype=np.float32)
+    c["Tcw2"][0, 3] = -0.1
+    A, B = _sides(c, s2, sc, K, K, c["ur1"], c["ur2"])
+    want, wn = ob.ref_search_for_triangulation_cam(0, A, B, 0.6, c["check_ori"], c["only_stereo"], c["coarse"])
+    got, gn = ob.ref_search_for_triangulation_cam(0, A, B, 0.6, c["check_ori"], c["only_stereo"], c["coarse"], shim=True)
+    assert wn == gn and np.array_equal(want, got) and gn > 20
