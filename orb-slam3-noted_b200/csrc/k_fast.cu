@@ -468,6 +468,9 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, FAST_WMINB) k_fast_warp(const
 #undef FAST_NMS
 }
 
+#ifndef FAST_SIDE
+#define FAST_SIDE 1       // measured (profiles/r05c_fast_side.txt): 200.8 -> 201.6 k frames/s, e2e 125.2 -> 126.3 k
+#endif
 #ifndef FAST_SMALL_ROWS
 #define FAST_SMALL_ROWS 48     // levels whose cells are at most this tall share a launch with a small shared-memory footprint
 #endif
@@ -482,6 +485,19 @@ static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
     // ... unless the whole launch fits the GPU at once anyway (single frames, stereo pairs): then occupancy is not the issue,
     // the second launch's ~15 us of cell latency is, and everything goes out together with the largest footprint.
     const bool oneLaunch = (long long)h->nCellsTotal * batch <= 24LL * h->smCount;
+    // ORBFE_FAST_SIDE=1: the launches after the first go to the compute stream's side stream (forked after the candidate counters
+    // are cleared, joined before the quadtree), so that the few tall cells run under the main launch instead of after it
+    static const int sideEnv = [] { const char* e = getenv("ORBFE_FAST_SIDE"); return e ? atoi(e) : FAST_SIDE; }();
+    int side = -1;
+    if (sideEnv && !oneLaunch && !h->profiling && !h->blurOverlap)
+        for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
+            if (h->sComp[i] == h->cur) side = i;
+    if (side >= 0) {
+        cudaError_t ef = cudaEventRecord(h->evPyr[side], h->cur);
+        if (ef == cudaSuccess) ef = cudaStreamWaitEvent(h->sSide[side], h->evPyr[side], 0);
+        if (ef != cudaSuccess) return ef;
+    }
+    int nLaunch = 0;
     for (int l = 0; l < nl;) {
         const bool small = oneLaunch || h->geom[l].fastBoxH <= FAST_SMALL_ROWS;
         int l1 = l, maxH = 0;
@@ -498,11 +514,13 @@ static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
         const int warpBytes = (tileStride + scoreStride + 2 * listCap + 2 * FAST_QCAP + 16 + 127) & ~127;
         const size_t smem = (size_t)warpBytes * FAST_WARPS;
         dim3 grid((cellEnd - cell0 + FAST_WARPS - 1) / FAST_WARPS, batch);
+        cudaStream_t st = (side >= 0 && nLaunch > 0) ? h->sSide[side] : h->cur;
+        ++nLaunch;
 #define ORBFE_FAST_WLAUNCH(TPC)                                                                                                  \
         do {                                                                                                                     \
             const cudaError_t ea = orbfe_ensure_dyn_smem(reinterpret_cast<const void*>(k_fast_warp<TPC>), smem);                 \
             if (ea != cudaSuccess) return ea;                                                                                    \
-            k_fast_warp<TPC><<<grid, 32 * FAST_WARPS, smem, h->cur>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount, \
+            k_fast_warp<TPC><<<grid, 32 * FAST_WARPS, smem, st>>>(h->fastMaps, h->dGeom, h->dCells, h->dCand, h->dCandCount,     \
                                                                       h->candPerFrame, nl, h->p.ini_th_fast, h->p.min_th_fast,   \
                                                                       h->fastBoxW, tileBytes, listCap, invTp, frame0, cell0, cellEnd, warpBytes, \
                                                                       sp, invSp, scoreStride);                                     \
@@ -512,6 +530,11 @@ static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
         else ORBFE_FAST_WLAUNCH(0);
 #undef ORBFE_FAST_WLAUNCH
         h->launches++;
+    }
+    if (side >= 0) {                               // join (also when nothing went to the side stream: a capture must not end forked)
+        cudaError_t ej = cudaEventRecord(h->evBlur[side], h->sSide[side]);
+        if (ej == cudaSuccess) ej = cudaStreamWaitEvent(h->cur, h->evBlur[side], 0);
+        if (ej != cudaSuccess) return ej;
     }
     return cudaGetLastError();
 }

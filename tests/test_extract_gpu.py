@@ -262,31 +262,34 @@ def test_fast_corner_list_overflow_path():
 
 
 @pytest.mark.parametrize("env", [{"ORBFE_PYR_TMA": "0"}, {"ORBFE_BLUR_OVERLAP": "1", "ORBFE_BLUR_PERSIST": "2"},
-                                 {"ORBFE_BLUR": "tensor"}, {"ORBFE_GRAPHS": "0", "ORBFE_DEV_CHUNK": "2", "ORBFE_DEV_STREAMS": "3"}],
-                         ids=["resize_through_L1", "blur_on_side_stream", "tensor_blur", "chunked_no_graphs"])
+                                 {"ORBFE_BLUR": "tensor"}, {"ORBFE_GRAPHS": "0", "ORBFE_DEV_CHUNK": "2", "ORBFE_DEV_STREAMS": "3"},
+                                 {"ORBFE_FAST_SIDE": "0", "ORBFE_TEST_FRAMES": "8"}, {"ORBFE_FAST_SIDE": "1", "ORBFE_TEST_FRAMES": "8"}],
+                         ids=["resize_through_L1", "blur_on_side_stream", "tensor_blur", "chunked_no_graphs", "fast_in_line",
+                              "fast_tall_cells_on_side_stream"])
 def test_selectable_paths_give_the_same_result(env):
     """The kernels and schedules that are not the default (read-once environment knobs) against the oracle: the L1 form of the
-    resize, the blur on a side stream with resident CTAs, the tensor-core blur, eager chunked launches on three streams."""
+    resize, the blur on a side stream with resident CTAs, the tensor-core blur, eager chunked launches on three streams, FAST's
+    two launches in line / forked (eight frames: more cells than fit the GPU at once, so that there ARE two launches)."""
     import os
     import subprocess
     import sys
     here = os.path.dirname(os.path.abspath(__file__))
     code = (
-        "import sys, numpy as np\n"
+        "import os, sys, numpy as np\n"
         f"sys.path[:0] = [{here!r}, {os.path.join(os.path.dirname(here), 'orb-slam3-noted_b200')!r}]\n"
         "import orbfe\n"
         "from oracle_binding import OrbRef\n"
-        "w, h = 640, 400\n"
-        "ex = orbfe.ORBextractor(800, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=5)\n"
+        "w, h, nfr = 640, 400, int(os.environ.get('ORBFE_TEST_FRAMES', '5'))\n"
+        "ex = orbfe.ORBextractor(800, 1.2, 8, 20, 7, max_width=w, max_height=h, max_batch=nfr)\n"
         "ref = OrbRef(800, 1.2, 8, 20, 7)\n"
-        "frames = np.stack([orbfe.synth.frame(4200 + i, w, h) for i in range(5)])\n"
+        "frames = np.stack([orbfe.synth.frame(4200 + i, w, h) for i in range(nfr)])\n"
         "for rep in range(3):\n"                       # eager, captured, replayed
         "    res = ex.extract_batch(frames, (0, 0))\n"
-        "for f in range(5):\n"
+        "for f in range(nfr):\n"
         "    rmono, rk, rd = ref(frames[f], (0, 0)); mono, k, d = res[f]\n"
         "    assert mono == rmono and all(np.array_equal(k[x], rk[x]) for x in ('octave', 'x', 'y', 'response')), f\n"
         "    assert np.array_equal(d, rd), f\n"
-        "    if f == 4:\n"
+        "    if f == nfr - 1:\n"
         "        for l in range(8): assert np.array_equal(ex.image_pyramid(l, f)[0], ref.level(l)), l\n"
         "print('selectable path ok')\n")
     r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, **env), capture_output=True, text=True, timeout=300)
