@@ -469,12 +469,12 @@ __global__ void __launch_bounds__(32 * FAST_WARPS, FAST_WMINB) k_fast_warp(const
 }
 
 #ifndef FAST_SIDE
-#define FAST_SIDE 1       // measured (profiles/r05c_fast_side.txt): 200.8 -> 201.6 k frames/s, e2e 125.2 -> 126.3 k
+#define FAST_SIDE 2       // measured (profiles/r05c_fast_side.txt, r05d): 0 / 1 / 2 = 200.8 / 201.6 / 201.8 k frames/s, e2e 125.2 / 126.3 / 126.8 k
 #endif
 #ifndef FAST_SMALL_ROWS
 #define FAST_SMALL_ROWS 48     // levels whose cells are at most this tall share a launch with a small shared-memory footprint
 #endif
-static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
+static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch, cudaStream_t sideStream) {
     // ORBFE_FAST_L2CAP (environment, tests only) shrinks the corner list so that ordinary frames take the overflow path
     static const int capEnv = [] { const char* e = getenv("ORBFE_FAST_L2CAP"); const int v = e ? atoi(e) : 0; return v >= 4 ? (v & ~3) : FAST_L2CAP; }();
     const uint32_t invTp = ((1u << 20) + h->fastBoxW - 1) / h->fastBoxW;
@@ -485,18 +485,6 @@ static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
     // ... unless the whole launch fits the GPU at once anyway (single frames, stereo pairs): then occupancy is not the issue,
     // the second launch's ~15 us of cell latency is, and everything goes out together with the largest footprint.
     const bool oneLaunch = (long long)h->nCellsTotal * batch <= 24LL * h->smCount;
-    // ORBFE_FAST_SIDE=1: the launches after the first go to the compute stream's side stream (forked after the candidate counters
-    // are cleared, joined before the quadtree), so that the few tall cells run under the main launch instead of after it
-    static const int sideEnv = [] { const char* e = getenv("ORBFE_FAST_SIDE"); return e ? atoi(e) : FAST_SIDE; }();
-    int side = -1;
-    if (sideEnv && !oneLaunch && !h->profiling && !h->blurOverlap)
-        for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
-            if (h->sComp[i] == h->cur) side = i;
-    if (side >= 0) {
-        cudaError_t ef = cudaEventRecord(h->evPyr[side], h->cur);
-        if (ef == cudaSuccess) ef = cudaStreamWaitEvent(h->sSide[side], h->evPyr[side], 0);
-        if (ef != cudaSuccess) return ef;
-    }
     int nLaunch = 0;
     for (int l = 0; l < nl;) {
         const bool small = oneLaunch || h->geom[l].fastBoxH <= FAST_SMALL_ROWS;
@@ -514,7 +502,7 @@ static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
         const int warpBytes = (tileStride + scoreStride + 2 * listCap + 2 * FAST_QCAP + 16 + 127) & ~127;
         const size_t smem = (size_t)warpBytes * FAST_WARPS;
         dim3 grid((cellEnd - cell0 + FAST_WARPS - 1) / FAST_WARPS, batch);
-        cudaStream_t st = (side >= 0 && nLaunch > 0) ? h->sSide[side] : h->cur;
+        cudaStream_t st = (sideStream && nLaunch > 0) ? sideStream : h->cur;
         ++nLaunch;
 #define ORBFE_FAST_WLAUNCH(TPC)                                                                                                  \
         do {                                                                                                                     \
@@ -531,18 +519,33 @@ static cudaError_t launch_fast_warp(orbfe_handle* h, int frame0, int batch) {
 #undef ORBFE_FAST_WLAUNCH
         h->launches++;
     }
-    if (side >= 0) {                               // join (also when nothing went to the side stream: a capture must not end forked)
-        cudaError_t ej = cudaEventRecord(h->evBlur[side], h->sSide[side]);
-        if (ej == cudaSuccess) ej = cudaStreamWaitEvent(h->cur, h->evBlur[side], 0);
-        if (ej != cudaSuccess) return ej;
-    }
     return cudaGetLastError();
 }
 
-cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch) {
-    cudaError_t e = cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->cur);
-    if (e != cudaSuccess) return e;
-    if (FAST_WARP) return launch_fast_warp(h, frame0, batch);
+// ORBFE_FAST_SIDE (read once): 0 = every launch in line on the compute stream; 1 = FAST's launches after the first (the tall-cell
+// class) on the side stream, under the main launch; 2 = the pyramid levels only those cells read go there too.
+int orbfe_fast_side_mode() {
+    static const int mode = [] { const char* e = getenv("ORBFE_FAST_SIDE"); return e ? atoi(e) : FAST_SIDE; }();
+    return FAST_WARP ? mode : 0;
+}
+
+// First level of the trailing run of tall-cell levels that k_fast_warp launches separately; nlevels when there is no such run
+// (one launch for everything, or no tall class at the end).
+int orbfe_fast_tall_from(const orbfe_handle* h, int batch) {
+    const int nl = h->p.nlevels;
+    if (!FAST_WARP || (long long)h->nCellsTotal * batch <= 24LL * h->smCount) return nl;
+    int l = nl;
+    while (l > 0 && h->geom[l - 1].fastBoxH > FAST_SMALL_ROWS) --l;
+    return l > 0 ? l : nl;
+}
+
+cudaError_t orbfe_clear_candidates(orbfe_handle* h, int frame0, int batch) {
+    return cudaMemsetAsync(h->dCandCount + (size_t)frame0 * h->p.nlevels, 0, sizeof(int) * (size_t)batch * h->p.nlevels, h->cur);
+}
+
+// The candidate counters must have been cleared (orbfe_clear_candidates) on a stream both h->cur and sideStream are ordered after.
+cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch, cudaStream_t sideStream) {
+    if (FAST_WARP) return launch_fast_warp(h, frame0, batch, sideStream);
     const int tileBytes = h->fastBoxW * h->fastBoxH;
     const size_t tileStride = ((size_t)tileBytes + 127) & ~(size_t)127;
     // maxCellBytes counts two unpadded maps; FAST_PAD re-pitches both to 68 bytes and 128-byte-aligns them

@@ -279,41 +279,46 @@ __global__ void __launch_bounds__(PYRTMA_THREADS, PYRTMA_MINB) k_pyr_resize_tma(
     }
 }
 
-cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int width, int height,
-                                 long long stride, long long frameStride) {
-    (void)width; (void)height;
-    const int nl = h->p.nlevels;
-    {
+// Levels [lFirst, lEnd) on stream st (level l needs level l - 1: the caller orders the streams).
+cudaError_t orbfe_launch_pyramid_levels(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, long long stride,
+                                        long long frameStride, int lFirst, int lEnd, cudaStream_t st) {
+    if (lFirst == 0 && lEnd > 0) {
         const LevelGeom& g = h->geom[0];
         if (h->inFormat == ORBFE_FORMAT_GRAY8) {
             dim3 grid(((g.pitch >> 4) + 7) / 8, batch, (g.rows + 32 * PYR_L0_ROWS - 1) / (32 * PYR_L0_ROWS));
-            k_pyr_level0<<<grid, 256, 0, h->cur>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
+            k_pyr_level0<<<grid, 256, 0, st>>>(dImages, stride, frameStride, h->dPyr, g, frame0);
         } else {
             dim3 grid((g.pitch / 4 + 127) / 128, g.rows, batch);
             const int rFirst = h->inFormat == ORBFE_FORMAT_RGB8 || h->inFormat == ORBFE_FORMAT_RGBA8;
             if (h->inFormat <= ORBFE_FORMAT_BGR8)
-                k_pyr_level0_color<3><<<grid, 128, 0, h->cur>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
+                k_pyr_level0_color<3><<<grid, 128, 0, st>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
             else
-                k_pyr_level0_color<4><<<grid, 128, 0, h->cur>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
+                k_pyr_level0_color<4><<<grid, 128, 0, st>>>(dImages, stride, frameStride, h->dPyr, g, frame0, rFirst);
         }
         h->launches++;
     }
-    for (int l = 1; l < nl; ++l) {
+    for (int l = lFirst > 1 ? lFirst : 1; l < lEnd; ++l) {
         const LevelGeom& gd = h->geom[l];
         if (gd.planBase >= 0 && h->pyrUseTma && h->pyrTma.lv[l].ok) {
             const PyrTmaLevel& L = h->pyrTma.lv[l];
             const size_t smem = (size_t)L.boxWords * 4 * L.boxH;
             dim3 grid(L.tilesX, L.groupsY, batch);
-            k_pyr_resize_tma<<<grid, PYRTMA_THREADS, smem, h->cur>>>(h->pyrMaps, h->dPyr, gd, h->dTaps, h->dPlans, h->dPyrTma, l, frame0);
+            k_pyr_resize_tma<<<grid, PYRTMA_THREADS, smem, st>>>(h->pyrMaps, h->dPyr, gd, h->dTaps, h->dPlans, h->dPyrTma, l, frame0);
         } else if (gd.planBase >= 0) {
             const int tilesX = gd.pitch / 128, total = tilesX * ((gd.rows + PYR_TH - 1) / PYR_TH);
             dim3 grid((total + 3) / 4, batch);
-            k_pyr_resize_plan<<<grid, 128, 0, h->cur>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total, frame0);
+            k_pyr_resize_plan<<<grid, 128, 0, st>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, h->dPlans, tilesX, total, frame0);
         } else {   // scale factors whose 2-column source window exceeds 8 bytes: generic kernel
             dim3 grid((gd.pitch / 4 + 127) / 128, gd.rows, batch);
-            k_pyr_resize<<<grid, 128, 0, h->cur>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, frame0);
+            k_pyr_resize<<<grid, 128, 0, st>>>(h->dPyr, h->geom[l - 1], gd, h->dTaps, frame0);
         }
         h->launches++;
     }
     return cudaGetLastError();
+}
+
+cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int width, int height,
+                                 long long stride, long long frameStride) {
+    (void)width; (void)height;
+    return orbfe_launch_pyramid_levels(h, dImages, frame0, batch, stride, frameStride, 0, h->p.nlevels, h->cur);
 }

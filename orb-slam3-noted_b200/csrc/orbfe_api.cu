@@ -606,8 +606,22 @@ static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int frame0, 
         ev = h->profEv[(h->profHead + h->profCount) % ORBFE_PROF_RING];
         CK(cudaEventRecord(ev[0], h->cur));
     }
-    if ((e = orbfe_launch_pyramid(h, dImages, frame0, batch, W, H, stride, frameStride)) != cudaSuccess) return cuda_fail(e, "pyramid");
+    // FAST's few tall cells (the coarsest levels) are a second, small launch: it goes to the side stream and runs under the main
+    // launch, and (mode 2) so do the resizes that produce the levels only those cells read.
+    const int nl = h->p.nlevels, sideMode = orbfe_fast_side_mode();
+    int fside = -1, tallFrom = nl;
+    if (sideMode && !h->profiling && !h->blurOverlap && (tallFrom = orbfe_fast_tall_from(h, batch)) < nl)
+        for (int i = 0; i < ORBFE_MAX_COMPUTE_STREAMS; ++i)
+            if (h->sComp[i] == h->cur) fside = i;
+    const int pyrOnCur = (fside >= 0 && sideMode >= 2) ? tallFrom : nl;
+    if ((e = orbfe_launch_pyramid_levels(h, dImages, frame0, batch, stride, frameStride, 0, pyrOnCur, h->cur)) != cudaSuccess) return cuda_fail(e, "pyramid");
     if (ev) CK(cudaEventRecord(ev[1], h->cur));
+    if ((e = orbfe_clear_candidates(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "fast");
+    if (fside >= 0) {
+        CK(cudaEventRecord(h->evPyr[fside], h->cur));
+        CK(cudaStreamWaitEvent(h->sSide[fside], h->evPyr[fside], 0));
+        if ((e = orbfe_launch_pyramid_levels(h, dImages, frame0, batch, stride, frameStride, pyrOnCur, nl, h->sSide[fside])) != cudaSuccess) return cuda_fail(e, "pyramid");
+    }
     // The blur needs the pyramid and nothing else, FAST + quadtree + assemble do not need the blur: it goes to a side stream
     // (forked from and joined back into h->cur, so a capture sees one graph) as a few RESIDENT CTAs per SM that walk the
     // tiles - FAST is latency-bound at two thirds of the issue slots and leaves registers free, the blur is pure ALU work.
@@ -621,7 +635,11 @@ static int enqueue_extract(orbfe_handle* h, const uint8_t* dImages, int frame0, 
         if ((e = orbfe_launch_blur(h, frame0, batch, h->sSide[side], h->blurPersist)) != cudaSuccess) return cuda_fail(e, "blur");
         CK(cudaEventRecord(h->evBlur[side], h->sSide[side]));
     }
-    if ((e = orbfe_launch_fast(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "fast");
+    if ((e = orbfe_launch_fast(h, frame0, batch, fside >= 0 ? h->sSide[fside] : nullptr)) != cudaSuccess) return cuda_fail(e, "fast");
+    if (fside >= 0) {
+        CK(cudaEventRecord(h->evBlur[fside], h->sSide[fside]));
+        CK(cudaStreamWaitEvent(h->cur, h->evBlur[fside], 0));
+    }
     if (ev) CK(cudaEventRecord(ev[2], h->cur));
     if ((e = orbfe_launch_octree(h, frame0, batch)) != cudaSuccess) return cuda_fail(e, "octree");
     if (ev) CK(cudaEventRecord(ev[3], h->cur));

@@ -196,7 +196,12 @@ cudaError_t orbfe_ensure_dyn_smem(const void* func, size_t bytes);
 // the host and device paths); dImages points at the first of those frames.
 cudaError_t orbfe_launch_pyramid(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, int width, int height,
                                  long long stride, long long frameStride);
-cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch);
+cudaError_t orbfe_launch_pyramid_levels(orbfe_handle* h, const uint8_t* dImages, int frame0, int batch, long long stride,
+                                        long long frameStride, int lFirst, int lEnd, cudaStream_t st);
+int orbfe_fast_side_mode();
+int orbfe_fast_tall_from(const orbfe_handle* h, int batch);
+cudaError_t orbfe_clear_candidates(orbfe_handle* h, int frame0, int batch);
+cudaError_t orbfe_launch_fast(orbfe_handle* h, int frame0, int batch, cudaStream_t sideStream);
 cudaError_t orbfe_launch_octree(orbfe_handle* h, int frame0, int batch);
 cudaError_t orbfe_launch_assemble(orbfe_handle* h, int frame0, int batch, int lap0, int lap1);
 cudaError_t orbfe_launch_blur(orbfe_handle* h, int frame0, int batch, cudaStream_t st, int persistPerSm);

@@ -263,9 +263,10 @@ def test_fast_corner_list_overflow_path():
 
 @pytest.mark.parametrize("env", [{"ORBFE_PYR_TMA": "0"}, {"ORBFE_BLUR_OVERLAP": "1", "ORBFE_BLUR_PERSIST": "2"},
                                  {"ORBFE_BLUR": "tensor"}, {"ORBFE_GRAPHS": "0", "ORBFE_DEV_CHUNK": "2", "ORBFE_DEV_STREAMS": "3"},
-                                 {"ORBFE_FAST_SIDE": "0", "ORBFE_TEST_FRAMES": "8"}, {"ORBFE_FAST_SIDE": "1", "ORBFE_TEST_FRAMES": "8"}],
+                                 {"ORBFE_FAST_SIDE": "0", "ORBFE_TEST_FRAMES": "8"}, {"ORBFE_FAST_SIDE": "1", "ORBFE_TEST_FRAMES": "8"},
+                                 {"ORBFE_FAST_SIDE": "2", "ORBFE_TEST_FRAMES": "8"}],
                          ids=["resize_through_L1", "blur_on_side_stream", "tensor_blur", "chunked_no_graphs", "fast_in_line",
-                              "fast_tall_cells_on_side_stream"])
+                              "fast_tall_cells_on_side_stream", "fast_tall_cells_and_their_levels_on_side_stream"])
 def test_selectable_paths_give_the_same_result(env):
     """The kernels and schedules that are not the default (read-once environment knobs) against the oracle: the L1 form of the
     resize, the blur on a side stream with resident CTAs, the tensor-core blur, eager chunked launches on three streams, FAST's

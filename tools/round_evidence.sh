@@ -30,6 +30,7 @@ ncu -i $out/${tag}_extract.ncu-rep --page raw --csv > $out/${tag}_extract_raw.cs
 python tools/summarize_ncu_full.py $out/${tag}_extract_raw.csv $out/${tag}_extract_summary.json > $out/${tag}_extract_summary.txt 2>&1
 cat $out/${tag}_extract_summary.txt
 
+[ "$2" = noknn2 ] && exit 0     # the matching kernels did not change since the last capture
 timeout 1200 ncu --set full --clock-control none --import-source on \
     -k regex:'k_knn2' --launch-skip 6 --launch-count 4 \
     -f -o $out/${tag}_knn2 python bench.py --steps 1 --warmup 3 --no-cpu --no-legs > $out/${tag}_ncu_knn2.log 2>&1
