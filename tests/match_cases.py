@@ -173,6 +173,15 @@ TRI_KB8_CASES = {
 }
 
 
+# more keyframe pairs for the runs against the reference's matcher + camera classes (no golden files: reference vs oracle vs GPU)
+TRI_KB8_EXTRA = {
+    "tri_kb8_dual_sideways": (2210, 1200, True, True, False, (-0.30, 0.05, 0.02)),
+    "tri_kb8_mono_forward": (2211, 1000, False, True, False, (0.02, -0.01, 0.35)),
+    "tri_kb8_dual_no_ori": (2212, 800, True, False, False, (0.12, 0.10, -0.08)),
+    "tri_kb8_mono_coarse": (2213, 900, False, True, True, (0.25, 0.0, 0.0)),
+}
+
+
 def _rot(rx, ry, rz):
     cx, sx, cy, sy, cz, sz = np.cos(rx), np.sin(rx), np.cos(ry), np.sin(ry), np.cos(rz), np.sin(rz)
     Rx = np.array([[1, 0, 0], [0, cx, -sx], [0, sx, cx]])
@@ -186,7 +195,7 @@ def tri_kb8_inputs(name):
     [left-camera features..., right-camera features...] (KeyFrame::NLeft splits them); every observation of
     a point carries the point's descriptor with a few bits flipped outside bytes 0-1 (which define the
     stand-in vocabulary node), pixel noise, and 6 % gross outliers so the geometric test rejects some."""
-    seed, n, dual, ori, coarse, trans = TRI_KB8_CASES[name]
+    seed, n, dual, ori, coarse, trans = (TRI_KB8_CASES.get(name) or TRI_KB8_EXTRA[name])
     rng = np.random.default_rng(seed)
     nlev = 8
     snap = lambda a: (np.round(a * 16) / 16).astype(np.float32)

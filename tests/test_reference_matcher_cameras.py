@@ -22,7 +22,7 @@ def _sides(c, s2, sc, cam1, cam2, ur1=None, ur2=None):
     return A, B
 
 
-@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES))
+@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES) + list(mc.TRI_KB8_EXTRA))
 def test_triangulation_search_on_the_real_kannala_brandt_camera(name):
     """Rows whose candidate pairs all sit > 1e-3 (relative) away from every threshold of the triangulation test must be identical:
     the reference multiplies the poses in float32 and ends in cv::SVD, the oracle receives float32 R12 / t12 computed in double."""

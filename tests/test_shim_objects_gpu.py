@@ -129,7 +129,7 @@ cam_libs = pytest.mark.skipif(not (ob.ref_matcher_cam_available() and ob.shim_ma
 
 
 @cam_libs
-@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES))
+@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES) + list(mc.TRI_KB8_EXTRA))
 def test_search_for_triangulation_objects_kannala_brandt(name):
     """SearchForTriangulation_ on keyframes that hold real KannalaBrandt8 objects: the shim reads GetType() / getParameter(), forms the
     relative poses of the four camera pairings from the keyframes' poses and runs orbfe_search_triangulation_kb8; the reference
