@@ -207,6 +207,9 @@ namespace {
 __device__ __forceinline__ uint32_t pyr_s32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 }
 #define PYRTMA_THREADS (ORBFE_PYRTMA_ROWS / PYR_TH * 32)
+#ifndef PYRTMA_TAPS_SMEM
+#define PYRTMA_TAPS_SMEM 1   // measured (profiles/r06b_variants.txt): pyramid 0.550 -> 0.504 ms per 512 frames, 201.7 -> 205.3 k frames/s
+#endif
 #ifndef PYRTMA_MINB
 #define PYRTMA_MINB 1
 #endif
@@ -231,6 +234,25 @@ __global__ void __launch_bounds__(PYRTMA_THREADS, PYRTMA_MINB) k_pyr_resize_tma(
     const int word = tx * 32 + lane;
     const ColPlan cp = plans[gd.planBase + word];
     const int row0 = ty * ORBFE_PYRTMA_ROWS + warp * PYR_TH, row1 = min(row0 + PYR_TH, gd.rows);
+#if PYRTMA_TAPS_SMEM
+    // The row's two source offsets and two weights come from shared memory as ONE broadcast 128-bit load instead of four shuffles
+    // (the kernel sits at 80 % of the shared-memory / L1 wavefront rate: 8 loads + 4 shuffles + 1 store per row), and the
+    // offsets are in bytes so that a load address is one add.
+    __shared__ __align__(16) uint4 rowTaps[PYRTMA_THREADS / 32][PYR_TH];
+    if (lane < PYR_TH) {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (row0 + lane < row1) {
+            const ResizeTap t = taps[gd.tabY + reflect101(row0 + lane - ORBFE_EDGE, gd.h)];
+            v.x = (unsigned)(t.s0 - rowLo) * (unsigned)boxWords * 4u; v.y = (unsigned)(t.s1 - rowLo) * (unsigned)boxWords * 4u;
+            v.z = (uint32_t)t.a0 << 16; v.w = (uint32_t)t.a1 << 16;
+        }
+        rowTaps[warp][lane] = v;
+    }
+    const unsigned b01 = (unsigned)(cp.base01 - colLo) * 4u, b23 = (unsigned)(cp.base23 - colLo) * 4u;
+    const uint8_t* S = tileBytes;
+#define PYRTMA_LD(off) (*reinterpret_cast<const uint32_t*>(S + (off)))
+#define PYRTMA_LD1(off) (*reinterpret_cast<const uint32_t*>(S + (off) + 4))
+#else
     unsigned myOff0 = 0, myOff1 = 0;
     uint32_t myA0 = 0, myA1 = 0;
     if (lane < PYR_TH && row0 + lane < row1) {
@@ -240,10 +262,13 @@ __global__ void __launch_bounds__(PYRTMA_THREADS, PYRTMA_MINB) k_pyr_resize_tma(
     }
     const unsigned b01 = (unsigned)(cp.base01 - colLo), b23 = (unsigned)(cp.base23 - colLo);
     const uint32_t* S = reinterpret_cast<const uint32_t*>(tileBytes);
+#define PYRTMA_LD(off) S[off]
+#define PYRTMA_LD1(off) S[(off) + 1]
+#endif
     uint32_t* dst = reinterpret_cast<uint32_t*>(pyr + gd.base + (long long)frame * gd.plane);
     const unsigned dpw = (unsigned)(gd.pitch >> 2);
     unsigned doff = (unsigned)row0 * dpw + (unsigned)word;
-    __syncthreads();                   // the barrier is initialised before anyone polls it
+    __syncthreads();                   // the barrier is initialised (and the row taps are written) before anyone goes on
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
@@ -259,12 +284,18 @@ __global__ void __launch_bounds__(PYRTMA_THREADS, PYRTMA_MINB) k_pyr_resize_tma(
 #pragma unroll 4
     for (int row = row0; row < row1; ++row) {
         const int j = row - row0;
+#if PYRTMA_TAPS_SMEM
+        const uint4 rt = rowTaps[warp][j];
+        const unsigned o0 = rt.x, o1 = rt.y;
+        const uint32_t a0s = rt.z, a1s = rt.w;
+#else
         const unsigned o0 = __shfl_sync(0xffffffffu, myOff0, j), o1 = __shfl_sync(0xffffffffu, myOff1, j);
         const uint32_t a0s = __shfl_sync(0xffffffffu, myA0, j), a1s = __shfl_sync(0xffffffffu, myA1, j);
-        const uint32_t p0a = __byte_perm(S[o0 + b01], S[o0 + b01 + 1], cp.sel & 0xFFFF);
-        const uint32_t p0b = __byte_perm(S[o0 + b23], S[o0 + b23 + 1], cp.sel >> 16);
-        const uint32_t p1a = __byte_perm(S[o1 + b01], S[o1 + b01 + 1], cp.sel & 0xFFFF);
-        const uint32_t p1b = __byte_perm(S[o1 + b23], S[o1 + b23 + 1], cp.sel >> 16);
+#endif
+        const uint32_t p0a = __byte_perm(PYRTMA_LD(o0 + b01), PYRTMA_LD1(o0 + b01), cp.sel & 0xFFFF);
+        const uint32_t p0b = __byte_perm(PYRTMA_LD(o0 + b23), PYRTMA_LD1(o0 + b23), cp.sel >> 16);
+        const uint32_t p1a = __byte_perm(PYRTMA_LD(o1 + b01), PYRTMA_LD1(o1 + b01), cp.sel & 0xFFFF);
+        const uint32_t p1b = __byte_perm(PYRTMA_LD(o1 + b23), PYRTMA_LD1(o1 + b23), cp.sel >> 16);
         int r0[4], r1[4];
         r0[0] = __dp2a_lo(cp.a[0], p0a, 0u); r0[1] = __dp2a_hi(cp.a[1], p0a, 0u);
         r0[2] = __dp2a_lo(cp.a[2], p0b, 0u); r0[3] = __dp2a_hi(cp.a[3], p0b, 0u);
@@ -277,6 +308,8 @@ __global__ void __launch_bounds__(PYRTMA_THREADS, PYRTMA_MINB) k_pyr_resize_tma(
         dst[doff] = v & cp.keep;
         doff += dpw;
     }
+#undef PYRTMA_LD
+#undef PYRTMA_LD1
 }
 
 // Levels [lFirst, lEnd) on stream st (level l needs level l - 1: the caller orders the streams).
