@@ -139,6 +139,122 @@ def cpu_frames_per_s(frames, nthreads, budget_s, extract_many=None):
     return reps * n / dt, reps * n
 
 
+def cpu_opencv_crosscheck(frames, orb_params, budget_s=3.0):
+    """the OpenCV calls one reference frame makes (7 resize + 8 copyMakeBorder, one FAST per 35-px cell with
+    the retry, 8 GaussianBlur), timed on ONE thread through cv2 (OpenCV's SIMD kernels, plus Python call overhead) and through
+    the scalar restatement the timed CPU arm links (oracle/cpu_ref/cvprim.cc), same frames, same calls.  Says how much of the
+    CPU arm's frame time is primitives and how much faster a build against the real OpenCV would run them.  None when cv2 is
+    not importable."""
+    try:
+        import cv2
+    except Exception:
+        return None
+    import ctypes as C
+    import math
+    import numpy as np
+    L = _oracle().lib()
+    P, I, LG = C.c_void_p, C.c_int, C.c_long
+    L.orbref_resize.argtypes = [P, I, I, LG, P, I, I, LG]
+    L.orbref_border101.argtypes = [P, I, I, I, LG]
+    L.orbref_fast.argtypes = [P, I, I, LG, I, P, I]
+    L.orbref_blur.argtypes = [P, I, I, LG, P, LG]
+    nfeatures, sf, nlevels, ini_th, min_th = orb_params
+    E = 19
+    inv = [np.float32(1.0)]
+    scale = [np.float32(1.0)]
+    for _ in range(1, nlevels):
+        scale.append(np.float32(scale[-1] * np.float32(sf)))
+        inv.append(np.float32(np.float32(1.0) / scale[-1]))
+    H0, W0 = frames[0].shape
+    sizes = [(int(np.rint(np.float32(W0) * inv[l])), int(np.rint(np.float32(H0) * inv[l]))) for l in range(nlevels)]
+    old_threads = cv2.getNumThreads()
+    cv2.setNumThreads(1)
+    det_ini, det_min = cv2.FastFeatureDetector_create(ini_th, True), cv2.FastFeatureDetector_create(min_th, True)
+    xys = np.zeros(3 * 4096, np.int32)
+    ptr = lambda a: a.ctypes.data_as(P)
+
+    def cells(w, h):
+        minB, maxBX, maxBY = E - 3, w - E + 3, h - E + 3
+        ncols, nrows = int((maxBX - minB) / 35), int((maxBY - minB) / 35)
+        wc, hc = int(math.ceil((maxBX - minB) / ncols)), int(math.ceil((maxBY - minB) / nrows))
+        for i in range(nrows):
+            y0 = minB + i * hc
+            if y0 >= maxBY - 3:
+                continue
+            y1 = min(y0 + hc + 6, maxBY)
+            for j in range(ncols):
+                x0 = minB + j * wc
+                if x0 >= maxBX - 6:
+                    continue
+                yield x0, y0, min(x0 + wc + 6, maxBX), y1
+
+    grids = [list(cells(w, h)) for (w, h) in sizes]
+
+    def frame_cv2(img):
+        pyr = [cv2.copyMakeBorder(img, E, E, E, E, cv2.BORDER_REFLECT_101)]
+        for l in range(1, nlevels):
+            pw, ph = sizes[l - 1]
+            lvl = cv2.resize(pyr[-1][E:E + ph, E:E + pw], sizes[l], interpolation=cv2.INTER_LINEAR)
+            pyr.append(cv2.copyMakeBorder(lvl, E, E, E, E, cv2.BORDER_REFLECT_101))
+        n = 0
+        for l in range(nlevels):
+            for (x0, y0, x1, y1) in grids[l]:
+                cell = np.ascontiguousarray(pyr[l][E + y0:E + y1, E + x0:E + x1])
+                k = det_ini.detect(cell)
+                if not k:
+                    k = det_min.detect(cell)
+                n += len(k)
+        for l in range(nlevels):
+            w, h = sizes[l]
+            cv2.GaussianBlur(pyr[l][E:E + h, E:E + w].copy(), (7, 7), 2, sigmaY=2, borderType=cv2.BORDER_REFLECT_101)
+        return n
+
+    def frame_scalar(img):
+        bufs = []
+        for l in range(nlevels):
+            w, h = sizes[l]
+            b = np.empty((h + 2 * E, w + 2 * E), np.uint8)
+            if l == 0:
+                b[E:E + h, E:E + w] = img
+            else:
+                pw, ph = sizes[l - 1]
+                src = bufs[-1]
+                L.orbref_resize(ptr(src[E:, E:]), pw, ph, src.strides[0], ptr(b[E:, E:]), w, h, b.strides[0])
+            L.orbref_border101(ptr(b), w, h, E, b.strides[0])
+            bufs.append(b)
+        n = 0
+        for l in range(nlevels):
+            b = bufs[l]
+            for (x0, y0, x1, y1) in grids[l]:
+                c = b[E + y0:, E + x0:]
+                k = L.orbref_fast(ptr(c), x1 - x0, y1 - y0, b.strides[0], ini_th, ptr(xys), 4096)
+                if k == 0:
+                    k = L.orbref_fast(ptr(c), x1 - x0, y1 - y0, b.strides[0], min_th, ptr(xys), 4096)
+                n += k
+        for l in range(nlevels):
+            w, h = sizes[l]
+            out = np.empty((h, w), np.uint8)
+            L.orbref_blur(ptr(bufs[l][E:, E:]), w, h, bufs[l].strides[0], ptr(out), w)
+        return n
+
+    res = {}
+    counts = {}
+    for name, fn in (("cv2", frame_cv2), ("scalar", frame_scalar)):
+        counts[name] = fn(frames[0])                       # warm-up
+        t0, done = time.perf_counter(), 0
+        while done < len(frames) and time.perf_counter() - t0 < budget_s / 2:
+            fn(frames[done])
+            done += 1
+        res[name] = 1e3 * (time.perf_counter() - t0) / max(done, 1)
+    cv2.setNumThreads(old_threads)
+    return {"opencv_version": cv2.__version__, "threads": 1, "calls_per_frame": {"resize": nlevels - 1, "copyMakeBorder": nlevels,
+                                                                              "FAST": sum(len(g) for g in grids), "GaussianBlur": nlevels},
+            "cv2_ms_per_frame": res["cv2"], "scalar_restatement_ms_per_frame": res["scalar"],
+            "fast_candidates_first_frame": counts,
+            "note": "primitive calls only (no quadtree, orientation, descriptors); the cv2 figure includes the Python call overhead "
+                    "of every cv2 call, the scalar figure that of ctypes"}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -159,6 +275,10 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     v = args.steps * per_step / dt
     sample = f"{per_step} frames per step x {args.steps} steps, frame-parallel over {cores} host threads"
+    try:                                  # outside the timed region: the OpenCV-SIMD cross-check of the primitive calls
+        xc = cpu_opencv_crosscheck(frames[:16], ORB_PARAMS, 3.0)
+    except Exception as exc:
+        xc = {"error": repr(exc)}
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -166,7 +286,7 @@ def run_reference(args):
         "config": {"workload": WORKLOAD, "lapping": list(LAPPING)},
         "config_detail": {"frames_per_step": per_step, "note": what, "primitives": CPU_PRIMITIVES},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample,
-                         "primitives": CPU_PRIMITIVES},
+                         "primitives": CPU_PRIMITIVES, "opencv_crosscheck": xc},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -702,6 +822,18 @@ def run_orbfe(args):
         v2, _ = cpu_frames_per_s(frames[:16], 2, 1.0)
         out["cpu_baseline"]["single_thread_ms_per_frame"] = 1e3 / v1
         out["cpu_baseline"]["two_thread_stereo_pairs_per_s"] = v2 / 2
+        # the same primitive calls through cv2 (OpenCV's SIMD kernels) and through the scalar restatement
+        try:
+            xc = cpu_opencv_crosscheck(frames[:16], ORB_PARAMS, 3.0)
+        except Exception as exc:          # a cross-check must not cost the bench line
+            xc = {"error": repr(exc)}
+        if xc is not None:
+            if "cv2_ms_per_frame" in xc:
+                t1 = 1e3 / v1
+                xc["single_thread_ms_per_frame_with_opencv_simd_estimated"] = t1 - xc["scalar_restatement_ms_per_frame"] + xc["cv2_ms_per_frame"]
+                xc["estimate_note"] = ("the timed arm's single-thread frame time with its scalar primitive calls replaced by the cv2 time of "
+                                       "the same calls: what a build of the reference against the real OpenCV would take, to first order")
+            out["cpu_baseline"]["opencv_crosscheck"] = xc
     if matching is not None:
         out["matching"] = matching
     if bow is not None:

@@ -153,3 +153,20 @@ def test_undistort_keypoints_equals_cv2(ci):
     assert np.array_equal(out["x"], want[:, 0]) and np.array_equal(out["y"], want[:, 1])
     assert np.array_equal(out["octave"], k["octave"]) and np.array_equal(out["angle"], k["angle"])
     assert np.abs(out["x"] - k["x"]).max() > 1.0
+
+
+def test_bench_opencv_crosscheck_runs_the_same_calls_both_ways():
+    """bench.py's cpu_baseline.opencv_crosscheck: the primitive calls of one reference frame through cv2 and
+    through the scalar restatement.  The two FAST cell loops must find the same number of candidates (they run the same calls)."""
+    import importlib.util
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("orbfe_bench_for_test", os.path.join(root, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    frames = orbfe.synth.frames(1000, 3, bench.W, bench.H)
+    threads = cv2.getNumThreads()
+    r = bench.cpu_opencv_crosscheck(frames, bench.ORB_PARAMS, budget_s=0.5)
+    assert cv2.getNumThreads() == threads                      # restored
+    assert r["calls_per_frame"] == {"resize": 7, "copyMakeBorder": 8, "FAST": 700, "GaussianBlur": 8}
+    assert r["fast_candidates_first_frame"]["cv2"] == r["fast_candidates_first_frame"]["scalar"] > 2000
+    assert r["cv2_ms_per_frame"] > 0 and r["scalar_restatement_ms_per_frame"] > 0
