@@ -26,6 +26,7 @@ namespace ORB_SLAM3 {
 class MapPoint;
 class GeometricCamera;
 class Frame;
+class KeyFrame;
 
 namespace IMU {                  // ImuTypes.h: the three types Frame.h holds by value or by pointer
 class Bias {
@@ -70,8 +71,20 @@ public:
     std::vector<MapPoint*> erased;
     unsigned long GetId() { return mnId; }
     void EraseMapPoint(MapPoint* p) { erased.push_back(p); }
+    // what KeyFrame.cc touches (liborbslam3_objects.so)
+    std::vector<KeyFrame*> erasedKeyFrames;
+    bool isImuInitialized() { return false; }
+    unsigned long GetInitKFid() { return 0; }
+    void EraseKeyFrame(KeyFrame* p) { erasedKeyFrames.push_back(p); }
 };
 
+class KeyFrameDatabase {         // KeyFrameDatabase.h: KeyFrame::SetBadFlag erases itself from it
+public:
+    std::vector<KeyFrame*> erased;
+    void erase(KeyFrame* p) { erased.push_back(p); }
+};
+
+#ifndef ORBSLAM3_REAL_KEYFRAME
 class KeyFrame {                 // KeyFrame.h members read by MapPoint.cc (Frame.cc only passes the pointer around)
 public:
     long unsigned int mnId = 0, mnFrameId = 0;
@@ -92,5 +105,7 @@ public:
     cv::Mat GetCameraCenter() { return Ow.clone(); }
     cv::Mat GetRightCameraCenter() { return OwRight.clone(); }
 };
+
+#endif  // ORBSLAM3_REAL_KEYFRAME (liborbslam3_keyframe.so compiles the reference's own KeyFrame.h / KeyFrame.cc instead)
 
 }  // namespace ORB_SLAM3

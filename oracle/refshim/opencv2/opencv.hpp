@@ -72,6 +72,10 @@ struct KeyPoint {          // 28 bytes, the layout of cv::KeyPoint
 };
 static_assert(sizeof(KeyPoint) == 28, "cv::KeyPoint layout");
 
+struct Scalar {               // what KeyFrame.cc names: cv::Scalar(0.0f) as a fill value
+    double val[4];
+    Scalar(double v0 = 0, double v1 = 0, double v2 = 0, double v3 = 0) : val{v0, v1, v2, v3} {}
+};
 class Mat;
 class MatExpr;
 class _OutputArray;
@@ -85,6 +89,14 @@ public:
     Mat() {}
     Mat(int r, int c, int type) { create(r, c, type); }
     Mat(Size s, int type) { create(s.height, s.width, type); }
+    Mat(int r, int c, int type, const Scalar& v) {
+        create(r, c, type);
+        for (int i = 0; i < r; ++i)
+            for (int j = 0; j < c; ++j) {
+                if (type == CV_32F) *reinterpret_cast<float*>(data + (size_t)i * step + 4 * (size_t)j) = (float)v.val[0];
+                else data[(size_t)i * step + j] = (uchar)v.val[0];
+            }
+    }
     // user-allocated data (not owned)
     Mat(int r, int c, int type, void* d, size_t st) : rows(r), cols(c), step(st), data((uchar*)d), esz_(type == CV_32F ? 4 : 1) {
         assert(type == CV_8U || type == CV_32F);

@@ -549,6 +549,57 @@ def ref_search_for_triangulation_cam(fisheye, A, B, nnratio, check_ori, only_ste
     return m12[:a.n], n
 
 
+# ---- the reference's matcher on its OWN Frame / KeyFrame / MapPoint / camera classes (oracle/_ref/liborbslam3_objects.so) ----
+REF_OBJECTS_LIB = os.path.join(os.path.dirname(REF_LIB), "liborbslam3_objects.so")
+_ref_objects = None
+
+
+def ref_objects_available():
+    return os.path.exists(REF_OBJECTS_LIB)
+
+
+def _ref_objects_lib():
+    global _ref_objects
+    if _ref_objects is None:
+        _ref_objects = C.CDLL(REF_OBJECTS_LIB)
+        _ref_objects.orbslam3_objects_search_for_triangulation.argtypes = [_F, _I, _I, _P, _P, _I, _I, _P]
+        _ref_objects.orbslam3_objects_search_by_bow_kf_kf.argtypes = [_F, _I, _P, _P, _P]
+    return _ref_objects
+
+
+def _kf_arrays(d, keep):
+    f = lambda a: np.ascontiguousarray(a, np.float32)
+    arrs = dict(kps=np.ascontiguousarray(d["kps"]), desc=np.ascontiguousarray(d["desc"], np.uint8),
+                hasMp=np.ascontiguousarray(d["mp"]).astype(np.uint8),
+                uRight=None if d.get("u_right") is None else f(d["u_right"]), nodes=np.ascontiguousarray(d["fv"].node_ids),
+                off=np.ascontiguousarray(d["fv"].offsets), idx=np.ascontiguousarray(d["fv"].indices), sigma2=f(d["sigma2"]),
+                scale=f(d["scale"]), cam=f(d["cam"]), Tcw=f(d["Tcw"]), Trl=f(d["Trl"]))
+    assert arrs["cam"].size == 16 and arrs["Tcw"].size == 16 and arrs["Trl"].size == 16
+    keep.append(arrs)
+    ptr = {k: (_pn(v) if v is None else _p(v)) for k, v in arrs.items()}
+    return _KfArrays(n=len(arrs["desc"]), nleft=int(d["nleft"]), nnodes=len(arrs["nodes"]), nlevels=len(arrs["sigma2"]), **ptr)
+
+
+def ref_objects_search_for_triangulation(fisheye, A, B, nnratio, check_ori, only_stereo, coarse):
+    """SearchForTriangulation_ of the reference on two KeyFrames made by the reference's own KeyFrame(Frame&, Map*, KeyFrameDatabase*)
+    from reference Frames; cameras are the reference's classes.  A, B as for ref_search_for_triangulation_cam."""
+    keep = []
+    a, b = _kf_arrays(A, keep), _kf_arrays(B, keep)
+    m12 = np.zeros(max(a.n, 1), np.int32)
+    n = _ref_objects_lib().orbslam3_objects_search_for_triangulation(float(nnratio), int(check_ori), int(fisheye), C.byref(a), C.byref(b),
+                                                                    int(only_stereo), int(coarse), _p(m12))
+    return m12[:a.n], n
+
+
+def ref_objects_search_by_bow_kf_kf(A, B, nnratio, check_ori):
+    """SearchByBoW(KeyFrame*, KeyFrame*, vpMatches12) on real KeyFrames holding real MapPoints.  Returns (a2b, nmatches)."""
+    keep = []
+    a, b = _kf_arrays(A, keep), _kf_arrays(B, keep)
+    a2b = np.zeros(max(a.n, 1), np.int32)
+    n = _ref_objects_lib().orbslam3_objects_search_by_bow_kf_kf(float(nnratio), int(check_ori), C.byref(a), C.byref(b), _p(a2b))
+    return a2b[:a.n], n
+
+
 # The orbfe shim's ORBmatcher object layer behind the same C entry points (make -C oracle shim): GPU-backed.
 SHIM_MATCHER_LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "cpp", "_build", "liborbfe_shim_orbmatcher.so")
 _shim_matcher = None

@@ -1,0 +1,74 @@
+"""CPU: the reference's matcher on the reference's OWN object model.  oracle/_ref/liborbslam3_objects.so compiles src/ORBmatcher.cc,
+KeyFrame.cc, Frame.cc, MapPoint.cc, ORBextractor.cc and both camera models together, each against its own header; the wrappers fill
+reference Frames, make KeyFrames with the reference's constructor (feature copies, SetPose, mTlr) and real MapPoints, and call the
+matcher.  No data-holder stand-in for Frame / KeyFrame / MapPoint is involved (compare tests/test_reference_orbmatcher.py, where
+oracle/refshim/orbslam3_standin.h supplies those classes)."""
+import numpy as np
+import pytest
+
+import match_cases as mc
+import oracle_binding as ob
+from oracle_binding import OrbRef
+from test_reference_matcher_cameras import _sides
+
+pytestmark = pytest.mark.skipif(not ob.ref_objects_available(), reason="oracle/_ref not built (needs /root/reference; make -C oracle ref)")
+
+
+@pytest.mark.parametrize("name", list(mc.TRI_KB8_CASES) + list(mc.TRI_KB8_EXTRA))
+def test_triangulation_search_on_real_keyframes_kannala_brandt(name):
+    """The keyframe's own pose algebra (KeyFrame::SetPose, GetRightRotation_ / GetRightTranslation_ out of mTlr) feeds the
+    reference's loop and KannalaBrandt8::epipolarConstrain_; rows outside the 1e-3 threshold margin must equal the oracle's."""
+    sc, isc, s2 = OrbRef(1000, *mc.ORB).tables()[:3]
+    c = mc.tri_kb8_inputs(name)
+    A, B = _sides(c, s2, sc, c["cam_a"], c["cam_b"])
+    m12, n = ob.ref_objects_search_for_triangulation(1, A, B, 0.6, c["check_ori"], False, c["coarse"])
+    om12, on, _, mg = ob.search_triangulation_kb8(c["k1"], c["d1"], c["fv1"], c["mp1"], s2, c["k2"], c["d2"], c["fv2"], c["mp2"], s2, sc,
+                                                  c["cam_a"], c["cam_b"], c["nleft_a"], c["nleft_b"], c["R12"], c["t12"], c["ep"],
+                                                  c["check_ori"], False, c["coarse"])
+    assert n == (m12 >= 0).sum() and n > 60
+    safe, differs = mg > 1e-3, m12 != om12
+    if not (c["check_ori"] and (differs & ~safe).any()):
+        assert not (differs & safe).any(), np.flatnonzero(differs & safe)
+        assert n == on or (differs & ~safe).any()
+    else:
+        assert differs.mean() < 0.01
+    # and the stand-in keyframe of liborbslam3_orbmatcher_cam.so gives what the real one gives
+    if ob.ref_matcher_cam_available():
+        sm12, sn = ob.ref_search_for_triangulation_cam(1, A, B, 0.6, c["check_ori"], False, c["coarse"])
+        assert sn == n or (differs & ~safe).any() or (mg <= 1e-3).any()
+        assert (sm12 == m12)[safe].all()
+
+
+@pytest.mark.parametrize("name", [k for k, v in mc.TRI_CASES.items() if v[7] is None])
+def test_triangulation_search_on_real_keyframes_pinhole(name):
+    from test_match_oracle import extract, tables
+    sc, isc, s2, is2, per, umax = tables()
+    c = mc.tri_inputs(name, extract, sc, s2)
+    cam = mc.TRI_CASES[name][0]
+    K = np.zeros((2, 8), np.float32)
+    K[:, :4] = (cam["fx"], cam["fy"], cam["cx"], cam["cy"])
+    c["Tcw1"], c["Tcw2"], c["Trl"] = np.eye(4, dtype=np.float32), np.eye(4, dtype=np.float32), np.eye(4, dtype=np.float32)
+    c["Tcw2"][0, 3] = -0.1
+    A, B = _sides(c, s2, sc, K, K, c["ur1"], c["ur2"])
+    m12, n = ob.ref_objects_search_for_triangulation(0, A, B, 0.6, c["check_ori"], c["only_stereo"], c["coarse"])
+    om12, on = ob.search_triangulation(c["k1"], c["d1"], c["fv1"], c["mp1"], c["ur1"], c["k2"], c["d2"], c["fv2"], c["mp2"], c["ur2"],
+                                       s2, sc, c["F12"], c["ep"], c["check_ori"], c["only_stereo"], c["coarse"])
+    assert n == on and np.array_equal(m12, om12) and n > 20
+
+
+@pytest.mark.parametrize("name", [k for k, v in mc.BOW_CASES.items() if v[5] == -1])
+def test_search_by_bow_between_real_keyframes(name):
+    """SearchByBoW(KeyFrame*, KeyFrame*) with real MapPoints behind GetMapPointMatches(): the matched MapPoint of every pKF1 feature,
+    mapped back to its pKF2 feature index, equals the oracle's."""
+    from test_match_oracle import extract, tables
+    sc, isc, s2, is2, per, umax = tables()
+    c = mc.bow_inputs(name, extract)
+    cam = np.zeros((2, 8), np.float32)
+    cam[:, :4] = (500, 500, 320, 240)
+    eye = np.eye(4, dtype=np.float32)
+    A = dict(kps=c["k1"], desc=c["d1"], fv=c["fv1"], mp=c["mp1"], nleft=-1, u_right=None, sigma2=s2, scale=sc, cam=cam, Tcw=eye, Trl=eye)
+    B = dict(kps=c["k2"], desc=c["d2"], fv=c["fv2"], mp=c["mp2"], nleft=-1, u_right=None, sigma2=s2, scale=sc, cam=cam, Tcw=eye, Trl=eye)
+    a2b, n = ob.ref_objects_search_by_bow_kf_kf(A, B, 0.8, c["check_ori"])
+    oa2b, _, on = ob.search_bow(c["d1"], c["fv1"], c["mp1"], c["k1"]["angle"], c["d2"], c["fv2"], c["mp2"], c["k2"]["angle"], 0.8,
+                                c["check_ori"], strict=True)
+    assert n == on and np.array_equal(a2b, oa2b) and n > 50
