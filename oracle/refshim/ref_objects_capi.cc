@@ -14,12 +14,18 @@
 #include <memory>
 #include <vector>
 
+// the wrappers set state the reference keeps private / protected (Frame::AssignFeaturesToGrid, MapPoint::mDescriptor, mbBad,
+// mWorldPos): access only, class layouts are unchanged
+#define private public
+#define protected public
 #include "ORBmatcher.h"
 #include "KeyFrame.h"
 #include "KeyFrameDatabase.h"
 #include "Map.h"
 #include "Pinhole.h"
 #include "KannalaBrandt8.h"
+#undef private
+#undef protected
 
 #include <cassert>
 #include "../cpu_ref/match_ref.h"
@@ -186,5 +192,299 @@ int orbslam3_objects_search_by_bow_kf_kf(float nnratio, int checkOri, const KfAr
                 if (pts[k].get() == m12[i]) { a2b[i] = featureOfB[k - firstB]; break; }
     }
     return n;
+}
+}
+
+// ---- the per-frame tracking matchers on real Frames and real MapPoints; same C names and argument lists as refshim/ref_matcher_capi.cc
+namespace {
+cv::Mat descRow(const uint8_t* d) {
+    cv::Mat m(1, 32, CV_8U);
+    memcpy(m.data, d, 32);
+    return m;
+}
+cv::Mat vec3(const float* v) {
+    cv::Mat m(3, 1, CV_32F);
+    memcpy(m.data, v, 12);
+    return m;
+}
+// a reference Frame from the arrays of orbfe_grid_frame: features, image bounds (the statics of Frame.cc:158-159), the 64 x 48 grid
+// filled by the reference's own AssignFeaturesToGrid
+void fillRealFrame(Frame& F, GeometricCamera* cam, GeometricCamera* rig, MapPoint* old, const KpPod* kps, const uint8_t* desc, int n, int nleft,
+                   const uint8_t* blocked, const float* uRight, float minX, float minY, float maxX, float maxY, const float* scaleFactors,
+                   int nlevels) {
+    std::vector<cv::KeyPoint> all(n);
+    if (n) memcpy((void*)all.data(), kps, sizeof(KpPod) * (size_t)n);
+    F.N = n; F.Nleft = nleft;
+    cv::Mat d(n > 0 ? n : 1, 32, CV_8U);
+    if (n > 0) memcpy(d.data, desc, 32 * (size_t)n);
+    F.mDescriptors = n > 0 ? d : d.rowRange(0, 0);
+    if (nleft == -1) { F.mvKeysUn = all; F.mvKeys = all; F.Nright = -1; F.mpCamera2 = nullptr; }
+    else {
+        F.mvKeys.assign(all.begin(), all.begin() + nleft); F.mvKeysRight.assign(all.begin() + nleft, all.end());
+        F.mvKeysUn = F.mvKeys; F.mpCamera2 = rig; F.Nright = n - nleft;
+    }
+    F.mpCamera = cam;
+    F.mvuRight.assign(n, -1.f);
+    if (uRight) F.mvuRight.assign(uRight, uRight + n);
+    F.mvDepth.assign(n, -1.f);
+    F.mvScaleFactors.assign(scaleFactors, scaleFactors + nlevels);
+    F.mnScaleLevels = nlevels;
+    Frame::mnMinX = minX; Frame::mnMinY = minY; Frame::mnMaxX = maxX; Frame::mnMaxY = maxY;
+    Frame::mfGridElementWidthInv = static_cast<float>(FRAME_GRID_COLS) / static_cast<float>(maxX - minX);
+    Frame::mfGridElementHeightInv = static_cast<float>(FRAME_GRID_ROWS) / static_cast<float>(maxY - minY);
+    F.AssignFeaturesToGrid();
+    F.mvpMapPoints.assign(n, static_cast<MapPoint*>(nullptr));
+    F.mvbOutlier.assign(n, false);
+    for (int i = 0; i < n; ++i) if (blocked && blocked[i]) F.mvpMapPoints[i] = old;
+}
+}  // namespace
+
+extern "C" {
+// SearchByProjection(Frame& F, const vector<MapPoint*>& vpMapPoints, th, bFarPoints, thFarPoints) (src/ORBmatcher.cc:44-236).
+int orbslam3_search_by_projection_mappoints(float nnratio, const KpPod* kps, const uint8_t* desc, int n, int nleft, const uint8_t* blocked,
+                                            const float* uRight, const int32_t* l2r, const int32_t* r2l, float minX, float minY, float maxX,
+                                            float maxY, const float* scaleFactors, int nlevels, int m, const uint8_t* inView,
+                                            const uint8_t* inViewR, const uint8_t* bad, const float* depth, const float* projX,
+                                            const float* projY, const float* projXR, const float* projYR, const int32_t* level,
+                                            const int32_t* levelR, const float* viewCos, const float* viewCosR, const uint8_t* mpDesc,
+                                            const int32_t* obs, float th, int bFarPoints, float thFarPoints, int32_t* mpOfFeature) {
+    World w;
+    ORBmatcher matcher(nnratio, true);
+    const float intr[8] = {1.f, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    w.cams.emplace_back(makeCamera(0, intr));
+    w.cams.emplace_back(makeCamera(0, intr));
+    MapPoint old;
+    old.nObs = 1;
+    Frame F;
+    fillRealFrame(F, w.cams[0].get(), w.cams[1].get(), &old, kps, desc, n, nleft, blocked, uRight, minX, minY, maxX, maxY, scaleFactors, nlevels);
+    if (nleft != -1) {
+        F.mvLeftToRightMatch.assign(nleft, -1);
+        F.mvRightToLeftMatch.assign(n - nleft, -1);
+        if (l2r) F.mvLeftToRightMatch.assign(l2r, l2r + nleft);
+        if (r2l) F.mvRightToLeftMatch.assign(r2l, r2l + (n - nleft));
+    }
+    std::vector<std::unique_ptr<MapPoint>> mps(m);
+    std::vector<MapPoint*> vp(m);
+    for (int i = 0; i < m; ++i) {
+        mps[i].reset(new MapPoint());
+        MapPoint& p = *mps[i];
+        p.mbTrackInView = inView[i]; p.mbTrackInViewR = inViewR[i]; p.mbBad = bad[i]; p.mTrackDepth = depth[i];
+        p.mTrackProjX = projX[i]; p.mTrackProjY = projY[i]; p.mTrackProjXR = projXR[i]; p.mTrackProjYR = projYR[i];
+        p.mnTrackScaleLevel = level[i]; p.mnTrackScaleLevelR = levelR[i]; p.mTrackViewCos = viewCos[i]; p.mTrackViewCosR = viewCosR[i];
+        p.mDescriptor = descRow(mpDesc + 32 * (size_t)i); p.nObs = obs[i];
+        p.mpReplaced = nullptr;
+        vp[i] = &p;
+    }
+    const int nm = matcher.SearchByProjection(F, vp, th, bFarPoints != 0, thFarPoints);
+    for (int i = 0; i < n; ++i) {
+        mpOfFeature[i] = -1;
+        MapPoint* q = F.mvpMapPoints[i];
+        if (q && q != &old)
+            for (int k = 0; k < m; ++k) if (mps[k].get() == q) { mpOfFeature[i] = k; break; }
+    }
+    return nm;
+}
+
+// SearchByProjection(Frame& CurrentFrame, const Frame& LastFrame, th, bMono) (src/ORBmatcher.cc:2173-2389).
+int orbslam3_search_by_projection_lastframe(int checkOri, const KpPod* kps, const uint8_t* desc, int n, int nleft, const uint8_t* blocked,
+                                            const float* uRight, float minX, float minY, float maxX, float maxY, const float* scaleFactors,
+                                            int nlevels, float mbf, float mb, const float* cam, const float* Tcw, const float* Tlw,
+                                            const float* Trl, int m, const uint8_t* hasMp, const uint8_t* outlier, const int32_t* octave,
+                                            const float* angle, const float* worldPos, const uint8_t* mpDesc, const int32_t* obs, float th,
+                                            int bMono, int32_t* lastOfFeature) {
+    World w;
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    const float intr[8] = {cam[0], cam[1], cam[2], cam[3], 0.f, 0.f, 0.f, 0.f}, unit[8] = {1.f, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    w.cams.emplace_back(makeCamera(0, intr));
+    w.cams.emplace_back(makeCamera(0, unit));
+    MapPoint old;
+    old.nObs = 1;
+    Frame Cur, Last;
+    fillRealFrame(Cur, w.cams[0].get(), w.cams[1].get(), &old, kps, desc, n, nleft, blocked, uRight, minX, minY, maxX, maxY, scaleFactors, nlevels);
+    Cur.mbf = mbf; Cur.mb = mb;
+    Cur.SetPose(mat44(Tcw));
+    if (Trl) Cur.mTrl = mat44(Trl).rowRange(0, 3).clone();       // Frame::mTrl is 3 x 4
+    Last.N = m;
+    Last.SetPose(mat44(Tlw));
+    Last.Nleft = -1;
+    Last.mvKeys.resize(m);
+    for (int i = 0; i < m; ++i) { Last.mvKeys[i].octave = octave[i]; Last.mvKeys[i].angle = angle[i]; }
+    Last.mvKeysUn = Last.mvKeys;
+    Last.mvbOutlier.resize(m);
+    std::vector<std::unique_ptr<MapPoint>> mps(m);
+    Last.mvpMapPoints.assign(m, static_cast<MapPoint*>(nullptr));
+    for (int i = 0; i < m; ++i) {
+        mps[i].reset(new MapPoint());
+        Last.mvbOutlier[i] = outlier[i] != 0;
+        mps[i]->SetWorldPos(vec3(worldPos + 3 * (size_t)i));
+        mps[i]->mDescriptor = descRow(mpDesc + 32 * (size_t)i);
+        mps[i]->nObs = obs[i];
+        mps[i]->mbBad = false;
+        mps[i]->mpReplaced = nullptr;
+        if (hasMp[i]) Last.mvpMapPoints[i] = mps[i].get();
+    }
+    const int nm = matcher.SearchByProjection(Cur, Last, th, bMono != 0);
+    for (int i = 0; i < n; ++i) {
+        lastOfFeature[i] = -1;
+        MapPoint* q = Cur.mvpMapPoints[i];
+        if (q && q != &old)
+            for (int k = 0; k < m; ++k) if (mps[k].get() == q) { lastOfFeature[i] = k; break; }
+    }
+    return nm;
+}
+}
+
+// ---- the keyframe-side searches on real KeyFrames (the reference's constructor, its own grid copy, IsInImage, GetFeaturesInArea, pose
+// accessors) and real MapPoints (their own PredictScale, distance invariance, observations); records as in refshim/ref_matcher_capi.cc
+namespace {
+struct KfInput {
+    const KpPod* kps; const uint8_t* desc; int n, nleft; const uint8_t* blocked; const float* uRight;
+    float minX, minY, maxX, maxY; const float* scaleFactors; const float* invLevelSigma2; int nlevels;
+    float cam[4]; float mbf; float logScaleFactor; const float* Tcw;
+};
+struct KfPoints {
+    int m; const uint8_t* null; const uint8_t* bad; const uint8_t* flagged; const float* worldPos; const float* normal;
+    const float* minDist; const float* maxDist; const uint8_t* desc;
+};
+struct Points {
+    std::vector<std::unique_ptr<MapPoint>> own;
+    std::vector<MapPoint*> vp;               // NULL where the test says so
+    int indexOf(const MapPoint* p) const {
+        for (size_t k = 0; k < own.size(); ++k) if (own[k].get() == p) return (int)k;
+        return -1;
+    }
+};
+void fillRealPoints(Points& P, const KfPoints& in) {
+    P.own.resize(in.m);
+    P.vp.assign(in.m, static_cast<MapPoint*>(nullptr));
+    for (int i = 0; i < in.m; ++i) {
+        P.own[i].reset(new MapPoint());
+        MapPoint& p = *P.own[i];
+        p.mbBad = in.bad && in.bad[i];
+        p.SetWorldPos(vec3(in.worldPos + 3 * (size_t)i));
+        p.mNormalVector = vec3(in.normal + 3 * (size_t)i);
+        p.mNormalVectorx = cv::Matx31f(in.normal[3 * i], in.normal[3 * i + 1], in.normal[3 * i + 2]);
+        p.mfMinDistance = in.minDist[i]; p.mfMaxDistance = in.maxDist[i];
+        p.mDescriptor = descRow(in.desc + 32 * (size_t)i);
+        p.nObs = 1;
+        if (!(in.null && in.null[i])) P.vp[i] = &p;
+    }
+}
+// a reference Frame from a KfInput: intrinsics are statics of Frame (Frame.cc:152-157), the keyframe copies them
+void fillRealFrameFromInput(Frame& F, World& w, const KfInput& in, MapPoint* old) {
+    const float intr[8] = {in.cam[0], in.cam[1], in.cam[2], in.cam[3], 0.f, 0.f, 0.f, 0.f};
+    w.cams.emplace_back(makeCamera(0, intr));
+    GeometricCamera* cam = w.cams.back().get();
+    fillRealFrame(F, cam, cam, old, in.kps, in.desc, in.n, in.nleft, in.blocked, in.uRight, in.minX, in.minY, in.maxX, in.maxY,
+                  in.scaleFactors, in.nlevels);
+    Frame::fx = in.cam[0]; Frame::fy = in.cam[1]; Frame::cx = in.cam[2]; Frame::cy = in.cam[3];
+    Frame::invfx = 1.0f / in.cam[0]; Frame::invfy = 1.0f / in.cam[1];
+    F.mbf = in.mbf; F.mb = in.mbf / in.cam[0];
+    F.mfLogScaleFactor = in.logScaleFactor;
+    if (in.invLevelSigma2) F.mvInvLevelSigma2.assign(in.invLevelSigma2, in.invLevelSigma2 + in.nlevels);
+    F.mTlr = cv::Mat::eye(4, 4, CV_32F);
+    F.SetPose(mat44(in.Tcw));
+}
+// KeyFrame(F, map, db); blocked features get an occupant MapPoint that observes the keyframe there
+KeyFrame* makeRealKeyFrame(World& w, const KfInput& in, std::vector<std::unique_ptr<MapPoint>>& occupants) {
+    Frame F;
+    fillRealFrameFromInput(F, w, in, nullptr);
+    KeyFrame* K = new KeyFrame(F, &w.map, &w.db);
+    w.kfs.emplace_back(K);
+    for (int i = 0; i < in.n; ++i)
+        if (in.blocked && in.blocked[i]) {
+            occupants.emplace_back(new MapPoint());
+            occupants.back()->AddObservation(K, (size_t)i);
+            K->AddMapPoint(occupants.back().get(), (size_t)i);
+        }
+    return K;
+}
+}  // namespace
+
+extern "C" {
+// SearchByProjection(KeyFrame* pKF, cv::Mat Scw, vpPoints, vpMatched, th, ratioHamming) (src/ORBmatcher.cc:473-585)
+int orbslam3_search_by_projection_sim3(const KfInput* in, const float* Scw, const KfPoints* P, int th, float ratioHamming, int32_t* pointOfFeature) {
+    World w;
+    ORBmatcher matcher(0.9f, true);
+    std::vector<std::unique_ptr<MapPoint>> occ;
+    KeyFrame* K = makeRealKeyFrame(w, *in, occ);
+    Points pts;
+    fillRealPoints(pts, *P);
+    std::vector<MapPoint*> vpMatched = K->GetMapPointMatches();
+    for (int i = 0; i < P->m; ++i) if (P->flagged && P->flagged[i]) vpMatched.push_back(pts.own[i].get());
+    const int nm = matcher.SearchByProjection(K, mat44(Scw), pts.vp, vpMatched, th, ratioHamming);
+    for (int i = 0; i < in->n; ++i) pointOfFeature[i] = vpMatched[i] ? pts.indexOf(vpMatched[i]) : -1;
+    return nm;
+}
+
+// SearchBySim3(pKF1, pKF2, vpMatches12, s12, R12, t12, th) (src/ORBmatcher.cc:1947-2171)
+int orbslam3_search_by_sim3(const KfInput* in1, const KfInput* in2, const KfPoints* P1, const KfPoints* P2, float s12, const float* R12,
+                            const float* t12, float th, int32_t* matches12) {
+    World w;
+    ORBmatcher matcher(0.9f, true);
+    std::vector<std::unique_ptr<MapPoint>> occ;
+    KfInput a = *in1, b = *in2;
+    a.blocked = nullptr; b.blocked = nullptr;                  // the keyframes' MapPoints are P1 / P2 themselves
+    KeyFrame* K1 = makeRealKeyFrame(w, a, occ);
+    KeyFrame* K2 = makeRealKeyFrame(w, b, occ);
+    Points p1, p2;
+    fillRealPoints(p1, *P1);
+    fillRealPoints(p2, *P2);
+    for (int i = 0; i < in1->n; ++i) if (p1.vp[i]) K1->AddMapPoint(p1.vp[i], (size_t)i);
+    for (int i = 0; i < in2->n; ++i) if (p2.vp[i]) K2->AddMapPoint(p2.vp[i], (size_t)i);
+    std::vector<int> marked;
+    for (int i = 0; i < in2->n; ++i) if (P2->flagged && P2->flagged[i]) marked.push_back(i);
+    std::vector<std::unique_ptr<MapPoint>> holders(in1->n);
+    std::vector<MapPoint*> vpMatches12(in1->n, static_cast<MapPoint*>(nullptr));
+    size_t k = 0;
+    for (int i = 0; i < in1->n; ++i)
+        if (P1->flagged && P1->flagged[i]) {
+            holders[i].reset(new MapPoint());
+            if (k < marked.size()) holders[i]->AddObservation(K2, (size_t)marked[k]);
+            ++k;
+            vpMatches12[i] = holders[i].get();
+        }
+    cv::Mat R(3, 3, CV_32F);
+    memcpy(R.data, R12, 36);
+    const int nFound = matcher.SearchBySim3(K1, K2, vpMatches12, s12, R, vec3(t12), th);
+    for (int i = 0; i < in1->n; ++i) matches12[i] = vpMatches12[i] ? p2.indexOf(vpMatches12[i]) : -1;
+    return nFound;
+}
+
+// SearchByProjection(Frame& CurrentFrame, KeyFrame* pKF, sAlreadyFound, th, ORBdist) (src/ORBmatcher.cc:2391-2510)
+int orbslam3_search_by_projection_reloc(int checkOri, const KfInput* cur, const KfPoints* P, const float* kfAngle, float th, int ORBdist,
+                                        int32_t* pointOfFeature) {
+    World w;
+    ORBmatcher matcher(0.9f, checkOri != 0);
+    MapPoint old;
+    old.nObs = 1;
+    Frame F;
+    fillRealFrameFromInput(F, w, *cur, &old);
+    // the keyframe: P->m features that only carry an angle, and the MapPoints
+    Frame G;
+    G.N = P->m; G.Nleft = -1; G.Nright = -1;
+    G.mvKeys.resize(P->m);
+    for (int i = 0; i < P->m; ++i) G.mvKeys[i].angle = kfAngle[i];
+    G.mvKeysUn = G.mvKeys;
+    G.mvuRight.assign(P->m, -1.f);
+    G.mvDepth.assign(P->m, -1.f);
+    G.mvpMapPoints.assign(P->m, static_cast<MapPoint*>(nullptr));
+    G.mDescriptors = cv::Mat(P->m > 0 ? P->m : 1, 32, CV_8U);
+    G.mTlr = cv::Mat::eye(4, 4, CV_32F);
+    G.mpCamera = F.mpCamera;
+    G.SetPose(cv::Mat::eye(4, 4, CV_32F));
+    KeyFrame* K = new KeyFrame(G, &w.map, &w.db);
+    w.kfs.emplace_back(K);
+    Points pts;
+    fillRealPoints(pts, *P);
+    for (int i = 0; i < P->m; ++i) if (pts.vp[i]) K->AddMapPoint(pts.vp[i], (size_t)i);
+    std::set<MapPoint*> found;
+    for (int i = 0; i < P->m; ++i) if (P->flagged && P->flagged[i]) found.insert(pts.own[i].get());
+    const int nm = matcher.SearchByProjection(F, K, found, th, ORBdist);
+    for (int i = 0; i < cur->n; ++i) {
+        MapPoint* q = F.mvpMapPoints[i];
+        pointOfFeature[i] = (q && q != &old) ? pts.indexOf(q) : -1;
+    }
+    return nm;
 }
 }

@@ -567,6 +567,27 @@ def _ref_objects_lib():
     return _ref_objects
 
 
+class objects_matcher_library:
+    """with objects_matcher_library(): the ref_search_by_projection_* calls below run on liborbslam3_objects.so - the same C names,
+    but real reference Frames (their own grid) and real MapPoints instead of the stand-ins of orbslam3_standin.h."""
+
+    def __enter__(self):
+        global _ref_matcher
+        L = _ref_objects_lib()
+        if not getattr(L, "_matcher_types_set", False):
+            L.orbslam3_search_by_projection_mappoints.argtypes = [_F, _P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I] + \
+                [_P] * 14 + [_F, _I, _F, _P]
+            L._matcher_types_set = True
+        self.saved = ref_matcher() if ref_matcher_available() else None
+        _ref_matcher = L
+        return self
+
+    def __exit__(self, *exc):
+        global _ref_matcher
+        _ref_matcher = self.saved
+        return False
+
+
 def _kf_arrays(d, keep):
     f = lambda a: np.ascontiguousarray(a, np.float32)
     arrs = dict(kps=np.ascontiguousarray(d["kps"]), desc=np.ascontiguousarray(d["desc"], np.uint8),

@@ -72,3 +72,91 @@ def test_search_by_bow_between_real_keyframes(name):
     oa2b, _, on = ob.search_bow(c["d1"], c["fv1"], c["mp1"], c["k1"]["angle"], c["d2"], c["fv2"], c["mp2"], c["k2"]["angle"], 0.8,
                                 c["check_ori"], strict=True)
     assert n == on and np.array_equal(a2b, oa2b) and n > 50
+
+
+@pytest.mark.parametrize("name", list(__import__("proj_cases").MP_CASES))
+def test_search_by_projection_local_points_on_real_frames(name):
+    """SearchByProjection(Frame&, vpMapPoints, ...) :44 (Tracking::SearchLocalPoints): a reference Frame whose 64 x 48 grid its own
+    AssignFeaturesToGrid filled, reference MapPoints carrying the tracking fields Frame::isInFrustum would have written."""
+    import os
+    import proj_cases as pc
+    from common import GOLDEN
+    from test_proj_oracle import run_mp
+    c = pc.mp_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    with ob.objects_matcher_library():
+        n, res = ob.ref_search_by_projection_mappoints(c["F"], c["mp"], c["th"], c["nnratio"], c["far"], c["th_far"])
+    ores, on, _, _ = run_mp(c, ob.search_by_projection)
+    assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["mappoint_of_feature"])
+
+
+@pytest.mark.parametrize("name", list(__import__("proj_cases").LF_CASES))
+def test_search_by_projection_last_frame_on_real_frames(name):
+    """SearchByProjection(CurrentFrame, LastFrame, th, bMono) :2173 (Tracking::TrackWithMotionModel) on two reference Frames (their
+    own SetPose / UpdatePoseMatrices, grid and GetFeaturesInArea) and reference MapPoints (SetWorldPos / GetWorldPos)."""
+    import os
+    import proj_cases as pc
+    from common import GOLDEN
+    from test_proj_oracle import run_lf
+    c = pc.lf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    Trl = np.eye(4, dtype=np.float32)
+    Trl[:3, 3] = (-0.101, 0.0, 0.0)
+    with ob.objects_matcher_library():
+        n, res = ob.ref_search_by_projection_lastframe(c["Cur"], c["last"], c["Tcw"], c["th"], c["fb"], pc.CAM, Trl, c["ori"])
+    ores, on, _, _ = run_lf(c, ob.search_by_projection)
+    assert n == on == int(g["n"])
+    assert np.array_equal(res, np.where(ores >= 0, ores, -1))
+
+
+@pytest.mark.parametrize("name", [k for k in __import__("proj_cases").KF_CASES if __import__("proj_cases").kf_inputs(k)["kind"] == "sim3"])
+def test_search_by_projection_sim3_on_real_keyframes(name):
+    """SearchByProjection(KeyFrame*, Scw, vpPoints, vpMatched, th, ratioHamming) :473 (loop closing): a reference KeyFrame (grid copied
+    by its constructor, its own IsInImage / GetFeaturesInArea) and reference MapPoints (their own PredictScale and distance bounds)."""
+    import os
+    import proj_cases as pc
+    from common import GOLDEN
+    from test_proj_oracle import run_kf
+    c = pc.kf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    ores, on, _, _ = run_kf(c, ob.search_by_projection)
+    with ob.objects_matcher_library():
+        n, res = ob.ref_search_by_projection_sim3(c["KF"], c["pts"], c["Scw"], c["th"], c["ratio"], pc.CAM, pc.LOG_SF)
+    assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["point_of_feature"])
+
+
+@pytest.mark.parametrize("name", list(__import__("proj_cases").SIM3_CASES))
+def test_search_by_sim3_on_real_keyframes(name):
+    import os
+    import proj_cases as pc
+    from common import GOLDEN
+    from test_proj_oracle import run_sim3
+    c = pc.sim3_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    with ob.objects_matcher_library():
+        n, m12 = ob.ref_search_by_sim3(c, pc.CAM, pc.LOG_SF)
+    vn1, vn2, pairs, on = run_sim3(c, ob.search_by_projection)
+    want = np.full(c["KF1"].n, -1, np.int32)
+    for i1, i2 in pairs:
+        want[i1] = i2
+    assert n == on == int(g["n"]) and np.array_equal(m12, want) and n > 100
+
+
+def test_search_by_projection_relocalisation_on_real_objects():
+    """SearchByProjection(CurrentFrame, pKF, sAlreadyFound, th, ORBdist) :2391 with a reference Frame, KeyFrame and MapPoints."""
+    import proj_cases as pc
+    from orbfe import projection as pj
+    from test_proj_oracle import owners
+    c = pc.lf_inputs("proj_last_mono")
+    rng = np.random.default_rng(77)
+    last, m = c["last"], len(c["last"]["has_mp"])
+    dist = np.sqrt((last["world_pos"].astype(np.float64) ** 2).sum(1)).astype(np.float32)
+    kf = dict(has_mp=last["has_mp"], bad=rng.random(m) < 0.03, already_found=rng.random(m) < 0.2, world_pos=last["world_pos"],
+              min_dist=(dist * rng.uniform(0.3, 1.05, m)).astype(np.float32), max_dist=(dist * rng.uniform(0.95, 4.0, m)).astype(np.float32),
+              angle=last["angle"], desc=last["desc"])
+    q, owner = pj.queries_from_keyframe(c["Cur"], kf, c["Tcw"], 10.0, c["project"], np.float32(np.log(1.2)))
+    for orbdist in (100, 64):
+        with ob.objects_matcher_library():
+            n, res = ob.ref_search_by_projection_reloc(c["Cur"], kf, c["Tcw"], 10.0, orbdist, pc.CAM, np.float32(np.log(1.2)))
+        assign, choice, on = ob.search_by_projection(c["Cur"], q, 0, orbdist, 0.9, False, True)
+        assert n == on and n > 60 and np.array_equal(res, np.where(assign >= 0, owners(assign, owner), -1))
