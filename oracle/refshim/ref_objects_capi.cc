@@ -488,3 +488,148 @@ int orbslam3_search_by_projection_reloc(int checkOri, const KfInput* cur, const 
     return nm;
 }
 }
+
+extern "C" {
+// Fuse(KeyFrame* pKF, vpMapPoints, th, bRight) (src/ORBmatcher.cc:1629-1821; Scw == NULL; P.flagged = the point is already observed by
+// pKF) and Fuse(KeyFrame* pKF, cv::Mat Scw, vpPoints, th, vpReplacePoint) (:1823-1945; P.flagged = the point is among pKF's MapPoints).
+// The map surgery is the reference's own (MapPoint::AddObservation, Replace with its observation transfer, KeyFrame::AddMapPoint /
+// ReplaceMapPointMatch); featureOfPoint[m] is read off the state it leaves: the feature where point i now sits in pKF, or where the
+// MapPoint that replaced it sits, or (Scw form) where the reported vpReplacePoint sits; -1 = not fused.  Returns nFused.
+int orbslam3_fuse(const KfInput* in, const float* Scw, const KfPoints* P, float th, int bRight, int32_t* featureOfPoint) {
+    World w;
+    ORBmatcher matcher(0.9f, true);
+    std::vector<std::unique_ptr<MapPoint>> occ;
+    KeyFrame* K = makeRealKeyFrame(w, *in, occ);
+    long unsigned int nextId = 1;
+    for (auto& o : occ) { o->nObs = 1; o->mnId = nextId++; o->mpMap = &w.map; o->mDescriptor = descRow(in->desc); }
+    Points pts;
+    fillRealPoints(pts, *P);
+    for (auto& p : pts.own) { p->mnId = nextId++; p->mpMap = &w.map; }
+    auto featureIn = [&](MapPoint* p) {
+        const std::tuple<int, int> ix = p->GetIndexInKeyFrame(K);
+        return std::get<0>(ix) >= 0 ? std::get<0>(ix) : std::get<1>(ix);
+    };
+    int nFused;
+    std::vector<MapPoint*> vpReplace(P->m, static_cast<MapPoint*>(nullptr));
+    if (Scw) {
+        // "among pKF's MapPoints" without taking one of the test's features: entries behind the keyframe's own N
+        for (int i = 0; i < P->m; ++i) if (P->flagged && P->flagged[i]) K->mvpMapPoints.push_back(pts.own[i].get());
+        nFused = matcher.Fuse(K, mat44(Scw), pts.vp, th, vpReplace);
+    } else {
+        for (int i = 0; i < P->m; ++i)       // "already in this keyframe": an observation at a feature outside the arrays
+            if (P->flagged && P->flagged[i]) pts.own[i]->mObservations[K] = std::tuple<int, int>(-1, -1);
+        nFused = matcher.Fuse(K, pts.vp, th, bRight != 0);
+    }
+    for (int i = 0; i < P->m; ++i) {
+        MapPoint* p = pts.own[i].get();
+        int f = -1;
+        if (!(P->flagged && P->flagged[i]) || Scw) f = p->IsInKeyFrame(K) ? featureIn(p) : -1;
+        if (Scw && P->flagged && P->flagged[i]) f = -1;            // it sat behind N before the call, not at a feature
+        if (f < 0 && p->isBad() && p->GetReplaced() && !(P->bad && P->bad[i])) f = featureIn(p->GetReplaced());
+        if (f < 0 && vpReplace[i]) f = featureIn(vpReplace[i]);
+        featureOfPoint[i] = f;
+    }
+    return nFused;
+}
+}
+
+namespace {
+// a keyframe / frame that only carries what SearchByBoW reads: features, descriptors, the feature vector, MapPoints by mask
+void fillBowFrame(Frame& F, const KpPod* kps, const uint8_t* desc, int n, int nleft, const uint32_t* nodes, const int32_t* off,
+                  const int32_t* idx, int nnodes, GeometricCamera* cam, GeometricCamera* rig) {
+    std::vector<cv::KeyPoint> all(n);
+    if (n) memcpy((void*)all.data(), kps, sizeof(KpPod) * (size_t)n);
+    F.N = n; F.Nleft = nleft; F.Nright = nleft == -1 ? -1 : n - nleft;
+    if (nleft == -1) { F.mvKeys = all; F.mvKeysUn = all; }
+    else { F.mvKeys.assign(all.begin(), all.begin() + nleft); F.mvKeysRight.assign(all.begin() + nleft, all.end()); F.mvKeysUn = F.mvKeys; }
+    cv::Mat d(n > 0 ? n : 1, 32, CV_8U);
+    if (n > 0) memcpy(d.data, desc, 32 * (size_t)n);
+    F.mDescriptors = n > 0 ? d : d.rowRange(0, 0);
+    for (int k = 0; k < nnodes; ++k)
+        for (int j = off[k]; j < off[k + 1]; ++j) F.mFeatVec.addFeature(nodes[k], (unsigned)idx[j]);
+    F.mvpMapPoints.assign(n, static_cast<MapPoint*>(nullptr));
+    F.mvuRight.assign(n, -1.f);
+    F.mvDepth.assign(n, -1.f);
+    F.mpCamera = cam;
+    F.mpCamera2 = nleft == -1 ? nullptr : rig;
+    F.mTlr = cv::Mat::eye(4, 4, CV_32F);
+    F.SetPose(cv::Mat::eye(4, 4, CV_32F));
+}
+}  // namespace
+
+extern "C" {
+// SearchByBoW.  form 0: (KeyFrame* A, Frame& B, vpMapPointMatches) (src/ORBmatcher.cc:269-471);  form 1: (KeyFrame* A, KeyFrame* B,
+// vpMatches12) (:823-963).  Real KeyFrames (GetMapPointMatches, mFeatVec copied by the constructor), a real Frame, real MapPoints.
+int orbslam3_search_bow(int form, float nnratio, int checkOri, const KpPod* kpsA, const uint8_t* descA, int nA, const uint8_t* maskA,
+                        const uint32_t* nodesA, const int32_t* offA, const int32_t* idxA, int nnodesA, const KpPod* kpsB,
+                        const uint8_t* descB, int nB, const uint8_t* maskB, const uint32_t* nodesB, const int32_t* offB, const int32_t* idxB,
+                        int nnodesB, int nleftB, int32_t* a2b, int32_t* b2a) {
+    World w;
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    const float unit[8] = {1.f, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    w.cams.emplace_back(makeCamera(0, unit));
+    w.cams.emplace_back(makeCamera(0, unit));
+    GeometricCamera *cam = w.cams[0].get(), *rig = w.cams[1].get();
+    std::vector<std::unique_ptr<MapPoint>> pool;
+    auto populate = [&](KeyFrame* K, const uint8_t* mask, int n) {
+        std::vector<MapPoint*> v(n, static_cast<MapPoint*>(nullptr));
+        for (int i = 0; i < n; ++i)
+            if (mask && mask[i]) { pool.emplace_back(new MapPoint()); v[i] = pool.back().get(); K->AddMapPoint(v[i], (size_t)i); }
+        return v;
+    };
+    for (int i = 0; i < nA; ++i) a2b[i] = -1;
+    for (int i = 0; i < nB; ++i) b2a[i] = -1;
+    // with a two-camera frame the reference reads the keyframe's features through mvKeys / mvKeysRight as well: every feature of A
+    // belongs to its left camera (NLeft = nA), as in the stand-in wrapper
+    Frame FA;
+    fillBowFrame(FA, kpsA, descA, nA, (form == 0 && nleftB != -1) ? nA : -1, nodesA, offA, idxA, nnodesA, cam, rig);
+    KeyFrame* A = new KeyFrame(FA, &w.map, &w.db);
+    w.kfs.emplace_back(A);
+    const std::vector<MapPoint*> ptsA = populate(A, maskA, nA);
+    int n;
+    if (form == 0) {
+        Frame B;
+        fillBowFrame(B, kpsB, descB, nB, nleftB, nodesB, offB, idxB, nnodesB, cam, rig);
+        std::vector<MapPoint*> out;
+        n = matcher.SearchByBoW(A, B, out);
+        for (int j = 0; j < (int)out.size() && j < nB; ++j)
+            if (out[j])
+                for (int i = 0; i < nA; ++i)
+                    if (ptsA[i] == out[j]) { b2a[j] = i; a2b[i] = j; break; }
+    } else {
+        Frame FB;
+        fillBowFrame(FB, kpsB, descB, nB, -1, nodesB, offB, idxB, nnodesB, cam, rig);
+        KeyFrame* B = new KeyFrame(FB, &w.map, &w.db);
+        w.kfs.emplace_back(B);
+        const std::vector<MapPoint*> ptsB = populate(B, maskB, nB);
+        std::vector<MapPoint*> out;
+        n = matcher.SearchByBoW(A, B, out);
+        for (int i = 0; i < (int)out.size() && i < nA; ++i)
+            if (out[i])
+                for (int j = 0; j < nB; ++j)
+                    if (ptsB[j] == out[i]) { a2b[i] = j; b2a[j] = i; break; }
+    }
+    return n;
+}
+
+// SearchForInitialization(F1, F2, vbPrevMatched, vnMatches12, windowSize) (src/ORBmatcher.cc:706-821) on two real Frames.
+int orbslam3_search_for_initialization(float nnratio, int checkOri, const KpPod* kps1, const uint8_t* desc1, int n1, const KpPod* kps2,
+                                       const uint8_t* desc2, int n2, float minX, float minY, float maxX, float maxY, float* prevMatched,
+                                       int windowSize, int32_t* matches12) {
+    World w;
+    ORBmatcher matcher(nnratio, checkOri != 0);
+    const float unit[8] = {1.f, 1.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    w.cams.emplace_back(makeCamera(0, unit));
+    GeometricCamera* cam = w.cams[0].get();
+    const float one = 1.f;
+    Frame F1, F2;
+    fillRealFrame(F1, cam, cam, nullptr, kps1, desc1, n1, -1, nullptr, nullptr, minX, minY, maxX, maxY, &one, 1);
+    fillRealFrame(F2, cam, cam, nullptr, kps2, desc2, n2, -1, nullptr, nullptr, minX, minY, maxX, maxY, &one, 1);
+    std::vector<cv::Point2f> prev(n1);
+    for (int i = 0; i < n1; ++i) prev[i] = cv::Point2f(prevMatched[2 * i], prevMatched[2 * i + 1]);
+    std::vector<int> m12;
+    const int n = matcher.SearchForInitialization(F1, F2, prev, m12, windowSize);
+    for (int i = 0; i < n1; ++i) { matches12[i] = m12[i]; prevMatched[2 * i] = prev[i].x; prevMatched[2 * i + 1] = prev[i].y; }
+    return n;
+}
+}

@@ -478,7 +478,10 @@ def ref_matcher_available():
 
 
 def _load_matcher(path):
-    L = C.CDLL(path)
+    return _set_matcher_argtypes(C.CDLL(path))
+
+
+def _set_matcher_argtypes(L):
     L.orbslam3_search_bow.argtypes = [_I, _F, _I, _P, _P, _I, _P, _P, _P, _P, _I, _P, _P, _I, _P, _P, _P, _P, _I, _I, _P, _P]
     L.orbslam3_search_for_initialization.argtypes = [_F, _I, _P, _P, _I, _P, _P, _I, _F, _F, _F, _F, _P, _I, _P]
     L.orbslam3_search_by_projection_mappoints.argtypes = [_F, _P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I] + [_P] * 14 + \
@@ -575,8 +578,7 @@ class objects_matcher_library:
         global _ref_matcher
         L = _ref_objects_lib()
         if not getattr(L, "_matcher_types_set", False):
-            L.orbslam3_search_by_projection_mappoints.argtypes = [_F, _P, _P, _I, _I, _P, _P, _P, _P, _F, _F, _F, _F, _P, _I, _I] + \
-                [_P] * 14 + [_F, _I, _F, _P]
+            _set_matcher_argtypes(L)
             L._matcher_types_set = True
         self.saved = ref_matcher() if ref_matcher_available() else None
         _ref_matcher = L

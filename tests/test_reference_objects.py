@@ -160,3 +160,54 @@ def test_search_by_projection_relocalisation_on_real_objects():
             n, res = ob.ref_search_by_projection_reloc(c["Cur"], kf, c["Tcw"], 10.0, orbdist, pc.CAM, np.float32(np.log(1.2)))
         assign, choice, on = ob.search_by_projection(c["Cur"], q, 0, orbdist, 0.9, False, True)
         assert n == on and n > 60 and np.array_equal(res, np.where(assign >= 0, owners(assign, owner), -1))
+
+
+@pytest.mark.parametrize("name", [k for k in __import__("proj_cases").KF_CASES if __import__("proj_cases").kf_inputs(k)["kind"] != "sim3"])
+def test_fuse_on_real_keyframes(name):
+    """Fuse(pKF, vpMapPoints, th, bRight) :1629 and Fuse(pKF, Scw, vpPoints, th, vpReplacePoint) :1823 with the reference's own map
+    surgery (MapPoint::AddObservation / Replace, KeyFrame::AddMapPoint / ReplaceMapPointMatch): the feature every point ends up at."""
+    import os
+    import proj_cases as pc
+    from common import GOLDEN
+    from test_proj_oracle import run_kf
+    c = pc.kf_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    ores, on, _, _ = run_kf(c, ob.search_by_projection)
+    sim3 = c["kind"] == "fuse_sim3"
+    with ob.objects_matcher_library():
+        n, res = ob.ref_fuse(c["KF"], c["pts"], None if sim3 else c["Tcw"], c["Scw"] if sim3 else None, c["th"], c["kind"] == "fuse_right",
+                             pc.CAM, pc.LOG_SF)
+    assert n == on == int(g["n"]) and np.array_equal(res, ores) and np.array_equal(res, g["feature_of_point"])
+
+
+@pytest.mark.parametrize("name", list(mc.BOW_CASES))
+def test_search_by_bow_on_real_objects(name):
+    """Both SearchByBoW overloads (:269 keyframe vs frame, with the left / right split of a two-camera frame; :823 keyframe vs
+    keyframe) on reference KeyFrames / Frame / MapPoints, against the oracle and the golden vectors."""
+    import os
+    from common import GOLDEN
+    from test_match_oracle import extract
+    c = mc.bow_inputs(name, extract)
+    g = np.load(os.path.join(GOLDEN, f"match_{name}.npz"))
+    ang1, ang2 = c["k1"]["angle"], c["k2"]["angle"]
+    with ob.objects_matcher_library():
+        a2b, b2a, n = ob.ref_search_bow(0, c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], None, ang2, 0.7, c["check_ori"], c["nleft"])
+    oa2b, ob2a, on = ob.search_bow(c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], None, ang2, 0.7, c["check_ori"], strict=False,
+                                   nleft=c["nleft"])
+    assert n == on == int(g["n_kf_f"]) and np.array_equal(b2a, ob2a) and np.array_equal(b2a, g["kf_f"]) and n > 100
+    with ob.objects_matcher_library():
+        a2b, b2a, n = ob.ref_search_bow(1, c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], c["mp2"], ang2, 0.8, c["check_ori"])
+    oa2b, ob2a, on = ob.search_bow(c["d1"], c["fv1"], c["mp1"], ang1, c["d2"], c["fv2"], c["mp2"], ang2, 0.8, c["check_ori"], strict=True)
+    assert n == on == int(g["n_kf_kf"]) and np.array_equal(a2b, oa2b) and np.array_equal(a2b, g["kf_kf"])
+
+
+@pytest.mark.parametrize("name", list(__import__("proj_cases").INIT_CASES))
+def test_search_for_initialization_on_real_frames(name):
+    import os
+    import proj_cases as pc
+    from common import GOLDEN
+    c = pc.init_inputs(name)
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    with ob.objects_matcher_library():
+        n, m12, prev = ob.ref_search_for_initialization(c["F1"].kps, c["F1"].desc, c["F2"], c["prev"], c["win"], c["nnratio"], c["ori"])
+    assert n == int(g["n"]) and np.array_equal(m12, g["vnMatches12"]) and np.array_equal(prev, g["prev_matched"])
