@@ -15,17 +15,13 @@
 #include <vector>
 
 // the wrappers set state the reference keeps private / protected (Frame::AssignFeaturesToGrid, MapPoint::mDescriptor, mbBad,
-// mWorldPos): access only, class layouts are unchanged
-#define private public
-#define protected public
+// mObservations): refshim/access_public.h, force-included ahead of everything by the Makefile, opens the access (layouts unchanged)
 #include "ORBmatcher.h"
 #include "KeyFrame.h"
 #include "KeyFrameDatabase.h"
 #include "Map.h"
 #include "Pinhole.h"
 #include "KannalaBrandt8.h"
-#undef private
-#undef protected
 
 #include <cassert>
 #include "../cpu_ref/match_ref.h"
