@@ -10,6 +10,9 @@ export PYTHONUNBUFFERED=1
 
 timeout 1500 python -m pytest tests -m gpu -q -x > $out/${tag}_pytest.txt 2>&1
 tail -3 $out/${tag}_pytest.txt
+# written in round 2 after the GPU budget was spent: the shim's object layer on the reference's real objects (gated until seen green)
+ORBFE_TEST_REAL_OBJECTS=1 timeout 300 python -m pytest tests/test_shim_real_objects.py -m gpu -q > $out/${tag}_pytest_real_objects.txt 2>&1
+tail -3 $out/${tag}_pytest_real_objects.txt
 
 timeout 600 python bench.py > $out/${tag}_bench.json 2> $out/${tag}_bench.err
 tail -c 600 $out/${tag}_bench.json
